@@ -1,0 +1,212 @@
+/*
+ * rbacknn.h — C-ABI of the B200-native RBAC-filtered kNN engine (librbacknn.so).
+ *
+ * Drop-in boundary for ONE hot path of rjzhb/VectorSearch-RBAC: the role / user permission
+ * prefilter fused with L2 / inner-product scoring and top-k selection that the reference runs
+ * as pgvector exact scans and IVFFlat index scans over role-partitioned tables and in its
+ * ground-truth computation.  Every entry point below names the reference interface it stands in
+ * for (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain C, no torch / C++ types in any signature; all sizes are explicit.
+ *   - the caller owns every host buffer it passes; the library copies what it keeps.
+ *   - no exceptions / longjmp cross this boundary: functions return 0 (RK_OK) or a negative
+ *     rk_status and leave a message for rk_last_error() (thread-local).  The reference reports the
+ *     same conditions through ereport(ERROR) (pgvector/src/vector.c:61-67, 102-113).
+ *   - there is NO CPU fallback: without a CUDA device rk_open() fails with RK_ERR_NO_DEVICE.
+ *   - an rk_index is immutable after rk_finalize(); any number of rk_scan handles (one per host
+ *     thread) may search it concurrently, like PostgreSQL backends each owning one IndexScanDesc
+ *     (pgvector/src/ivfflat.c:203 amcanparallel=false, one scan == one thread).
+ */
+#ifndef RBACKNN_H
+#define RBACKNN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RK_ABI_VERSION 1
+
+typedef struct rk_index rk_index;
+typedef struct rk_scan rk_scan;
+
+typedef enum rk_status {
+    RK_OK = 0,
+    RK_ERR_INVALID = -1,      /* bad argument (NULL, k out of range, ...)                         */
+    RK_ERR_DIM = -2,          /* "different vector dimensions %d and %d"  (vector.c:61-67)        */
+    RK_ERR_NONFINITE = -3,    /* NaN / Inf element in a vector            (vector.c:102-113)      */
+    RK_ERR_STATE = -4,        /* call order violated (e.g. search before rk_finalize)             */
+    RK_ERR_NO_DEVICE = -5,    /* no CUDA device / wrong architecture: the engine has no CPU path  */
+    RK_ERR_CUDA = -6,         /* a CUDA runtime call failed; message carries cudaGetErrorString   */
+    RK_ERR_NOMEM = -7,
+    RK_ERR_UNSUPPORTED = -8,  /* e.g. dim > RK_MAX_DIM                                            */
+    RK_ERR_NO_ORDER = -9      /* "cannot scan ivfflat index without order" (ivfscan.c:360-361)    */
+} rk_status;
+
+/* Distance operators.  RK_METRIC_L2 is SQL `<->` (l2_distance, vector.c:568-578: sqrt((double)
+ * fp32 sum)); RK_METRIC_IP is SQL `<#>` (vector_negative_inner_product, vector.c:626-636:
+ * -(double) fp32 sum).  Index scans order by opclass FUNCTION 1, i.e. the squared L2 sum widened to
+ * double (vector.c:584-594) — the same order as `<->`. */
+typedef enum rk_metric { RK_METRIC_L2 = 0, RK_METRIC_IP = 1 } rk_metric;
+
+/* How the permission prefilter is applied.
+ *   RK_FILTER_PARTITION  layout-faithful: user -> role set -> partition ids -> scan each partition,
+ *                        merge + dedup on tuple id (controller/baseline/prefilter/prefilter_role.py:
+ *                        120-189; prefilter_combination_role.py:122-161; controller/dynamic_partition/
+ *                        search.py:44-111,347-364).
+ *   RK_FILTER_BITMASK    one pass over the row store with the per-document role mask tested against
+ *                        the user's role mask inside the scan kernel — the RLS predicate of
+ *                        controller/baseline/pg_row_security/row_level_security.py:55-65.
+ *   RK_FILTER_NONE       no permission filter (plain pgvector scan). */
+typedef enum rk_filter { RK_FILTER_PARTITION = 0, RK_FILTER_BITMASK = 1, RK_FILTER_NONE = 2 } rk_filter;
+
+#define RK_MAX_DIM 2048   /* pgvector IVFFLAT_MAX_DIM is 2000 (pgvector/src/ivfflat.h:24)          */
+#define RK_MAX_K 1024     /* top-k limit of the GPU selection network                               */
+#define RK_MAX_LISTS 32768 /* IVFFLAT_MAX_LISTS (pgvector/src/ivfflat.h:44)                         */
+
+typedef struct rk_config {
+    int32_t abi_version;  /* RK_ABI_VERSION */
+    int32_t dim;          /* vector dimension, 1..RK_MAX_DIM (vector.h:11-17 `int16 dim`)           */
+    int32_t metric;       /* rk_metric */
+    int32_t device;       /* CUDA device ordinal */
+    int32_t k_max;        /* largest k any scan will ask for, 1..RK_MAX_K */
+    int32_t reserved[11];
+} rk_config;
+
+/* ---- lifecycle ------------------------------------------------------------------------------ */
+
+/* Stands in for opening the relation + index (RelationGetIndexScan / IvfflatGetMetaPageInfo,
+ * pgvector/src/ivfscan.c:252-255).  Returns NULL on failure (see rk_last_error()). */
+rk_index *rk_open(const rk_config *cfg);
+void rk_close(rk_index *ix);
+const char *rk_last_error(void);
+int rk_abi_version(void);
+
+/* ---- loading: what PostgreSQL's heap + catalog hold today ------------------------------------ */
+
+/* Append n rows of table `documentblocks` (controller/initialize_main_tables.py:52-63):
+ * x[n*dim] row-major fp32 (struct Vector payload, pgvector/src/vector.h:11-17), tid[n] the tuple
+ * id handed back by scans (block_id, or a packed ItemPointer), doc[n] the row's document_id.
+ * Rejects NaN/Inf like vector_in (vector.c:102-113). */
+int rk_load_rows(rk_index *ix, const float *x, const uint64_t *tid, const uint32_t *doc, size_t n);
+
+/* PermissionAssignment(role_id, document_id) pairs (initialize_main_tables.py:66-72). */
+int rk_set_doc_roles(rk_index *ix, const uint32_t *doc, const uint32_t *role, size_t n);
+/* UserRoles(user_id, role_id) pairs (initialize_main_tables.py:33-39). */
+int rk_set_user_roles(rk_index *ix, const uint32_t *user, const uint32_t *role, size_t n);
+
+/* One table documentblocks_role_<r> per role: rows whose document is granted to r
+ * (controller/baseline/prefilter/initialize_partitions.py:281-311). Partition id == role id. */
+int rk_build_role_partitions(rk_index *ix);
+/* One table per distinct sorted role set of a user, holding the de-duplicated union
+ * (initialize_partitions.py:549-555, 610-700). */
+int rk_build_combination_partitions(rk_index *ix);
+/* Dynamic-partition layout: documentblocks_partition_<p> (controller/dynamic_partition/
+ * load_result_to_database.py:207-219) and CombRolePartitions(comb_role INT[], partition_id)
+ * (:293-299).  `roles` must be sorted ascending like search.py:44-52 does. */
+int rk_define_partition(rk_index *ix, uint32_t part_id, const uint32_t *docs, size_t n);
+int rk_map_roleset_to_partitions(rk_index *ix, const uint32_t *roles, size_t nroles,
+                                 const uint32_t *parts, size_t nparts);
+
+/* Freeze the index: rows are ordered by document, uploaded to HBM, partitions become extent
+ * tables over the single row store, per-document and per-user role masks are built. */
+int rk_finalize(rk_index *ix);
+
+/* ---- IVFFlat (pgvector/src/ivfbuild.c, ivfkmeans.c, ivfscan.c) ------------------------------- */
+
+/* CREATE INDEX ... USING ivfflat (vector vector_l2_ops|vector_ip_ops) WITH (lists = L):
+ * sample max(10000, 50*L) rows (ivfbuild.c:404-441), k-means (ivfkmeans.c), assign every row to
+ * its nearest centre (ivfbuild.c:141-198), store rows list-contiguous (ivfbuild.c:251-310). */
+int rk_build_ivf(rk_index *ix, int lists, uint64_t seed);
+/* Same index from caller-supplied centres[lists*dim] (assignment + packing only). */
+int rk_build_ivf_from_centers(rk_index *ix, int lists, const float *centers);
+/* Introspection for tests: copies out centres and the row->list assignment. */
+int rk_ivf_info(const rk_index *ix, int *lists, float *centers, uint32_t *row_list /* by load order */);
+
+/* ---- scans: the IndexAmRoutine contract (pgvector/src/ivfflat.c:236-240, ivfflat.h:335-338) --- */
+
+typedef struct rk_scan_opts {
+    int32_t k;              /* LIMIT pushed into the scan; 1..k_max                                 */
+    int32_t probes;         /* ivfflat.probes; 0 = exact scan (SeqScan + top-N sort)                */
+    int32_t max_probes;     /* ivfflat.max_probes; > probes turns on iterative_scan=relaxed_order   */
+    int32_t filter;         /* rk_filter */
+    int32_t null_query;     /* ORDER BY vec <-> NULL: every distance is 0 (ivfscan.c:181-200)       */
+    int32_t reserved[3];
+} rk_scan_opts;
+
+/* ivfflatbeginscan (ivfscan.c:241-315): allocates scan state (result ring, device scratch). */
+rk_scan *rk_beginscan(rk_index *ix);
+/* ivfflatrescan (ivfscan.c:320-334) + the first-call work of ivfflatgettuple (:355-373):
+ * binds the ORDER BY operand `q` (borrowed for this call only) and the user whose permissions
+ * filter the rows, and runs the scan on the GPU.  An unknown user has no roles and gets an empty
+ * result (prefilter_role.py:120-124). */
+int rk_rescan(rk_scan *sc, const float *q, int32_t q_dim, uint32_t user_id, const rk_scan_opts *o);
+/* ivfflatgettuple (ivfscan.c:339-389): next tuple in ascending distance.  1 = *tid / *distance
+ * set (distance is what `vector <-> q` / `vector <#> q` evaluates to, float8); 0 = exhausted
+ * (after the last probe batch in iterative mode, ivfscan.c:375-381); <0 = error. */
+int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *distance);
+/* ivfflatendscan (ivfscan.c:394-406). */
+void rk_endscan(rk_scan *sc);
+
+/* Throughput entry point: nq independent scans in one persistent launch.  Equivalent to nq
+ * (rk_rescan + k x rk_gettuple) sequences; replaces the per-query loop of
+ * basic_benchmark/common_function.py:1366-1382 and the ground truth of :671-759 / :859-1139.
+ *   Q[nq*dim], user_ids[nq]            host buffers
+ *   out_tid[nq*k], out_doc[nq*k] (may be NULL), out_dist[nq*k], out_count[nq]   host buffers
+ * Rows past out_count[i] are filled with tid = UINT64_MAX, distance = +Inf. */
+int rk_search_batch(rk_index *ix, size_t nq, const float *Q, const uint32_t *user_ids,
+                    const rk_scan_opts *o, uint64_t *out_tid, uint32_t *out_doc, double *out_dist,
+                    int32_t *out_count);
+
+/* Same, with the query matrix and outputs already resident in HBM (device pointers); user_ids
+ * stays a host array (it drives the host-side plan).  Asynchronous on the index stream. */
+int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                           const rk_scan_opts *o, uint64_t *d_out_tid, uint32_t *d_out_doc,
+                           double *d_out_dist, int32_t *d_out_count);
+
+/* ---- multi-GPU shard merge (new; the reference has no collective) ------------- */
+
+/* Local shard result in exchange form: per query k (fp32 ordering key, tid, doc) triples sorted
+ * ascending, padded with (+Inf, UINT64_MAX).  d_key/d_tid/d_doc are device buffers [nq*k]. */
+int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                          const rk_scan_opts *o, float *d_key, uint64_t *d_tid, uint32_t *d_doc);
+/* G-way select over all-gathered shard results laid out [G][nq][k]; writes the final
+ * [nq][k] like rk_search_batch_device.  Device pointers. */
+int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, const float *d_key,
+                    const uint64_t *d_tid, const uint32_t *d_doc, uint64_t *d_out_tid,
+                    uint32_t *d_out_doc, double *d_out_dist, int32_t *d_out_count);
+
+/* ---- plumbing ------------------------------------------------------------------------------- */
+
+/* Run on the caller's CUDA stream (a cudaStream_t), e.g. torch's current stream. NULL = own stream. */
+int rk_set_stream(rk_index *ix, void *cuda_stream);
+int rk_synchronize(rk_index *ix);
+
+typedef struct rk_stats {
+    uint64_t rows;             /* rows in the store                                                */
+    uint64_t docs;
+    uint64_t partitions;
+    uint64_t device_bytes;     /* HBM held by the index                                            */
+    /* last batch */
+    uint64_t launches;         /* kernels launched by the last search call                         */
+    uint64_t segments;         /* work-list segments of the last scan launch                       */
+    uint64_t rows_scanned;     /* rows whose vectors the plan makes the kernel read                */
+    uint64_t algo_bytes;       /* rows_scanned*4d + mask bytes + 12k per query    */
+    float scan_ms;             /* CUDA-event time of the dominant scan kernel (timing enabled)     */
+    float select_ms;           /* CUDA-event time of the merge/select kernel                       */
+    float probe_ms;            /* IVF centre scoring + list choice                                 */
+    float reserved_f;
+    uint64_t total_launches;   /* kernels launched since rk_open                                   */
+    uint64_t reserved[7];
+} rk_stats;
+int rk_get_stats(rk_index *ix, rk_stats *out);
+/* Record CUDA events around the kernels of each search call (costs two events per kernel). */
+int rk_enable_timing(rk_index *ix, int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RBACKNN_H */
