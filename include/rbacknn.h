@@ -27,6 +27,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define RK_ABI_VERSION 1
 
@@ -63,6 +66,14 @@ typedef enum rk_metric { RK_METRIC_L2 = 0, RK_METRIC_IP = 1 } rk_metric;
  *   RK_FILTER_NONE       no permission filter (plain pgvector scan). */
 typedef enum rk_filter { RK_FILTER_PARTITION = 0, RK_FILTER_BITMASK = 1, RK_FILTER_NONE = 2 } rk_filter;
 
+/* Which materialised layout a partition-filtered scan uses.
+ *   RK_LAYOUT_ROLE         one scan per role of the user, merged (prefilter_role.py:124-189)
+ *   RK_LAYOUT_COMBINATION  the single table of the user's role set (prefilter_combination_role.py:122-161)
+ *   RK_LAYOUT_DYNAMIC      CombRolePartitions lookup, RLS predicate inside impure partitions
+ *                          (dynamic_partition/search.py:44-111; load_result_to_database.py:591-622)
+ *   RK_LAYOUT_AUTO         dynamic if a role-set map was given, else combination, else role */
+typedef enum rk_layout { RK_LAYOUT_AUTO = 0, RK_LAYOUT_ROLE = 1, RK_LAYOUT_COMBINATION = 2, RK_LAYOUT_DYNAMIC = 3 } rk_layout;
+
 #define RK_MAX_DIM 2048   /* pgvector IVFFLAT_MAX_DIM is 2000 (pgvector/src/ivfflat.h:24)          */
 #define RK_MAX_K 1024     /* top-k limit of the GPU selection network                               */
 #define RK_MAX_LISTS 32768 /* IVFFLAT_MAX_LISTS (pgvector/src/ivfflat.h:44)                         */
@@ -92,6 +103,9 @@ int rk_abi_version(void);
  * id handed back by scans (block_id, or a packed ItemPointer), doc[n] the row's document_id.
  * Rejects NaN/Inf like vector_in (vector.c:102-113). */
 int rk_load_rows(rk_index *ix, const float *x, const uint64_t *tid, const uint32_t *doc, size_t n);
+
+/* Optional: size the HBM row store once for n rows before a chunked rk_load_rows sequence. */
+int rk_reserve_rows(rk_index *ix, size_t n);
 
 /* PermissionAssignment(role_id, document_id) pairs (initialize_main_tables.py:66-72). */
 int rk_set_doc_roles(rk_index *ix, const uint32_t *doc, const uint32_t *role, size_t n);
@@ -134,7 +148,9 @@ typedef struct rk_scan_opts {
     int32_t max_probes;     /* ivfflat.max_probes; > probes turns on iterative_scan=relaxed_order   */
     int32_t filter;         /* rk_filter */
     int32_t null_query;     /* ORDER BY vec <-> NULL: every distance is 0 (ivfscan.c:181-200)       */
-    int32_t reserved[3];
+    int32_t layout;         /* rk_layout: which partition layout RK_FILTER_PARTITION walks          */
+    int32_t keep_duplicates;/* 1 = ground-truth merge without dedup (common_function.py:713-714)    */
+    int32_t reserved[1];
 } rk_scan_opts;
 
 /* ivfflatbeginscan (ivfscan.c:241-315): allocates scan state (result ring, device scratch). */
@@ -206,6 +222,9 @@ int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */
 int rk_enable_timing(rk_index *ix, int on);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,88 @@
+"""ctypes binding of include/rbacknn.h.
+
+There is no Python or CPU fallback: if librbacknn.so is missing this module raises at import, and
+without a CUDA device rk_open() fails with RK_ERR_NO_DEVICE.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librbacknn.so")
+
+RK_ABI_VERSION = 1
+
+
+class RkConfig(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("dim", C.c_int32), ("metric", C.c_int32), ("device", C.c_int32),
+                ("k_max", C.c_int32), ("reserved", C.c_int32 * 11)]
+
+
+class RkScanOpts(C.Structure):
+    _fields_ = [("k", C.c_int32), ("probes", C.c_int32), ("max_probes", C.c_int32), ("filter", C.c_int32),
+                ("null_query", C.c_int32), ("layout", C.c_int32), ("keep_duplicates", C.c_int32),
+                ("reserved", C.c_int32 * 1)]
+
+
+class RkStats(C.Structure):
+    _fields_ = [("rows", C.c_uint64), ("docs", C.c_uint64), ("partitions", C.c_uint64), ("device_bytes", C.c_uint64),
+                ("launches", C.c_uint64), ("segments", C.c_uint64), ("rows_scanned", C.c_uint64),
+                ("algo_bytes", C.c_uint64), ("scan_ms", C.c_float), ("select_ms", C.c_float), ("probe_ms", C.c_float),
+                ("reserved_f", C.c_float), ("total_launches", C.c_uint64), ("reserved", C.c_uint64 * 7)]
+
+
+# every symbol include/rbacknn.h declares: name -> (restype, argtypes)
+_P = C.c_void_p
+SIGNATURES = {
+    "rk_open": (_P, [C.POINTER(RkConfig)]),
+    "rk_close": (None, [_P]),
+    "rk_last_error": (C.c_char_p, []),
+    "rk_abi_version": (C.c_int, []),
+    "rk_load_rows": (C.c_int, [_P, _P, _P, _P, C.c_size_t]),
+    "rk_reserve_rows": (C.c_int, [_P, C.c_size_t]),
+    "rk_set_doc_roles": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "rk_set_user_roles": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "rk_build_role_partitions": (C.c_int, [_P]),
+    "rk_build_combination_partitions": (C.c_int, [_P]),
+    "rk_define_partition": (C.c_int, [_P, C.c_uint32, _P, C.c_size_t]),
+    "rk_map_roleset_to_partitions": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_size_t]),
+    "rk_finalize": (C.c_int, [_P]),
+    "rk_build_ivf": (C.c_int, [_P, C.c_int, C.c_uint64]),
+    "rk_build_ivf_from_centers": (C.c_int, [_P, C.c_int, _P]),
+    "rk_ivf_info": (C.c_int, [_P, C.POINTER(C.c_int), _P, _P]),
+    "rk_beginscan": (_P, [_P]),
+    "rk_rescan": (C.c_int, [_P, _P, C.c_int32, C.c_uint32, C.POINTER(RkScanOpts)]),
+    "rk_gettuple": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]),
+    "rk_endscan": (None, [_P]),
+    "rk_search_batch": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
+    "rk_search_batch_device": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
+    "rk_search_batch_shard": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P]),
+    "rk_merge_shards": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, _P]),
+    "rk_set_stream": (C.c_int, [_P, _P]),
+    "rk_synchronize": (C.c_int, [_P]),
+    "rk_get_stats": (C.c_int, [_P, C.POINTER(RkStats)]),
+    "rk_enable_timing": (C.c_int, [_P, C.c_int]),
+}
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python __graft_entry__.py` (nvcc, sm_100a). "
+            "This engine has no CPU or pure-Python fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)   # AttributeError here == header / library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    if lib.rk_abi_version() != RK_ABI_VERSION:
+        raise ImportError(f"librbacknn ABI {lib.rk_abi_version()} != binding {RK_ABI_VERSION}")
+    return lib
+
+
+lib = _load()
+
+
+def last_error() -> str:
+    return (lib.rk_last_error() or b"").decode()

@@ -1,0 +1,481 @@
+// rk_api.cu — host side of librbacknn behind the C-ABI of include/rbacknn.h.
+//
+// Holds what PostgreSQL's catalog + heap hold for the reference (rows, PermissionAssignment,
+// UserRoles, the role / combination / dynamic partition layouts), turns a batch of
+// (query vector, user) pairs into a work list for the persistent scan kernel, and mirrors the
+// pgvector index-scan contract (begin / rescan / gettuple / endscan).  No CPU scoring path exists
+// here: every distance is computed by rk_scan.cu on the GPU.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/rbacknn.h"
+#include "rk_host.h"
+
+// ---------------------------------------------------------------------------------------------
+// errors
+
+static thread_local std::string g_err;
+
+int rk_fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define RK_CUDA(call)                                                                                    \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return rk_fail(RK_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char *rk_last_error(void) { return g_err.c_str(); }
+extern "C" int rk_abi_version(void) { return RK_ABI_VERSION; }
+
+// ---------------------------------------------------------------------------------------------
+// buffers
+
+int DevBuf::ensure(size_t bytes)
+{
+    if (bytes <= cap) return 0;
+    size_t want = std::max(bytes, cap + cap / 2);
+    want = (want + 255) & ~(size_t) 255;
+    void *np = nullptr;
+    RK_CUDA(cudaMalloc(&np, want));
+    if (p) cudaFree(p);
+    p = np;
+    cap = want;
+    return 0;
+}
+void DevBuf::release()
+{
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+}
+int PinBuf::ensure(size_t bytes)
+{
+    if (bytes <= cap) return 0;
+    size_t want = std::max(bytes, cap * 2);
+    void *np = nullptr;
+    RK_CUDA(cudaHostAlloc(&np, want, cudaHostAllocDefault));
+    if (p) cudaFreeHost(p);
+    p = np;
+    cap = want;
+    return 0;
+}
+void PinBuf::release()
+{
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+}
+
+int Workspace::init(int device_)
+{
+    device = device_;
+    RK_CUDA(cudaSetDevice(device));
+    RK_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+    stream = own_stream;
+    for (auto &e : ev) RK_CUDA(cudaEventCreate(&e));
+    for (auto &e : ev_plan) RK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    return 0;
+}
+void Workspace::destroy()
+{
+    DevBuf *bufs[] = {&segs, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
+                      &out_doc, &out_dist, &out_count, &probe_key, &probe_list, &ex_key, &ex_tid, &ex_doc};
+    for (auto *b : bufs) b->release();
+    h_plan_ring[0].release();
+    h_plan_ring[1].release();
+    h_out.release();
+    for (auto &e : ev_plan)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : ev)
+        if (e) cudaEventDestroy(e);
+    if (own_stream) cudaStreamDestroy(own_stream);
+    own_stream = nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------
+// lifecycle
+
+extern "C" rk_index *rk_open(const rk_config *cfg)
+{
+    if (!cfg) { rk_fail(RK_ERR_INVALID, "rk_open: cfg is NULL"); return nullptr; }
+    if (cfg->abi_version != RK_ABI_VERSION) { rk_fail(RK_ERR_INVALID, "rk_open: ABI version %d, library is %d", cfg->abi_version, RK_ABI_VERSION); return nullptr; }
+    if (cfg->dim < 1 || cfg->dim > RK_MAX_DIM) { rk_fail(RK_ERR_UNSUPPORTED, "rk_open: dim %d outside 1..%d", cfg->dim, RK_MAX_DIM); return nullptr; }
+    if (cfg->metric != RK_METRIC_L2 && cfg->metric != RK_METRIC_IP) { rk_fail(RK_ERR_INVALID, "rk_open: unknown metric %d", cfg->metric); return nullptr; }
+    if (cfg->k_max < 1 || cfg->k_max > RK_MAX_K) { rk_fail(RK_ERR_INVALID, "rk_open: k_max %d outside 1..%d", cfg->k_max, RK_MAX_K); return nullptr; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        rk_fail(RK_ERR_NO_DEVICE, "rk_open: no CUDA device (%s); this engine has no CPU path", e == cudaSuccess ? "0 devices" : cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { rk_fail(RK_ERR_INVALID, "rk_open: device %d of %d", cfg->device, ndev); return nullptr; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major != 10) {
+        rk_fail(RK_ERR_NO_DEVICE, "rk_open: device %d is sm_%d%d; kernels are built for sm_100a only", cfg->device, prop.major, prop.minor);
+        return nullptr;
+    }
+    rk_index *ix = new rk_index();
+    ix->cfg = *cfg;
+    ix->dim = cfg->dim;
+    ix->dim_pad = (cfg->dim + 3) & ~3;
+    ix->metric = cfg->metric;
+    ix->device = cfg->device;
+    ix->k_max = cfg->k_max;
+    ix->sm_count = prop.multiProcessorCount;
+    rk_scan_geometry(ix->dim_pad, &ix->tile_rows, &ix->nstages, &ix->scan_smem);
+    if (ix->ws.init(cfg->device) != 0) { delete ix; return nullptr; }
+    return ix;
+}
+
+extern "C" void rk_close(rk_index *ix)
+{
+    if (!ix) return;
+    cudaSetDevice(ix->device);
+    cudaDeviceSynchronize();
+    ix->ws.destroy();
+    DevBuf *bufs[] = {&ix->d_x, &ix->d_tid, &ix->d_rowdoc, &ix->d_doc_ids, &ix->d_doc_mask, &ix->d_ext_row,
+                      &ix->d_ext_vstart, &ix->d_ext_mask, &ix->d_part_ext_off, &ix->ivf.d_x, &ix->ivf.d_tid,
+                      &ix->ivf.d_rowdoc, &ix->ivf.d_centers, &ix->ivf.d_center_tid, &ix->ivf.d_list_start};
+    for (auto *b : bufs) b->release();
+    delete ix;
+}
+
+// ---------------------------------------------------------------------------------------------
+// loading
+
+static int check_finite(const float *x, size_t n)
+{
+    for (size_t i = 0; i < n; i++)
+        if (!std::isfinite(x[i])) return -1;
+    return 0;
+}
+
+extern "C" int rk_load_rows(rk_index *ix, const float *x, const uint64_t *tid, const uint32_t *doc, size_t n)
+{
+    if (!ix || (!x && n) || (!tid && n) || (!doc && n)) return rk_fail(RK_ERR_INVALID, "rk_load_rows: NULL argument");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_load_rows: index already finalized");
+    if (n == 0) return RK_OK;
+    if (ix->nrows + n >= 0xFFFFFFF0ull) return rk_fail(RK_ERR_UNSUPPORTED, "rk_load_rows: more than 2^32 rows");
+    // vector_in rejects NaN and infinity (pgvector/src/vector.c:102-113)
+    if (check_finite(x, n * (size_t) ix->dim) != 0) return rk_fail(RK_ERR_NONFINITE, "rk_load_rows: NaN or infinite value not allowed in vector");
+    RK_CUDA(cudaSetDevice(ix->device));
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    const size_t need = (ix->nrows + n) * rb;
+    if (need > ix->d_x.cap) {
+        // grow, keeping what is already loaded
+        DevBuf nb;
+        size_t want = std::max(need, ix->d_x.cap * 2);
+        if (nb.ensure(want) != 0) return RK_ERR_CUDA;
+        if (ix->nrows) RK_CUDA(cudaMemcpy(nb.p, ix->d_x.p, ix->nrows * rb, cudaMemcpyDeviceToDevice));
+        ix->d_x.release();
+        ix->d_x = nb;
+    }
+    unsigned char *dst = (unsigned char *) ix->d_x.p + ix->nrows * rb;
+    if (ix->dim == ix->dim_pad) {
+        RK_CUDA(cudaMemcpy(dst, x, n * rb, cudaMemcpyHostToDevice));
+    } else {
+        RK_CUDA(cudaMemset(dst, 0, n * rb));
+        RK_CUDA(cudaMemcpy2D(dst, rb, x, (size_t) ix->dim * 4, (size_t) ix->dim * 4, n, cudaMemcpyHostToDevice));
+    }
+    ix->h_tid.insert(ix->h_tid.end(), tid, tid + n);
+    ix->h_doc.insert(ix->h_doc.end(), doc, doc + n);
+    ix->nrows += n;
+    return RK_OK;
+}
+
+extern "C" int rk_reserve_rows(rk_index *ix, size_t n)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "rk_reserve_rows: NULL index");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_reserve_rows: index already finalized");
+    RK_CUDA(cudaSetDevice(ix->device));
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    if (n * rb > ix->d_x.cap) {
+        DevBuf nb;
+        if (nb.ensure(n * rb) != 0) return RK_ERR_CUDA;
+        if (ix->nrows) RK_CUDA(cudaMemcpy(nb.p, ix->d_x.p, ix->nrows * rb, cudaMemcpyDeviceToDevice));
+        ix->d_x.release();
+        ix->d_x = nb;
+    }
+    ix->h_tid.reserve(n);
+    ix->h_doc.reserve(n);
+    return RK_OK;
+}
+
+extern "C" int rk_set_doc_roles(rk_index *ix, const uint32_t *doc, const uint32_t *role, size_t n)
+{
+    if (!ix || ((!doc || !role) && n)) return rk_fail(RK_ERR_INVALID, "rk_set_doc_roles: NULL argument");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_set_doc_roles: index already finalized");
+    for (size_t i = 0; i < n; i++) ix->doc_roles.push_back({doc[i], role[i]});
+    return RK_OK;
+}
+
+extern "C" int rk_set_user_roles(rk_index *ix, const uint32_t *user, const uint32_t *role, size_t n)
+{
+    if (!ix || ((!user || !role) && n)) return rk_fail(RK_ERR_INVALID, "rk_set_user_roles: NULL argument");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_set_user_roles: index already finalized");
+    for (size_t i = 0; i < n; i++) ix->user_roles.push_back({user[i], role[i]});
+    return RK_OK;
+}
+
+extern "C" int rk_build_role_partitions(rk_index *ix)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_build_role_partitions: index already finalized");
+    ix->want_role_parts = true;
+    return RK_OK;
+}
+
+extern "C" int rk_build_combination_partitions(rk_index *ix)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_build_combination_partitions: index already finalized");
+    ix->want_combo_parts = true;
+    return RK_OK;
+}
+
+extern "C" int rk_define_partition(rk_index *ix, uint32_t part_id, const uint32_t *docs, size_t n)
+{
+    if (!ix || (!docs && n)) return rk_fail(RK_ERR_INVALID, "rk_define_partition: NULL argument");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_define_partition: index already finalized");
+    auto &v = ix->part_defs[part_id];
+    v.insert(v.end(), docs, docs + n);
+    return RK_OK;
+}
+
+extern "C" int rk_map_roleset_to_partitions(rk_index *ix, const uint32_t *roles, size_t nroles, const uint32_t *parts, size_t nparts)
+{
+    if (!ix || (!roles && nroles) || (!parts && nparts)) return rk_fail(RK_ERR_INVALID, "rk_map_roleset_to_partitions: NULL argument");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_map_roleset_to_partitions: index already finalized");
+    std::vector<uint32_t> key(roles, roles + nroles);
+    std::sort(key.begin(), key.end());
+    key.erase(std::unique(key.begin(), key.end()), key.end());
+    auto &v = ix->roleset_parts[key];
+    v.insert(v.end(), parts, parts + nparts);
+    return RK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// finalize: freeze the layout and upload it
+
+template <typename T>
+static int upload(DevBuf &b, const std::vector<T> &v, uint64_t *acc)
+{
+    size_t bytes = std::max<size_t>(v.size() * sizeof(T), 16);
+    if (b.ensure(bytes) != 0) return RK_ERR_CUDA;
+    if (!v.empty()) RK_CUDA(cudaMemcpy(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    if (acc) *acc += b.cap;
+    return 0;
+}
+
+static void role_mask_of(const rk_index *ix, const std::vector<uint32_t> &roles, uint64_t *mask)
+{
+    for (int w = 0; w < ix->mask_words; w++) mask[w] = 0;
+    for (uint32_t r : roles) {
+        auto it = std::lower_bound(ix->role_ids.begin(), ix->role_ids.end(), r);
+        if (it == ix->role_ids.end() || *it != r) continue;
+        size_t b = (size_t) (it - ix->role_ids.begin());
+        mask[b >> 6] |= 1ull << (b & 63);
+    }
+}
+
+static inline bool mask_hit(const uint64_t *a, const uint64_t *b, int w)
+{
+    uint64_t acc = 0;
+    for (int i = 0; i < w; i++) acc |= a[i] & b[i];
+    return acc != 0;
+}
+
+extern "C" int rk_finalize(rk_index *ix)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_finalize: already finalized");
+    RK_CUDA(cudaSetDevice(ix->device));
+    const size_t n = ix->nrows;
+    const size_t rb = (size_t) ix->dim_pad * 4;
+
+    // documents: dense index in ascending raw id
+    ix->doc_ids = ix->h_doc;
+    std::sort(ix->doc_ids.begin(), ix->doc_ids.end());
+    ix->doc_ids.erase(std::unique(ix->doc_ids.begin(), ix->doc_ids.end()), ix->doc_ids.end());
+    const size_t D = ix->doc_ids.size();
+    std::vector<uint32_t> dense(n);
+    bool sorted = true;
+    for (size_t i = 0; i < n; i++) {
+        dense[i] = (uint32_t) (std::lower_bound(ix->doc_ids.begin(), ix->doc_ids.end(), ix->h_doc[i]) - ix->doc_ids.begin());
+        if (i && dense[i] < dense[i - 1]) sorted = false;
+    }
+    // rows ordered by document (stable), so a document is one contiguous extent
+    ix->load_to_row.resize(n);
+    if (sorted) {
+        for (size_t i = 0; i < n; i++) ix->load_to_row[i] = (uint32_t) i;
+        ix->h_rowdoc.swap(dense);
+    } else {
+        std::vector<uint32_t> perm(n);   // finalized row -> load index
+        for (size_t i = 0; i < n; i++) perm[i] = (uint32_t) i;
+        std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t b) { return dense[a] < dense[b]; });
+        std::vector<uint64_t> t2(n);
+        ix->h_rowdoc.resize(n);
+        for (size_t i = 0; i < n; i++) {
+            t2[i] = ix->h_tid[perm[i]];
+            ix->h_rowdoc[i] = dense[perm[i]];
+            ix->load_to_row[perm[i]] = (uint32_t) i;
+        }
+        ix->h_tid.swap(t2);
+        DevBuf d_perm, nx;
+        if (upload(d_perm, perm, nullptr) != 0) return RK_ERR_CUDA;
+        if (nx.ensure(std::max<size_t>(n * rb, 16)) != 0) return RK_ERR_CUDA;
+        RK_CUDA(rk_launch_gather_rows(ix->d_x.as<float>(), nx.as<float>(), d_perm.as<uint32_t>(), n, ix->dim_pad, 0));
+        RK_CUDA(cudaDeviceSynchronize());
+        ix->d_x.release();
+        ix->d_x = nx;
+        d_perm.release();
+    }
+    if (ix->d_x.p == nullptr && ix->d_x.ensure(16) != 0) return RK_ERR_CUDA;
+    ix->doc_row_start.assign(D + 1, 0);
+    for (size_t i = 0; i < n; i++) ix->doc_row_start[ix->h_rowdoc[i] + 1]++;
+    for (size_t d = 0; d < D; d++) ix->doc_row_start[d + 1] += ix->doc_row_start[d];
+
+    // roles: dense bit positions in ascending raw id
+    for (auto &pr : ix->doc_roles) ix->role_ids.push_back(pr.second);
+    for (auto &pr : ix->user_roles) ix->role_ids.push_back(pr.second);
+    std::sort(ix->role_ids.begin(), ix->role_ids.end());
+    ix->role_ids.erase(std::unique(ix->role_ids.begin(), ix->role_ids.end()), ix->role_ids.end());
+    ix->mask_words = std::max<int>(1, (int) ((ix->role_ids.size() + 63) / 64));
+    if (ix->mask_words > 16) return rk_fail(RK_ERR_UNSUPPORTED, "rk_finalize: %zu roles, at most 1024 supported", ix->role_ids.size());
+    const int W = ix->mask_words;
+    ix->doc_mask.assign(std::max<size_t>(D, 1) * W, 0);
+    for (auto &pr : ix->doc_roles) {
+        auto it = std::lower_bound(ix->doc_ids.begin(), ix->doc_ids.end(), pr.first);
+        if (it == ix->doc_ids.end() || *it != pr.first) continue;   // permission for a document with no rows
+        size_t d = (size_t) (it - ix->doc_ids.begin());
+        size_t b = (size_t) (std::lower_bound(ix->role_ids.begin(), ix->role_ids.end(), pr.second) - ix->role_ids.begin());
+        ix->doc_mask[d * W + (b >> 6)] |= 1ull << (b & 63);
+    }
+
+    // users
+    for (auto &pr : ix->user_roles) ix->users[pr.first].roles.push_back(pr.second);
+    std::map<std::vector<uint32_t>, std::pair<uint64_t, uint64_t>> set_rows;   // role set -> (rows, docs)
+    for (auto &kv : ix->users) {
+        UserInfo &u = kv.second;
+        std::sort(u.roles.begin(), u.roles.end());
+        u.roles.erase(std::unique(u.roles.begin(), u.roles.end()), u.roles.end());
+        u.mask.assign(W, 0);
+        role_mask_of(ix, u.roles, u.mask.data());
+        auto it = set_rows.find(u.roles);
+        if (it == set_rows.end()) {
+            uint64_t rows = 0, docs = 0;
+            for (size_t d = 0; d < D; d++)
+                if (mask_hit(&ix->doc_mask[d * W], u.mask.data(), W)) {
+                    rows += ix->doc_row_start[d + 1] - ix->doc_row_start[d];
+                    docs++;
+                }
+            it = set_rows.emplace(u.roles, std::make_pair(rows, docs)).first;
+        }
+        u.allowed_rows = it->second.first;
+        u.allowed_docs = it->second.second;
+    }
+
+    // partitions; [0] = every document (bitmask / unfiltered scans walk it)
+    ix->parts.clear();
+    ix->parts.emplace_back();
+    ix->parts[0].docs.resize(D);
+    for (size_t d = 0; d < D; d++) ix->parts[0].docs[d] = (uint32_t) d;
+    auto docs_matching = [&](const uint64_t *m, std::vector<uint32_t> &out) {
+        out.clear();
+        for (size_t d = 0; d < D; d++)
+            if (mask_hit(&ix->doc_mask[d * W], m, W)) out.push_back((uint32_t) d);
+    };
+    if (ix->want_role_parts) {
+        // initialize_partitions.py:302-311 — documentblocks_role_<r>
+        std::vector<uint64_t> m(W);
+        for (uint32_t r : ix->role_ids) {
+            role_mask_of(ix, std::vector<uint32_t>{r}, m.data());
+            PartInfo pi;
+            docs_matching(m.data(), pi.docs);
+            ix->role_part[r] = (uint32_t) ix->parts.size();
+            ix->parts.push_back(std::move(pi));
+        }
+    }
+    if (ix->want_combo_parts) {
+        // initialize_partitions.py:549-555, 682-693 — one table per distinct role set, DISTINCT union
+        std::vector<uint64_t> m(W);
+        for (auto &kv : ix->users) {
+            const auto &rs = kv.second.roles;
+            if (rs.empty() || ix->combo_part.count(rs)) continue;
+            role_mask_of(ix, rs, m.data());
+            PartInfo pi;
+            docs_matching(m.data(), pi.docs);
+            ix->combo_part[rs] = (uint32_t) ix->parts.size();
+            ix->parts.push_back(std::move(pi));
+        }
+    }
+    for (auto &kv : ix->part_defs) {
+        // load_result_to_database.py:207-250 — documentblocks_partition_<p>
+        PartInfo pi;
+        for (uint32_t raw : kv.second) {
+            auto it = std::lower_bound(ix->doc_ids.begin(), ix->doc_ids.end(), raw);
+            if (it != ix->doc_ids.end() && *it == raw) pi.docs.push_back((uint32_t) (it - ix->doc_ids.begin()));
+        }
+        std::sort(pi.docs.begin(), pi.docs.end());
+        pi.docs.erase(std::unique(pi.docs.begin(), pi.docs.end()), pi.docs.end());
+        ix->dyn_part[kv.first] = (uint32_t) ix->parts.size();
+        ix->parts.push_back(std::move(pi));
+    }
+    for (auto &kv : ix->roleset_parts)
+        for (uint32_t pid : kv.second)
+            if (!ix->dyn_part.count(pid)) return rk_fail(RK_ERR_INVALID, "rk_finalize: role set maps to undefined partition %u", pid);
+
+    // extent tables: one extent per document, plus a sentinel per partition
+    std::vector<uint32_t> ext_row, ext_vstart, part_off;
+    std::vector<uint64_t> ext_mask;
+    for (auto &pi : ix->parts) {
+        pi.ext_off = (uint32_t) ext_row.size();
+        part_off.push_back(pi.ext_off);
+        uint64_t v = 0;
+        for (uint32_t d : pi.docs) {
+            uint32_t r0 = ix->doc_row_start[d], r1 = ix->doc_row_start[d + 1];
+            ext_row.push_back(r0);
+            ext_vstart.push_back((uint32_t) v);
+            for (int w = 0; w < W; w++) ext_mask.push_back(ix->doc_mask[(size_t) d * W + w]);
+            v += r1 - r0;
+        }
+        pi.n_ext = (uint32_t) pi.docs.size();
+        pi.rows = v;
+        if (v >= 0xFFFFFFFFull) return rk_fail(RK_ERR_UNSUPPORTED, "rk_finalize: partition with 2^32 rows");
+        ext_row.push_back(0);
+        ext_vstart.push_back((uint32_t) v);
+        for (int w = 0; w < W; w++) ext_mask.push_back(0);
+    }
+    part_off.push_back((uint32_t) ext_row.size());
+
+    ix->device_bytes = ix->d_x.cap;
+    if (upload(ix->d_tid, ix->h_tid, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_rowdoc, ix->h_rowdoc, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_doc_ids, ix->doc_ids, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_doc_mask, ix->doc_mask, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_ext_row, ext_row, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_ext_vstart, ext_vstart, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_ext_mask, ext_mask, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    if (upload(ix->d_part_ext_off, part_off, &ix->device_bytes) != 0) return RK_ERR_CUDA;
+    std::vector<uint32_t>().swap(ix->h_doc);
+    ix->finalized = true;
+    return RK_OK;
+}

@@ -1,0 +1,177 @@
+// rk_common.cuh — shared device/host definitions of librbacknn (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define RK_SEG_EXTENTS 0u   // virtual row range [begin,end) of an extent table (partition)
+#define RK_SEG_ROWS 2u      // physical row range [begin,end), no predicate
+#define RK_SEG_ROWMASK 3u   // physical row range [begin,end), role mask tested per row through rowdoc[]
+
+#define RK_SEGF_MASKED 1u   // test the extent's role mask against the user's before loading it
+
+#define RK_KEY_SENTINEL 0xFFFFFFFFu
+
+// One unit of scan work: rows of ONE query's visible set.  Segments of a query are contiguous in
+// the work list so that the select kernel finds them as [qseg[q], qseg[q+1]).
+struct RkSegment {
+    uint32_t query;   // index into the batch
+    uint32_t kind;    // RK_SEG_*
+    uint32_t src;     // partition id (extent table) for RK_SEG_EXTENTS
+    uint32_t flags;   // RK_SEGF_*
+    uint64_t begin;
+    uint64_t end;
+};
+
+// Device view of one row store (the main doc-sorted store or the IVF list-sorted copy).
+struct RkStoreView {
+    const float *x;            // [rows][dim_pad]
+    const uint64_t *tid;       // [rows]
+    const uint32_t *rowdoc;    // [rows] dense document index
+    uint64_t rows;
+};
+
+struct RkScanParams {
+    RkStoreView store;
+    // permission data (main store is sorted by document)
+    const uint64_t *doc_mask;       // [docs][mask_words] (row-mask segments go through store.rowdoc)
+    const uint64_t *qmask;          // [nq][mask_words] role mask of each query's user
+    int mask_words;
+    // extent tables
+    const uint32_t *ext_row;        // physical first row of each extent (+ sentinel per partition)
+    const uint32_t *ext_vstart;     // virtual row offset of each extent inside its partition (+ sentinel = partition rows)
+    const uint64_t *ext_mask;       // [extents][mask_words] role mask of the extent's document
+    const uint32_t *part_ext_off;   // [partitions+1] index into ext_*; partition p owns [off[p], off[p+1]-1) plus its sentinel
+    // queries
+    const float *q;                 // [nq][dim_pad]
+    int null_query;                 // ORDER BY v <-> NULL: all distances 0
+    // work list
+    const RkSegment *segs;
+    const uint32_t *nseg_ptr;       // number of segments (device resident so plans can be built on device)
+    uint32_t *seg_counter;          // dynamic scheduler
+    // per-segment output (k_pad entries each)
+    uint32_t *cand_key;
+    uint64_t *cand_tid;
+    uint32_t *cand_row;
+    int32_t *cand_count;
+    // geometry
+    int dim4;        // dim_pad / 4
+    int row_bytes;   // dim_pad * 4
+    int tile_rows;   // rows per pipeline stage
+    int nstages;
+    int k;
+    int metric;      // 0 = L2, 1 = IP
+};
+
+struct RkSelectParams {
+    const uint32_t *cand_key;
+    const uint64_t *cand_tid;
+    const uint32_t *cand_row;
+    const int32_t *cand_count;
+    const uint32_t *qseg;       // [nq+1] segment range per query
+    int lists_per_query;        // if > 0: query q owns lists [q*L, (q+1)*L) (shard merge / fixed plans) and qseg is ignored
+    int list_stride;            // entries between consecutive lists
+    int k;
+    int metric;
+    int dedup;
+    int null_query;
+    int key_is_float;           // cand_key holds fp32 ordering values (exchange form) instead of uint keys
+    // row -> document id (may be NULL when cand_row already holds document ids)
+    const uint32_t *rowdoc;
+    const uint32_t *doc_ids;
+    // outputs (any may be NULL)
+    uint64_t *out_tid;
+    uint32_t *out_doc;
+    double *out_dist;
+    int32_t *out_count;
+    float *out_key;             // exchange form: fp32 ordering value
+    uint32_t *out_row;
+};
+
+// ---------------------------------------------------------------------------------------------
+// order-preserving float <-> uint key
+
+__host__ __device__ __forceinline__ uint32_t rk_float_to_key(float v)
+{
+#ifdef __CUDA_ARCH__
+    uint32_t u = __float_as_uint(v);
+#else
+    union { float f; uint32_t u; } c; c.f = v; uint32_t u = c.u;
+#endif
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__host__ __device__ __forceinline__ float rk_key_to_float(uint32_t k)
+{
+    uint32_t u = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    union { float f; uint32_t u; } c; c.u = u; return c.f;
+#endif
+}
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers: mbarrier + 1-D bulk async copy (TMA unit, SASS UBLKCP)
+
+__device__ __forceinline__ uint32_t rk_smem_u32(const void *p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void rk_mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rk_smem_u32(bar)), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void rk_fence_barrier_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void rk_fence_proxy_async()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void rk_mbar_arrive(uint64_t *bar)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(rk_smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void rk_mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(rk_smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+
+__device__ __forceinline__ void rk_mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "RK_WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra RK_WAIT_DONE;\n\t"
+        "bra RK_WAIT_LOOP;\n\t"
+        "RK_WAIT_DONE:\n\t"
+        "}" ::"r"(rk_smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// global -> shared bulk copy completing on an mbarrier.  dst, src and bytes must be multiples of 16.
+__device__ __forceinline__ void rk_bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     rk_smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(rk_smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ void rk_named_bar_sync(int id, int nthreads)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+#endif  // __CUDACC__

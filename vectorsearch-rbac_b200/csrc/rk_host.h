@@ -1,0 +1,136 @@
+// rk_host.h — host-side state of librbacknn (internal; the public surface is include/rbacknn.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+#include "../../include/rbacknn.h"
+#include "rk_kernels.h"
+
+int rk_fail(int code, const char *fmt, ...);
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes);   // grows (contents NOT preserved)
+    void release();
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct PinBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes);
+    void release();
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// Everything one search context needs: a stream, the uploaded plan, per-segment candidate lists
+// and result buffers.  The index owns one (rk_search_batch*), every rk_scan owns another.
+struct Workspace {
+    int device = 0;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    DevBuf segs, ctl /* [0]=nseg [1]=counter */, cand_key, cand_tid, cand_row, cand_count, qseg, qmask, dq;
+    DevBuf out_tid, out_doc, out_dist, out_count;
+    DevBuf probe_key, probe_list;        // IVF: per-query selected lists
+    DevBuf ex_key, ex_tid, ex_doc;       // exchange-form results
+    PinBuf h_plan_ring[2], h_out;        // plan staging alternates so the host may run one batch ahead
+    cudaEvent_t ev_plan[2] = {nullptr, nullptr};
+    bool ev_plan_used[2] = {false, false};
+    int plan_idx = 0;
+    bool timing = false;
+    // stats of the last call
+    uint64_t launches = 0, segments = 0, rows_scanned = 0, algo_bytes = 0;
+    bool timed_scan = false, timed_select = false, timed_probe = false;
+    int init(int device);
+    void destroy();
+};
+
+struct PartInfo {
+    uint32_t ext_off = 0;     // index of first extent in the global extent arrays
+    uint32_t n_ext = 0;
+    uint64_t rows = 0;
+    std::vector<uint32_t> docs;   // dense document indices, ascending
+};
+
+struct UserInfo {
+    std::vector<uint32_t> roles;        // raw role ids, ascending, unique
+    std::vector<uint64_t> mask;         // [mask_words]
+    uint64_t allowed_rows = 0;          // rows the RLS predicate lets this user see
+    uint64_t allowed_docs = 0;
+};
+
+struct IvfIndex {
+    bool built = false;
+    int lists = 0;
+    DevBuf d_x, d_tid, d_rowdoc;        // list-sorted copy of the row store
+    DevBuf d_centers, d_center_tid, d_list_start;
+    std::vector<uint32_t> list_start;   // [lists+1]
+    std::vector<uint32_t> row_list;     // by finalized row order
+    std::vector<float> centers;         // [lists][dim]
+    uint32_t max_list_len = 0;
+    int chunks_per_list = 1;
+};
+
+struct rk_index {
+    rk_config cfg{};
+    int dim = 0, dim_pad = 0, metric = 0, device = 0, k_max = 0, sm_count = 148;
+    int tile_rows = 0, nstages = 0;
+    size_t scan_smem = 0;
+    bool finalized = false;
+    // staging
+    size_t nrows = 0;
+    DevBuf d_x;                                   // [nrows][dim_pad]
+    std::vector<uint64_t> h_tid;
+    std::vector<uint32_t> h_doc;                  // raw document ids (by row)
+    std::vector<std::pair<uint32_t, uint32_t>> doc_roles, user_roles;
+    std::map<uint32_t, std::vector<uint32_t>> part_defs;
+    std::map<std::vector<uint32_t>, std::vector<uint32_t>> roleset_parts;
+    bool want_role_parts = false, want_combo_parts = false;
+    // finalized layout
+    std::vector<uint32_t> load_to_row;            // load order -> finalized row
+    std::vector<uint32_t> doc_ids;                // dense -> raw document id (ascending)
+    std::vector<uint32_t> doc_row_start;          // [docs+1]
+    std::vector<uint32_t> h_rowdoc;               // dense doc of each finalized row
+    std::vector<uint32_t> role_ids;               // dense -> raw role id (ascending)
+    int mask_words = 1;
+    std::vector<uint64_t> doc_mask;               // [docs][mask_words]
+    std::unordered_map<uint32_t, UserInfo> users;
+    std::vector<PartInfo> parts;                  // [0] = ALL documents
+    std::unordered_map<uint32_t, uint32_t> role_part;                    // raw role -> parts index
+    std::map<std::vector<uint32_t>, uint32_t> combo_part;                // role set -> parts index
+    std::unordered_map<uint32_t, uint32_t> dyn_part;                     // part_id -> parts index
+    std::map<std::pair<std::vector<uint32_t>, uint32_t>, bool> pure_cache;  // (role set, part) -> pure?
+    std::mutex mu;
+    DevBuf d_tid, d_rowdoc, d_doc_ids, d_doc_mask, d_ext_row, d_ext_vstart, d_ext_mask, d_part_ext_off;
+    uint64_t device_bytes = 0;
+    IvfIndex ivf;
+    Workspace ws;
+    uint64_t total_launches = 0;
+    float last_scan_ms = 0, last_select_ms = 0, last_probe_ms = 0;
+};
+
+struct rk_scan {
+    rk_index *ix = nullptr;
+    Workspace ws;
+    std::vector<float> q;
+    uint32_t user = 0;
+    rk_scan_opts opts{};
+    bool bound = false;
+    // result ring of the current probe batch
+    std::vector<uint64_t> r_tid;
+    std::vector<uint32_t> r_doc;
+    std::vector<double> r_dist;
+    int r_count = 0, r_pos = 0;
+    int probes_done = 0;        // lists consumed so far (iterative scan)
+    int max_probes_eff = 0, probes_eff = 0;
+};
+
+// rk_ivf.cu
+int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids,
+                  const rk_scan_opts *o, int probe_offset, const RkSelectParams &out);

@@ -1,0 +1,145 @@
+// rk_merge.cu — per-query k-way select over the candidate lists the scan kernel (or an all-gather
+// across GPUs) produced.
+//
+// Stands in for the harness merge: "sort by distance, drop duplicates on (document_id, block_id),
+// stop at k" (controller/baseline/prefilter/prefilter_role.py:174-189;
+// controller/dynamic_partition/search.py:347-364) and for the final `[:topk]` of the ground truth
+// (basic_benchmark/common_function.py:713-714, 1114-1124).  Also converts the fp32 sum to what the
+// SQL operator returns: sqrt((double) sum) for `<->` (pgvector/src/vector.c:577), -(double) sum for
+// `<#>` (vector.c:635).
+#include "rk_common.cuh"
+#include "rk_select.cuh"
+#include "rk_kernels.h"
+
+#define RK_SEL_THREADS 256
+#define RK_SEL_CHUNK 1024
+
+__global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelectParams p)
+{
+    __shared__ __align__(16) uint64_t s_tid[RK_CAND_CAP];
+    __shared__ uint32_t s_key[RK_CAND_CAP];
+    __shared__ uint32_t s_row[RK_CAND_CAP];
+    __shared__ uint32_t s_count, s_tau, s_scan[RK_SEL_THREADS / 32];
+
+    const int q = blockIdx.x;
+    const int t = threadIdx.x;
+    RkCandBuf cb{s_key, s_row, s_tid};
+    auto sync = [] { __syncthreads(); };
+
+    uint32_t l0, l1;
+    if (p.lists_per_query > 0) { l0 = 0; l1 = (uint32_t) p.lists_per_query; }
+    else { l0 = p.qseg[q]; l1 = p.qseg[q + 1]; }
+    const uint32_t nl = l1 - l0;
+    const int k = p.k;
+
+    // In fixed-list mode list j of query q lives at ((j * nq) + q) * k  ([G][nq][k] all-gather layout).
+    auto list_base = [&](uint32_t j) -> size_t {
+        return p.lists_per_query > 0 ? ((size_t) j * gridDim.x + q) * (size_t) p.list_stride
+                                     : (size_t) (l0 + j) * (size_t) p.list_stride;
+    };
+    auto list_count = [&](uint32_t j) -> int { return p.cand_count ? p.cand_count[p.lists_per_query > 0 ? j * gridDim.x + q : l0 + j] : k; };
+
+    auto load_key = [&](size_t a) -> uint32_t {
+        const uint32_t raw = p.cand_key[a];
+        return p.key_is_float ? rk_float_to_key(__uint_as_float(raw)) : raw;
+    };
+    if (t == 0) { s_count = 0; s_tau = RK_KEY_SENTINEL; }
+    __syncthreads();
+    // upper bound of the k-th best: any list holding k entries proves tau <= its last key
+    for (uint32_t j = t; j < nl; j += RK_SEL_THREADS) {
+        if (list_count(j) >= k) atomicMin(&s_tau, load_key(list_base(j) + k - 1));
+    }
+    __syncthreads();
+
+    const size_t total = (size_t) nl * k;
+    for (size_t c0 = 0; c0 < total; c0 += RK_SEL_CHUNK) {
+        const uint32_t tau = s_tau;
+        for (size_t idx = c0 + t; idx < total && idx < c0 + RK_SEL_CHUNK; idx += RK_SEL_THREADS) {
+            const uint32_t j = (uint32_t) (idx / k);
+            const int i = (int) (idx % k);
+            if (i < list_count(j)) {
+                const size_t a = list_base(j) + i;
+                const uint32_t key = load_key(a);
+                const uint64_t tid = p.cand_tid[a];
+                // padding: sentinel key, or (+Inf, UINT64_MAX) in exchange form
+                const bool pad = key == RK_KEY_SENTINEL || (tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u);
+                if (key <= tau && !pad) {
+                    const uint32_t slot = atomicAdd(&s_count, 1u);
+                    s_key[slot] = key; s_tid[slot] = tid; s_row[slot] = p.cand_row[a];
+                }
+            }
+        }
+        __syncthreads();
+        const int n = (int) s_count;
+        const bool lastc = c0 + RK_SEL_CHUNK >= total;
+        if (lastc || n > RK_CAND_CAP - RK_SEL_CHUNK) {
+            rk_bitonic_sort(cb, n, t, RK_SEL_THREADS, sync);
+            int m = n;
+            if (p.dedup && n > 1) {
+                // drop entries equal to their predecessor (same tuple reached through two partitions)
+                // stable compaction with a block-wide exclusive scan over keep flags
+                const int per = (n + RK_SEL_THREADS - 1) / RK_SEL_THREADS;
+                const int b0 = t * per, b1 = min(n, b0 + per);
+                int cnt = 0;
+                for (int i = b0; i < b1; i++) cnt += !(i > 0 && s_tid[i] == s_tid[i - 1] && s_key[i] == s_key[i - 1]);
+                int inc = cnt;
+                for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, inc, o); if ((t & 31) >= o) inc += v; }
+                if ((t & 31) == 31) s_scan[t >> 5] = (uint32_t) inc;
+                __syncthreads();
+                int woff = 0, tot = 0;
+                for (int w = 0; w < RK_SEL_THREADS / 32; w++) { if (w < (t >> 5)) woff += (int) s_scan[w]; tot += (int) s_scan[w]; }
+                int pos = woff + inc - cnt;
+                // read my block into registers is unbounded; instead write through a second pass:
+                // entries only move left (pos <= i), and blocks are processed in index order per thread,
+                // but different threads may race, so stage keep flags first, then move after a barrier.
+                uint64_t mt[8]; uint32_t mk[8], mr[8]; int mp[8]; int mc = 0;   // per <= 8 since n <= 2048, 256 threads
+                for (int i = b0; i < b1; i++) {
+                    bool keepf = !(i > 0 && s_tid[i] == s_tid[i - 1] && s_key[i] == s_key[i - 1]);
+                    if (keepf) { mt[mc] = s_tid[i]; mk[mc] = s_key[i]; mr[mc] = s_row[i]; mp[mc] = pos++; mc++; }
+                }
+                __syncthreads();
+                for (int i = 0; i < mc; i++) { s_tid[mp[i]] = mt[i]; s_key[mp[i]] = mk[i]; s_row[mp[i]] = mr[i]; }
+                __syncthreads();
+                m = tot;
+            }
+            const int keep = m < k ? m : k;
+            if (t == 0) {
+                s_count = (uint32_t) keep;
+                if (m >= k) { uint32_t kk = s_key[k - 1]; if (kk < s_tau) s_tau = kk; }
+            }
+            __syncthreads();
+        }
+    }
+
+    const int cnt = (int) s_count;
+    const size_t ob = (size_t) q * k;
+    for (int i = t; i < k; i += RK_SEL_THREADS) {
+        const bool ok = i < cnt;
+        const uint32_t key = ok ? s_key[i] : RK_KEY_SENTINEL;
+        const float ord = ok ? rk_key_to_float(key) : __int_as_float(0x7f800000);
+        if (p.out_tid) p.out_tid[ob + i] = ok ? s_tid[i] : 0xFFFFFFFFFFFFFFFFull;
+        if (p.out_row) p.out_row[ob + i] = ok ? s_row[i] : 0xFFFFFFFFu;
+        if (p.out_key) p.out_key[ob + i] = ord;
+        if (p.out_doc) {
+            uint32_t d = 0xFFFFFFFFu;
+            if (ok) d = p.rowdoc ? p.doc_ids[p.rowdoc[s_row[i]]] : s_row[i];
+            p.out_doc[ob + i] = d;
+        }
+        if (p.out_dist) {
+            double v;
+            if (!ok) v = __longlong_as_double(0x7ff0000000000000ll);
+            else if (p.null_query) v = 0.0;
+            else if (p.metric == 0) v = sqrt((double) ord);     // vector.c:577
+            else v = (double) ord;                              // ord already holds -sum (vector.c:635)
+            p.out_dist[ob + i] = v;
+        }
+    }
+    if (t == 0 && p.out_count) p.out_count[q] = cnt;
+}
+
+cudaError_t rk_launch_select(const RkSelectParams &p, int nq, cudaStream_t stream)
+{
+    if (nq <= 0) return cudaSuccess;
+    rk_select_kernel<<<nq, RK_SEL_THREADS, 0, stream>>>(p);
+    return cudaGetLastError();
+}

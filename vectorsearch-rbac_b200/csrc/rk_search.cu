@@ -1,0 +1,527 @@
+// rk_search.cu — query planning and launches: (query vector, user) batches -> work list -> scan
+// kernel -> select kernel; plus the pgvector-shaped scan iterator.
+//
+// Mirrors, on the host, what the harness does around each SQL statement:
+//   user -> roles                 prefilter_role.py:120-124 (unknown user -> no roles -> empty result)
+//   roles -> role partitions      prefilter_role.py:124-172
+//   roles -> combination table    prefilter_combination_role.py:122-133
+//   roles -> dynamic partitions   controller/dynamic_partition/search.py:44-60, RLS unless pure
+//                                 (load_result_to_database.py:591-622)
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "rk_host.h"
+
+#define RK_CUDA(call)                                                                                    \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return rk_fail(RK_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+static int validate_opts(const rk_index *ix, const rk_scan_opts *o)
+{
+    if (!o) return rk_fail(RK_ERR_INVALID, "scan options are NULL");
+    if (o->k < 1 || o->k > ix->k_max) return rk_fail(RK_ERR_INVALID, "k = %d outside 1..k_max (%d)", o->k, ix->k_max);
+    if (o->probes < 0 || o->probes > RK_MAX_LISTS) return rk_fail(RK_ERR_INVALID, "probes = %d outside 0..%d", o->probes, RK_MAX_LISTS);
+    if (o->filter < RK_FILTER_PARTITION || o->filter > RK_FILTER_NONE) return rk_fail(RK_ERR_INVALID, "unknown filter %d", o->filter);
+    if (o->probes > 0 && !ix->ivf.built) return rk_fail(RK_ERR_STATE, "probes > 0 but no IVFFlat index was built");
+    return 0;
+}
+
+static bool partition_pure(rk_index *ix, const UserInfo &u, uint32_t pidx)
+{
+    // a partition is pure for a role set when every document in it is visible to that role set
+    // (load_result_to_database.py:591-604 skips the RLS policy for those)
+    std::lock_guard<std::mutex> g(ix->mu);
+    auto key = std::make_pair(u.roles, pidx);
+    auto it = ix->pure_cache.find(key);
+    if (it != ix->pure_cache.end()) return it->second;
+    bool pure = true;
+    const int W = ix->mask_words;
+    for (uint32_t d : ix->parts[pidx].docs) {
+        uint64_t acc = 0;
+        for (int w = 0; w < W; w++) acc |= ix->doc_mask[(size_t) d * W + w] & u.mask[w];
+        if (!acc) { pure = false; break; }
+    }
+    ix->pure_cache[key] = pure;
+    return pure;
+}
+
+struct PlanItem { uint32_t part; uint32_t flags; uint64_t rows_est; };
+
+// Which partitions does this user's scan walk?  Returns <0 on error.
+static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std::vector<PlanItem> &items)
+{
+    items.clear();
+    if (o->filter == RK_FILTER_NONE) {
+        items.push_back({0u, 0u, ix->parts[0].rows});
+        return 0;
+    }
+    if (!u || u->roles.empty()) return 0;   // no roles -> nothing visible
+    if (o->filter == RK_FILTER_BITMASK) {
+        if (u->allowed_rows) items.push_back({0u, RK_SEGF_MASKED, u->allowed_rows});
+        return 0;
+    }
+    int layout = o->layout;
+    if (layout == RK_LAYOUT_AUTO) {
+        if (!ix->roleset_parts.empty()) layout = RK_LAYOUT_DYNAMIC;
+        else if (ix->want_combo_parts) layout = RK_LAYOUT_COMBINATION;
+        else if (ix->want_role_parts) layout = RK_LAYOUT_ROLE;
+        else return rk_fail(RK_ERR_STATE, "partition filter requested but no partition layout was built");
+    }
+    if (layout == RK_LAYOUT_ROLE) {
+        if (!ix->want_role_parts) return rk_fail(RK_ERR_STATE, "role partitions were not built");
+        for (uint32_t r : u->roles) {
+            auto it = ix->role_part.find(r);
+            if (it != ix->role_part.end() && ix->parts[it->second].rows)
+                items.push_back({it->second, 0u, ix->parts[it->second].rows});
+        }
+    } else if (layout == RK_LAYOUT_COMBINATION) {
+        if (!ix->want_combo_parts) return rk_fail(RK_ERR_STATE, "combination partitions were not built");
+        auto it = ix->combo_part.find(u->roles);
+        if (it != ix->combo_part.end() && ix->parts[it->second].rows)
+            items.push_back({it->second, 0u, ix->parts[it->second].rows});
+    } else if (layout == RK_LAYOUT_DYNAMIC) {
+        auto it = ix->roleset_parts.find(u->roles);
+        if (it == ix->roleset_parts.end()) return 0;   // no CombRolePartitions row -> no partitions (search.py:54-60)
+        for (uint32_t pid : it->second) {
+            uint32_t pidx = ix->dyn_part[pid];
+            if (!ix->parts[pidx].rows) continue;
+            bool pure = partition_pure(ix, *u, pidx);
+            items.push_back({pidx, pure ? 0u : RK_SEGF_MASKED, ix->parts[pidx].rows});
+        }
+    } else {
+        return rk_fail(RK_ERR_INVALID, "unknown layout %d", layout);
+    }
+    return 0;
+}
+
+// Build the work list of an exact (probes == 0) batch into ws.h_plan and upload it.
+static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32_t *user_ids, const rk_scan_opts *o,
+                            uint32_t *out_nseg)
+{
+    const int W = ix->mask_words;
+    std::vector<std::vector<PlanItem>> per_q(nq);
+    std::vector<const UserInfo *> uinfo(nq, nullptr);
+    uint64_t total_rows = 0;
+    for (size_t q = 0; q < nq; q++) {
+        auto it = ix->users.find(user_ids ? user_ids[q] : 0u);
+        uinfo[q] = it == ix->users.end() ? nullptr : &it->second;
+        int rc = plan_user(ix, uinfo[q], o, per_q[q]);
+        if (rc < 0) return rc;
+        for (auto &pi : per_q[q]) total_rows += pi.rows_est;
+    }
+    // segment sizing: ~8 segments per CTA for balance, but never below ~128 KB of row data
+    const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4;
+    uint64_t min_rows = std::max<uint64_t>((uint64_t) ix->tile_rows, (128 * 1024) / row_bytes);
+    uint64_t target = std::max<uint64_t>(min_rows, total_rows / ((uint64_t) ix->sm_count * 8) + 1);
+
+    std::vector<RkSegment> segs;
+    std::vector<uint32_t> qseg(nq + 1, 0);
+    uint64_t mask_bytes = 0;
+    for (size_t q = 0; q < nq; q++) {
+        qseg[q] = (uint32_t) segs.size();
+        for (auto &pi : per_q[q]) {
+            const PartInfo &P = ix->parts[pi.part];
+            uint64_t nchunks = (pi.rows_est + target - 1) / target;
+            if (nchunks < 1) nchunks = 1;
+            if (nchunks > P.rows) nchunks = P.rows;
+            for (uint64_t c = 0; c < nchunks; c++) {
+                RkSegment s;
+                s.query = (uint32_t) q; s.kind = RK_SEG_EXTENTS; s.src = pi.part; s.flags = pi.flags;
+                s.begin = P.rows * c / nchunks;
+                s.end = P.rows * (c + 1) / nchunks;
+                if (s.end > s.begin) segs.push_back(s);
+            }
+            if (pi.flags & RK_SEGF_MASKED) mask_bytes += (uint64_t) P.n_ext * (8ull * W + 8);
+        }
+    }
+    qseg[nq] = (uint32_t) segs.size();
+    const uint32_t nseg = (uint32_t) segs.size();
+
+    // pinned staging: [segments][qseg][qmask]
+    const size_t b_segs = (size_t) nseg * sizeof(RkSegment), b_qseg = (nq + 1) * 4, b_qmask = nq * (size_t) W * 8;
+    ws.plan_idx ^= 1;
+    const int pi_ = ws.plan_idx;
+    if (ws.ev_plan_used[pi_]) RK_CUDA(cudaEventSynchronize(ws.ev_plan[pi_]));   // staging buffer free again?
+    PinBuf &h_plan = ws.h_plan_ring[pi_];
+    if (h_plan.ensure(b_segs + b_qseg + b_qmask + 64) != 0) return RK_ERR_CUDA;
+    unsigned char *hp = h_plan.as<unsigned char>();
+    if (nseg) memcpy(hp, segs.data(), b_segs);
+    memcpy(hp + b_segs, qseg.data(), b_qseg);
+    uint64_t *hm = reinterpret_cast<uint64_t *>(hp + b_segs + b_qseg);
+    for (size_t q = 0; q < nq; q++)
+        for (int w = 0; w < W; w++) hm[q * W + w] = uinfo[q] ? uinfo[q]->mask[w] : 0ull;
+    if (ws.segs.ensure(std::max<size_t>(b_segs, 16)) != 0) return RK_ERR_CUDA;
+    if (ws.qseg.ensure(b_qseg) != 0) return RK_ERR_CUDA;
+    if (ws.qmask.ensure(std::max<size_t>(b_qmask, 16)) != 0) return RK_ERR_CUDA;
+    if (ws.ctl.ensure(64) != 0) return RK_ERR_CUDA;
+    if (nseg) RK_CUDA(cudaMemcpyAsync(ws.segs.p, hp, b_segs, cudaMemcpyHostToDevice, ws.stream));
+    RK_CUDA(cudaMemcpyAsync(ws.qseg.p, hp + b_segs, b_qseg, cudaMemcpyHostToDevice, ws.stream));
+    if (b_qmask) RK_CUDA(cudaMemcpyAsync(ws.qmask.p, hm, b_qmask, cudaMemcpyHostToDevice, ws.stream));
+    uint32_t *hc = reinterpret_cast<uint32_t *>(hp + b_segs + b_qseg + b_qmask);
+    hc = reinterpret_cast<uint32_t *>(((uintptr_t) hc + 15) & ~(uintptr_t) 15);
+    hc[0] = nseg; hc[1] = 0;
+    RK_CUDA(cudaMemcpyAsync(ws.ctl.p, hc, 8, cudaMemcpyHostToDevice, ws.stream));
+    RK_CUDA(cudaEventRecord(ws.ev_plan[pi_], ws.stream));
+    ws.ev_plan_used[pi_] = true;
+
+    ws.segments = nseg;
+    ws.rows_scanned = total_rows;
+    ws.algo_bytes = total_rows * row_bytes + mask_bytes + (uint64_t) nq * 12ull * (uint64_t) o->k;
+    *out_nseg = nseg;
+    return 0;
+}
+
+int rk_ensure_cand(Workspace &ws, size_t nlists, int k)
+{
+    const size_t n = std::max<size_t>(nlists, 1) * (size_t) k;
+    if (ws.cand_key.ensure(n * 4) != 0) return RK_ERR_CUDA;
+    if (ws.cand_tid.ensure(n * 8) != 0) return RK_ERR_CUDA;
+    if (ws.cand_row.ensure(n * 4) != 0) return RK_ERR_CUDA;
+    if (ws.cand_count.ensure(std::max<size_t>(nlists, 1) * 4) != 0) return RK_ERR_CUDA;
+    return 0;
+}
+
+void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &p, bool ivf_store, const float *dQ,
+                         const rk_scan_opts *o, int k)
+{
+    memset(&p, 0, sizeof p);
+    if (ivf_store) {
+        p.store.x = ix->ivf.d_x.as<float>();
+        p.store.tid = ix->ivf.d_tid.as<uint64_t>();
+        p.store.rowdoc = ix->ivf.d_rowdoc.as<uint32_t>();
+    } else {
+        p.store.x = ix->d_x.as<float>();
+        p.store.tid = ix->d_tid.as<uint64_t>();
+        p.store.rowdoc = ix->d_rowdoc.as<uint32_t>();
+    }
+    p.store.rows = ix->nrows;
+    p.doc_mask = ix->d_doc_mask.as<uint64_t>();
+    p.qmask = ws.qmask.as<uint64_t>();
+    p.mask_words = ix->mask_words;
+    p.ext_row = ix->d_ext_row.as<uint32_t>();
+    p.ext_vstart = ix->d_ext_vstart.as<uint32_t>();
+    p.ext_mask = ix->d_ext_mask.as<uint64_t>();
+    p.part_ext_off = ix->d_part_ext_off.as<uint32_t>();
+    p.q = dQ;
+    p.null_query = o->null_query;
+    p.segs = ws.segs.as<RkSegment>();
+    p.nseg_ptr = ws.ctl.as<uint32_t>();
+    p.seg_counter = ws.ctl.as<uint32_t>() + 1;
+    p.cand_key = ws.cand_key.as<uint32_t>();
+    p.cand_tid = ws.cand_tid.as<uint64_t>();
+    p.cand_row = ws.cand_row.as<uint32_t>();
+    p.cand_count = ws.cand_count.as<int32_t>();
+    p.dim4 = ix->dim_pad / 4;
+    p.row_bytes = ix->dim_pad * 4;
+    p.tile_rows = ix->tile_rows;
+    p.nstages = ix->nstages;
+    p.k = k;
+    p.metric = ix->metric;
+}
+
+// One batch on device: dQ [nq][dim_pad].  `out` carries the destination pointers (device).
+static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids,
+                         const rk_scan_opts *o, int probe_offset, RkSelectParams out)
+{
+    RK_CUDA(cudaSetDevice(ix->device));
+    ws.launches = 0;
+    ws.timed_scan = ws.timed_select = ws.timed_probe = false;
+    if (nq == 0) return RK_OK;
+    if (o->probes > 0) return rk_ivf_search(ix, ws, nq, dQ, user_ids, o, probe_offset, out);
+
+    uint32_t nseg = 0;
+    int rc = build_exact_plan(ix, ws, nq, user_ids, o, &nseg);
+    if (rc < 0) return rc;
+    if (rk_ensure_cand(ws, nseg, o->k) != 0) return RK_ERR_CUDA;
+    if (nseg) {
+        RkScanParams p;
+        rk_fill_scan_params(ix, ws, p, false, dQ, o, o->k);
+        if (ws.timing) RK_CUDA(cudaEventRecord(ws.ev[0], ws.stream));
+        const int grid = (int) std::min<uint32_t>((uint32_t) ix->sm_count, nseg);
+        RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid));
+        if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ev[1], ws.stream)); ws.timed_scan = true; }
+        ws.launches++;
+    }
+    out.cand_key = ws.cand_key.as<uint32_t>();
+    out.cand_tid = ws.cand_tid.as<uint64_t>();
+    out.cand_row = ws.cand_row.as<uint32_t>();
+    out.cand_count = ws.cand_count.as<int32_t>();
+    out.qseg = ws.qseg.as<uint32_t>();
+    out.lists_per_query = 0;
+    out.list_stride = o->k;
+    out.k = o->k;
+    out.metric = ix->metric;
+    out.dedup = o->keep_duplicates ? 0 : 1;
+    out.null_query = o->null_query;
+    out.key_is_float = 0;
+    out.rowdoc = ix->d_rowdoc.as<uint32_t>();
+    out.doc_ids = ix->d_doc_ids.as<uint32_t>();
+    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ev[2], ws.stream));
+    RK_CUDA(rk_launch_select(out, (int) nq, ws.stream));
+    if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ev[3], ws.stream)); ws.timed_select = true; }
+    ws.launches++;
+    ix->total_launches += ws.launches;
+    return RK_OK;
+}
+
+static int collect_timing(rk_index *ix, Workspace &ws)
+{
+    if (!ws.timing) return 0;
+    if (ws.timed_scan) { RK_CUDA(cudaEventSynchronize(ws.ev[1])); RK_CUDA(cudaEventElapsedTime(&ix->last_scan_ms, ws.ev[0], ws.ev[1])); }
+    if (ws.timed_select) { RK_CUDA(cudaEventSynchronize(ws.ev[3])); RK_CUDA(cudaEventElapsedTime(&ix->last_select_ms, ws.ev[2], ws.ev[3])); }
+    if (ws.timed_probe) { RK_CUDA(cudaEventSynchronize(ws.ev[5])); RK_CUDA(cudaEventElapsedTime(&ix->last_probe_ms, ws.ev[4], ws.ev[5])); }
+    return 0;
+}
+
+// Copy host queries into ws.dq, padded to dim_pad.
+static int stage_queries(rk_index *ix, Workspace &ws, size_t nq, const float *Q)
+{
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    if (ws.dq.ensure(std::max<size_t>(nq * rb, 16)) != 0) return RK_ERR_CUDA;
+    if (ix->dim == ix->dim_pad) {
+        RK_CUDA(cudaMemcpyAsync(ws.dq.p, Q, nq * rb, cudaMemcpyHostToDevice, ws.stream));
+    } else {
+        RK_CUDA(cudaMemsetAsync(ws.dq.p, 0, nq * rb, ws.stream));
+        RK_CUDA(cudaMemcpy2DAsync(ws.dq.p, rb, Q, (size_t) ix->dim * 4, (size_t) ix->dim * 4, nq, cudaMemcpyHostToDevice, ws.stream));
+    }
+    return 0;
+}
+
+static int host_search(rk_index *ix, Workspace &ws, size_t nq, const float *Q, const uint32_t *user_ids,
+                       const rk_scan_opts *o, int probe_offset, uint64_t *out_tid, uint32_t *out_doc, double *out_dist,
+                       int32_t *out_count)
+{
+    RK_CUDA(cudaSetDevice(ix->device));
+    if (!o->null_query) {
+        for (size_t i = 0; i < nq * (size_t) ix->dim; i++)
+            if (!std::isfinite(Q[i])) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
+    }
+    int rc = stage_queries(ix, ws, nq, Q);
+    if (rc < 0) return rc;
+    const size_t nk = nq * (size_t) o->k;
+    if (ws.out_tid.ensure(std::max<size_t>(nk * 8, 16)) != 0 || ws.out_doc.ensure(std::max<size_t>(nk * 4, 16)) != 0 ||
+        ws.out_dist.ensure(std::max<size_t>(nk * 8, 16)) != 0 || ws.out_count.ensure(std::max<size_t>(nq * 4, 16)) != 0)
+        return RK_ERR_CUDA;
+    RkSelectParams out;
+    memset(&out, 0, sizeof out);
+    out.out_tid = ws.out_tid.as<uint64_t>();
+    out.out_doc = out_doc ? ws.out_doc.as<uint32_t>() : nullptr;
+    out.out_dist = ws.out_dist.as<double>();
+    out.out_count = ws.out_count.as<int32_t>();
+    rc = search_device(ix, ws, nq, ws.dq.as<float>(), user_ids, o, probe_offset, out);
+    if (rc < 0) return rc;
+    RK_CUDA(cudaMemcpyAsync(out_tid, ws.out_tid.p, nk * 8, cudaMemcpyDeviceToHost, ws.stream));
+    if (out_doc) RK_CUDA(cudaMemcpyAsync(out_doc, ws.out_doc.p, nk * 4, cudaMemcpyDeviceToHost, ws.stream));
+    RK_CUDA(cudaMemcpyAsync(out_dist, ws.out_dist.p, nk * 8, cudaMemcpyDeviceToHost, ws.stream));
+    RK_CUDA(cudaMemcpyAsync(out_count, ws.out_count.p, nq * 4, cudaMemcpyDeviceToHost, ws.stream));
+    RK_CUDA(cudaStreamSynchronize(ws.stream));
+    return collect_timing(ix, ws);
+}
+
+extern "C" int rk_search_batch(rk_index *ix, size_t nq, const float *Q, const uint32_t *user_ids, const rk_scan_opts *o,
+                               uint64_t *out_tid, uint32_t *out_doc, double *out_dist, int32_t *out_count)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (!ix->finalized) return rk_fail(RK_ERR_STATE, "rk_search_batch: call rk_finalize first");
+    int rc = validate_opts(ix, o);
+    if (rc < 0) return rc;
+    if (nq == 0) return RK_OK;
+    if (!Q || !out_tid || !out_dist || !out_count) return rk_fail(RK_ERR_INVALID, "rk_search_batch: NULL buffer");
+    if (!user_ids && o->filter != RK_FILTER_NONE) return rk_fail(RK_ERR_INVALID, "rk_search_batch: user_ids is NULL");
+    return host_search(ix, ix->ws, nq, Q, user_ids, o, 0, out_tid, out_doc, out_dist, out_count);
+}
+
+extern "C" int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                                      const rk_scan_opts *o, uint64_t *d_out_tid, uint32_t *d_out_doc,
+                                      double *d_out_dist, int32_t *d_out_count)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (!ix->finalized) return rk_fail(RK_ERR_STATE, "rk_search_batch_device: call rk_finalize first");
+    int rc = validate_opts(ix, o);
+    if (rc < 0) return rc;
+    if (nq == 0) return RK_OK;
+    if (!dQ) return rk_fail(RK_ERR_INVALID, "rk_search_batch_device: NULL query pointer");
+    if (ix->dim != ix->dim_pad) return rk_fail(RK_ERR_UNSUPPORTED, "device queries need dim %% 4 == 0 (dim = %d)", ix->dim);
+    RkSelectParams out;
+    memset(&out, 0, sizeof out);
+    out.out_tid = d_out_tid; out.out_doc = d_out_doc; out.out_dist = d_out_dist; out.out_count = d_out_count;
+    return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
+}
+
+extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                                     const rk_scan_opts *o, float *d_key, uint64_t *d_tid, uint32_t *d_doc)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (!ix->finalized) return rk_fail(RK_ERR_STATE, "rk_search_batch_shard: call rk_finalize first");
+    int rc = validate_opts(ix, o);
+    if (rc < 0) return rc;
+    if (nq == 0) return RK_OK;
+    if (!dQ || !d_key || !d_tid) return rk_fail(RK_ERR_INVALID, "rk_search_batch_shard: NULL pointer");
+    if (ix->dim != ix->dim_pad) return rk_fail(RK_ERR_UNSUPPORTED, "device queries need dim %% 4 == 0 (dim = %d)", ix->dim);
+    RkSelectParams out;
+    memset(&out, 0, sizeof out);
+    out.out_key = d_key; out.out_tid = d_tid; out.out_doc = d_doc;
+    return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
+}
+
+extern "C" int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, const float *d_key, const uint64_t *d_tid,
+                               const uint32_t *d_doc, uint64_t *d_out_tid, uint32_t *d_out_doc, double *d_out_dist,
+                               int32_t *d_out_count)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (k < 1 || k > RK_MAX_K || n_shards < 1) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: k = %d, n_shards = %d", k, n_shards);
+    if (!d_key || !d_tid) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: NULL pointer");
+    if (nq == 0) return RK_OK;
+    RK_CUDA(cudaSetDevice(ix->device));
+    RkSelectParams p;
+    memset(&p, 0, sizeof p);
+    p.cand_key = reinterpret_cast<const uint32_t *>(d_key);
+    p.cand_tid = d_tid;
+    p.cand_row = d_doc ? d_doc : reinterpret_cast<const uint32_t *>(d_key);   // doc ids ride in the row slot
+    p.cand_count = nullptr;
+    p.lists_per_query = n_shards;
+    p.list_stride = k;
+    p.k = k;
+    p.metric = ix->metric;
+    p.dedup = 0;   // a physical row lives on exactly one shard
+    p.key_is_float = 1;
+    p.rowdoc = nullptr;
+    p.out_tid = d_out_tid; p.out_doc = d_doc ? d_out_doc : nullptr; p.out_dist = d_out_dist; p.out_count = d_out_count;
+    Workspace &ws = ix->ws;
+    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ev[2], ws.stream));
+    RK_CUDA(rk_launch_select(p, (int) nq, ws.stream));
+    if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ev[3], ws.stream)); ws.timed_select = true; }
+    ws.launches = 1;
+    ix->total_launches += 1;
+    return RK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the index-scan iterator (pgvector/src/ivfscan.c:241-406)
+
+extern "C" rk_scan *rk_beginscan(rk_index *ix)
+{
+    if (!ix) { rk_fail(RK_ERR_INVALID, "NULL index"); return nullptr; }
+    if (!ix->finalized) { rk_fail(RK_ERR_STATE, "rk_beginscan: call rk_finalize first"); return nullptr; }
+    rk_scan *sc = new rk_scan();
+    sc->ix = ix;
+    if (sc->ws.init(ix->device) != 0) { delete sc; return nullptr; }
+    return sc;
+}
+
+static int scan_fetch_batch(rk_scan *sc)
+{
+    rk_index *ix = sc->ix;
+    const int k = sc->opts.k;
+    sc->r_tid.resize(k); sc->r_doc.resize(k); sc->r_dist.resize(k);
+    int32_t cnt = 0;
+    rk_scan_opts o = sc->opts;
+    o.probes = sc->probes_eff;
+    int rc = host_search(ix, sc->ws, 1, sc->q.data(), &sc->user, &o, sc->probes_done, sc->r_tid.data(), sc->r_doc.data(),
+                         sc->r_dist.data(), &cnt);
+    if (rc < 0) return rc;
+    sc->r_count = cnt;
+    sc->r_pos = 0;
+    sc->probes_done += sc->probes_eff;
+    return 0;
+}
+
+extern "C" int rk_rescan(rk_scan *sc, const float *q, int32_t q_dim, uint32_t user_id, const rk_scan_opts *o)
+{
+    if (!sc) return rk_fail(RK_ERR_INVALID, "NULL scan");
+    rk_index *ix = sc->ix;
+    int rc = validate_opts(ix, o);
+    if (rc < 0) return rc;
+    if (!q && !o->null_query) return rk_fail(RK_ERR_NO_ORDER, "cannot scan without order");   // ivfscan.c:360-361
+    if (q && q_dim != ix->dim) return rk_fail(RK_ERR_DIM, "different vector dimensions %d and %d", ix->dim, q_dim);   // vector.c:61-67
+    sc->q.assign((size_t) ix->dim, 0.0f);
+    if (q) memcpy(sc->q.data(), q, (size_t) ix->dim * 4);
+    sc->user = user_id;
+    sc->opts = *o;
+    sc->probes_done = 0;
+    if (o->probes > 0) {
+        // ivfscan.c:257-266: maxProbes = max(max_probes, probes) when iterating, both clamped to lists
+        int lists = ix->ivf.lists;
+        sc->probes_eff = std::min(o->probes, lists);
+        sc->max_probes_eff = std::min(std::max(o->max_probes, o->probes), lists);
+    } else {
+        sc->probes_eff = 0;
+        sc->max_probes_eff = 0;
+    }
+    sc->bound = true;
+    return scan_fetch_batch(sc);
+}
+
+extern "C" int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *distance)
+{
+    if (!sc) return rk_fail(RK_ERR_INVALID, "NULL scan");
+    if (!sc->bound) return rk_fail(RK_ERR_NO_ORDER, "cannot scan without order");
+    while (sc->r_pos >= sc->r_count) {
+        // ivfscan.c:375-381: refill from the next `probes` lists until max_probes is reached
+        if (sc->probes_eff == 0 || sc->probes_done >= sc->max_probes_eff) return 0;
+        int rc = scan_fetch_batch(sc);
+        if (rc < 0) return rc;
+    }
+    if (tid) *tid = sc->r_tid[sc->r_pos];
+    if (doc) *doc = sc->r_doc[sc->r_pos];
+    if (distance) *distance = sc->r_dist[sc->r_pos];
+    sc->r_pos++;
+    return 1;
+}
+
+extern "C" void rk_endscan(rk_scan *sc)
+{
+    if (!sc) return;
+    cudaSetDevice(sc->ix->device);
+    if (sc->ws.stream) cudaStreamSynchronize(sc->ws.stream);
+    sc->ws.destroy();
+    delete sc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// plumbing
+
+extern "C" int rk_set_stream(rk_index *ix, void *cuda_stream)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    ix->ws.stream = cuda_stream ? (cudaStream_t) cuda_stream : ix->ws.own_stream;
+    return RK_OK;
+}
+
+extern "C" int rk_synchronize(rk_index *ix)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    RK_CUDA(cudaSetDevice(ix->device));
+    RK_CUDA(cudaStreamSynchronize(ix->ws.stream));
+    return collect_timing(ix, ix->ws);
+}
+
+extern "C" int rk_enable_timing(rk_index *ix, int on)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    ix->ws.timing = on != 0;
+    return RK_OK;
+}
+
+extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)
+{
+    if (!ix || !out) return rk_fail(RK_ERR_INVALID, "NULL argument");
+    memset(out, 0, sizeof *out);
+    out->rows = ix->nrows;
+    out->docs = ix->doc_ids.size();
+    out->partitions = ix->parts.size();
+    out->device_bytes = ix->device_bytes;
+    out->launches = ix->ws.launches;
+    out->segments = ix->ws.segments;
+    out->rows_scanned = ix->ws.rows_scanned;
+    out->algo_bytes = ix->ws.algo_bytes;
+    out->scan_ms = ix->last_scan_ms;
+    out->select_ms = ix->last_select_ms;
+    out->probe_ms = ix->last_probe_ms;
+    out->total_launches = ix->total_launches;
+    return RK_OK;
+}

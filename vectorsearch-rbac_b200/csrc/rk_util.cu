@@ -1,0 +1,42 @@
+// rk_util.cu — layout helpers run once at load / index-build time (not on the query path).
+#include "rk_common.cuh"
+#include "rk_kernels.h"
+
+// dst[i][:] = src[perm[i]][:]  (rows of dim_pad floats, float4 granularity)
+__global__ void rk_gather_rows_kernel(const float4 *__restrict__ src, float4 *__restrict__ dst,
+                                      const uint32_t *__restrict__ perm, size_t n, int dim4)
+{
+    const size_t total = n * (size_t) dim4;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < total; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / dim4;
+        const int c = (int) (i % dim4);
+        dst[i] = src[(size_t) perm[r] * dim4 + c];
+    }
+}
+
+// dst[n][dim_pad] = src[n][dim] zero-padded
+__global__ void rk_pad_rows_kernel(const float *__restrict__ src, float *__restrict__ dst, size_t n, int dim, int dim_pad)
+{
+    const size_t total = n * (size_t) dim_pad;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < total; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / dim_pad;
+        const int c = (int) (i % dim_pad);
+        dst[i] = c < dim ? src[r * dim + c] : 0.0f;
+    }
+}
+
+cudaError_t rk_launch_gather_rows(const float *src, float *dst, const uint32_t *perm, size_t n, int dim_pad,
+                                  cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    rk_gather_rows_kernel<<<148 * 8, 256, 0, stream>>>(reinterpret_cast<const float4 *>(src),
+                                                       reinterpret_cast<float4 *>(dst), perm, n, dim_pad / 4);
+    return cudaGetLastError();
+}
+
+cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, int dim_pad, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    rk_pad_rows_kernel<<<148 * 8, 256, 0, stream>>>(src, dst, n, dim, dim_pad);
+    return cudaGetLastError();
+}
