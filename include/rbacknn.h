@@ -104,6 +104,10 @@ int rk_abi_version(void);
  * Rejects NaN/Inf like vector_in (vector.c:102-113). */
 int rk_load_rows(rk_index *ix, const float *x, const uint64_t *tid, const uint32_t *doc, size_t n);
 
+/* Same, with x[n*dim] already resident in HBM on the index's device (tid / doc stay host arrays).
+ * The NaN/Inf check runs as a kernel. */
+int rk_load_rows_device(rk_index *ix, const float *d_x, const uint64_t *tid, const uint32_t *doc, size_t n);
+
 /* Optional: size the HBM row store once for n rows before a chunked rk_load_rows sequence. */
 int rk_reserve_rows(rk_index *ix, size_t n);
 
@@ -189,11 +193,13 @@ int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint3
  * ascending, padded with (+Inf, UINT64_MAX).  d_key/d_tid/d_doc are device buffers [nq*k]. */
 int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
                           const rk_scan_opts *o, float *d_key, uint64_t *d_tid, uint32_t *d_doc);
-/* G-way select over all-gathered shard results laid out [G][nq][k]; writes the final
- * [nq][k] like rk_search_batch_device.  Device pointers. */
-int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, const float *d_key,
-                    const uint64_t *d_tid, const uint32_t *d_doc, uint64_t *d_out_tid,
-                    uint32_t *d_out_doc, double *d_out_dist, int32_t *d_out_count);
+/* G-way select over all-gathered shard results; writes the final [nq][k] like
+ * rk_search_batch_device.  Device pointers.  Shard j's block of each array starts
+ * shard_stride_bytes * j bytes after shard 0's (0 = dense [G][nq][k] arrays), so one all-gather of
+ * a packed per-rank buffer {key[nq*k] | doc[nq*k] | tid[nq*k]} can feed it directly. */
+int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, size_t shard_stride_bytes,
+                    const float *d_key, const uint64_t *d_tid, const uint32_t *d_doc,
+                    uint64_t *d_out_tid, uint32_t *d_out_doc, double *d_out_dist, int32_t *d_out_count);
 
 /* ---- plumbing ------------------------------------------------------------------------------- */
 
@@ -221,6 +227,10 @@ typedef struct rk_stats {
 int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */
 int rk_enable_timing(rk_index *ix, int on);
+/* Durations (ms) of the most recent scan-kernel launches made with timing enabled, newest last;
+ * up to RK_TIMING_RING are kept.  Synchronizes the index stream.  Returns how many were written. */
+#define RK_TIMING_RING 64
+int rk_get_scan_times(rk_index *ix, float *out_ms, int max_n);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

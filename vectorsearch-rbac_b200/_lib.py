@@ -40,6 +40,7 @@ SIGNATURES = {
     "rk_last_error": (C.c_char_p, []),
     "rk_abi_version": (C.c_int, []),
     "rk_load_rows": (C.c_int, [_P, _P, _P, _P, C.c_size_t]),
+    "rk_load_rows_device": (C.c_int, [_P, _P, _P, _P, C.c_size_t]),
     "rk_reserve_rows": (C.c_int, [_P, C.c_size_t]),
     "rk_set_doc_roles": (C.c_int, [_P, _P, _P, C.c_size_t]),
     "rk_set_user_roles": (C.c_int, [_P, _P, _P, C.c_size_t]),
@@ -58,11 +59,12 @@ SIGNATURES = {
     "rk_search_batch": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_search_batch_device": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_search_batch_shard": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P]),
-    "rk_merge_shards": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, _P]),
+    "rk_merge_shards": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_size_t, _P, _P, _P, _P, _P, _P, _P]),
     "rk_set_stream": (C.c_int, [_P, _P]),
     "rk_synchronize": (C.c_int, [_P]),
     "rk_get_stats": (C.c_int, [_P, C.POINTER(RkStats)]),
     "rk_enable_timing": (C.c_int, [_P, C.c_int]),
+    "rk_get_scan_times": (C.c_int, [_P, _P, C.c_int]),
 }
 
 

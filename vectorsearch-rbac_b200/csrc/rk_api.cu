@@ -91,6 +91,8 @@ int Workspace::init(int device_)
     RK_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
     stream = own_stream;
     for (auto &e : ev) RK_CUDA(cudaEventCreate(&e));
+    for (auto &e : ring_a) RK_CUDA(cudaEventCreate(&e));
+    for (auto &e : ring_b) RK_CUDA(cudaEventCreate(&e));
     for (auto &e : ev_plan) RK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     return 0;
 }
@@ -105,6 +107,10 @@ void Workspace::destroy()
     for (auto &e : ev_plan)
         if (e) cudaEventDestroy(e);
     for (auto &e : ev)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : ring_a)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : ring_b)
         if (e) cudaEventDestroy(e);
     if (own_stream) cudaStreamDestroy(own_stream);
     own_stream = nullptr;
@@ -194,6 +200,38 @@ extern "C" int rk_load_rows(rk_index *ix, const float *x, const uint64_t *tid, c
     } else {
         RK_CUDA(cudaMemset(dst, 0, n * rb));
         RK_CUDA(cudaMemcpy2D(dst, rb, x, (size_t) ix->dim * 4, (size_t) ix->dim * 4, n, cudaMemcpyHostToDevice));
+    }
+    ix->h_tid.insert(ix->h_tid.end(), tid, tid + n);
+    ix->h_doc.insert(ix->h_doc.end(), doc, doc + n);
+    ix->nrows += n;
+    return RK_OK;
+}
+
+extern "C" int rk_load_rows_device(rk_index *ix, const float *d_x, const uint64_t *tid, const uint32_t *doc, size_t n)
+{
+    if (!ix || (!d_x && n) || (!tid && n) || (!doc && n)) return rk_fail(RK_ERR_INVALID, "rk_load_rows_device: NULL argument");
+    if (ix->finalized) return rk_fail(RK_ERR_STATE, "rk_load_rows_device: index already finalized");
+    if (n == 0) return RK_OK;
+    if (ix->nrows + n >= 0xFFFFFFF0ull) return rk_fail(RK_ERR_UNSUPPORTED, "rk_load_rows_device: more than 2^32 rows");
+    RK_CUDA(cudaSetDevice(ix->device));
+    unsigned long long bad = 0;
+    RK_CUDA(rk_count_nonfinite(d_x, n * (size_t) ix->dim, &bad, 0));
+    if (bad) return rk_fail(RK_ERR_NONFINITE, "rk_load_rows_device: NaN or infinite value not allowed in vector");
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    const size_t need = (ix->nrows + n) * rb;
+    if (need > ix->d_x.cap) {
+        DevBuf nb;
+        if (nb.ensure(std::max(need, ix->nrows ? ix->d_x.cap * 2 : need)) != 0) return RK_ERR_CUDA;
+        if (ix->nrows) RK_CUDA(cudaMemcpy(nb.p, ix->d_x.p, ix->nrows * rb, cudaMemcpyDeviceToDevice));
+        ix->d_x.release();
+        ix->d_x = nb;
+    }
+    unsigned char *dst = (unsigned char *) ix->d_x.p + ix->nrows * rb;
+    if (ix->dim == ix->dim_pad) {
+        RK_CUDA(cudaMemcpy(dst, d_x, n * rb, cudaMemcpyDeviceToDevice));
+    } else {
+        RK_CUDA(rk_launch_pad_rows(d_x, reinterpret_cast<float *>(dst), n, ix->dim, ix->dim_pad, 0));
+        RK_CUDA(cudaDeviceSynchronize());
     }
     ix->h_tid.insert(ix->h_tid.end(), tid, tid + n);
     ix->h_doc.insert(ix->h_doc.end(), doc, doc + n);

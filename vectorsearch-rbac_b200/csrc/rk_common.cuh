@@ -70,6 +70,7 @@ struct RkSelectParams {
     const uint32_t *qseg;       // [nq+1] segment range per query
     int lists_per_query;        // if > 0: query q owns lists [q*L, (q+1)*L) (shard merge / fixed plans) and qseg is ignored
     int list_stride;            // entries between consecutive lists
+    size_t shard_stride_bytes;  // fixed-list mode: bytes between list j and j+1 of one array (0 = dense nq*k elements)
     int k;
     int metric;
     int dedup;

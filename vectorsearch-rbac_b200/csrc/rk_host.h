@@ -40,6 +40,8 @@ struct Workspace {
     DevBuf probe_key, probe_list;        // IVF: per-query selected lists
     DevBuf ex_key, ex_tid, ex_doc;       // exchange-form results
     PinBuf h_plan_ring[2], h_out;        // plan staging alternates so the host may run one batch ahead
+    cudaEvent_t ring_a[RK_TIMING_RING] = {}, ring_b[RK_TIMING_RING] = {};   // scan-kernel event pairs
+    uint64_t ring_n = 0;
     cudaEvent_t ev_plan[2] = {nullptr, nullptr};
     bool ev_plan_used[2] = {false, false};
     int plan_idx = 0;

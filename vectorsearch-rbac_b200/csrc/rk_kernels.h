@@ -15,3 +15,5 @@ cudaError_t rk_launch_select(const RkSelectParams &p, int nq, cudaStream_t strea
 cudaError_t rk_launch_gather_rows(const float *src, float *dst, const uint32_t *perm, size_t n, int dim_pad,
                                   cudaStream_t stream);
 cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, int dim_pad, cudaStream_t stream);
+// counts NaN / Inf elements of a device array (synchronous; result in *out)
+cudaError_t rk_count_nonfinite(const float *d_x, size_t n, unsigned long long *out, cudaStream_t stream);

@@ -32,10 +32,17 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     const uint32_t nl = l1 - l0;
     const int k = p.k;
 
-    // In fixed-list mode list j of query q lives at ((j * nq) + q) * k  ([G][nq][k] all-gather layout).
-    auto list_base = [&](uint32_t j) -> size_t {
-        return p.lists_per_query > 0 ? ((size_t) j * gridDim.x + q) * (size_t) p.list_stride
-                                     : (size_t) (l0 + j) * (size_t) p.list_stride;
+    // In fixed-list mode list j of query q lives at shard j's block + q * k; blocks are dense
+    // ([G][nq][k]) or shard_stride_bytes apart (packed all-gather buffer).  b4 / b8 index 4- and
+    // 8-byte arrays respectively.
+    const size_t dense = (size_t) gridDim.x * (size_t) p.list_stride;
+    const size_t st4 = p.shard_stride_bytes ? p.shard_stride_bytes / 4 : dense;
+    const size_t st8 = p.shard_stride_bytes ? p.shard_stride_bytes / 8 : dense;
+    auto b4 = [&](uint32_t j) -> size_t {
+        return p.lists_per_query > 0 ? (size_t) j * st4 + (size_t) q * p.list_stride : (size_t) (l0 + j) * (size_t) p.list_stride;
+    };
+    auto b8 = [&](uint32_t j) -> size_t {
+        return p.lists_per_query > 0 ? (size_t) j * st8 + (size_t) q * p.list_stride : (size_t) (l0 + j) * (size_t) p.list_stride;
     };
     auto list_count = [&](uint32_t j) -> int { return p.cand_count ? p.cand_count[p.lists_per_query > 0 ? j * gridDim.x + q : l0 + j] : k; };
 
@@ -47,7 +54,7 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     __syncthreads();
     // upper bound of the k-th best: any list holding k entries proves tau <= its last key
     for (uint32_t j = t; j < nl; j += RK_SEL_THREADS) {
-        if (list_count(j) >= k) atomicMin(&s_tau, load_key(list_base(j) + k - 1));
+        if (list_count(j) >= k) atomicMin(&s_tau, load_key(b4(j) + k - 1));
     }
     __syncthreads();
 
@@ -58,9 +65,9 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
             const uint32_t j = (uint32_t) (idx / k);
             const int i = (int) (idx % k);
             if (i < list_count(j)) {
-                const size_t a = list_base(j) + i;
+                const size_t a = b4(j) + i;
                 const uint32_t key = load_key(a);
-                const uint64_t tid = p.cand_tid[a];
+                const uint64_t tid = p.cand_tid[b8(j) + i];
                 // padding: sentinel key, or (+Inf, UINT64_MAX) in exchange form
                 const bool pad = key == RK_KEY_SENTINEL || (tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u);
                 if (key <= tau && !pad) {

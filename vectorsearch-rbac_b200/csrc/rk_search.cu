@@ -113,10 +113,11 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
         if (rc < 0) return rc;
         for (auto &pi : per_q[q]) total_rows += pi.rows_est;
     }
-    // segment sizing: ~8 segments per CTA for balance, but never below ~128 KB of row data
+    // segment sizing: ~32 segments per CTA so the tail of the dynamic schedule stays ~3 % of the
+    // launch, but never below ~128 KB of row data (a segment ends with a top-k compaction)
     const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4;
     uint64_t min_rows = std::max<uint64_t>((uint64_t) ix->tile_rows, (128 * 1024) / row_bytes);
-    uint64_t target = std::max<uint64_t>(min_rows, total_rows / ((uint64_t) ix->sm_count * 8) + 1);
+    uint64_t target = std::max<uint64_t>(min_rows, total_rows / ((uint64_t) ix->sm_count * 32) + 1);
 
     std::vector<RkSegment> segs;
     std::vector<uint32_t> qseg(nq + 1, 0);
@@ -240,10 +241,11 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
     if (nseg) {
         RkScanParams p;
         rk_fill_scan_params(ix, ws, p, false, dQ, o, o->k);
-        if (ws.timing) RK_CUDA(cudaEventRecord(ws.ev[0], ws.stream));
+        const int slot = (int) (ws.ring_n % RK_TIMING_RING);
+        if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot], ws.stream));
         const int grid = (int) std::min<uint32_t>((uint32_t) ix->sm_count, nseg);
         RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid));
-        if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ev[1], ws.stream)); ws.timed_scan = true; }
+        if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot], ws.stream)); ws.timed_scan = true; ws.ring_n++; }
         ws.launches++;
     }
     out.cand_key = ws.cand_key.as<uint32_t>();
@@ -271,7 +273,11 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
 static int collect_timing(rk_index *ix, Workspace &ws)
 {
     if (!ws.timing) return 0;
-    if (ws.timed_scan) { RK_CUDA(cudaEventSynchronize(ws.ev[1])); RK_CUDA(cudaEventElapsedTime(&ix->last_scan_ms, ws.ev[0], ws.ev[1])); }
+    if (ws.timed_scan && ws.ring_n) {
+        const int slot = (int) ((ws.ring_n - 1) % RK_TIMING_RING);
+        RK_CUDA(cudaEventSynchronize(ws.ring_b[slot]));
+        RK_CUDA(cudaEventElapsedTime(&ix->last_scan_ms, ws.ring_a[slot], ws.ring_b[slot]));
+    }
     if (ws.timed_select) { RK_CUDA(cudaEventSynchronize(ws.ev[3])); RK_CUDA(cudaEventElapsedTime(&ix->last_select_ms, ws.ev[2], ws.ev[3])); }
     if (ws.timed_probe) { RK_CUDA(cudaEventSynchronize(ws.ev[5])); RK_CUDA(cudaEventElapsedTime(&ix->last_probe_ms, ws.ev[4], ws.ev[5])); }
     return 0;
@@ -368,13 +374,14 @@ extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, c
     return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
 }
 
-extern "C" int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, const float *d_key, const uint64_t *d_tid,
-                               const uint32_t *d_doc, uint64_t *d_out_tid, uint32_t *d_out_doc, double *d_out_dist,
-                               int32_t *d_out_count)
+extern "C" int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, size_t shard_stride_bytes, const float *d_key,
+                               const uint64_t *d_tid, const uint32_t *d_doc, uint64_t *d_out_tid, uint32_t *d_out_doc,
+                               double *d_out_dist, int32_t *d_out_count)
 {
     if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
     if (k < 1 || k > RK_MAX_K || n_shards < 1) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: k = %d, n_shards = %d", k, n_shards);
     if (!d_key || !d_tid) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: NULL pointer");
+    if (shard_stride_bytes % 8) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: shard stride must be a multiple of 8 bytes");
     if (nq == 0) return RK_OK;
     RK_CUDA(cudaSetDevice(ix->device));
     RkSelectParams p;
@@ -385,6 +392,7 @@ extern "C" int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, con
     p.cand_count = nullptr;
     p.lists_per_query = n_shards;
     p.list_stride = k;
+    p.shard_stride_bytes = shard_stride_bytes;
     p.k = k;
     p.metric = ix->metric;
     p.dedup = 0;   // a physical row lives on exactly one shard
@@ -505,6 +513,21 @@ extern "C" int rk_enable_timing(rk_index *ix, int on)
     if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
     ix->ws.timing = on != 0;
     return RK_OK;
+}
+
+extern "C" int rk_get_scan_times(rk_index *ix, float *out_ms, int max_n)
+{
+    if (!ix || (!out_ms && max_n > 0)) return rk_fail(RK_ERR_INVALID, "NULL argument");
+    RK_CUDA(cudaSetDevice(ix->device));
+    RK_CUDA(cudaStreamSynchronize(ix->ws.stream));
+    Workspace &ws = ix->ws;
+    int n = (int) std::min<uint64_t>(ws.ring_n, RK_TIMING_RING);
+    if (n > max_n) n = max_n;
+    for (int i = 0; i < n; i++) {
+        const int slot = (int) ((ws.ring_n - (uint64_t) n + (uint64_t) i) % RK_TIMING_RING);
+        RK_CUDA(cudaEventElapsedTime(&out_ms[i], ws.ring_a[slot], ws.ring_b[slot]));
+    }
+    return n;
 }
 
 extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)

@@ -40,3 +40,25 @@ cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, 
     rk_pad_rows_kernel<<<148 * 8, 256, 0, stream>>>(src, dst, n, dim, dim_pad);
     return cudaGetLastError();
 }
+
+__global__ void rk_count_nonfinite_kernel(const float *__restrict__ x, size_t n, unsigned long long *out)
+{
+    unsigned long long c = 0;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
+        c += !isfinite(x[i]);
+    c = __reduce_add_sync(0xffffffffu, (unsigned) c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+cudaError_t rk_count_nonfinite(const float *d_x, size_t n, unsigned long long *out, cudaStream_t stream)
+{
+    unsigned long long *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, sizeof *d);
+    if (e != cudaSuccess) return e;
+    cudaMemsetAsync(d, 0, sizeof *d, stream);
+    rk_count_nonfinite_kernel<<<148 * 8, 256, 0, stream>>>(d_x, n, d);
+    e = cudaMemcpyAsync(out, d, sizeof *d, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(d);
+    return e;
+}

@@ -83,6 +83,13 @@ class Index:
         assert len(tid) == len(doc) == x.shape[0]
         _check(lib.rk_load_rows(self._h, x.ctypes.data, tid.ctypes.data, doc.ctypes.data, x.shape[0]))
 
+    def load_rows_device(self, d_x_ptr: int, n: int, tid: np.ndarray, doc: np.ndarray) -> None:
+        """Rows already resident in HBM: d_x_ptr is a raw device address of n*dim fp32."""
+        tid = np.ascontiguousarray(tid, dtype=np.uint64)
+        doc = _u32(doc)
+        assert len(tid) == len(doc) == n
+        _check(lib.rk_load_rows_device(self._h, d_x_ptr, tid.ctypes.data, doc.ctypes.data, n))
+
     def set_doc_roles(self, doc: Iterable[int], role: Iterable[int]) -> None:
         d, r = _u32(doc), _u32(role)
         _check(lib.rk_set_doc_roles(self._h, d.ctypes.data, r.ctypes.data, len(d)))
@@ -161,9 +168,9 @@ class Index:
         _check(lib.rk_search_batch_shard(self._h, nq, dQ_ptr, users.ctypes.data, C.byref(opts), d_key, d_tid, d_doc))
 
     def merge_shards(self, nq: int, k: int, n_shards: int, d_key: int, d_tid: int, d_doc: int, d_out_tid: int,
-                     d_out_doc: int, d_out_dist: int, d_out_count: int) -> None:
-        _check(lib.rk_merge_shards(self._h, nq, k, n_shards, d_key, d_tid, d_doc, d_out_tid, d_out_doc, d_out_dist,
-                                   d_out_count))
+                     d_out_doc: int, d_out_dist: int, d_out_count: int, shard_stride_bytes: int = 0) -> None:
+        _check(lib.rk_merge_shards(self._h, nq, k, n_shards, shard_stride_bytes, d_key, d_tid, d_doc, d_out_tid,
+                                   d_out_doc, d_out_dist, d_out_count))
 
     def begin_scan(self) -> "Scan":
         return Scan(self)
@@ -177,6 +184,12 @@ class Index:
 
     def enable_timing(self, on: bool = True) -> None:
         _check(lib.rk_enable_timing(self._h, int(on)))
+
+    def scan_times_ms(self, max_n: int = 64) -> np.ndarray:
+        """CUDA-event durations of the most recent scan-kernel launches (timing must be enabled)."""
+        out = np.zeros(max_n, dtype=np.float32)
+        n = _check(lib.rk_get_scan_times(self._h, out.ctypes.data, max_n))
+        return out[:n]
 
     def stats(self) -> dict:
         s = RkStats()

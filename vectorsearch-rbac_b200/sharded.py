@@ -1,0 +1,133 @@
+"""sharded.py — one process per GPU: a document-striped corpus searched by every rank, the ranks'
+local top-k exchanged with ONE all-gather over NVLink and merged by a G-way select kernel.
+
+The reference has no multi-GPU path; the closest thing it touches is FAISS's
+host-thread shards with a CPU merge (logical_partition_benchmark/benchmark/faiss/faiss/
+IndexShards.cpp:197-256).  Here:
+
+  partitioning   document d lives on rank  d mod G  (a document's rows and its role mask stay
+                 together, services/read_dataset_function.py:338-339 keeps them contiguous), so
+                 every role / combination / dynamic partition is split ~evenly over all ranks.
+  local search   Index.search_batch_shard -> per query k (fp32 key, doc, tid) triples, ascending,
+                 written into ONE packed device buffer  [key nq*k f32 | doc nq*k u32 | tid nq*k u64].
+  exchange       torch.distributed.all_gather_into_tensor of that buffer (16*nq*k bytes per rank).
+  merge          Index.merge_shards with shard_stride_bytes = 16*nq*k on every rank.
+
+A physical row lives on exactly one rank, so the merge needs no dedup; ties are broken by tuple id
+exactly as on one GPU, which makes the result independent of G.
+
+`local_search` / `merge` are injectable so the exchange logic is testable with the gloo backend on
+CPU (tests/test_sharded_gloo.py); the defaults are the CUDA paths and there is no CPU fallback.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import engine as _engine
+
+
+def owner_of_doc(doc_id: np.ndarray, world: int) -> np.ndarray:
+    """Rank that stores a document: d mod G."""
+    return (np.asarray(doc_id, dtype=np.int64) % world).astype(np.int32)
+
+
+def local_row_mask(row_doc: np.ndarray, rank: int, world: int) -> np.ndarray:
+    return owner_of_doc(row_doc, world) == rank
+
+
+def packed_bytes(nq: int, k: int) -> int:
+    return 16 * nq * k
+
+
+def split_packed(buf: torch.Tensor, nq: int, k: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Views (key f32[nq,k], doc i32[nq,k], tid i64[nq,k]) into one rank's packed exchange buffer."""
+    n = nq * k
+    key = buf[: 4 * n].view(torch.float32).view(nq, k)
+    doc = buf[4 * n: 8 * n].view(torch.int32).view(nq, k)
+    tid = buf[8 * n: 16 * n].view(torch.int64).view(nq, k)
+    return key, doc, tid
+
+
+class ShardedSearcher:
+    """Search over this rank's shard + all-gather merge.  `index` is this rank's engine.Index (already
+    loaded with the rows of the documents it owns, and finalized)."""
+
+    def __init__(self, index, rank: int, world: int, group=None, device: Optional[torch.device] = None,
+                 local_search: Optional[Callable] = None, merge: Optional[Callable] = None):
+        self.index, self.rank, self.world, self.group = index, rank, world, group
+        self.device = device if device is not None else torch.device("cuda", index.device)
+        self._local_search = local_search or self._cuda_local_search
+        self._merge = merge or self._cuda_merge
+        self._bufs = {}
+
+    # -- default (CUDA) stages ---------------------------------------------------------------
+    def _cuda_local_search(self, dQ: torch.Tensor, users: np.ndarray, opts, send: torch.Tensor) -> None:
+        nq = dQ.shape[0]
+        key, doc, tid = split_packed(send, nq, opts.k)
+        self.index.search_batch_shard(dQ.data_ptr(), nq, users, opts, key.data_ptr(), tid.data_ptr(), doc.data_ptr())
+
+    def _cuda_merge(self, recv: torch.Tensor, nq: int, k: int, out) -> None:
+        o_tid, o_doc, o_dist, o_cnt = out
+        n = nq * k
+        base = recv.data_ptr()
+        self.index.merge_shards(nq, k, self.world, base, base + 8 * n, base + 4 * n, o_tid.data_ptr(), o_doc.data_ptr(),
+                                o_dist.data_ptr(), o_cnt.data_ptr(), shard_stride_bytes=packed_bytes(nq, k))
+
+    # -- buffers -----------------------------------------------------------------------------
+    def _get_bufs(self, nq: int, k: int):
+        keyb = (nq, k)
+        if keyb not in self._bufs:
+            dev = self.device
+            nb = packed_bytes(nq, k)
+            self._bufs[keyb] = dict(
+                send=torch.empty(nb, dtype=torch.uint8, device=dev),
+                recv=torch.empty(nb * self.world, dtype=torch.uint8, device=dev),
+                tid=torch.empty((nq, k), dtype=torch.int64, device=dev),
+                doc=torch.empty((nq, k), dtype=torch.int32, device=dev),
+                dist=torch.empty((nq, k), dtype=torch.float64, device=dev),
+                cnt=torch.empty(nq, dtype=torch.int32, device=dev))
+        return self._bufs[keyb]
+
+    # -- public ------------------------------------------------------------------------------
+    def search_device(self, dQ: torch.Tensor, users: Sequence[int], opts):
+        """dQ [nq, dim] fp32 resident on this rank's device (identical on all ranks).  Returns device
+        tensors (tid i64 [nq,k] — the uint64 tuple ids bit-cast, doc i32, dist f64, count i32); every
+        rank holds the full merged result.  Asynchronous on the current stream."""
+        nq, k = dQ.shape[0], opts.k
+        users = np.ascontiguousarray(users, dtype=np.uint32)
+        b = self._get_bufs(nq, k)
+        self._local_search(dQ, users, opts, b["send"])
+        if self.world > 1:
+            dist.all_gather_into_tensor(b["recv"], b["send"], group=self.group)
+            recv = b["recv"]
+        else:
+            recv = b["send"]
+        self._merge(recv, nq, k, (b["tid"], b["doc"], b["dist"], b["cnt"]))
+        return b["tid"], b["doc"], b["dist"], b["cnt"]
+
+    def search(self, Q_host: torch.Tensor, users: Sequence[int], opts, out_host=None):
+        """End-to-end call with HOST buffers: Q_host is a (pinned) CPU tensor [nq, dim]; results come
+        back as CPU tensors (pinned when `out_host` supplies them).  Synchronous."""
+        dQ = Q_host.to(self.device, non_blocking=True)
+        tid, doc, dst, cnt = self.search_device(dQ, users, opts)
+        if out_host is None:
+            out_host = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=self.device.type == "cuda") for t in (tid, doc, dst, cnt))
+        for h, d in zip(out_host, (tid, doc, dst, cnt)):
+            h.copy_(d, non_blocking=True)
+        if self.device.type == "cuda":
+            torch.cuda.current_stream(self.device).synchronize()
+        return out_host
+
+
+def use_torch_stream(index, device: Optional[torch.device] = None) -> None:
+    """Run the index's kernels on torch's current CUDA stream so torch events and NCCL collectives
+    order with them."""
+    index.set_stream(torch.cuda.current_stream(device).cuda_stream)
+
+
+def make_opts(*a, **kw):
+    return _engine.make_opts(*a, **kw)
