@@ -320,6 +320,7 @@ def main():
     Q, qusers = make_queries(wl, args.nq, dev)
     Q = Q.contiguous()
     opts = vr.engine.make_opts(args.k, filter=flt, layout=vr.LAYOUT_ROLE if flt == vr.FILTER_PARTITION else 0)
+    torch.cuda.set_stream(torch.cuda.Stream(dev))     # a real stream: torch events, NCCL and the engine share it
     stream = torch.cuda.current_stream(dev)
     sharded.use_torch_stream(ix, dev)
     searcher = sharded.ShardedSearcher(ix, rank, world, device=dev)

@@ -488,13 +488,16 @@ extern "C" int rk_finalize(rk_index *ix)
         pi.ext_off = (uint32_t) ext_row.size();
         part_off.push_back(pi.ext_off);
         uint64_t v = 0;
+        pi.vstart.reserve(pi.docs.size() + 1);
         for (uint32_t d : pi.docs) {
             uint32_t r0 = ix->doc_row_start[d], r1 = ix->doc_row_start[d + 1];
             ext_row.push_back(r0);
             ext_vstart.push_back((uint32_t) v);
+            pi.vstart.push_back((uint32_t) v);
             for (int w = 0; w < W; w++) ext_mask.push_back(ix->doc_mask[(size_t) d * W + w]);
             v += r1 - r0;
         }
+        pi.vstart.push_back((uint32_t) v);
         pi.n_ext = (uint32_t) pi.docs.size();
         pi.rows = v;
         if (v >= 0xFFFFFFFFull) return rk_fail(RK_ERR_UNSUPPORTED, "rk_finalize: partition with 2^32 rows");

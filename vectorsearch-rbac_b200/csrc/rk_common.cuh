@@ -15,10 +15,11 @@
 // the work list so that the select kernel finds them as [qseg[q], qseg[q+1]).
 struct RkSegment {
     uint32_t query;   // index into the batch
-    uint32_t kind;    // RK_SEG_*
-    uint32_t src;     // partition id (extent table) for RK_SEG_EXTENTS
-    uint32_t flags;   // RK_SEGF_*
-    uint64_t begin;
+    uint16_t kind;    // RK_SEG_*
+    uint16_t flags;   // RK_SEGF_*
+    uint32_t ext_lo;  // RK_SEG_EXTENTS: global index of the first extent touching [begin, end) ...
+    uint32_t ext_hi;  // ... and one past the last (resolved on the host when the plan is built)
+    uint64_t begin;   // virtual row range inside the partition (EXTENTS) or physical rows (ROWS / ROWMASK)
     uint64_t end;
 };
 
@@ -40,7 +41,6 @@ struct RkScanParams {
     const uint32_t *ext_row;        // physical first row of each extent (+ sentinel per partition)
     const uint32_t *ext_vstart;     // virtual row offset of each extent inside its partition (+ sentinel = partition rows)
     const uint64_t *ext_mask;       // [extents][mask_words] role mask of the extent's document
-    const uint32_t *part_ext_off;   // [partitions+1] index into ext_*; partition p owns [off[p], off[p+1]-1) plus its sentinel
     // queries
     const float *q;                 // [nq][dim_pad]
     int null_query;                 // ORDER BY v <-> NULL: all distances 0
@@ -174,5 +174,23 @@ __device__ __forceinline__ void rk_bulk_g2s(void *smem_dst, const void *gmem_src
 __device__ __forceinline__ void rk_named_bar_sync(int id, int nthreads)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Named barrier that also ORs a predicate over all participating threads; every thread receives
+// the same result.
+__device__ __forceinline__ bool rk_named_bar_red_or(int id, int nthreads, bool pred)
+{
+    uint32_t r;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "setp.ne.u32 q, %3, 0;\n\t"
+        "barrier.cta.red.or.pred p, %1, %2, q;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(r)
+        : "r"(id), "r"(nthreads), "r"((uint32_t) pred)
+        : "memory");
+    return r != 0;
 }
 #endif  // __CUDACC__

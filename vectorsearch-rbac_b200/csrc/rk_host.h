@@ -58,6 +58,7 @@ struct PartInfo {
     uint32_t n_ext = 0;
     uint64_t rows = 0;
     std::vector<uint32_t> docs;   // dense document indices, ascending
+    std::vector<uint32_t> vstart; // [n_ext + 1] virtual row offset of each extent, last = rows
 };
 
 struct UserInfo {

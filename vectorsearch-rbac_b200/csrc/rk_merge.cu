@@ -11,7 +11,7 @@
 #include "rk_select.cuh"
 #include "rk_kernels.h"
 
-#define RK_SEL_THREADS 256
+#define RK_SEL_THREADS 512
 #define RK_SEL_CHUNK 1024
 
 __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelectParams p)
@@ -58,8 +58,36 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     }
     __syncthreads();
 
-    const size_t total = (size_t) nl * k;
-    for (size_t c0 = 0; c0 < total; c0 += RK_SEL_CHUNK) {
+    // Fast path: every list is sorted ascending, so the entries with key <= tau form a prefix of
+    // each list.  Walk the prefixes and gather them; only if they do not fit the buffer (more than
+    // RK_CAND_CAP entries tie below tau) fall back to the chunked scan with compactions.
+    __shared__ uint32_t s_overflow;
+    if (t == 0) s_overflow = 0;
+    __syncthreads();
+    {
+        const uint32_t tau = s_tau;
+        for (uint32_t j = t; j < nl; j += RK_SEL_THREADS) {
+            const int cnt = list_count(j);
+            const size_t a4 = b4(j), a8 = b8(j);
+            for (int i = 0; i < cnt; i++) {
+                const uint32_t key = load_key(a4 + i);
+                if (key > tau || key == RK_KEY_SENTINEL) break;
+                const uint64_t tid = p.cand_tid[a8 + i];
+                if (tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u) break;   // exchange-form padding
+                const uint32_t slot = atomicAdd(&s_count, 1u);
+                if (slot >= RK_CAND_CAP) { s_overflow = 1; break; }
+                s_key[slot] = key; s_tid[slot] = tid; s_row[slot] = p.cand_row[a4 + i];
+            }
+        }
+    }
+    __syncthreads();
+    const bool overflow = s_overflow != 0;
+    __syncthreads();
+    if (overflow && t == 0) s_count = 0;
+    __syncthreads();
+
+    const size_t total = overflow ? (size_t) nl * k : 0;
+    for (size_t c0 = 0; c0 < total || c0 == 0; c0 += RK_SEL_CHUNK) {
         const uint32_t tau = s_tau;
         for (size_t idx = c0 + t; idx < total && idx < c0 + RK_SEL_CHUNK; idx += RK_SEL_THREADS) {
             const uint32_t j = (uint32_t) (idx / k);
@@ -99,7 +127,7 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
                 // read my block into registers is unbounded; instead write through a second pass:
                 // entries only move left (pos <= i), and blocks are processed in index order per thread,
                 // but different threads may race, so stage keep flags first, then move after a barrier.
-                uint64_t mt[8]; uint32_t mk[8], mr[8]; int mp[8]; int mc = 0;   // per <= 8 since n <= 2048, 256 threads
+                uint64_t mt[8]; uint32_t mk[8], mr[8]; int mp[8]; int mc = 0;   // per <= 4 since n <= 2048, 512 threads
                 for (int i = b0; i < b1; i++) {
                     bool keepf = !(i > 0 && s_tid[i] == s_tid[i - 1] && s_key[i] == s_key[i - 1]);
                     if (keepf) { mt[mc] = s_tid[i]; mk[mc] = s_key[i]; mr[mc] = s_row[i]; mp[mc] = pos++; mc++; }

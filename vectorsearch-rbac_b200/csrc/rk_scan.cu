@@ -7,12 +7,18 @@
 // (controller/baseline/pg_row_security/row_level_security.py:55-65) is evaluated by the producer
 // warp BEFORE a row's bytes are requested, so masked-out rows cost no HBM traffic.
 //
-// Shape: persistent kernel, one CTA per SM.  Warp 8 is the producer: it pops segments from the
-// work list, resolves them to runs of physical rows (extent table, document mask or row mask) and
-// streams those rows into a shared-memory ring with 1-D bulk async copies (TMA unit, UBLKCP)
-// completing on mbarriers.  Warps 0-7 are consumers: 8 lanes per row, fp32 FMA, shuffle reduce,
-// threshold test against the CTA's running k-th best, append to a shared candidate buffer that is
-// compacted by a bitonic sort when it fills and at each segment end.
+// Shape: persistent kernel, one CTA per SM, dynamic segment scheduler.
+//   warp 8 (producer)  pops segments (claimed two ahead so the counter round trip and the segment
+//       descriptor load are off the critical path), resolves them to runs of physical rows (extent
+//       table + role-mask test, 128 extents per step) and streams those rows into a shared-memory
+//       ring with 1-D bulk async copies (TMA unit, SASS UBLKCP) completing on mbarriers.
+//   warps 0-7 (consumers)  run decoupled: each waits on a stage's full barrier, scores its own rows
+//       of the tile (8 lanes per row, fp32 FMA, shuffle reduce), tests them against the CTA's running
+//       k-th best and appends survivors (key, row) to a shared candidate buffer with one
+//       warp-aggregated atomic, then releases the stage.  They meet only at a checkpoint every
+//       RK_CKPT_ROWS rows and at segment ends, where one reducing barrier decides uniformly whether
+//       the buffer is compacted.  Compaction is an exact 4-pass radix select of the k-th smallest key
+//       (not a sort); tuple ids are gathered and the survivors sorted only when a segment ends.
 #include "rk_common.cuh"
 #include "rk_select.cuh"
 #include "rk_kernels.h"
@@ -20,6 +26,8 @@
 #define RK_CONS_WARPS 8
 #define RK_CONS_THREADS (RK_CONS_WARPS * 32)
 #define RK_SCAN_THREADS (RK_CONS_THREADS + 32)
+#define RK_CKPT_ROWS 512     // consumer warps meet at least every this many rows of a segment
+#define RK_EPL 4             // extents resolved per producer lane per step
 
 #define RK_FLAG_FIRST 1u
 #define RK_FLAG_LAST 2u
@@ -32,7 +40,7 @@ struct RkStageMeta {
 // Shared-memory carve-up, identical on host and device.
 struct RkScanSmem {
     uint32_t tile_bytes, off_tiles, off_qslot, off_qcur, off_rowid, off_ckey, off_crow, off_ctid, off_meta, off_bar,
-        off_misc, total;
+        off_hist, off_misc, total;
 };
 
 __host__ __device__ inline RkScanSmem rk_scan_smem_layout(int row_bytes, int tile_rows, int nstages)
@@ -51,7 +59,8 @@ __host__ __device__ inline RkScanSmem rk_scan_smem_layout(int row_bytes, int til
     o = (o + 15) & ~15u;
     s.off_meta = o; o += 16u * nstages;
     s.off_bar = o; o += 16u * nstages;
-    s.off_misc = o; o += 64;
+    s.off_hist = o; o += 256 * 4;
+    s.off_misc = o; o += 128;
     s.total = o;
     return s;
 }
@@ -62,6 +71,7 @@ size_t rk_scan_smem_bytes(int row_bytes, int tile_rows, int nstages)
 }
 
 // ---------------------------------------------------------------------------------------------
+// producer
 
 struct RkProducer {
     const RkScanParams &p;
@@ -135,7 +145,7 @@ struct RkProducer {
     __device__ __forceinline__ bool mask_hit(const uint64_t *m, const uint64_t *um) const
     {
         uint64_t acc = 0;
-        for (int w = 0; w < p.mask_words; w++) acc |= m[w] & um[w];
+        for (int w = 0; w < p.mask_words; w++) acc |= __ldg(m + w) & um[w];
         return acc != 0;
     }
 
@@ -147,48 +157,62 @@ struct RkProducer {
         if (s.kind == RK_SEG_ROWS) {
             emit_run(s.begin, s.end - s.begin);
         } else if (s.kind == RK_SEG_EXTENTS) {
-            // Partition = table of per-document extents.  32 extents are resolved per step, one per
-            // lane (coalesced loads of the extent table and, when the segment is masked, of the
-            // extent's 128-bit role mask); allowed extents are then streamed in order.
-            const uint32_t e0 = p.part_ext_off[s.src];
-            const uint32_t e1 = p.part_ext_off[s.src + 1] - 1;  // sentinel index
+            // Partition = table of per-document extents; the host resolved which extents touch
+            // [begin, end).  RK_EPL * 32 extents are resolved per step: every lane first tests the
+            // role masks of its RK_EPL extents (independent loads), then fetches row / virtual
+            // offsets only for the ones that passed; allowed extents are streamed in order and
+            // physically adjacent ones are fused into one longer copy.
             const bool masked = (s.flags & RK_SEGF_MASKED) != 0;
             const uint64_t *um = p.qmask + (size_t) query * p.mask_words;
-            uint32_t lo = e0, hi = e1;                       // last extent with vstart <= begin
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if ((uint64_t) p.ext_vstart[mid] <= s.begin) lo = mid; else hi = mid;
-            }
             uint64_t run_start = 0, run_len = 0;
-            for (uint32_t eb = lo; eb < e1; eb += 32) {
-                const uint32_t e = eb + lane;
-                bool ok = false, past = true;
-                uint64_t v0 = 0, v1 = 0, prow = 0;
-                if (e < e1) {
-                    const uint64_t vs = p.ext_vstart[e], ve = p.ext_vstart[e + 1];
-                    past = vs >= s.end;
-                    v0 = vs > s.begin ? vs : s.begin;
-                    v1 = ve < s.end ? ve : s.end;
-                    if (v1 > v0) {
-                        ok = masked ? mask_hit(p.ext_mask + (size_t) e * p.mask_words, um) : true;
-                        prow = (uint64_t) p.ext_row[e] + (v0 - vs);
+            for (uint32_t eb = s.ext_lo; eb < s.ext_hi; eb += 32 * RK_EPL) {
+                bool ok[RK_EPL];
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) {
+                    const uint32_t e = eb + j * 32 + lane;
+                    ok[j] = e < s.ext_hi;
+                    if (ok[j] && masked) ok[j] = mask_hit(p.ext_mask + (size_t) e * p.mask_words, um);
+                }
+                uint64_t prow[RK_EPL];
+                uint32_t plen[RK_EPL];
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) {
+                    prow[j] = 0; plen[j] = 0;
+                    if (ok[j]) {
+                        const uint32_t e = eb + j * 32 + lane;
+                        const uint64_t vs = __ldg(p.ext_vstart + e), ve = __ldg(p.ext_vstart + e + 1);
+                        const uint64_t v0 = vs > s.begin ? vs : s.begin;
+                        const uint64_t v1 = ve < s.end ? ve : s.end;
+                        if (v1 > v0) {
+                            prow[j] = (uint64_t) __ldg(p.ext_row + e) + (v0 - vs);
+                            plen[j] = (uint32_t) (v1 - v0);
+                        }
                     }
                 }
-                unsigned bal = __ballot_sync(0xffffffffu, ok);
-                while (bal) {
-                    const int b = __ffs(bal) - 1;
-                    bal &= bal - 1;
-                    const uint64_t r0 = __shfl_sync(0xffffffffu, prow, b);
-                    const uint64_t n = __shfl_sync(0xffffffffu, v1 - v0, b);
-                    if (run_len && run_start + run_len == r0) {
-                        run_len += n;                        // physically adjacent: one longer copy
-                    } else {
-                        if (run_len) emit_run(run_start, run_len);
-                        run_start = r0;
-                        run_len = n;
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) {
+                    unsigned bal = __ballot_sync(0xffffffffu, plen[j] != 0);
+                    while (bal) {
+                        const int b = __ffs(bal) - 1;
+                        bal &= bal - 1;
+                        const uint64_t r0 = __shfl_sync(0xffffffffu, prow[j], b);
+                        const uint64_t n = __shfl_sync(0xffffffffu, plen[j], b);
+                        if (run_len && run_start + run_len == r0) {
+                            run_len += n;                        // physically adjacent: one longer copy
+                        } else {
+                            if (run_len) emit_run(run_start, run_len);
+                            run_start = r0;
+                            run_len = n;
+                        }
                     }
                 }
-                if (__any_sync(0xffffffffu, past)) break;
+                // keep the pipeline fed: do not hold more than a few tiles of rows back while resolving
+                if (run_len >= 4u * (uint32_t) p.tile_rows) {
+                    const uint64_t n = run_len - (run_len % (uint32_t) p.tile_rows);
+                    emit_run(run_start, n);
+                    run_start += n;
+                    run_len -= n;
+                }
             }
             if (run_len) emit_run(run_start, run_len);
         } else {  // RK_SEG_ROWMASK
@@ -220,6 +244,7 @@ struct RkProducer {
 };
 
 // ---------------------------------------------------------------------------------------------
+// consumer helpers
 
 template <int METRIC>
 __device__ __forceinline__ void rk_acc(float4 &acc, const float4 &x, const float4 &q)
@@ -234,6 +259,89 @@ __device__ __forceinline__ void rk_acc(float4 &acc, const float4 &x, const float
     }
 }
 
+// Inclusive scan of one value per consumer thread (RK_CONS_THREADS threads); wsum = 8 words of smem.
+// Returns the inclusive prefix; *total receives the sum over all threads.  Two consumer barriers.
+template <typename Sync>
+__device__ __forceinline__ uint32_t rk_block_scan(uint32_t v, int t, volatile uint32_t *wsum, uint32_t *total, Sync sync)
+{
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+        if ((t & 31) >= o) inc += u;
+    }
+    sync();                                   // previous users of wsum are done
+    if ((t & 31) == 31) wsum[t >> 5] = inc;
+    sync();
+    uint32_t off = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < RK_CONS_WARPS; w++) {
+        const uint32_t x = wsum[w];
+        if (w < (t >> 5)) off += x;
+        tot += x;
+    }
+    *total = tot;
+    return off + inc;
+}
+
+// Exact k-th smallest (1-based) of key[0..n), n >= k, by a 4-pass 8-bit radix select over the
+// order-preserving uint keys.  All RK_CONS_THREADS consumer threads participate.
+template <typename Sync>
+__device__ __forceinline__ uint32_t rk_radix_kth(const uint32_t *key, int n, int k, uint32_t *hist, volatile uint32_t *wsum,
+                                                 volatile uint32_t *sel, int t, Sync sync)
+{
+    uint32_t prefix = 0, mask = 0, kk = (uint32_t) k;
+#pragma unroll 1
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        hist[t] = 0;
+        sync();
+        for (int i = t; i < n; i += RK_CONS_THREADS) {
+            const uint32_t kv = key[i];
+            if ((kv & mask) == prefix) atomicAdd(&hist[(kv >> shift) & 255u], 1u);
+        }
+        sync();
+        const uint32_t c = hist[t];
+        uint32_t tot;
+        const uint32_t incl = rk_block_scan(c, t, wsum, &tot, sync);
+        const uint32_t excl = incl - c;
+        if (excl < kk && kk <= incl) { sel[0] = (uint32_t) t; sel[1] = kk - excl; }
+        sync();
+        prefix |= sel[0] << shift;
+        mask |= 0xFFu << shift;
+        kk = sel[1];
+    }
+    return prefix;
+}
+
+// Keep the entries of (key,row)[0..n) with key <= tau, packed to the front (order not preserved
+// across threads' blocks but deterministic).  Returns the number kept.
+template <typename Sync>
+__device__ __forceinline__ int rk_compact_le(RkCandBuf cb, int n, uint32_t tau, int t, volatile uint32_t *wsum, Sync sync)
+{
+    constexpr int PER = RK_CAND_CAP / RK_CONS_THREADS;   // 8
+    uint32_t mk[PER], mr[PER];
+    int mc = 0;
+    const int b0 = t * PER;
+#pragma unroll
+    for (int i = 0; i < PER; i++) {
+        const int idx = b0 + i;
+        if (idx < n) {
+            const uint32_t kv = cb.key[idx];
+            if (kv <= tau) { mk[mc] = kv; mr[mc] = cb.row[idx]; mc++; }
+        }
+    }
+    uint32_t tot;
+    const uint32_t incl = rk_block_scan((uint32_t) mc, t, wsum, &tot, sync);   // its barriers also order the reads above
+    int pos = (int) (incl - (uint32_t) mc);
+#pragma unroll
+    for (int i = 0; i < PER; i++)
+        if (i < mc) { cb.key[pos + i] = mk[i]; cb.row[pos + i] = mr[i]; }
+    sync();
+    return (int) tot;
+}
+
+// ---------------------------------------------------------------------------------------------
+
 template <int METRIC>
 __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkScanParams p)
 {
@@ -244,6 +352,9 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     RkStageMeta *meta = reinterpret_cast<RkStageMeta *>(smem + L.off_meta);
     volatile uint32_t *s_count = reinterpret_cast<volatile uint32_t *>(smem + L.off_misc);
     volatile uint32_t *s_tau = s_count + 1;
+    volatile uint32_t *s_sel = s_count + 2;     // [2] radix-select hand-off
+    volatile uint32_t *s_wsum = s_count + 8;    // [8] block-scan scratch
+    uint32_t *s_hist = reinterpret_cast<uint32_t *>(smem + L.off_hist);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -264,14 +375,27 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     if (warp == RK_CONS_WARPS) {
         // ===================== producer warp =====================
         RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, true};
-        for (;;) {
-            uint32_t sid = 0;
-            if (lane == 0) sid = atomicAdd(p.seg_counter, 1u);
-            sid = __shfl_sync(0xffffffffu, sid, 0);
-            if (sid >= nseg) break;
-            pr.seg_id = sid;
-            RkSegment s = p.segs[sid];
-            pr.run_segment(s);
+        // claim two segments ahead: the next descriptor is loaded while the current one streams
+        uint32_t sid0 = 0, sid1 = 0;
+        if (lane == 0) { sid0 = atomicAdd(p.seg_counter, 1u); sid1 = atomicAdd(p.seg_counter, 1u); }
+        sid0 = __shfl_sync(0xffffffffu, sid0, 0);
+        sid1 = __shfl_sync(0xffffffffu, sid1, 0);
+        RkSegment cur;
+        if (sid0 < nseg) cur = p.segs[sid0];
+        while (sid0 < nseg) {
+            RkSegment nxt;
+            uint32_t sid2 = 0;
+            if (sid1 < nseg) {
+                nxt = p.segs[sid1];
+                if (lane == 0) sid2 = atomicAdd(p.seg_counter, 1u);
+            } else {
+                sid2 = sid1;
+            }
+            pr.seg_id = sid0;
+            pr.run_segment(cur);
+            sid2 = __shfl_sync(0xffffffffu, sid2, 0);
+            sid0 = sid1; sid1 = sid2;
+            cur = nxt;
         }
         pr.open_tile();
         pr.first = false;
@@ -288,18 +412,31 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     const int t = threadIdx.x;
     const int g = lane >> 3, l8 = lane & 7;
     auto csync = [] { rk_named_bar_sync(1, RK_CONS_THREADS); };
+    // checkpoint every `ckpt` tiles: at most ckpt * tile_rows appends can land between two
+    // checkpoints, so the buffer cannot overflow if it is compacted above `trigger`
+    int ckpt = RK_CKPT_ROWS / p.tile_rows;
+    if (ckpt < 1) ckpt = 1;
+    if (ckpt > 16) ckpt = 16;
+    const uint32_t trigger = (uint32_t) (RK_CAND_CAP - ckpt * p.tile_rows);
+    // after a radix-select compaction more than this many survivors means "too many ties at the
+    // k-th key": fall back to the exact (key, tid) sort that keeps precisely k
+    const int tie_limit = p.k + ((int) trigger - p.k) / 2;
 
     int stage = 0;
     uint32_t phase = 0;
+    int since_ckpt = 0;
     for (;;) {
         rk_mbar_wait(&full[stage], phase);
         const RkStageMeta m = meta[stage];
         if (m.flags & RK_FLAG_END) break;
         if (m.flags & RK_FLAG_FIRST) {
+            // Every warp copies the segment's query for itself (identical values from all warps).
+            // All warps have left the previous segment through its final barriers, so nobody still
+            // reads the old contents.
             const float4 *qs = reinterpret_cast<const float4 *>(smem + L.off_qslot + (size_t) stage * p.row_bytes);
             float4 *qd = reinterpret_cast<float4 *>(smem + L.off_qcur);
-            for (int i = t; i < p.dim4; i += RK_CONS_THREADS) qd[i] = qs[i];
-            csync();
+            for (int i = lane; i < p.dim4; i += 32) qd[i] = qs[i];
+            __syncwarp();
         }
         const float4 *tile = reinterpret_cast<const float4 *>(smem + L.off_tiles + (size_t) stage * L.tile_bytes);
         const uint32_t *rid = reinterpret_cast<const uint32_t *>(smem + L.off_rowid) + (size_t) stage * p.tile_rows;
@@ -325,51 +462,61 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
             sa += __shfl_xor_sync(0xffffffffu, sa, 4); sb += __shfl_xor_sync(0xffffffffu, sb, 4);
             sa += __shfl_xor_sync(0xffffffffu, sa, 2); sb += __shfl_xor_sync(0xffffffffu, sb, 2);
             sa += __shfl_xor_sync(0xffffffffu, sa, 1); sb += __shfl_xor_sync(0xffffffffu, sb, 1);
-            if (l8 == 0) {
-                const uint32_t tau = *s_tau;
-                if (va) {
-                    const uint32_t key = rk_float_to_key(METRIC == 0 ? sa : -sa);
-                    if (key <= tau) {
-                        const uint32_t slot = atomicAdd((uint32_t *) s_count, 1u);
-                        const uint32_t row = rid[ra];
-                        cb.key[slot] = key; cb.row[slot] = row; cb.tid[slot] = p.store.tid[row];
-                    }
-                }
-                if (vb) {
-                    const uint32_t key = rk_float_to_key(METRIC == 0 ? sb : -sb);
-                    if (key <= tau) {
-                        const uint32_t slot = atomicAdd((uint32_t *) s_count, 1u);
-                        const uint32_t row = rid[rb];
-                        cb.key[slot] = key; cb.row[slot] = row; cb.tid[slot] = p.store.tid[row];
-                    }
-                }
+            // survivors of this warp step: one aggregated atomic for the whole warp
+            const uint32_t tau = *s_tau;
+            const uint32_t ka = rk_float_to_key(METRIC == 0 ? sa : -sa);
+            const uint32_t kb = rk_float_to_key(METRIC == 0 ? sb : -sb);
+            const bool ca = l8 == 0 && va && ka <= tau;
+            const bool cb2 = l8 == 0 && vb && kb <= tau;
+            const unsigned ma = __ballot_sync(0xffffffffu, ca), mb = __ballot_sync(0xffffffffu, cb2);
+            if (ma | mb) {
+                const int na = __popc(ma);
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd((uint32_t *) s_count, (uint32_t) (na + __popc(mb)));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const unsigned below = (1u << lane) - 1u;
+                if (ca) { const uint32_t slot = base + __popc(ma & below); cb.key[slot] = ka; cb.row[slot] = rid[ra]; }
+                if (cb2) { const uint32_t slot = base + na + __popc(mb & below); cb.key[slot] = kb; cb.row[slot] = rid[rb]; }
             }
         }
         __syncwarp();
         if (lane == 0) rk_mbar_arrive(&empty[stage]);
-        csync();
-        const int n = (int) *s_count;
         const bool last = (m.flags & RK_FLAG_LAST) != 0;
-        if (last || n > RK_CAND_CAP - p.tile_rows) {
-            rk_bitonic_sort(cb, n, t, RK_CONS_THREADS, csync);
-            const int keep = n < p.k ? n : p.k;
-            if (last) {
-                const size_t base = (size_t) m.seg * p.k;
-                for (int i = t; i < keep; i += RK_CONS_THREADS) {
-                    p.cand_key[base + i] = cb.key[i];
-                    p.cand_tid[base + i] = cb.tid[i];
-                    p.cand_row[base + i] = cb.row[i];
+        if (last || ++since_ckpt == ckpt) {
+            since_ckpt = 0;
+            // one reducing barrier: every warp gets the same verdict whatever it read itself
+            const bool full_buf = rk_named_bar_red_or(1, RK_CONS_THREADS, *s_count > trigger);
+            if (last || full_buf) {
+                int n = (int) *s_count;              // stable: nobody appends before the next barrier
+                uint32_t tau = RK_KEY_SENTINEL;
+                if (n > p.k) {
+                    tau = rk_radix_kth(cb.key, n, p.k, s_hist, s_wsum, s_sel, t, csync);
+                    n = rk_compact_le(cb, n, tau, t, s_wsum, csync);
                 }
-                if (t == 0) {
-                    p.cand_count[m.seg] = keep;
-                    *s_count = 0;
-                    *s_tau = RK_KEY_SENTINEL;
+                if (last || n > tie_limit) {
+                    // exact order: (key, tuple id) ascending over the survivors
+                    for (int i = t; i < n; i += RK_CONS_THREADS) cb.tid[i] = p.store.tid[cb.row[i]];
+                    rk_bitonic_sort(cb, n, t, RK_CONS_THREADS, csync);
+                    if (n > p.k) n = p.k;
                 }
-            } else if (t == 0) {
-                *s_count = (uint32_t) keep;
-                *s_tau = (n >= p.k) ? cb.key[p.k - 1] : RK_KEY_SENTINEL;
+                if (last) {
+                    const size_t base = (size_t) m.seg * p.k;
+                    for (int i = t; i < n; i += RK_CONS_THREADS) {
+                        p.cand_key[base + i] = cb.key[i];
+                        p.cand_tid[base + i] = cb.tid[i];
+                        p.cand_row[base + i] = cb.row[i];
+                    }
+                    if (t == 0) {
+                        p.cand_count[m.seg] = n;
+                        *s_count = 0;
+                        *s_tau = RK_KEY_SENTINEL;
+                    }
+                } else if (t == 0) {
+                    *s_count = (uint32_t) n;
+                    *s_tau = tau;
+                }
+                csync();
             }
-            csync();
         }
         if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
     }

@@ -113,11 +113,17 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
         if (rc < 0) return rc;
         for (auto &pi : per_q[q]) total_rows += pi.rows_est;
     }
-    // segment sizing: ~32 segments per CTA so the tail of the dynamic schedule stays ~3 % of the
-    // launch, but never below ~128 KB of row data (a segment ends with a top-k compaction)
+    // Segment sizing.  A segment costs a few microseconds of fixed work (pipeline refill, final
+    // compaction + sort) and the dynamic schedule wastes about half a segment per CTA at the tail,
+    // so with T = streaming time per CTA the best count per CTA is ~sqrt(T / 2o), o ~ 4 us.
     const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4;
-    uint64_t min_rows = std::max<uint64_t>((uint64_t) ix->tile_rows, (128 * 1024) / row_bytes);
-    uint64_t target = std::max<uint64_t>(min_rows, total_rows / ((uint64_t) ix->sm_count * 32) + 1);
+    const uint64_t sm = (uint64_t) ix->sm_count;
+    const double t_cta_us = (double) total_rows * (double) row_bytes / (double) sm / 44.0e3;   // ~44 GB/s per SM
+    double per_cta = std::sqrt(t_cta_us / 8.0);
+    if (per_cta < 1.0) per_cta = 1.0;
+    if (per_cta > 64.0) per_cta = 64.0;
+    uint64_t target = (uint64_t) ((double) total_rows / ((double) sm * per_cta)) + 1;
+    if (target < (uint64_t) ix->tile_rows) target = (uint64_t) ix->tile_rows;
 
     std::vector<RkSegment> segs;
     std::vector<uint32_t> qseg(nq + 1, 0);
@@ -131,10 +137,17 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
             if (nchunks > P.rows) nchunks = P.rows;
             for (uint64_t c = 0; c < nchunks; c++) {
                 RkSegment s;
-                s.query = (uint32_t) q; s.kind = RK_SEG_EXTENTS; s.src = pi.part; s.flags = pi.flags;
+                s.query = (uint32_t) q; s.kind = RK_SEG_EXTENTS; s.flags = (uint16_t) pi.flags;
                 s.begin = P.rows * c / nchunks;
                 s.end = P.rows * (c + 1) / nchunks;
-                if (s.end > s.begin) segs.push_back(s);
+                if (s.end <= s.begin) continue;
+                // extents [lo, hi) of the partition intersect virtual rows [begin, end)
+                const auto vb = P.vstart.begin(), ve = P.vstart.end();
+                const uint32_t lo = (uint32_t) (std::upper_bound(vb, ve, (uint32_t) s.begin) - vb) - 1;
+                const uint32_t hi = (uint32_t) (std::lower_bound(vb, ve, (uint32_t) s.end) - vb);
+                s.ext_lo = P.ext_off + lo;
+                s.ext_hi = P.ext_off + hi;
+                segs.push_back(s);
             }
             if (pi.flags & RK_SEGF_MASKED) mask_bytes += (uint64_t) P.n_ext * (8ull * W + 8);
         }
@@ -206,7 +219,6 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
     p.ext_row = ix->d_ext_row.as<uint32_t>();
     p.ext_vstart = ix->d_ext_vstart.as<uint32_t>();
     p.ext_mask = ix->d_ext_mask.as<uint64_t>();
-    p.part_ext_off = ix->d_part_ext_off.as<uint32_t>();
     p.q = dQ;
     p.null_query = o->null_query;
     p.segs = ws.segs.as<RkSegment>();

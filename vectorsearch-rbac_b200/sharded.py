@@ -126,7 +126,8 @@ class ShardedSearcher:
 def use_torch_stream(index, device: Optional[torch.device] = None) -> None:
     """Run the index's kernels on torch's current CUDA stream so torch events and NCCL collectives
     order with them."""
-    index.set_stream(torch.cuda.current_stream(device).cuda_stream)
+    h = torch.cuda.current_stream(device).cuda_stream
+    index.set_stream(h if h else 1)     # 0 is the legacy default stream: name it explicitly (cudaStreamLegacy)
 
 
 def make_opts(*a, **kw):
