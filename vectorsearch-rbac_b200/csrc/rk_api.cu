@@ -98,7 +98,7 @@ int Workspace::init(int device_)
 }
 void Workspace::destroy()
 {
-    DevBuf *bufs[] = {&segs, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
+    DevBuf *bufs[] = {&segs, &order, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
                       &out_doc, &out_dist, &out_count, &probe_key, &probe_list, &ex_key, &ex_tid, &ex_doc};
     for (auto *b : bufs) b->release();
     h_plan_ring[0].release();

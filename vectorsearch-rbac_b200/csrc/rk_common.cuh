@@ -46,6 +46,7 @@ struct RkScanParams {
     int null_query;                 // ORDER BY v <-> NULL: all distances 0
     // work list
     const RkSegment *segs;
+    const uint32_t *seg_order;      // execution order: position -> segment index (NULL = identity)
     const uint32_t *nseg_ptr;       // number of segments (device resident so plans can be built on device)
     uint32_t *seg_counter;          // dynamic scheduler
     // per-segment output (k_pad entries each)
@@ -169,6 +170,45 @@ __device__ __forceinline__ void rk_bulk_g2s(void *smem_dst, const void *gmem_src
                      rk_smem_u32(smem_dst)),
                  "l"(gmem_src), "r"(bytes), "r"(rk_smem_u32(bar))
                  : "memory");
+}
+
+// L2 eviction policies: row data streams through once (evict_first); the small extent / mask
+// tables are re-read by every segment (evict_last) and must survive the stream.
+__device__ __forceinline__ uint64_t rk_policy_evict_first()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
+__device__ __forceinline__ uint64_t rk_policy_evict_last()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
+__device__ __forceinline__ void rk_bulk_g2s_hint(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar, uint64_t pol)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            rk_smem_u32(smem_dst)),
+        "l"(gmem_src), "r"(bytes), "r"(rk_smem_u32(bar)), "l"(pol)
+        : "memory");
+}
+
+__device__ __forceinline__ uint32_t rk_ld_u32_hint(const uint32_t *p, uint64_t pol)
+{
+    uint32_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+    return v;
+}
+
+__device__ __forceinline__ uint64_t rk_ld_u64_hint(const uint64_t *p, uint64_t pol)
+{
+    uint64_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+    return v;
 }
 
 __device__ __forceinline__ void rk_named_bar_sync(int id, int nthreads)

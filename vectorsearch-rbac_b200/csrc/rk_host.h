@@ -35,7 +35,7 @@ struct Workspace {
     int device = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    DevBuf segs, ctl /* [0]=nseg [1]=counter */, cand_key, cand_tid, cand_row, cand_count, qseg, qmask, dq;
+    DevBuf segs, order, ctl /* [0]=nseg [1]=counter */, cand_key, cand_tid, cand_row, cand_count, qseg, qmask, dq;
     DevBuf out_tid, out_doc, out_dist, out_count;
     DevBuf probe_key, probe_list;        // IVF: per-query selected lists
     DevBuf ex_key, ex_tid, ex_doc;       // exchange-form results

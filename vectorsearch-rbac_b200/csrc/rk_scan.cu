@@ -85,6 +85,7 @@ struct RkProducer {
     uint32_t cur_rows, tx;
     uint32_t seg_id, query;
     bool first;
+    uint64_t pol_stream, pol_keep;
 
     __device__ __forceinline__ void open_tile()
     {
@@ -125,9 +126,9 @@ struct RkProducer {
             uint32_t space = (uint32_t) p.tile_rows - cur_rows;
             uint32_t n = len < space ? (uint32_t) len : space;
             if (lane == 0) {
-                rk_bulk_g2s(smem + L.off_tiles + (size_t) stage * L.tile_bytes + (size_t) cur_rows * p.row_bytes,
-                            reinterpret_cast<const unsigned char *>(p.store.x) + phys * (uint64_t) p.row_bytes,
-                            n * (uint32_t) p.row_bytes, &full[stage]);
+                rk_bulk_g2s_hint(smem + L.off_tiles + (size_t) stage * L.tile_bytes + (size_t) cur_rows * p.row_bytes,
+                                 reinterpret_cast<const unsigned char *>(p.store.x) + phys * (uint64_t) p.row_bytes,
+                                 n * (uint32_t) p.row_bytes, &full[stage], pol_stream);
             }
             uint32_t *rid = reinterpret_cast<uint32_t *>(smem + L.off_rowid) + (size_t) stage * p.tile_rows + cur_rows;
             for (uint32_t i = lane; i < n; i += 32) rid[i] = (uint32_t) (phys + i);
@@ -159,35 +160,53 @@ struct RkProducer {
         } else if (s.kind == RK_SEG_EXTENTS) {
             // Partition = table of per-document extents; the host resolved which extents touch
             // [begin, end).  RK_EPL * 32 extents are resolved per step: every lane first tests the
-            // role masks of its RK_EPL extents (independent loads), then fetches row / virtual
-            // offsets only for the ones that passed; allowed extents are streamed in order and
-            // physically adjacent ones are fused into one longer copy.
+            // role masks of its RK_EPL extents and fetches their row / virtual offsets (all loads
+            // independent); allowed extents are streamed in order and physically adjacent ones are
+            // fused into one longer copy.
             const bool masked = (s.flags & RK_SEGF_MASKED) != 0;
             const uint64_t *um = p.qmask + (size_t) query * p.mask_words;
             uint64_t run_start = 0, run_len = 0;
             for (uint32_t eb = s.ext_lo; eb < s.ext_hi; eb += 32 * RK_EPL) {
+                // all loads of a step are unconditional and independent (indices clamped), so the
+                // step costs one memory round trip, not one per extent
+                uint32_t ec[RK_EPL];
                 bool ok[RK_EPL];
 #pragma unroll
                 for (int j = 0; j < RK_EPL; j++) {
                     const uint32_t e = eb + j * 32 + lane;
                     ok[j] = e < s.ext_hi;
-                    if (ok[j] && masked) ok[j] = mask_hit(p.ext_mask + (size_t) e * p.mask_words, um);
+                    ec[j] = ok[j] ? e : s.ext_hi - 1;
+                }
+                if (masked) {
+                    uint64_t hit[RK_EPL];
+#pragma unroll
+                    for (int j = 0; j < RK_EPL; j++) hit[j] = 0;
+                    for (int w = 0; w < p.mask_words; w++) {
+                        const uint64_t u = __ldg(um + w);
+#pragma unroll
+                        for (int j = 0; j < RK_EPL; j++)
+                            hit[j] |= rk_ld_u64_hint(p.ext_mask + (size_t) ec[j] * p.mask_words + w, pol_keep) & u;
+                    }
+#pragma unroll
+                    for (int j = 0; j < RK_EPL; j++) ok[j] = ok[j] && hit[j] != 0;
                 }
                 uint64_t prow[RK_EPL];
                 uint32_t plen[RK_EPL];
+                uint32_t vs_[RK_EPL], ve_[RK_EPL], er_[RK_EPL];
 #pragma unroll
                 for (int j = 0; j < RK_EPL; j++) {
-                    prow[j] = 0; plen[j] = 0;
-                    if (ok[j]) {
-                        const uint32_t e = eb + j * 32 + lane;
-                        const uint64_t vs = __ldg(p.ext_vstart + e), ve = __ldg(p.ext_vstart + e + 1);
-                        const uint64_t v0 = vs > s.begin ? vs : s.begin;
-                        const uint64_t v1 = ve < s.end ? ve : s.end;
-                        if (v1 > v0) {
-                            prow[j] = (uint64_t) __ldg(p.ext_row + e) + (v0 - vs);
-                            plen[j] = (uint32_t) (v1 - v0);
-                        }
-                    }
+                    vs_[j] = rk_ld_u32_hint(p.ext_vstart + ec[j], pol_keep);
+                    ve_[j] = rk_ld_u32_hint(p.ext_vstart + ec[j] + 1, pol_keep);
+                    er_[j] = rk_ld_u32_hint(p.ext_row + ec[j], pol_keep);
+                }
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) {
+                    const uint64_t vs = vs_[j], ve = ve_[j];
+                    const uint64_t v0 = vs > s.begin ? vs : s.begin;
+                    const uint64_t v1 = ve < s.end ? ve : s.end;
+                    const bool take = ok[j] && v1 > v0;
+                    prow[j] = (uint64_t) er_[j] + (v0 - vs);
+                    plen[j] = take ? (uint32_t) (v1 - v0) : 0u;
                 }
 #pragma unroll
                 for (int j = 0; j < RK_EPL; j++) {
@@ -374,25 +393,30 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
 
     if (warp == RK_CONS_WARPS) {
         // ===================== producer warp =====================
-        RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, true};
+        RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, true, rk_policy_evict_first(),
+                      rk_policy_evict_last()};
+        auto seg_at = [&](uint32_t pos) -> uint32_t { return p.seg_order ? p.seg_order[pos] : pos; };
         // claim two segments ahead: the next descriptor is loaded while the current one streams
         uint32_t sid0 = 0, sid1 = 0;
         if (lane == 0) { sid0 = atomicAdd(p.seg_counter, 1u); sid1 = atomicAdd(p.seg_counter, 1u); }
         sid0 = __shfl_sync(0xffffffffu, sid0, 0);
         sid1 = __shfl_sync(0xffffffffu, sid1, 0);
         RkSegment cur;
-        if (sid0 < nseg) cur = p.segs[sid0];
+        uint32_t cur_id = 0, nxt_id = 0;
+        if (sid0 < nseg) { cur_id = seg_at(sid0); cur = p.segs[cur_id]; }
         while (sid0 < nseg) {
             RkSegment nxt;
             uint32_t sid2 = 0;
             if (sid1 < nseg) {
-                nxt = p.segs[sid1];
+                nxt_id = seg_at(sid1);
+                nxt = p.segs[nxt_id];
                 if (lane == 0) sid2 = atomicAdd(p.seg_counter, 1u);
             } else {
                 sid2 = sid1;
             }
-            pr.seg_id = sid0;
+            pr.seg_id = cur_id;
             pr.run_segment(cur);
+            cur_id = nxt_id;
             sid2 = __shfl_sync(0xffffffffu, sid2, 0);
             sid0 = sid1; sid1 = sid2;
             cur = nxt;

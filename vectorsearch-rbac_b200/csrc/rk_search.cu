@@ -155,13 +155,47 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
     qseg[nq] = (uint32_t) segs.size();
     const uint32_t nseg = (uint32_t) segs.size();
 
-    // pinned staging: [segments][qseg][qmask]
+    // Execution order.  Queries that walk the same rows (same partitions, same permission mask)
+    // are interleaved chunk by chunk: chunk c of every query of the group is claimed by different
+    // CTAs at about the same time, so the rows one of them pulls from HBM are served to the others
+    // from the 126 MB L2.  Candidate lists stay indexed by segment, so the select kernel is unaffected.
+    std::vector<uint32_t> order;
+    order.reserve(nseg);
+    {
+        std::map<std::vector<uint64_t>, std::vector<uint32_t>> groups;
+        std::vector<const std::vector<uint32_t> *> group_seq;
+        std::vector<uint64_t> key;
+        for (size_t q = 0; q < nq; q++) {
+            if (qseg[q + 1] == qseg[q]) continue;
+            key.clear();
+            bool any_masked = false;
+            for (auto &pi : per_q[q]) {
+                key.push_back(((uint64_t) pi.part << 32) | pi.flags);
+                any_masked |= (pi.flags & RK_SEGF_MASKED) != 0;
+            }
+            key.push_back(~0ull);
+            if (any_masked && uinfo[q])
+                for (uint64_t w : uinfo[q]->mask) key.push_back(w);
+            key.push_back((uint64_t) (qseg[q + 1] - qseg[q]));
+            auto ins = groups.emplace(key, std::vector<uint32_t>());
+            if (ins.second) group_seq.push_back(&ins.first->second);
+            ins.first->second.push_back((uint32_t) q);
+        }
+        for (auto *g : group_seq) {
+            const uint32_t n = qseg[(*g)[0] + 1] - qseg[(*g)[0]];
+            for (uint32_t c = 0; c < n; c++)
+                for (uint32_t q : *g) order.push_back(qseg[q] + c);
+        }
+    }
+
+    // pinned staging: [segments][qseg][qmask][order]
     const size_t b_segs = (size_t) nseg * sizeof(RkSegment), b_qseg = (nq + 1) * 4, b_qmask = nq * (size_t) W * 8;
+    const size_t b_order = (size_t) nseg * 4;
     ws.plan_idx ^= 1;
     const int pi_ = ws.plan_idx;
     if (ws.ev_plan_used[pi_]) RK_CUDA(cudaEventSynchronize(ws.ev_plan[pi_]));   // staging buffer free again?
     PinBuf &h_plan = ws.h_plan_ring[pi_];
-    if (h_plan.ensure(b_segs + b_qseg + b_qmask + 64) != 0) return RK_ERR_CUDA;
+    if (h_plan.ensure(b_segs + b_qseg + b_qmask + b_order + 128) != 0) return RK_ERR_CUDA;
     unsigned char *hp = h_plan.as<unsigned char>();
     if (nseg) memcpy(hp, segs.data(), b_segs);
     memcpy(hp + b_segs, qseg.data(), b_qseg);
@@ -179,6 +213,12 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
     hc = reinterpret_cast<uint32_t *>(((uintptr_t) hc + 15) & ~(uintptr_t) 15);
     hc[0] = nseg; hc[1] = 0;
     RK_CUDA(cudaMemcpyAsync(ws.ctl.p, hc, 8, cudaMemcpyHostToDevice, ws.stream));
+    uint32_t *ho = hc + 4;
+    if (ws.order.ensure(std::max<size_t>(b_order, 16)) != 0) return RK_ERR_CUDA;
+    if (nseg) {
+        memcpy(ho, order.data(), b_order);
+        RK_CUDA(cudaMemcpyAsync(ws.order.p, ho, b_order, cudaMemcpyHostToDevice, ws.stream));
+    }
     RK_CUDA(cudaEventRecord(ws.ev_plan[pi_], ws.stream));
     ws.ev_plan_used[pi_] = true;
 
@@ -222,6 +262,7 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
     p.q = dQ;
     p.null_query = o->null_query;
     p.segs = ws.segs.as<RkSegment>();
+    p.seg_order = ws.order.as<uint32_t>();
     p.nseg_ptr = ws.ctl.as<uint32_t>();
     p.seg_counter = ws.ctl.as<uint32_t>() + 1;
     p.cand_key = ws.cand_key.as<uint32_t>();
