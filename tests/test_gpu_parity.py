@@ -154,3 +154,45 @@ def test_large_scan_many_segments_and_compactions():
     got = ix2.search_batch(Q[:1], users[:1], 100, filter=vr.FILTER_NONE)
     exp = oracle_role_search(ds2, Q[:1], users[:1], orc.METRIC_L2, 100, mode="none")
     assert_topk_matches(got, exp, exact=True)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_shard_exchange_form_and_merge(world):
+    """G shards (document d -> shard d mod G) searched separately on one GPU, their packed exchange
+    buffers concatenated exactly as an all-gather would lay them out, then rk_merge_shards with
+    shard_stride_bytes: must equal the oracle over the whole corpus."""
+    import torch
+    import vectorsearch_rbac_b200 as vr
+    from vectorsearch_rbac_b200 import sharded
+    ds = make_dataset("sift", n=9000, dim=64, rows_per_doc=15, rbac="random", num_users=20, num_roles=8)
+    Q, users = _queries(ds, 24)
+    k, nq = 40, 24
+    dev = torch.device("cuda", 0)
+    dQ = torch.from_numpy(Q).to(dev)
+    per = sharded.packed_bytes(nq, k)
+    recv = torch.empty(per * world, dtype=torch.uint8, device=dev)
+    shards = []
+    for r in range(world):
+        mine = sharded.local_row_mask(ds["doc"], r, world)
+        local = dict(ds, X=ds["X"][mine], tid=ds["tid"][mine], doc=ds["doc"][mine])
+        ix = load_index(local, role_parts=False, combo_parts=False)
+        ix.finalize()
+        shards.append(ix)
+        s = sharded.ShardedSearcher(ix, r, world, device=dev)
+        opts = sharded.make_opts(k, filter=vr.FILTER_BITMASK)
+        s._cuda_local_search(dQ, users, opts, recv[r * per:(r + 1) * per])
+        ix.synchronize()
+    s = sharded.ShardedSearcher(shards[0], 0, world, device=dev)
+    b = s._get_bufs(nq, k)
+    s._cuda_merge(recv, nq, k, (b["tid"], b["doc"], b["dist"], b["cnt"]))
+    shards[0].synchronize()
+    got = (b["tid"].cpu().numpy().view(np.uint64), b["doc"].cpu().numpy(), b["dist"].cpu().numpy(), b["cnt"].cpu().numpy())
+    exp = oracle_role_search(ds, Q, users, orc.METRIC_L2, k, mode="bitmask")
+    assert_topk_matches(got, exp, exact=True)
+    # document ids ride along
+    row_of_tid = {int(t): i for i, t in enumerate(ds["tid"])}
+    for q in range(nq):
+        for i in range(int(got[3][q])):
+            assert got[1][q, i] == ds["doc"][row_of_tid[int(got[0][q, i])]]
+    for ix in shards:
+        ix.close()
