@@ -1,11 +1,303 @@
-// rk_ivf.cu — IVFFlat (placeholder until the list-probe path lands).
+// rk_ivf.cu — IVFFlat host side: CREATE INDEX (sample, k-means, assign, pack lists) and the list-probe
+// search, behind rk_build_ivf / rk_build_ivf_from_centers / rk_ivf_info and the probes > 0 branch
+// of every search entry point.
+//
+// Reference (paths relative to the reference checkout):
+//   build ...... pgvector/src/ivfbuild.c:404-441 (sample max(10000, 50*lists) rows), ivfkmeans.c (k-means;
+//                spherical for vector_ip_ops: sql/vector.sql:298-303 FUNCTION 3/4), ivfbuild.c:141-198
+//                (assign every tuple to its nearest centre by FUNCTION 1), :251-310 (pack lists)
+//   scan ....... pgvector/src/ivfscan.c:36-107 (choose lists), :112-176 (score every tuple of the
+//                probed lists), :257-266 (probe clamps), :375-381 (iterative refill)
+// The executor's WHERE / RLS post-filter on what the index returns becomes the
+// role-mask test inside the list scan: same rows, same order.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <random>
+#include <unordered_set>
+
 #include "rk_host.h"
 
-int rk_ivf_search(rk_index *, Workspace &, size_t, const float *, const uint32_t *, const rk_scan_opts *, int,
-                  const RkSelectParams &)
+#define RK_CUDA(call)                                                                                    \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return rk_fail(RK_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+#define RK_IVF_MAX_LISTS_SMEM 16384   // the probe kernel sorts (key, list) pairs of one query in shared memory
+#define RK_IVF_MAX_SEGS (1u << 18)    // segments per sub-batch (bounds the candidate buffers)
+
+// Upload padded centres, assign every row, pack the list-sorted copy of the store.
+static int build_from_device_centers(rk_index *ix, int lists, const float *d_centers)
 {
-    return rk_fail(RK_ERR_UNSUPPORTED, "IVFFlat scan not built yet");
+    IvfIndex &iv = ix->ivf;
+    const size_t n = ix->nrows;
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    cudaStream_t st = 0;
+    DevBuf d_row_list;
+    if (d_row_list.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
+    RK_CUDA(rk_launch_assign(ix->d_x.as<float>(), n, d_centers, lists, ix->dim_pad, ix->metric, d_row_list.as<uint32_t>(),
+                             nullptr, st));
+    iv.row_list.assign(n, 0);
+    if (n) RK_CUDA(cudaMemcpy(iv.row_list.data(), d_row_list.p, n * 4, cudaMemcpyDeviceToHost));
+    d_row_list.release();
+    // counting sort by list, stable in finalized row order (ivfbuild.c:251-310 packs tuples list by list)
+    iv.list_start.assign((size_t) lists + 1, 0);
+    for (size_t r = 0; r < n; r++) iv.list_start[iv.row_list[r] + 1]++;
+    iv.max_list_len = 0;
+    for (int l = 0; l < lists; l++) {
+        iv.max_list_len = std::max(iv.max_list_len, iv.list_start[l + 1]);
+        iv.list_start[l + 1] += iv.list_start[l];
+    }
+    std::vector<uint32_t> perm(n), cursor(iv.list_start.begin(), iv.list_start.end() - 1);
+    for (size_t r = 0; r < n; r++) perm[cursor[iv.row_list[r]]++] = (uint32_t) r;
+    DevBuf d_perm;
+    if (d_perm.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
+    if (n) RK_CUDA(cudaMemcpy(d_perm.p, perm.data(), n * 4, cudaMemcpyHostToDevice));
+    if (iv.d_x.ensure(std::max<size_t>(n * rb, 16)) != 0 || iv.d_tid.ensure(std::max<size_t>(n * 8, 16)) != 0 ||
+        iv.d_rowdoc.ensure(std::max<size_t>(n * 4, 16)) != 0 || iv.d_list_start.ensure(((size_t) lists + 1) * 4) != 0)
+        return RK_ERR_CUDA;
+    RK_CUDA(rk_launch_gather_rows(ix->d_x.as<float>(), iv.d_x.as<float>(), d_perm.as<uint32_t>(), n, ix->dim_pad, st));
+    RK_CUDA(rk_launch_gather_u64(ix->d_tid.as<uint64_t>(), iv.d_tid.as<uint64_t>(), d_perm.as<uint32_t>(), n, st));
+    RK_CUDA(rk_launch_gather_u32(ix->d_rowdoc.as<uint32_t>(), iv.d_rowdoc.as<uint32_t>(), d_perm.as<uint32_t>(), n, st));
+    RK_CUDA(cudaMemcpy(iv.d_list_start.p, iv.list_start.data(), ((size_t) lists + 1) * 4, cudaMemcpyHostToDevice));
+    RK_CUDA(cudaDeviceSynchronize());
+    d_perm.release();
+    if (iv.d_centers.p != d_centers) {
+        if (iv.d_centers.ensure((size_t) lists * rb) != 0) return RK_ERR_CUDA;
+        RK_CUDA(cudaMemcpy(iv.d_centers.p, d_centers, (size_t) lists * rb, cudaMemcpyDeviceToDevice));
+    }
+    // keep an unpadded host copy for rk_ivf_info
+    std::vector<float> padded((size_t) lists * ix->dim_pad);
+    RK_CUDA(cudaMemcpy(padded.data(), iv.d_centers.p, (size_t) lists * rb, cudaMemcpyDeviceToHost));
+    iv.centers.assign((size_t) lists * ix->dim, 0.f);
+    for (int l = 0; l < lists; l++)
+        memcpy(&iv.centers[(size_t) l * ix->dim], &padded[(size_t) l * ix->dim_pad], (size_t) ix->dim * 4);
+    iv.lists = lists;
+    iv.built = true;
+    ix->device_bytes += iv.d_x.cap + iv.d_tid.cap + iv.d_rowdoc.cap + iv.d_centers.cap + iv.d_list_start.cap;
+    return RK_OK;
 }
-extern "C" int rk_build_ivf(rk_index *, int, uint64_t) { return rk_fail(RK_ERR_UNSUPPORTED, "rk_build_ivf not built yet"); }
-extern "C" int rk_build_ivf_from_centers(rk_index *, int, const float *) { return rk_fail(RK_ERR_UNSUPPORTED, "not built yet"); }
-extern "C" int rk_ivf_info(const rk_index *, int *, float *, uint32_t *) { return rk_fail(RK_ERR_UNSUPPORTED, "not built yet"); }
+
+static int check_build_args(rk_index *ix, int lists, const char *who)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "%s: NULL index", who);
+    if (!ix->finalized) return rk_fail(RK_ERR_STATE, "%s: call rk_finalize first", who);
+    if (ix->ivf.built) return rk_fail(RK_ERR_STATE, "%s: an IVFFlat index already exists", who);
+    if (lists < 1 || lists > RK_MAX_LISTS) return rk_fail(RK_ERR_INVALID, "value %d out of bounds for option \"lists\" (1 .. %d)", lists, RK_MAX_LISTS);   // ivfflat.c:36-38
+    if (lists > RK_IVF_MAX_LISTS_SMEM) return rk_fail(RK_ERR_UNSUPPORTED, "%s: lists > %d not supported by the probe kernel", who, RK_IVF_MAX_LISTS_SMEM);
+    if (ix->dim > 2000) return rk_fail(RK_ERR_UNSUPPORTED, "column cannot have more than 2000 dimensions for ivfflat index");   // ivfflat.h:24
+    return 0;
+}
+
+extern "C" int rk_build_ivf_from_centers(rk_index *ix, int lists, const float *centers)
+{
+    int rc = check_build_args(ix, lists, "rk_build_ivf_from_centers");
+    if (rc < 0) return rc;
+    if (!centers) return rk_fail(RK_ERR_INVALID, "rk_build_ivf_from_centers: NULL centers");
+    for (size_t i = 0; i < (size_t) lists * ix->dim; i++)
+        if (!std::isfinite(centers[i])) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
+    RK_CUDA(cudaSetDevice(ix->device));
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    if (ix->ivf.d_centers.ensure((size_t) lists * rb) != 0) return RK_ERR_CUDA;
+    RK_CUDA(cudaMemset(ix->ivf.d_centers.p, 0, (size_t) lists * rb));
+    RK_CUDA(cudaMemcpy2D(ix->ivf.d_centers.p, rb, centers, (size_t) ix->dim * 4, (size_t) ix->dim * 4, lists, cudaMemcpyHostToDevice));
+    return build_from_device_centers(ix, lists, ix->ivf.d_centers.as<float>());
+}
+
+extern "C" int rk_build_ivf(rk_index *ix, int lists, uint64_t seed)
+{
+    int rc = check_build_args(ix, lists, "rk_build_ivf");
+    if (rc < 0) return rc;
+    RK_CUDA(cudaSetDevice(ix->device));
+    const size_t n = ix->nrows;
+    if (n == 0) return rk_fail(RK_ERR_STATE, "rk_build_ivf: the index holds no rows");
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    cudaStream_t st = 0;
+    // ivfbuild.c:412-414: sample 50 rows per list, at least 10000
+    size_t ns = std::max<size_t>(10000, (size_t) 50 * lists);
+    if (ns > n) ns = n;
+    std::vector<uint32_t> sample(ns);
+    std::mt19937_64 rng(seed);
+    if (ns == n) {
+        for (size_t i = 0; i < n; i++) sample[i] = (uint32_t) i;
+        std::shuffle(sample.begin(), sample.end(), rng);
+    } else {
+        std::unordered_set<uint32_t> seen;
+        seen.reserve(ns * 2);
+        size_t i = 0;
+        while (i < ns) {
+            uint32_t r = (uint32_t) (rng() % n);
+            if (seen.insert(r).second) sample[i++] = r;
+        }
+    }
+    DevBuf d_sidx, d_s, d_label, d_prev, d_sums, d_counts, d_changed;
+    if (d_sidx.ensure(ns * 4) != 0 || d_s.ensure(ns * rb) != 0 || d_label.ensure(ns * 4) != 0 || d_prev.ensure(ns * 4) != 0 ||
+        d_sums.ensure((size_t) lists * rb) != 0 || d_counts.ensure((size_t) lists * 4) != 0 || d_changed.ensure(16) != 0 ||
+        ix->ivf.d_centers.ensure((size_t) lists * rb) != 0)
+        return RK_ERR_CUDA;
+    RK_CUDA(cudaMemcpy(d_sidx.p, sample.data(), ns * 4, cudaMemcpyHostToDevice));
+    RK_CUDA(rk_launch_gather_rows(ix->d_x.as<float>(), d_s.as<float>(), d_sidx.as<uint32_t>(), ns, ix->dim_pad, st));
+    const int spherical = ix->metric == RK_METRIC_IP;      // vector_ip_ops: FUNCTION 3 spherical distance, FUNCTION 4 norm
+    if (spherical) RK_CUDA(rk_launch_km_normalize_rows(d_s.as<float>(), ns, ix->dim_pad, st));
+    // initial centres: the first `lists` sampled rows (the sample is a random permutation); with fewer
+    // samples than lists the rest wrap around (pgvector warns "index created with little data")
+    float *C = ix->ivf.d_centers.as<float>();
+    for (size_t l = 0; l < (size_t) lists; l += ns) {
+        const size_t cnt = std::min<size_t>(ns, (size_t) lists - l);
+        RK_CUDA(cudaMemcpyAsync((unsigned char *) C + l * rb, d_s.p, cnt * rb, cudaMemcpyDeviceToDevice, st));
+    }
+    RK_CUDA(cudaMemsetAsync(d_prev.p, 0xFF, ns * 4, st));
+    const int max_iter = 25;
+    for (int it = 0; it < max_iter; it++) {
+        // on normalised data the nearest centre by L2 is the one with the largest dot product
+        RK_CUDA(rk_launch_assign(d_s.as<float>(), ns, C, lists, ix->dim_pad, spherical ? 1 : 0, d_label.as<uint32_t>(), nullptr, st));
+        RK_CUDA(cudaMemsetAsync(d_changed.p, 0, 8, st));
+        RK_CUDA(rk_launch_count_changed(d_label.as<uint32_t>(), d_prev.as<uint32_t>(), ns, d_changed.as<unsigned long long>(), st));
+        unsigned long long changed = 0;
+        RK_CUDA(cudaMemcpyAsync(&changed, d_changed.p, 8, cudaMemcpyDeviceToHost, st));
+        RK_CUDA(cudaStreamSynchronize(st));
+        if (changed * 1000 < ns && it > 0) break;          // < 0.1 % of the sample moved
+        RK_CUDA(cudaMemsetAsync(d_sums.p, 0, (size_t) lists * rb, st));
+        RK_CUDA(cudaMemsetAsync(d_counts.p, 0, (size_t) lists * 4, st));
+        RK_CUDA(rk_launch_km_accumulate(d_s.as<float>(), ns, ix->dim_pad, d_label.as<uint32_t>(), d_sums.as<float>(), d_counts.as<uint32_t>(), st));
+        RK_CUDA(rk_launch_km_finalize(C, d_sums.as<float>(), d_counts.as<uint32_t>(), lists, ix->dim_pad, d_s.as<float>(), ns,
+                                      seed * 1315423911ull + (uint64_t) it, spherical, st));
+        RK_CUDA(cudaMemcpyAsync(d_prev.p, d_label.p, ns * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    RK_CUDA(cudaStreamSynchronize(st));
+    DevBuf *tmp[] = {&d_sidx, &d_s, &d_label, &d_prev, &d_sums, &d_counts, &d_changed};
+    for (auto *b : tmp) b->release();
+    return build_from_device_centers(ix, lists, C);
+}
+
+extern "C" int rk_ivf_info(const rk_index *ix, int *lists, float *centers, uint32_t *row_list)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (!ix->ivf.built) return rk_fail(RK_ERR_STATE, "rk_ivf_info: no IVFFlat index was built");
+    if (lists) *lists = ix->ivf.lists;
+    if (centers) memcpy(centers, ix->ivf.centers.data(), ix->ivf.centers.size() * 4);
+    if (row_list)
+        for (size_t i = 0; i < ix->nrows; i++) row_list[i] = ix->ivf.row_list[ix->load_to_row[i]];
+    return RK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// search
+
+void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &p, bool ivf_store, const float *dQ,
+                         const rk_scan_opts *o, int k);
+int rk_ensure_cand(Workspace &ws, size_t nlists, int k);
+
+int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_all, const uint32_t *user_ids,
+                  const rk_scan_opts *o, int probe_offset, const RkSelectParams &out_all)
+{
+    IvfIndex &iv = ix->ivf;
+    const int lists = iv.lists;
+    const int W = ix->mask_words;
+    const int k = o->k;
+    int probes = std::min(o->probes, lists - probe_offset);        // ivfscan.c:262-266
+    if (probes < 0) probes = 0;
+    const uint32_t kind = o->filter == RK_FILTER_NONE ? RK_SEG_ROWS : RK_SEG_ROWMASK;
+    const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4;
+    // chunking of long lists so that a small batch still spreads over all SMs
+    const double avg_len = lists ? (double) ix->nrows / lists : 0.0;
+    const double total_est = (double) nq_all * std::max(probes, 1) * avg_len;
+    uint64_t rows_per_seg = std::max<uint64_t>((256 * 1024) / row_bytes, (uint64_t) (total_est / (ix->sm_count * 4.0)));
+    rows_per_seg = std::max<uint64_t>(rows_per_seg, (uint64_t) ix->tile_rows);
+    int chunks = (int) ((iv.max_list_len + rows_per_seg - 1) / rows_per_seg);
+    chunks = std::max(1, std::min(chunks, 64));
+    const uint32_t chunk_rows = std::max<uint32_t>(1u, (iv.max_list_len + chunks - 1) / chunks);
+    const size_t per_q = (size_t) std::max(probes, 0) * chunks;
+    size_t qb = per_q ? std::max<size_t>(1, RK_IVF_MAX_SEGS / per_q) : nq_all;
+    if (qb > nq_all) qb = nq_all;
+
+    ws.segments = 0;
+    ws.rows_scanned = (uint64_t) total_est;
+    ws.algo_bytes = (uint64_t) nq_all * ((uint64_t) lists * row_bytes + 12ull * k) + (uint64_t) (total_est * row_bytes);
+    for (size_t q0 = 0; q0 < nq_all; q0 += qb) {
+        const size_t nq = std::min(qb, nq_all - q0);
+        const float *dQ = dQ_all + q0 * (size_t) ix->dim_pad;
+        const uint32_t nseg = (uint32_t) (nq * per_q);
+        // staging: [qseg][qmask][ctl]
+        const size_t b_qseg = (nq + 1) * 4, b_qmask = nq * (size_t) W * 8;
+        ws.plan_idx ^= 1;
+        const int pi_ = ws.plan_idx;
+        if (ws.ev_plan_used[pi_]) RK_CUDA(cudaEventSynchronize(ws.ev_plan[pi_]));
+        PinBuf &hp_ = ws.h_plan_ring[pi_];
+        if (hp_.ensure(b_qseg + b_qmask + 128) != 0) return RK_ERR_CUDA;
+        unsigned char *hp = hp_.as<unsigned char>();
+        uint32_t *hq = reinterpret_cast<uint32_t *>(hp);
+        for (size_t q = 0; q <= nq; q++) hq[q] = (uint32_t) (q * per_q);
+        uint64_t *hm = reinterpret_cast<uint64_t *>(hp + ((b_qseg + 7) & ~(size_t) 7));
+        for (size_t q = 0; q < nq; q++) {
+            const UserInfo *u = nullptr;
+            if (user_ids) {
+                auto it = ix->users.find(user_ids[q0 + q]);
+                if (it != ix->users.end()) u = &it->second;
+            }
+            for (int w = 0; w < W; w++) hm[q * W + w] = u ? u->mask[w] : 0ull;
+        }
+        uint32_t *hc = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(hm) + ((b_qmask + 15) & ~(size_t) 15));
+        hc[0] = nseg; hc[1] = 0;
+        if (ws.qseg.ensure(b_qseg) != 0 || ws.qmask.ensure(std::max<size_t>(b_qmask, 16)) != 0 || ws.ctl.ensure(64) != 0 ||
+            ws.segs.ensure(std::max<size_t>((size_t) nseg * sizeof(RkSegment), 16)) != 0 ||
+            ws.probe_list.ensure(std::max<size_t>(nq * (size_t) std::max(probes, 1) * 4, 16)) != 0)
+            return RK_ERR_CUDA;
+        RK_CUDA(cudaMemcpyAsync(ws.qseg.p, hq, b_qseg, cudaMemcpyHostToDevice, ws.stream));
+        if (b_qmask) RK_CUDA(cudaMemcpyAsync(ws.qmask.p, hm, b_qmask, cudaMemcpyHostToDevice, ws.stream));
+        RK_CUDA(cudaMemcpyAsync(ws.ctl.p, hc, 8, cudaMemcpyHostToDevice, ws.stream));
+        RK_CUDA(cudaEventRecord(ws.ev_plan[pi_], ws.stream));
+        ws.ev_plan_used[pi_] = true;
+        if (rk_ensure_cand(ws, nseg, k) != 0) return RK_ERR_CUDA;
+
+        if (nseg) {
+            if (ws.timing && q0 == 0) RK_CUDA(cudaEventRecord(ws.ev[4], ws.stream));
+            RK_CUDA(rk_launch_ivf_probe(dQ, (int) nq, iv.d_centers.as<float>(), lists, ix->dim_pad, ix->metric, o->null_query,
+                                        probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.stream));
+            RK_CUDA(rk_launch_ivf_plan(ws.probe_list.as<uint32_t>(), iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
+                                       chunk_rows, kind, ws.segs.as<RkSegment>(), ws.stream));
+            if (ws.timing && q0 == 0) { RK_CUDA(cudaEventRecord(ws.ev[5], ws.stream)); ws.timed_probe = true; }
+            RkScanParams p;
+            rk_fill_scan_params(ix, ws, p, true, dQ, o, k);
+            p.seg_order = nullptr;
+            const int slot = (int) (ws.ring_n % RK_TIMING_RING);
+            if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot], ws.stream));
+            const int grid = (int) std::min<uint32_t>((uint32_t) ix->sm_count, nseg);
+            RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid));
+            if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot], ws.stream)); ws.timed_scan = true; ws.ring_n++; }
+            ws.launches += 3;
+        }
+        RkSelectParams out = out_all;
+        const size_t ob = q0 * (size_t) k;
+        if (out.out_tid) out.out_tid += ob;
+        if (out.out_doc) out.out_doc += ob;
+        if (out.out_dist) out.out_dist += ob;
+        if (out.out_key) out.out_key += ob;
+        if (out.out_row) out.out_row += ob;
+        if (out.out_count) out.out_count += q0;
+        out.cand_key = ws.cand_key.as<uint32_t>();
+        out.cand_tid = ws.cand_tid.as<uint64_t>();
+        out.cand_row = ws.cand_row.as<uint32_t>();
+        out.cand_count = ws.cand_count.as<int32_t>();
+        out.qseg = ws.qseg.as<uint32_t>();
+        out.lists_per_query = 0;
+        out.list_stride = k;
+        out.shard_stride_bytes = 0;
+        out.k = k;
+        out.metric = ix->metric;
+        out.dedup = 0;                         // a tuple sits in exactly one list
+        out.null_query = o->null_query;
+        out.key_is_float = 0;
+        out.rowdoc = iv.d_rowdoc.as<uint32_t>();
+        out.doc_ids = ix->d_doc_ids.as<uint32_t>();
+        if (ws.timing && q0 == 0) RK_CUDA(cudaEventRecord(ws.ev[2], ws.stream));
+        RK_CUDA(rk_launch_select(out, (int) nq, ws.stream));
+        if (ws.timing && q0 == 0) { RK_CUDA(cudaEventRecord(ws.ev[3], ws.stream)); ws.timed_select = true; }
+        ws.launches++;
+        ws.segments += nseg;
+    }
+    ix->total_launches += ws.launches;
+    return RK_OK;
+}

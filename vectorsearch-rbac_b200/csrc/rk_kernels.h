@@ -17,3 +17,20 @@ cudaError_t rk_launch_gather_rows(const float *src, float *dst, const uint32_t *
 cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, int dim_pad, cudaStream_t stream);
 // counts NaN / Inf elements of a device array (synchronous; result in *out)
 cudaError_t rk_count_nonfinite(const float *d_x, size_t n, unsigned long long *out, cudaStream_t stream);
+
+// IVFFlat (rk_ivf_kernels.cu)
+cudaError_t rk_launch_assign(const float *X, size_t nrows, const float *C, int lists, int dim_pad, int metric,
+                             uint32_t *out_list, float *out_val, cudaStream_t stream);
+cudaError_t rk_launch_km_accumulate(const float *S, size_t ns, int dim_pad, const uint32_t *label, float *sums, uint32_t *counts,
+                                    cudaStream_t stream);
+cudaError_t rk_launch_km_finalize(float *C, const float *sums, const uint32_t *counts, int lists, int dim_pad, const float *S,
+                                  size_t ns, uint64_t seed, int normalize, cudaStream_t stream);
+cudaError_t rk_launch_km_normalize_rows(float *S, size_t ns, int dim_pad, cudaStream_t stream);
+cudaError_t rk_launch_count_changed(const uint32_t *a, const uint32_t *b, size_t n, unsigned long long *d_out, cudaStream_t stream);
+cudaError_t rk_launch_gather_u32(const uint32_t *src, uint32_t *dst, const uint32_t *perm, size_t n, cudaStream_t stream);
+cudaError_t rk_launch_gather_u64(const uint64_t *src, uint64_t *dst, const uint32_t *perm, size_t n, cudaStream_t stream);
+size_t rk_ivf_probe_smem(int lists, int dim_pad);
+cudaError_t rk_launch_ivf_probe(const float *Q, int nq, const float *C, int lists, int dim_pad, int metric, int null_query,
+                                int probe_offset, int probes, uint32_t *out_list, cudaStream_t stream);
+cudaError_t rk_launch_ivf_plan(const uint32_t *probe_list, const uint32_t *list_start, int nq, int probes, int chunks,
+                               uint32_t chunk_rows, uint32_t kind, RkSegment *segs, cudaStream_t stream);

@@ -235,25 +235,45 @@ struct RkProducer {
             }
             if (run_len) emit_run(run_start, run_len);
         } else {  // RK_SEG_ROWMASK
+            // Rows of a store that is NOT sorted by document (IVF lists): the role mask is reached
+            // through rowdoc[].  RK_EPL * 32 rows per step, two rounds of independent loads.
             const uint64_t *um = p.qmask + (size_t) query * p.mask_words;
             uint64_t run_start = 0, run_len = 0;
-            for (uint64_t r0 = s.begin; r0 < s.end; r0 += 32) {
-                uint64_t r = r0 + lane;
-                bool ok = false;
-                if (r < s.end) ok = mask_hit(p.doc_mask + (size_t) p.store.rowdoc[r] * p.mask_words, um);
-                unsigned bal = __ballot_sync(0xffffffffu, ok);
-                while (bal) {
-                    int b = __ffs(bal) - 1;
-                    unsigned rest = bal >> b;              // run of consecutive set bits starting at b
-                    int n = (~rest == 0u) ? 32 - b : __ffs(~rest) - 1;
-                    if (run_len && run_start + run_len == r0 + b) {
-                        run_len += n;
-                    } else {
-                        if (run_len) emit_run(run_start, run_len);
-                        run_start = r0 + b;
-                        run_len = n;
+            for (uint64_t r0 = s.begin; r0 < s.end; r0 += 32 * RK_EPL) {
+                uint32_t dd[RK_EPL];
+                bool ok[RK_EPL];
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) {
+                    const uint64_t r = r0 + (uint64_t) j * 32 + lane;
+                    ok[j] = r < s.end;
+                    dd[j] = __ldg(p.store.rowdoc + (ok[j] ? r : s.end - 1));
+                }
+                uint64_t hit[RK_EPL];
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) hit[j] = 0;
+                for (int w = 0; w < p.mask_words; w++) {
+                    const uint64_t u = __ldg(um + w);
+#pragma unroll
+                    for (int j = 0; j < RK_EPL; j++)
+                        hit[j] |= rk_ld_u64_hint(p.doc_mask + (size_t) dd[j] * p.mask_words + w, pol_keep) & u;
+                }
+#pragma unroll
+                for (int j = 0; j < RK_EPL; j++) {
+                    unsigned bal = __ballot_sync(0xffffffffu, ok[j] && hit[j] != 0);
+                    const uint64_t rb = r0 + (uint64_t) j * 32;
+                    while (bal) {
+                        int b = __ffs(bal) - 1;
+                        unsigned rest = bal >> b;              // run of consecutive set bits starting at b
+                        int n = (~rest == 0u) ? 32 - b : __ffs(~rest) - 1;
+                        if (run_len && run_start + run_len == rb + b) {
+                            run_len += n;
+                        } else {
+                            if (run_len) emit_run(run_start, run_len);
+                            run_start = rb + b;
+                            run_len = n;
+                        }
+                        bal = (b + n >= 32) ? 0u : (bal & ~((1u << (b + n)) - 1u));
                     }
-                    bal = (b + n >= 32) ? 0u : (bal & ~((1u << (b + n)) - 1u));
                 }
             }
             if (run_len) emit_run(run_start, run_len);

@@ -482,6 +482,7 @@ static int scan_fetch_batch(rk_scan *sc)
     int32_t cnt = 0;
     rk_scan_opts o = sc->opts;
     o.probes = sc->probes_eff;
+    if (o.probes > 0) o.probes = std::min(o.probes, sc->max_probes_eff - sc->probes_done);   // ivfscan.c:128 listIndex < maxProbes
     int rc = host_search(ix, sc->ws, 1, sc->q.data(), &sc->user, &o, sc->probes_done, sc->r_tid.data(), sc->r_doc.data(),
                          sc->r_dist.data(), &cnt);
     if (rc < 0) return rc;
