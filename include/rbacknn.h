@@ -74,6 +74,17 @@ typedef enum rk_filter { RK_FILTER_PARTITION = 0, RK_FILTER_BITMASK = 1, RK_FILT
  *   RK_LAYOUT_AUTO         dynamic if a role-set map was given, else combination, else role */
 typedef enum rk_layout { RK_LAYOUT_AUTO = 0, RK_LAYOUT_ROLE = 1, RK_LAYOUT_COMBINATION = 2, RK_LAYOUT_DYNAMIC = 3 } rk_layout;
 
+/* Scoring engine of a batched search.
+ *   RK_ENGINE_SCAN    bandwidth-bound CUDA-core scan, one pass over the visible rows per query
+ *                     (what a single pgvector scan does; exact fp32).
+ *   RK_ENGINE_TENSOR  tcgen05 tensor cores: the whole query batch against the row store as a dense
+ *                     contraction (|q|^2 - 2 q.x + |x|^2 or -q.x) with the permission mask in the
+ *                     epilogue; nominates candidates in TF32, re-scores them in exact fp32 and falls
+ *                     back to the scan for any query whose answer it cannot prove.  Results are
+ *                     identical to RK_ENGINE_SCAN.  Exact scans only (probes = 0), k <= 256.
+ *   RK_ENGINE_AUTO    currently RK_ENGINE_SCAN. */
+typedef enum rk_engine { RK_ENGINE_AUTO = 0, RK_ENGINE_SCAN = 1, RK_ENGINE_TENSOR = 2 } rk_engine;
+
 #define RK_MAX_DIM 2048   /* pgvector IVFFLAT_MAX_DIM is 2000 (pgvector/src/ivfflat.h:24)          */
 #define RK_MAX_K 1024     /* top-k limit of the GPU selection network                               */
 #define RK_MAX_LISTS 32768 /* IVFFLAT_MAX_LISTS (pgvector/src/ivfflat.h:44)                         */
@@ -154,7 +165,7 @@ typedef struct rk_scan_opts {
     int32_t null_query;     /* ORDER BY vec <-> NULL: every distance is 0 (ivfscan.c:181-200)       */
     int32_t layout;         /* rk_layout: which partition layout RK_FILTER_PARTITION walks          */
     int32_t keep_duplicates;/* 1 = ground-truth merge without dedup (common_function.py:713-714)    */
-    int32_t reserved[1];
+    int32_t engine;         /* rk_engine: which kernels score the batch                             */
 } rk_scan_opts;
 
 /* ivfflatbeginscan (ivfscan.c:241-315): allocates scan state (result ring, device scratch). */
@@ -222,7 +233,9 @@ typedef struct rk_stats {
     float probe_ms;            /* IVF centre scoring + list choice                                 */
     float reserved_f;
     uint64_t total_launches;   /* kernels launched since rk_open                                   */
-    uint64_t reserved[7];
+    uint64_t tensor_redo;      /* RK_ENGINE_TENSOR: queries of the last batch re-run on the scan   */
+    uint64_t tensor_exact;     /* RK_ENGINE_TENSOR: 1 = TF32 was exact for the last batch          */
+    uint64_t reserved[5];
 } rk_stats;
 int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */

@@ -10,4 +10,5 @@ Layout:
 """
 from . import _lib  # noqa: F401
 from .engine import Index, Scan, RkError, METRIC_L2, METRIC_IP, FILTER_PARTITION, FILTER_BITMASK, FILTER_NONE  # noqa: F401
+from .engine import ENGINE_AUTO, ENGINE_SCAN, ENGINE_TENSOR  # noqa: F401
 from .engine import LAYOUT_AUTO, LAYOUT_ROLE, LAYOUT_COMBINATION, LAYOUT_DYNAMIC  # noqa: F401

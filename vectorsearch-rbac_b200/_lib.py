@@ -22,14 +22,15 @@ class RkConfig(C.Structure):
 class RkScanOpts(C.Structure):
     _fields_ = [("k", C.c_int32), ("probes", C.c_int32), ("max_probes", C.c_int32), ("filter", C.c_int32),
                 ("null_query", C.c_int32), ("layout", C.c_int32), ("keep_duplicates", C.c_int32),
-                ("reserved", C.c_int32 * 1)]
+                ("engine", C.c_int32)]
 
 
 class RkStats(C.Structure):
     _fields_ = [("rows", C.c_uint64), ("docs", C.c_uint64), ("partitions", C.c_uint64), ("device_bytes", C.c_uint64),
                 ("launches", C.c_uint64), ("segments", C.c_uint64), ("rows_scanned", C.c_uint64),
                 ("algo_bytes", C.c_uint64), ("scan_ms", C.c_float), ("select_ms", C.c_float), ("probe_ms", C.c_float),
-                ("reserved_f", C.c_float), ("total_launches", C.c_uint64), ("reserved", C.c_uint64 * 7)]
+                ("reserved_f", C.c_float), ("total_launches", C.c_uint64), ("tensor_redo", C.c_uint64),
+                ("tensor_exact", C.c_uint64), ("reserved", C.c_uint64 * 5)]
 
 
 # every symbol include/rbacknn.h declares: name -> (restype, argtypes)

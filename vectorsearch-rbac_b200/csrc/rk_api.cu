@@ -161,6 +161,11 @@ extern "C" void rk_close(rk_index *ix)
                       &ix->d_ext_vstart, &ix->d_ext_mask, &ix->d_part_ext_off, &ix->ivf.d_x, &ix->ivf.d_tid,
                       &ix->ivf.d_rowdoc, &ix->ivf.d_centers, &ix->ivf.d_center_tid, &ix->ivf.d_list_start};
     for (auto *b : bufs) b->release();
+    TensorState &ts = ix->tensor;
+    DevBuf *tb[] = {&ts.d_xnorm, &ts.d_rowmask, &ts.d_probe, &ts.d_units, &ts.d_qnorm, &ts.d_scratch, &ts.d_cand_key, &ts.d_cand_row,
+                    &ts.d_cand_count, &ts.d_sel_key, &ts.d_sel_row, &ts.d_sel_count, &ts.d_flags};
+    for (auto *b : tb) b->release();
+    ts.h_flags.release();
     delete ix;
 }
 

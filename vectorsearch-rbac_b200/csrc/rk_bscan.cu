@@ -1,0 +1,678 @@
+// rk_bscan.cu — batched scoring on the 5th-generation tensor cores (tcgen05 + TMEM + TMA).
+//
+// For a batch of queries the distance computation is a dense contraction: with D = X · Qᵀ
+//   L2:  ‖x − q‖² = ‖x‖² − 2·D + ‖q‖²        (pgvector/src/vector.c:549-563)
+//   IP:  −x·q     = −D                         (pgvector/src/vector.c:596-606, :626-636)
+// so every 128-row tile of the row store is multiplied against a tile of up to 128 queries with
+// `tcgen05.mma.cta_group::1.kind::tf32` (fp32 operands straight from HBM, TF32 inside the MMA, fp32
+// accumulation in TMEM).  The permission predicate (row_level_security.py:55-65) is a per-(row, query)
+// role-mask test in the epilogue.  Tensor-core values are APPROXIMATE (TF32), so this kernel only
+// nominates candidates: per (unit, query) the `kp` rows with the smallest approximate distance.
+// rk_rescore_kernel then recomputes those rows' distances in exact fp32 with the scan kernel's
+// summation order, takes the final top-k by (distance, tuple id) and proves — or refuses to — that
+// no row outside the candidate set could belong to the answer (refused queries are re-run on the
+// exact scan path by the host).  On integer-valued data (SIFT shape) TF32 is exact and the proof
+// needs no margin.
+//
+// Shape: persistent, one 192-thread CTA per SM, static unit schedule.
+//   warp 0   TMA producer: per k-chunk of 32 floats one 128x32 box of X and one of Q
+//            (cp.async.bulk.tensor.2d, 128-byte swizzle) into a ring of stages.
+//   warp 1   MMA issuer: 4 x (M=128, N<=128, K=8) tcgen05.mma per stage, accumulators double-buffered
+//            in TMEM (2 x 128 columns); tcgen05.commit releases stages and publishes accumulators.
+//   warps 2-5  epilogue: tcgen05.ld (one TMEM lane = one row), distance, mask test, threshold test
+//            against the running per-query tau, append to per-query candidate buffers (global
+//            scratch, L2 resident); warp-parallel radix-select compaction when a buffer fills.
+#include <cuda.h>
+
+#include "rk_common.cuh"
+#include "rk_kernels.h"
+
+#define BS_M 128
+#define BS_N 128
+#define BS_KC 32
+#define BS_STAGES 5
+#define BS_CAP 1024
+#define BS_THREADS 192
+#define BS_STAGE_BYTES 32768u          // X box 16 KB + Q box 16 KB
+#define BS_SORT_MAX 512                // entries one warp sorts at unit end
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers
+
+__device__ __forceinline__ void bs_tma_2d(void *smem_dst, const CUtensorMap *tm, int c0, int c1, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+                     rk_smem_u32(smem_dst)),
+                 "l"(tm), "r"(rk_smem_u32(bar)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+
+__device__ __forceinline__ void bs_tmem_alloc(uint32_t *smem_dst, uint32_t ncols)
+{
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(rk_smem_u32(smem_dst)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void bs_tmem_dealloc(uint32_t taddr, uint32_t ncols)
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+__device__ __forceinline__ void bs_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void bs_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void bs_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(rk_smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void bs_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__device__ __forceinline__ void bs_tmem_ld16(uint32_t taddr, uint32_t (&r)[16])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte swizzle, 8-row atoms 1024 bytes apart (what the 2-D TMA box above writes).
+__device__ __forceinline__ uint64_t bs_smem_desc(uint32_t smem_addr)
+{
+    return (uint64_t) ((smem_addr >> 4) & 0x3FFFu) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// ---------------------------------------------------------------------------------------------
+
+struct BsSmem {
+    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_qn, off_um, off_hist, off_sel, off_sort, total;
+};
+
+__host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
+{
+    BsSmem s;
+    uint32_t o = 0;
+    s.off_stage = o; o += BS_STAGES * BS_STAGE_BYTES;
+    s.off_bar = o; o += 8u * (2 * BS_STAGES + 4);
+    s.off_tmem = o; o += 16;
+    s.off_tau = o; o += BS_N * 4;
+    s.off_cnt = o; o += BS_N * 4;
+    s.off_qn = o; o += BS_N * 4;
+    s.off_um = o; o += BS_N * 8u * (uint32_t) mask_words;
+    s.off_hist = o; o += 4 * 256 * 4;
+    s.off_sel = o; o += 4 * 16;
+    o = (o + 15) & ~15u;
+    s.off_sort = o; o += 4 * BS_SORT_MAX * 8;
+    s.total = o + 1024;     // slack for the manual 1024-byte alignment of the stage ring
+    return s;
+}
+
+struct BsCtx {
+    uint32_t *tau, *cnt, *hist, *sel;
+    uint2 *scratch;     // this CTA's [BS_N][BS_CAP]
+    uint64_t *sortbuf;  // this warp's [BS_SORT_MAX]
+    int lane;
+};
+
+// Exact kp-th smallest key of one query's buffer by a warp-level 4-pass radix select, then in-place
+// compaction key <= tau.  n <= BS_CAP.  Returns the new count; *tau_out receives the threshold.
+__device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint32_t n, uint32_t kp, uint32_t *tau_out)
+{
+    uint2 *buf = c.scratch + (size_t) q * BS_CAP;
+    uint32_t key[BS_CAP / 32];
+#pragma unroll
+    for (int j = 0; j < BS_CAP / 32; j++) {
+        const uint32_t i = (uint32_t) c.lane + 32u * j;
+        key[j] = i < n ? buf[i].x : RK_KEY_SENTINEL;
+    }
+    uint32_t prefix = 0, mask = 0, kk = kp;
+#pragma unroll 1
+    for (int shift = 24; shift >= 0; shift -= 8) {
+#pragma unroll
+        for (int b = 0; b < 8; b++) c.hist[c.lane * 8 + b] = 0;
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < BS_CAP / 32; j++) {
+            const uint32_t i = (uint32_t) c.lane + 32u * j;
+            if (i < n && (key[j] & mask) == prefix) atomicAdd(&c.hist[(key[j] >> shift) & 255u], 1u);
+        }
+        __syncwarp();
+        uint32_t h[8], tot = 0;
+#pragma unroll
+        for (int b = 0; b < 8; b++) { h[b] = c.hist[c.lane * 8 + b]; tot += h[b]; }
+        uint32_t inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (c.lane >= o) inc += u; }
+        uint32_t run = inc - tot;
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            if (run < kk && kk <= run + h[b]) { c.sel[0] = (uint32_t) (c.lane * 8 + b); c.sel[1] = kk - run; }
+            run += h[b];
+        }
+        __syncwarp();
+        prefix |= c.sel[0] << shift;
+        mask |= 0xFFu << shift;
+        kk = c.sel[1];
+        __syncwarp();
+    }
+    const uint32_t tau = prefix;
+    // compaction: rows of the survivors are read before anything is overwritten
+    uint32_t row[BS_CAP / 32];
+    uint32_t mine = 0;
+#pragma unroll
+    for (int j = 0; j < BS_CAP / 32; j++) {
+        const uint32_t i = (uint32_t) c.lane + 32u * j;
+        const bool keep = i < n && key[j] <= tau;
+        row[j] = keep ? buf[i].y : 0u;
+        mine += keep;
+    }
+    uint32_t inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (c.lane >= o) inc += u; }
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    uint32_t pos = inc - mine;
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < BS_CAP / 32; j++) {
+        const uint32_t i = (uint32_t) c.lane + 32u * j;
+        if (i < n && key[j] <= tau) buf[pos++] = make_uint2(key[j], row[j]);
+    }
+    __syncwarp();
+    *tau_out = tau;
+    return total;
+}
+
+// Keep the entries with key <= bound (in place).  Returns the new count.
+__device__ __forceinline__ uint32_t bs_warp_filter(const BsCtx &c, int q, uint32_t n, uint32_t bound)
+{
+    uint2 *buf = c.scratch + (size_t) q * BS_CAP;
+    uint2 e[BS_CAP / 32];
+    uint32_t mine = 0;
+#pragma unroll
+    for (int j = 0; j < BS_CAP / 32; j++) {
+        const uint32_t i = (uint32_t) c.lane + 32u * j;
+        e[j] = i < n ? buf[i] : make_uint2(RK_KEY_SENTINEL, 0u);
+        mine += i < n && e[j].x <= bound;
+    }
+    uint32_t inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (c.lane >= o) inc += u; }
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    uint32_t pos = inc - mine;
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < BS_CAP / 32; j++) {
+        const uint32_t i = (uint32_t) c.lane + 32u * j;
+        if (i < n && e[j].x <= bound) buf[pos++] = e[j];
+    }
+    __syncwarp();
+    return total;
+}
+
+// Sort the first n (<= BS_SORT_MAX) entries of a query's buffer by (key, row) in this warp's shared
+// scratch and write the first min(n, kp) to the unit's candidate list.
+__device__ __forceinline__ void bs_warp_emit(const BsCtx &c, int q, uint32_t n, uint32_t kp, uint32_t *out_key, uint32_t *out_row,
+                                             int32_t *out_count)
+{
+    const uint2 *buf = c.scratch + (size_t) q * BS_CAP;
+    uint32_t P = 32;
+    while (P < n) P <<= 1;
+    for (uint32_t i = c.lane; i < P; i += 32) {
+        uint64_t v = ~0ull;
+        if (i < n) { const uint2 e = buf[i]; v = ((uint64_t) e.x << 32) | e.y; }
+        c.sortbuf[i] = v;
+    }
+    __syncwarp();
+    for (uint32_t size = 2; size <= P; size <<= 1) {
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            for (uint32_t i = c.lane; i < (P >> 1); i += 32) {
+                const uint32_t lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const uint64_t a = c.sortbuf[lo], b = c.sortbuf[hi];
+                if (up ? (b < a) : (a < b)) { c.sortbuf[lo] = b; c.sortbuf[hi] = a; }
+            }
+            __syncwarp();
+        }
+    }
+    const uint32_t m = n < kp ? n : kp;
+    for (uint32_t i = c.lane; i < m; i += 32) {
+        const uint64_t v = c.sortbuf[i];
+        out_key[i] = (uint32_t) (v >> 32);
+        out_row[i] = (uint32_t) v;
+    }
+    if (c.lane == 0) *out_count = (int32_t) m;
+    __syncwarp();
+}
+
+template <int METRIC>
+__global__ void __launch_bounds__(BS_THREADS, 1)
+rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmq, const RkBScanParams p)
+{
+    extern __shared__ unsigned char smem_raw[];
+    const BsSmem L = bs_smem_layout(p.mask_words);
+    // the swizzled stage ring must sit on a 1024-byte boundary
+    unsigned char *smem = smem_raw + ((1024u - (rk_smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.off_bar);
+    uint64_t *empty = full + BS_STAGES;
+    uint64_t *tfull = empty + BS_STAGES;      // [2] accumulator ready
+    uint64_t *tempty = tfull + 2;             // [2] accumulator drained
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(smem + L.off_tmem);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < BS_STAGES; s++) { rk_mbar_init(&full[s], 1); rk_mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; b++) { rk_mbar_init(&tfull[b], 1); rk_mbar_init(&tempty[b], 4); }
+        rk_fence_barrier_init();
+    }
+    if (warp == 1) bs_tmem_alloc(s_tmem, 2 * BS_N);
+    bs_fence_before();
+    __syncthreads();
+    bs_fence_after();
+    const uint32_t tmem_base = *s_tmem;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
+                const RkBUnit un = p.units[u];
+                for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++) {
+                    const int row0 = (int) (tile * BS_M);
+                    for (int kc = 0; kc < p.kchunks; kc++) {
+                        rk_mbar_wait(&empty[stage], phase ^ 1u);
+                        unsigned char *st = smem + L.off_stage + (size_t) stage * BS_STAGE_BYTES;
+                        rk_mbar_arrive_expect_tx(&full[stage], BS_STAGE_BYTES);
+                        bs_tma_2d(st, &tmx, kc * BS_KC, row0, &full[stage]);
+                        bs_tma_2d(st + 16384, &tmq, kc * BS_KC, (int) un.q0, &full[stage]);
+                        if (++stage == BS_STAGES) { stage = 0; phase ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        int stage = 0;
+        uint32_t phase = 0, tcount = 0;
+        for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
+            const RkBUnit un = p.units[u];
+            uint32_t ncol = (un.nq + 15u) & ~15u;
+            if (ncol < 16) ncol = 16;
+            // c=F32, a=b=TF32, K-major both, N>>3, M>>4
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((ncol >> 3) << 17) | ((BS_M >> 4) << 24);
+            for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
+                const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
+                rk_mbar_wait(&tempty[buf], tph ^ 1u);
+                bs_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * BS_N;
+                for (int kc = 0; kc < p.kchunks; kc++) {
+                    rk_mbar_wait(&full[stage], phase);
+                    bs_fence_after();
+                    if (lane == 0) {
+                        const uint32_t a0 = rk_smem_u32(smem + L.off_stage + (size_t) stage * BS_STAGE_BYTES);
+                        const uint64_t ad = bs_smem_desc(a0), bd = bs_smem_desc(a0 + 16384u);
+#pragma unroll
+                        for (int k = 0; k < BS_KC / 8; k++)      // 8 tf32 = 32 bytes per MMA: +2 in 16-byte units
+                            bs_mma_tf32(d_tmem, ad + (uint64_t) (2 * k), bd + (uint64_t) (2 * k), idesc, (kc | k) != 0);
+                        bs_commit(&empty[stage]);
+                        if (kc == p.kchunks - 1) bs_commit(&tfull[buf]);
+                    }
+                    __syncwarp();
+                    if (++stage == BS_STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int ew = warp - 2;                       // 0..3 (compaction work split)
+        const int quarter = warp & 3;                  // TMEM lanes this warp may read: [32 * (warp % 4), +32)
+        const int erow = quarter * 32 + lane;          // row of the tile == TMEM lane
+        const int et = ew * 32 + lane;                 // 0..127 epilogue thread index
+        BsCtx c;
+        c.tau = reinterpret_cast<uint32_t *>(smem + L.off_tau);
+        c.cnt = reinterpret_cast<uint32_t *>(smem + L.off_cnt);
+        c.hist = reinterpret_cast<uint32_t *>(smem + L.off_hist) + ew * 256;
+        c.sel = reinterpret_cast<uint32_t *>(smem + L.off_sel) + ew * 4;
+        c.scratch = p.scratch + (size_t) blockIdx.x * BS_N * BS_CAP;
+        c.sortbuf = reinterpret_cast<uint64_t *>(smem + L.off_sort) + ew * BS_SORT_MAX;
+        c.lane = lane;
+        float *s_qn = reinterpret_cast<float *>(smem + L.off_qn);
+        uint64_t *s_um = reinterpret_cast<uint64_t *>(smem + L.off_um);
+        const int W = p.mask_words;
+        auto esync = [] { rk_named_bar_sync(2, 128); };
+        uint32_t tcount = 0;
+        for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
+            const RkBUnit un = p.units[u];
+            esync();                                   // previous unit fully emitted
+            c.tau[et] = RK_KEY_SENTINEL;
+            c.cnt[et] = 0;
+            s_qn[et] = (uint32_t) et < un.nq ? p.qnorm[un.q0 + et] : 0.f;
+            for (int w = 0; w < W; w++) s_um[et * W + w] = ((uint32_t) et < un.nq && p.qmask) ? p.qmask[(size_t) (un.q0 + et) * W + w] : 0ull;
+            esync();
+            const uint32_t ncol = (un.nq + 15u) & ~15u;
+            for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
+                const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
+                const uint64_t row = (uint64_t) tile * BS_M + (uint64_t) erow;
+                const bool valid = row < p.nrows;
+                float xn = 0.f;
+                uint64_t m0 = 0, m1 = 0;
+                if (valid) {
+                    if (METRIC == 0) xn = p.xnorm[row];
+                    if (p.use_mask) {
+                        m0 = p.rowmask[row * W];
+                        if (W > 1) m1 = p.rowmask[row * W + 1];
+                    }
+                }
+                rk_mbar_wait(&tfull[buf], tph);
+                bs_fence_after();
+                const uint32_t taddr = tmem_base + buf * BS_N + ((uint32_t) (quarter * 32) << 16);
+                for (uint32_t c0 = 0; c0 < ncol; c0 += 16) {
+                    uint32_t r[16];
+                    bs_tmem_ld16(taddr + c0, r);
+#pragma unroll
+                    for (int j = 0; j < 16; j++) {
+                        const uint32_t q = c0 + j;
+                        if (q < un.nq) {               // uniform across the CTA
+                            const float v = __uint_as_float(r[j]);
+                            const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn + s_qn[q]) : -v;
+                            bool ok = valid;
+                            if (p.use_mask && valid) {
+                                uint64_t hit = (m0 & s_um[q * W]) | (W > 1 ? (m1 & s_um[q * W + 1]) : 0ull);
+                                for (int w = 2; w < W; w++) hit |= p.rowmask[row * W + w] & s_um[q * W + w];
+                                ok = hit != 0;
+                            }
+                            const uint32_t key = rk_float_to_key(dist);
+                            if (ok && key <= c.tau[q]) {
+                                const uint32_t slot = atomicAdd(&c.cnt[q], 1u);
+                                c.scratch[(size_t) q * BS_CAP + slot] = make_uint2(key, (uint32_t) row);
+                            }
+                        }
+                    }
+                }
+                bs_fence_before();
+                __syncwarp();
+                if (lane == 0) rk_mbar_arrive(&tempty[buf]);
+                esync();                               // all appends of this tile are in
+                // a tile adds at most 128 entries per query: compact what could overflow on the next one
+                for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
+                    const uint32_t n = c.cnt[q];
+                    if (n > BS_CAP - BS_M) {
+                        uint32_t tau;
+                        uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                        if (m > BS_CAP / 2 && tau > 0) {
+                            // more than half the buffer ties at the kp-th key: drop that key altogether
+                            // and record that the list is no longer complete (the query is re-run exactly)
+                            tau -= 1u;
+                            m = bs_warp_filter(c, (int) q, m, tau);
+                            if (lane == 0) p.trunc[un.q0 + q] = 1;
+                        }
+                        if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; }
+                    }
+                }
+                esync();
+            }
+            // unit end: every query's list, sorted by (approximate key, row), at most kp entries
+            for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
+                uint32_t n = c.cnt[q];
+                if (n > (uint32_t) p.kp) {
+                    uint32_t tau;
+                    n = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                    if (n > BS_SORT_MAX && tau > 0) {
+                        n = bs_warp_filter(c, (int) q, n, tau - 1u);
+                        if (lane == 0) p.trunc[un.q0 + q] = 1;
+                    }
+                    if (n > BS_SORT_MAX) n = BS_SORT_MAX;
+                }
+                const size_t list = (size_t) u * BS_N + q;
+                bs_warp_emit(c, (int) q, n, (uint32_t) p.kp, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
+            }
+        }
+    }
+    __syncthreads();
+    if (warp == 1) bs_tmem_dealloc(tmem_base, 2 * BS_N);
+}
+
+// ---------------------------------------------------------------------------------------------
+// exact re-scoring of the nominated rows + final top-k + sufficiency proof
+
+#define RS_THREADS 256
+#define RS_MAX 512
+
+template <int METRIC>
+__global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreParams p)
+{
+    extern __shared__ __align__(16) unsigned char rs_smem[];
+    float4 *qs = reinterpret_cast<float4 *>(rs_smem);                                  // [dim4]
+    uint64_t *s_tid = reinterpret_cast<uint64_t *>(rs_smem + (size_t) p.dim_pad * 4);   // [RS_MAX]
+    uint32_t *s_key = reinterpret_cast<uint32_t *>(s_tid + RS_MAX);
+    uint32_t *s_row = s_key + RS_MAX;
+    const int q = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int dim4 = p.dim_pad >> 2;
+    const float4 *q4 = reinterpret_cast<const float4 *>(p.q + (size_t) q * p.dim_pad);
+    for (int i = t; i < dim4; i += RS_THREADS) qs[i] = q4[i];
+    const int n = p.sel_count[q];
+    int P = 32;
+    while (P < n) P <<= 1;
+    for (int i = n + t; i < P; i += RS_THREADS) { s_key[i] = RK_KEY_SENTINEL; s_tid[i] = ~0ull; s_row[i] = 0xFFFFFFFFu; }
+    __syncthreads();
+    // 4 rows per warp step, 8 lanes per row: the scan kernel's summation order
+    const int g = lane >> 3, l8 = lane & 7;
+    for (int i0 = warp * 4; i0 < n; i0 += (RS_THREADS / 32) * 4) {
+        const int i = i0 + g;
+        const bool v = i < n;
+        const uint32_t row = p.sel_row[(size_t) q * p.kp + (v ? i : 0)];
+        const float4 *xr = reinterpret_cast<const float4 *>(p.x + (size_t) row * p.dim_pad);
+        float s = 0.f;
+        if (!p.null_query) s = rk_row_sum8<METRIC>(xr, qs, dim4, l8);
+        if (v && l8 == 0) {
+            s_key[i] = rk_float_to_key(METRIC == 0 ? s : -s);
+            s_row[i] = row;
+            s_tid[i] = p.tid[row];
+        }
+    }
+    __syncthreads();
+    // bitonic sort by (key, tid)
+    for (int size = 2; size <= P; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = t; i < (P >> 1); i += RS_THREADS) {
+                const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const uint32_t ka = s_key[lo], kb = s_key[hi];
+                const uint64_t ta = s_tid[lo], tb = s_tid[hi];
+                const bool a_lt_b = ka < kb || (ka == kb && ta < tb), b_lt_a = kb < ka || (ka == kb && tb < ta);
+                if (up ? b_lt_a : a_lt_b) {
+                    s_key[lo] = kb; s_key[hi] = ka; s_tid[lo] = tb; s_tid[hi] = ta;
+                    const uint32_t ra = s_row[lo], rb = s_row[hi];
+                    s_row[lo] = rb; s_row[hi] = ra;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    const int k = p.k;
+    const int cnt = n < k ? n : k;
+    const size_t ob = (size_t) q * k;
+    for (int i = t; i < k; i += RS_THREADS) {
+        const bool ok = i < cnt;
+        const float ord = ok ? rk_key_to_float(s_key[i]) : __int_as_float(0x7f800000);
+        if (p.out_tid) p.out_tid[ob + i] = ok ? s_tid[i] : ~0ull;
+        if (p.out_key) p.out_key[ob + i] = ord;
+        if (p.out_doc) p.out_doc[ob + i] = ok ? p.doc_ids[p.rowdoc[s_row[i]]] : 0xFFFFFFFFu;
+        if (p.out_dist) {
+            double v;
+            if (!ok) v = __longlong_as_double(0x7ff0000000000000ll);
+            else if (p.null_query) v = 0.0;
+            else if (METRIC == 0) v = sqrt((double) ord);      // vector.c:577
+            else v = (double) ord;                             // vector.c:635
+            p.out_dist[ob + i] = v;
+        }
+    }
+    if (t == 0) {
+        if (p.out_count) p.out_count[q] = cnt;
+        // Sufficiency: a row outside the candidate set has approximate value >= a_last (the largest
+        // approximate value kept, when the list is saturated).  Its exact value is then >= a_last - eps.
+        // The answer is proven iff that exceeds the exact k-th value (strictly, so that no tie on the
+        // k-th value with a smaller tuple id can hide outside).
+        int uncertain = p.trunc ? p.trunc[q] : 0;
+        if (n >= p.kp && cnt > 0) {
+            const float a_last = p.sel_key[(size_t) q * p.kp + (n - 1)];
+            const float e_k = rk_key_to_float(s_key[cnt - 1]);
+            float eps = 0.f;
+            if (p.eps_scale > 0.f) eps = p.eps_scale * sqrtf(p.xnorm_max * p.qnorm[q]) + 1e-6f * (p.xnorm_max + p.qnorm[q]);
+            if (cnt < k || !(a_last - eps > e_k)) uncertain = 1;
+        }
+        p.uncertain[q] = uncertain;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// preparation kernels: row norms, per-row masks, TF32-exactness probe
+
+__global__ void rk_row_norms_kernel(const float *__restrict__ x, size_t n, int dim_pad, float *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const size_t warp = (blockIdx.x * (size_t) blockDim.x + threadIdx.x) >> 5;
+    const size_t nw = ((size_t) gridDim.x * blockDim.x) >> 5;
+    const int dim4 = dim_pad >> 2;
+    for (size_t r = warp; r < n; r += nw) {
+        const float4 *p4 = reinterpret_cast<const float4 *>(x + r * (size_t) dim_pad);
+        float s = 0.f;
+        for (int c = lane; c < dim4; c += 32) { const float4 v = p4[c]; s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s); }
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) out[r] = s;
+    }
+}
+
+__global__ void rk_rowmask_kernel(const uint32_t *__restrict__ rowdoc, const uint64_t *__restrict__ doc_mask, size_t n, int W,
+                                  uint64_t *__restrict__ out)
+{
+    const size_t total = n * (size_t) W;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < total; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / W;
+        const int w = (int) (i % W);
+        out[i] = doc_mask[(size_t) rowdoc[r] * W + w];
+    }
+}
+
+// out[0] = number of elements that are not small integers (|v| <= 2047, v == rint(v)); out[1] = max |v| bits
+__global__ void rk_tf32_probe_kernel(const float *__restrict__ x, size_t n, unsigned long long *out)
+{
+    unsigned bad = 0;
+    unsigned mx = 0;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const float v = x[i];
+        const float a = fabsf(v);
+        bad += !(a <= 2047.0f && v == rintf(v));
+        mx = max(mx, __float_as_uint(a));
+    }
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0) {
+        if (bad) atomicAdd(&out[0], (unsigned long long) bad);
+        atomicMax(&out[1], (unsigned long long) mx);
+    }
+}
+
+__global__ void rk_max_f32_kernel(const float *__restrict__ x, size_t n, unsigned *out)
+{
+    unsigned mx = 0;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
+        mx = max(mx, __float_as_uint(fabsf(x[i])));
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0) atomicMax(out, mx);
+}
+
+cudaError_t rk_launch_row_norms(const float *x, size_t n, int dim_pad, float *out, cudaStream_t stream)
+{
+    if (n) rk_row_norms_kernel<<<148 * 8, 256, 0, stream>>>(x, n, dim_pad, out);
+    return cudaGetLastError();
+}
+cudaError_t rk_launch_rowmask(const uint32_t *rowdoc, const uint64_t *doc_mask, size_t n, int W, uint64_t *out, cudaStream_t stream)
+{
+    if (n) rk_rowmask_kernel<<<148 * 8, 256, 0, stream>>>(rowdoc, doc_mask, n, W, out);
+    return cudaGetLastError();
+}
+cudaError_t rk_launch_tf32_probe(const float *x, size_t n, unsigned long long *d_out2, cudaStream_t stream)
+{
+    if (n) rk_tf32_probe_kernel<<<148 * 8, 256, 0, stream>>>(x, n, d_out2);
+    return cudaGetLastError();
+}
+cudaError_t rk_launch_max_f32(const float *x, size_t n, unsigned *d_out, cudaStream_t stream)
+{
+    if (n) rk_max_f32_kernel<<<148 * 4, 256, 0, stream>>>(x, n, d_out);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// host launchers
+
+size_t rk_bscan_smem_bytes(int mask_words) { return bs_smem_layout(mask_words).total; }
+size_t rk_bscan_scratch_bytes(int grid) { return (size_t) grid * BS_N * BS_CAP * sizeof(uint2); }
+
+typedef CUresult (*rk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 2-D fp32 tensor [rows][dim_pad], box = 32 floats x 128 rows, 128-byte swizzle, zero fill out of bounds.
+static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad)
+{
+    static rk_encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess) return e;
+        if (!fn || qres != cudaDriverEntryPointSuccess) return cudaErrorNotSupported;
+        encode = reinterpret_cast<rk_encode_fn>(fn);
+    }
+    cuuint64_t gdim[2] = {(cuuint64_t) dim_pad, (cuuint64_t) (rows ? rows : 1)};
+    cuuint64_t gstride[1] = {(cuuint64_t) dim_pad * 4};
+    cuuint32_t box[2] = {BS_KC, BS_M};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream)
+{
+    CUtensorMap tmx, tmq;
+    cudaError_t e = make_tensor_map(&tmx, x, p.nrows, p.dim_pad);
+    if (e != cudaSuccess) return e;
+    e = make_tensor_map(&tmq, q, nq, p.dim_pad);
+    if (e != cudaSuccess) return e;
+    const size_t smem = rk_bscan_smem_bytes(p.mask_words);
+    auto kern = p.metric == 0 ? rk_bscan_kernel<0> : rk_bscan_kernel<1>;
+    static bool attr_set[2];
+    if (!attr_set[p.metric & 1]) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set[p.metric & 1] = true;
+    }
+    kern<<<grid, BS_THREADS, smem, stream>>>(tmx, tmq, p);
+    return cudaGetLastError();
+}
+
+cudaError_t rk_launch_rescore(const RkRescoreParams &p, int nq, cudaStream_t stream)
+{
+    if (nq <= 0) return cudaSuccess;
+    const size_t smem = (size_t) p.dim_pad * 4 + RS_MAX * 16;
+    if (p.metric == 0) rk_rescore_kernel<0><<<nq, RS_THREADS, smem, stream>>>(p);
+    else rk_rescore_kernel<1><<<nq, RS_THREADS, smem, stream>>>(p);
+    return cudaGetLastError();
+}

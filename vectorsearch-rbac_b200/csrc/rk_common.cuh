@@ -71,6 +71,7 @@ struct RkSelectParams {
     const uint32_t *qseg;       // [nq+1] segment range per query
     int lists_per_query;        // if > 0: query q owns lists [q*L, (q+1)*L) (shard merge / fixed plans) and qseg is ignored
     int list_stride;            // entries between consecutive lists
+    int count_stride;           // fixed-list mode: cand_count[j * count_stride + q] (0 = number of queries launched)
     size_t shard_stride_bytes;  // fixed-list mode: bytes between list j and j+1 of one array (0 = dense nq*k elements)
     int k;
     int metric;
@@ -87,6 +88,49 @@ struct RkSelectParams {
     int32_t *out_count;
     float *out_key;             // exchange form: fp32 ordering value
     uint32_t *out_row;
+};
+
+// ---- batched tensor-core engine (rk_bscan.cu) ------------------------------------------------
+// One unit = one tile of up to 128 queries x a contiguous range of 128-row tiles of the row store.
+struct RkBUnit {
+    uint32_t q0, nq;             // queries [q0, q0 + nq)
+    uint32_t tile_begin, tile_end;
+};
+
+struct RkBScanParams {
+    const RkBUnit *units;
+    uint32_t nunits;
+    uint64_t nrows;
+    int dim_pad, kchunks, metric, kp, mask_words, use_mask;
+    const float *xnorm;          // [rows] squared norms (L2 only)
+    const uint64_t *rowmask;     // [rows][mask_words] role mask of each row's document
+    const float *qnorm;          // [nq]
+    const uint64_t *qmask;       // [nq][mask_words]
+    uint2 *scratch;              // [grid][128][1024] (approximate key, row) candidate buffers
+    uint32_t *cand_key;          // [nunits * 128][kp] sorted by (key, row)
+    uint32_t *cand_row;
+    int32_t *cand_count;         // [nunits * 128]
+    int32_t *trunc;              // [nq] set when ties at a threshold had to be dropped
+};
+
+struct RkRescoreParams {
+    const float *x;              // row store
+    const uint64_t *tid;
+    const uint32_t *rowdoc, *doc_ids;
+    const float *q;              // [nq][dim_pad]
+    const float *qnorm;
+    int dim_pad, k, kp, metric, null_query;
+    const float *sel_key;        // [nq][kp] approximate ordering values, ascending
+    const uint32_t *sel_row;
+    const int32_t *sel_count;
+    const int32_t *trunc;
+    float eps_scale, xnorm_max;  // error bound of the tensor-core value: eps_scale * sqrt(xnorm_max * qnorm) (0 = exact)
+    uint64_t *out_tid;
+    uint32_t *out_doc;
+    double *out_dist;
+    float *out_key;
+    int32_t *out_count;
+    int32_t *uncertain;          // [nq] 1 = the candidate set is not provably sufficient: re-run on the exact path
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -214,6 +258,34 @@ __device__ __forceinline__ uint64_t rk_ld_u64_hint(const uint64_t *p, uint64_t p
 __device__ __forceinline__ void rk_named_bar_sync(int id, int nthreads)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Exact fp32 sum of one row against one query as the scan kernel forms it: 8 lanes per row, lane l8
+// takes float4 columns l8, l8+8, ...; partial sums (x+y)+(z+w), then xor-shuffles 4, 2, 1.  Every
+// kernel that reports a distance uses this order so that all engines agree bit for bit.
+template <int METRIC>
+__device__ __forceinline__ void rk_acc4(float4 &acc, const float4 &x, const float4 &q)
+{
+    if (METRIC == 0) {
+        float d0 = x.x - q.x, d1 = x.y - q.y, d2 = x.z - q.z, d3 = x.w - q.w;
+        acc.x = fmaf(d0, d0, acc.x); acc.y = fmaf(d1, d1, acc.y);
+        acc.z = fmaf(d2, d2, acc.z); acc.w = fmaf(d3, d3, acc.w);
+    } else {
+        acc.x = fmaf(x.x, q.x, acc.x); acc.y = fmaf(x.y, q.y, acc.y);
+        acc.z = fmaf(x.z, q.z, acc.z); acc.w = fmaf(x.w, q.w, acc.w);
+    }
+}
+
+template <int METRIC>
+__device__ __forceinline__ float rk_row_sum8(const float4 *__restrict__ row, const float4 *__restrict__ q, int dim4, int l8)
+{
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = l8; c < dim4; c += 8) rk_acc4<METRIC>(a, row[c], q[c]);
+    float s = (a.x + a.y) + (a.z + a.w);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    return s;
 }
 
 // Named barrier that also ORs a predicate over all participating threads; every thread receives

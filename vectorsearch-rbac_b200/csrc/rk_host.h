@@ -80,6 +80,20 @@ struct IvfIndex {
     int chunks_per_list = 1;
 };
 
+// State of the batched tensor-core engine (rk_tensor.cu / rk_bscan.cu); used by the index's own
+// workspace only (rk_search_batch*).
+struct TensorState {
+    bool ready = false;
+    DevBuf d_xnorm, d_rowmask, d_probe;
+    bool x_integer = false;
+    float x_absmax = 0.f, xnorm_max = 0.f;
+    DevBuf d_units, d_qnorm, d_scratch, d_cand_key, d_cand_row, d_cand_count, d_sel_key, d_sel_row, d_sel_count, d_flags;
+    PinBuf h_flags;
+    double last_flop = 0.0;
+    uint32_t last_redo = 0;
+    bool last_exact = false;
+};
+
 struct rk_index {
     rk_config cfg{};
     int dim = 0, dim_pad = 0, metric = 0, device = 0, k_max = 0, sm_count = 148;
@@ -113,6 +127,7 @@ struct rk_index {
     DevBuf d_tid, d_rowdoc, d_doc_ids, d_doc_mask, d_ext_row, d_ext_vstart, d_ext_mask, d_part_ext_off;
     uint64_t device_bytes = 0;
     IvfIndex ivf;
+    TensorState tensor;
     Workspace ws;
     uint64_t total_launches = 0;
     float last_scan_ms = 0, last_select_ms = 0, last_probe_ms = 0;
@@ -133,6 +148,11 @@ struct rk_scan {
     int probes_done = 0;        // lists consumed so far (iterative scan)
     int max_probes_eff = 0, probes_eff = 0;
 };
+
+// rk_tensor.cu
+int rk_tensor_supported(const rk_index *ix, const rk_scan_opts *o);
+int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids, const rk_scan_opts *o,
+                     const RkSelectParams &out, std::vector<uint32_t> &redo);
 
 // rk_ivf.cu
 int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids,

@@ -44,7 +44,10 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     auto b8 = [&](uint32_t j) -> size_t {
         return p.lists_per_query > 0 ? (size_t) j * st8 + (size_t) q * p.list_stride : (size_t) (l0 + j) * (size_t) p.list_stride;
     };
-    auto list_count = [&](uint32_t j) -> int { return p.cand_count ? p.cand_count[p.lists_per_query > 0 ? j * gridDim.x + q : l0 + j] : k; };
+    const uint32_t cstride = p.count_stride ? (uint32_t) p.count_stride : gridDim.x;
+    auto list_count = [&](uint32_t j) -> int { return p.cand_count ? p.cand_count[p.lists_per_query > 0 ? j * cstride + q : l0 + j] : k; };
+    // lists without tuple ids (tensor-engine nominations) order ties by row
+    auto load_tid = [&](size_t a8, size_t a4) -> uint64_t { return p.cand_tid ? p.cand_tid[a8] : (uint64_t) p.cand_row[a4]; };
 
     auto load_key = [&](size_t a) -> uint32_t {
         const uint32_t raw = p.cand_key[a];
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
             for (int i = 0; i < cnt; i++) {
                 const uint32_t key = load_key(a4 + i);
                 if (key > tau || key == RK_KEY_SENTINEL) break;
-                const uint64_t tid = p.cand_tid[a8 + i];
+                const uint64_t tid = load_tid(a8 + i, a4 + i);
                 if (tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u) break;   // exchange-form padding
                 const uint32_t slot = atomicAdd(&s_count, 1u);
                 if (slot >= RK_CAND_CAP) { s_overflow = 1; break; }
@@ -95,7 +98,7 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
             if (i < list_count(j)) {
                 const size_t a = b4(j) + i;
                 const uint32_t key = load_key(a);
-                const uint64_t tid = p.cand_tid[b8(j) + i];
+                const uint64_t tid = load_tid(b8(j) + i, a);
                 // padding: sentinel key, or (+Inf, UINT64_MAX) in exchange form
                 const bool pad = key == RK_KEY_SENTINEL || (tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u);
                 if (key <= tau && !pad) {

@@ -26,6 +26,7 @@ static int validate_opts(const rk_index *ix, const rk_scan_opts *o)
     if (o->k < 1 || o->k > ix->k_max) return rk_fail(RK_ERR_INVALID, "k = %d outside 1..k_max (%d)", o->k, ix->k_max);
     if (o->probes < 0 || o->probes > RK_MAX_LISTS) return rk_fail(RK_ERR_INVALID, "probes = %d outside 0..%d", o->probes, RK_MAX_LISTS);
     if (o->filter < RK_FILTER_PARTITION || o->filter > RK_FILTER_NONE) return rk_fail(RK_ERR_INVALID, "unknown filter %d", o->filter);
+    if (o->engine < RK_ENGINE_AUTO || o->engine > RK_ENGINE_TENSOR) return rk_fail(RK_ERR_INVALID, "unknown engine %d", o->engine);
     if (o->probes > 0 && !ix->ivf.built) return rk_fail(RK_ERR_STATE, "probes > 0 but no IVFFlat index was built");
     return 0;
 }
@@ -279,6 +280,9 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
 
 // One batch on device: dQ [nq][dim_pad].  `out` carries the destination pointers (device).
 static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids,
+                         const rk_scan_opts *o, int probe_offset, RkSelectParams out);
+
+static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids,
                          const rk_scan_opts *o, int probe_offset, RkSelectParams out)
 {
     RK_CUDA(cudaSetDevice(ix->device));
@@ -286,6 +290,37 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
     ws.timed_scan = ws.timed_select = ws.timed_probe = false;
     if (nq == 0) return RK_OK;
     if (o->probes > 0) return rk_ivf_search(ix, ws, nq, dQ, user_ids, o, probe_offset, out);
+    if (o->engine == RK_ENGINE_TENSOR) {
+        if (!rk_tensor_supported(ix, o)) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR needs an exact scan (probes = 0), k <= 256, no keep_duplicates / NULL query");
+        if (&ws != &ix->ws) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR is a batch engine (rk_search_batch*), not available on scan handles");
+        std::vector<uint32_t> redo;
+        int rc = rk_tensor_search(ix, ws, nq, dQ, user_ids, o, out, redo);
+        if (rc < 0) return rc;
+        ix->total_launches += ws.launches;
+        if (redo.empty()) return RK_OK;
+        // unproven answers go through the exact scan; the whole batch if that is most of it
+        rk_scan_opts o2 = *o;
+        o2.engine = RK_ENGINE_SCAN;
+        const uint64_t tl = ws.launches;
+        if (redo.size() * 4 > nq) {
+            rc = search_device(ix, ws, nq, dQ, user_ids, &o2, 0, out);
+        } else {
+            for (uint32_t q : redo) {
+                RkSelectParams o1 = out;
+                const size_t ob = (size_t) q * o->k;
+                if (o1.out_tid) o1.out_tid += ob;
+                if (o1.out_doc) o1.out_doc += ob;
+                if (o1.out_dist) o1.out_dist += ob;
+                if (o1.out_key) o1.out_key += ob;
+                if (o1.out_row) o1.out_row += ob;
+                if (o1.out_count) o1.out_count += q;
+                rc = search_device(ix, ws, 1, dQ + (size_t) q * ix->dim_pad, user_ids ? user_ids + q : nullptr, &o2, 0, o1);
+                if (rc < 0) break;
+            }
+        }
+        ws.launches += tl;
+        return rc;
+    }
 
     uint32_t nseg = 0;
     int rc = build_exact_plan(ix, ws, nq, user_ids, o, &nseg);
@@ -600,5 +635,7 @@ extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)
     out->select_ms = ix->last_select_ms;
     out->probe_ms = ix->last_probe_ms;
     out->total_launches = ix->total_launches;
+    out->tensor_redo = ix->tensor.last_redo;
+    out->tensor_exact = ix->tensor.last_exact ? 1 : 0;
     return RK_OK;
 }

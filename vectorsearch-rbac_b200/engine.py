@@ -13,6 +13,7 @@ from ._lib import RkConfig, RkScanOpts, RkStats, lib
 METRIC_L2, METRIC_IP = 0, 1
 FILTER_PARTITION, FILTER_BITMASK, FILTER_NONE = 0, 1, 2
 LAYOUT_AUTO, LAYOUT_ROLE, LAYOUT_COMBINATION, LAYOUT_DYNAMIC = 0, 1, 2, 3
+ENGINE_AUTO, ENGINE_SCAN, ENGINE_TENSOR = 0, 1, 2
 
 
 class RkError(RuntimeError):
@@ -34,8 +35,9 @@ def _u32(a) -> np.ndarray:
 
 
 def make_opts(k: int, probes: int = 0, max_probes: int = 0, filter: int = FILTER_PARTITION, null_query: bool = False,
-              layout: int = LAYOUT_AUTO, keep_duplicates: bool = False) -> RkScanOpts:
+              layout: int = LAYOUT_AUTO, keep_duplicates: bool = False, engine: int = ENGINE_AUTO) -> RkScanOpts:
     o = RkScanOpts()
+    o.engine = int(engine)
     o.k, o.probes, o.max_probes, o.filter = int(k), int(probes), int(max_probes), int(filter)
     o.null_query, o.layout, o.keep_duplicates = int(bool(null_query)), int(layout), int(bool(keep_duplicates))
     return o
@@ -135,7 +137,7 @@ class Index:
     # -- search
     def search_batch(self, Q: np.ndarray, user_ids: Optional[Sequence[int]], k: int, probes: int = 0,
                      filter: int = FILTER_PARTITION, layout: int = LAYOUT_AUTO, keep_duplicates: bool = False,
-                     null_query: bool = False, max_probes: int = 0):
+                     null_query: bool = False, max_probes: int = 0, engine: int = ENGINE_AUTO):
         """nq independent filtered top-k scans (host buffers, copies inside).  Returns
         (tid[nq,k] uint64, doc[nq,k] uint32, dist[nq,k] float64, count[nq] int32)."""
         Q = np.ascontiguousarray(Q, dtype=np.float32)
@@ -145,7 +147,7 @@ class Index:
             raise RkError(-2, f"different vector dimensions {self.dim} and {Q.shape[1]}")
         nq = Q.shape[0]
         users = None if user_ids is None else _u32(user_ids)
-        o = make_opts(k, probes, max_probes, filter, null_query, layout, keep_duplicates)
+        o = make_opts(k, probes, max_probes, filter, null_query, layout, keep_duplicates, engine)
         tid = np.empty((nq, k), dtype=np.uint64)
         doc = np.empty((nq, k), dtype=np.uint32)
         dist = np.empty((nq, k), dtype=np.float64)
