@@ -98,7 +98,7 @@ __device__ __forceinline__ uint64_t bs_smem_desc(uint32_t smem_addr)
 // ---------------------------------------------------------------------------------------------
 
 struct BsSmem {
-    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_qn, off_um, off_hist, off_sel, off_sort, total;
+    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_qn, off_qa, off_um, off_hist, off_sel, off_sort, total;
 };
 
 __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
@@ -111,6 +111,8 @@ __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
     s.off_tau = o; o += BS_N * 4;
     s.off_cnt = o; o += BS_N * 4;
     s.off_qn = o; o += BS_N * 4;
+    o = (o + 15) & ~15u;
+    s.off_qa = o; o += BS_N * 16;       // first two mask words of each query as one 16-byte load
     s.off_um = o; o += BS_N * 8u * (uint32_t) mask_words;
     s.off_hist = o; o += 4 * 256 * 4;
     s.off_sel = o; o += 4 * 16;
@@ -351,6 +353,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         c.sortbuf = reinterpret_cast<uint64_t *>(smem + L.off_sort) + ew * BS_SORT_MAX;
         c.lane = lane;
         float *s_qn = reinterpret_cast<float *>(smem + L.off_qn);
+        uint4 *s_qa = reinterpret_cast<uint4 *>(smem + L.off_qa);
         uint64_t *s_um = reinterpret_cast<uint64_t *>(smem + L.off_um);
         const int W = p.mask_words;
         auto esync = [] { rk_named_bar_sync(2, 128); };
@@ -358,10 +361,20 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
             const RkBUnit un = p.units[u];
             esync();                                   // previous unit fully emitted
-            c.tau[et] = RK_KEY_SENTINEL;
-            c.cnt[et] = 0;
-            s_qn[et] = (uint32_t) et < un.nq ? p.qnorm[un.q0 + et] : 0.f;
-            for (int w = 0; w < W; w++) s_um[et * W + w] = ((uint32_t) et < un.nq && p.qmask) ? p.qmask[(size_t) (un.q0 + et) * W + w] : 0ull;
+            {
+                const bool live = (uint32_t) et < un.nq;
+                // a padded column keeps tau = 0: no key is ever <= 0, so it never collects anything
+                c.tau[et] = live ? RK_KEY_SENTINEL : 0u;
+                c.cnt[et] = 0;
+                s_qn[et] = live ? p.qnorm[un.q0 + et] : 0.f;
+                uint64_t w0 = ~0ull, w1 = 0ull;        // no permission filter: every row passes
+                if (p.use_mask) {
+                    w0 = live ? p.qmask[(size_t) (un.q0 + et) * W] : 0ull;
+                    w1 = (live && W > 1) ? p.qmask[(size_t) (un.q0 + et) * W + 1] : 0ull;
+                }
+                s_qa[et] = make_uint4((uint32_t) w0, (uint32_t) (w0 >> 32), (uint32_t) w1, (uint32_t) (w1 >> 32));
+                for (int w = 2; w < W; w++) s_um[et * W + w] = live ? p.qmask[(size_t) (un.q0 + et) * W + w] : 0ull;
+            }
             esync();
             const uint32_t ncol = (un.nq + 15u) & ~15u;
             for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
@@ -369,12 +382,15 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 const uint64_t row = (uint64_t) tile * BS_M + (uint64_t) erow;
                 const bool valid = row < p.nrows;
                 float xn = 0.f;
-                uint64_t m0 = 0, m1 = 0;
+                uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
                 if (valid) {
                     if (METRIC == 0) xn = p.xnorm[row];
                     if (p.use_mask) {
-                        m0 = p.rowmask[row * W];
-                        if (W > 1) m1 = p.rowmask[row * W + 1];
+                        const uint64_t a = p.rowmask[row * W];
+                        const uint64_t b = W > 1 ? p.rowmask[row * W + 1] : 0ull;
+                        m0 = (uint32_t) a; m1 = (uint32_t) (a >> 32); m2 = (uint32_t) b; m3 = (uint32_t) (b >> 32);
+                    } else {
+                        m0 = 1u;                        // matches the all-ones query word
                     }
                 }
                 rk_mbar_wait(&tfull[buf], tph);
@@ -383,22 +399,36 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 for (uint32_t c0 = 0; c0 < ncol; c0 += 16) {
                     uint32_t r[16];
                     bs_tmem_ld16(taddr + c0, r);
+                    // straight-line: 16 columns, one 16-byte + two 4-byte broadcast loads each, no branches
+                    uint32_t pass = 0;
 #pragma unroll
                     for (int j = 0; j < 16; j++) {
                         const uint32_t q = c0 + j;
-                        if (q < un.nq) {               // uniform across the CTA
-                            const float v = __uint_as_float(r[j]);
-                            const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn + s_qn[q]) : -v;
-                            bool ok = valid;
-                            if (p.use_mask && valid) {
-                                uint64_t hit = (m0 & s_um[q * W]) | (W > 1 ? (m1 & s_um[q * W + 1]) : 0ull);
-                                for (int w = 2; w < W; w++) hit |= p.rowmask[row * W + w] & s_um[q * W + w];
-                                ok = hit != 0;
-                            }
-                            const uint32_t key = rk_float_to_key(dist);
-                            if (ok && key <= c.tau[q]) {
+                        const uint4 qa = s_qa[q];
+                        const float v = __uint_as_float(r[j]);
+                        const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn + s_qn[q]) : -v;
+                        const uint32_t hit = (m0 & qa.x) | (m1 & qa.y) | (m2 & qa.z) | (m3 & qa.w);
+                        const uint32_t key = rk_float_to_key(dist);
+                        r[j] = key;
+                        pass |= (uint32_t) (hit != 0 && key <= c.tau[q]) << j;
+                    }
+                    if (W > 2 && p.use_mask && valid) {
+                        // more than 128 roles: the remaining mask words (rare, slow path)
+#pragma unroll
+                        for (int j = 0; j < 16; j++) {
+                            const uint32_t q = c0 + j;
+                            uint64_t hit = 0;
+                            for (int w = 2; w < W; w++) hit |= p.rowmask[row * W + w] & s_um[q * W + w];
+                            if (hit != 0 && r[j] <= c.tau[q]) pass |= 1u << j;
+                        }
+                    }
+                    if (__any_sync(0xffffffffu, pass != 0)) {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) {
+                            if (pass & (1u << j)) {
+                                const uint32_t q = c0 + j;
                                 const uint32_t slot = atomicAdd(&c.cnt[q], 1u);
-                                c.scratch[(size_t) q * BS_CAP + slot] = make_uint2(key, (uint32_t) row);
+                                c.scratch[(size_t) q * BS_CAP + slot] = make_uint2(r[j], (uint32_t) row);
                             }
                         }
                     }
@@ -406,24 +436,27 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 bs_fence_before();
                 __syncwarp();
                 if (lane == 0) rk_mbar_arrive(&tempty[buf]);
-                esync();                               // all appends of this tile are in
                 // a tile adds at most 128 entries per query: compact what could overflow on the next one
-                for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
-                    const uint32_t n = c.cnt[q];
-                    if (n > BS_CAP - BS_M) {
-                        uint32_t tau;
-                        uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
-                        if (m > BS_CAP / 2 && tau > 0) {
-                            // more than half the buffer ties at the kp-th key: drop that key altogether
-                            // and record that the list is no longer complete (the query is re-run exactly)
-                            tau -= 1u;
-                            m = bs_warp_filter(c, (int) q, m, tau);
-                            if (lane == 0) p.trunc[un.q0 + q] = 1;
+                // (the reducing barrier also publishes this tile's appends)
+                const bool need = rk_named_bar_red_or(2, 128, c.cnt[et] > BS_CAP - BS_M);
+                if (need) {
+                    for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
+                        const uint32_t n = c.cnt[q];
+                        if (n > BS_CAP - BS_M) {
+                            uint32_t tau;
+                            uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                            if (m > BS_CAP / 2 && tau > 0) {
+                                // more than half the buffer ties at the kp-th key: drop that key altogether
+                                // and record that the list is no longer complete (the query is re-run exactly)
+                                tau -= 1u;
+                                m = bs_warp_filter(c, (int) q, m, tau);
+                                if (lane == 0) p.trunc[un.q0 + q] = 1;
+                            }
+                            if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; }
                         }
-                        if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; }
                     }
+                    esync();
                 }
-                esync();
             }
             // unit end: every query's list, sorted by (approximate key, row), at most kp entries
             for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
