@@ -163,7 +163,7 @@ extern "C" void rk_close(rk_index *ix)
     for (auto *b : bufs) b->release();
     TensorState &ts = ix->tensor;
     DevBuf *tb[] = {&ts.d_xnorm, &ts.d_rowmask, &ts.d_probe, &ts.d_units, &ts.d_qnorm, &ts.d_scratch, &ts.d_cand_key, &ts.d_cand_row,
-                    &ts.d_cand_count, &ts.d_sel_key, &ts.d_sel_row, &ts.d_sel_count, &ts.d_flags};
+                    &ts.d_cand_count, &ts.d_sel_key, &ts.d_sel_row, &ts.d_sel_count, &ts.d_flags, &ts.d_plan, &ts.d_qp, &ts.d_tiles};
     for (auto *b : tb) b->release();
     ts.h_flags.release();
     delete ix;

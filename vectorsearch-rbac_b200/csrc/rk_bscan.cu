@@ -261,7 +261,9 @@ __device__ __forceinline__ void bs_warp_emit(const BsCtx &c, int q, uint32_t n, 
 
 template <int METRIC>
 __global__ void __launch_bounds__(BS_THREADS, 1)
-rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmq, const RkBScanParams p)
+rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmq16,
+                const __grid_constant__ CUtensorMap tmq32, const __grid_constant__ CUtensorMap tmq64,
+                const __grid_constant__ CUtensorMap tmq128, const RkBScanParams p)
 {
     extern __shared__ unsigned char smem_raw[];
     const BsSmem L = bs_smem_layout(p.mask_words);
@@ -288,21 +290,35 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
-                const RkBUnit un = p.units[u];
-                for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++) {
-                    const int row0 = (int) (tile * BS_M);
-                    for (int kc = 0; kc < p.kchunks; kc++) {
-                        rk_mbar_wait(&empty[stage], phase ^ 1u);
-                        unsigned char *st = smem + L.off_stage + (size_t) stage * BS_STAGE_BYTES;
-                        rk_mbar_arrive_expect_tx(&full[stage], BS_STAGE_BYTES);
-                        bs_tma_2d(st, &tmx, kc * BS_KC, row0, &full[stage]);
-                        bs_tma_2d(st + 16384, &tmq, kc * BS_KC, (int) un.q0, &full[stage]);
-                        if (++stage == BS_STAGES) { stage = 0; phase ^= 1u; }
+        int stage = 0;
+        uint32_t phase = 0;
+        for (uint32_t ui = p.cta_off[blockIdx.x]; ui < p.cta_off[blockIdx.x + 1]; ui++) {
+            const RkBUnit un = p.units[p.cta_units[ui]];
+            // the query box is only as tall as the unit needs (16 / 32 / 64 / 128 rows)
+            const uint32_t ncol = (un.nq + 15u) & ~15u;
+            const CUtensorMap *tq = ncol <= 16 ? &tmq16 : ncol <= 32 ? &tmq32 : ncol <= 64 ? &tmq64 : &tmq128;
+            const uint32_t qbox = ncol <= 16 ? 16u : ncol <= 32 ? 32u : ncol <= 64 ? 64u : 128u;
+            const uint32_t tx = 16384u + qbox * 128u;
+            for (uint32_t t0 = un.tile_begin; t0 < un.tile_end; t0 += 32) {
+                // first rows of the next 32 tiles in one coalesced load (keeps the list lookup off the
+                // per-tile critical path)
+                const uint32_t tmine = t0 + (uint32_t) lane;
+                uint32_t rmine = 0;
+                if (tmine < un.tile_end) rmine = p.tile_rows ? p.tile_rows[un.tl_off + tmine] : tmine * BS_M;
+                const uint32_t nt = min(32u, un.tile_end - t0);
+                for (uint32_t j = 0; j < nt; j++) {
+                    const int row0 = (int) __shfl_sync(0xffffffffu, rmine, (int) j);
+                    if (lane == 0) {
+                        for (int kc = 0; kc < p.kchunks; kc++) {
+                            rk_mbar_wait(&empty[stage], phase ^ 1u);
+                            unsigned char *st = smem + L.off_stage + (size_t) stage * BS_STAGE_BYTES;
+                            rk_mbar_arrive_expect_tx(&full[stage], tx);
+                            bs_tma_2d(st, &tmx, kc * BS_KC, row0, &full[stage]);
+                            bs_tma_2d(st + 16384, tq, kc * BS_KC, (int) un.q0, &full[stage]);
+                            if (++stage == BS_STAGES) { stage = 0; phase ^= 1u; }
+                        }
                     }
+                    __syncwarp();
                 }
             }
         }
@@ -310,8 +326,8 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         // ===================== MMA issuer =====================
         int stage = 0;
         uint32_t phase = 0, tcount = 0;
-        for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
-            const RkBUnit un = p.units[u];
+        for (uint32_t ui = p.cta_off[blockIdx.x]; ui < p.cta_off[blockIdx.x + 1]; ui++) {
+            const RkBUnit un = p.units[p.cta_units[ui]];
             uint32_t ncol = (un.nq + 15u) & ~15u;
             if (ncol < 16) ncol = 16;
             // c=F32, a=b=TF32, K-major both, N>>3, M>>4
@@ -358,8 +374,8 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         const int W = p.mask_words;
         auto esync = [] { rk_named_bar_sync(2, 128); };
         uint32_t tcount = 0;
-        for (uint32_t u = blockIdx.x; u < p.nunits; u += gridDim.x) {
-            const RkBUnit un = p.units[u];
+        for (uint32_t ui = p.cta_off[blockIdx.x]; ui < p.cta_off[blockIdx.x + 1]; ui++) {
+            const RkBUnit un = p.units[p.cta_units[ui]];
             esync();                                   // previous unit fully emitted
             {
                 const bool live = (uint32_t) et < un.nq;
@@ -377,22 +393,38 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             }
             esync();
             const uint32_t ncol = (un.nq + 15u) & ~15u;
-            for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
-                const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
-                const uint64_t row = (uint64_t) tile * BS_M + (uint64_t) erow;
-                const bool valid = row < p.nrows;
-                float xn = 0.f;
-                uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
-                if (valid) {
-                    if (METRIC == 0) xn = p.xnorm[row];
+            // per-row inputs are fetched one tile ahead (row start two tiles ahead) so that no global
+            // load latency sits between two tiles
+            auto tile_row0 = [&](uint32_t t) -> uint32_t {
+                return t < un.tile_end ? (p.tile_rows ? p.tile_rows[un.tl_off + t] : t * BS_M) : 0xFFFFFFF0u;
+            };
+            uint32_t r0_cur = tile_row0(un.tile_begin), r0_next = tile_row0(un.tile_begin + 1);
+            float xn_n = 0.f;
+            uint64_t ma_n = 0, mb_n = 0;
+            auto fetch_row = [&](uint32_t r0) {
+                const uint64_t rr = (uint64_t) r0 + (uint64_t) erow;
+                xn_n = 0.f; ma_n = 0; mb_n = 0;
+                if (rr < p.nrows) {
+                    if (METRIC == 0) xn_n = p.xnorm[rr];
                     if (p.use_mask) {
-                        const uint64_t a = p.rowmask[row * W];
-                        const uint64_t b = W > 1 ? p.rowmask[row * W + 1] : 0ull;
-                        m0 = (uint32_t) a; m1 = (uint32_t) (a >> 32); m2 = (uint32_t) b; m3 = (uint32_t) (b >> 32);
+                        ma_n = p.rowmask[rr * W];
+                        if (W > 1) mb_n = p.rowmask[rr * W + 1];
                     } else {
-                        m0 = 1u;                        // matches the all-ones query word
+                        ma_n = 1ull;                    // matches the all-ones query word
                     }
                 }
+            };
+            fetch_row(r0_cur);
+            for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
+                const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
+                const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
+                const bool valid = row < p.nrows;
+                const float xn = xn_n;
+                const uint32_t m0 = (uint32_t) ma_n, m1 = (uint32_t) (ma_n >> 32), m2 = (uint32_t) mb_n, m3 = (uint32_t) (mb_n >> 32);
+                // issue the next tile's loads now; they are consumed on the next iteration
+                r0_cur = r0_next;
+                r0_next = tile_row0(tile + 2);
+                fetch_row(r0_cur);
                 rk_mbar_wait(&tfull[buf], tph);
                 bs_fence_after();
                 const uint32_t taddr = tmem_base + buf * BS_N + ((uint32_t) (quarter * 32) << 16);
@@ -470,7 +502,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                     }
                     if (n > BS_SORT_MAX) n = BS_SORT_MAX;
                 }
-                const size_t list = (size_t) u * BS_N + q;
+                const size_t list = (size_t) un.list_base + q;
                 bs_warp_emit(c, (int) q, n, (uint32_t) p.kp, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
             }
         }
@@ -538,7 +570,8 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
     }
     const int k = p.k;
     const int cnt = n < k ? n : k;
-    const size_t ob = (size_t) q * k;
+    const int oq = p.slot_q ? (int) p.slot_q[q] : q;      // the caller's query index
+    const size_t ob = (size_t) oq * k;
     for (int i = t; i < k; i += RS_THREADS) {
         const bool ok = i < cnt;
         const float ord = ok ? rk_key_to_float(s_key[i]) : __int_as_float(0x7f800000);
@@ -555,7 +588,7 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
         }
     }
     if (t == 0) {
-        if (p.out_count) p.out_count[q] = cnt;
+        if (p.out_count) p.out_count[oq] = cnt;
         // Sufficiency: a row outside the candidate set has approximate value >= a_last (the largest
         // approximate value kept, when the list is saturated).  Its exact value is then >= a_last - eps.
         // The answer is proven iff that exceeds the exact k-th value (strictly, so that no tie on the
@@ -568,7 +601,7 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
             if (p.eps_scale > 0.f) eps = p.eps_scale * sqrtf(p.xnorm_max * p.qnorm[q]) + 1e-6f * (p.xnorm_max + p.qnorm[q]);
             if (cnt < k || !(a_last - eps > e_k)) uncertain = 1;
         }
-        p.uncertain[q] = uncertain;
+        p.uncertain[oq] = uncertain;
     }
 }
 
@@ -661,7 +694,7 @@ typedef CUresult (*rk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t,
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 // 2-D fp32 tensor [rows][dim_pad], box = 32 floats x 128 rows, 128-byte swizzle, zero fill out of bounds.
-static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad)
+static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad, uint32_t box_rows = BS_M)
 {
     static rk_encode_fn encode = nullptr;
     if (!encode) {
@@ -674,7 +707,7 @@ static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t 
     }
     cuuint64_t gdim[2] = {(cuuint64_t) dim_pad, (cuuint64_t) (rows ? rows : 1)};
     cuuint64_t gstride[1] = {(cuuint64_t) dim_pad * 4};
-    cuuint32_t box[2] = {BS_KC, BS_M};
+    cuuint32_t box[2] = {BS_KC, box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -684,11 +717,13 @@ static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t 
 
 cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream)
 {
-    CUtensorMap tmx, tmq;
+    CUtensorMap tmx, tmq[4];
     cudaError_t e = make_tensor_map(&tmx, x, p.nrows, p.dim_pad);
     if (e != cudaSuccess) return e;
-    e = make_tensor_map(&tmq, q, nq, p.dim_pad);
-    if (e != cudaSuccess) return e;
+    for (int i = 0; i < 4; i++) {
+        e = make_tensor_map(&tmq[i], q, nq, p.dim_pad, 16u << i);
+        if (e != cudaSuccess) return e;
+    }
     const size_t smem = rk_bscan_smem_bytes(p.mask_words);
     auto kern = p.metric == 0 ? rk_bscan_kernel<0> : rk_bscan_kernel<1>;
     static bool attr_set[2];
@@ -697,7 +732,7 @@ cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float 
         if (e != cudaSuccess) return e;
         attr_set[p.metric & 1] = true;
     }
-    kern<<<grid, BS_THREADS, smem, stream>>>(tmx, tmq, p);
+    kern<<<grid, BS_THREADS, smem, stream>>>(tmx, tmq[0], tmq[1], tmq[2], tmq[3], p);
     return cudaGetLastError();
 }
 

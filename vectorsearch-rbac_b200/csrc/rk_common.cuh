@@ -71,6 +71,9 @@ struct RkSelectParams {
     const uint32_t *qseg;       // [nq+1] segment range per query
     int lists_per_query;        // if > 0: query q owns lists [q*L, (q+1)*L) (shard merge / fixed plans) and qseg is ignored
     int list_stride;            // entries between consecutive lists
+    // list-id mode (tensor engine): query q owns lists lid0[q] + j * lstep[q], j < nlists[q]; a list's
+    // entries start at id * list_stride and its count is cand_count[id]
+    const uint32_t *lid0, *lstep, *nlists;
     int count_stride;           // fixed-list mode: cand_count[j * count_stride + q] (0 = number of queries launched)
     size_t shard_stride_bytes;  // fixed-list mode: bytes between list j and j+1 of one array (0 = dense nq*k elements)
     int k;
@@ -93,13 +96,19 @@ struct RkSelectParams {
 // ---- batched tensor-core engine (rk_bscan.cu) ------------------------------------------------
 // One unit = one tile of up to 128 queries x a contiguous range of 128-row tiles of the row store.
 struct RkBUnit {
-    uint32_t q0, nq;             // queries [q0, q0 + nq)
-    uint32_t tile_begin, tile_end;
+    uint32_t q0, nq;             // query slots [q0, q0 + nq) of the (group-ordered) query matrix
+    uint32_t tile_begin, tile_end;   // tiles [begin, end) of the unit's tile list (or of the dense tiling)
+    uint32_t tl_off;             // offset of the group's tile list in tile_rows[]
+    uint32_t list_base;          // candidate list of slot q0 + i is list_base + i
+    uint32_t pad0, pad1;
 };
 
 struct RkBScanParams {
     const RkBUnit *units;
     uint32_t nunits;
+    const uint32_t *cta_off;     // [grid + 1] balanced static schedule: CTA b runs units cta_units[cta_off[b] .. cta_off[b+1])
+    const uint32_t *cta_units;
+    const uint32_t *tile_rows;   // first row of every listed tile (NULL = dense tiling, tile t starts at row 128 t)
     uint64_t nrows;
     int dim_pad, kchunks, metric, kp, mask_words, use_mask;
     const float *xnorm;          // [rows] squared norms (L2 only)
@@ -107,18 +116,19 @@ struct RkBScanParams {
     const float *qnorm;          // [nq]
     const uint64_t *qmask;       // [nq][mask_words]
     uint2 *scratch;              // [grid][128][1024] (approximate key, row) candidate buffers
-    uint32_t *cand_key;          // [nunits * 128][kp] sorted by (key, row)
+    uint32_t *cand_key;          // [lists][kp] sorted by (key, row)
     uint32_t *cand_row;
-    int32_t *cand_count;         // [nunits * 128]
-    int32_t *trunc;              // [nq] set when ties at a threshold had to be dropped
+    int32_t *cand_count;         // [lists]
+    int32_t *trunc;              // [slots] set when ties at a threshold had to be dropped
 };
 
 struct RkRescoreParams {
     const float *x;              // row store
     const uint64_t *tid;
     const uint32_t *rowdoc, *doc_ids;
-    const float *q;              // [nq][dim_pad]
+    const float *q;              // [slots][dim_pad] (group-ordered)
     const float *qnorm;
+    const uint32_t *slot_q;      // slot -> query index of the caller's batch (outputs are written there); NULL = identity
     int dim_pad, k, kp, metric, null_query;
     const float *sel_key;        // [nq][kp] approximate ordering values, ascending
     const uint32_t *sel_row;

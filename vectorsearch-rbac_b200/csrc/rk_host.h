@@ -87,6 +87,10 @@ struct TensorState {
     DevBuf d_xnorm, d_rowmask, d_probe;
     bool x_integer = false;
     float x_absmax = 0.f, xnorm_max = 0.f;
+    DevBuf d_plan, d_qp, d_tiles;
+    std::vector<uint32_t> h_tiles;                                              // tile lists of all cached role masks
+    std::map<std::vector<uint64_t>, std::pair<uint32_t, uint32_t>> tile_cache;  // role mask -> (offset, count) in h_tiles
+    bool last_grouped = false;
     DevBuf d_units, d_qnorm, d_scratch, d_cand_key, d_cand_row, d_cand_count, d_sel_key, d_sel_row, d_sel_count, d_flags;
     PinBuf h_flags;
     double last_flop = 0.0;
