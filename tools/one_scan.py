@@ -22,6 +22,10 @@ a = ap.parse_args()
 wl = (a.rows, a.dim, a.kind, 100, 1000, 100, "one")
 dev = torch.device("cuda", 0)
 tid, doc, ur, dr = bench.build_rbac(wl)
+if a.rbac == "random":
+    import vectorsearch_rbac_b200.synth as synth
+    ndoc = (a.rows + 99) // 100
+    ur, dr = synth.random_rbac(1000, 100, list(range(1, ndoc + 1)), 3, 9 * ndoc // 100, seed=42)
 metric = vr.METRIC_L2 if a.metric == "l2" else vr.METRIC_IP
 ix = vr.Index(a.dim, metric=metric, device=0, k_max=max(128, a.k))
 for s in range(0, a.rows, 1 << 20):
@@ -29,12 +33,15 @@ for s in range(0, a.rows, 1 << 20):
     xb = bench.gen_rows(wl, idx, dev)
     ix.load_rows_device(xb.data_ptr(), len(idx), tid[idx], doc[idx])
 ix.set_doc_roles(dr[:, 0], dr[:, 1]); ix.set_user_roles(ur[:, 0], ur[:, 1])
-ix.build_role_partitions(); ix.finalize(); ix.enable_timing(True)
+ix.build_role_partitions()
+if a.filter == "combination":
+    ix.build_combination_partitions()
+ix.finalize(); ix.enable_timing(True)
 Q, users = bench.make_queries(wl, a.nq, dev)
 Q = Q.contiguous()
-flt = {"none": vr.FILTER_NONE, "bitmask": vr.FILTER_BITMASK, "partition": vr.FILTER_PARTITION}[a.filter]
+flt = {"none": vr.FILTER_NONE, "bitmask": vr.FILTER_BITMASK, "partition": vr.FILTER_PARTITION, "combination": vr.FILTER_PARTITION}[a.filter]
 eng = {"scan": vr.ENGINE_SCAN, "tensor": vr.ENGINE_TENSOR}[a.engine]
-opts = vr.engine.make_opts(a.k, filter=flt, layout=vr.LAYOUT_ROLE if flt == vr.FILTER_PARTITION else 0, engine=eng)
+opts = vr.engine.make_opts(a.k, filter=flt, layout=(vr.LAYOUT_COMBINATION if a.filter == "combination" else vr.LAYOUT_ROLE) if flt == vr.FILTER_PARTITION else 0, engine=eng)
 o = [torch.empty((a.nq, a.k), dtype=t, device=dev) for t in (torch.int64, torch.int32, torch.float64)] + [torch.empty(a.nq, dtype=torch.int32, device=dev)]
 import time
 for _ in range(a.reps):

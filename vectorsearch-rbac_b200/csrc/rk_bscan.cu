@@ -7,7 +7,9 @@
 // `tcgen05.mma.cta_group::1.kind::tf32` (fp32 operands straight from HBM, TF32 inside the MMA, fp32
 // accumulation in TMEM).  The permission predicate (row_level_security.py:55-65) is a per-(row, query)
 // role-mask test in the epilogue.  Tensor-core values are APPROXIMATE (TF32), so this kernel only
-// nominates candidates: per (unit, query) the `kp` rows with the smallest approximate distance.
+// nominates candidates: per (unit, query) the `kp` rows with the smallest approximate ordering value
+// (‖x‖² − 2·D for L2 — the query's own norm is a constant of the ordering and is added back by
+// rk_rescore_kernel — and −D for IP).
 // rk_rescore_kernel then recomputes those rows' distances in exact fp32 with the scan kernel's
 // summation order, takes the final top-k by (distance, tuple id) and proves — or refuses to — that
 // no row outside the candidate set could belong to the answer (refused queries are re-run on the
@@ -98,7 +100,7 @@ __device__ __forceinline__ uint64_t bs_smem_desc(uint32_t smem_addr)
 // ---------------------------------------------------------------------------------------------
 
 struct BsSmem {
-    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_qn, off_qa, off_um, off_hist, off_sel, off_sort, total;
+    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_trunc, off_qa, off_um, off_hist, off_sel, off_sort, total;
 };
 
 __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
@@ -110,8 +112,8 @@ __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
     s.off_tmem = o; o += 16;
     s.off_tau = o; o += BS_N * 4;
     s.off_cnt = o; o += BS_N * 4;
-    s.off_qn = o; o += BS_N * 4;
     o = (o + 15) & ~15u;
+    s.off_trunc = o; o += BS_N * 8;
     s.off_qa = o; o += BS_N * 16;       // first two mask words of each query as one 16-byte load
     s.off_um = o; o += BS_N * 8u * (uint32_t) mask_words;
     s.off_hist = o; o += 4 * 256 * 4;
@@ -259,6 +261,12 @@ __device__ __forceinline__ void bs_warp_emit(const BsCtx &c, int q, uint32_t n, 
     __syncwarp();
 }
 
+// Tiles a unit visits: tile_begin, tile_begin + step, ... below tile_end.
+__device__ __forceinline__ uint32_t bs_unit_tiles(const RkBUnit &un)
+{
+    return un.tile_end > un.tile_begin ? (un.tile_end - un.tile_begin + un.tile_step - 1u) / un.tile_step : 0u;
+}
+
 template <int METRIC>
 __global__ void __launch_bounds__(BS_THREADS, 1)
 rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmq16,
@@ -299,13 +307,14 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             const CUtensorMap *tq = ncol <= 16 ? &tmq16 : ncol <= 32 ? &tmq32 : ncol <= 64 ? &tmq64 : &tmq128;
             const uint32_t qbox = ncol <= 16 ? 16u : ncol <= 32 ? 32u : ncol <= 64 ? 64u : 128u;
             const uint32_t tx = 16384u + qbox * 128u;
-            for (uint32_t t0 = un.tile_begin; t0 < un.tile_end; t0 += 32) {
-                // first rows of the next 32 tiles in one coalesced load (keeps the list lookup off the
-                // per-tile critical path)
-                const uint32_t tmine = t0 + (uint32_t) lane;
+            const uint32_t ntiles = bs_unit_tiles(un);
+            for (uint32_t i0 = 0; i0 < ntiles; i0 += 32) {
+                // first rows of the next 32 tiles in one load (keeps the list lookup off the per-tile
+                // critical path)
+                const uint32_t tmine = un.tile_begin + (i0 + (uint32_t) lane) * un.tile_step;
                 uint32_t rmine = 0;
-                if (tmine < un.tile_end) rmine = p.tile_rows ? p.tile_rows[un.tl_off + tmine] : tmine * BS_M;
-                const uint32_t nt = min(32u, un.tile_end - t0);
+                if (i0 + (uint32_t) lane < ntiles) rmine = p.tile_rows ? p.tile_rows[un.tl_off + tmine] : tmine * BS_M;
+                const uint32_t nt = min(32u, ntiles - i0);
                 for (uint32_t j = 0; j < nt; j++) {
                     const int row0 = (int) __shfl_sync(0xffffffffu, rmine, (int) j);
                     if (lane == 0) {
@@ -332,7 +341,8 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             if (ncol < 16) ncol = 16;
             // c=F32, a=b=TF32, K-major both, N>>3, M>>4
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((ncol >> 3) << 17) | ((BS_M >> 4) << 24);
-            for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
+            const uint32_t ntiles = bs_unit_tiles(un);
+            for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 rk_mbar_wait(&tempty[buf], tph ^ 1u);
                 bs_fence_after();
@@ -368,7 +378,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         c.scratch = p.scratch + (size_t) blockIdx.x * BS_N * BS_CAP;
         c.sortbuf = reinterpret_cast<uint64_t *>(smem + L.off_sort) + ew * BS_SORT_MAX;
         c.lane = lane;
-        float *s_qn = reinterpret_cast<float *>(smem + L.off_qn);
+        int32_t **s_trunc = reinterpret_cast<int32_t **>(smem + L.off_trunc);     // each query's trunc flag
         uint4 *s_qa = reinterpret_cast<uint4 *>(smem + L.off_qa);
         uint64_t *s_um = reinterpret_cast<uint64_t *>(smem + L.off_um);
         const int W = p.mask_words;
@@ -380,9 +390,13 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             {
                 const bool live = (uint32_t) et < un.nq;
                 // a padded column keeps tau = 0: no key is ever <= 0, so it never collects anything
-                c.tau[et] = live ? RK_KEY_SENTINEL : 0u;
+                uint32_t tau0 = live ? RK_KEY_SENTINEL : 0u;
+                // seeded threshold: the kp-th smallest ordering value over a SAMPLE of the rows this query
+                // sees bounds the kp-th smallest over all of them from above
+                if (live && p.tau_key && p.tau_count[un.q0 + et] >= p.kp) tau0 = rk_float_to_key(p.tau_key[(size_t) (un.q0 + et) * p.kp + (p.kp - 1)]);
+                c.tau[et] = tau0;
                 c.cnt[et] = 0;
-                s_qn[et] = live ? p.qnorm[un.q0 + et] : 0.f;
+                s_trunc[et] = p.trunc + (live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u);
                 uint64_t w0 = ~0ull, w1 = 0ull;        // no permission filter: every row passes
                 if (p.use_mask) {
                     w0 = live ? p.qmask[(size_t) (un.q0 + et) * W] : 0ull;
@@ -395,10 +409,12 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             const uint32_t ncol = (un.nq + 15u) & ~15u;
             // per-row inputs are fetched one tile ahead (row start two tiles ahead) so that no global
             // load latency sits between two tiles
-            auto tile_row0 = [&](uint32_t t) -> uint32_t {
-                return t < un.tile_end ? (p.tile_rows ? p.tile_rows[un.tl_off + t] : t * BS_M) : 0xFFFFFFF0u;
+            const uint32_t ntiles = bs_unit_tiles(un);
+            auto tile_row0 = [&](uint32_t i) -> uint32_t {       // first row of the unit's i-th tile
+                const uint32_t t = un.tile_begin + i * un.tile_step;
+                return i < ntiles ? (p.tile_rows ? p.tile_rows[un.tl_off + t] : t * BS_M) : 0xFFFFFFF0u;
             };
-            uint32_t r0_cur = tile_row0(un.tile_begin), r0_next = tile_row0(un.tile_begin + 1);
+            uint32_t r0_cur = tile_row0(0), r0_next = tile_row0(1);
             float xn_n = 0.f;
             uint64_t ma_n = 0, mb_n = 0;
             auto fetch_row = [&](uint32_t r0) {
@@ -407,15 +423,16 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 if (rr < p.nrows) {
                     if (METRIC == 0) xn_n = p.xnorm[rr];
                     if (p.use_mask) {
-                        ma_n = p.rowmask[rr * W];
-                        if (W > 1) mb_n = p.rowmask[rr * W + 1];
+                        const ulonglong2 m2 = reinterpret_cast<const ulonglong2 *>(p.rowmask2)[rr];
+                        ma_n = m2.x;
+                        mb_n = m2.y;
                     } else {
                         ma_n = 1ull;                    // matches the all-ones query word
                     }
                 }
             };
             fetch_row(r0_cur);
-            for (uint32_t tile = un.tile_begin; tile < un.tile_end; tile++, tcount++) {
+            for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
                 const bool valid = row < p.nrows;
@@ -423,7 +440,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 const uint32_t m0 = (uint32_t) ma_n, m1 = (uint32_t) (ma_n >> 32), m2 = (uint32_t) mb_n, m3 = (uint32_t) (mb_n >> 32);
                 // issue the next tile's loads now; they are consumed on the next iteration
                 r0_cur = r0_next;
-                r0_next = tile_row0(tile + 2);
+                r0_next = tile_row0(ti + 2);
                 fetch_row(r0_cur);
                 rk_mbar_wait(&tfull[buf], tph);
                 bs_fence_after();
@@ -438,7 +455,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         const uint32_t q = c0 + j;
                         const uint4 qa = s_qa[q];
                         const float v = __uint_as_float(r[j]);
-                        const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn + s_qn[q]) : -v;
+                        const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn) : -v;
                         const uint32_t hit = (m0 & qa.x) | (m1 & qa.y) | (m2 & qa.z) | (m3 & qa.w);
                         const uint32_t key = rk_float_to_key(dist);
                         r[j] = key;
@@ -482,7 +499,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                                 // and record that the list is no longer complete (the query is re-run exactly)
                                 tau -= 1u;
                                 m = bs_warp_filter(c, (int) q, m, tau);
-                                if (lane == 0) p.trunc[un.q0 + q] = 1;
+                                if (lane == 0) *s_trunc[q] = 1;
                             }
                             if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; }
                         }
@@ -498,7 +515,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                     n = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
                     if (n > BS_SORT_MAX && tau > 0) {
                         n = bs_warp_filter(c, (int) q, n, tau - 1u);
-                        if (lane == 0) p.trunc[un.q0 + q] = 1;
+                        if (lane == 0) *s_trunc[q] = 1;
                     }
                     if (n > BS_SORT_MAX) n = BS_SORT_MAX;
                 }
@@ -595,7 +612,8 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
         // k-th value with a smaller tuple id can hide outside).
         int uncertain = p.trunc ? p.trunc[q] : 0;
         if (n >= p.kp && cnt > 0) {
-            const float a_last = p.sel_key[(size_t) q * p.kp + (n - 1)];
+            // the nominated ordering value leaves the query's own norm out (L2): add it back
+            const float a_last = p.sel_key[(size_t) q * p.kp + (n - 1)] + (METRIC == 0 ? p.qnorm[q] : 0.f);
             const float e_k = rk_key_to_float(s_key[cnt - 1]);
             float eps = 0.f;
             if (p.eps_scale > 0.f) eps = p.eps_scale * sqrtf(p.xnorm_max * p.qnorm[q]) + 1e-6f * (p.xnorm_max + p.qnorm[q]);
@@ -631,6 +649,22 @@ __global__ void rk_rowmask_kernel(const uint32_t *__restrict__ rowdoc, const uin
         const size_t r = i / W;
         const int w = (int) (i % W);
         out[i] = doc_mask[(size_t) rowdoc[r] * W + w];
+    }
+}
+
+// First two mask words of every row as one 16-byte record (what the tensor kernel stages per tile);
+// rows [n, n_pad) get an empty mask so that a tile reaching past the store never passes the test.
+__global__ void rk_rowmask2_kernel(const uint32_t *__restrict__ rowdoc, const uint64_t *__restrict__ doc_mask, size_t n, size_t n_pad,
+                                   int W, ulonglong2 *__restrict__ out)
+{
+    for (size_t r = blockIdx.x * (size_t) blockDim.x + threadIdx.x; r < n_pad; r += (size_t) gridDim.x * blockDim.x) {
+        ulonglong2 v = make_ulonglong2(0ull, 0ull);
+        if (r < n) {
+            const uint64_t *m = doc_mask + (size_t) rowdoc[r] * W;
+            v.x = m[0];
+            if (W > 1) v.y = m[1];
+        }
+        out[r] = v;
     }
 }
 
@@ -672,6 +706,12 @@ cudaError_t rk_launch_rowmask(const uint32_t *rowdoc, const uint64_t *doc_mask, 
     if (n) rk_rowmask_kernel<<<148 * 8, 256, 0, stream>>>(rowdoc, doc_mask, n, W, out);
     return cudaGetLastError();
 }
+cudaError_t rk_launch_rowmask2(const uint32_t *rowdoc, const uint64_t *doc_mask, size_t n, size_t n_pad, int W, uint64_t *out,
+                               cudaStream_t stream)
+{
+    if (n_pad) rk_rowmask2_kernel<<<148 * 8, 256, 0, stream>>>(rowdoc, doc_mask, n, n_pad, W, reinterpret_cast<ulonglong2 *>(out));
+    return cudaGetLastError();
+}
 cudaError_t rk_launch_tf32_probe(const float *x, size_t n, unsigned long long *d_out2, cudaStream_t stream)
 {
     if (n) rk_tf32_probe_kernel<<<148 * 8, 256, 0, stream>>>(x, n, d_out2);
@@ -688,12 +728,13 @@ cudaError_t rk_launch_max_f32(const float *x, size_t n, unsigned *d_out, cudaStr
 
 size_t rk_bscan_smem_bytes(int mask_words) { return bs_smem_layout(mask_words).total; }
 size_t rk_bscan_scratch_bytes(int grid) { return (size_t) grid * BS_N * BS_CAP * sizeof(uint2); }
+int rk_bscan_lists_per_query() { return 1; }
 
 typedef CUresult (*rk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// 2-D fp32 tensor [rows][dim_pad], box = 32 floats x 128 rows, 128-byte swizzle, zero fill out of bounds.
+// 2-D fp32 tensor [rows][dim_pad], box = 32 floats x box_rows, 128-byte swizzle, zero fill out of bounds.
 static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad, uint32_t box_rows = BS_M)
 {
     static rk_encode_fn encode = nullptr;

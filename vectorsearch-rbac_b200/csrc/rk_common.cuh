@@ -74,6 +74,8 @@ struct RkSelectParams {
     // list-id mode (tensor engine): query q owns lists lid0[q] + j * lstep[q], j < nlists[q]; a list's
     // entries start at id * list_stride and its count is cand_count[id]
     const uint32_t *lid0, *lstep, *nlists;
+    // explicit mode: query q owns lists list_ids[qseg[q] .. qseg[q+1])
+    const uint32_t *list_ids;
     int count_stride;           // fixed-list mode: cand_count[j * count_stride + q] (0 = number of queries launched)
     size_t shard_stride_bytes;  // fixed-list mode: bytes between list j and j+1 of one array (0 = dense nq*k elements)
     int k;
@@ -100,7 +102,8 @@ struct RkBUnit {
     uint32_t tile_begin, tile_end;   // tiles [begin, end) of the unit's tile list (or of the dense tiling)
     uint32_t tl_off;             // offset of the group's tile list in tile_rows[]
     uint32_t list_base;          // candidate list of slot q0 + i is list_base + i
-    uint32_t pad0, pad1;
+    uint32_t tile_step;          // the unit visits tiles tile_begin, tile_begin + tile_step, ... (> 1: sampling pass)
+    uint32_t pad1;
 };
 
 struct RkBScanParams {
@@ -111,15 +114,20 @@ struct RkBScanParams {
     const uint32_t *tile_rows;   // first row of every listed tile (NULL = dense tiling, tile t starts at row 128 t)
     uint64_t nrows;
     int dim_pad, kchunks, metric, kp, mask_words, use_mask;
-    const float *xnorm;          // [rows] squared norms (L2 only)
-    const uint64_t *rowmask;     // [rows][mask_words] role mask of each row's document
+    const float *xnorm;          // [rows + 128] squared norms (L2 only), zero padded
+    const uint64_t *rowmask;     // [rows][mask_words] role mask of each row's document (words >= 2 read from here)
+    const uint64_t *rowmask2;    // [rows + 128][2] first two mask words of each row, zero padded
     const float *qnorm;          // [nq]
     const uint64_t *qmask;       // [nq][mask_words]
     uint2 *scratch;              // [grid][128][1024] (approximate key, row) candidate buffers
     uint32_t *cand_key;          // [lists][kp] sorted by (key, row)
     uint32_t *cand_row;
     int32_t *cand_count;         // [lists]
-    int32_t *trunc;              // [slots] set when ties at a threshold had to be dropped
+    int32_t *trunc;              // [queries] set when ties at a threshold had to be dropped
+    // optional seed thresholds (sampling pass): slot s starts at tau_key[s * kp + kp - 1] when tau_count[s] >= kp
+    const float *tau_key;
+    const int32_t *tau_count;
+    const uint32_t *slot_q;      // slot -> query of the caller's batch (trunc[] is indexed by query); NULL = identity
 };
 
 struct RkRescoreParams {

@@ -84,14 +84,17 @@ struct IvfIndex {
 // workspace only (rk_search_batch*).
 struct TensorState {
     bool ready = false;
-    DevBuf d_xnorm, d_rowmask, d_probe;
+    DevBuf d_xnorm, d_rowmask, d_rowmask2, d_probe;
     bool x_integer = false;
     float x_absmax = 0.f, xnorm_max = 0.f;
     DevBuf d_plan, d_qp, d_tiles;
     std::vector<uint32_t> h_tiles;                                              // tile lists of all cached role masks
     std::map<std::vector<uint64_t>, std::pair<uint32_t, uint32_t>> tile_cache;  // role mask -> (offset, count) in h_tiles
-    bool last_grouped = false;
-    DevBuf d_units, d_qnorm, d_scratch, d_cand_key, d_cand_row, d_cand_count, d_sel_key, d_sel_row, d_sel_count, d_flags;
+    struct Atom { std::vector<uint64_t> mask; uint32_t tl_off = 0, tl_n = 0; uint64_t rows = 0; };
+    std::vector<Atom> atoms;                                                    // document classes by role mask (empty: too many)
+    bool tiles_dirty = false;                                                   // h_tiles grew since the last upload
+    int last_plan = 0;
+    DevBuf d_units, d_qnorm, d_scratch, d_cand_key, d_cand_row, d_cand_count, d_sel_key, d_sel_row, d_sel_count, d_tau_key, d_tau_count, d_flags;
     PinBuf h_flags;
     double last_flop = 0.0;
     uint32_t last_redo = 0;

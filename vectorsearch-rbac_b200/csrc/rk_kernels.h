@@ -37,10 +37,13 @@ cudaError_t rk_launch_ivf_plan(const uint32_t *probe_list, const uint32_t *list_
 
 // batched tensor-core engine (rk_bscan.cu)
 size_t rk_bscan_smem_bytes(int mask_words);
+int rk_bscan_lists_per_query();   // candidate lists one unit writes per query (one per epilogue set)
 size_t rk_bscan_scratch_bytes(int grid);
 cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream);
 cudaError_t rk_launch_rescore(const RkRescoreParams &p, int nq, cudaStream_t stream);
 cudaError_t rk_launch_row_norms(const float *x, size_t n, int dim_pad, float *out, cudaStream_t stream);
 cudaError_t rk_launch_rowmask(const uint32_t *rowdoc, const uint64_t *doc_mask, size_t n, int W, uint64_t *out, cudaStream_t stream);
+cudaError_t rk_launch_rowmask2(const uint32_t *rowdoc, const uint64_t *doc_mask, size_t n, size_t n_pad, int W, uint64_t *out,
+                               cudaStream_t stream);
 cudaError_t rk_launch_tf32_probe(const float *x, size_t n, unsigned long long *d_out2, cudaStream_t stream);
 cudaError_t rk_launch_max_f32(const float *x, size_t n, unsigned *d_out, cudaStream_t stream);

@@ -27,9 +27,11 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     auto sync = [] { __syncthreads(); };
 
     uint32_t l0, l1;
-    const bool by_id = p.lid0 != nullptr;
-    const uint32_t id0 = by_id ? p.lid0[q] : 0u, idstep = by_id ? p.lstep[q] : 0u;
-    if (by_id) { l0 = 0; l1 = p.nlists[q]; }
+    const bool by_id = p.lid0 != nullptr || p.list_ids != nullptr;
+    const uint32_t id0 = p.lid0 ? p.lid0[q] : 0u, idstep = p.lid0 ? p.lstep[q] : 0u;
+    const uint32_t *ids = p.list_ids ? p.list_ids + p.qseg[q] : nullptr;       // explicit list ids of this query
+    if (p.list_ids) { l0 = 0; l1 = p.qseg[q + 1] - p.qseg[q]; }
+    else if (by_id) { l0 = 0; l1 = p.nlists[q]; }
     else if (p.lists_per_query > 0) { l0 = 0; l1 = (uint32_t) p.lists_per_query; }
     else { l0 = p.qseg[q]; l1 = p.qseg[q + 1]; }
     const uint32_t nl = l1 - l0;
@@ -42,16 +44,16 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     const size_t st4 = p.shard_stride_bytes ? p.shard_stride_bytes / 4 : dense;
     const size_t st8 = p.shard_stride_bytes ? p.shard_stride_bytes / 8 : dense;
     auto b4 = [&](uint32_t j) -> size_t {
-        if (by_id) return (size_t) (id0 + j * idstep) * (size_t) p.list_stride;
+        if (by_id) return (size_t) (ids ? ids[j] : id0 + j * idstep) * (size_t) p.list_stride;
         return p.lists_per_query > 0 ? (size_t) j * st4 + (size_t) q * p.list_stride : (size_t) (l0 + j) * (size_t) p.list_stride;
     };
     auto b8 = [&](uint32_t j) -> size_t {
-        if (by_id) return (size_t) (id0 + j * idstep) * (size_t) p.list_stride;
+        if (by_id) return (size_t) (ids ? ids[j] : id0 + j * idstep) * (size_t) p.list_stride;
         return p.lists_per_query > 0 ? (size_t) j * st8 + (size_t) q * p.list_stride : (size_t) (l0 + j) * (size_t) p.list_stride;
     };
     const uint32_t cstride = p.count_stride ? (uint32_t) p.count_stride : gridDim.x;
     auto list_count = [&](uint32_t j) -> int {
-        if (by_id) return p.cand_count[id0 + j * idstep];
+        if (by_id) return p.cand_count[ids ? ids[j] : id0 + j * idstep];
         return p.cand_count ? p.cand_count[p.lists_per_query > 0 ? j * cstride + q : l0 + j] : k;
     };
     // lists without tuple ids (tensor-engine nominations) order ties by row

@@ -8,6 +8,7 @@
 // exact scan path.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 
@@ -28,11 +29,15 @@ static int tensor_prepare(rk_index *ix)
     const size_t n = ix->nrows;
     const int W = ix->mask_words;
     cudaStream_t st = 0;
-    if (ts.d_xnorm.ensure(std::max<size_t>(n * 4, 16)) != 0 || ts.d_rowmask.ensure(std::max<size_t>(n * (size_t) W * 8, 16)) != 0 ||
-        ts.d_probe.ensure(64) != 0)
-        return RK_ERR_CUDA;
+    // norms and the 16-byte row masks are padded by one tile: the kernel stages them with bulk copies of
+    // whole tiles, and a tile may reach past the last row
+    const size_t n_pad = n + 128;
+    if (ts.d_xnorm.ensure(n_pad * 4) != 0 || ts.d_rowmask2.ensure(n_pad * 16) != 0 || ts.d_probe.ensure(64) != 0) return RK_ERR_CUDA;
+    if (W > 2 && ts.d_rowmask.ensure(std::max<size_t>(n * (size_t) W * 8, 16)) != 0) return RK_ERR_CUDA;
+    RK_CUDA(cudaMemsetAsync(ts.d_xnorm.p, 0, n_pad * 4, st));
     RK_CUDA(rk_launch_row_norms(ix->d_x.as<float>(), n, ix->dim_pad, ts.d_xnorm.as<float>(), st));
-    RK_CUDA(rk_launch_rowmask(ix->d_rowdoc.as<uint32_t>(), ix->d_doc_mask.as<uint64_t>(), n, W, ts.d_rowmask.as<uint64_t>(), st));
+    if (W > 2) RK_CUDA(rk_launch_rowmask(ix->d_rowdoc.as<uint32_t>(), ix->d_doc_mask.as<uint64_t>(), n, W, ts.d_rowmask.as<uint64_t>(), st));
+    RK_CUDA(rk_launch_rowmask2(ix->d_rowdoc.as<uint32_t>(), ix->d_doc_mask.as<uint64_t>(), n, n_pad, W, ts.d_rowmask2.as<uint64_t>(), st));
     RK_CUDA(cudaMemsetAsync(ts.d_probe.p, 0, 64, st));
     RK_CUDA(rk_launch_tf32_probe(ix->d_x.as<float>(), n * (size_t) ix->dim_pad, ts.d_probe.as<unsigned long long>(), st));
     RK_CUDA(rk_launch_max_f32(ts.d_xnorm.as<float>(), n, ts.d_probe.as<unsigned>() + 8, st));
@@ -43,7 +48,52 @@ static int tensor_prepare(rk_index *ix)
     memcpy(&ts.x_absmax, &b, 4);
     b = (uint32_t) (h[4] & 0xFFFFFFFFull);
     memcpy(&ts.xnorm_max, &b, 4);
-    ix->device_bytes += ts.d_xnorm.cap + ts.d_rowmask.cap;
+    ix->device_bytes += ts.d_xnorm.cap + ts.d_rowmask.cap + ts.d_rowmask2.cap;
+
+    // Atoms: documents with the same role mask are visible to exactly the same users.  When there are
+    // few of them (role hierarchies: one per role) a batch is scored atom by atom — every atom's rows
+    // once, against all the queries that may see it — instead of once per distinct user.
+    {
+        const size_t D = ix->doc_ids.size();
+        std::map<std::vector<uint64_t>, uint32_t> by_mask;
+        std::vector<uint32_t> doc_atom(D, 0xFFFFFFFFu);
+        std::vector<uint64_t> key((size_t) W);
+        bool ok = true;
+        for (size_t d = 0; d < D && ok; d++) {
+            bool any = false;
+            for (int w = 0; w < W; w++) { key[(size_t) w] = ix->doc_mask[d * W + w]; any |= key[(size_t) w] != 0; }
+            if (!any) continue;                                      // nobody can see it
+            auto ins = by_mask.emplace(key, (uint32_t) ts.atoms.size());
+            if (ins.second) {
+                if (ts.atoms.size() >= 4096) { ok = false; break; }
+                ts.atoms.emplace_back();
+                ts.atoms.back().mask = key;
+            }
+            doc_atom[d] = ins.first->second;
+        }
+        if (!ok) ts.atoms.clear();
+        if (!ts.atoms.empty()) {
+            // tile lists: per atom the 128-row tiles covering its documents, in physical order
+            std::vector<std::vector<uint32_t>> tl(ts.atoms.size());
+            std::vector<uint64_t> covered(ts.atoms.size(), 0);
+            for (size_t d = 0; d < D; d++) {
+                const uint32_t a = doc_atom[d];
+                if (a == 0xFFFFFFFFu) continue;
+                const uint64_t r0 = ix->doc_row_start[d], r1 = ix->doc_row_start[d + 1];
+                ts.atoms[a].rows += r1 - r0;
+                if (covered[a] >= r1) continue;
+                uint64_t start = std::max(r0, covered[a]) & ~(uint64_t) 3;
+                while (start < r1) { tl[a].push_back((uint32_t) start); start += 128; }
+                covered[a] = start;
+            }
+            for (size_t a = 0; a < ts.atoms.size(); a++) {
+                ts.atoms[a].tl_off = (uint32_t) ts.h_tiles.size();
+                ts.atoms[a].tl_n = (uint32_t) tl[a].size();
+                ts.h_tiles.insert(ts.h_tiles.end(), tl[a].begin(), tl[a].end());
+            }
+            ts.tiles_dirty = true;
+        }
+    }
     ts.ready = true;
     return 0;
 }
@@ -75,7 +125,8 @@ static int tiles_for_mask(rk_index *ix, const std::vector<uint64_t> &mask, uint3
         if (!acc) continue;
         const uint64_t r0 = ix->doc_row_start[d], r1 = ix->doc_row_start[d + 1];
         if (covered >= r1) continue;
-        uint64_t start = std::max(r0, covered);
+        // tile starts are multiples of 4 rows: the tile's norms are fetched with a 16-byte aligned bulk copy
+        uint64_t start = std::max(r0, covered) & ~(uint64_t) 3;
         while (start < r1) { ts.h_tiles.push_back((uint32_t) start); start += 128; }
         covered = start;
     }
@@ -90,7 +141,123 @@ struct TGroup {
     std::vector<uint32_t> queries;
     const UserInfo *user = nullptr;
     uint32_t tl_off = 0, tl_n = 0;
+    uint64_t min_visible = 0;      // fewest rows any query of the group can see
 };
+
+// One launch of the scoring kernel: units, their balanced assignment to CTAs, and which candidate
+// lists each query slot owns afterwards.
+struct TPass {
+    std::vector<RkBUnit> units;
+    std::vector<uint32_t> cta_off, cta_units, lid0, lstep, nlists;
+    uint32_t list_total = 0;
+    int grid = 1;
+    double tile_visits = 0.0;
+    size_t o_units = 0, o_coff = 0, o_cu = 0, o_lid0 = 0, o_lstep = 0, o_nl = 0;     // offsets in the staged plan
+};
+
+// Cuts every (group, tile of 128 queries) pair into units over the group's tiles visited with stride
+// step[g] (0 = the group takes no part in this pass) and balances the units onto the CTAs.
+static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint32_t> &step, int sm, uint32_t LPQ, size_t nslots,
+                       TPass &ps)
+{
+    double total_work = 0.0;
+    size_t max_gq = 0;
+    for (size_t gi = 0; gi < groups.size(); gi++) {
+        if (!step[gi]) continue;
+        const TGroup &g = groups[gi];
+        const double visits = (double) ((g.tl_n + step[gi] - 1) / step[gi]);
+        total_work += visits * (double) ((g.queries.size() + 127) / 128);
+        max_gq = std::max(max_gq, std::min<size_t>(128, g.queries.size()));
+    }
+    ps.tile_visits = total_work;
+    // tiles per unit: ~8 units per CTA, but a unit ends with one compaction + sort per query, so it
+    // must be long enough to amortise them; with few units, size them to fill whole rounds of CTAs
+    uint32_t tpu = (uint32_t) std::max(32.0 + 2.0 * (double) max_gq, total_work / ((double) sm * 8.0));
+    {
+        const double est_units = total_work / (double) tpu;
+        if (est_units < 4.0 * sm) {
+            // few units: they must fill whole rounds of CTAs — one unit too many doubles the makespan.
+            // Grow the unit length until the units of all (group, query tile) pairs fit m rounds.
+            const double m = std::max(1.0, std::floor(est_units / sm));
+            tpu = (uint32_t) std::max(1.0, std::ceil(total_work / (m * sm)));
+            // (with many (group, query tile) pairs the units differ in length anyway and the
+            // longest-first schedule below balances them: more, shorter units are better there)
+            size_t npairs = 0;
+            for (size_t gi = 0; gi < groups.size(); gi++)
+                if (step[gi]) npairs += (groups[gi].queries.size() + 127) / 128;
+            for (int it = 0; it < 64 && npairs * 2 <= (size_t) sm; it++) {
+                uint64_t units = 0;
+                for (size_t gi = 0; gi < groups.size(); gi++) {
+                    if (!step[gi]) continue;
+                    const uint64_t visits = (groups[gi].tl_n + step[gi] - 1) / step[gi];
+                    units += std::max<uint64_t>(1, (visits + tpu - 1) / tpu) * ((groups[gi].queries.size() + 127) / 128);
+                }
+                if ((double) units <= m * sm) break;
+                tpu += std::max<uint32_t>(1, tpu / 64);
+            }
+        }
+    }
+    ps.lid0.assign(nslots, 0); ps.lstep.assign(nslots, 0); ps.nlists.assign(nslots, 0);
+    std::vector<double> unit_work;
+    uint32_t slot = 0;
+    for (size_t gi = 0; gi < groups.size(); gi++) {
+        const TGroup &g = groups[gi];
+        const size_t gq = g.queries.size();
+        if (!step[gi]) { slot += (uint32_t) gq; continue; }
+        const uint32_t st = step[gi];
+        const uint32_t visits = (g.tl_n + st - 1) / st;
+        for (size_t b = 0; b < gq; b += 128) {
+            const uint32_t qn = (uint32_t) std::min<size_t>(128, gq - b);
+            const uint32_t R = std::max<uint32_t>(1, (visits + tpu - 1) / tpu);
+            for (uint32_t i = 0; i < qn; i++) {
+                ps.lid0[slot + i] = ps.list_total + i;
+                ps.lstep[slot + i] = qn;
+                ps.nlists[slot + i] = R * LPQ;          // every unit writes one list per epilogue set
+            }
+            for (uint32_t r = 0; r < R; r++) {
+                RkBUnit u;
+                memset(&u, 0, sizeof u);
+                const uint32_t lo = (uint32_t) ((uint64_t) visits * r / R), hi = (uint32_t) ((uint64_t) visits * (r + 1) / R);
+                u.q0 = slot; u.nq = qn;
+                u.tile_begin = lo * st;
+                u.tile_end = hi == visits ? g.tl_n : hi * st;
+                u.tile_step = st;
+                u.tl_off = g.tl_off;
+                u.list_base = ps.list_total;
+                ps.list_total += qn * LPQ;
+                ps.units.push_back(u);
+                unit_work.push_back((double) (hi - lo) * (128.0 + (double) ((qn + 15) & ~15u)) + 2000.0 * qn);
+            }
+            slot += qn;
+        }
+    }
+    const uint32_t nunits = (uint32_t) ps.units.size();
+    ps.grid = (int) std::min<uint32_t>((uint32_t) sm, std::max<uint32_t>(nunits, 1));
+    // balanced static schedule: longest unit first onto the least loaded CTA
+    std::vector<uint32_t> order(nunits);
+    ps.cta_off.assign((size_t) ps.grid + 1, 0);
+    ps.cta_units.assign(nunits, 0);
+    for (uint32_t i = 0; i < nunits; i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return unit_work[x] > unit_work[y]; });
+    std::vector<std::vector<uint32_t>> per((size_t) ps.grid);
+    std::vector<std::pair<double, int>> heap;            // (load, cta) min-heap
+    for (int c = 0; c < ps.grid; c++) heap.push_back({0.0, c});
+    auto cmp = [](const std::pair<double, int> &x, const std::pair<double, int> &y) { return x.first > y.first; };
+    std::make_heap(heap.begin(), heap.end(), cmp);
+    for (uint32_t u : order) {
+        std::pop_heap(heap.begin(), heap.end(), cmp);
+        auto &top = heap.back();
+        per[(size_t) top.second].push_back(u);
+        top.first += unit_work[u];
+        std::push_heap(heap.begin(), heap.end(), cmp);
+    }
+    uint32_t pos = 0;
+    for (int c = 0; c < ps.grid; c++) {
+        ps.cta_off[(size_t) c] = pos;
+        for (uint32_t u : per[(size_t) c]) ps.cta_units[pos++] = u;
+    }
+    ps.cta_off[(size_t) ps.grid] = pos;
+}
 
 // Runs the batch on the tensor engine.  `out` carries the final device destinations.  On return
 // `redo` lists the queries whose answer could not be proven (to be re-run on the exact scan path).
@@ -113,7 +280,6 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
 
     // ---- groups: queries that see the same rows (same role mask) share one pass over those rows
     std::vector<TGroup> groups;
-    std::vector<uint32_t> empty_queries;           // users without roles: nothing visible
     {
         std::map<std::vector<uint64_t>, uint32_t> by_mask;
         std::vector<uint64_t> key((size_t) W);
@@ -124,131 +290,131 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
                     auto it = ix->users.find(user_ids[q]);
                     if (it != ix->users.end()) u = &it->second;
                 }
-                if (!u || u->allowed_rows == 0) { empty_queries.push_back((uint32_t) q); continue; }
+                if (!u || u->allowed_rows == 0) continue;          // nothing visible: the query owns no list
                 key = u->mask;
             } else {
                 std::fill(key.begin(), key.end(), ~0ull);
             }
             auto ins = by_mask.emplace(key, (uint32_t) groups.size());
-            if (ins.second) { groups.emplace_back(); groups.back().user = u; }
+            if (ins.second) { groups.emplace_back(); groups.back().user = u; groups.back().min_visible = u ? u->allowed_rows : n; }
             groups[ins.first->second].queries.push_back((uint32_t) q);
         }
     }
-    // grouped (visit only tiles with visible rows, once per group) or dense (every tile, all queries
-    // together)?  Compare the bytes each plan stages into shared memory: (128 + padded queries) per tile.
-    bool grouped = use_mask;
+    // Three ways to walk the rows; the plan that stages the fewest bytes into shared memory wins
+    // ((128 rows + padded queries) per tile visit):
+    //   dense    every tile against all queries together, mask test per (row, query)
+    //   grouped  per distinct user mask: only the tiles holding rows that user sees
+    //   atoms    per document class (same role mask): its tiles once, against every query that sees it
+    auto visit_cost = [](double tiles, size_t qn) {
+        return tiles * (double) ((qn + 127) / 128) * (128.0 + (double) std::min<size_t>(128, (qn + 15) & ~(size_t) 15));
+    };
+    enum { PLAN_DENSE, PLAN_GROUPED, PLAN_ATOMS } plan = PLAN_DENSE;
     bool grew = false;
-    if (grouped) {
-        double cost_g = 0.0;
+    std::vector<std::vector<uint32_t>> atom_groups;          // atoms plan: user groups that see each atom
+    if (use_mask && !groups.empty()) {
+        double cost_g = 0.0, cost_a = 0.0;
+        size_t nq_live = 0;
         for (auto &g : groups) {
             rc = tiles_for_mask(ix, g.user->mask, &g.tl_off, &g.tl_n, &grew);
             if (rc < 0) return rc;
-            const size_t qn = g.queries.size();
-            cost_g += (double) g.tl_n * (double) ((qn + 127) / 128) * (128.0 + (double) std::min<size_t>(128, (qn + 15) & ~(size_t) 15));
+            cost_g += visit_cost((double) g.tl_n, g.queries.size());
+            nq_live += g.queries.size();
         }
-        const double cost_d = (double) T * (double) ((nq + 127) / 128) * 256.0;
-        if (cost_g > cost_d) grouped = false;
+        const double cost_d = visit_cost((double) T, nq_live);
+        double best = cost_d;
+        if (cost_g < best) { best = cost_g; plan = PLAN_GROUPED; }
+        if (!ts.atoms.empty()) {
+            atom_groups.resize(ts.atoms.size());
+            for (size_t a = 0; a < ts.atoms.size(); a++) {
+                size_t qn = 0;
+                for (size_t gi = 0; gi < groups.size(); gi++) {
+                    uint64_t acc = 0;
+                    for (int w = 0; w < W; w++) acc |= ts.atoms[a].mask[(size_t) w] & groups[gi].user->mask[(size_t) w];
+                    if (acc) { atom_groups[a].push_back((uint32_t) gi); qn += groups[gi].queries.size(); }
+                }
+                if (qn) cost_a += visit_cost((double) ts.atoms[a].tl_n, qn);
+            }
+            if (cost_a < 0.9 * best) { best = cost_a; plan = PLAN_ATOMS; }
+        }
     }
-    if (!grouped && groups.size() != 1) {
-        // dense: one group holding every query that can see something; the mask test is per (row, query)
+    const bool per_slot_mask = plan != PLAN_GROUPED;       // which mask a slot carries: its query's own, or the group's
+    if (plan == PLAN_DENSE && groups.size() > 1) {
+        // one group holding every query that can see something
         TGroup all;
-        for (auto &g : groups) all.queries.insert(all.queries.end(), g.queries.begin(), g.queries.end());
+        all.min_visible = n;
+        for (auto &g : groups) {
+            all.queries.insert(all.queries.end(), g.queries.begin(), g.queries.end());
+            all.min_visible = std::min(all.min_visible, g.min_visible);
+        }
         std::sort(all.queries.begin(), all.queries.end());
         groups.clear();
         groups.push_back(std::move(all));
     }
-    if (!grouped)
+    if (plan == PLAN_DENSE)
         for (auto &g : groups) { g.tl_off = 0; g.tl_n = T; }
-    if (grouped && grew) {
+    if (plan == PLAN_ATOMS) {
+        // the units' groups become the atoms; a query appears once per atom it can see
+        std::vector<TGroup> ag;
+        for (size_t a = 0; a < ts.atoms.size(); a++) {
+            if (atom_groups[a].empty()) continue;
+            TGroup g;
+            g.tl_off = ts.atoms[a].tl_off; g.tl_n = ts.atoms[a].tl_n;
+            g.min_visible = ts.atoms[a].rows;
+            for (uint32_t gi : atom_groups[a]) g.queries.insert(g.queries.end(), groups[gi].queries.begin(), groups[gi].queries.end());
+            ag.push_back(std::move(g));
+        }
+        groups.swap(ag);
+    }
+    if (plan != PLAN_DENSE && (grew || ts.tiles_dirty)) {
         if (ts.d_tiles.ensure(std::max<size_t>(ts.h_tiles.size() * 4, 16)) != 0) return RK_ERR_CUDA;
         RK_CUDA(cudaMemcpyAsync(ts.d_tiles.p, ts.h_tiles.data(), ts.h_tiles.size() * 4, cudaMemcpyHostToDevice, st));
         RK_CUDA(cudaStreamSynchronize(st));      // h_tiles may reallocate on the next call
+        ts.tiles_dirty = false;
     }
 
-    // ---- slots (group-ordered queries), units, lists
+    // ---- slots (group-ordered queries; a query owns one slot per group it appears in) and the two passes
     size_t nslots = 0;
     for (auto &g : groups) nslots += g.queries.size();
-    double total_work = 0.0;
-    for (auto &g : groups) total_work += (double) g.tl_n * (double) ((g.queries.size() + 127) / 128);
-    // tiles per unit: ~8 units per CTA, but a unit ends with one compaction + sort per query, so it
-    // must be long enough to amortise them; with few units, size them to fill whole rounds of CTAs
-    size_t max_gq = 0;
-    for (auto &g : groups) max_gq = std::max(max_gq, std::min<size_t>(128, g.queries.size()));
-    uint32_t tpu = (uint32_t) std::max(32.0 + 2.0 * (double) max_gq, total_work / ((double) sm * 8.0));
-    uint32_t single_R = 0;
+    const uint32_t LPQ = (uint32_t) rk_bscan_lists_per_query();
+    std::vector<uint32_t> slot_q(nslots);
     {
-        const double est_units = total_work / (double) tpu;
-        if (est_units < 4.0 * sm) {
-            const double m = std::max(1.0, std::floor(est_units / sm));
-            tpu = (uint32_t) std::ceil(total_work / (m * sm));
-            if (groups.size() == 1) {
-                const uint32_t qt = (uint32_t) ((groups[0].queries.size() + 127) / 128);
-                single_R = std::max<uint32_t>(1, (uint32_t) (m * sm) / std::max<uint32_t>(qt, 1));
-                single_R = std::min<uint32_t>(single_R, std::max<uint32_t>(1, groups[0].tl_n));
-            }
-        }
+        uint32_t s = 0;
+        for (auto &g : groups)
+            for (uint32_t q : g.queries) slot_q[s++] = q;
     }
-    std::vector<RkBUnit> units;
-    std::vector<uint32_t> slot_q(nslots), lid0(nslots), lstep(nslots), nlists(nslots);
-    std::vector<double> unit_work;
-    uint32_t slot = 0, list_total = 0;
-    for (auto &g : groups) {
-        const size_t gq = g.queries.size();
-        for (size_t b = 0; b < gq; b += 128) {
-            const uint32_t qn = (uint32_t) std::min<size_t>(128, gq - b);
-            const uint32_t R = single_R ? single_R : std::max<uint32_t>(1, (g.tl_n + tpu - 1) / tpu);
-            for (uint32_t i = 0; i < qn; i++) {
-                slot_q[slot + i] = g.queries[b + i];
-                lid0[slot + i] = list_total + i;
-                lstep[slot + i] = qn;
-                nlists[slot + i] = R;
-            }
-            for (uint32_t r = 0; r < R; r++) {
-                RkBUnit u;
-                memset(&u, 0, sizeof u);
-                u.q0 = slot; u.nq = qn;
-                u.tile_begin = (uint32_t) ((uint64_t) g.tl_n * r / R);
-                u.tile_end = (uint32_t) ((uint64_t) g.tl_n * (r + 1) / R);
-                u.tl_off = g.tl_off;
-                u.list_base = list_total;
-                list_total += qn;
-                units.push_back(u);
-                unit_work.push_back((double) (u.tile_end - u.tile_begin) * (128.0 + (double) ((qn + 15) & ~15u)) + 2000.0 * qn);
-            }
-            slot += qn;
-        }
+    // Sampling pass: the kp-th smallest value over every S-th tile bounds the kp-th smallest over all
+    // tiles from above, so the main pass can start every unit at that threshold instead of +inf: far
+    // fewer (query, row) pairs survive the threshold test, and units may be cut as small as load
+    // balance wants.
+    std::vector<uint32_t> step_main(groups.size(), 1), step_sample(groups.size(), 0);
+    bool sampled = false;
+    static const int env_sample = getenv("RK_TENSOR_SAMPLE") ? atoi(getenv("RK_TENSOR_SAMPLE")) : 1;    // tuning aid: 0 disables the sampling pass
+    static const int env_sdiv = getenv("RK_TENSOR_SDIV") ? atoi(getenv("RK_TENSOR_SDIV")) : 400;
+    for (size_t gi = 0; gi < groups.size() && env_sample; gi++) {
+        const TGroup &g = groups[gi];
+        if (g.tl_n < 1024) continue;
+        // about 1 in 400 of the (visible row, query) pairs should survive the seeded threshold: kp S / visible
+        const uint64_t S = std::min<uint64_t>(64, g.min_visible / ((uint64_t) env_sdiv * (uint64_t) kp));
+        if (S >= 4) { step_sample[gi] = (uint32_t) S; sampled = true; }
     }
-    const uint32_t nunits = (uint32_t) units.size();
-    const int grid = (int) std::min<uint32_t>((uint32_t) sm, std::max<uint32_t>(nunits, 1));
-    // balanced static schedule: longest unit first onto the least loaded CTA
-    std::vector<uint32_t> order(nunits), cta_off((size_t) grid + 1, 0), cta_units(nunits);
+    TPass pm_, ps_;
+    build_pass(groups, step_main, sm, LPQ, nslots, pm_);
+    if (sampled) build_pass(groups, step_sample, sm, LPQ, nslots, ps_);
+    // final merge: every query owns the main-pass lists of all its slots
+    std::vector<uint32_t> qoff(nq + 1, 0), qlist;
     {
-        for (uint32_t i = 0; i < nunits; i++) order[i] = i;
-        std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return unit_work[a] > unit_work[b]; });
-        std::vector<std::vector<uint32_t>> per((size_t) grid);
-        std::vector<std::pair<double, int>> heap;            // (load, cta) min-heap
-        for (int c = 0; c < grid; c++) heap.push_back({0.0, c});
-        auto cmp = [](const std::pair<double, int> &a, const std::pair<double, int> &b) { return a.first > b.first; };
-        std::make_heap(heap.begin(), heap.end(), cmp);
-        for (uint32_t u : order) {
-            std::pop_heap(heap.begin(), heap.end(), cmp);
-            auto &top = heap.back();
-            per[(size_t) top.second].push_back(u);
-            top.first += unit_work[u];
-            std::push_heap(heap.begin(), heap.end(), cmp);
-        }
-        uint32_t pos = 0;
-        for (int c = 0; c < grid; c++) {
-            cta_off[(size_t) c] = pos;
-            for (uint32_t u : per[(size_t) c]) cta_units[pos++] = u;
-        }
-        cta_off[(size_t) grid] = pos;
+        for (size_t s_ = 0; s_ < nslots; s_++) qoff[slot_q[s_] + 1] += pm_.nlists[s_];
+        for (size_t q = 0; q < nq; q++) qoff[q + 1] += qoff[q];
+        qlist.resize(qoff[nq]);
+        std::vector<uint32_t> fill(qoff.begin(), qoff.end() - 1);
+        for (size_t s_ = 0; s_ < nslots; s_++)
+            for (uint32_t j = 0; j < pm_.nlists[s_]; j++) qlist[fill[slot_q[s_]]++] = pm_.lid0[s_] + j * pm_.lstep[s_];
     }
 
-    // ---- staging: [units][cta_off][cta_units][slot_q][lid0][lstep][nlists][qmask per slot]
-    const size_t b_units = (size_t) nunits * sizeof(RkBUnit), b_coff = ((size_t) grid + 1) * 4, b_cu = (size_t) nunits * 4;
+    // ---- staging: per pass [units][cta_off][cta_units][lid0][lstep][nlists], then [slot_q][qoff][qlist][qmask per slot]
     const size_t b_slot = nslots * 4, b_qmask = nslots * (size_t) W * 8;
-    const size_t total_stage = b_units + b_coff + b_cu + 4 * b_slot + b_qmask + 256;
+    auto pass_bytes = [&](const TPass &t) { return t.units.size() * sizeof(RkBUnit) + (t.cta_off.size() + t.cta_units.size()) * 4 + 3 * b_slot + 128; };
+    const size_t total_stage = pass_bytes(pm_) + (sampled ? pass_bytes(ps_) : 0) + b_slot + (qoff.size() + qlist.size()) * 4 + b_qmask + 256;
     ws.plan_idx ^= 1;
     const int pi_ = ws.plan_idx;
     if (ws.ev_plan_used[pi_]) RK_CUDA(cudaEventSynchronize(ws.ev_plan[pi_]));
@@ -263,69 +429,144 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         off = (off + bytes + 15) & ~(size_t) 15;
         return at;
     };
-    const size_t o_units = put(units.data(), b_units), o_coff = put(cta_off.data(), b_coff), o_cu = put(cta_units.data(), b_cu);
-    const size_t o_slotq = put(slot_q.data(), b_slot), o_lid0 = put(lid0.data(), b_slot), o_lstep = put(lstep.data(), b_slot);
-    const size_t o_nl = put(nlists.data(), b_slot);
+    auto stage_pass = [&](TPass &t) {
+        t.o_units = put(t.units.data(), t.units.size() * sizeof(RkBUnit));
+        t.o_coff = put(t.cta_off.data(), t.cta_off.size() * 4);
+        t.o_cu = put(t.cta_units.data(), t.cta_units.size() * 4);
+        t.o_lid0 = put(t.lid0.data(), b_slot);
+        t.o_lstep = put(t.lstep.data(), b_slot);
+        t.o_nl = put(t.nlists.data(), b_slot);
+    };
+    stage_pass(pm_);
+    if (sampled) stage_pass(ps_);
+    const size_t o_slotq = put(slot_q.data(), b_slot);
+    const size_t o_qoff = put(qoff.data(), qoff.size() * 4);
+    const size_t o_qlist = put(qlist.data(), qlist.size() * 4);
     const size_t o_qmask = off;
     {
         uint64_t *hm = reinterpret_cast<uint64_t *>(hp + o_qmask);
-        uint32_t s = 0;
+        uint32_t s_ = 0;
         for (auto &g : groups) {
-            // grouped: the group's mask; dense: each query's own mask
             for (uint32_t q : g.queries) {
                 const UserInfo *u = g.user;
-                if (!grouped && use_mask && user_ids) {
+                if (per_slot_mask && use_mask && user_ids) {
                     auto it = ix->users.find(user_ids[q]);
                     u = it == ix->users.end() ? nullptr : &it->second;
                 }
-                for (int w = 0; w < W; w++) hm[(size_t) s * W + w] = u ? u->mask[w] : 0ull;
-                s++;
+                for (int w = 0; w < W; w++) hm[(size_t) s_ * W + w] = u ? u->mask[(size_t) w] : 0ull;
+                s_++;
             }
         }
         off += b_qmask;
     }
     const unsigned char *dplan = ts.d_plan.as<unsigned char>();
+    const uint32_t list_max = std::max(pm_.list_total, ps_.list_total);
+    const int grid_max = std::max(pm_.grid, ps_.grid);
     if (ts.d_qp.ensure(std::max<size_t>(nslots * (size_t) ix->dim_pad * 4, 16)) != 0 ||
-        ts.d_qnorm.ensure(std::max<size_t>(nslots * 4, 16)) != 0 || ts.d_scratch.ensure(rk_bscan_scratch_bytes(grid)) != 0 ||
-        ts.d_cand_key.ensure(std::max<size_t>((size_t) list_total * kp * 4, 16)) != 0 ||
-        ts.d_cand_row.ensure(std::max<size_t>((size_t) list_total * kp * 4, 16)) != 0 ||
-        ts.d_cand_count.ensure(std::max<size_t>((size_t) list_total * 4, 16)) != 0 ||
-        ts.d_sel_key.ensure(std::max<size_t>(nslots * (size_t) kp * 4, 16)) != 0 ||
-        ts.d_sel_row.ensure(std::max<size_t>(nslots * (size_t) kp * 4, 16)) != 0 || ts.d_sel_count.ensure(std::max<size_t>(nslots * 4, 16)) != 0 ||
-        ts.d_flags.ensure(std::max<size_t>((nq + nslots) * 4, 16)) != 0 || ts.h_flags.ensure(std::max<size_t>(nq * 4 + 128, 128)) != 0)
+        ts.d_qnorm.ensure(std::max<size_t>(nq * 4, 16)) != 0 || ts.d_scratch.ensure(rk_bscan_scratch_bytes(grid_max)) != 0 ||
+        ts.d_cand_key.ensure(std::max<size_t>((size_t) list_max * kp * 4, 16)) != 0 ||
+        ts.d_cand_row.ensure(std::max<size_t>((size_t) list_max * kp * 4, 16)) != 0 ||
+        ts.d_cand_count.ensure(std::max<size_t>((size_t) list_max * 4, 16)) != 0 ||
+        ts.d_sel_key.ensure(std::max<size_t>(nq * (size_t) kp * 4, 16)) != 0 ||
+        ts.d_sel_row.ensure(std::max<size_t>(nq * (size_t) kp * 4, 16)) != 0 || ts.d_sel_count.ensure(std::max<size_t>(nq * 4, 16)) != 0 ||
+        ts.d_tau_key.ensure(std::max<size_t>(nslots * (size_t) kp * 4, 16)) != 0 || ts.d_tau_count.ensure(std::max<size_t>(nslots * 4, 16)) != 0 ||
+        ts.d_flags.ensure(std::max<size_t>(3 * nq * 4, 16)) != 0 || ts.h_flags.ensure(std::max<size_t>(nq * 4 + 128, 128)) != 0)
         return RK_ERR_CUDA;
     RK_CUDA(cudaMemcpyAsync(ts.d_plan.p, hp, off, cudaMemcpyHostToDevice, st));
     RK_CUDA(cudaEventRecord(ws.ev_plan[pi_], st));
     ws.ev_plan_used[pi_] = true;
-    RK_CUDA(cudaMemsetAsync(ts.d_flags.p, 0, (nq + nslots) * 4, st));      // [uncertain per query][trunc per slot]
+    RK_CUDA(cudaMemsetAsync(ts.d_flags.p, 0, 3 * nq * 4, st));      // [uncertain][trunc][sample-pass trunc], each per query
     RK_CUDA(cudaMemsetAsync(ts.d_probe.p, 0, 64, st));
+    uint64_t launches = 0;
 
-    // queries nobody can answer from (no visible rows): empty results straight away
-    if (!empty_queries.empty() || nslots == 0) {
-        RkSelectParams ep = out;
-        ep.cand_key = nullptr; ep.cand_tid = nullptr; ep.cand_row = nullptr; ep.cand_count = nullptr;
-        if (ws.qseg.ensure((nq + 1) * 4) != 0) return RK_ERR_CUDA;
-        RK_CUDA(cudaMemsetAsync(ws.qseg.p, 0, (nq + 1) * 4, st));           // every query owns zero lists
-        ep.qseg = ws.qseg.as<uint32_t>();
-        ep.lists_per_query = 0; ep.lid0 = nullptr; ep.list_stride = k; ep.k = k; ep.metric = ix->metric; ep.dedup = 0;
-        ep.key_is_float = 0; ep.rowdoc = nullptr; ep.doc_ids = nullptr;
-        RK_CUDA(rk_launch_select(ep, (int) nq, st));                         // fills padding + count 0 for all; real answers overwrite below
-        ws.launches++;
-    }
-    if (nslots == 0) {
-        ts.last_redo = 0; ts.last_exact = true; ts.last_flop = 0.0;
-        return RK_OK;
-    }
-
-    // group-ordered query matrix, its norms and TF32-exactness
+    // norms and TF32-exactness of the queries; the group-ordered copy of the query matrix the TMA reads
     const uint32_t *d_slotq = reinterpret_cast<const uint32_t *>(dplan + o_slotq);
-    RK_CUDA(rk_launch_gather_rows(dQ, ts.d_qp.as<float>(), d_slotq, nslots, ix->dim_pad, st));
-    const float *dQp = ts.d_qp.as<float>();
-    RK_CUDA(rk_launch_row_norms(dQp, nslots, ix->dim_pad, ts.d_qnorm.as<float>(), st));
-    RK_CUDA(rk_launch_tf32_probe(dQp, nslots * (size_t) ix->dim_pad, ts.d_probe.as<unsigned long long>(), st));
-    RK_CUDA(rk_launch_max_f32(ts.d_qnorm.as<float>(), nslots, ts.d_probe.as<unsigned>() + 8, st));
+    RK_CUDA(rk_launch_row_norms(dQ, nq, ix->dim_pad, ts.d_qnorm.as<float>(), st));
+    RK_CUDA(rk_launch_tf32_probe(dQ, nq * (size_t) ix->dim_pad, ts.d_probe.as<unsigned long long>(), st));
+    RK_CUDA(rk_launch_max_f32(ts.d_qnorm.as<float>(), nq, ts.d_probe.as<unsigned>() + 8, st));
+    launches += 3;
     unsigned long long *hprobe = reinterpret_cast<unsigned long long *>(ts.h_flags.as<unsigned char>() + ((nq * 4 + 15) & ~(size_t) 15));
     RK_CUDA(cudaMemcpyAsync(hprobe, ts.d_probe.p, 40, cudaMemcpyDeviceToHost, st));
+    // (the probe result is only needed for the rescore launch: the scoring passes are queued first)
+    const float *dQp = ts.d_qp.as<float>();
+    if (nslots) { RK_CUDA(rk_launch_gather_rows(dQ, ts.d_qp.as<float>(), d_slotq, nslots, ix->dim_pad, st)); launches++; }
+
+    RkBScanParams bp;
+    memset(&bp, 0, sizeof bp);
+    bp.tile_rows = plan != PLAN_DENSE ? ts.d_tiles.as<uint32_t>() : nullptr;
+    bp.nrows = n;
+    bp.dim_pad = ix->dim_pad;
+    bp.kchunks = (ix->dim_pad + 31) / 32;
+    bp.metric = ix->metric;
+    bp.kp = kp;
+    bp.mask_words = W;
+    bp.use_mask = use_mask ? 1 : 0;
+    bp.xnorm = ts.d_xnorm.as<float>();
+    bp.rowmask = ts.d_rowmask.as<uint64_t>();
+    bp.rowmask2 = ts.d_rowmask2.as<uint64_t>();
+    bp.qnorm = nullptr;
+    bp.qmask = reinterpret_cast<const uint64_t *>(dplan + o_qmask);
+    bp.slot_q = d_slotq;
+    bp.scratch = ts.d_scratch.as<uint2>();
+    bp.cand_key = ts.d_cand_key.as<uint32_t>();
+    bp.cand_row = ts.d_cand_row.as<uint32_t>();
+    bp.cand_count = ts.d_cand_count.as<int32_t>();
+    auto bind_pass = [&](const TPass &t) {
+        bp.units = reinterpret_cast<const RkBUnit *>(dplan + t.o_units);
+        bp.nunits = (uint32_t) t.units.size();
+        bp.cta_off = reinterpret_cast<const uint32_t *>(dplan + t.o_coff);
+        bp.cta_units = reinterpret_cast<const uint32_t *>(dplan + t.o_cu);
+    };
+    // merge of nominations: top-kp by (approximate key, row)
+    RkSelectParams sp;
+    memset(&sp, 0, sizeof sp);
+    sp.cand_key = ts.d_cand_key.as<uint32_t>();
+    sp.cand_tid = nullptr;
+    sp.cand_row = ts.d_cand_row.as<uint32_t>();
+    sp.cand_count = ts.d_cand_count.as<int32_t>();
+    sp.list_stride = kp;
+    sp.k = kp;
+    sp.metric = ix->metric;
+    sp.dedup = 0;
+
+    const int slot_ev = (int) (ws.ring_n % RK_TIMING_RING);
+    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot_ev], st));
+    if (sampled) {
+        bind_pass(ps_);
+        bp.trunc = ts.d_flags.as<int32_t>() + 2 * nq;      // ties dropped here only loosen the seed
+        bp.tau_key = nullptr; bp.tau_count = nullptr;
+        RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, ps_.grid, st));
+        // per slot: the sample's kp smallest values
+        sp.lid0 = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lid0);
+        sp.lstep = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lstep);
+        sp.nlists = reinterpret_cast<const uint32_t *>(dplan + ps_.o_nl);
+        sp.out_key = ts.d_tau_key.as<float>();
+        sp.out_row = nullptr;
+        sp.out_count = ts.d_tau_count.as<int32_t>();
+        RK_CUDA(rk_launch_select(sp, (int) nslots, st));
+        launches += 2;
+    }
+    if (nslots) {
+        bind_pass(pm_);
+        bp.trunc = ts.d_flags.as<int32_t>() + nq;
+        bp.tau_key = sampled ? ts.d_tau_key.as<float>() : nullptr;
+        bp.tau_count = sampled ? ts.d_tau_count.as<int32_t>() : nullptr;
+        RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, pm_.grid, st));
+        launches++;
+    }
+    if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot_ev], st)); ws.timed_scan = true; ws.ring_n++; }
+
+    // per query: the kp best nominations over all its slots' lists
+    sp.lid0 = nullptr; sp.lstep = nullptr; sp.nlists = nullptr;
+    sp.qseg = reinterpret_cast<const uint32_t *>(dplan + o_qoff);
+    sp.list_ids = reinterpret_cast<const uint32_t *>(dplan + o_qlist);
+    sp.out_key = ts.d_sel_key.as<float>();
+    sp.out_row = ts.d_sel_row.as<uint32_t>();
+    sp.out_count = ts.d_sel_count.as<int32_t>();
+    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ev[2], st));
+    RK_CUDA(rk_launch_select(sp, (int) nq, st));
+    launches++;
+
     RK_CUDA(cudaStreamSynchronize(st));
     float qnorm_max;
     { uint32_t b = (uint32_t) (hprobe[4] & 0xFFFFFFFFull); memcpy(&qnorm_max, &b, 4); }
@@ -337,63 +578,17 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // product by < 2^-9; |x.q| error <= 2^-9 * |x||q|; the L2 form doubles it
     const float eps_scale = exact ? 0.f : (ix->metric == RK_METRIC_L2 ? 2.f : 1.f) * (1.0f / 512.0f);
 
-    RkBScanParams bp;
-    memset(&bp, 0, sizeof bp);
-    bp.units = reinterpret_cast<const RkBUnit *>(dplan + o_units);
-    bp.nunits = nunits;
-    bp.cta_off = reinterpret_cast<const uint32_t *>(dplan + o_coff);
-    bp.cta_units = reinterpret_cast<const uint32_t *>(dplan + o_cu);
-    bp.tile_rows = grouped ? ts.d_tiles.as<uint32_t>() : nullptr;
-    bp.nrows = n;
-    bp.dim_pad = ix->dim_pad;
-    bp.kchunks = (ix->dim_pad + 31) / 32;
-    bp.metric = ix->metric;
-    bp.kp = kp;
-    bp.mask_words = W;
-    bp.use_mask = use_mask ? 1 : 0;
-    bp.xnorm = ts.d_xnorm.as<float>();
-    bp.rowmask = ts.d_rowmask.as<uint64_t>();
-    bp.qnorm = ts.d_qnorm.as<float>();
-    bp.qmask = reinterpret_cast<const uint64_t *>(dplan + o_qmask);
-    bp.scratch = ts.d_scratch.as<uint2>();
-    bp.cand_key = ts.d_cand_key.as<uint32_t>();
-    bp.cand_row = ts.d_cand_row.as<uint32_t>();
-    bp.cand_count = ts.d_cand_count.as<int32_t>();
-    bp.trunc = ts.d_flags.as<int32_t>() + nq;
-    const int slot_ev = (int) (ws.ring_n % RK_TIMING_RING);
-    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot_ev], st));
-    RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, grid, st));
-    if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot_ev], st)); ws.timed_scan = true; ws.ring_n++; }
-
-    // merge the nominations of each slot: top-kp by (approximate key, row)
-    RkSelectParams sp;
-    memset(&sp, 0, sizeof sp);
-    sp.cand_key = ts.d_cand_key.as<uint32_t>();
-    sp.cand_tid = nullptr;
-    sp.cand_row = ts.d_cand_row.as<uint32_t>();
-    sp.cand_count = ts.d_cand_count.as<int32_t>();
-    sp.lid0 = reinterpret_cast<const uint32_t *>(dplan + o_lid0);
-    sp.lstep = reinterpret_cast<const uint32_t *>(dplan + o_lstep);
-    sp.nlists = reinterpret_cast<const uint32_t *>(dplan + o_nl);
-    sp.list_stride = kp;
-    sp.k = kp;
-    sp.metric = ix->metric;
-    sp.dedup = 0;
-    sp.out_key = ts.d_sel_key.as<float>();
-    sp.out_row = ts.d_sel_row.as<uint32_t>();
-    sp.out_count = ts.d_sel_count.as<int32_t>();
-    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ev[2], st));
-    RK_CUDA(rk_launch_select(sp, (int) nslots, st));
-
+    // exact re-score of every query's nominations in the caller's order (a query without lists gets an
+    // empty result)
     RkRescoreParams rp;
     memset(&rp, 0, sizeof rp);
     rp.x = ix->d_x.as<float>();
     rp.tid = ix->d_tid.as<uint64_t>();
     rp.rowdoc = ix->d_rowdoc.as<uint32_t>();
     rp.doc_ids = ix->d_doc_ids.as<uint32_t>();
-    rp.q = dQp;
+    rp.q = dQ;
     rp.qnorm = ts.d_qnorm.as<float>();
-    rp.slot_q = d_slotq;
+    rp.slot_q = nullptr;
     rp.dim_pad = ix->dim_pad;
     rp.k = k;
     rp.kp = kp;
@@ -411,7 +606,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     rp.out_key = out.out_key;
     rp.out_count = out.out_count;
     rp.uncertain = ts.d_flags.as<int32_t>();
-    RK_CUDA(rk_launch_rescore(rp, (int) nslots, st));
+    RK_CUDA(rk_launch_rescore(rp, (int) nq, st));
+    launches++;
     if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ev[3], st)); ws.timed_select = true; }
     int32_t *hflags = ts.h_flags.as<int32_t>();
     RK_CUDA(cudaMemcpyAsync(hflags, ts.d_flags.p, nq * 4, cudaMemcpyDeviceToHost, st));
@@ -419,17 +615,15 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     for (size_t q = 0; q < nq; q++)
         if (hflags[q]) redo.push_back((uint32_t) q);
 
-    ws.launches += 7;
-    ws.segments = nunits;
-    uint64_t tile_visits = 0, unique_tiles = 0;
-    for (auto &g : groups) { tile_visits += (uint64_t) g.tl_n * ((g.queries.size() + 127) / 128); unique_tiles += g.tl_n; }
+    ws.launches += launches;
+    ws.segments = pm_.units.size() + ps_.units.size();
+    const uint64_t tile_visits = (uint64_t) (pm_.tile_visits + 0.5);
     ws.rows_scanned = tile_visits * 128;
     // bytes this plan must move: every visited tile once per query tile, plus the queries
     ws.algo_bytes = (uint64_t) ix->dim_pad * 4ull * (tile_visits * 128ull + nslots);
     ts.last_flop = 2.0 * (double) ix->dim * 128.0 * (double) tile_visits * 128.0;
     ts.last_redo = (uint32_t) redo.size();
     ts.last_exact = exact;
-    ts.last_grouped = grouped;
-    (void) unique_tiles;
+    ts.last_plan = (int) plan;
     return RK_OK;
 }
