@@ -82,7 +82,8 @@ typedef enum rk_layout { RK_LAYOUT_AUTO = 0, RK_LAYOUT_ROLE = 1, RK_LAYOUT_COMBI
  *                     epilogue; nominates candidates in TF32, re-scores them in exact fp32 and falls
  *                     back to the scan for any query whose answer it cannot prove.  Results are
  *                     identical to RK_ENGINE_SCAN.  Exact scans only (probes = 0), k <= 256.
- *   RK_ENGINE_AUTO    currently RK_ENGINE_SCAN. */
+ *   RK_ENGINE_AUTO    RK_ENGINE_TENSOR for batches of 32 or more exact scans it supports (role,
+ *                     combination, bitmask or no filter), RK_ENGINE_SCAN otherwise. */
 typedef enum rk_engine { RK_ENGINE_AUTO = 0, RK_ENGINE_SCAN = 1, RK_ENGINE_TENSOR = 2 } rk_engine;
 
 #define RK_MAX_DIM 2048   /* pgvector IVFFLAT_MAX_DIM is 2000 (pgvector/src/ivfflat.h:24)          */
@@ -235,7 +236,10 @@ typedef struct rk_stats {
     uint64_t total_launches;   /* kernels launched since rk_open                                   */
     uint64_t tensor_redo;      /* RK_ENGINE_TENSOR: queries of the last batch re-run on the scan   */
     uint64_t tensor_exact;     /* RK_ENGINE_TENSOR: 1 = TF32 was exact for the last batch          */
-    uint64_t reserved[5];
+    uint64_t tensor_plan;      /* last batch: 0 = not on the tensor engine, 1 = dense, 2 = per user mask,
+                                  3 = per document class (atoms); +16 when the sampling pass ran      */
+    uint64_t tensor_flop;      /* last tensor batch: 2 * dim * 128 * 128 * tile visits (main pass)   */
+    uint64_t reserved[3];
 } rk_stats;
 int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */

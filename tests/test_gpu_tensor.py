@@ -70,3 +70,70 @@ def test_tensor_engine_unfiltered_and_small_visible_sets():
     with pytest.raises(vr.RkError):
         ix.search_batch(Q, users, 300, engine=vr.ENGINE_TENSOR)        # k > 256
     ix.close()
+
+
+@pytest.mark.parametrize("plan", ["dense", "grouped", "atoms"])
+def test_tensor_engine_plans_agree(plan, monkeypatch):
+    """Dense / per-user-mask / per-document-class (atoms) plans walk different tiles with different query
+    groupings; all must return the oracle's answer (a query appears in several atoms' units and its
+    lists are merged per query)."""
+    import vectorsearch_rbac_b200 as vr
+    monkeypatch.setenv("RK_TENSOR_PLAN", plan)
+    ds = make_dataset("sift", n=30000, dim=64, rows_per_doc=25, rbac="tree", num_users=60, num_roles=20)
+    ix = load_index(ds, k_max=256)
+    ix.finalize()
+    Q, users = _queries(ds, 200, seed=5)
+    users[3] = 999999                                  # unknown user
+    k = 50
+    got = ix.search_batch(Q, users, k, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_TENSOR)
+    exp = oracle_role_search(ds, Q, users, orc.METRIC_L2, k, mode="bitmask")
+    assert_topk_matches(got, exp, exact=True)
+    assert got[3][3] == 0
+    assert ix.stats()["tensor_plan"] & 15 == {"dense": 1, "grouped": 2, "atoms": 3}[plan]
+    ix.close()
+
+
+@pytest.mark.parametrize("kind,metric,flt", [("sift", 0, "none"), ("cohere", 1, "bitmask")])
+def test_tensor_engine_sampling_pass(kind, metric, flt, monkeypatch):
+    """The sampling pass seeds every unit's threshold with the kp-th best value of every S-th tile;
+    the answer must not change (thresholds are upper bounds), with and without it."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset(kind, n=60000, dim=32, rows_per_doc=50, rbac="random", num_users=20, num_roles=6)
+    ix = load_index(ds, metric=metric, role_parts=False, combo_parts=False, k_max=256)
+    ix.finalize()
+    Q, users = _queries(ds, 64, seed=9)
+    k = 10
+    f = vr.FILTER_NONE if flt == "none" else vr.FILTER_BITMASK
+    monkeypatch.setenv("RK_TENSOR_PLAN", "dense")
+    monkeypatch.setenv("RK_TENSOR_SAMPLE", "0")
+    base = ix.search_batch(Q, users, k, filter=f, engine=vr.ENGINE_TENSOR)
+    units0 = ix.stats()["segments"]
+    monkeypatch.setenv("RK_TENSOR_SAMPLE", "1")
+    monkeypatch.setenv("RK_TENSOR_SDIV", "4")          # sample every 4th.. tile already on this small corpus
+    monkeypatch.setenv("RK_TENSOR_SMIN", "64")
+    got = ix.search_batch(Q, users, k, filter=f, engine=vr.ENGINE_TENSOR)
+    assert ix.stats()["tensor_plan"] == 1 + 16         # dense plan, sampling pass ran
+    assert ix.stats()["segments"] > units0
+    for a, b in zip(got, base):
+        np.testing.assert_array_equal(a, b)
+    exp = oracle_role_search(ds, Q, users, metric, k, mode=flt)
+    assert_topk_matches(got, exp, exact=(kind == "sift"))
+    ix.close()
+
+
+def test_engine_auto_picks_tensor_for_batches():
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("sift", n=8000, dim=128, rows_per_doc=20, rbac="tree", num_users=30, num_roles=10)
+    ix = load_index(ds, k_max=128)
+    ix.finalize()
+    Q, users = _queries(ds, 64, seed=2)
+    got = ix.search_batch(Q, users, 20, filter=vr.FILTER_PARTITION, layout=vr.LAYOUT_ROLE)          # ENGINE_AUTO
+    assert ix.stats()["tensor_plan"] != 0                                         # went through the tensor engine
+    ref = ix.search_batch(Q, users, 20, filter=vr.FILTER_PARTITION, layout=vr.LAYOUT_ROLE, engine=vr.ENGINE_SCAN)
+    for a, b in zip(got, ref):
+        np.testing.assert_array_equal(a, b)
+    small = ix.search_batch(Q[:8], users[:8], 20, filter=vr.FILTER_BITMASK)      # below the batch threshold: scan
+    assert ix.stats()["tensor_plan"] == 0
+    for a, b in zip(small, [x[:8] for x in ref]):
+        np.testing.assert_array_equal(a, b)
+    ix.close()

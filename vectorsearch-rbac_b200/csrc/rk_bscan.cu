@@ -417,6 +417,11 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             uint32_t r0_cur = tile_row0(0), r0_next = tile_row0(1);
             float xn_n = 0.f;
             uint64_t ma_n = 0, mb_n = 0;
+            bool own_n = true;
+            // atoms plan: the unit nominates only rows of ITS document class (rows a tile drags in from
+            // other classes are some other unit's to nominate — no row is nominated twice)
+            const uint64_t *umask = (un.mask_id && p.unit_mask) ? p.unit_mask + (size_t) (un.mask_id - 1u) * W : nullptr;
+            const uint64_t um0 = umask ? umask[0] : 0ull, um1 = (umask && W > 1) ? umask[1] : 0ull;
             auto fetch_row = [&](uint32_t r0) {
                 const uint64_t rr = (uint64_t) r0 + (uint64_t) erow;
                 xn_n = 0.f; ma_n = 0; mb_n = 0;
@@ -426,6 +431,12 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         const ulonglong2 m2 = reinterpret_cast<const ulonglong2 *>(p.rowmask2)[rr];
                         ma_n = m2.x;
                         mb_n = m2.y;
+                        own_n = true;
+                        if (umask) {
+                            own_n = ma_n == um0 && mb_n == um1;
+                            for (int w = 2; w < W && own_n; w++) own_n = p.rowmask[rr * W + w] == umask[w];
+                            if (!own_n) { ma_n = 0; mb_n = 0; }
+                        }
                     } else {
                         ma_n = 1ull;                    // matches the all-ones query word
                     }
@@ -435,7 +446,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
-                const bool valid = row < p.nrows;
+                const bool valid = row < p.nrows && own_n;
                 const float xn = xn_n;
                 const uint32_t m0 = (uint32_t) ma_n, m1 = (uint32_t) (ma_n >> 32), m2 = (uint32_t) mb_n, m3 = (uint32_t) (mb_n >> 32);
                 // issue the next tile's loads now; they are consumed on the next iteration

@@ -103,7 +103,7 @@ struct RkBUnit {
     uint32_t tl_off;             // offset of the group's tile list in tile_rows[]
     uint32_t list_base;          // candidate list of slot q0 + i is list_base + i
     uint32_t tile_step;          // the unit visits tiles tile_begin, tile_begin + tile_step, ... (> 1: sampling pass)
-    uint32_t pad1;
+    uint32_t mask_id;            // > 0: nominate only rows whose role mask equals unit_mask[mask_id - 1] (atoms plan)
 };
 
 struct RkBScanParams {
@@ -127,6 +127,7 @@ struct RkBScanParams {
     // optional seed thresholds (sampling pass): slot s starts at tau_key[s * kp + kp - 1] when tau_count[s] >= kp
     const float *tau_key;
     const int32_t *tau_count;
+    const uint64_t *unit_mask;   // [masks][mask_words] exact row masks of the atoms plan's units (see RkBUnit::mask_id)
     const uint32_t *slot_q;      // slot -> query of the caller's batch (trunc[] is indexed by query); NULL = identity
 };
 
@@ -136,6 +137,7 @@ struct RkRescoreParams {
     const uint32_t *rowdoc, *doc_ids;
     const float *q;              // [slots][dim_pad] (group-ordered)
     const float *qnorm;
+    const uint64_t *unit_mask;   // [masks][mask_words] exact row masks of the atoms plan's units (see RkBUnit::mask_id)
     const uint32_t *slot_q;      // slot -> query index of the caller's batch (outputs are written there); NULL = identity
     int dim_pad, k, kp, metric, null_query;
     const float *sel_key;        // [nq][kp] approximate ordering values, ascending

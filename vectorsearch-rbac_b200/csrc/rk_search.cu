@@ -288,9 +288,16 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
     RK_CUDA(cudaSetDevice(ix->device));
     ws.launches = 0;
     ws.timed_scan = ws.timed_select = ws.timed_probe = false;
+    if (&ws == &ix->ws) ix->tensor.last_plan = 0;
     if (nq == 0) return RK_OK;
     if (o->probes > 0) return rk_ivf_search(ix, ws, nq, dQ, user_ids, o, probe_offset, out);
-    if (o->engine == RK_ENGINE_TENSOR) {
+    // RK_ENGINE_AUTO: a batch of 32 or more exact scans goes to the tensor engine (every row a group of
+    // queries shares is read once and scored on the tensor cores; measured crossover on the C3 shape is
+    // ~16 queries), anything smaller — and everything the tensor engine does not cover — is scanned.
+    // The dynamic layout stays on the scan: its partitions need not cover a user's whole visible set.
+    const bool auto_tensor = o->engine == RK_ENGINE_AUTO && nq >= 32 && &ws == &ix->ws && rk_tensor_supported(ix, o) &&
+                             !(o->filter == RK_FILTER_PARTITION && (o->layout == RK_LAYOUT_DYNAMIC || (o->layout == RK_LAYOUT_AUTO && !ix->roleset_parts.empty())));
+    if (o->engine == RK_ENGINE_TENSOR || auto_tensor) {
         if (!rk_tensor_supported(ix, o)) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR needs an exact scan (probes = 0), k <= 256, no keep_duplicates / NULL query");
         if (&ws != &ix->ws) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR is a batch engine (rk_search_batch*), not available on scan handles");
         std::vector<uint32_t> redo;
@@ -302,6 +309,7 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
         rk_scan_opts o2 = *o;
         o2.engine = RK_ENGINE_SCAN;
         const uint64_t tl = ws.launches;
+        const int plan_used = ix->tensor.last_plan;
         if (redo.size() * 4 > nq) {
             rc = search_device(ix, ws, nq, dQ, user_ids, &o2, 0, out);
         } else {
@@ -319,6 +327,7 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
             }
         }
         ws.launches += tl;
+        ix->tensor.last_plan = plan_used;
         return rc;
     }
 
@@ -637,5 +646,7 @@ extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)
     out->total_launches = ix->total_launches;
     out->tensor_redo = ix->tensor.last_redo;
     out->tensor_exact = ix->tensor.last_exact ? 1 : 0;
+    out->tensor_plan = (uint64_t) ix->tensor.last_plan;
+    out->tensor_flop = (uint64_t) ix->tensor.last_flop;
     return RK_OK;
 }

@@ -142,6 +142,7 @@ struct TGroup {
     const UserInfo *user = nullptr;
     uint32_t tl_off = 0, tl_n = 0;
     uint64_t min_visible = 0;      // fewest rows any query of the group can see
+    const std::vector<uint64_t> *own_mask = nullptr;   // atoms plan: the document class the group's units may nominate
 };
 
 // One launch of the scoring kernel: units, their balanced assignment to CTAs, and which candidate
@@ -223,6 +224,7 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
                 u.tile_end = hi == visits ? g.tl_n : hi * st;
                 u.tile_step = st;
                 u.tl_off = g.tl_off;
+                u.mask_id = g.own_mask ? (uint32_t) gi + 1u : 0u;
                 u.list_base = ps.list_total;
                 ps.list_total += qn * LPQ;
                 ps.units.push_back(u);
@@ -336,6 +338,12 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
             }
             if (cost_a < 0.9 * best) { best = cost_a; plan = PLAN_ATOMS; }
         }
+        // test aid: RK_TENSOR_PLAN=dense|grouped|atoms forces a plan (all three give the same answers)
+        if (const char *force = getenv("RK_TENSOR_PLAN")) {
+            if (!strcmp(force, "dense")) plan = PLAN_DENSE;
+            else if (!strcmp(force, "grouped")) plan = PLAN_GROUPED;
+            else if (!strcmp(force, "atoms") && !ts.atoms.empty()) plan = PLAN_ATOMS;
+        }
     }
     const bool per_slot_mask = plan != PLAN_GROUPED;       // which mask a slot carries: its query's own, or the group's
     if (plan == PLAN_DENSE && groups.size() > 1) {
@@ -360,6 +368,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
             TGroup g;
             g.tl_off = ts.atoms[a].tl_off; g.tl_n = ts.atoms[a].tl_n;
             g.min_visible = ts.atoms[a].rows;
+            g.own_mask = &ts.atoms[a].mask;
             for (uint32_t gi : atom_groups[a]) g.queries.insert(g.queries.end(), groups[gi].queries.begin(), groups[gi].queries.end());
             ag.push_back(std::move(g));
         }
@@ -388,11 +397,14 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // balance wants.
     std::vector<uint32_t> step_main(groups.size(), 1), step_sample(groups.size(), 0);
     bool sampled = false;
-    static const int env_sample = getenv("RK_TENSOR_SAMPLE") ? atoi(getenv("RK_TENSOR_SAMPLE")) : 1;    // tuning aid: 0 disables the sampling pass
-    static const int env_sdiv = getenv("RK_TENSOR_SDIV") ? atoi(getenv("RK_TENSOR_SDIV")) : 400;
+    // test / tuning aids: RK_TENSOR_SAMPLE=0 disables the sampling pass, RK_TENSOR_SDIV and RK_TENSOR_SMIN move
+    // the point where it starts to pay (parity tests use them to exercise it on small corpora)
+    const int env_sample = getenv("RK_TENSOR_SAMPLE") ? atoi(getenv("RK_TENSOR_SAMPLE")) : 1;
+    const int env_sdiv = getenv("RK_TENSOR_SDIV") ? std::max(1, atoi(getenv("RK_TENSOR_SDIV"))) : 400;
+    const uint32_t env_smin = getenv("RK_TENSOR_SMIN") ? (uint32_t) std::max(1, atoi(getenv("RK_TENSOR_SMIN"))) : 1024u;
     for (size_t gi = 0; gi < groups.size() && env_sample; gi++) {
         const TGroup &g = groups[gi];
-        if (g.tl_n < 1024) continue;
+        if (g.tl_n < env_smin) continue;
         // about 1 in 400 of the (visible row, query) pairs should survive the seeded threshold: kp S / visible
         const uint64_t S = std::min<uint64_t>(64, g.min_visible / ((uint64_t) env_sdiv * (uint64_t) kp));
         if (S >= 4) { step_sample[gi] = (uint32_t) S; sampled = true; }
@@ -414,7 +426,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // ---- staging: per pass [units][cta_off][cta_units][lid0][lstep][nlists], then [slot_q][qoff][qlist][qmask per slot]
     const size_t b_slot = nslots * 4, b_qmask = nslots * (size_t) W * 8;
     auto pass_bytes = [&](const TPass &t) { return t.units.size() * sizeof(RkBUnit) + (t.cta_off.size() + t.cta_units.size()) * 4 + 3 * b_slot + 128; };
-    const size_t total_stage = pass_bytes(pm_) + (sampled ? pass_bytes(ps_) : 0) + b_slot + (qoff.size() + qlist.size()) * 4 + b_qmask + 256;
+    const size_t total_stage = pass_bytes(pm_) + (sampled ? pass_bytes(ps_) : 0) + b_slot + (qoff.size() + qlist.size()) * 4 + b_qmask +
+                               groups.size() * (size_t) W * 8 + 256;
     ws.plan_idx ^= 1;
     const int pi_ = ws.plan_idx;
     if (ws.ev_plan_used[pi_]) RK_CUDA(cudaEventSynchronize(ws.ev_plan[pi_]));
@@ -439,6 +452,13 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     };
     stage_pass(pm_);
     if (sampled) stage_pass(ps_);
+    size_t o_umask = 0;
+    if (plan == PLAN_ATOMS) {
+        std::vector<uint64_t> um(groups.size() * (size_t) W);
+        for (size_t gi = 0; gi < groups.size(); gi++)
+            for (int w = 0; w < W; w++) um[gi * W + w] = (*groups[gi].own_mask)[(size_t) w];
+        o_umask = put(um.data(), um.size() * 8);
+    }
     const size_t o_slotq = put(slot_q.data(), b_slot);
     const size_t o_qoff = put(qoff.data(), qoff.size() * 4);
     const size_t o_qlist = put(qlist.data(), qlist.size() * 4);
@@ -507,6 +527,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     bp.qnorm = nullptr;
     bp.qmask = reinterpret_cast<const uint64_t *>(dplan + o_qmask);
     bp.slot_q = d_slotq;
+    bp.unit_mask = plan == PLAN_ATOMS ? reinterpret_cast<const uint64_t *>(dplan + o_umask) : nullptr;
     bp.scratch = ts.d_scratch.as<uint2>();
     bp.cand_key = ts.d_cand_key.as<uint32_t>();
     bp.cand_row = ts.d_cand_row.as<uint32_t>();
@@ -624,6 +645,6 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     ts.last_flop = 2.0 * (double) ix->dim * 128.0 * (double) tile_visits * 128.0;
     ts.last_redo = (uint32_t) redo.size();
     ts.last_exact = exact;
-    ts.last_plan = (int) plan;
+    ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0);
     return RK_OK;
 }
