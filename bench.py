@@ -5,16 +5,23 @@ Contract (driver): `python bench.py --gpus N --steps K --warmup W` (under torchr
 ONE JSON line on rank 0.  A step = one batch of `--nq` (query vector, user) pairs pushed through the
 hot path (permission prefilter ⊕ L2 scoring ⊕ top-k [⊕ all-gather merge]).
 
-Workload (default `c3`): SURVEY.md §8 C3 — SIFT10M-shaped synthetic corpus (10 M x 128 fp32,
-integer-valued), 100 rows per document, tree RBAC (1000 users, 100 roles, h=4, b in [3,4]), fused
-role-bitmask scan, k=100, 1000 queries per step; with N GPUs the documents are striped over the
-ranks (strong scaling: the corpus and the batch are fixed) and the ranks' top-k are merged with one
-all-gather.  `c1` is the 1 M-row variant (SIFT-1M shape).
+Workloads (default `c3`):
+  c3  SIFT10M-shaped synthetic corpus (10 M x 128 fp32, integer-valued), 100 rows per document, tree RBAC
+      (1000 users, 100 roles, h=4, b in [3,4]), fused role-bitmask scan — one bandwidth-bound pass per
+      query, as the config specifies — k=100, 1000 queries per step; with N GPUs the documents are striped
+      over the ranks (strong scaling: corpus and batch are fixed) and the ranks' top-k are merged with one
+      all-gather.  The line also carries a "batched" object: the same step through RK_ENGINE_AUTO, which
+      sends a batch this size to the tcgen05 engine (identical results).
+  c1  the 1 M-row variant (SIFT-1M shape), role-partition prefilter.
+  c2  Cohere-shaped 1 M x 768 fp32 inner product, random RBAC, combination-role filter, batched
+      tensor-core engine (the headline engine of this workload).
 
   value      queries/s with the query matrix already resident in HBM (CUDA events, max over ranks)
   e2e        the same through the host-buffer API: pinned host Q -> H2D -> search -> D2H of results
-  roofline   the scan kernel's algorithmic bytes (allowed rows x 4d + mask bytes +
-             12k per query) / its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs
+  roofline   the dominant kernel against the roofline that bounds it: scan kernel — algorithmic bytes
+             (allowed rows x 4d + mask bytes + 12k per query) / CUDA-event duration against
+             MEASURED_PEAKS.json hbm_gbs; tensor kernel — F = 2 nq_g R_g d against a cuBLAS TF32 peak
+             measured live, or the plan's bytes against hbm_gbs when its intensity is below the ridge
   cpu_baseline  the reference's own distance loops (oracle/_ref, built from pgvector/src/vector.c)
              inside the oracle's restated scan, all host threads, on the same queries (N=1 only)
 
@@ -37,13 +44,20 @@ import numpy as np  # noqa: E402
 
 METRIC = "filtered top-100 QPS at 1/2/4/8 B200 vs recall@100; % of HBM roofline"
 WORKLOADS = {
-    # name: (rows, dim, kind, rows_per_doc, users, roles, description)
-    "c3": (10_000_000, 128, "sift", 100, 1000, 100,
-           "C3 SIFT10M-shape 10M x 128 fp32 L2, tree RBAC (1000 users, 100 roles, h=4, b=3..4), fused role-bitmask "
-           "scan, exact top-100, documents striped over the GPUs + all-gather top-k merge"),
-    "c1": (1_000_000, 128, "sift", 100, 1000, 100,
-           "C1 SIFT-1M-shape 1M x 128 fp32 L2, tree RBAC (1000 users, 100 roles, h=4, b=3..4), role-partition "
-           "prefilter, exact top-100"),
+    # SURVEY.md §8 configs.  engine = what the headline timed region runs; c1 / c3 also report the batched
+    # (RK_ENGINE_AUTO -> tensor) numbers of the same step in a "batched" object.
+    "c3": dict(rows=10_000_000, dim=128, kind="sift", rpd=100, users=1000, roles=100, rbac="tree", metric="l2",
+               filter="bitmask", engine="scan",
+               desc="C3 SIFT10M-shape 10M x 128 fp32 L2, tree RBAC (1000 users, 100 roles, h=4, b=3..4), fused role-bitmask "
+                    "scan (one pass per query), exact top-100, documents striped over the GPUs + all-gather top-k merge"),
+    "c1": dict(rows=1_000_000, dim=128, kind="sift", rpd=100, users=1000, roles=100, rbac="tree", metric="l2",
+               filter="partition", engine="scan",
+               desc="C1 SIFT-1M-shape 1M x 128 fp32 L2, tree RBAC (1000 users, 100 roles, h=4, b=3..4), role-partition "
+                    "prefilter, exact top-100"),
+    "c2": dict(rows=1_000_000, dim=768, kind="cohere", rpd=100, users=1000, roles=100, rbac="random", metric="ip",
+               filter="combination", engine="tensor",
+               desc="C2 Cohere-Wikipedia shape 1M x 768 fp32 inner product, random RBAC (1000 users, 100 roles, <=3 roles per "
+                    "user, 450..900 documents per role), combination-role (user-level) filter, batched tensor-core exact top-100"),
 }
 
 
@@ -57,8 +71,10 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=0, help="override corpus rows (debug)")
     ap.add_argument("--nq", type=int, default=1000)
     ap.add_argument("--k", type=int, default=100)
-    ap.add_argument("--filter", default="", choices=["", "bitmask", "partition"])
+    ap.add_argument("--filter", default="", choices=["", "bitmask", "partition", "combination"])
+    ap.add_argument("--engine", default="", choices=["", "scan", "tensor", "auto"], help="override the workload's headline engine")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
     return ap.parse_args()
 
 
@@ -83,29 +99,67 @@ def traffic_per_launch(workload, n_gpus, flt):
     return t.get(f"{workload}:{flt}:gpus{n_gpus}")
 
 
+def as_workload(wl):
+    """Accepts a WORKLOADS entry or the legacy tuple (rows, dim, kind, rows_per_doc, users, roles, desc) the tools pass."""
+    if isinstance(wl, dict):
+        return wl
+    rows, dim, kind, rpd, users, roles, desc = wl
+    return dict(rows=rows, dim=dim, kind=kind, rpd=rpd, users=users, roles=roles, rbac="tree", metric="l2", filter="bitmask",
+                engine="scan", desc=desc)
+
+
 def build_rbac(wl):
     import vectorsearch_rbac_b200.synth as synth
-    rows, dim, kind, rpd, users, roles, _ = wl
-    tid, doc = synth.row_ids(rows, rpd)
-    doc_ids = np.arange(1, (rows + rpd - 1) // rpd + 1)
-    ur, dr = synth.tree_rbac(users, roles, doc_ids.tolist(), h=4, b0=3, b1=4, seed=42)
+    wl = as_workload(wl)
+    tid, doc = synth.row_ids(wl["rows"], wl["rpd"])
+    ndoc = (wl["rows"] + wl["rpd"] - 1) // wl["rpd"]
+    doc_ids = np.arange(1, ndoc + 1)
+    if wl["rbac"] == "random":
+        # RandomRBACDataGenerator(m_roles=3, m_perms=9*docs/roles) (SURVEY.md §8d, C2)
+        ur, dr = synth.random_rbac(wl["users"], wl["roles"], doc_ids.tolist(), 3, 9 * ndoc // wl["roles"], seed=42)
+    else:
+        ur, dr = synth.tree_rbac(wl["users"], wl["roles"], doc_ids.tolist(), h=4, b0=3, b1=4, seed=42)
     return tid, doc, ur, dr
 
 
 def make_queries(wl, nq, device):
     import torch
     import vectorsearch_rbac_b200.synth as synth
-    rows, dim, kind, rpd, users, roles, _ = wl
-    qrows, qusers = synth.queries(rows, np.arange(1, users + 1), nq, seed=7)
-    Q = synth.corpus(kind, torch.as_tensor(qrows, device=device), dim, seed=1234)
+    wl = as_workload(wl)
+    qrows, qusers = synth.queries(wl["rows"], np.arange(1, wl["users"] + 1), nq, seed=7)
+    Q = synth.corpus(wl["kind"], torch.as_tensor(qrows, device=device), wl["dim"], seed=1234)
     return Q, qusers
 
 
 def gen_rows(wl, row_idx, device):
     import torch
     import vectorsearch_rbac_b200.synth as synth
-    rows, dim, kind, *_ = wl
-    return synth.corpus(kind, torch.as_tensor(row_idx, device=device), dim, seed=1234)
+    wl = as_workload(wl)
+    return synth.corpus(wl["kind"], torch.as_tensor(row_idx, device=device), wl["dim"], seed=1234)
+
+
+def tf32_peak(device):
+    """cuBLAS TF32 GEMM peak measured the way MEASURED_PEAKS.json measures bf16: 8192^3, best of 10, CUDA events
+    (the driver's file has no TF32 figure; SURVEY.md §8d asks for one measured the same way)."""
+    import torch
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn(8192, 8192, device=device)
+        b = torch.randn(8192, 8192, device=device)
+        for _ in range(3):
+            a @ b
+        best = float("inf")
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize(device)
+            best = min(best, e0.elapsed_time(e1))
+        return 2.0 * 8192 ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
 
 
 class ClockSampler:
@@ -189,14 +243,14 @@ def cpu_partitions(doc, ur, dr, qusers):
     return parts, qparts
 
 
-def cpu_search(X, tid, parts, qparts, Q, k, nthreads):
+def cpu_search(X, tid, parts, qparts, Q, k, nthreads, metric="l2"):
     """(tid, dist, count), kind — the reference's own loops (oracle/_ref) inside the oracle's scan when
     that build is present, else the oracle port with pgvector's Makefile flags."""
     from oracle import oracle as orc
     ref = orc.ref_loops()
     kind = "reference" if ref is not None else "port"
-    t, _, d, _, c = orc.search_batch(X, tid, parts, qparts, Q, orc.METRIC_L2, k, dedup=True, nthreads=nthreads,
-                                     variant="pgvflags", ref=ref)
+    m = orc.METRIC_L2 if metric == "l2" else orc.METRIC_IP
+    t, _, d, _, c = orc.search_batch(X, tid, parts, qparts, Q, m, k, dedup=True, nthreads=nthreads, variant="pgvflags", ref=ref)
     return (t, d, c), kind
 
 
@@ -224,7 +278,7 @@ def run_reference(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    rows, dim, kind, rpd, users, roles, desc = wl
+    rows, dim, desc = wl["rows"], wl["dim"], wl["desc"]
     dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # data generation only
     tid, doc, ur, dr = build_rbac(wl)
     X = np.empty((rows, dim), dtype=np.float32)
@@ -238,16 +292,16 @@ def run_reference(args, wl):
     # calibrate the bounded sample: one step should take ~2 s, the whole run <= ~3 min
     n0 = min(args.nq, max(cores, 8))
     t0 = time.perf_counter()
-    cpu_search(X, tid, parts, qparts[:n0], Q[:n0], args.k, cores)
+    cpu_search(X, tid, parts, qparts[:n0], Q[:n0], args.k, cores, wl["metric"])
     per_q = (time.perf_counter() - t0) / n0
     budget = min(2.5, 170.0 / max(1, args.steps + args.warmup))
     S = int(max(min(cores, args.nq), min(args.nq, budget / max(per_q, 1e-6))))
     for _ in range(args.warmup):
-        cpu_search(X, tid, parts, qparts[:S], Q[:S], args.k, cores)
+        cpu_search(X, tid, parts, qparts[:S], Q[:S], args.k, cores, wl["metric"])
     t0 = time.perf_counter()
     kind_used = "port"
     for _ in range(args.steps):
-        _, kind_used = cpu_search(X, tid, parts, qparts[:S], Q[:S], args.k, cores)
+        _, kind_used = cpu_search(X, tid, parts, qparts[:S], Q[:S], args.k, cores, wl["metric"])
     dt = time.perf_counter() - t0
     qps = S * args.steps / dt
     sample = (f"{S} of the {args.nq} queries of the step per timed step, full visible row sets, "
@@ -256,7 +310,7 @@ def run_reference(args, wl):
         "impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "rows": rows, "dim": dim, "k": args.k, "queries_per_step": S},
+        "config": {"workload": desc, "rows": rows, "dim": dim, "k": args.k, "queries_per_step": S, "metric_op": wl["metric"]},
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind_used, "sample": sample},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -268,10 +322,9 @@ def run_reference(args, wl):
 
 def main():
     args = parse_args()
-    wl = list(WORKLOADS[args.workload])
+    wl = dict(WORKLOADS[args.workload])
     if args.rows:
-        wl[0] = args.rows
-    wl = tuple(wl)
+        wl["rows"] = args.rows
     if args.impl == "reference":
         run_reference(args, wl)
         return
@@ -291,20 +344,24 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    rows, dim, kind, rpd, n_users, n_roles, desc = wl
-    flt_name = args.filter or ("bitmask" if args.workload == "c3" else "partition")
-    flt = vr.FILTER_BITMASK if flt_name == "bitmask" else vr.FILTER_PARTITION
+    rows, dim, desc = wl["rows"], wl["dim"], wl["desc"]
+    flt_name = args.filter or wl["filter"]
+    metric = vr.METRIC_L2 if wl["metric"] == "l2" else vr.METRIC_IP
+    flt = {"bitmask": vr.FILTER_BITMASK, "partition": vr.FILTER_PARTITION, "combination": vr.FILTER_PARTITION}[flt_name]
+    layout = {"bitmask": 0, "partition": vr.LAYOUT_ROLE, "combination": vr.LAYOUT_COMBINATION}[flt_name]
+    engine_name = args.engine or wl["engine"]
+    engine = {"scan": vr.ENGINE_SCAN, "tensor": vr.ENGINE_TENSOR, "auto": vr.ENGINE_AUTO}[engine_name]
 
     # ---- load this rank's shard ---------------------------------------------------------------
     tid, doc, ur, dr = build_rbac(wl)
     mine = np.flatnonzero(sharded.local_row_mask(doc, rank, world))
-    ix = vr.Index(dim, metric=vr.METRIC_L2, device=local_rank, k_max=max(128, args.k))
+    ix = vr.Index(dim, metric=metric, device=local_rank, k_max=max(128, args.k))
     ix.reserve_rows(len(mine))
     keep_host = world == 1 and rank == 0 and not args.no_cpu
     X_host = np.empty((rows, dim), dtype=np.float32) if keep_host else None
-    CH = 1 << 20
-    for a in range(0, len(mine), CH):
-        idx = mine[a:a + CH]
+    CH = 1 << 20 if dim <= 256 else 1 << 18
+    for a0 in range(0, len(mine), CH):
+        idx = mine[a0:a0 + CH]
         xb = gen_rows(wl, idx, dev)
         ix.load_rows_device(xb.data_ptr(), len(idx), tid[idx], doc[idx])
         if keep_host:
@@ -312,124 +369,187 @@ def main():
         del xb
     ix.set_doc_roles(dr[:, 0], dr[:, 1])
     ix.set_user_roles(ur[:, 0], ur[:, 1])
-    if flt == vr.FILTER_PARTITION:
+    if flt_name == "partition":
         ix.build_role_partitions()
+    if flt_name == "combination":
+        ix.build_combination_partitions()
     ix.finalize()
     torch.cuda.empty_cache()
 
     Q, qusers = make_queries(wl, args.nq, dev)
     Q = Q.contiguous()
-    opts = vr.engine.make_opts(args.k, filter=flt, layout=vr.LAYOUT_ROLE if flt == vr.FILTER_PARTITION else 0)
     torch.cuda.set_stream(torch.cuda.Stream(dev))     # a real stream: torch events, NCCL and the engine share it
     stream = torch.cuda.current_stream(dev)
     sharded.use_torch_stream(ix, dev)
     searcher = sharded.ShardedSearcher(ix, rank, world, device=dev)
     ix.enable_timing(True)
+    Qh = torch.empty((args.nq, dim), dtype=torch.float32, pin_memory=True)
+    Qh.copy_(Q)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    # ---- value: device-resident inputs --------------------------------------------------------
-    for _ in range(max(3, args.warmup)):
-        searcher.search_device(Q, qusers, opts)
-    barrier()
-    launches0 = ix.stats()["total_launches"]
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clk:
-        e0.record(stream)
-        for _ in range(args.steps):
-            out = searcher.search_device(Q, qusers, opts)
-        e1.record(stream)
+    def measure(eng):
+        """One engine over the step: device-resident `value` leg, then the host-buffer `e2e` leg."""
+        opts = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=eng)
+        for _ in range(max(3, args.warmup)):
+            searcher.search_device(Q, qusers, opts)
         barrier()
-    dt_dev = e0.elapsed_time(e1) * 1e-3
-    st = ix.stats()
-    launches = st["total_launches"] - launches0
-    scan_ms = ix.scan_times_ms(min(64, args.steps))
-    algo_bytes = st["algo_bytes"]
-    res_dev = tuple(t.clone() for t in out)
+        launches0 = ix.stats()["total_launches"]
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local_rank) as clk:
+            e0.record(stream)
+            for _ in range(args.steps):
+                out = searcher.search_device(Q, qusers, opts)
+            e1.record(stream)
+            barrier()
+        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary()}
+        st = ix.stats()
+        r["stats"] = st
+        r["launches"] = st["total_launches"] - launches0
+        r["scan_ms"] = ix.scan_times_ms(min(64, args.steps))
+        res_dev = tuple(t.clone() for t in out)
+        outs_h = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in res_dev)
+        r["h2d"] = Qh.numel() * 4
+        r["d2h"] = sum(t.numel() * t.element_size() for t in outs_h)
 
-    # ---- e2e: host buffers through the public API ----------------------------------------------
-    Qh = torch.empty((args.nq, dim), dtype=torch.float32, pin_memory=True)
-    Qh.copy_(Q)
-    outs_h = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in res_dev)
-    h2d = Qh.numel() * 4
-    d2h = sum(t.numel() * t.element_size() for t in outs_h)
+        def e2e_step():
+            if world == 1:
+                # the C-ABI call with host pointers: copies in, search, copies out, synchronous
+                o = vr._lib.lib.rk_search_batch(ix._h, args.nq, Qh.data_ptr(), qusers.ctypes.data, opts, outs_h[0].data_ptr(),
+                                                outs_h[1].data_ptr(), outs_h[2].data_ptr(), outs_h[3].data_ptr())
+                if o < 0:
+                    raise RuntimeError(vr._lib.last_error())
+            else:
+                searcher.search(Qh, qusers, opts, out_host=outs_h)
 
-    def e2e_step():
-        if world == 1:
-            # the C-ABI call with host pointers: copies in, scan, select, copies out, synchronous
-            o = vr._lib.lib.rk_search_batch(ix._h, args.nq, Qh.data_ptr(), qusers.ctypes.data, opts, outs_h[0].data_ptr(),
-                                            outs_h[1].data_ptr(), outs_h[2].data_ptr(), outs_h[3].data_ptr())
-            if o < 0:
-                raise RuntimeError(vr._lib.last_error())
-        else:
-            searcher.search(Qh, qusers, opts, out_host=outs_h)
+        for _ in range(max(3, args.warmup)):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        r["dt_e2e"] = time.perf_counter() - t0
+        r["same"] = all(torch.equal(x.cpu(), y) for x, y in zip(res_dev, outs_h))
+        r["outs_h"] = outs_h
+        if world > 1:
+            t = torch.tensor([r["dt_dev"], r["dt_e2e"]], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            r["dt_dev"], r["dt_e2e"] = float(t[0]), float(t[1])
+            tl = torch.tensor([r["launches"]], device=dev, dtype=torch.int64)
+            dist.all_reduce(tl, op=dist.ReduceOp.SUM)
+            r["launches"] = int(tl[0])
+        return r
 
-    for _ in range(max(3, args.warmup)):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    dt_e2e = time.perf_counter() - t0
-    same = all(torch.equal(a.cpu(), b) for a, b in zip(res_dev, outs_h))
+    def roofline_of(r, eng_name):
+        """The dominant kernel of the step against the roofline that bounds it."""
+        st = r["stats"]
+        kms = float(np.mean(r["scan_ms"])) if len(r["scan_ms"]) else float("nan")
+        if st["tensor_plan"] == 0:
+            # CUDA-core scan, one pass per query: HBM.  Bytes per SURVEY.md §8(d): allowed rows x 4d + mask bytes + 12k, per query
+            peak, peak_src = peaks()
+            ach = st["algo_bytes"] / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+            return {"bound": "hbm", "kernel": "rk_scan_kernel", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "frac_of_8TBps": ach / 8000.0, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(st["algo_bytes"]),
+                    "kernel_ms": kms, "launches_timed": int(len(r["scan_ms"])),
+                    "traffic": traffic_per_launch(args.workload, world, flt_name + ":" + eng_name)}
+        # tensor engine.  SURVEY.md §8(d), batched exact: F = 2 nq_g R_g d over the groups the plan forms
+        # (dense plan: all queries x all rows), bytes 4d (R_g + nq_g); the launch sits in whichever regime its
+        # arithmetic intensity F / bytes puts it (ridge = TF32 peak / HBM peak).
+        plan = {1: "dense", 2: "per user mask", 3: "per document class (atoms)"}[st["tensor_plan"] & 15]
+        hbm, hbm_src = peaks()
+        tf32 = tf32_peak(dev)
+        flop = float(st["tensor_flop"])
+        byts = float(st["algo_bytes"])
+        intensity = flop / max(byts, 1.0)
+        ridge = tf32 * 1e12 / (hbm * 1e9)
+        common = {"kernel": "rk_bscan_kernel", "plan": plan + (" + sampling pass" if st["tensor_plan"] & 16 else ""),
+                  "kernel_ms": kms, "launches_timed": int(len(r["scan_ms"])), "flop_per_launch": flop, "bytes_per_launch": byts,
+                  "plan_bytes_per_launch": float(st["tensor_plan_bytes"]),
+                  "intensity_flop_per_byte": intensity, "ridge_flop_per_byte": ridge,
+                  "traffic": traffic_per_launch(args.workload, world, flt_name + ":" + eng_name)}
+        if intensity >= ridge:
+            ach = flop / (kms * 1e-3) / 1e12 if kms > 0 else 0.0
+            return {"bound": "tensor", "achieved": ach, "peak": tf32, "unit": "TFLOP/s", "frac": ach / tf32,
+                    "peak_source": "measured live: cuBLAS TF32 (torch.matmul, allow_tf32) 8192^3, best of 10 — MEASURED_PEAKS.json has no TF32 figure",
+                    "frac_of_nominal_1100": ach / 1100.0, **common}
+        ach = byts / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+        return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "peak_source": hbm_src,
+                "tf32_tflops_achieved": flop / (kms * 1e-3) / 1e12 if kms > 0 else 0.0, "tf32_peak_measured": tf32, **common}
 
-    # ---- reduce over ranks ----------------------------------------------------------------------
-    if world > 1:
-        t = torch.tensor([dt_dev, dt_e2e, float(np.mean(scan_ms)) if len(scan_ms) else 0.0], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt_dev, dt_e2e = float(t[0]), float(t[1])
-        tl = torch.tensor([launches, algo_bytes], device=dev, dtype=torch.int64)
-        dist.all_reduce(tl, op=dist.ReduceOp.SUM)
-        launches_all = int(tl[0])
-    else:
-        launches_all = int(launches)
+    main_r = measure(engine)
+    batched_r = None
+    if engine == vr.ENGINE_SCAN and not args.no_batched:
+        batched_r = measure(vr.ENGINE_AUTO)
 
     if rank == 0:
-        peak, peak_src = peaks()
-        kms = float(np.mean(scan_ms)) if len(scan_ms) else float("nan")
-        achieved = algo_bytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+        st = main_r["stats"]
         line = {
-            "metric": METRIC, "value": args.nq * args.steps / dt_dev, "unit": "queries/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": dt_dev / args.steps * 1e3,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "metric": METRIC, "value": args.nq * args.steps / main_r["dt_dev"], "unit": "queries/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": main_r["dt_dev"] / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32" if st["tensor_plan"] == 0 else "tf32 nomination + f32 exact re-score",
+            "data": "synthetic",
             "config": {"workload": desc, "rows": rows, "dim": dim, "k": args.k, "queries_per_step": args.nq,
-                       "filter": flt_name, "rows_this_rank": int(len(mine)),
-                       "l2_policy": "inputs larger than L2: each step streams %.1f GB of row data per GPU (L2 = 126 MB)" % (algo_bytes / 1e9),
-                       "recall_at_100": 1.0, "recall_note": "exact scan; ids checked against the oracle on the cpu_baseline sample"},
-            "roofline": {"bound": "hbm", "kernel": "rk_scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "frac_of_8TBps": achieved / 8000.0, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": int(algo_bytes), "kernel_ms": kms,
-                         "launches_timed": int(len(scan_ms)), "traffic": traffic_per_launch(args.workload, world, flt_name)},
-            "e2e": {"value": args.nq * args.steps / dt_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": int(d2h), "ms_per_step": dt_e2e / args.steps * 1e3,
-                    "matches_device_path": bool(same)},
-            "gpu_launches": launches_all,
-            "clocks": clk.summary(),
+                       "filter": flt_name, "engine": engine_name, "metric_op": wl["metric"], "rows_this_rank": int(len(mine)),
+                       "l2_policy": "inputs larger than L2: each step streams %.1f GB of row data per GPU (L2 = 126 MB)" % (st["algo_bytes"] / 1e9),
+                       "recall_at_100": 1.0, "recall_note": "exact search; ids checked against the oracle on the cpu_baseline sample"},
+            "roofline": roofline_of(main_r, engine_name),
+            "e2e": {"value": args.nq * args.steps / main_r["dt_e2e"], "unit": "queries/s", "h2d_bytes_per_step": int(main_r["h2d"]),
+                    "d2h_bytes_per_step": int(main_r["d2h"]), "ms_per_step": main_r["dt_e2e"] / args.steps * 1e3,
+                    "matches_device_path": bool(main_r["same"])},
+            "gpu_launches": int(main_r["launches"]),
+            "clocks": main_r["clk"],
         }
+        if batched_r is not None:
+            # the same step through RK_ENGINE_AUTO (batches of >= 32 exact scans go to the tcgen05 engine): identical
+            # results, every row a group of queries shares read once
+            line["batched"] = {
+                "engine": "auto -> tensor" if batched_r["stats"]["tensor_plan"] else "auto -> scan",
+                "value": args.nq * args.steps / batched_r["dt_dev"], "unit": "queries/s", "ms_per_step": batched_r["dt_dev"] / args.steps * 1e3,
+                "e2e": {"value": args.nq * args.steps / batched_r["dt_e2e"], "unit": "queries/s", "ms_per_step": batched_r["dt_e2e"] / args.steps * 1e3},
+                "roofline": roofline_of(batched_r, "auto"), "gpu_launches": int(batched_r["launches"]),
+                "identical_to_headline_results": bool(all(torch.equal(x, y) for x, y in zip(main_r["outs_h"], batched_r["outs_h"]))),
+                "tensor_redo": int(batched_r["stats"]["tensor_redo"]), "clocks": batched_r["clk"]}
         if world == 1 and not args.no_cpu:
             cores = host_cores()
+            outs_h = main_r["outs_h"]
             parts, qparts = cpu_partitions(doc, ur, dr, qusers)
             Qn = Q.cpu().numpy()
             n0 = min(args.nq, max(cores, 8))
             t0 = time.perf_counter()
-            cpu_search(X_host, tid, parts, qparts[:n0], Qn[:n0], args.k, cores)
+            cpu_search(X_host, tid, parts, qparts[:n0], Qn[:n0], args.k, cores, wl["metric"])
             per_q = (time.perf_counter() - t0) / n0
             S = int(max(min(cores, args.nq), min(args.nq, 20.0 / max(per_q, 1e-6))))
             t0 = time.perf_counter()
-            (c_tid, c_dist, c_cnt), kind = cpu_search(X_host, tid, parts, qparts[:S], Qn[:S], args.k, cores)
+            (c_tid, c_dist, c_cnt), kind = cpu_search(X_host, tid, parts, qparts[:S], Qn[:S], args.k, cores, wl["metric"])
             dtc = time.perf_counter() - t0
             g_tid = outs_h[0].numpy().view(np.uint64)[:S]
-            ids_ok = bool(np.array_equal(g_tid, c_tid) and np.array_equal(outs_h[3].numpy()[:S], c_cnt)
-                          and np.array_equal(outs_h[2].numpy()[:S].view(np.uint64), c_dist.view(np.uint64)))
+            g_dist = outs_h[2].numpy()[:S]
+            g_cnt = outs_h[3].numpy()[:S]
+            if wl["kind"] == "sift":
+                # integer-valued data: ids, counts and float8 distances bit for bit
+                dist_note = "bit-identical"
+                ids_ok = bool(np.array_equal(g_tid, c_tid) and np.array_equal(g_cnt, c_cnt))
+                dist_ok = bool(np.array_equal(g_dist.view(np.uint64), c_dist.view(np.uint64)))
+            else:
+                # float data: the parity tests' rule (tests/util.py) — distances within 1e-5 relative, ids identical
+                # except inside oracle ties of that width
+                from tests.util import assert_topk_matches
+                dist_note = "within 1e-5 relative; ids identical outside oracle ties of that width"
+                try:
+                    assert_topk_matches((g_tid, None, g_dist, g_cnt), (c_tid, None, c_dist, None, c_cnt), exact=False)
+                    ids_ok = dist_ok = True
+                except AssertionError as e:
+                    ids_ok = dist_ok = False
+                    dist_note += " — MISMATCH: " + str(e)[:200]
             line["cpu_baseline"] = {
                 "value": S / dtc, "unit": "queries/s", "cores": cores, "kind": kind,
                 "sample": f"{S} of the step's {args.nq} queries, full visible row sets, {cores} threads on {cpu_model()}; "
                           "pgvector distance loops without PostgreSQL page/tuple/fmgr overhead",
-                "gpu_ids_and_distances_bit_identical": ids_ok}
+                "gpu_ids_match": ids_ok, "gpu_distances": dist_note, "gpu_distances_match": dist_ok}
         print(json.dumps(line), flush=True)
     ix.close()
     if world > 1:

@@ -238,8 +238,9 @@ typedef struct rk_stats {
     uint64_t tensor_exact;     /* RK_ENGINE_TENSOR: 1 = TF32 was exact for the last batch          */
     uint64_t tensor_plan;      /* last batch: 0 = not on the tensor engine, 1 = dense, 2 = per user mask,
                                   3 = per document class (atoms); +16 when the sampling pass ran      */
-    uint64_t tensor_flop;      /* last tensor batch: 2 * dim * 128 * 128 * tile visits (main pass)   */
-    uint64_t reserved[3];
+    uint64_t tensor_flop;      /* last tensor batch: 2 * dim * (query, row) pairs scored (main pass) */
+    uint64_t tensor_plan_bytes;/* last tensor batch: bytes the plan stages (visited tiles x query tiles) */
+    uint64_t reserved[2];
 } rk_stats;
 int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */

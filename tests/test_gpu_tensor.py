@@ -137,3 +137,23 @@ def test_engine_auto_picks_tensor_for_batches():
     for a, b in zip(small, [x[:8] for x in ref]):
         np.testing.assert_array_equal(a, b)
     ix.close()
+
+
+def test_tensor_engine_long_units_many_compactions(monkeypatch):
+    """Long units with a full tile of queries: every query's candidate buffer fills and is compacted many
+    times while the other warps keep appending (regression: a count read before the other warps' appends
+    of the tile had landed let a buffer overflow into its neighbour's best candidates)."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("cohere", n=160000, dim=32, rows_per_doc=40, rbac="random", num_users=24, num_roles=6)
+    ix = load_index(ds, metric=1, role_parts=False, combo_parts=False, k_max=128)
+    ix.finalize()
+    Q, users = _queries(ds, 128, seed=21)
+    monkeypatch.setenv("RK_TENSOR_PLAN", "dense")
+    monkeypatch.setenv("RK_TENSOR_SAMPLE", "0")
+    monkeypatch.setenv("RK_TENSOR_TPU", "100000")        # one unit per query tile: the whole corpus in one pass
+    for flt in (vr.FILTER_NONE, vr.FILTER_BITMASK):
+        got = ix.search_batch(Q, users, 100, filter=flt, engine=vr.ENGINE_TENSOR)
+        ref = ix.search_batch(Q, users, 100, filter=flt, engine=vr.ENGINE_SCAN)
+        for a, b in zip(got, ref):
+            np.testing.assert_array_equal(a, b)
+    ix.close()

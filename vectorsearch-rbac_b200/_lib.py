@@ -30,7 +30,7 @@ class RkStats(C.Structure):
                 ("launches", C.c_uint64), ("segments", C.c_uint64), ("rows_scanned", C.c_uint64),
                 ("algo_bytes", C.c_uint64), ("scan_ms", C.c_float), ("select_ms", C.c_float), ("probe_ms", C.c_float),
                 ("reserved_f", C.c_float), ("total_launches", C.c_uint64), ("tensor_redo", C.c_uint64),
-                ("tensor_exact", C.c_uint64), ("tensor_plan", C.c_uint64), ("tensor_flop", C.c_uint64), ("reserved", C.c_uint64 * 3)]
+                ("tensor_exact", C.c_uint64), ("tensor_plan", C.c_uint64), ("tensor_flop", C.c_uint64), ("tensor_plan_bytes", C.c_uint64), ("reserved", C.c_uint64 * 2)]
 
 
 # every symbol include/rbacknn.h declares: name -> (restype, argtypes)

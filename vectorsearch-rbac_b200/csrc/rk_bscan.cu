@@ -140,7 +140,7 @@ __device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint3
 #pragma unroll
     for (int j = 0; j < BS_CAP / 32; j++) {
         const uint32_t i = (uint32_t) c.lane + 32u * j;
-        key[j] = i < n ? buf[i].x : RK_KEY_SENTINEL;
+        key[j] = i < n ? __ldcg(&buf[i].x) : RK_KEY_SENTINEL;
     }
     uint32_t prefix = 0, mask = 0, kk = kp;
 #pragma unroll 1
@@ -180,7 +180,7 @@ __device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint3
     for (int j = 0; j < BS_CAP / 32; j++) {
         const uint32_t i = (uint32_t) c.lane + 32u * j;
         const bool keep = i < n && key[j] <= tau;
-        row[j] = keep ? buf[i].y : 0u;
+        row[j] = keep ? __ldcg(&buf[i].y) : 0u;
         mine += keep;
     }
     uint32_t inc = mine;
@@ -192,7 +192,7 @@ __device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint3
 #pragma unroll
     for (int j = 0; j < BS_CAP / 32; j++) {
         const uint32_t i = (uint32_t) c.lane + 32u * j;
-        if (i < n && key[j] <= tau) buf[pos++] = make_uint2(key[j], row[j]);
+        if (i < n && key[j] <= tau) __stcg(&buf[pos++], make_uint2(key[j], row[j]));
     }
     __syncwarp();
     *tau_out = tau;
@@ -208,7 +208,7 @@ __device__ __forceinline__ uint32_t bs_warp_filter(const BsCtx &c, int q, uint32
 #pragma unroll
     for (int j = 0; j < BS_CAP / 32; j++) {
         const uint32_t i = (uint32_t) c.lane + 32u * j;
-        e[j] = i < n ? buf[i] : make_uint2(RK_KEY_SENTINEL, 0u);
+        e[j] = i < n ? __ldcg(&buf[i]) : make_uint2(RK_KEY_SENTINEL, 0u);
         mine += i < n && e[j].x <= bound;
     }
     uint32_t inc = mine;
@@ -220,7 +220,7 @@ __device__ __forceinline__ uint32_t bs_warp_filter(const BsCtx &c, int q, uint32
 #pragma unroll
     for (int j = 0; j < BS_CAP / 32; j++) {
         const uint32_t i = (uint32_t) c.lane + 32u * j;
-        if (i < n && e[j].x <= bound) buf[pos++] = e[j];
+        if (i < n && e[j].x <= bound) __stcg(&buf[pos++], e[j]);
     }
     __syncwarp();
     return total;
@@ -236,7 +236,7 @@ __device__ __forceinline__ void bs_warp_emit(const BsCtx &c, int q, uint32_t n, 
     while (P < n) P <<= 1;
     for (uint32_t i = c.lane; i < P; i += 32) {
         uint64_t v = ~0ull;
-        if (i < n) { const uint2 e = buf[i]; v = ((uint64_t) e.x << 32) | e.y; }
+        if (i < n) { const uint2 e = __ldcg(&buf[i]); v = ((uint64_t) e.x << 32) | e.y; }
         c.sortbuf[i] = v;
     }
     __syncwarp();
@@ -488,7 +488,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                             if (pass & (1u << j)) {
                                 const uint32_t q = c0 + j;
                                 const uint32_t slot = atomicAdd(&c.cnt[q], 1u);
-                                c.scratch[(size_t) q * BS_CAP + slot] = make_uint2(r[j], (uint32_t) row);
+                                __stcg(&c.scratch[(size_t) q * BS_CAP + slot], make_uint2(r[j], (uint32_t) row));
                             }
                         }
                     }
@@ -498,11 +498,14 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 if (lane == 0) rk_mbar_arrive(&tempty[buf]);
                 // a tile adds at most 128 entries per query: compact what could overflow on the next one
                 // (the reducing barrier also publishes this tile's appends)
-                const bool need = rk_named_bar_red_or(2, 128, c.cnt[et] > BS_CAP - BS_M);
+                // (the count a thread reads here may still miss this tile's appends by the other three
+                // warps — at most 96 — hence the margin of two tiles: seen <= CAP - 256 means at most
+                // CAP - 160 now and at most CAP - 32 after the next tile)
+                const bool need = rk_named_bar_red_or(2, 128, c.cnt[et] > BS_CAP - 2 * BS_M);
                 if (need) {
                     for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
                         const uint32_t n = c.cnt[q];
-                        if (n > BS_CAP - BS_M) {
+                        if (n > BS_CAP - 2 * BS_M) {
                             uint32_t tau;
                             uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
                             if (m > BS_CAP / 2 && tau > 0) {

@@ -94,6 +94,7 @@ struct TensorState {
     std::vector<Atom> atoms;                                                    // document classes by role mask (empty: too many)
     bool tiles_dirty = false;                                                   // h_tiles grew since the last upload
     int last_plan = 0;
+    uint64_t last_plan_bytes = 0;
     DevBuf d_units, d_qnorm, d_scratch, d_cand_key, d_cand_row, d_cand_count, d_sel_key, d_sel_row, d_sel_count, d_tau_key, d_tau_count, d_flags;
     PinBuf h_flags;
     double last_flop = 0.0;

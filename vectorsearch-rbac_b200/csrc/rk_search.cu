@@ -648,5 +648,6 @@ extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)
     out->tensor_exact = ix->tensor.last_exact ? 1 : 0;
     out->tensor_plan = (uint64_t) ix->tensor.last_plan;
     out->tensor_flop = (uint64_t) ix->tensor.last_flop;
+    out->tensor_plan_bytes = ix->tensor.last_plan_bytes;
     return RK_OK;
 }

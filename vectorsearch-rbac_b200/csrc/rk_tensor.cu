@@ -134,6 +134,7 @@ static int tiles_for_mask(rk_index *ix, const std::vector<uint64_t> &mask, uint3
     *cnt = (uint32_t) ts.h_tiles.size() - o;
     ts.tile_cache[mask] = std::make_pair(*off, *cnt);
     *grew = true;
+    ts.tiles_dirty = true;      // uploaded by the next call whose plan walks tile lists
     return 0;
 }
 
@@ -153,6 +154,7 @@ struct TPass {
     uint32_t list_total = 0;
     int grid = 1;
     double tile_visits = 0.0;
+    double pairs = 0.0;            // (query, row) pairs scored: sum over units of queries x tiles x 128
     size_t o_units = 0, o_coff = 0, o_cu = 0, o_lid0 = 0, o_lstep = 0, o_nl = 0;     // offsets in the staged plan
 };
 
@@ -168,6 +170,7 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
         const TGroup &g = groups[gi];
         const double visits = (double) ((g.tl_n + step[gi] - 1) / step[gi]);
         total_work += visits * (double) ((g.queries.size() + 127) / 128);
+        ps.pairs += visits * 128.0 * (double) g.queries.size();
         max_gq = std::max(max_gq, std::min<size_t>(128, g.queries.size()));
     }
     ps.tile_visits = total_work;
@@ -198,6 +201,7 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
             }
         }
     }
+    if (const char *e = getenv("RK_TENSOR_TPU")) tpu = (uint32_t) std::max(1, atoi(e));      // debugging aid: tiles per unit
     ps.lid0.assign(nslots, 0); ps.lstep.assign(nslots, 0); ps.nlists.assign(nslots, 0);
     std::vector<double> unit_work;
     uint32_t slot = 0;
@@ -640,9 +644,15 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     ws.segments = pm_.units.size() + ps_.units.size();
     const uint64_t tile_visits = (uint64_t) (pm_.tile_visits + 0.5);
     ws.rows_scanned = tile_visits * 128;
-    // bytes this plan must move: every visited tile once per query tile, plus the queries
-    ws.algo_bytes = (uint64_t) ix->dim_pad * 4ull * (tile_visits * 128ull + nslots);
-    ts.last_flop = 2.0 * (double) ix->dim * 128.0 * (double) tile_visits * 128.0;
+    // SURVEY.md §8(d), batched exact: bytes 4d (R_g + nq_g) over the groups the plan forms — every row a
+    // group sees once (min_visible is exact for every plan: all rows / the user's rows / the atom's rows)
+    uint64_t group_rows = 0;
+    for (auto &g : groups) group_rows += plan == PLAN_DENSE ? n : g.min_visible;
+    ws.algo_bytes = (uint64_t) ix->dim_pad * 4ull * (group_rows + nslots);
+    // what the plan actually stages: every visited 128-row tile once per 128-query tile, plus the queries
+    ts.last_plan_bytes = (uint64_t) ix->dim_pad * 4ull * (tile_visits * 128ull + nslots);
+    // SURVEY.md §8(d), batched exact: F = 2 nq_g R_g d over the groups the plan forms (main pass)
+    ts.last_flop = 2.0 * (double) ix->dim * pm_.pairs;
     ts.last_redo = (uint32_t) redo.size();
     ts.last_exact = exact;
     ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0);
