@@ -10,6 +10,14 @@ from tests.util import assert_topk_matches, load_index, make_dataset, oracle_rol
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["one-cta", "cta-pair"])
+def scoring_kernel(request, monkeypatch):
+    """Every case runs on both scoring kernels: rk_bscan_kernel (cta_group::1, 128-query tiles) and
+    rk_bscan2_kernel (cta_group::2 CTA pairs, 256-query tiles)."""
+    monkeypatch.setenv("RK_TENSOR_PAIR", "1" if request.param == "cta-pair" else "0")
+    return request.param
+
+
 def _queries(ds, nq, seed=11):
     rng = np.random.default_rng(seed)
     rows = rng.integers(0, len(ds["X"]), nq)
@@ -73,7 +81,7 @@ def test_tensor_engine_unfiltered_and_small_visible_sets():
 
 
 @pytest.mark.parametrize("plan", ["dense", "grouped", "atoms"])
-def test_tensor_engine_plans_agree(plan, monkeypatch):
+def test_tensor_engine_plans_agree(plan, monkeypatch, scoring_kernel):
     """Dense / per-user-mask / per-document-class (atoms) plans walk different tiles with different query
     groupings; all must return the oracle's answer (a query appears in several atoms' units and its
     lists are merged per query)."""
@@ -90,6 +98,7 @@ def test_tensor_engine_plans_agree(plan, monkeypatch):
     assert_topk_matches(got, exp, exact=True)
     assert got[3][3] == 0
     assert ix.stats()["tensor_plan"] & 15 == {"dense": 1, "grouped": 2, "atoms": 3}[plan]
+    assert bool(ix.stats()["tensor_plan"] & 32) == (scoring_kernel == "cta-pair")
     ix.close()
 
 
@@ -112,7 +121,7 @@ def test_tensor_engine_sampling_pass(kind, metric, flt, monkeypatch):
     monkeypatch.setenv("RK_TENSOR_SDIV", "4")          # sample every 4th.. tile already on this small corpus
     monkeypatch.setenv("RK_TENSOR_SMIN", "64")
     got = ix.search_batch(Q, users, k, filter=f, engine=vr.ENGINE_TENSOR)
-    assert ix.stats()["tensor_plan"] == 1 + 16         # dense plan, sampling pass ran
+    assert ix.stats()["tensor_plan"] & 31 == 1 + 16    # dense plan, sampling pass ran
     assert ix.stats()["segments"] > units0
     for a, b in zip(got, base):
         np.testing.assert_array_equal(a, b)

@@ -24,78 +24,15 @@
 //   warps 2-5  epilogue: tcgen05.ld (one TMEM lane = one row), distance, mask test, threshold test
 //            against the running per-query tau, append to per-query candidate buffers (global
 //            scratch, L2 resident); warp-parallel radix-select compaction when a buffer fills.
-#include <cuda.h>
-
-#include "rk_common.cuh"
+#include "rk_bscan_dev.cuh"
 #include "rk_kernels.h"
 
 #define BS_M 128
 #define BS_N 128
 #define BS_KC 32
 #define BS_STAGES 5
-#define BS_CAP 1024
 #define BS_THREADS 192
 #define BS_STAGE_BYTES 32768u          // X box 16 KB + Q box 16 KB
-#define BS_SORT_MAX 512                // entries one warp sorts at unit end
-
-// ---------------------------------------------------------------------------------------------
-// PTX wrappers
-
-__device__ __forceinline__ void bs_tma_2d(void *smem_dst, const CUtensorMap *tm, int c0, int c1, uint64_t *bar)
-{
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-                     rk_smem_u32(smem_dst)),
-                 "l"(tm), "r"(rk_smem_u32(bar)), "r"(c0), "r"(c1)
-                 : "memory");
-}
-
-__device__ __forceinline__ void bs_tmem_alloc(uint32_t *smem_dst, uint32_t ncols)
-{
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(rk_smem_u32(smem_dst)), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-
-__device__ __forceinline__ void bs_tmem_dealloc(uint32_t taddr, uint32_t ncols)
-{
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-
-__device__ __forceinline__ void bs_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void bs_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void bs_commit(uint64_t *bar)
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(rk_smem_u32(bar)) : "memory");
-}
-
-__device__ __forceinline__ void bs_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
-{
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-        "}" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-
-__device__ __forceinline__ void bs_tmem_ld16(uint32_t taddr, uint32_t (&r)[16])
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major, 128-byte swizzle, 8-row atoms 1024 bytes apart (what the 2-D TMA box above writes).
-__device__ __forceinline__ uint64_t bs_smem_desc(uint32_t smem_addr)
-{
-    return (uint64_t) ((smem_addr >> 4) & 0x3FFFu) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
 
 // ---------------------------------------------------------------------------------------------
 
@@ -124,148 +61,6 @@ __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
     return s;
 }
 
-struct BsCtx {
-    uint32_t *tau, *cnt, *hist, *sel;
-    uint2 *scratch;     // this CTA's [BS_N][BS_CAP]
-    uint64_t *sortbuf;  // this warp's [BS_SORT_MAX]
-    int lane;
-};
-
-// Exact kp-th smallest key of one query's buffer by a warp-level 4-pass radix select, then in-place
-// compaction key <= tau.  n <= BS_CAP.  Returns the new count; *tau_out receives the threshold.
-__device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint32_t n, uint32_t kp, uint32_t *tau_out)
-{
-    uint2 *buf = c.scratch + (size_t) q * BS_CAP;
-    uint32_t key[BS_CAP / 32];
-#pragma unroll
-    for (int j = 0; j < BS_CAP / 32; j++) {
-        const uint32_t i = (uint32_t) c.lane + 32u * j;
-        key[j] = i < n ? __ldcg(&buf[i].x) : RK_KEY_SENTINEL;
-    }
-    uint32_t prefix = 0, mask = 0, kk = kp;
-#pragma unroll 1
-    for (int shift = 24; shift >= 0; shift -= 8) {
-#pragma unroll
-        for (int b = 0; b < 8; b++) c.hist[c.lane * 8 + b] = 0;
-        __syncwarp();
-#pragma unroll
-        for (int j = 0; j < BS_CAP / 32; j++) {
-            const uint32_t i = (uint32_t) c.lane + 32u * j;
-            if (i < n && (key[j] & mask) == prefix) atomicAdd(&c.hist[(key[j] >> shift) & 255u], 1u);
-        }
-        __syncwarp();
-        uint32_t h[8], tot = 0;
-#pragma unroll
-        for (int b = 0; b < 8; b++) { h[b] = c.hist[c.lane * 8 + b]; tot += h[b]; }
-        uint32_t inc = tot;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (c.lane >= o) inc += u; }
-        uint32_t run = inc - tot;
-#pragma unroll
-        for (int b = 0; b < 8; b++) {
-            if (run < kk && kk <= run + h[b]) { c.sel[0] = (uint32_t) (c.lane * 8 + b); c.sel[1] = kk - run; }
-            run += h[b];
-        }
-        __syncwarp();
-        prefix |= c.sel[0] << shift;
-        mask |= 0xFFu << shift;
-        kk = c.sel[1];
-        __syncwarp();
-    }
-    const uint32_t tau = prefix;
-    // compaction: rows of the survivors are read before anything is overwritten
-    uint32_t row[BS_CAP / 32];
-    uint32_t mine = 0;
-#pragma unroll
-    for (int j = 0; j < BS_CAP / 32; j++) {
-        const uint32_t i = (uint32_t) c.lane + 32u * j;
-        const bool keep = i < n && key[j] <= tau;
-        row[j] = keep ? __ldcg(&buf[i].y) : 0u;
-        mine += keep;
-    }
-    uint32_t inc = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (c.lane >= o) inc += u; }
-    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-    uint32_t pos = inc - mine;
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < BS_CAP / 32; j++) {
-        const uint32_t i = (uint32_t) c.lane + 32u * j;
-        if (i < n && key[j] <= tau) __stcg(&buf[pos++], make_uint2(key[j], row[j]));
-    }
-    __syncwarp();
-    *tau_out = tau;
-    return total;
-}
-
-// Keep the entries with key <= bound (in place).  Returns the new count.
-__device__ __forceinline__ uint32_t bs_warp_filter(const BsCtx &c, int q, uint32_t n, uint32_t bound)
-{
-    uint2 *buf = c.scratch + (size_t) q * BS_CAP;
-    uint2 e[BS_CAP / 32];
-    uint32_t mine = 0;
-#pragma unroll
-    for (int j = 0; j < BS_CAP / 32; j++) {
-        const uint32_t i = (uint32_t) c.lane + 32u * j;
-        e[j] = i < n ? __ldcg(&buf[i]) : make_uint2(RK_KEY_SENTINEL, 0u);
-        mine += i < n && e[j].x <= bound;
-    }
-    uint32_t inc = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (c.lane >= o) inc += u; }
-    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-    uint32_t pos = inc - mine;
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < BS_CAP / 32; j++) {
-        const uint32_t i = (uint32_t) c.lane + 32u * j;
-        if (i < n && e[j].x <= bound) __stcg(&buf[pos++], e[j]);
-    }
-    __syncwarp();
-    return total;
-}
-
-// Sort the first n (<= BS_SORT_MAX) entries of a query's buffer by (key, row) in this warp's shared
-// scratch and write the first min(n, kp) to the unit's candidate list.
-__device__ __forceinline__ void bs_warp_emit(const BsCtx &c, int q, uint32_t n, uint32_t kp, uint32_t *out_key, uint32_t *out_row,
-                                             int32_t *out_count)
-{
-    const uint2 *buf = c.scratch + (size_t) q * BS_CAP;
-    uint32_t P = 32;
-    while (P < n) P <<= 1;
-    for (uint32_t i = c.lane; i < P; i += 32) {
-        uint64_t v = ~0ull;
-        if (i < n) { const uint2 e = __ldcg(&buf[i]); v = ((uint64_t) e.x << 32) | e.y; }
-        c.sortbuf[i] = v;
-    }
-    __syncwarp();
-    for (uint32_t size = 2; size <= P; size <<= 1) {
-        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-            for (uint32_t i = c.lane; i < (P >> 1); i += 32) {
-                const uint32_t lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
-                const bool up = (lo & size) == 0;
-                const uint64_t a = c.sortbuf[lo], b = c.sortbuf[hi];
-                if (up ? (b < a) : (a < b)) { c.sortbuf[lo] = b; c.sortbuf[hi] = a; }
-            }
-            __syncwarp();
-        }
-    }
-    const uint32_t m = n < kp ? n : kp;
-    for (uint32_t i = c.lane; i < m; i += 32) {
-        const uint64_t v = c.sortbuf[i];
-        out_key[i] = (uint32_t) (v >> 32);
-        out_row[i] = (uint32_t) v;
-    }
-    if (c.lane == 0) *out_count = (int32_t) m;
-    __syncwarp();
-}
-
-// Tiles a unit visits: tile_begin, tile_begin + step, ... below tile_end.
-__device__ __forceinline__ uint32_t bs_unit_tiles(const RkBUnit &un)
-{
-    return un.tile_end > un.tile_begin ? (un.tile_end - un.tile_begin + un.tile_step - 1u) / un.tile_step : 0u;
-}
 
 template <int METRIC>
 __global__ void __launch_bounds__(BS_THREADS, 1)
@@ -749,7 +544,7 @@ typedef CUresult (*rk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t,
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 // 2-D fp32 tensor [rows][dim_pad], box = 32 floats x box_rows, 128-byte swizzle, zero fill out of bounds.
-static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad, uint32_t box_rows = BS_M)
+cudaError_t rk_make_tensor_map_2d(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad, uint32_t box_rows)
 {
     static rk_encode_fn encode = nullptr;
     if (!encode) {
@@ -773,10 +568,10 @@ static cudaError_t make_tensor_map(CUtensorMap *tm, const float *base, uint64_t 
 cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream)
 {
     CUtensorMap tmx, tmq[4];
-    cudaError_t e = make_tensor_map(&tmx, x, p.nrows, p.dim_pad);
+    cudaError_t e = rk_make_tensor_map_2d(&tmx, x, p.nrows, p.dim_pad, BS_M);
     if (e != cudaSuccess) return e;
     for (int i = 0; i < 4; i++) {
-        e = make_tensor_map(&tmq[i], q, nq, p.dim_pad, 16u << i);
+        e = rk_make_tensor_map_2d(&tmq[i], q, nq, p.dim_pad, 16u << i);
         if (e != cudaSuccess) return e;
     }
     const size_t smem = rk_bscan_smem_bytes(p.mask_words);

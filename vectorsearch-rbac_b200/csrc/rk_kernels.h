@@ -40,6 +40,11 @@ size_t rk_bscan_smem_bytes(int mask_words);
 int rk_bscan_lists_per_query();   // candidate lists one unit writes per query (one per epilogue set)
 size_t rk_bscan_scratch_bytes(int grid);
 cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream);
+// CTA-pair variant (rk_bscan2.cu): units come in pairs (2p, 2p + 1) sharing a tile of up to 256 queries;
+// cta_off / cta_units schedule PAIRS onto clusters; grid = 2 x clusters
+size_t rk_bscan2_smem_bytes(int mask_words);
+size_t rk_bscan2_scratch_bytes(int grid);
+cudaError_t rk_launch_bscan2(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream);
 cudaError_t rk_launch_rescore(const RkRescoreParams &p, int nq, cudaStream_t stream);
 cudaError_t rk_launch_row_norms(const float *x, size_t n, int dim_pad, float *out, cudaStream_t stream);
 cudaError_t rk_launch_rowmask(const uint32_t *rowdoc, const uint64_t *doc_mask, size_t n, int W, uint64_t *out, cudaStream_t stream);

@@ -160,18 +160,22 @@ struct TPass {
 
 // Cuts every (group, tile of 128 queries) pair into units over the group's tiles visited with stride
 // step[g] (0 = the group takes no part in this pass) and balances the units onto the CTAs.
+// Paired mode (rk_bscan2_kernel): query tiles are `qt` = 256 wide, every range of tiles becomes a PAIR of units
+// (2p walks the even visits of the range, 2p + 1 the odd ones) and the schedule places pairs onto clusters.
 static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint32_t> &step, int sm, uint32_t LPQ, size_t nslots,
-                       TPass &ps)
+                       TPass &ps, bool paired)
 {
+    const size_t qt = paired ? 256 : 128;
+    const uint32_t upr = paired ? 2u : 1u;           // units per range of tiles
     double total_work = 0.0;
     size_t max_gq = 0;
     for (size_t gi = 0; gi < groups.size(); gi++) {
         if (!step[gi]) continue;
         const TGroup &g = groups[gi];
         const double visits = (double) ((g.tl_n + step[gi] - 1) / step[gi]);
-        total_work += visits * (double) ((g.queries.size() + 127) / 128);
+        total_work += visits * (double) ((g.queries.size() + qt - 1) / qt);
         ps.pairs += visits * 128.0 * (double) g.queries.size();
-        max_gq = std::max(max_gq, std::min<size_t>(128, g.queries.size()));
+        max_gq = std::max(max_gq, std::min<size_t>(qt, g.queries.size()));
     }
     ps.tile_visits = total_work;
     // tiles per unit: ~8 units per CTA, but a unit ends with one compaction + sort per query, so it
@@ -188,13 +192,13 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
             // longest-first schedule below balances them: more, shorter units are better there)
             size_t npairs = 0;
             for (size_t gi = 0; gi < groups.size(); gi++)
-                if (step[gi]) npairs += (groups[gi].queries.size() + 127) / 128;
+                if (step[gi]) npairs += (groups[gi].queries.size() + qt - 1) / qt;
             for (int it = 0; it < 64 && npairs * 2 <= (size_t) sm; it++) {
                 uint64_t units = 0;
                 for (size_t gi = 0; gi < groups.size(); gi++) {
                     if (!step[gi]) continue;
                     const uint64_t visits = (groups[gi].tl_n + step[gi] - 1) / step[gi];
-                    units += std::max<uint64_t>(1, (visits + tpu - 1) / tpu) * ((groups[gi].queries.size() + 127) / 128);
+                    units += upr * std::max<uint64_t>(1, (visits + upr * tpu - 1) / (upr * tpu)) * ((groups[gi].queries.size() + qt - 1) / qt);
                 }
                 if ((double) units <= m * sm) break;
                 tpu += std::max<uint32_t>(1, tpu / 64);
@@ -211,34 +215,39 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
         if (!step[gi]) { slot += (uint32_t) gq; continue; }
         const uint32_t st = step[gi];
         const uint32_t visits = (g.tl_n + st - 1) / st;
-        for (size_t b = 0; b < gq; b += 128) {
-            const uint32_t qn = (uint32_t) std::min<size_t>(128, gq - b);
-            const uint32_t R = std::max<uint32_t>(1, (visits + tpu - 1) / tpu);
+        for (size_t b = 0; b < gq; b += qt) {
+            const uint32_t qn = (uint32_t) std::min<size_t>(qt, gq - b);
+            const uint32_t R = std::max<uint32_t>(1, (visits + upr * tpu - 1) / (upr * tpu));
             for (uint32_t i = 0; i < qn; i++) {
                 ps.lid0[slot + i] = ps.list_total + i;
                 ps.lstep[slot + i] = qn;
-                ps.nlists[slot + i] = R * LPQ;          // every unit writes one list per epilogue set
+                ps.nlists[slot + i] = R * upr * LPQ;    // every unit writes one list per epilogue set
             }
             for (uint32_t r = 0; r < R; r++) {
-                RkBUnit u;
-                memset(&u, 0, sizeof u);
                 const uint32_t lo = (uint32_t) ((uint64_t) visits * r / R), hi = (uint32_t) ((uint64_t) visits * (r + 1) / R);
-                u.q0 = slot; u.nq = qn;
-                u.tile_begin = lo * st;
-                u.tile_end = hi == visits ? g.tl_n : hi * st;
-                u.tile_step = st;
-                u.tl_off = g.tl_off;
-                u.mask_id = g.own_mask ? (uint32_t) gi + 1u : 0u;
-                u.list_base = ps.list_total;
-                ps.list_total += qn * LPQ;
-                ps.units.push_back(u);
-                unit_work.push_back((double) (hi - lo) * (128.0 + (double) ((qn + 15) & ~15u)) + 2000.0 * qn);
+                for (uint32_t h = 0; h < upr; h++) {
+                    RkBUnit u;
+                    memset(&u, 0, sizeof u);
+                    u.q0 = slot; u.nq = qn;
+                    u.tile_begin = (lo + h) * st;
+                    u.tile_end = hi == visits ? g.tl_n : hi * st;
+                    u.tile_step = st * upr;
+                    u.tl_off = g.tl_off;
+                    u.mask_id = g.own_mask ? (uint32_t) gi + 1u : 0u;
+                    u.list_base = ps.list_total;
+                    ps.list_total += qn * LPQ;
+                    ps.units.push_back(u);
+                }
+                // per CTA: tiles walked x bytes staged per tile, plus the unit-end sorts
+                unit_work.push_back((double) ((hi - lo + upr - 1) / upr) * (128.0 + (double) (((qn + 15) & ~15u) / upr)) + 2000.0 * qn / (paired ? 2.0 : 1.0));
             }
             slot += qn;
         }
     }
-    const uint32_t nunits = (uint32_t) ps.units.size();
-    ps.grid = (int) std::min<uint32_t>((uint32_t) sm, std::max<uint32_t>(nunits, 1));
+    // schedulable items: units, or unit pairs onto clusters of two CTAs
+    const uint32_t nunits = (uint32_t) unit_work.size();
+    const int bins = (int) std::min<uint32_t>((uint32_t) (paired ? sm / 2 : sm), std::max<uint32_t>(nunits, 1));
+    ps.grid = bins;
     // balanced static schedule: longest unit first onto the least loaded CTA
     std::vector<uint32_t> order(nunits);
     ps.cta_off.assign((size_t) ps.grid + 1, 0);
@@ -263,6 +272,7 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
         for (uint32_t u : per[(size_t) c]) ps.cta_units[pos++] = u;
     }
     ps.cta_off[(size_t) ps.grid] = pos;
+    if (paired) ps.grid *= 2;        // cta_off stays per cluster
 }
 
 // Runs the batch on the tensor engine.  `out` carries the final device destinations.  On return
@@ -311,8 +321,15 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     //   dense    every tile against all queries together, mask test per (row, query)
     //   grouped  per distinct user mask: only the tiles holding rows that user sees
     //   atoms    per document class (same role mask): its tiles once, against every query that sees it
-    auto visit_cost = [](double tiles, size_t qn) {
-        return tiles * (double) ((qn + 127) / 128) * (128.0 + (double) std::min<size_t>(128, (qn + 15) & ~(size_t) 15));
+    // Which scoring kernel: long rows make the one-CTA kernel L2-feed-bound (32 flop per staged byte), so from 256
+    // dimensions on the CTA-pair kernel (64 flop per staged byte, query tiles of 256) takes the batch; short rows
+    // are bound by the epilogue's select work, which the pair does not change.  RK_TENSOR_PAIR=0|1 forces it (tests).
+    bool paired = ix->dim_pad >= 256;
+    if (const char *e = getenv("RK_TENSOR_PAIR")) paired = atoi(e) != 0;
+    const size_t qt = paired ? 256 : 128;
+    auto visit_cost = [&](double tiles, size_t qn) {
+        const double qcols = (double) std::min<size_t>(qt, (qn + 15) & ~(size_t) 15);
+        return tiles * (double) ((qn + qt - 1) / qt) * (128.0 + (paired ? 0.5 * qcols : qcols));
     };
     enum { PLAN_DENSE, PLAN_GROUPED, PLAN_ATOMS } plan = PLAN_DENSE;
     bool grew = false;
@@ -410,12 +427,23 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         const TGroup &g = groups[gi];
         if (g.tl_n < env_smin) continue;
         // about 1 in 400 of the (visible row, query) pairs should survive the seeded threshold: kp S / visible
-        const uint64_t S = std::min<uint64_t>(64, g.min_visible / ((uint64_t) env_sdiv * (uint64_t) kp));
+        uint64_t S = std::min<uint64_t>(64, g.min_visible / ((uint64_t) env_sdiv * (uint64_t) kp));
+        if (S < 4 && !getenv("RK_TENSOR_SDIV")) {
+            // Too few visible rows for that, but a coarser seed still pays: a unit that starts at +inf collects about
+            // kp ln(rows / kp) entries per query and stops the whole CTA for a compaction every few tiles.  Seeded
+            // from every S-th tile a unit collects about kp S / (ranges the tiles are cut into): keep that near
+            // 300, well under one buffer, at a pass that costs 1 / S of the main one.
+            const double qblocks = std::max(1.0, std::ceil((double) nslots / (double) qt));
+            const double ranges = std::max(1.0, (paired ? sm / 2 : sm) / qblocks);
+            S = (uint64_t) std::min(64.0, 300.0 * ranges / (double) kp);
+            S = std::min<uint64_t>(S, g.min_visible / (4ull * (uint64_t) kp));     // the sample itself must hold >= 4 kp visible rows
+            if (S < 8) S = 0;
+        }
         if (S >= 4) { step_sample[gi] = (uint32_t) S; sampled = true; }
     }
     TPass pm_, ps_;
-    build_pass(groups, step_main, sm, LPQ, nslots, pm_);
-    if (sampled) build_pass(groups, step_sample, sm, LPQ, nslots, ps_);
+    build_pass(groups, step_main, sm, LPQ, nslots, pm_, paired);
+    if (sampled) build_pass(groups, step_sample, sm, LPQ, nslots, ps_, paired);
     // final merge: every query owns the main-pass lists of all its slots
     std::vector<uint32_t> qoff(nq + 1, 0), qlist;
     {
@@ -487,7 +515,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     const uint32_t list_max = std::max(pm_.list_total, ps_.list_total);
     const int grid_max = std::max(pm_.grid, ps_.grid);
     if (ts.d_qp.ensure(std::max<size_t>(nslots * (size_t) ix->dim_pad * 4, 16)) != 0 ||
-        ts.d_qnorm.ensure(std::max<size_t>(nq * 4, 16)) != 0 || ts.d_scratch.ensure(rk_bscan_scratch_bytes(grid_max)) != 0 ||
+        ts.d_qnorm.ensure(std::max<size_t>(nq * 4, 16)) != 0 || ts.d_scratch.ensure(paired ? rk_bscan2_scratch_bytes(grid_max) : rk_bscan_scratch_bytes(grid_max)) != 0 ||
         ts.d_cand_key.ensure(std::max<size_t>((size_t) list_max * kp * 4, 16)) != 0 ||
         ts.d_cand_row.ensure(std::max<size_t>((size_t) list_max * kp * 4, 16)) != 0 ||
         ts.d_cand_count.ensure(std::max<size_t>((size_t) list_max * 4, 16)) != 0 ||
@@ -560,7 +588,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         bind_pass(ps_);
         bp.trunc = ts.d_flags.as<int32_t>() + 2 * nq;      // ties dropped here only loosen the seed
         bp.tau_key = nullptr; bp.tau_count = nullptr;
-        RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, ps_.grid, st));
+        RK_CUDA((paired ? rk_launch_bscan2 : rk_launch_bscan)(bp, ix->d_x.as<float>(), dQp, nslots, ps_.grid, st));
         // per slot: the sample's kp smallest values
         sp.lid0 = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lid0);
         sp.lstep = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lstep);
@@ -576,7 +604,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         bp.trunc = ts.d_flags.as<int32_t>() + nq;
         bp.tau_key = sampled ? ts.d_tau_key.as<float>() : nullptr;
         bp.tau_count = sampled ? ts.d_tau_count.as<int32_t>() : nullptr;
-        RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, pm_.grid, st));
+        RK_CUDA((paired ? rk_launch_bscan2 : rk_launch_bscan)(bp, ix->d_x.as<float>(), dQp, nslots, pm_.grid, st));
         launches++;
     }
     if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot_ev], st)); ws.timed_scan = true; ws.ring_n++; }
@@ -655,6 +683,6 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     ts.last_flop = 2.0 * (double) ix->dim * pm_.pairs;
     ts.last_redo = (uint32_t) redo.size();
     ts.last_exact = exact;
-    ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0);
+    ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0) + (paired ? 32 : 0);
     return RK_OK;
 }
