@@ -329,7 +329,8 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                     if (n > BS_SORT_MAX) n = BS_SORT_MAX;
                 }
                 const size_t list = (size_t) un.list_base + q;
-                bs_warp_emit(c, (int) q, n, (uint32_t) p.kp, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
+                if (n <= (uint32_t) p.kp) bs_warp_emit_unsorted(c, (int) q, n, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
+                else bs_warp_emit(c, (int) q, n, (uint32_t) p.kp, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
             }
         }
     }

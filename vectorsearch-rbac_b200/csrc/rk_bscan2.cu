@@ -138,7 +138,7 @@ __device__ __forceinline__ void b2_mma_tf32(uint32_t tmem_d, uint64_t adesc, uin
 // ---------------------------------------------------------------------------------------------
 
 struct B2Smem {
-    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_trunc, off_qa, off_um, off_hist, off_sel, off_sort, total;
+    uint32_t off_stage, off_bar, off_tmem, off_tau, off_tauf, off_cnt, off_trunc, off_qa, off_um, off_hist, off_sel, off_sort, total;
     int stages;
 };
 
@@ -151,6 +151,7 @@ __host__ __device__ inline B2Smem b2_smem_layout(int mask_words)
     s.off_bar = o; o += 8u * (2 * 5 + 4);
     s.off_tmem = o; o += 16;
     s.off_tau = o; o += B2_N * 4;
+    s.off_tauf = o; o += B2_N * 4;     // the same thresholds as floats (16-byte aligned: read four at a time)
     s.off_cnt = o; o += B2_N * 4;
     o = (o + 15) & ~15u;
     s.off_trunc = o; o += B2_N * 8;
@@ -294,6 +295,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
         c.scratch = p.scratch + (size_t) blockIdx.x * B2_N * BS_CAP;
         c.sortbuf = reinterpret_cast<uint64_t *>(smem + L.off_sort) + ew * BS_SORT_MAX;
         c.lane = lane;
+        float *tauf = reinterpret_cast<float *>(smem + L.off_tauf);
         int32_t **s_trunc = reinterpret_cast<int32_t **>(smem + L.off_trunc);
         uint4 *s_qa = reinterpret_cast<uint4 *>(smem + L.off_qa);
         uint64_t *s_um = reinterpret_cast<uint64_t *>(smem + L.off_um);
@@ -312,6 +314,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 uint32_t tau0 = live ? RK_KEY_SENTINEL : 0u;      // a padded column never collects anything
                 if (live && p.tau_key && p.tau_count[un.q0 + et] >= p.kp) tau0 = rk_float_to_key(p.tau_key[(size_t) (un.q0 + et) * p.kp + (p.kp - 1)]);
                 c.tau[et] = tau0;
+                tauf[et] = bs_tau_float(tau0);
                 c.cnt[et] = 0;
                 s_trunc[et] = p.trunc + (live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u);
                 uint64_t w0 = ~0ull, w1 = 0ull;
@@ -360,35 +363,71 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
                 const bool valid = row < p.nrows && own_n;
                 const float xn = xn_n;
-                const uint32_t m0 = (uint32_t) ma_n, m1 = (uint32_t) (ma_n >> 32), m2 = (uint32_t) mb_n, m3 = (uint32_t) (mb_n >> 32);
+                // which of this warp's queries may see each row: the 32 rows of a warp belong to a few documents, so
+                // the mask test runs once per (distinct row mask, query) — lanes test 16 queries at a time and vote —
+                // instead of once per (row, query)
+                uint32_t hitw[4] = {0u, 0u, 0u, 0u};
+                {
+                    const uint64_t ma = ma_n, mb = mb_n;
+                    const uint32_t grp = __match_any_sync(0xffffffffu, ma) & __match_any_sync(0xffffffffu, mb);
+                    uint32_t todo = 0xffffffffu;
+                    while (todo) {
+                        const int ld = __ffs((int) todo) - 1;
+                        const uint32_t g = __shfl_sync(0xffffffffu, grp, ld);
+                        const uint64_t a = __shfl_sync(0xffffffffu, ma, ld), b = __shfl_sync(0xffffffffu, mb, ld);
+                        todo &= ~g;
+                        if ((a | b) == 0ull) continue;
+                        const bool mine = (g >> lane) & 1u;
+                        const uint32_t a0 = (uint32_t) a, a1 = (uint32_t) (a >> 32), b0 = (uint32_t) b, b1 = (uint32_t) (b >> 32);
+#pragma unroll
+                        for (int i = 0; i < 8; i++) {
+                            const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
+                            if (c0 >= ncol) break;
+                            const uint4 qa = s_qa[c0 + (uint32_t) (lane & 15)];
+                            const uint32_t hit = (a0 & qa.x) | (a1 & qa.y) | (b0 & qa.z) | (b1 & qa.w);
+                            const uint32_t bal = __ballot_sync(0xffffffffu, hit != 0) & 0xFFFFu;
+                            if (mine) hitw[i >> 1] |= bal << (16 * (i & 1));
+                        }
+                    }
+                }
                 r0_cur = r0_next;
                 r0_next = tile_row0(ti + 2);
                 fetch_row(r0_cur);
                 b2_mbar_wait(&tfull[buf], tph);
                 bs_fence_after();
                 const uint32_t taddr = tmem_base + buf * B2_N + ((uint32_t) (quarter * 32) << 16);
-                for (uint32_t c0 = 16u * (uint32_t) chalf; c0 < ncol; c0 += 32) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
+                    if (c0 >= ncol) break;
+                    const uint32_t h16 = (hitw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu;
+                    if (W <= 2 && !__any_sync(0xffffffffu, h16 != 0)) continue;      // none of the 32 rows is visible to these 16 queries
                     uint32_t r[16];
                     bs_tmem_ld16(taddr + c0, r);
+                    // straight-line: per column one FMA, a quarter of a 16-byte threshold load, one compare
                     uint32_t pass = 0;
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        const uint32_t q = c0 + j;
-                        const uint4 qa = s_qa[q];
-                        const float v = __uint_as_float(r[j]);
-                        const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn) : -v;
-                        const uint32_t hit = (m0 & qa.x) | (m1 & qa.y) | (m2 & qa.z) | (m3 & qa.w);
-                        const uint32_t key = rk_float_to_key(dist);
-                        r[j] = key;
-                        pass |= (uint32_t) (hit != 0 && key <= c.tau[q]) << j;
+                    for (int j4 = 0; j4 < 4; j4++) {
+                        const float4 t4 = reinterpret_cast<const float4 *>(tauf + c0)[j4];
+                        const float tj[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+                        for (int jj = 0; jj < 4; jj++) {
+                            const int j = j4 * 4 + jj;
+                            const float v = __uint_as_float(r[j]);
+                            const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn) : -v;
+                            r[j] = __float_as_uint(dist);
+                            pass |= (uint32_t) (dist <= tj[jj]) << j;
+                        }
                     }
+                    pass &= h16;
                     if (W > 2 && p.use_mask && valid) {
+                        // more than 128 roles: the remaining mask words (rare, slow path)
 #pragma unroll
                         for (int j = 0; j < 16; j++) {
                             const uint32_t q = c0 + j;
                             uint64_t hit = 0;
                             for (int w = 2; w < W; w++) hit |= p.rowmask[row * W + w] & s_um[q * W + w];
-                            if (hit != 0 && r[j] <= c.tau[q]) pass |= 1u << j;
+                            if (hit != 0 && __uint_as_float(r[j]) <= tauf[q]) pass |= 1u << j;
                         }
                     }
                     if (__any_sync(0xffffffffu, pass != 0)) {
@@ -397,7 +436,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                             if (pass & (1u << j)) {
                                 const uint32_t q = c0 + j;
                                 const uint32_t slot = atomicAdd(&c.cnt[q], 1u);
-                                __stcg(&c.scratch[(size_t) q * BS_CAP + slot], make_uint2(r[j], (uint32_t) row));
+                                __stcg(&c.scratch[(size_t) q * BS_CAP + slot], make_uint2(rk_float_to_key(__uint_as_float(r[j])), (uint32_t) row));
                             }
                         }
                     }
@@ -420,7 +459,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                                 m = bs_warp_filter(c, (int) q, m, tau);
                                 if (lane == 0) *s_trunc[q] = 1;
                             }
-                            if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; }
+                            if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; tauf[q] = bs_tau_float(tau); }
                         }
                     }
                     esync();
@@ -438,7 +477,8 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                     if (n > BS_SORT_MAX) n = BS_SORT_MAX;
                 }
                 const size_t list = (size_t) un.list_base + q;
-                bs_warp_emit(c, (int) q, n, (uint32_t) p.kp, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
+                if (n <= (uint32_t) p.kp) bs_warp_emit_unsorted(c, (int) q, n, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
+                else bs_warp_emit(c, (int) q, n, (uint32_t) p.kp, p.cand_key + list * p.kp, p.cand_row + list * p.kp, p.cand_count + list);
             }
         }
     }

@@ -69,6 +69,14 @@ __device__ __forceinline__ uint64_t bs_smem_desc(uint32_t smem_addr)
 }
 
 
+// A threshold key as the float the epilogue compares ordering values with: `v <= bs_tau_float(tau)` holds for every
+// v with rk_float_to_key(v) <= tau (it may also admit +0.0 against a threshold of -0.0: an extra candidate, dropped by
+// the next compaction).  The open threshold admits everything but NaN; key 0 (a padded column) admits nothing.
+__device__ __forceinline__ float bs_tau_float(uint32_t tau)
+{
+    return tau == RK_KEY_SENTINEL ? __int_as_float(0x7f800000) : rk_key_to_float(tau);
+}
+
 struct BsCtx {
     uint32_t *tau, *cnt, *hist, *sel;
     uint2 *scratch;     // this CTA's [BS_N][BS_CAP]
@@ -203,6 +211,40 @@ __device__ __forceinline__ void bs_warp_emit(const BsCtx &c, int q, uint32_t n, 
         out_row[i] = (uint32_t) v;
     }
     if (c.lane == 0) *out_count = (int32_t) m;
+    __syncwarp();
+}
+
+// The first n <= kp entries of a query's buffer as the unit's candidate list, UNSORTED except that the largest
+// (key, row) goes last — all the per-query merge (rk_select_kernel, `unsorted`) needs: a full list's last key bounds
+// the kp-th best from above.  Keeps the sort out of the scoring kernel's tail.
+__device__ __forceinline__ void bs_warp_emit_unsorted(const BsCtx &c, int q, uint32_t n, uint32_t *out_key, uint32_t *out_row,
+                                                      int32_t *out_count)
+{
+    const uint2 *buf = c.scratch + (size_t) q * BS_CAP;
+    uint64_t best = 0;
+    uint32_t besti = 0;
+    for (uint32_t i = c.lane; i < n; i += 32) {
+        const uint2 e = __ldcg(&buf[i]);
+        const uint64_t v = ((uint64_t) e.x << 32) | e.y;
+        if (v >= best) { best = v; besti = i; }
+        out_key[i] = e.x;
+        out_row[i] = e.y;
+    }
+    uint64_t wbest = best;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const uint64_t u = __shfl_xor_sync(0xffffffffu, wbest, o); wbest = u > wbest ? u : wbest; }
+    __syncwarp();
+    if (n > 1) {
+        // (key, row) pairs of one list are distinct: exactly one lane owns the largest
+        const bool owner = best == wbest && (uint32_t) c.lane < n;
+        const uint32_t oi = __shfl_sync(0xffffffffu, besti, __ffs((int) __ballot_sync(0xffffffffu, owner)) - 1);
+        if (c.lane == 0 && oi != n - 1) {
+            const uint2 last = __ldcg(&buf[n - 1]);
+            out_key[oi] = last.x; out_row[oi] = last.y;
+            out_key[n - 1] = (uint32_t) (wbest >> 32); out_row[n - 1] = (uint32_t) wbest;
+        }
+    }
+    if (c.lane == 0) *out_count = (int32_t) n;
     __syncwarp();
 }
 

@@ -77,19 +77,39 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     __shared__ uint32_t s_overflow;
     if (t == 0) s_overflow = 0;
     __syncthreads();
+    // One warp per list, 32 consecutive entries per step (one coalesced load instead of a chain of dependent ones).
+    // Unsorted lists (tensor-engine nominations: only the last entry is known to be the largest) are read whole.
     {
         const uint32_t tau = s_tau;
-        for (uint32_t j = t; j < nl; j += RK_SEL_THREADS) {
+        const int warp = t >> 5, lane = t & 31;
+        for (uint32_t j = (uint32_t) warp; j < nl; j += RK_SEL_THREADS / 32) {
             const int cnt = list_count(j);
             const size_t a4 = b4(j), a8 = b8(j);
-            for (int i = 0; i < cnt; i++) {
-                const uint32_t key = load_key(a4 + i);
-                if (key > tau || key == RK_KEY_SENTINEL) break;
-                const uint64_t tid = load_tid(a8 + i, a4 + i);
-                if (tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u) break;   // exchange-form padding
-                const uint32_t slot = atomicAdd(&s_count, 1u);
-                if (slot >= RK_CAND_CAP) { s_overflow = 1; break; }
-                s_key[slot] = key; s_tid[slot] = tid; s_row[slot] = p.cand_row[a4 + i];
+            for (int i0 = 0; i0 < cnt; i0 += 32) {
+                const int i = i0 + lane;
+                bool take = false;
+                uint32_t key = RK_KEY_SENTINEL;
+                uint64_t tid = 0;
+                if (i < cnt) {
+                    key = load_key(a4 + i);
+                    if (key <= tau && key != RK_KEY_SENTINEL) {
+                        tid = load_tid(a8 + i, a4 + i);
+                        take = !(tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u);   // exchange-form padding
+                    }
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, take);
+                if (bal) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&s_count, (uint32_t) __popc(bal));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (take) {
+                        const uint32_t slot = base + (uint32_t) __popc(bal & ((1u << lane) - 1u));
+                        if (slot >= RK_CAND_CAP) s_overflow = 1;
+                        else { s_key[slot] = key; s_tid[slot] = tid; s_row[slot] = p.cand_row[a4 + i]; }
+                    }
+                }
+                // sorted list: the first entry that fails ends the prefix
+                if (!p.unsorted && __any_sync(0xffffffffu, i < cnt && !take)) break;
             }
         }
     }

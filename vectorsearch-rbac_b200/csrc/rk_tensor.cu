@@ -581,6 +581,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     sp.k = kp;
     sp.metric = ix->metric;
     sp.dedup = 0;
+    sp.unsorted = 1;       // unit lists come unsorted, largest entry last (bs_warp_emit_unsorted)
 
     const int slot_ev = (int) (ws.ring_n % RK_TIMING_RING);
     if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot_ev], st));
