@@ -119,6 +119,63 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     if (overflow && t == 0) s_count = 0;
     __syncthreads();
 
+    __shared__ uint32_t s_hist[256], s_sel[2];
+    // keeps the entries with key <= (k-th smallest key) at the front of the buffer; returns how many
+    auto sel_reduce = [&](int n) -> int {
+        uint32_t prefix = 0, mask = 0, kk = (uint32_t) k;
+#pragma unroll 1
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            if (t < 256) s_hist[t] = 0;
+            __syncthreads();
+            for (int i = t; i < n; i += RK_SEL_THREADS) {
+                const uint32_t kv = s_key[i];
+                if ((kv & mask) == prefix) atomicAdd(&s_hist[(kv >> shift) & 255u], 1u);
+            }
+            __syncthreads();
+            if (t < 32) {
+                uint32_t h[8], tot = 0;
+#pragma unroll
+                for (int b = 0; b < 8; b++) { h[b] = s_hist[t * 8 + b]; tot += h[b]; }
+                uint32_t inc = tot;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (t >= o) inc += u; }
+                uint32_t run = inc - tot;
+#pragma unroll
+                for (int b = 0; b < 8; b++) {
+                    if (run < kk && kk <= run + h[b]) { s_sel[0] = (uint32_t) (t * 8 + b); s_sel[1] = kk - run; }
+                    run += h[b];
+                }
+            }
+            __syncthreads();
+            prefix |= s_sel[0] << shift;
+            mask |= 0xFFu << shift;
+            kk = s_sel[1];
+        }
+        const uint32_t kth = prefix;
+        constexpr int PER = RK_CAND_CAP / RK_SEL_THREADS;      // 4
+        uint32_t mk[PER], mr[PER];
+        uint64_t mt[PER];
+        int mc = 0;
+#pragma unroll
+        for (int i = 0; i < PER; i++) {
+            const int idx = t * PER + i;
+            if (idx < n && s_key[idx] <= kth) { mk[mc] = s_key[idx]; mr[mc] = s_row[idx]; mt[mc] = s_tid[idx]; mc++; }
+        }
+        int inc = mc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if ((t & 31) >= o) inc += v; }
+        if ((t & 31) == 31) s_scan[t >> 5] = (uint32_t) inc;
+        __syncthreads();                      // also orders the reads above before the writes below
+        int woff = 0, tot = 0;
+        for (int w = 0; w < RK_SEL_THREADS / 32; w++) { if (w < (t >> 5)) woff += (int) s_scan[w]; tot += (int) s_scan[w]; }
+        const int pos = woff + inc - mc;
+#pragma unroll
+        for (int i = 0; i < PER; i++)
+            if (i < mc) { s_key[pos + i] = mk[i]; s_row[pos + i] = mr[i]; s_tid[pos + i] = mt[i]; }
+        __syncthreads();
+        return tot;
+    };
+
     const size_t total = overflow ? (size_t) nl * k : 0;
     for (size_t c0 = 0; c0 < total || c0 == 0; c0 += RK_SEL_CHUNK) {
         const uint32_t tau = s_tau;
@@ -138,9 +195,13 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
             }
         }
         __syncthreads();
-        const int n = (int) s_count;
+        int n = (int) s_count;
         const bool lastc = c0 + RK_SEL_CHUNK >= total;
         if (lastc || n > RK_CAND_CAP - RK_SEL_CHUNK) {
+            // Without dedup only the k smallest keys can reach the output: cut the buffer down to them (exact 4-pass radix
+            // select of the k-th smallest key, ties kept) before sorting, so the sort runs over ~k entries instead of up to
+            // RK_CAND_CAP.  (With dedup a duplicate may sit among the k smallest, so everything gathered is sorted.)
+            if (!p.dedup && n > 2 * k && n > 64) n = sel_reduce(n);
             rk_bitonic_sort(cb, n, t, RK_SEL_THREADS, sync);
             int m = n;
             if (p.dedup && n > 1) {
