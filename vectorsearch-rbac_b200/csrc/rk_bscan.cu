@@ -37,7 +37,7 @@
 // ---------------------------------------------------------------------------------------------
 
 struct BsSmem {
-    uint32_t off_stage, off_bar, off_tmem, off_tau, off_cnt, off_trunc, off_qa, off_um, off_hist, off_sel, off_sort, total;
+    uint32_t off_stage, off_bar, off_tmem, off_tau, off_tauf, off_cnt, off_trunc, off_qa, off_um, off_hist, off_sel, off_sort, total;
 };
 
 __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
@@ -48,6 +48,7 @@ __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
     s.off_bar = o; o += 8u * (2 * BS_STAGES + 4);
     s.off_tmem = o; o += 16;
     s.off_tau = o; o += BS_N * 4;
+    s.off_tauf = o; o += BS_N * 4;     // the same thresholds as floats (16-byte aligned: read four at a time)
     s.off_cnt = o; o += BS_N * 4;
     o = (o + 15) & ~15u;
     s.off_trunc = o; o += BS_N * 8;
@@ -167,6 +168,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         const int et = ew * 32 + lane;                 // 0..127 epilogue thread index
         BsCtx c;
         c.tau = reinterpret_cast<uint32_t *>(smem + L.off_tau);
+        float *tauf = reinterpret_cast<float *>(smem + L.off_tauf);
         c.cnt = reinterpret_cast<uint32_t *>(smem + L.off_cnt);
         c.hist = reinterpret_cast<uint32_t *>(smem + L.off_hist) + ew * 256;
         c.sel = reinterpret_cast<uint32_t *>(smem + L.off_sel) + ew * 4;
@@ -190,6 +192,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 // sees bounds the kp-th smallest over all of them from above
                 if (live && p.tau_key && p.tau_count[un.q0 + et] >= p.kp) tau0 = rk_float_to_key(p.tau_key[(size_t) (un.q0 + et) * p.kp + (p.kp - 1)]);
                 c.tau[et] = tau0;
+                tauf[et] = bs_tau_float(tau0);
                 c.cnt[et] = 0;
                 s_trunc[et] = p.trunc + (live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u);
                 uint64_t w0 = ~0ull, w1 = 0ull;        // no permission filter: every row passes
@@ -226,12 +229,10 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         const ulonglong2 m2 = reinterpret_cast<const ulonglong2 *>(p.rowmask2)[rr];
                         ma_n = m2.x;
                         mb_n = m2.y;
+                        // (the comparison with the unit's class waits until the values are used, one tile later: doing it
+                        // here would expose the load's latency on every tile)
                         own_n = true;
-                        if (umask) {
-                            own_n = ma_n == um0 && mb_n == um1;
-                            for (int w = 2; w < W && own_n; w++) own_n = p.rowmask[rr * W + w] == umask[w];
-                            if (!own_n) { ma_n = 0; mb_n = 0; }
-                        }
+                        if (umask) for (int w = 2; w < W && own_n; w++) own_n = p.rowmask[rr * W + w] == umask[w];
                     } else {
                         ma_n = 1ull;                    // matches the all-ones query word
                     }
@@ -241,9 +242,35 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
+                if (umask && !(own_n && ma_n == um0 && mb_n == um1)) { own_n = false; ma_n = 0; mb_n = 0; }
                 const bool valid = row < p.nrows && own_n;
                 const float xn = xn_n;
-                const uint32_t m0 = (uint32_t) ma_n, m1 = (uint32_t) (ma_n >> 32), m2 = (uint32_t) mb_n, m3 = (uint32_t) (mb_n >> 32);
+                // which queries may see each row: the 32 rows of a warp belong to a few documents, so the mask test runs
+                // once per (distinct row mask, query) — lanes test 16 queries at a time and vote — not per (row, query)
+                uint64_t hit_lo = 0ull, hit_hi = 0ull;      // 16 bits per chunk of 16 queries
+                {
+                    const uint64_t ma = ma_n, mb = mb_n;
+                    const uint32_t grp = __match_any_sync(0xffffffffu, ma) & __match_any_sync(0xffffffffu, mb);
+                    uint32_t todo = 0xffffffffu;
+                    while (todo) {
+                        const int ld = __ffs((int) todo) - 1;
+                        const uint32_t g = __shfl_sync(0xffffffffu, grp, ld);
+                        const uint64_t a = __shfl_sync(0xffffffffu, ma, ld), b = __shfl_sync(0xffffffffu, mb, ld);
+                        todo &= ~g;
+                        if ((a | b) == 0ull) continue;
+                        const bool mine = (g >> lane) & 1u;
+                        const uint32_t a0 = (uint32_t) a, a1 = (uint32_t) (a >> 32), b0 = (uint32_t) b, b1 = (uint32_t) (b >> 32);
+#pragma unroll 1
+                        for (int i = 0; i < 8; i++) {
+                            const uint32_t c0 = 16u * (uint32_t) i;
+                            if (c0 >= ncol) break;
+                            const uint4 qa = s_qa[c0 + (uint32_t) (lane & 15)];
+                            const uint32_t hit = (a0 & qa.x) | (a1 & qa.y) | (b0 & qa.z) | (b1 & qa.w);
+                            const uint32_t bal = __ballot_sync(0xffffffffu, hit != 0) & 0xFFFFu;
+                            if (mine) { if (i < 4) hit_lo |= (uint64_t) bal << (16 * i); else hit_hi |= (uint64_t) bal << (16 * (i - 4)); }
+                        }
+                    }
+                }
                 // issue the next tile's loads now; they are consumed on the next iteration
                 r0_cur = r0_next;
                 r0_next = tile_row0(ti + 2);
@@ -251,22 +278,30 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 rk_mbar_wait(&tfull[buf], tph);
                 bs_fence_after();
                 const uint32_t taddr = tmem_base + buf * BS_N + ((uint32_t) (quarter * 32) << 16);
-                for (uint32_t c0 = 0; c0 < ncol; c0 += 16) {
+#pragma unroll 1
+                for (int i = 0; i < 8; i++) {
+                    const uint32_t c0 = 16u * (uint32_t) i;
+                    if (c0 >= ncol) break;
+                    const uint32_t h16 = (uint32_t) (i < 4 ? hit_lo >> (16 * i) : hit_hi >> (16 * (i - 4))) & 0xFFFFu;
+                    if (W <= 2 && !__any_sync(0xffffffffu, h16 != 0)) continue;      // none of the 32 rows is visible to these 16 queries
                     uint32_t r[16];
                     bs_tmem_ld16(taddr + c0, r);
-                    // straight-line: 16 columns, one 16-byte + two 4-byte broadcast loads each, no branches
+                    // straight-line: per column one FMA, a quarter of a 16-byte threshold load, one compare
                     uint32_t pass = 0;
 #pragma unroll
-                    for (int j = 0; j < 16; j++) {
-                        const uint32_t q = c0 + j;
-                        const uint4 qa = s_qa[q];
-                        const float v = __uint_as_float(r[j]);
-                        const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn) : -v;
-                        const uint32_t hit = (m0 & qa.x) | (m1 & qa.y) | (m2 & qa.z) | (m3 & qa.w);
-                        const uint32_t key = rk_float_to_key(dist);
-                        r[j] = key;
-                        pass |= (uint32_t) (hit != 0 && key <= c.tau[q]) << j;
+                    for (int j4 = 0; j4 < 4; j4++) {
+                        const float4 t4 = reinterpret_cast<const float4 *>(tauf + c0)[j4];
+                        const float tj[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+                        for (int jj = 0; jj < 4; jj++) {
+                            const int j = j4 * 4 + jj;
+                            const float v = __uint_as_float(r[j]);
+                            const float dist = METRIC == 0 ? fmaf(-2.0f, v, xn) : -v;
+                            r[j] = __float_as_uint(dist);
+                            pass |= (uint32_t) (dist <= tj[jj]) << j;
+                        }
                     }
+                    pass &= h16;
                     if (W > 2 && p.use_mask && valid) {
                         // more than 128 roles: the remaining mask words (rare, slow path)
 #pragma unroll
@@ -274,7 +309,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                             const uint32_t q = c0 + j;
                             uint64_t hit = 0;
                             for (int w = 2; w < W; w++) hit |= p.rowmask[row * W + w] & s_um[q * W + w];
-                            if (hit != 0 && r[j] <= c.tau[q]) pass |= 1u << j;
+                            if (hit != 0 && __uint_as_float(r[j]) <= tauf[q]) pass |= 1u << j;
                         }
                     }
                     if (__any_sync(0xffffffffu, pass != 0)) {
@@ -283,7 +318,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                             if (pass & (1u << j)) {
                                 const uint32_t q = c0 + j;
                                 const uint32_t slot = atomicAdd(&c.cnt[q], 1u);
-                                __stcg(&c.scratch[(size_t) q * BS_CAP + slot], make_uint2(r[j], (uint32_t) row));
+                                __stcg(&c.scratch[(size_t) q * BS_CAP + slot], make_uint2(rk_float_to_key(__uint_as_float(r[j])), (uint32_t) row));
                             }
                         }
                     }
@@ -302,7 +337,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         const uint32_t n = c.cnt[q];
                         if (n > BS_CAP - 2 * BS_M) {
                             uint32_t tau;
-                            uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                            uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
                             if (m > BS_CAP / 2 && tau > 0) {
                                 // more than half the buffer ties at the kp-th key: drop that key altogether
                                 // and record that the list is no longer complete (the query is re-run exactly)
@@ -310,7 +345,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                                 m = bs_warp_filter(c, (int) q, m, tau);
                                 if (lane == 0) *s_trunc[q] = 1;
                             }
-                            if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; }
+                            if (lane == 0) { c.cnt[q] = m; c.tau[q] = tau; tauf[q] = bs_tau_float(tau); }
                         }
                     }
                     esync();

@@ -346,12 +346,10 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                         const ulonglong2 m2 = reinterpret_cast<const ulonglong2 *>(p.rowmask2)[rr];
                         ma_n = m2.x;
                         mb_n = m2.y;
+                        // (the comparison with the unit's class waits until the values are used, one tile later: doing it
+                        // here would expose the load's latency on every tile)
                         own_n = true;
-                        if (umask) {
-                            own_n = ma_n == um0 && mb_n == um1;
-                            for (int w = 2; w < W && own_n; w++) own_n = p.rowmask[rr * W + w] == umask[w];
-                            if (!own_n) { ma_n = 0; mb_n = 0; }
-                        }
+                        if (umask) for (int w = 2; w < W && own_n; w++) own_n = p.rowmask[rr * W + w] == umask[w];
                     } else {
                         ma_n = 1ull;
                     }
@@ -361,12 +359,13 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
+                if (umask && !(own_n && ma_n == um0 && mb_n == um1)) { own_n = false; ma_n = 0; mb_n = 0; }
                 const bool valid = row < p.nrows && own_n;
                 const float xn = xn_n;
                 // which of this warp's queries may see each row: the 32 rows of a warp belong to a few documents, so
                 // the mask test runs once per (distinct row mask, query) — lanes test 16 queries at a time and vote —
                 // instead of once per (row, query)
-                uint32_t hitw[4] = {0u, 0u, 0u, 0u};
+                uint64_t hit_lo = 0ull, hit_hi = 0ull;      // 16 bits per chunk of 16 queries
                 {
                     const uint64_t ma = ma_n, mb = mb_n;
                     const uint32_t grp = __match_any_sync(0xffffffffu, ma) & __match_any_sync(0xffffffffu, mb);
@@ -379,14 +378,14 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                         if ((a | b) == 0ull) continue;
                         const bool mine = (g >> lane) & 1u;
                         const uint32_t a0 = (uint32_t) a, a1 = (uint32_t) (a >> 32), b0 = (uint32_t) b, b1 = (uint32_t) (b >> 32);
-#pragma unroll
+#pragma unroll 1
                         for (int i = 0; i < 8; i++) {
                             const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
                             if (c0 >= ncol) break;
                             const uint4 qa = s_qa[c0 + (uint32_t) (lane & 15)];
                             const uint32_t hit = (a0 & qa.x) | (a1 & qa.y) | (b0 & qa.z) | (b1 & qa.w);
                             const uint32_t bal = __ballot_sync(0xffffffffu, hit != 0) & 0xFFFFu;
-                            if (mine) hitw[i >> 1] |= bal << (16 * (i & 1));
+                            if (mine) { if (i < 4) hit_lo |= (uint64_t) bal << (16 * i); else hit_hi |= (uint64_t) bal << (16 * (i - 4)); }
                         }
                     }
                 }
@@ -396,11 +395,11 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 b2_mbar_wait(&tfull[buf], tph);
                 bs_fence_after();
                 const uint32_t taddr = tmem_base + buf * B2_N + ((uint32_t) (quarter * 32) << 16);
-#pragma unroll
+#pragma unroll 1
                 for (int i = 0; i < 8; i++) {
                     const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
                     if (c0 >= ncol) break;
-                    const uint32_t h16 = (hitw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu;
+                    const uint32_t h16 = (uint32_t) (i < 4 ? hit_lo >> (16 * i) : hit_hi >> (16 * (i - 4))) & 0xFFFFu;
                     if (W <= 2 && !__any_sync(0xffffffffu, h16 != 0)) continue;      // none of the 32 rows is visible to these 16 queries
                     uint32_t r[16];
                     bs_tmem_ld16(taddr + c0, r);
@@ -453,7 +452,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                         const uint32_t n = c.cnt[q];
                         if (n > BS_CAP - 2 * B2_M) {
                             uint32_t tau;
-                            uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                            uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
                             if (m > BS_CAP / 2 && tau > 0) {
                                 tau -= 1u;
                                 m = bs_warp_filter(c, (int) q, m, tau);

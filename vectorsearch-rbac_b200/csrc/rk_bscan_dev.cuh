@@ -84,9 +84,12 @@ struct BsCtx {
     int lane;
 };
 
-// Exact kp-th smallest key of one query's buffer by a warp-level 4-pass radix select, then in-place
+// kp-th smallest key of one query's buffer by a warp-level radix select (8 bits per pass), then in-place
 // compaction key <= tau.  n <= BS_CAP.  Returns the new count; *tau_out receives the threshold.
-__device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint32_t n, uint32_t kp, uint32_t *tau_out)
+// exact: all four passes, tau = the kp-th smallest key.  Otherwise the select stops after two or three passes as soon
+// as the bucket holding the kp-th key is small (tau = the bucket's upper end: at most kp + 128 entries survive, and at
+// most BS_CAP / 2) — a mid-unit compaction only has to make room and tighten the threshold, not hit kp exactly.
+__device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint32_t n, uint32_t kp, uint32_t *tau_out, bool exact = true)
 {
     uint2 *buf = c.scratch + (size_t) q * BS_CAP;
     uint32_t key[BS_CAP / 32];
@@ -95,7 +98,8 @@ __device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint3
         const uint32_t i = (uint32_t) c.lane + 32u * j;
         key[j] = i < n ? __ldcg(&buf[i].x) : RK_KEY_SENTINEL;
     }
-    uint32_t prefix = 0, mask = 0, kk = kp;
+    uint32_t prefix = 0, mask = 0, kk = kp, below = 0, tau = 0;
+    const uint32_t loose = min(kp + 128u, (uint32_t) BS_CAP / 2u);
 #pragma unroll 1
     for (int shift = 24; shift >= 0; shift -= 8) {
 #pragma unroll
@@ -116,16 +120,19 @@ __device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint3
         uint32_t run = inc - tot;
 #pragma unroll
         for (int b = 0; b < 8; b++) {
-            if (run < kk && kk <= run + h[b]) { c.sel[0] = (uint32_t) (c.lane * 8 + b); c.sel[1] = kk - run; }
+            if (run < kk && kk <= run + h[b]) { c.sel[0] = (uint32_t) (c.lane * 8 + b); c.sel[1] = kk - run; c.sel[2] = run; c.sel[3] = h[b]; }
             run += h[b];
         }
         __syncwarp();
         prefix |= c.sel[0] << shift;
         mask |= 0xFFu << shift;
         kk = c.sel[1];
+        below += c.sel[2];                        // keys below the bucket that holds the kp-th
+        const uint32_t in_bucket = c.sel[3];
         __syncwarp();
+        tau = prefix | ((1u << shift) - 1u);      // the bucket's largest key
+        if (!exact && shift <= 16 && below + in_bucket <= loose) break;
     }
-    const uint32_t tau = prefix;
     // compaction: rows of the survivors are read before anything is overwritten
     uint32_t row[BS_CAP / 32];
     uint32_t mine = 0;
