@@ -466,7 +466,7 @@ def main():
         byts = float(st["algo_bytes"])
         intensity = flop / max(byts, 1.0)
         ridge = tf32 * 1e12 / (hbm * 1e9)
-        common = {"kernel": "rk_bscan_kernel", "plan": plan + (" + sampling pass" if st["tensor_plan"] & 16 else ""),
+        common = {"kernel": "rk_bscan2_kernel (CTA pairs, tcgen05 cta_group::2)" if st["tensor_plan"] & 32 else "rk_bscan_kernel", "plan": plan + (" + sampling pass" if st["tensor_plan"] & 16 else ""),
                   "kernel_ms": kms, "launches_timed": int(len(r["scan_ms"])), "flop_per_launch": flop, "bytes_per_launch": byts,
                   "plan_bytes_per_launch": float(st["tensor_plan_bytes"]),
                   "intensity_flop_per_byte": intensity, "ridge_flop_per_byte": ridge,

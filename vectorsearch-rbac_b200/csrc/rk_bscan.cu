@@ -461,7 +461,14 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
             const float a_last = p.sel_key[(size_t) q * p.kp + (n - 1)] + (METRIC == 0 ? p.qnorm[q] : 0.f);
             const float e_k = rk_key_to_float(s_key[cnt - 1]);
             float eps = 0.f;
-            if (p.eps_scale > 0.f) eps = p.eps_scale * sqrtf(p.xnorm_max * p.qnorm[q]) + 1e-6f * (p.xnorm_max + p.qnorm[q]);
+            float eps_scale = p.eps_scale;
+            if (p.probe) {
+                // exact iff operands are small integers (exact in TF32, products exact in fp32) and every partial sum
+                // stays below 2^24: |x|^2 + |q|^2 + 2 |x.q| <= (|x| + |q|)^2 by Cauchy-Schwarz
+                const float nx = sqrtf(p.xnorm_max), nq = sqrtf(__uint_as_float((uint32_t) (p.probe[4] & 0xFFFFFFFFull)));
+                if (p.x_integer && p.probe[0] == 0ull && (nx + nq) * (nx + nq) < 16700000.0f) eps_scale = 0.f;
+            }
+            if (eps_scale > 0.f) eps = eps_scale * sqrtf(p.xnorm_max * p.qnorm[q]) + 1e-6f * (p.xnorm_max + p.qnorm[q]);
             if (cnt < k || !(a_last - eps > e_k)) uncertain = 1;
         }
         p.uncertain[oq] = uncertain;

@@ -146,6 +146,10 @@ struct RkRescoreParams {
     const int32_t *sel_count;
     const int32_t *trunc;
     float eps_scale, xnorm_max;  // error bound of the tensor-core value: eps_scale * sqrt(xnorm_max * qnorm) (0 = exact)
+    // when set, the kernel decides itself whether TF32 was exact for this batch (no host round trip between the passes):
+    // probe[0] = query elements that are not small integers, low word of probe[4] = bits of the largest squared query norm
+    const unsigned long long *probe;
+    int x_integer;               // the corpus holds only small integers
     uint64_t *out_tid;
     uint32_t *out_doc;
     double *out_dist;

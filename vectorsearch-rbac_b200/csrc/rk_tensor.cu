@@ -621,16 +621,10 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     RK_CUDA(rk_launch_select(sp, (int) nq, st));
     launches++;
 
-    RK_CUDA(cudaStreamSynchronize(st));
-    float qnorm_max;
-    { uint32_t b = (uint32_t) (hprobe[4] & 0xFFFFFFFFull); memcpy(&qnorm_max, &b, 4); }
-    // exact iff operands are small integers (exact in TF32, products exact in fp32) and every partial
-    // sum stays below 2^24: |x|^2 + |q|^2 + 2 |x.q| <= (|x| + |q|)^2 by Cauchy-Schwarz
-    const double nx = std::sqrt((double) ts.xnorm_max), nqm = std::sqrt((double) qnorm_max);
-    const bool exact = ts.x_integer && hprobe[0] == 0 && (nx + nqm) * (nx + nqm) < 16777216.0;
     // TF32 keeps 10 mantissa bits and the MMA truncates: each operand is off by < 2^-10 relative, a
-    // product by < 2^-9; |x.q| error <= 2^-9 * |x||q|; the L2 form doubles it
-    const float eps_scale = exact ? 0.f : (ix->metric == RK_METRIC_L2 ? 2.f : 1.f) * (1.0f / 512.0f);
+    // product by < 2^-9; |x.q| error <= 2^-9 * |x||q|; the L2 form doubles it.  Whether this batch is exact instead
+    // (small-integer corpus and queries) is decided by the re-score kernel from the probe results on the device.
+    const float eps_scale = (ix->metric == RK_METRIC_L2 ? 2.f : 1.f) * (1.0f / 512.0f);
 
     // exact re-score of every query's nominations in the caller's order (a query without lists gets an
     // empty result)
@@ -653,6 +647,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     rp.sel_count = ts.d_sel_count.as<int32_t>();
     rp.trunc = ts.d_flags.as<int32_t>() + nq;
     rp.eps_scale = eps_scale;
+    rp.probe = ts.d_probe.as<unsigned long long>();
+    rp.x_integer = ts.x_integer ? 1 : 0;
     rp.xnorm_max = ts.xnorm_max;
     rp.out_tid = out.out_tid;
     rp.out_doc = out.out_doc;
@@ -668,6 +664,10 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     RK_CUDA(cudaStreamSynchronize(st));
     for (size_t q = 0; q < nq; q++)
         if (hflags[q]) redo.push_back((uint32_t) q);
+    float qnorm_max;
+    { uint32_t b = (uint32_t) (hprobe[4] & 0xFFFFFFFFull); memcpy(&qnorm_max, &b, 4); }
+    const double nx = std::sqrt((double) ts.xnorm_max), nqm = std::sqrt((double) qnorm_max);
+    const bool exact = ts.x_integer && hprobe[0] == 0 && (nx + nqm) * (nx + nqm) < 16777216.0;      // (statistics only)
 
     ws.launches += launches;
     ws.segments = pm_.units.size() + ps_.units.size();
