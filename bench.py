@@ -61,6 +61,16 @@ WORKLOADS = {
 }
 
 
+# The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's "NCCL version ..." banner at the first
+# collective), so everything else written to fd 1 is sent to stderr and only emit() reaches the real stdout.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -74,6 +84,7 @@ def parse_args():
     ap.add_argument("--filter", default="", choices=["", "bitmask", "partition", "combination"])
     ap.add_argument("--engine", default="", choices=["", "scan", "tensor", "auto"], help="override the workload's headline engine")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-pipeline", action="store_true", help="N > 1: do not overlap a step's exchange with the next step's scan")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
     return ap.parse_args()
 
@@ -315,7 +326,7 @@ def run_reference(args, wl):
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -394,18 +405,25 @@ def main():
     def measure(eng):
         """One engine over the step: device-resident `value` leg, then the host-buffer `e2e` leg."""
         opts = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=eng)
+        # N > 1: the exchange of step i (all-gather + merge, side stream) overlaps the scan of step i + 1; every step's
+        # result is complete before the timed region ends (flush).  --no-pipeline serialises them.
+        step_fn = searcher.search_device if (world == 1 or args.no_pipeline) else searcher.search_device_pipelined
         for _ in range(max(3, args.warmup)):
-            searcher.search_device(Q, qusers, opts)
+            step_fn(Q, qusers, opts)
+        searcher.flush()
         barrier()
         launches0 = ix.stats()["total_launches"]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        searcher.stage_events = [] if world > 1 else None
         with ClockSampler(local_rank) as clk:
             e0.record(stream)
             for _ in range(args.steps):
-                out = searcher.search_device(Q, qusers, opts)
+                out = step_fn(Q, qusers, opts)
+            searcher.flush()
             e1.record(stream)
             barrier()
-        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary()}
+        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary(), "stages": searcher.stage_ms(), "pipelined": not (world == 1 or args.no_pipeline)}
+        searcher.stage_events = None
         st = ix.stats()
         r["stats"] = st
         r["launches"] = st["total_launches"] - launches0
@@ -503,6 +521,12 @@ def main():
             "gpu_launches": int(main_r["launches"]),
             "clocks": main_r["clk"],
         }
+        if main_r.get("stages"):
+            # rank 0's mean device time per stage of a step (the all-gather also absorbs waiting for the slowest rank)
+            line["stages_ms"] = main_r["stages"]
+        if world > 1:
+            line["config"]["exchange"] = ("all-gather + merge of step i on a side stream, overlapping the scan of step i + 1"
+                                          if main_r["pipelined"] else "all-gather + merge after every scan, same stream")
         if batched_r is not None:
             # the same step through RK_ENGINE_AUTO (batches of >= 32 exact scans go to the tcgen05 engine): identical
             # results, every row a group of queries shares read once
@@ -550,7 +574,7 @@ def main():
                 "sample": f"{S} of the step's {args.nq} queries, full visible row sets, {cores} threads on {cpu_model()}; "
                           "pgvector distance loops without PostgreSQL page/tuple/fmgr overhead",
                 "gpu_ids_match": ids_ok, "gpu_distances": dist_note, "gpu_distances_match": dist_ok}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ix.close()
     if world > 1:
         dist.destroy_process_group()

@@ -63,6 +63,19 @@ class ShardedSearcher:
         self._local_search = local_search or self._cuda_local_search
         self._merge = merge or self._cuda_merge
         self._bufs = {}
+        # optional per-stage CUDA events of every call (local search | all-gather | merge), for bench.py's "stages_ms"
+        self.stage_events = None
+
+    def stage_ms(self):
+        """Mean device time of the three stages over the calls recorded since stage_events was last reset."""
+        ev = self.stage_events or []
+        if not ev:
+            return None
+        torch.cuda.synchronize(self.device)
+        n = float(len(ev))
+        return {"local_search": sum(a.elapsed_time(b) for a, b, _, _ in ev) / n,
+                "all_gather": sum(b.elapsed_time(c) for _, b, c, _ in ev) / n,
+                "merge": sum(c.elapsed_time(d) for _, _, c, d in ev) / n}
 
     # -- default (CUDA) stages ---------------------------------------------------------------
     def _cuda_local_search(self, dQ: torch.Tensor, users: np.ndarray, opts, send: torch.Tensor) -> None:
@@ -78,8 +91,8 @@ class ShardedSearcher:
                                 o_dist.data_ptr(), o_cnt.data_ptr(), shard_stride_bytes=packed_bytes(nq, k))
 
     # -- buffers -----------------------------------------------------------------------------
-    def _get_bufs(self, nq: int, k: int):
-        keyb = (nq, k)
+    def _get_bufs(self, nq: int, k: int, which: int = 0):
+        keyb = (nq, k, which)
         if keyb not in self._bufs:
             dev = self.device
             nb = packed_bytes(nq, k)
@@ -100,14 +113,64 @@ class ShardedSearcher:
         nq, k = dQ.shape[0], opts.k
         users = np.ascontiguousarray(users, dtype=np.uint32)
         b = self._get_bufs(nq, k)
+        rec = self.stage_events is not None and self.device.type == "cuda"
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if rec else None
+        if rec: ev[0].record()
         self._local_search(dQ, users, opts, b["send"])
+        if rec: ev[1].record()
         if self.world > 1:
             dist.all_gather_into_tensor(b["recv"], b["send"], group=self.group)
             recv = b["recv"]
         else:
             recv = b["send"]
+        if rec: ev[2].record()
         self._merge(recv, nq, k, (b["tid"], b["doc"], b["dist"], b["cnt"]))
+        if rec:
+            ev[3].record()
+            self.stage_events.append(tuple(ev))
         return b["tid"], b["doc"], b["dist"], b["cnt"]
+
+    def search_device_pipelined(self, dQ: torch.Tensor, users: Sequence[int], opts):
+        """Same result as search_device, but the exchange (all-gather + G-way merge) of this batch runs on a side
+        stream while the current stream is free to start the NEXT batch's scan: with short scans (8 GPUs: 4 ms) the
+        exchange and the wait for the slowest rank would otherwise sit between two scans.  Two buffer sets alternate.
+        The returned tensors are complete once `flush()` (or the next-but-one call) has ordered the side stream
+        before the current one."""
+        if self.world == 1 or self.device.type != "cuda":
+            return self.search_device(dQ, users, opts)
+        nq, k = dQ.shape[0], opts.k
+        users = np.ascontiguousarray(users, dtype=np.uint32)
+        if not hasattr(self, "_side"):
+            self._side = torch.cuda.Stream(device=self.device)
+            self._pipe_n = 0
+            self._pipe_done = [None, None]
+        s = self._pipe_n & 1
+        self._pipe_n += 1
+        b = self._get_bufs(nq, k, s)
+        main = torch.cuda.current_stream(self.device)
+        if self._pipe_done[s] is not None:
+            main.wait_event(self._pipe_done[s])          # the exchange that last read this set's send buffer
+        self._local_search(dQ, users, opts, b["send"])
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._side.wait_event(ev)
+        with torch.cuda.stream(self._side):
+            dist.all_gather_into_tensor(b["recv"], b["send"], group=self.group)
+            self.index.set_stream(self._side.cuda_stream)
+            try:
+                self._merge(b["recv"], nq, k, (b["tid"], b["doc"], b["dist"], b["cnt"]))
+            finally:
+                self.index.set_stream(main.cuda_stream if main.cuda_stream else 1)
+            done = torch.cuda.Event()
+            done.record(self._side)
+        self._pipe_done[s] = done
+        return b["tid"], b["doc"], b["dist"], b["cnt"]
+
+    def flush(self) -> None:
+        """Orders every pipelined exchange issued so far before the current stream."""
+        for d in getattr(self, "_pipe_done", []):
+            if d is not None:
+                torch.cuda.current_stream(self.device).wait_event(d)
 
     def search(self, Q_host: torch.Tensor, users: Sequence[int], opts, out_host=None):
         """End-to-end call with HOST buffers: Q_host is a (pinned) CPU tensor [nq, dim]; results come
