@@ -58,6 +58,12 @@ WORKLOADS = {
                filter="combination", engine="tensor",
                desc="C2 Cohere-Wikipedia shape 1M x 768 fp32 inner product, random RBAC (1000 users, 100 roles, <=3 roles per "
                     "user, 450..900 documents per role), combination-role (user-level) filter, batched tensor-core exact top-100"),
+    "c5": dict(rows=1_000_000, dim=128, kind="sift", rpd=100, users=1000, roles=100, rbac="random", metric="l2",
+               filter="dynamic", engine="scan",
+               desc="C5 dynamic-partition workload replayed as GPU filtered scans: SIFT-1M-shape 1M x 128 fp32 L2, random RBAC "
+                    "(1000 users, 100 roles, <=3 roles per user), partitions from the AnonySys greedy role splitter restated with "
+                    "a linear scan-cost model at storage alpha = 2.0 (the optimiser's fitted HNSW constants are not shipped), "
+                    "per-row permission predicate inside impure partitions, exact top-100 (recall 1.0 >= the 0.95 target)"),
 }
 
 
@@ -81,7 +87,7 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=0, help="override corpus rows (debug)")
     ap.add_argument("--nq", type=int, default=1000)
     ap.add_argument("--k", type=int, default=100)
-    ap.add_argument("--filter", default="", choices=["", "bitmask", "partition", "combination"])
+    ap.add_argument("--filter", default="", choices=["", "bitmask", "partition", "combination", "dynamic"])
     ap.add_argument("--engine", default="", choices=["", "scan", "tensor", "auto"], help="override the workload's headline engine")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-pipeline", action="store_true", help="N > 1: do not overlap a step's exchange with the next step's scan")
@@ -358,8 +364,9 @@ def main():
     rows, dim, desc = wl["rows"], wl["dim"], wl["desc"]
     flt_name = args.filter or wl["filter"]
     metric = vr.METRIC_L2 if wl["metric"] == "l2" else vr.METRIC_IP
-    flt = {"bitmask": vr.FILTER_BITMASK, "partition": vr.FILTER_PARTITION, "combination": vr.FILTER_PARTITION}[flt_name]
-    layout = {"bitmask": 0, "partition": vr.LAYOUT_ROLE, "combination": vr.LAYOUT_COMBINATION}[flt_name]
+    flt = {"bitmask": vr.FILTER_BITMASK, "partition": vr.FILTER_PARTITION, "combination": vr.FILTER_PARTITION,
+           "dynamic": vr.FILTER_PARTITION}[flt_name]
+    layout = {"bitmask": 0, "partition": vr.LAYOUT_ROLE, "combination": vr.LAYOUT_COMBINATION, "dynamic": vr.LAYOUT_DYNAMIC}[flt_name]
     engine_name = args.engine or wl["engine"]
     engine = {"scan": vr.ENGINE_SCAN, "tensor": vr.ENGINE_TENSOR, "auto": vr.ENGINE_AUTO}[engine_name]
 
@@ -384,6 +391,11 @@ def main():
         ix.build_role_partitions()
     if flt_name == "combination":
         ix.build_combination_partitions()
+    layout_info = None
+    if flt_name == "dynamic":
+        from vectorsearch_rbac_b200 import dynamic_layout
+        parts_d, roleset_parts, layout_info = dynamic_layout.split_roles(dr, ur, alpha=2.0)
+        dynamic_layout.apply_layout(ix, parts_d, roleset_parts)
     ix.finalize()
     torch.cuda.empty_cache()
 
@@ -521,6 +533,8 @@ def main():
             "gpu_launches": int(main_r["launches"]),
             "clocks": main_r["clk"],
         }
+        if layout_info is not None:
+            line["config"]["dynamic_layout"] = layout_info
         if main_r.get("stages"):
             # rank 0's mean device time per stage of a step (the all-gather also absorbs waiting for the slowest rank)
             line["stages_ms"] = main_r["stages"]

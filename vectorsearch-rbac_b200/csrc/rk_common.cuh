@@ -8,6 +8,8 @@
 #define RK_SEG_ROWMASK 3u   // physical row range [begin,end), role mask tested per row through rowdoc[]
 
 #define RK_SEGF_MASKED 1u   // test the extent's role mask against the user's before loading it
+#define RK_SEGF_MERGE_OK 2u // the query walks ONE partition: no tuple can reach it twice, so a CTA that runs two of its
+                            // segments back to back keeps one candidate buffer (and one threshold) across them
 
 #define RK_KEY_SENTINEL 0xFFFFFFFFu
 

@@ -131,6 +131,7 @@ struct rk_index {
     std::map<std::vector<uint32_t>, uint32_t> combo_part;                // role set -> parts index
     std::unordered_map<uint32_t, uint32_t> dyn_part;                     // part_id -> parts index
     std::map<std::pair<std::vector<uint32_t>, uint32_t>, bool> pure_cache;  // (role set, part) -> pure?
+    std::map<std::pair<std::vector<uint32_t>, uint32_t>, uint64_t> visible_cache;  // (role set, part) -> rows of the part the role set sees
     std::mutex mu;
     DevBuf d_tid, d_rowdoc, d_doc_ids, d_doc_mask, d_ext_row, d_ext_vstart, d_ext_mask, d_part_ext_off;
     uint64_t device_bytes = 0;

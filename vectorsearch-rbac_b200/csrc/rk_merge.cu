@@ -13,6 +13,7 @@
 
 #define RK_SEL_THREADS 512
 #define RK_SEL_CHUNK 1024
+#define RK_SEL_LISTS 1024       // non-empty list ids staged per round
 
 __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelectParams p)
 {
@@ -74,7 +75,8 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     // Fast path: every list is sorted ascending, so the entries with key <= tau form a prefix of
     // each list.  Walk the prefixes and gather them; only if they do not fit the buffer (more than
     // RK_CAND_CAP entries tie below tau) fall back to the chunked scan with compactions.
-    __shared__ uint32_t s_overflow;
+    __shared__ uint32_t s_overflow, s_nlists;
+    __shared__ uint32_t s_lists[RK_SEL_LISTS];
     if (t == 0) s_overflow = 0;
     __syncthreads();
     // One warp per list, 32 consecutive entries per step (one coalesced load instead of a chain of dependent ones).
@@ -82,7 +84,18 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     {
         const uint32_t tau = s_tau;
         const int warp = t >> 5, lane = t & 31;
-        for (uint32_t j = (uint32_t) warp; j < nl; j += RK_SEL_THREADS / 32) {
+        // non-empty lists first (all counts fetched in one parallel round): a single query cut into a thousand
+        // segments leaves most lists empty once CTAs carry their buffer across segments
+        for (uint32_t lbase = 0; lbase < nl; lbase += RK_SEL_LISTS) {
+        __syncthreads();
+        if (t == 0) s_nlists = 0;
+        __syncthreads();
+        for (uint32_t j = lbase + (uint32_t) t; j < nl && j < lbase + RK_SEL_LISTS; j += RK_SEL_THREADS)
+            if (list_count(j) > 0) s_lists[atomicAdd(&s_nlists, 1u)] = j;
+        __syncthreads();
+        const uint32_t nlive = s_nlists;
+        for (uint32_t li = (uint32_t) warp; li < nlive; li += RK_SEL_THREADS / 32) {
+            const uint32_t j = s_lists[li];
             const int cnt = list_count(j);
             const size_t a4 = b4(j), a8 = b8(j);
             for (int i0 = 0; i0 < cnt; i0 += 32) {
@@ -111,6 +124,7 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
                 // sorted list: the first entry that fails ends the prefix
                 if (!p.unsorted && __any_sync(0xffffffffu, i < cnt && !take)) break;
             }
+        }
         }
     }
     __syncthreads();

@@ -32,6 +32,7 @@
 #define RK_FLAG_FIRST 1u
 #define RK_FLAG_LAST 2u
 #define RK_FLAG_END 4u
+#define RK_FLAG_CONT 8u     // with LAST: the CTA's next segment continues the same query's single partition — keep the buffer
 
 struct RkStageMeta {
     uint32_t nrows, seg, query, flags;
@@ -84,6 +85,7 @@ struct RkProducer {
     uint32_t phase;
     uint32_t cur_rows, tx;
     uint32_t seg_id, query;
+    bool cont_next;     // the segment after this one may share its candidate buffer (set by the claim loop)
     bool first;
     uint64_t pol_stream, pol_keep;
 
@@ -278,7 +280,7 @@ struct RkProducer {
             }
             if (run_len) emit_run(run_start, run_len);
         }
-        close_tile(RK_FLAG_LAST);
+        close_tile(RK_FLAG_LAST | (cont_next ? RK_FLAG_CONT : 0u));
     }
 };
 
@@ -413,7 +415,7 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
 
     if (warp == RK_CONS_WARPS) {
         // ===================== producer warp =====================
-        RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, true, rk_policy_evict_first(),
+        RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, false, true, rk_policy_evict_first(),
                       rk_policy_evict_last()};
         auto seg_at = [&](uint32_t pos) -> uint32_t { return p.seg_order ? p.seg_order[pos] : pos; };
         // claim two segments ahead: the next descriptor is loaded while the current one streams
@@ -435,6 +437,7 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
                 sid2 = sid1;
             }
             pr.seg_id = cur_id;
+            pr.cont_next = sid1 < nseg && nxt.query == cur.query && (cur.flags & nxt.flags & RK_SEGF_MERGE_OK) != 0;
             pr.run_segment(cur);
             cur_id = nxt_id;
             sid2 = __shfl_sync(0xffffffffu, sid2, 0);
@@ -526,24 +529,28 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
         __syncwarp();
         if (lane == 0) rk_mbar_arrive(&empty[stage]);
         const bool last = (m.flags & RK_FLAG_LAST) != 0;
+        // a segment whose successor on this CTA continues the same single-partition query ends without a final
+        // select: the buffer and the threshold carry over, and this segment's own list stays empty
+        const bool cont = last && (m.flags & RK_FLAG_CONT) != 0;
+        const bool fin = last && !cont;
         if (last || ++since_ckpt == ckpt) {
             since_ckpt = 0;
             // one reducing barrier: every warp gets the same verdict whatever it read itself
             const bool full_buf = rk_named_bar_red_or(1, RK_CONS_THREADS, *s_count > trigger);
-            if (last || full_buf) {
+            if (fin || full_buf) {
                 int n = (int) *s_count;              // stable: nobody appends before the next barrier
                 uint32_t tau = RK_KEY_SENTINEL;
                 if (n > p.k) {
                     tau = rk_radix_kth(cb.key, n, p.k, s_hist, s_wsum, s_sel, t, csync);
                     n = rk_compact_le(cb, n, tau, t, s_wsum, csync);
                 }
-                if (last || n > tie_limit) {
+                if (fin || n > tie_limit) {
                     // exact order: (key, tuple id) ascending over the survivors
                     for (int i = t; i < n; i += RK_CONS_THREADS) cb.tid[i] = p.store.tid[cb.row[i]];
                     rk_bitonic_sort(cb, n, t, RK_CONS_THREADS, csync);
                     if (n > p.k) n = p.k;
                 }
-                if (last) {
+                if (fin) {
                     const size_t base = (size_t) m.seg * p.k;
                     for (int i = t; i < n; i += RK_CONS_THREADS) {
                         p.cand_key[base + i] = cb.key[i];
@@ -557,10 +564,12 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
                     }
                 } else if (t == 0) {
                     *s_count = (uint32_t) n;
+                    // (after the exact sort n == k entries remain and the k-th key is still the threshold)
                     *s_tau = tau;
                 }
                 csync();
             }
+            if (cont && t == 0) p.cand_count[m.seg] = 0;
         }
         if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
     }

@@ -50,19 +50,39 @@ static bool partition_pure(rk_index *ix, const UserInfo &u, uint32_t pidx)
     return pure;
 }
 
-struct PlanItem { uint32_t part; uint32_t flags; uint64_t rows_est; };
+// Rows of a partition a role set may see (what a row-filtered scan of an impure partition reads: SURVEY.md §8(d) counts
+// only those towards the algorithmic bytes).
+static uint64_t partition_visible_rows(rk_index *ix, const UserInfo &u, uint32_t pidx)
+{
+    std::lock_guard<std::mutex> g(ix->mu);
+    auto key = std::make_pair(u.roles, pidx);
+    auto it = ix->visible_cache.find(key);
+    if (it != ix->visible_cache.end()) return it->second;
+    const int W = ix->mask_words;
+    uint64_t rows = 0;
+    for (uint32_t d : ix->parts[pidx].docs) {
+        uint64_t acc = 0;
+        for (int w = 0; w < W; w++) acc |= ix->doc_mask[(size_t) d * W + w] & u.mask[w];
+        if (acc) rows += ix->doc_row_start[d + 1] - ix->doc_row_start[d];
+    }
+    ix->visible_cache[key] = rows;
+    return rows;
+}
+
+// rows_est: rows the segments cover (sizing, scheduling); rows_algo: rows that count as algorithmic traffic
+struct PlanItem { uint32_t part; uint32_t flags; uint64_t rows_est; uint64_t rows_algo; };
 
 // Which partitions does this user's scan walk?  Returns <0 on error.
 static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std::vector<PlanItem> &items)
 {
     items.clear();
     if (o->filter == RK_FILTER_NONE) {
-        items.push_back({0u, 0u, ix->parts[0].rows});
+        items.push_back({0u, 0u, ix->parts[0].rows, ix->parts[0].rows});
         return 0;
     }
     if (!u || u->roles.empty()) return 0;   // no roles -> nothing visible
     if (o->filter == RK_FILTER_BITMASK) {
-        if (u->allowed_rows) items.push_back({0u, RK_SEGF_MASKED, u->allowed_rows});
+        if (u->allowed_rows) items.push_back({0u, RK_SEGF_MASKED, u->allowed_rows, u->allowed_rows});
         return 0;
     }
     int layout = o->layout;
@@ -77,13 +97,13 @@ static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std
         for (uint32_t r : u->roles) {
             auto it = ix->role_part.find(r);
             if (it != ix->role_part.end() && ix->parts[it->second].rows)
-                items.push_back({it->second, 0u, ix->parts[it->second].rows});
+                items.push_back({it->second, 0u, ix->parts[it->second].rows, ix->parts[it->second].rows});
         }
     } else if (layout == RK_LAYOUT_COMBINATION) {
         if (!ix->want_combo_parts) return rk_fail(RK_ERR_STATE, "combination partitions were not built");
         auto it = ix->combo_part.find(u->roles);
         if (it != ix->combo_part.end() && ix->parts[it->second].rows)
-            items.push_back({it->second, 0u, ix->parts[it->second].rows});
+            items.push_back({it->second, 0u, ix->parts[it->second].rows, ix->parts[it->second].rows});
     } else if (layout == RK_LAYOUT_DYNAMIC) {
         auto it = ix->roleset_parts.find(u->roles);
         if (it == ix->roleset_parts.end()) return 0;   // no CombRolePartitions row -> no partitions (search.py:54-60)
@@ -91,7 +111,7 @@ static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std
             uint32_t pidx = ix->dyn_part[pid];
             if (!ix->parts[pidx].rows) continue;
             bool pure = partition_pure(ix, *u, pidx);
-            items.push_back({pidx, pure ? 0u : RK_SEGF_MASKED, ix->parts[pidx].rows});
+            items.push_back({pidx, pure ? 0u : RK_SEGF_MASKED, ix->parts[pidx].rows, pure ? ix->parts[pidx].rows : partition_visible_rows(ix, *u, pidx)});
         }
     } else {
         return rk_fail(RK_ERR_INVALID, "unknown layout %d", layout);
@@ -106,13 +126,13 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
     const int W = ix->mask_words;
     std::vector<std::vector<PlanItem>> per_q(nq);
     std::vector<const UserInfo *> uinfo(nq, nullptr);
-    uint64_t total_rows = 0;
+    uint64_t total_rows = 0, algo_rows = 0;
     for (size_t q = 0; q < nq; q++) {
         auto it = ix->users.find(user_ids ? user_ids[q] : 0u);
         uinfo[q] = it == ix->users.end() ? nullptr : &it->second;
         int rc = plan_user(ix, uinfo[q], o, per_q[q]);
         if (rc < 0) return rc;
-        for (auto &pi : per_q[q]) total_rows += pi.rows_est;
+        for (auto &pi : per_q[q]) { total_rows += pi.rows_est; algo_rows += pi.rows_algo; }
     }
     // Segment sizing.  A segment costs a few microseconds of fixed work (pipeline refill, final
     // compaction + sort) and the dynamic schedule wastes about half a segment per CTA at the tail,
@@ -138,7 +158,8 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
             if (nchunks > P.rows) nchunks = P.rows;
             for (uint64_t c = 0; c < nchunks; c++) {
                 RkSegment s;
-                s.query = (uint32_t) q; s.kind = RK_SEG_EXTENTS; s.flags = (uint16_t) pi.flags;
+                s.query = (uint32_t) q; s.kind = RK_SEG_EXTENTS;
+                s.flags = (uint16_t) (pi.flags | (per_q[q].size() == 1 ? RK_SEGF_MERGE_OK : 0u));
                 s.begin = P.rows * c / nchunks;
                 s.end = P.rows * (c + 1) / nchunks;
                 if (s.end <= s.begin) continue;
@@ -225,7 +246,7 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
 
     ws.segments = nseg;
     ws.rows_scanned = total_rows;
-    ws.algo_bytes = total_rows * row_bytes + mask_bytes + (uint64_t) nq * 12ull * (uint64_t) o->k;
+    ws.algo_bytes = algo_rows * row_bytes + mask_bytes + (uint64_t) nq * 12ull * (uint64_t) o->k;
     *out_nseg = nseg;
     return 0;
 }
