@@ -416,6 +416,7 @@ extern "C" int rk_finalize(rk_index *ix)
     // users
     for (auto &pr : ix->user_roles) ix->users[pr.first].roles.push_back(pr.second);
     std::map<std::vector<uint32_t>, std::pair<uint64_t, uint64_t>> set_rows;   // role set -> (rows, docs)
+    std::map<std::vector<uint64_t>, uint32_t> mask_ids;
     for (auto &kv : ix->users) {
         UserInfo &u = kv.second;
         std::sort(u.roles.begin(), u.roles.end());
@@ -434,7 +435,9 @@ extern "C" int rk_finalize(rk_index *ix)
         }
         u.allowed_rows = it->second.first;
         u.allowed_docs = it->second.second;
+        u.mask_id = mask_ids.emplace(u.mask, (uint32_t) mask_ids.size()).first->second;
     }
+    ix->n_mask_ids = (uint32_t) mask_ids.size();
 
     // partitions; [0] = every document (bitmask / unfiltered scans walk it)
     ix->parts.clear();

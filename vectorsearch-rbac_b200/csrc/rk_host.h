@@ -66,6 +66,7 @@ struct UserInfo {
     std::vector<uint64_t> mask;         // [mask_words]
     uint64_t allowed_rows = 0;          // rows the RLS predicate lets this user see
     uint64_t allowed_docs = 0;
+    uint32_t mask_id = 0;               // users with the same role mask share an id (dense, assigned by rk_finalize)
 };
 
 struct IvfIndex {
@@ -90,6 +91,7 @@ struct TensorState {
     DevBuf d_plan, d_qp, d_tiles;
     std::vector<uint32_t> h_tiles;                                              // tile lists of all cached role masks
     std::map<std::vector<uint64_t>, std::pair<uint32_t, uint32_t>> tile_cache;  // role mask -> (offset, count) in h_tiles
+    std::vector<std::pair<uint32_t, uint32_t>> tile_by_mask_id;                 // the same, by UserInfo::mask_id (count ~0u = not built yet)
     struct Atom { std::vector<uint64_t> mask; uint32_t tl_off = 0, tl_n = 0; uint64_t rows = 0; };
     std::vector<Atom> atoms;                                                    // document classes by role mask (empty: too many)
     bool tiles_dirty = false;                                                   // h_tiles grew since the last upload
@@ -130,6 +132,7 @@ struct rk_index {
     std::unordered_map<uint32_t, uint32_t> role_part;                    // raw role -> parts index
     std::map<std::vector<uint32_t>, uint32_t> combo_part;                // role set -> parts index
     std::unordered_map<uint32_t, uint32_t> dyn_part;                     // part_id -> parts index
+    uint32_t n_mask_ids = 0;                      // distinct user role masks (UserInfo::mask_id < n_mask_ids)
     std::map<std::pair<std::vector<uint32_t>, uint32_t>, bool> pure_cache;  // (role set, part) -> pure?
     std::map<std::pair<std::vector<uint32_t>, uint32_t>, uint64_t> visible_cache;  // (role set, part) -> rows of the part the role set sees
     std::mutex mu;

@@ -10,6 +10,8 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
+#include <cstdio>
 #include <map>
 
 #include "rk_host.h"
@@ -110,6 +112,21 @@ int rk_tensor_supported(const rk_index *ix, const rk_scan_opts *o)
 // Documents are contiguous extents, so a visible document starts a tile unless the previous tile
 // already reaches into it; rows a tile drags in beyond the visible ones are rejected by the
 // epilogue's mask test.  Cached per role mask (there are as many as distinct role sets).
+static int tiles_for_mask(rk_index *ix, const std::vector<uint64_t> &mask, uint32_t *off, uint32_t *cnt, bool *grew);
+
+static int tiles_for_user(rk_index *ix, const UserInfo &u, uint32_t *off, uint32_t *cnt, bool *grew)
+{
+    TensorState &ts = ix->tensor;
+    if (ts.tile_by_mask_id.size() != ix->n_mask_ids) ts.tile_by_mask_id.assign(ix->n_mask_ids, std::make_pair(0u, ~0u));
+    auto &e = ts.tile_by_mask_id[u.mask_id];
+    if (e.second == ~0u) {
+        int rc = tiles_for_mask(ix, u.mask, &e.first, &e.second, grew);
+        if (rc < 0) return rc;
+    }
+    *off = e.first; *cnt = e.second;
+    return 0;
+}
+
 static int tiles_for_mask(rk_index *ix, const std::vector<uint64_t> &mask, uint32_t *off, uint32_t *cnt, bool *grew)
 {
     TensorState &ts = ix->tensor;
@@ -281,6 +298,16 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
                      const RkSelectParams &out, std::vector<uint32_t> &redo)
 {
     redo.clear();
+    // RK_TENSOR_HOST_TIMING=1: host microseconds per phase of this call on stderr (tuning aid)
+    static const bool host_timing = getenv("RK_TENSOR_HOST_TIMING") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    double t_phase[6] = {0, 0, 0, 0, 0, 0};
+    auto tick = [&](int i) {
+        if (!host_timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        t_phase[i] += std::chrono::duration<double, std::micro>(now - t_prev).count();
+        t_prev = now;
+    };
     int rc = tensor_prepare(ix);
     if (rc < 0) return rc;
     TensorState &ts = ix->tensor;
@@ -297,23 +324,26 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // ---- groups: queries that see the same rows (same role mask) share one pass over those rows
     std::vector<TGroup> groups;
     {
-        std::map<std::vector<uint64_t>, uint32_t> by_mask;
-        std::vector<uint64_t> key((size_t) W);
+        // users with the same role mask carry the same dense mask id (rk_finalize): grouping is a table lookup
+        std::vector<int32_t> gid((size_t) ix->n_mask_ids + 1, -1);
         for (size_t q = 0; q < nq; q++) {
             const UserInfo *u = nullptr;
+            size_t slot = ix->n_mask_ids;                            // unfiltered: one group
             if (use_mask) {
                 if (user_ids) {
                     auto it = ix->users.find(user_ids[q]);
                     if (it != ix->users.end()) u = &it->second;
                 }
                 if (!u || u->allowed_rows == 0) continue;          // nothing visible: the query owns no list
-                key = u->mask;
-            } else {
-                std::fill(key.begin(), key.end(), ~0ull);
+                slot = u->mask_id;
             }
-            auto ins = by_mask.emplace(key, (uint32_t) groups.size());
-            if (ins.second) { groups.emplace_back(); groups.back().user = u; groups.back().min_visible = u ? u->allowed_rows : n; }
-            groups[ins.first->second].queries.push_back((uint32_t) q);
+            if (gid[slot] < 0) {
+                gid[slot] = (int32_t) groups.size();
+                groups.emplace_back();
+                groups.back().user = u;
+                groups.back().min_visible = u ? u->allowed_rows : n;
+            }
+            groups[(size_t) gid[slot]].queries.push_back((uint32_t) q);
         }
     }
     // Three ways to walk the rows; the plan that stages the fewest bytes into shared memory wins
@@ -338,7 +368,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         double cost_g = 0.0, cost_a = 0.0;
         size_t nq_live = 0;
         for (auto &g : groups) {
-            rc = tiles_for_mask(ix, g.user->mask, &g.tl_off, &g.tl_n, &grew);
+            rc = tiles_for_user(ix, *g.user, &g.tl_off, &g.tl_n, &grew);
             if (rc < 0) return rc;
             cost_g += visit_cost((double) g.tl_n, g.queries.size());
             nq_live += g.queries.size();
@@ -402,6 +432,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         ts.tiles_dirty = false;
     }
 
+    tick(0);      // groups + plan choice
     // ---- slots (group-ordered queries; a query owns one slot per group it appears in) and the two passes
     size_t nslots = 0;
     for (auto &g : groups) nslots += g.queries.size();
@@ -455,6 +486,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
             for (uint32_t j = 0; j < pm_.nlists[s_]; j++) qlist[fill[slot_q[s_]]++] = pm_.lid0[s_] + j * pm_.lstep[s_];
     }
 
+    tick(1);      // passes built
     // ---- staging: per pass [units][cta_off][cta_units][lid0][lstep][nlists], then [slot_q][qoff][qlist][qmask per slot]
     const size_t b_slot = nslots * 4, b_qmask = nslots * (size_t) W * 8;
     auto pass_bytes = [&](const TPass &t) { return t.units.size() * sizeof(RkBUnit) + (t.cta_off.size() + t.cta_units.size()) * 4 + 3 * b_slot + 128; };
@@ -543,6 +575,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     const float *dQp = ts.d_qp.as<float>();
     if (nslots) { RK_CUDA(rk_launch_gather_rows(dQ, ts.d_qp.as<float>(), d_slotq, nslots, ix->dim_pad, st)); launches++; }
 
+    tick(2);      // staged, uploads and query preparation enqueued
     RkBScanParams bp;
     memset(&bp, 0, sizeof bp);
     bp.tile_rows = plan != PLAN_DENSE ? ts.d_tiles.as<uint32_t>() : nullptr;
@@ -661,7 +694,9 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ev[3], st)); ws.timed_select = true; }
     int32_t *hflags = ts.h_flags.as<int32_t>();
     RK_CUDA(cudaMemcpyAsync(hflags, ts.d_flags.p, nq * 4, cudaMemcpyDeviceToHost, st));
+    tick(3);      // everything enqueued
     RK_CUDA(cudaStreamSynchronize(st));
+    tick(4);      // device done
     for (size_t q = 0; q < nq; q++)
         if (hflags[q]) redo.push_back((uint32_t) q);
     float qnorm_max;
@@ -684,6 +719,9 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     ts.last_flop = 2.0 * (double) ix->dim * pm_.pairs;
     ts.last_redo = (uint32_t) redo.size();
     ts.last_exact = exact;
+    if (host_timing)
+        fprintf(stderr, "rk_tensor_search host us: groups %.0f passes %.0f stage %.0f launch %.0f wait %.0f\n", t_phase[0], t_phase[1],
+                t_phase[2], t_phase[3], t_phase[4]);
     ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0) + (paired ? 32 : 0);
     return RK_OK;
 }
