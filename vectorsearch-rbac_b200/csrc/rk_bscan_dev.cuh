@@ -230,12 +230,25 @@ __device__ __forceinline__ void bs_warp_emit_unsorted(const BsCtx &c, int q, uin
     const uint2 *buf = c.scratch + (size_t) q * BS_CAP;
     uint64_t best = 0;
     uint32_t besti = 0;
-    for (uint32_t i = c.lane; i < n; i += 32) {
-        const uint2 e = __ldcg(&buf[i]);
-        const uint64_t v = ((uint64_t) e.x << 32) | e.y;
-        if (v >= best) { best = v; besti = i; }
-        out_key[i] = e.x;
-        out_row[i] = e.y;
+    // eight of a lane's entries are fetched before any is used (one memory round trip per 256 entries; n <= kp <= 512)
+#pragma unroll 1
+    for (uint32_t b0 = 0; b0 < n; b0 += 256) {
+        uint2 e[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint32_t i = b0 + (uint32_t) c.lane + 32u * j;
+            e[j] = i < n ? __ldcg(&buf[i]) : make_uint2(0u, 0u);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint32_t i = b0 + (uint32_t) c.lane + 32u * j;
+            if (i < n) {
+                const uint64_t v = ((uint64_t) e[j].x << 32) | e[j].y;
+                if (v >= best) { best = v; besti = i; }
+                out_key[i] = e[j].x;
+                out_row[i] = e[j].y;
+            }
+        }
     }
     uint64_t wbest = best;
 #pragma unroll

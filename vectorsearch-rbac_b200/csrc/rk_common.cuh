@@ -86,6 +86,7 @@ struct RkSelectParams {
     int null_query;
     int key_is_float;           // cand_key holds fp32 ordering values (exchange form) instead of uint keys
     int unsorted;               // lists are not sorted; only their LAST entry is their largest (tensor-engine nominations)
+    int out_maxlast;            // the consumer only needs the k best as a SET with the largest entry last (no dedup): skip the sort
     // row -> document id (may be NULL when cand_row already holds document ids)
     const uint32_t *rowdoc;
     const uint32_t *doc_ids;

@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     // each list.  Walk the prefixes and gather them; only if they do not fit the buffer (more than
     // RK_CAND_CAP entries tie below tau) fall back to the chunked scan with compactions.
     __shared__ uint32_t s_overflow, s_nlists;
+    __shared__ uint32_t s_hist[256], s_sel[2];
     __shared__ uint32_t s_lists[RK_SEL_LISTS];
     if (t == 0) s_overflow = 0;
     __syncthreads();
@@ -98,31 +99,43 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
             const uint32_t j = s_lists[li];
             const int cnt = list_count(j);
             const size_t a4 = b4(j), a8 = b8(j);
-            for (int i0 = 0; i0 < cnt; i0 += 32) {
-                const int i = i0 + lane;
-                bool take = false;
-                uint32_t key = RK_KEY_SENTINEL;
-                uint64_t tid = 0;
-                if (i < cnt) {
-                    key = load_key(a4 + i);
-                    if (key <= tau && key != RK_KEY_SENTINEL) {
-                        tid = load_tid(a8 + i, a4 + i);
-                        take = !(tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u);   // exchange-form padding
+            // keys (and rows) of up to eight 32-entry steps are fetched together: one memory round trip per eight steps
+            for (int b0 = 0; b0 < cnt; b0 += 256) {
+                uint32_t kreg[8], rreg[8];
+#pragma unroll
+                for (int s8 = 0; s8 < 8; s8++) {
+                    const int i = b0 + s8 * 32 + lane;
+                    kreg[s8] = i < cnt ? load_key(a4 + i) : RK_KEY_SENTINEL;
+                    rreg[s8] = i < cnt ? p.cand_row[a4 + i] : 0u;
+                }
+                bool stop = false;
+#pragma unroll
+                for (int s8 = 0; s8 < 8; s8++) {
+                    const int i = b0 + s8 * 32 + lane;
+                    if (!stop && b0 + s8 * 32 < cnt) {          // warp-uniform
+                        bool take = false;
+                        const uint32_t key = kreg[s8];
+                        uint64_t tid = 0;
+                        if (i < cnt && key <= tau && key != RK_KEY_SENTINEL) {
+                            tid = p.cand_tid ? p.cand_tid[a8 + i] : (uint64_t) rreg[s8];
+                            take = !(tid == 0xFFFFFFFFFFFFFFFFull && key == 0xFF800000u);   // exchange-form padding
+                        }
+                        const uint32_t bal = __ballot_sync(0xffffffffu, take);
+                        if (bal) {
+                            uint32_t base = 0;
+                            if (lane == 0) base = atomicAdd(&s_count, (uint32_t) __popc(bal));
+                            base = __shfl_sync(0xffffffffu, base, 0);
+                            if (take) {
+                                const uint32_t slot = base + (uint32_t) __popc(bal & ((1u << lane) - 1u));
+                                if (slot >= RK_CAND_CAP) s_overflow = 1;
+                                else { s_key[slot] = key; s_tid[slot] = tid; s_row[slot] = rreg[s8]; }
+                            }
+                        }
+                        // sorted list: the first entry that fails ends the prefix
+                        if (!p.unsorted && __any_sync(0xffffffffu, i < cnt && !take)) stop = true;
                     }
                 }
-                const uint32_t bal = __ballot_sync(0xffffffffu, take);
-                if (bal) {
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&s_count, (uint32_t) __popc(bal));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (take) {
-                        const uint32_t slot = base + (uint32_t) __popc(bal & ((1u << lane) - 1u));
-                        if (slot >= RK_CAND_CAP) s_overflow = 1;
-                        else { s_key[slot] = key; s_tid[slot] = tid; s_row[slot] = p.cand_row[a4 + i]; }
-                    }
-                }
-                // sorted list: the first entry that fails ends the prefix
-                if (!p.unsorted && __any_sync(0xffffffffu, i < cnt && !take)) break;
+                if (stop) break;
             }
         }
         }
@@ -133,7 +146,6 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     if (overflow && t == 0) s_count = 0;
     __syncthreads();
 
-    __shared__ uint32_t s_hist[256], s_sel[2];
     // keeps the entries with key <= (k-th smallest key) at the front of the buffer; returns how many
     auto sel_reduce = [&](int n) -> int {
         uint32_t prefix = 0, mask = 0, kk = (uint32_t) k;
@@ -190,7 +202,77 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
         return tot;
     };
 
-    const size_t total = overflow ? (size_t) nl * k : 0;
+    bool need_chunks = overflow;
+    if (overflow && !p.dedup && (size_t) nl * (size_t) k <= 32u * RK_SEL_THREADS) {
+        // More than RK_CAND_CAP entries lie below the bound the full lists gave (many unsorted lists of similar
+        // quality: the tensor engine's unit lists).  Instead of sorting them chunk by chunk, find the k-th smallest key
+        // over ALL the lists exactly: every thread takes up to 32 entries into registers (all loads independent: a couple
+        // of memory round trips), a 4-pass radix select runs over the registers, and only the entries up to the k-th key
+        // are gathered and sorted.
+        const uint32_t flat = nl * (uint32_t) k;
+        uint32_t kr[32];
+#pragma unroll
+        for (int r = 0; r < 32; r++) {
+            const uint32_t e = (uint32_t) t + (uint32_t) RK_SEL_THREADS * r;
+            uint32_t kv = RK_KEY_SENTINEL;
+            if (e < flat) {
+                const uint32_t j = e / (uint32_t) k, i = e - j * (uint32_t) k;
+                if ((int) i < list_count(j)) {
+                    kv = load_key(b4(j) + i);
+                    if (kv == 0xFF800000u && load_tid(b8(j) + i, b4(j) + i) == 0xFFFFFFFFFFFFFFFFull) kv = RK_KEY_SENTINEL;   // padding
+                }
+            }
+            kr[r] = kv;
+        }
+        uint32_t prefix = 0, mask = 0, kk = (uint32_t) k;
+#pragma unroll 1
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            if (t < 256) s_hist[t] = 0;
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < 32; r++)
+                if (kr[r] != RK_KEY_SENTINEL && (kr[r] & mask) == prefix) atomicAdd(&s_hist[(kr[r] >> shift) & 255u], 1u);
+            __syncthreads();
+            if (t < 32) {
+                uint32_t h[8], tot = 0;
+#pragma unroll
+                for (int b = 0; b < 8; b++) { h[b] = s_hist[t * 8 + b]; tot += h[b]; }
+                uint32_t inc = tot;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (t >= o) inc += u; }
+                uint32_t run = inc - tot;
+#pragma unroll
+                for (int b = 0; b < 8; b++) {
+                    if (run < kk && kk <= run + h[b]) { s_sel[0] = (uint32_t) (t * 8 + b); s_sel[1] = kk - run; }
+                    run += h[b];
+                }
+            }
+            __syncthreads();
+            prefix |= s_sel[0] << shift;
+            mask |= 0xFFu << shift;
+            kk = s_sel[1];
+        }
+        const uint32_t kth = prefix;
+        if (t == 0) { s_overflow = 0; if (kth < s_tau) s_tau = kth; }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < 32; r++) {
+            if (kr[r] != RK_KEY_SENTINEL && kr[r] <= kth) {
+                const uint32_t e = (uint32_t) t + (uint32_t) RK_SEL_THREADS * r;
+                const uint32_t j = e / (uint32_t) k, i = e - j * (uint32_t) k;
+                const uint32_t slot = atomicAdd(&s_count, 1u);
+                if (slot >= RK_CAND_CAP) s_overflow = 1;       // more than RK_CAND_CAP ties at the k-th key
+                else { s_key[slot] = kr[r]; s_tid[slot] = load_tid(b8(j) + i, b4(j) + i); s_row[slot] = p.cand_row[b4(j) + i]; }
+            }
+        }
+        __syncthreads();
+        need_chunks = s_overflow != 0;
+        __syncthreads();
+        if (need_chunks && t == 0) s_count = 0;      // the chunked pass below redoes it with the tight bound
+        __syncthreads();
+    }
+
+    const size_t total = need_chunks ? (size_t) nl * k : 0;
     for (size_t c0 = 0; c0 < total || c0 == 0; c0 += RK_SEL_CHUNK) {
         const uint32_t tau = s_tau;
         for (size_t idx = c0 + t; idx < total && idx < c0 + RK_SEL_CHUNK; idx += RK_SEL_THREADS) {
@@ -215,8 +297,42 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
             // Without dedup only the k smallest keys can reach the output: cut the buffer down to them (exact 4-pass radix
             // select of the k-th smallest key, ties kept) before sorting, so the sort runs over ~k entries instead of up to
             // RK_CAND_CAP.  (With dedup a duplicate may sit among the k smallest, so everything gathered is sorted.)
-            if (!p.dedup && n > 2 * k && n > 64) n = sel_reduce(n);
-            rk_bitonic_sort(cb, n, t, RK_SEL_THREADS, sync);
+            const bool setonly = p.out_maxlast && !p.dedup && lastc;
+            if (!p.dedup && ((n > 2 * k && n > 64) || (setonly && n > k))) n = sel_reduce(n);
+            if (setonly && n <= k) {
+                // the k smallest are all there is: no order needed, only the largest (key, tid) moved to the end
+                uint32_t bk = 0; uint64_t bt = 0; int bi = -1;
+                for (int i = t; i < n; i += RK_SEL_THREADS)
+                    if (bi < 0 || rk_cand_less(bk, bt, s_key[i], s_tid[i])) { bk = s_key[i]; bt = s_tid[i]; bi = i; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const uint32_t ok = __shfl_xor_sync(0xffffffffu, bk, o);
+                    const uint64_t ot = __shfl_xor_sync(0xffffffffu, bt, o);
+                    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                    if (oi >= 0 && (bi < 0 || rk_cand_less(bk, bt, ok, ot))) { bk = ok; bt = ot; bi = oi; }
+                }
+                __syncthreads();                       // s_hist is free again
+                if ((t & 31) == 0) {
+                    s_hist[(t >> 5) * 4 + 0] = bk; s_hist[(t >> 5) * 4 + 1] = (uint32_t) bi;
+                    s_hist[(t >> 5) * 4 + 2] = (uint32_t) bt; s_hist[(t >> 5) * 4 + 3] = (uint32_t) (bt >> 32);
+                }
+                __syncthreads();
+                if (t == 0 && n > 1) {
+                    for (int w = 0; w < RK_SEL_THREADS / 32; w++) {
+                        const uint32_t ok = s_hist[w * 4]; const int oi = (int) s_hist[w * 4 + 1];
+                        const uint64_t ot = (uint64_t) s_hist[w * 4 + 2] | ((uint64_t) s_hist[w * 4 + 3] << 32);
+                        if (oi >= 0 && (bi < 0 || rk_cand_less(bk, bt, ok, ot))) { bk = ok; bt = ot; bi = oi; }
+                    }
+                    if (bi >= 0 && bi != n - 1) {
+                        const uint32_t lk = s_key[n - 1], lr = s_row[n - 1]; const uint64_t lt = s_tid[n - 1];
+                        s_key[n - 1] = s_key[bi]; s_row[n - 1] = s_row[bi]; s_tid[n - 1] = s_tid[bi];
+                        s_key[bi] = lk; s_row[bi] = lr; s_tid[bi] = lt;
+                    }
+                }
+                __syncthreads();
+            } else {
+                rk_bitonic_sort(cb, n, t, RK_SEL_THREADS, sync);
+            }
             int m = n;
             if (p.dedup && n > 1) {
                 // drop entries equal to their predecessor (same tuple reached through two partitions)

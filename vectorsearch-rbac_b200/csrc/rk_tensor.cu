@@ -615,6 +615,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     sp.metric = ix->metric;
     sp.dedup = 0;
     sp.unsorted = 1;       // unit lists come unsorted, largest entry last (bs_warp_emit_unsorted)
+    sp.out_maxlast = 1;    // both consumers (the threshold seed, the exact re-score) need the kp best as a set + its largest value
 
     const int slot_ev = (int) (ws.ring_n % RK_TIMING_RING);
     if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot_ev], st));
