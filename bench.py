@@ -64,6 +64,11 @@ WORKLOADS = {
                     "(1000 users, 100 roles, <=3 roles per user), partitions from the AnonySys greedy role splitter restated with "
                     "a linear scan-cost model at storage alpha = 2.0 (the optimiser's fitted HNSW constants are not shipped), "
                     "per-row permission predicate inside impure partitions, exact top-100 (recall 1.0 >= the 0.95 target)"),
+    "c4": dict(rows=10_000_000, dim=768, kind="cohere", rpd=100, users=1000, roles=100, rbac="tree", metric="l2",
+               filter="bitmask", engine="scan", ivf_lists=4096,
+               desc="C4 IVFFlat role-filtered search: synthetic Cohere shape 10M x 768 fp32 L2, tree RBAC mask fused into the list "
+                    "scan, nlist = 4096 (GPU k-means build), one nprobe point per run (--nprobe; sweep: tools/ivf_sweep.py), "
+                    "top-100, recall@100 against the engine's exact filtered result"),
 }
 
 
@@ -89,6 +94,7 @@ def parse_args():
     ap.add_argument("--k", type=int, default=100)
     ap.add_argument("--filter", default="", choices=["", "bitmask", "partition", "combination", "dynamic"])
     ap.add_argument("--engine", default="", choices=["", "scan", "tensor", "auto"], help="override the workload's headline engine")
+    ap.add_argument("--nprobe", type=int, default=16, help="workload c4: lists probed per query")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--pipeline", action="store_true", help="N > 1: overlap a step's exchange (side stream) with the next step's scan")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
@@ -295,6 +301,11 @@ def run_reference(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if wl.get("ivf_lists"):
+        # the CPU leg of c4 scans the lists of the index the GPU arm builds (k-means centres are part of the workload);
+        # it is timed inside that arm's cpu_baseline
+        emit({"impl": "reference", "unavailable": "workload c4: the IVFFlat CPU leg runs inside the b200 arm (cpu_baseline) on the index it builds"})
+        return
     rows, dim, desc = wl["rows"], wl["dim"], wl["desc"]
     dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # data generation only
     tid, doc, ur, dr = build_rbac(wl)
@@ -375,7 +386,10 @@ def main():
     mine = np.flatnonzero(sharded.local_row_mask(doc, rank, world))
     ix = vr.Index(dim, metric=metric, device=local_rank, k_max=max(128, args.k))
     ix.reserve_rows(len(mine))
-    keep_host = world == 1 and rank == 0 and not args.no_cpu
+    ivf_lists = int(wl.get("ivf_lists", 0))
+    if ivf_lists and world > 1:
+        raise SystemExit("bench.py: workload c4 (IVFFlat) runs on one GPU")
+    keep_host = world == 1 and rank == 0 and not args.no_cpu and not ivf_lists
     X_host = np.empty((rows, dim), dtype=np.float32) if keep_host else None
     CH = 1 << 20 if dim <= 256 else 1 << 18
     for a0 in range(0, len(mine), CH):
@@ -397,6 +411,12 @@ def main():
         parts_d, roleset_parts, layout_info = dynamic_layout.split_roles(dr, ur, alpha=2.0)
         dynamic_layout.apply_layout(ix, parts_d, roleset_parts)
     ix.finalize()
+    ivf_build_s = None
+    if ivf_lists:
+        t_b = time.perf_counter()
+        ix.build_ivf(ivf_lists, seed=42)
+        torch.cuda.synchronize()
+        ivf_build_s = time.perf_counter() - t_b
     torch.cuda.empty_cache()
 
     Q, qusers = make_queries(wl, args.nq, dev)
@@ -416,12 +436,18 @@ def main():
 
     def measure(eng):
         """One engine over the step: device-resident `value` leg, then the host-buffer `e2e` leg."""
-        opts = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=eng)
+        opts = vr.engine.make_opts(args.k, probes=args.nprobe if ivf_lists else 0, filter=flt, layout=layout, engine=eng)
         # N > 1: scan, all-gather and merge of a step run back to back on one stream (stages_ms reports each).  With
         # --pipeline the exchange of step i moves to a side stream under the scan of step i + 1 (measured on 8xB200:
         # 4.45-4.60 ms per step against 4.53 serial — the collective's CTAs slow the persistent scan kernel by what the
         # overlap saves — so it is not the default).
         step_fn = searcher.search_device_pipelined if (world > 1 and args.pipeline) else searcher.search_device
+        if ivf_lists:
+            def step_fn(Qd, users, o):       # the index-probe path of the C-ABI (one GPU)
+                bf = searcher._get_bufs(Qd.shape[0], o.k)
+                ix.search_batch_device(Qd.data_ptr(), Qd.shape[0], users, o, bf["tid"].data_ptr(), bf["doc"].data_ptr(),
+                                       bf["dist"].data_ptr(), bf["cnt"].data_ptr())
+                return bf["tid"], bf["doc"], bf["dist"], bf["cnt"]
         for _ in range(max(3, args.warmup)):
             step_fn(Q, qusers, opts)
         searcher.flush()
@@ -438,6 +464,8 @@ def main():
             barrier()
         r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary(), "stages": searcher.stage_ms(), "pipelined": world > 1 and args.pipeline}
         searcher.stage_events = None
+        if ivf_lists:
+            ix.synchronize()                 # collects the last launch's probe / list-scan event times
         st = ix.stats()
         r["stats"] = st
         r["launches"] = st["total_launches"] - launches0
@@ -480,6 +508,16 @@ def main():
         """The dominant kernel of the step against the roofline that bounds it."""
         st = r["stats"]
         kms = float(np.mean(r["scan_ms"])) if len(r["scan_ms"]) else float("nan")
+        if ivf_lists:
+            # IVFFlat probe: SURVEY.md §8(d) B = lists x 4d + rows of the probed lists the user may see x 4d + 12k per query;
+            # time = the centre-scoring kernel + the list-scan kernel (CUDA events of both, last launch)
+            peak, peak_src = peaks()
+            tms = float(st["scan_ms"] + st["probe_ms"])
+            ach = st["algo_bytes"] / (tms * 1e-3) / 1e9 if tms > 0 else 0.0
+            return {"bound": "hbm", "kernel": "rk_ivf_probe_kernel + rk_scan_kernel (list segments)", "achieved": ach, "peak": peak,
+                    "unit": "GB/s", "frac": ach / peak, "frac_of_8TBps": ach / 8000.0, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": int(st["algo_bytes"]), "kernel_ms": tms, "probe_ms": float(st["probe_ms"]),
+                    "list_scan_ms": float(st["scan_ms"]), "launches_timed": 1, "traffic": None}
         if st["tensor_plan"] == 0:
             # CUDA-core scan, one pass per query: HBM.  Bytes per SURVEY.md §8(d): allowed rows x 4d + mask bytes + 12k, per query
             peak, peak_src = peaks()
@@ -514,7 +552,7 @@ def main():
 
     main_r = measure(engine)
     batched_r = None
-    if engine == vr.ENGINE_SCAN and not args.no_batched:
+    if engine == vr.ENGINE_SCAN and not args.no_batched and not ivf_lists:
         batched_r = measure(vr.ENGINE_AUTO)
 
     if rank == 0:
@@ -553,7 +591,105 @@ def main():
                 "roofline": roofline_of(batched_r, "auto"), "gpu_launches": int(batched_r["launches"]),
                 "identical_to_headline_results": bool(all(torch.equal(x, y) for x, y in zip(main_r["outs_h"], batched_r["outs_h"]))),
                 "tensor_redo": int(batched_r["stats"]["tensor_redo"]), "clocks": batched_r["clk"]}
-        if world == 1 and not args.no_cpu:
+        if ivf_lists:
+            # recall@k against the engine's own exact filtered result (probes = 0), which the parity tests pin to the oracle
+            opts0 = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=vr.ENGINE_AUTO)
+            ex = [t.cpu().numpy() for t in searcher.search_device(Q, qusers, opts0)]
+            got_t, got_c = main_r["outs_h"][0].numpy(), main_r["outs_h"][3].numpy()
+            rec = float(np.mean([len(set(ex[0][i, :ex[3][i]].tolist()) & set(got_t[i, :got_c[i]].tolist())) / max(1, int(ex[3][i]))
+                                 for i in range(args.nq)]))
+            # algorithmic bytes per SURVEY.md §8(d): per query lists x 4d (centres) + VISIBLE rows of the probed lists x 4d
+            # + mask bytes (row -> document -> role mask, 20 B per probed row) + 12k.  The engine's own figure counts every
+            # row of the probed lists, so the visible rows are recounted here from the index's list assignment.
+            from oracle import oracle as orc_
+            m_ = orc_.METRIC_L2 if wl["metric"] == "l2" else orc_.METRIC_IP
+            centers_, row_list_ = ix.ivf_info(rows)
+            off_, lrows_ = orc_.ivf_lists_csr(row_list_, ivf_lists)
+            doc_np = np.asarray(doc)
+            roles_of_, docs_of_ = {}, {}
+            for u_, r_ in ur:
+                roles_of_.setdefault(int(u_), set()).add(int(r_))
+            for d_, r_ in dr:
+                docs_of_.setdefault(int(r_), []).append(int(d_))
+            vis_cache, Qn_ = {}, Q.cpu().numpy()
+            probed_rows = visible_rows = 0
+            for i in range(args.nq):
+                u_ = int(qusers[i])
+                if u_ not in vis_cache:
+                    v_ = np.zeros(int(doc_np.max()) + 2, dtype=bool)
+                    for r_ in roles_of_.get(u_, ()):
+                        v_[np.asarray(docs_of_.get(r_, []), dtype=np.int64)] = True
+                    vis_cache[u_] = v_
+                for l_ in orc_.ivf_order_lists(centers_, Qn_[i], m_, args.nprobe)[0]:
+                    rr = lrows_[int(off_[l_]):int(off_[l_ + 1])]
+                    probed_rows += len(rr)
+                    visible_rows += int(vis_cache[u_][doc_np[rr]].sum())
+            rb_ = dim * 4
+            b_centres = args.nq * ivf_lists * rb_
+            b_lists = visible_rows * rb_ + probed_rows * 20 + args.nq * 12 * args.k
+            rf = line["roofline"]
+            tms = rf["kernel_ms"] * 1e-3
+            rf.update({"algorithmic_bytes_per_launch": int(b_centres + b_lists), "achieved": (b_centres + b_lists) / tms / 1e9,
+                       "frac": (b_centres + b_lists) / tms / 1e9 / rf["peak"], "frac_of_8TBps": (b_centres + b_lists) / tms / 1e9 / 8000.0,
+                       "probed_rows": int(probed_rows), "visible_rows": int(visible_rows),
+                       "centre_bytes": int(b_centres), "centre_GBps": b_centres / (rf["probe_ms"] * 1e-3) / 1e9 if rf["probe_ms"] > 0 else None,
+                       "list_bytes": int(b_lists), "list_GBps": b_lists / (rf["list_scan_ms"] * 1e-3) / 1e9 if rf["list_scan_ms"] > 0 else None,
+                       "note": "centres are scored once per query by definition (12.6 MB x queries) although the probe kernel shares them "
+                               "across a batch; the list scan reads only rows the user may see: short, latency-bound segments"})
+            line["config"].update({"recall_at_100": rec, "nprobe": args.nprobe, "lists": ivf_lists, "ivf_build_s": ivf_build_s,
+                                   "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
+        if ivf_lists and not args.no_cpu:
+            # CPU leg: the oracle's restatement of ivfscan.c with the reference's distance loops, same centres and lists, on
+            # a sample of the queries; only the rows of the lists the sample probes are brought to the host
+            from oracle import oracle as orc
+            from tests.util import assert_topk_matches
+            S = min(args.nq, 32)
+            m = orc.METRIC_L2 if wl["metric"] == "l2" else orc.METRIC_IP
+            centers, row_list = ix.ivf_info(rows)
+            Qn = Q.cpu().numpy()[:S]
+            need = set()
+            for q in Qn:
+                need.update(int(x) for x in orc.ivf_order_lists(centers, q, m, args.nprobe)[0])
+            need_rows = np.flatnonzero(np.isin(row_list, np.fromiter(need, dtype=np.uint32)))
+            X_sub = np.empty((len(need_rows), dim), dtype=np.float32)
+            for a0 in range(0, len(need_rows), CH):
+                X_sub[a0:a0 + CH] = gen_rows(wl, need_rows[a0:a0 + CH], dev).cpu().numpy()
+            off, lrows = orc.ivf_lists_csr(row_list[need_rows], ivf_lists)
+            tid_sub, doc_sub = tid[need_rows], np.asarray(doc)[need_rows]
+            roles_of, docs_of = {}, {}
+            for u, r in ur:
+                roles_of.setdefault(int(u), set()).add(int(r))
+            for d_, r in dr:
+                docs_of.setdefault(int(r), []).append(int(d_))
+            c_tid = np.full((S, args.k), np.uint64(0xFFFFFFFFFFFFFFFF), dtype=np.uint64)
+            c_dist = np.full((S, args.k), np.inf)
+            c_cnt = np.zeros(S, dtype=np.int32)
+            t0 = time.perf_counter()
+            for i in range(S):
+                vis = np.zeros(int(doc_sub.max()) + 2, dtype=np.uint8)
+                for r in roles_of.get(int(qusers[i]), ()):
+                    dd = np.asarray(docs_of.get(r, []), dtype=np.int64)
+                    vis[dd[dd < len(vis)]] = 1
+                (t_, _, d_), = orc.ivf_scan(X_sub, tid_sub, centers, off, lrows, Qn[i], m, probes=args.nprobe, allowed=vis[doc_sub])
+                n = min(args.k, len(t_))
+                c_tid[i, :n], c_dist[i, :n], c_cnt[i] = t_[:n], d_[:n], n
+            dtc = time.perf_counter() - t0
+            g_tid = main_r["outs_h"][0].numpy().view(np.uint64)[:S]
+            g_dist, g_cnt = main_r["outs_h"][2].numpy()[:S], main_r["outs_h"][3].numpy()[:S]
+            note = "within 1e-5 relative; ids identical outside oracle ties of that width"
+            try:
+                assert_topk_matches((g_tid, None, g_dist, g_cnt), (c_tid, None, c_dist, None, c_cnt), exact=False)
+                ok = True
+            except AssertionError as e:
+                ok = False
+                note += " — MISMATCH: " + str(e)[:200]
+            line["cpu_baseline"] = {
+                "value": S / dtc, "unit": "queries/s", "cores": 1, "kind": "port",
+                "sample": f"{S} of the step's {args.nq} queries, nprobe {args.nprobe}, the oracle's restatement of ivfscan.c (centre scoring, "
+                          f"full sort of the probed lists' visible tuples) on one thread of {cpu_model()}, the GPU build's centres and lists; "
+                          "no PostgreSQL page/tuple/fmgr overhead",
+                "gpu_ids_match": ok, "gpu_distances": note, "gpu_distances_match": ok}
+        if world == 1 and not args.no_cpu and not ivf_lists:
             cores = host_cores()
             outs_h = main_r["outs_h"]
             parts, qparts = cpu_partitions(doc, ur, dr, qusers)
