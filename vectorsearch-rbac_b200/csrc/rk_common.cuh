@@ -6,6 +6,8 @@
 #define RK_SEG_EXTENTS 0u   // virtual row range [begin,end) of an extent table (partition)
 #define RK_SEG_ROWS 2u      // physical row range [begin,end), no predicate
 #define RK_SEG_ROWMASK 3u   // physical row range [begin,end), role mask tested per row through rowdoc[]
+#define RK_SEG_IVFQ 4u      // probed lists [begin,end) of the query's probe order; every list's rows are ordered by document class
+                            // (distinct role mask), so the rows a user may see are a few extents per list: ivf_cls_off[]
 
 #define RK_SEGF_MASKED 1u   // test the extent's role mask against the user's before loading it
 #define RK_SEGF_MERGE_OK 2u // the query walks ONE partition: no tuple can reach it twice, so a CTA that runs two of its
@@ -43,6 +45,11 @@ struct RkScanParams {
     const uint32_t *ext_row;        // physical first row of each extent (+ sentinel per partition)
     const uint32_t *ext_vstart;     // virtual row offset of each extent inside its partition (+ sentinel = partition rows)
     const uint64_t *ext_mask;       // [extents][mask_words] role mask of the extent's document
+    // IVFFlat lists ordered by document class (RK_SEG_IVFQ)
+    const uint32_t *ivf_probe_list; // [nq][ivf_probes] lists of each query, nearest first
+    const uint32_t *ivf_cls_off;    // [lists][ivf_ncls + 1] (+ 1 sentinel) first row of each (list, class) in the list-sorted store
+    const uint64_t *ivf_qcls;       // [nq][2] classes the query's user may see (bit c of 128)
+    int ivf_probes, ivf_ncls;
     // queries
     const float *q;                 // [nq][dim_pad]
     int null_query;                 // ORDER BY v <-> NULL: all distances 0

@@ -79,6 +79,11 @@ struct IvfIndex {
     std::vector<float> centers;         // [lists][dim]
     uint32_t max_list_len = 0;
     int chunks_per_list = 1;
+    // rows of every list ordered by document class (distinct role mask) when there are at most 128 classes
+    int ncls = 0;                                   // 0 = lists keep row order, masks are tested per row
+    DevBuf d_cls_off;                               // [lists * (ncls + 1) + 1]
+    std::vector<std::vector<uint64_t>> cls_mask;    // role mask of each class
+    std::vector<uint64_t> qcls_by_mask_id;          // [n_mask_ids][2] visible classes per user mask id (filled lazily; ~0 = unset)
 };
 
 // State of the batched tensor-core engine (rk_tensor.cu / rk_bscan.cu); used by the index's own

@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
 #include <random>
 #include <unordered_set>
 
@@ -42,16 +43,57 @@ static int build_from_device_centers(rk_index *ix, int lists, const float *d_cen
     iv.row_list.assign(n, 0);
     if (n) RK_CUDA(cudaMemcpy(iv.row_list.data(), d_row_list.p, n * 4, cudaMemcpyDeviceToHost));
     d_row_list.release();
-    // counting sort by list, stable in finalized row order (ivfbuild.c:251-310 packs tuples list by list)
-    iv.list_start.assign((size_t) lists + 1, 0);
-    for (size_t r = 0; r < n; r++) iv.list_start[iv.row_list[r] + 1]++;
-    iv.max_list_len = 0;
-    for (int l = 0; l < lists; l++) {
-        iv.max_list_len = std::max(iv.max_list_len, iv.list_start[l + 1]);
-        iv.list_start[l + 1] += iv.list_start[l];
+    // Document classes: documents with the same role mask are visible to exactly the same users.  With at most 128 of them
+    // (role hierarchies: one per role) every list keeps its rows ordered by class, so the rows a user may see in a list are
+    // one extent per visible class and the list scan needs no per-row permission test.  Class `ncls` holds the documents
+    // nobody can see.  (Row order inside a list is not observable: results are ordered by (distance, tuple id).)
+    const int W = ix->mask_words;
+    const size_t D = ix->doc_ids.size();
+    std::vector<uint32_t> doc_cls(D, 0);
+    iv.ncls = 0;
+    iv.cls_mask.clear();
+    {
+        std::map<std::vector<uint64_t>, uint32_t> by_mask;
+        std::vector<uint64_t> key((size_t) W);
+        bool ok = true;
+        for (size_t dd = 0; dd < D && ok; dd++) {
+            bool any = false;
+            for (int w = 0; w < W; w++) { key[(size_t) w] = ix->doc_mask[dd * W + w]; any |= key[(size_t) w] != 0; }
+            if (!any) { doc_cls[dd] = 0xFFFFFFFFu; continue; }
+            auto ins = by_mask.emplace(key, (uint32_t) by_mask.size());
+            if (ins.second) {
+                if (by_mask.size() > 128) { ok = false; break; }
+                iv.cls_mask.push_back(key);
+            }
+            doc_cls[dd] = ins.first->second;
+        }
+        if (ok && !by_mask.empty()) iv.ncls = (int) by_mask.size();
+        else iv.cls_mask.clear();
     }
-    std::vector<uint32_t> perm(n), cursor(iv.list_start.begin(), iv.list_start.end() - 1);
-    for (size_t r = 0; r < n; r++) perm[cursor[iv.row_list[r]]++] = (uint32_t) r;
+    const uint32_t NB = (uint32_t) iv.ncls + 1;            // buckets per list (ncls == 0: one bucket = the list itself)
+    std::vector<uint32_t> row_cls;
+    if (iv.ncls) {
+        row_cls.resize(n);
+        for (size_t dd = 0; dd < D; dd++) {
+            const uint32_t c = doc_cls[dd] == 0xFFFFFFFFu ? (uint32_t) iv.ncls : doc_cls[dd];
+            for (uint64_t r = ix->doc_row_start[dd]; r < ix->doc_row_start[dd + 1]; r++) row_cls[r] = c;
+        }
+    }
+    // counting sort by (list, class), stable in finalized row order (ivfbuild.c:251-310 packs tuples list by list)
+    std::vector<uint32_t> bucket_start((size_t) lists * NB + 1, 0);
+    for (size_t r = 0; r < n; r++) bucket_start[(size_t) iv.row_list[r] * NB + (iv.ncls ? row_cls[r] : 0u) + 1]++;
+    for (size_t b = 0; b < (size_t) lists * NB; b++) bucket_start[b + 1] += bucket_start[b];
+    iv.list_start.assign((size_t) lists + 1, 0);
+    iv.max_list_len = 0;
+    for (int l = 0; l <= lists; l++) iv.list_start[l] = bucket_start[(size_t) l * NB];
+    for (int l = 0; l < lists; l++) iv.max_list_len = std::max(iv.max_list_len, iv.list_start[l + 1] - iv.list_start[l]);
+    std::vector<uint32_t> perm(n), cursor(bucket_start.begin(), bucket_start.end() - 1);
+    for (size_t r = 0; r < n; r++) perm[cursor[(size_t) iv.row_list[r] * NB + (iv.ncls ? row_cls[r] : 0u)]++] = (uint32_t) r;
+    if (iv.ncls) {
+        if (iv.d_cls_off.ensure(bucket_start.size() * 4) != 0) return RK_ERR_CUDA;
+        RK_CUDA(cudaMemcpy(iv.d_cls_off.p, bucket_start.data(), bucket_start.size() * 4, cudaMemcpyHostToDevice));
+        iv.qcls_by_mask_id.assign((size_t) ix->n_mask_ids * 2, ~0ull);
+    }
     DevBuf d_perm;
     if (d_perm.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
     if (n) RK_CUDA(cudaMemcpy(d_perm.p, perm.data(), n * 4, cudaMemcpyHostToDevice));
@@ -209,7 +251,17 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
     int chunks = (int) ((iv.max_list_len + rows_per_seg - 1) / rows_per_seg);
     chunks = std::max(1, std::min(chunks, 64));
     const uint32_t chunk_rows = std::max<uint32_t>(1u, (iv.max_list_len + chunks - 1) / chunks);
-    const size_t per_q = (size_t) std::max(probes, 0) * chunks;
+    // Class-ordered lists (at most 128 document classes): segments are (query, a few probed lists) and the producer walks
+    // one extent per visible class; they do not depend on the probe result, so the host writes them.
+    const bool cls_mode = iv.ncls > 0 && o->filter != RK_FILTER_NONE && probes > 0;
+    int cls_group = 1, cls_spq = 0;
+    if (cls_mode) {
+        // enough segments to fill the SMs four times over, at most one per probed list
+        int spq = (int) std::min<size_t>((size_t) probes, std::max<size_t>(1, ((size_t) ix->sm_count * 4 + nq_all - 1) / std::max<size_t>(nq_all, 1)));
+        cls_group = (probes + spq - 1) / spq;
+        cls_spq = (probes + cls_group - 1) / cls_group;
+    }
+    const size_t per_q = cls_mode ? (size_t) cls_spq : (size_t) std::max(probes, 0) * chunks;
     size_t qb = per_q ? std::max<size_t>(1, RK_IVF_MAX_SEGS / per_q) : nq_all;
     if (qb > nq_all) qb = nq_all;
 
@@ -220,13 +272,14 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
         const size_t nq = std::min(qb, nq_all - q0);
         const float *dQ = dQ_all + q0 * (size_t) ix->dim_pad;
         const uint32_t nseg = (uint32_t) (nq * per_q);
-        // staging: [qseg][qmask][ctl]
+        // staging: [qseg][qmask][ctl] (+ [segments][visible classes per query] for class-ordered lists)
         const size_t b_qseg = (nq + 1) * 4, b_qmask = nq * (size_t) W * 8;
+        const size_t b_csegs = cls_mode ? (size_t) nseg * sizeof(RkSegment) : 0, b_qcls = cls_mode ? nq * 16 : 0;
         ws.plan_idx ^= 1;
         const int pi_ = ws.plan_idx;
         if (ws.ev_plan_used[pi_]) RK_CUDA(cudaEventSynchronize(ws.ev_plan[pi_]));
         PinBuf &hp_ = ws.h_plan_ring[pi_];
-        if (hp_.ensure(b_qseg + b_qmask + 128) != 0) return RK_ERR_CUDA;
+        if (hp_.ensure(b_qseg + b_qmask + b_csegs + b_qcls + 256) != 0) return RK_ERR_CUDA;
         unsigned char *hp = hp_.as<unsigned char>();
         uint32_t *hq = reinterpret_cast<uint32_t *>(hp);
         for (size_t q = 0; q <= nq; q++) hq[q] = (uint32_t) (q * per_q);
@@ -241,6 +294,41 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
         }
         uint32_t *hc = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(hm) + ((b_qmask + 15) & ~(size_t) 15));
         hc[0] = nseg; hc[1] = 0;
+        RkSegment *hs = reinterpret_cast<RkSegment *>((reinterpret_cast<uintptr_t>(hc + 4) + 15) & ~(uintptr_t) 15);
+        uint64_t *hcl = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(hs) + b_csegs);
+        if (cls_mode) {
+            for (size_t q = 0; q < nq; q++) {
+                for (int s_ = 0; s_ < cls_spq; s_++) {
+                    RkSegment &sg = hs[q * (size_t) cls_spq + s_];
+                    memset(&sg, 0, sizeof sg);
+                    sg.query = (uint32_t) q; sg.kind = RK_SEG_IVFQ;
+                    sg.begin = (uint64_t) s_ * cls_group;
+                    sg.end = (uint64_t) std::min(probes, (s_ + 1) * cls_group);
+                }
+                // classes this user may see (cached per distinct role mask)
+                uint64_t c0 = 0, c1 = 0;
+                const UserInfo *u = nullptr;
+                if (user_ids) {
+                    auto it = ix->users.find(user_ids[q0 + q]);
+                    if (it != ix->users.end()) u = &it->second;
+                }
+                if (u) {
+                    uint64_t *cache = &iv.qcls_by_mask_id[(size_t) u->mask_id * 2];
+                    if (cache[0] == ~0ull && cache[1] == ~0ull) {
+                        uint64_t a0 = 0, a1 = 0;
+                        for (int c = 0; c < iv.ncls; c++) {
+                            uint64_t acc = 0;
+                            for (int w = 0; w < W; w++) acc |= iv.cls_mask[(size_t) c][(size_t) w] & u->mask[(size_t) w];
+                            if (acc) { if (c < 64) a0 |= 1ull << c; else a1 |= 1ull << (c - 64); }
+                        }
+                        // (all 128 bits set cannot be confused with "unset": it is stored as computed and recomputed each time)
+                        cache[0] = a0; cache[1] = a1;
+                    }
+                    c0 = cache[0]; c1 = cache[1];
+                }
+                hcl[q * 2] = c0; hcl[q * 2 + 1] = c1;
+            }
+        }
         if (ws.qseg.ensure(b_qseg) != 0 || ws.qmask.ensure(std::max<size_t>(b_qmask, 16)) != 0 || ws.ctl.ensure(64) != 0 ||
             ws.segs.ensure(std::max<size_t>((size_t) nseg * sizeof(RkSegment), 16)) != 0 ||
             ws.probe_list.ensure(std::max<size_t>(nq * (size_t) std::max(probes, 1) * 4, 16)) != 0)
@@ -248,6 +336,11 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
         RK_CUDA(cudaMemcpyAsync(ws.qseg.p, hq, b_qseg, cudaMemcpyHostToDevice, ws.stream));
         if (b_qmask) RK_CUDA(cudaMemcpyAsync(ws.qmask.p, hm, b_qmask, cudaMemcpyHostToDevice, ws.stream));
         RK_CUDA(cudaMemcpyAsync(ws.ctl.p, hc, 8, cudaMemcpyHostToDevice, ws.stream));
+        if (cls_mode) {
+            if (ws.order.ensure(std::max<size_t>(b_qcls, 16)) != 0) return RK_ERR_CUDA;
+            RK_CUDA(cudaMemcpyAsync(ws.segs.p, hs, b_csegs, cudaMemcpyHostToDevice, ws.stream));
+            RK_CUDA(cudaMemcpyAsync(ws.order.p, hcl, b_qcls, cudaMemcpyHostToDevice, ws.stream));
+        }
         RK_CUDA(cudaEventRecord(ws.ev_plan[pi_], ws.stream));
         ws.ev_plan_used[pi_] = true;
         if (rk_ensure_cand(ws, nseg, k) != 0) return RK_ERR_CUDA;
@@ -256,12 +349,20 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
             if (ws.timing && q0 == 0) RK_CUDA(cudaEventRecord(ws.ev[4], ws.stream));
             RK_CUDA(rk_launch_ivf_probe(dQ, (int) nq, iv.d_centers.as<float>(), lists, ix->dim_pad, ix->metric, o->null_query,
                                         probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.stream));
-            RK_CUDA(rk_launch_ivf_plan(ws.probe_list.as<uint32_t>(), iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
-                                       chunk_rows, kind, ws.segs.as<RkSegment>(), ws.stream));
+            if (!cls_mode)
+                RK_CUDA(rk_launch_ivf_plan(ws.probe_list.as<uint32_t>(), iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
+                                           chunk_rows, kind, ws.segs.as<RkSegment>(), ws.stream));
             if (ws.timing && q0 == 0) { RK_CUDA(cudaEventRecord(ws.ev[5], ws.stream)); ws.timed_probe = true; }
             RkScanParams p;
             rk_fill_scan_params(ix, ws, p, true, dQ, o, k);
             p.seg_order = nullptr;
+            if (cls_mode) {
+                p.ivf_probe_list = ws.probe_list.as<uint32_t>();
+                p.ivf_probes = probes;
+                p.ivf_cls_off = iv.d_cls_off.as<uint32_t>();
+                p.ivf_ncls = iv.ncls;
+                p.ivf_qcls = ws.order.as<uint64_t>();
+            }
             const int slot = (int) (ws.ring_n % RK_TIMING_RING);
             if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot], ws.stream));
             const int grid = (int) std::min<uint32_t>((uint32_t) ix->sm_count, nseg);

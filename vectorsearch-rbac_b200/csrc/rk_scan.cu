@@ -159,6 +159,28 @@ struct RkProducer {
         open_tile();
         if (s.kind == RK_SEG_ROWS) {
             emit_run(s.begin, s.end - s.begin);
+        } else if (s.kind == RK_SEG_IVFQ) {
+            // probed lists [begin, end) of this query; in every list the rows of one document class are contiguous, so
+            // what the user may see is one extent per visible class: no per-row test, masked-out rows cost nothing
+            const uint64_t c0 = p.ivf_qcls[2 * (size_t) s.query], c1 = p.ivf_qcls[2 * (size_t) s.query + 1];
+            const int nc = p.ivf_ncls;
+            for (uint32_t pi = (uint32_t) s.begin; pi < (uint32_t) s.end; pi++) {
+                const uint32_t l = p.ivf_probe_list[(size_t) s.query * p.ivf_probes + pi];
+                const uint32_t *co = p.ivf_cls_off + (size_t) l * (nc + 1);
+                for (int cb = 0; cb < nc; cb += 32) {
+                    const int c = cb + lane;
+                    const bool vis = c < nc && (((c < 64 ? c0 >> c : c1 >> (c - 64)) & 1ull) != 0);
+                    uint32_t lo = 0, hi = 0;
+                    if (vis) { lo = co[c]; hi = co[c + 1]; }
+                    uint32_t m = __ballot_sync(0xffffffffu, vis && hi > lo);
+                    while (m) {
+                        const int j = __ffs((int) m) - 1;
+                        m &= m - 1;
+                        const uint32_t a = __shfl_sync(0xffffffffu, lo, j), b = __shfl_sync(0xffffffffu, hi, j);
+                        emit_run(a, b - a);
+                    }
+                }
+            }
         } else if (s.kind == RK_SEG_EXTENTS) {
             // Partition = table of per-document extents; the host resolved which extents touch
             // [begin, end).  RK_EPL * 32 extents are resolved per step: every lane first tests the
