@@ -158,3 +158,39 @@ def test_ivf_float_data_bitmask_and_errors():
         if n == len(t):
             np.testing.assert_allclose(got[2][qi, :n], d, rtol=1e-5)
     ix.close()
+
+
+@pytest.mark.parametrize("metric,dim", [(0, 100), (1, 100), (0, 772), (0, 1540)])
+def test_ivf_probe_batched_path_matches_single_query_path(metric, dim, monkeypatch):
+    """The batched probe (keys kernel + radix-select ordering) must choose the lists the one-block-per-query kernel
+    (full sort of (key, list)) chooses: same arithmetic per (query, centre), ties to the lower list number
+    (ivfscan.c:36-107 pushes lists in order and keeps the earlier one on equal distance).  Repeated centres make ties
+    that straddle the probe cut; dims that are not a multiple of 128 exercise the column tail."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("sift", n=4000, dim=dim, rows_per_doc=8, rbac="random", num_users=16, num_roles=6)
+    rng = np.random.default_rng(5)
+    base = ds["X"][rng.choice(len(ds["X"]), 75, replace=False)]
+    centers = np.concatenate([base, base, base[:37], base]).copy()       # 262 lists, every centre two to four times
+    lists = len(centers)
+    ix = load_index(ds, metric=metric, role_parts=False, combo_parts=False)
+    ix.finalize()
+    ix.build_ivf_from_centers(centers)
+    exp_list = orc.ivf_assign(ds["X"], centers, metric)
+    off, rows = orc.ivf_lists_csr(exp_list, lists)
+    Q, users = _queries(ds, 37)
+    k = 25
+    for probes in (1, 3, 6, 40, lists):
+        monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
+        got_b = ix.search_batch(Q, users, k, probes=probes, filter=vr.FILTER_BITMASK)
+        monkeypatch.setenv("RK_IVF_PROBE_SINGLE", "1")
+        got_s = ix.search_batch(Q, users, k, probes=probes, filter=vr.FILTER_BITMASK)
+        for a, b in zip(got_b, got_s):
+            np.testing.assert_array_equal(a, b)
+        if dim == 100:
+            for qi in range(0, len(Q), 6):
+                t, d = _oracle_ivf_topk(ds, centers, off, rows, Q[qi], metric, probes, k, allowed=_allowed_mask(ds, users[qi]))
+                n = len(t)
+                assert got_b[3][qi] == n
+                np.testing.assert_array_equal(got_b[0][qi, :n], t)
+    monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
+    ix.close()

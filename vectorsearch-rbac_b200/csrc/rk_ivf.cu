@@ -232,6 +232,12 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
                          const rk_scan_opts *o, int k);
 int rk_ensure_cand(Workspace &ws, size_t nlists, int k);
 
+static int ivf_seg_factor()
+{
+    static int f = [] { const char *e = getenv("RK_IVF_SEG_FACTOR"); int v = e ? atoi(e) : 4; return v < 1 ? 1 : v; }();
+    return f;
+}
+
 int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_all, const uint32_t *user_ids,
                   const rk_scan_opts *o, int probe_offset, const RkSelectParams &out_all)
 {
@@ -257,7 +263,7 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
     int cls_group = 1, cls_spq = 0;
     if (cls_mode) {
         // enough segments to fill the SMs four times over, at most one per probed list
-        int spq = (int) std::min<size_t>((size_t) probes, std::max<size_t>(1, ((size_t) ix->sm_count * 4 + nq_all - 1) / std::max<size_t>(nq_all, 1)));
+        int spq = (int) std::min<size_t>((size_t) probes, std::max<size_t>(1, ((size_t) ix->sm_count * ivf_seg_factor() + nq_all - 1) / std::max<size_t>(nq_all, 1)));
         cls_group = (probes + spq - 1) / spq;
         cls_spq = (probes + cls_group - 1) / cls_group;
     }
@@ -331,7 +337,8 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
         }
         if (ws.qseg.ensure(b_qseg) != 0 || ws.qmask.ensure(std::max<size_t>(b_qmask, 16)) != 0 || ws.ctl.ensure(64) != 0 ||
             ws.segs.ensure(std::max<size_t>((size_t) nseg * sizeof(RkSegment), 16)) != 0 ||
-            ws.probe_list.ensure(std::max<size_t>(nq * (size_t) std::max(probes, 1) * 4, 16)) != 0)
+            ws.probe_list.ensure(std::max<size_t>(nq * (size_t) std::max(probes, 1) * 4, 16)) != 0 ||
+            ws.probe_key.ensure(std::max<size_t>(rk_ivf_probe_keys_bytes((int) nq, lists), 16)) != 0)
             return RK_ERR_CUDA;
         RK_CUDA(cudaMemcpyAsync(ws.qseg.p, hq, b_qseg, cudaMemcpyHostToDevice, ws.stream));
         if (b_qmask) RK_CUDA(cudaMemcpyAsync(ws.qmask.p, hm, b_qmask, cudaMemcpyHostToDevice, ws.stream));
@@ -348,7 +355,7 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
         if (nseg) {
             if (ws.timing && q0 == 0) RK_CUDA(cudaEventRecord(ws.ev[4], ws.stream));
             RK_CUDA(rk_launch_ivf_probe(dQ, (int) nq, iv.d_centers.as<float>(), lists, ix->dim_pad, ix->metric, o->null_query,
-                                        probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.stream));
+                                        probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.probe_key.as<uint32_t>(), ws.stream));
             if (!cls_mode)
                 RK_CUDA(rk_launch_ivf_plan(ws.probe_list.as<uint32_t>(), iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
                                            chunk_rows, kind, ws.segs.as<RkSegment>(), ws.stream));

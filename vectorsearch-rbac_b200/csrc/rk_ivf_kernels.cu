@@ -232,59 +232,306 @@ cudaError_t rk_launch_gather_u64(const uint64_t *src, uint64_t *dst, const uint3
 // [probe_offset, probe_offset + probes) is written nearest first.
 
 #define PR_THREADS 256
+// (PR_QB queries per block; launched with 1: the general path — any probe count, single queries.  Batches take the
+// two-kernel path below.)
 
-template <int METRIC>
-__global__ void __launch_bounds__(PR_THREADS) rk_ivf_probe_kernel(const float *__restrict__ Q, const float *__restrict__ Cn, int lists,
+template <int METRIC, int PR_QB>
+__global__ void __launch_bounds__(PR_THREADS) rk_ivf_probe_kernel(const float *__restrict__ Q, int nq, const float *__restrict__ Cn, int lists,
                                                                   int dim_pad, int null_query, int probe_offset, int probes,
                                                                   uint32_t *__restrict__ out_list)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t *ent = reinterpret_cast<uint64_t *>(smem_raw);                 // [P] (key << 32 | list)
     int P = 32;
     while (P < lists) P <<= 1;
-    float4 *qs = reinterpret_cast<float4 *>(ent + P);                        // [dim_pad / 4]
-    const int q = blockIdx.x;
+    uint64_t *ent = reinterpret_cast<uint64_t *>(smem_raw);                 // [PR_QB][P] (key << 32 | list)
+    float4 *qs = reinterpret_cast<float4 *>(ent + (size_t) PR_QB * P);       // [PR_QB][dim_pad / 4]
+    const int q0 = blockIdx.x * PR_QB;
+    const int nqb = min(PR_QB, nq - q0);
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int dim4 = dim_pad >> 2;
-    const float4 *q4 = reinterpret_cast<const float4 *>(Q + (size_t) q * dim_pad);
-    for (int i = t; i < dim4; i += PR_THREADS) qs[i] = q4[i];
-    for (int i = lists + t; i < P; i += PR_THREADS) ent[i] = ~0ull;
+    for (int i = t; i < PR_QB * dim4; i += PR_THREADS) {
+        const int b = i / dim4, j = i - b * dim4;
+        qs[i] = b < nqb ? reinterpret_cast<const float4 *>(Q + (size_t) (q0 + b) * dim_pad)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int b = 0; b < PR_QB; b++)
+        for (int i = lists + t; i < P; i += PR_THREADS) ent[(size_t) b * P + i] = ~0ull;
     __syncthreads();
-    // one warp per centre
+    // one warp per centre, PR_QB queries at a time; per (query, centre) the arithmetic is what a single-query pass does
+    // (lane j takes float4 columns j, j + 32, ...; (x + y) + (z + w); xor-shuffles 16 .. 1)
     for (int c = warp; c < lists; c += PR_THREADS / 32) {
         const float4 *c4 = reinterpret_cast<const float4 *>(Cn + (size_t) c * dim_pad);
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 acc[PR_QB];
+#pragma unroll
+        for (int b = 0; b < PR_QB; b++) acc[b] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (!null_query) {
             for (int j = lane; j < dim4; j += 32) {
-                const float4 x = c4[j], y = qs[j];
-                if (METRIC == 0) {
-                    const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
-                    acc.x = fmaf(d0, d0, acc.x); acc.y = fmaf(d1, d1, acc.y); acc.z = fmaf(d2, d2, acc.z); acc.w = fmaf(d3, d3, acc.w);
-                } else {
-                    acc.x = fmaf(x.x, y.x, acc.x); acc.y = fmaf(x.y, y.y, acc.y); acc.z = fmaf(x.z, y.z, acc.z); acc.w = fmaf(x.w, y.w, acc.w);
+                const float4 x = c4[j];
+#pragma unroll
+                for (int b = 0; b < PR_QB; b++) {
+                    const float4 y = qs[b * dim4 + j];
+                    if (METRIC == 0) {
+                        const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
+                        acc[b].x = fmaf(d0, d0, acc[b].x); acc[b].y = fmaf(d1, d1, acc[b].y);
+                        acc[b].z = fmaf(d2, d2, acc[b].z); acc[b].w = fmaf(d3, d3, acc[b].w);
+                    } else {
+                        acc[b].x = fmaf(x.x, y.x, acc[b].x); acc[b].y = fmaf(x.y, y.y, acc[b].y);
+                        acc[b].z = fmaf(x.z, y.z, acc[b].z); acc[b].w = fmaf(x.w, y.w, acc[b].w);
+                    }
                 }
             }
         }
-        float s = (acc.x + acc.y) + (acc.z + acc.w);
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) ent[c] = ((uint64_t) rk_float_to_key(METRIC == 0 ? s : -s) << 32) | (uint32_t) c;
+#pragma unroll
+        for (int b = 0; b < PR_QB; b++) {
+            float sv = (acc[b].x + acc[b].y) + (acc[b].z + acc[b].w);
+            for (int o = 16; o > 0; o >>= 1) sv += __shfl_xor_sync(0xffffffffu, sv, o);
+            if (lane == 0) ent[(size_t) b * P + c] = ((uint64_t) rk_float_to_key(METRIC == 0 ? sv : -sv) << 32) | (uint32_t) c;
+        }
     }
     __syncthreads();
+    // the PR_QB orderings: bitonic sorts side by side (P / 2 compare-exchanges per query and stage)
     for (int size = 2; size <= P; size <<= 1) {
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int i = t; i < (P >> 1); i += PR_THREADS) {
-                const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+            for (int i = t; i < nqb * (P >> 1); i += PR_THREADS) {
+                const int b = i / (P >> 1), ii = i - b * (P >> 1);
+                const int lo = 2 * ii - (ii & (stride - 1)), hi = lo + stride;
                 const bool up = (lo & size) == 0;
-                const uint64_t a = ent[lo], b = ent[hi];
-                if (up ? (b < a) : (a < b)) { ent[lo] = b; ent[hi] = a; }
+                uint64_t *e = ent + (size_t) b * P;
+                const uint64_t x = e[lo], y = e[hi];
+                if (up ? (y < x) : (x < y)) { e[lo] = y; e[hi] = x; }
             }
             __syncthreads();
         }
     }
-    for (int j = t; j < probes; j += PR_THREADS) {
+    for (int i = t; i < nqb * probes; i += PR_THREADS) {
+        const int b = i / probes, j = i - b * probes;
         const int src = probe_offset + j;
-        out_list[(size_t) q * probes + j] = src < lists ? (uint32_t) (ent[src] & 0xFFFFFFFFu) : 0xFFFFFFFFu;
+        out_list[(size_t) (q0 + b) * probes + j] = src < lists ? (uint32_t) (ent[(size_t) b * P + src] & 0xFFFFFFFFu) : 0xFFFFFFFFu;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// list probe, batched (the path every multi-query call takes): two kernels.
+//
+//   rk_ivf_keys_kernel   value(q, centre) for a tile of queries x a range of centres -> keys[q][centre].  A warp keeps
+//                        QW queries in registers (lane j holds float4 columns j, j + 32, ... of each) and walks the
+//                        centres of a tile staged in shared memory by cp.async (two buffers); a block of PK_WARPS warps
+//                        shares every centre tile, so a centre is fetched from L2 once per PK_WARPS * QW queries instead
+//                        of once per query.  Per (query, centre) the arithmetic is the one-block-per-query kernel's, in
+//                        the same order (columns j, j + 32, ... into x / y / z / w sums, (x + y) + (z + w), xor-shuffles
+//                        16 .. 1; out-of-range columns contribute fma(0, 0, acc) = acc), so the keys are bit-identical.
+//   rk_ivf_order_kernel  one block per query: the `need` = probe_offset + probes smallest (key, list) pairs by radix
+//                        select over the keys (bytes of key - min, so the bins spread), gathered in list order (ties at
+//                        the threshold go to the lower list numbers, as the full sort would place them), sorted.
+
+#define PK_WARPS 4
+#define PK_THREADS (PK_WARPS * 32)
+#define PO_THREADS 256
+#define PO_MAX_NEED 1024
+
+__device__ __forceinline__ void pk_cp_async16(void *smem, const void *g)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(g) : "memory");
+}
+
+template <int METRIC, int NJ, int QW, int TC>
+__global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__restrict__ Q, int nq, const float *__restrict__ Cn, int lists,
+                                                                 int dim_pad, int null_query, int centres_per_block,
+                                                                 uint32_t *__restrict__ keys)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4 *tile = reinterpret_cast<float4 *>(smem_raw);                    // [2][TC][dim4]
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int dim4 = dim_pad >> 2;
+    const int qbase = (blockIdx.x * PK_WARPS + warp) * QW;
+    const int c_begin = blockIdx.y * centres_per_block;
+    const int c_end = min(lists, c_begin + centres_per_block);
+    const int ntiles = (c_end - c_begin + TC - 1) / TC;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    auto load_tile = [&](int ti, int buf) {
+        const int c0 = c_begin + ti * TC;
+        const int n4 = min(TC, c_end - c0) * dim4;
+        const float4 *src = reinterpret_cast<const float4 *>(Cn + (size_t) c0 * dim_pad);
+        float4 *dst = tile + (size_t) buf * TC * dim4;
+        for (int i = t; i < n4; i += PK_THREADS) pk_cp_async16(dst + i, src + i);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (ntiles > 0) load_tile(0, 0);
+
+    float4 qr[QW][NJ];
+#pragma unroll
+    for (int b = 0; b < QW; b++)
+#pragma unroll
+        for (int jj = 0; jj < NJ; jj++) {
+            const int j = lane + 32 * jj;
+            qr[b][jj] = (qbase + b < nq && j < dim4) ? reinterpret_cast<const float4 *>(Q + (size_t) (qbase + b) * dim_pad)[j] : zero4;
+        }
+
+    for (int ti = 0; ti < ntiles; ti++) {
+        if (ti + 1 < ntiles) {
+            load_tile(ti + 1, (ti + 1) & 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const float4 *tb = tile + (size_t) (ti & 1) * TC * dim4;
+        const int c0 = c_begin + ti * TC;
+        const int nc = min(TC, c_end - c0);
+        uint32_t mykey = 0;
+        for (int c = 0; c < nc; c++) {
+            float4 acc[QW];
+#pragma unroll
+            for (int b = 0; b < QW; b++) acc[b] = zero4;
+            if (!null_query) {
+                float4 x[NJ];
+#pragma unroll
+                for (int jj = 0; jj < NJ; jj++) {
+                    const int j = lane + 32 * jj;
+                    x[jj] = j < dim4 ? tb[c * dim4 + j] : zero4;
+                }
+#pragma unroll
+                for (int jj = 0; jj < NJ; jj++)
+#pragma unroll
+                    for (int b = 0; b < QW; b++) {
+                        const float4 y = qr[b][jj];
+                        if (METRIC == 0) {
+                            const float d0 = x[jj].x - y.x, d1 = x[jj].y - y.y, d2 = x[jj].z - y.z, d3 = x[jj].w - y.w;
+                            acc[b].x = fmaf(d0, d0, acc[b].x); acc[b].y = fmaf(d1, d1, acc[b].y);
+                            acc[b].z = fmaf(d2, d2, acc[b].z); acc[b].w = fmaf(d3, d3, acc[b].w);
+                        } else {
+                            acc[b].x = fmaf(x[jj].x, y.x, acc[b].x); acc[b].y = fmaf(x[jj].y, y.y, acc[b].y);
+                            acc[b].z = fmaf(x[jj].z, y.z, acc[b].z); acc[b].w = fmaf(x[jj].w, y.w, acc[b].w);
+                        }
+                    }
+            }
+#pragma unroll
+            for (int b = 0; b < QW; b++) {
+                float sv = (acc[b].x + acc[b].y) + (acc[b].z + acc[b].w);
+                for (int o = 16; o > 0; o >>= 1) sv += __shfl_xor_sync(0xffffffffu, sv, o);
+                if (lane == b * TC + c) mykey = rk_float_to_key(METRIC == 0 ? sv : -sv);
+            }
+        }
+        // lane b * TC + c holds key(query b, centre c0 + c): QW runs of TC consecutive keys
+        {
+            const int b = lane / TC, c = lane - b * TC;
+            if (b < QW && c < nc && qbase + b < nq) keys[(size_t) (qbase + b) * lists + c0 + c] = mykey;
+        }
+        __syncthreads();                                                    // the buffer is refilled two tiles on
+    }
+}
+
+__global__ void __launch_bounds__(PO_THREADS) rk_ivf_order_kernel(const uint32_t *__restrict__ keys, int lists, int probe_offset, int probes,
+                                                                  uint32_t *__restrict__ out_list)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t *sel = reinterpret_cast<uint64_t *>(smem_raw);                 // [N2] chosen (key << 32 | list)
+    const int need = probe_offset + probes;                                  // <= lists, <= PO_MAX_NEED
+    int N2 = 32;
+    while (N2 < need) N2 <<= 1;
+    uint32_t *ks = reinterpret_cast<uint32_t *>(sel + N2);                  // [lists] key - min
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t red[2][PO_THREADS / 32];
+    __shared__ uint32_t s_prefix, s_remaining, s_taken_lt, s_taken_eq;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t *kq = keys + (size_t) blockIdx.x * lists;
+
+    uint32_t mn = 0xFFFFFFFFu, mx = 0;
+    for (int i = t; i < lists; i += PO_THREADS) {
+        const uint32_t v = kq[i];
+        ks[i] = v;
+        mn = min(mn, v); mx = max(mx, v);
+    }
+    mn = __reduce_min_sync(0xffffffffu, mn); mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0) { red[0][warp] = mn; red[1][warp] = mx; }
+    __syncthreads();
+    mn = red[0][0]; mx = red[1][0];
+    for (int w = 1; w < PO_THREADS / 32; w++) { mn = min(mn, red[0][w]); mx = max(mx, red[1][w]); }
+    const uint32_t range = mx - mn;
+    const int bits = 32 - __clz(range | 1u);
+    const int npass = (bits + 7) >> 3;
+    if (t == 0) { s_prefix = 0; s_remaining = (uint32_t) need; s_taken_lt = 0; s_taken_eq = 0; }
+    for (int i = t; i < lists; i += PO_THREADS) ks[i] -= mn;                // own entries: no barrier needed in between
+    // radix select of the need-th smallest of ks: one byte per pass, high to low
+    for (int pass = npass - 1; pass >= 0; pass--) {
+        const int shift = pass * 8;
+        hist[t] = 0;
+        __syncthreads();
+        const uint32_t prefix = s_prefix;
+        const uint32_t himask = pass == npass - 1 ? 0u : (0xFFFFFFFFu << (shift + 8));
+        for (int i = t; i < lists; i += PO_THREADS) {
+            const uint32_t v = ks[i];
+            if ((v & himask) == prefix) atomicAdd(&hist[(v >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (warp == 0) {
+            // bin holding the remaining-th entry: 8 bins per lane, warp scan of the lane sums
+            uint32_t h[8], sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) { h[i] = hist[lane * 8 + i]; sum += h[i]; }
+            uint32_t inc = sum;
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            const uint32_t rem = s_remaining;
+            const uint32_t before = inc - sum;
+            if (before < rem && rem <= inc) {
+                uint32_t cum = before;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    if (cum < rem && rem <= cum + h[i]) {
+                        s_prefix = prefix | ((uint32_t) (lane * 8 + i) << shift);
+                        s_remaining = rem - cum;
+                    }
+                    cum += h[i];
+                }
+            }
+        }
+        __syncthreads();
+    }
+    // threshold = s_prefix; s_remaining of the entries equal to it are wanted (lowest list numbers first)
+    const uint32_t thr = s_prefix;
+    const uint32_t want_eq = s_remaining;
+    const uint32_t want_lt = (uint32_t) need - want_eq;
+    for (int i = need + t; i < N2; i += PO_THREADS) sel[i] = ~0ull;
+    for (int base = 0; base < lists; base += PO_THREADS) {
+        const int i = base + t;
+        const uint32_t v = i < lists ? ks[i] : 0xFFFFFFFFu;
+        const bool lt = i < lists && v < thr, eq = i < lists && v == thr;
+        const uint32_t blt = __ballot_sync(0xffffffffu, lt), beq = __ballot_sync(0xffffffffu, eq);
+        if (lane == 0) { red[0][warp] = __popc(blt); red[1][warp] = __popc(beq); }
+        __syncthreads();
+        uint32_t plt = s_taken_lt, peq = s_taken_eq, tlt = 0, teq = 0;
+        for (int w = 0; w < PO_THREADS / 32; w++) {
+            if (w < warp) { plt += red[0][w]; peq += red[1][w]; }
+            tlt += red[0][w]; teq += red[1][w];
+        }
+        plt += __popc(blt & ((1u << lane) - 1u));
+        peq += __popc(beq & ((1u << lane) - 1u));
+        const uint64_t e = ((uint64_t) (v + mn) << 32) | (uint32_t) i;
+        if (lt) sel[plt] = e;                                               // all of them: fewer than need
+        if (eq && peq < want_eq) sel[want_lt + peq] = e;
+        __syncthreads();
+        if (t == 0) { s_taken_lt += tlt; s_taken_eq += teq; }
+        // (the next round reads the counters after its own barrier)
+        __syncthreads();
+        if (s_taken_lt >= want_lt && s_taken_eq >= want_eq) break;
+    }
+    __syncthreads();
+    for (int size = 2; size <= N2; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = t; i < (N2 >> 1); i += PO_THREADS) {
+                const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const uint64_t x = sel[lo], y = sel[hi];
+                if (up ? (y < x) : (x < y)) { sel[lo] = y; sel[hi] = x; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int j = t; j < probes; j += PO_THREADS)
+        out_list[(size_t) blockIdx.x * probes + j] = (uint32_t) (sel[probe_offset + j] & 0xFFFFFFFFu);
 }
 
 size_t rk_ivf_probe_smem(int lists, int dim_pad)
@@ -294,18 +541,75 @@ size_t rk_ivf_probe_smem(int lists, int dim_pad)
     return (size_t) P * 8 + (size_t) dim_pad * 4;
 }
 
-cudaError_t rk_launch_ivf_probe(const float *Q, int nq, const float *C, int lists, int dim_pad, int metric, int null_query,
-                                int probe_offset, int probes, uint32_t *out_list, cudaStream_t stream)
+size_t rk_ivf_probe_keys_bytes(int nq, int lists) { return (size_t) nq * lists * 4; }
+
+template <int METRIC, int NJ, int QW, int TC>
+static cudaError_t launch_keys(const float *Q, int nq, const float *C, int lists, int dim_pad, int null_query, uint32_t *keys, cudaStream_t stream)
 {
+    auto kern = rk_ivf_keys_kernel<METRIC, NJ, QW, TC>;
+    const size_t smem = (size_t) 2 * TC * dim_pad * 4;
+    static bool attr_set = false;
+    if (smem > 48 * 1024 && !attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const int qblocks = (nq + PK_WARPS * QW - 1) / (PK_WARPS * QW);
+    // centre ranges: enough blocks for about eight per SM, at least four tiles each
+    int splits = std::max(1, std::min((lists + 4 * TC - 1) / (4 * TC), (148 * 8 + qblocks - 1) / qblocks));
+    int cpb = (lists + splits - 1) / splits;
+    cpb = (cpb + TC - 1) / TC * TC;
+    splits = (lists + cpb - 1) / cpb;
+    kern<<<dim3(qblocks, splits), PK_THREADS, smem, stream>>>(Q, nq, C, lists, dim_pad, null_query, cpb, keys);
+    return cudaGetLastError();
+}
+
+template <int METRIC>
+static cudaError_t launch_keys_m(const float *Q, int nq, const float *C, int lists, int dim_pad, int null_query, uint32_t *keys, cudaStream_t stream)
+{
+    const int nj = ((dim_pad >> 2) + 31) / 32;
+    if (nj <= 1) return launch_keys<METRIC, 1, 4, 8>(Q, nq, C, lists, dim_pad, null_query, keys, stream);
+    if (nj <= 2) return launch_keys<METRIC, 2, 4, 8>(Q, nq, C, lists, dim_pad, null_query, keys, stream);
+    if (nj <= 4) return launch_keys<METRIC, 4, 4, 8>(Q, nq, C, lists, dim_pad, null_query, keys, stream);
+    if (nj <= 6) return launch_keys<METRIC, 6, 4, 8>(Q, nq, C, lists, dim_pad, null_query, keys, stream);
+    if (nj <= 8) return launch_keys<METRIC, 8, 4, 8>(Q, nq, C, lists, dim_pad, null_query, keys, stream);
+    if (nj <= 12) return launch_keys<METRIC, 12, 2, 4>(Q, nq, C, lists, dim_pad, null_query, keys, stream);
+    return launch_keys<METRIC, 16, 2, 4>(Q, nq, C, lists, dim_pad, null_query, keys, stream);   // dim <= 2000 (ivfflat.h:24)
+}
+
+// keys_ws: nq * lists uint32 of scratch (rk_ivf_probe_keys_bytes) for the batched path, or null.
+cudaError_t rk_launch_ivf_probe(const float *Q, int nq, const float *C, int lists, int dim_pad, int metric, int null_query,
+                                int probe_offset, int probes, uint32_t *out_list, uint32_t *keys_ws, cudaStream_t stream)
+{
+    if (nq <= 0 || probes <= 0) return cudaSuccess;
+    const int need = probe_offset + probes;
+    const bool batched = keys_ws != nullptr && nq >= 4 && need <= PO_MAX_NEED && need <= lists && (dim_pad >> 2) <= 512 &&
+                         getenv("RK_IVF_PROBE_SINGLE") == nullptr;
+    if (batched) {
+        cudaError_t e = metric == 0 ? launch_keys_m<0>(Q, nq, C, lists, dim_pad, null_query, keys_ws, stream)
+                                    : launch_keys_m<1>(Q, nq, C, lists, dim_pad, null_query, keys_ws, stream);
+        if (e != cudaSuccess) return e;
+        int N2 = 32;
+        while (N2 < need) N2 <<= 1;
+        const size_t smem = (size_t) N2 * 8 + (size_t) lists * 4;
+        static bool attr_set = false;
+        if (smem > 48 * 1024 && !attr_set) {
+            e = cudaFuncSetAttribute(rk_ivf_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_set = true;
+        }
+        rk_ivf_order_kernel<<<nq, PO_THREADS, smem, stream>>>(keys_ws, lists, probe_offset, probes, out_list);
+        return cudaGetLastError();
+    }
     const size_t smem = rk_ivf_probe_smem(lists, dim_pad);
-    auto kern = metric == 0 ? rk_ivf_probe_kernel<0> : rk_ivf_probe_kernel<1>;
+    auto kern = metric == 0 ? rk_ivf_probe_kernel<0, 1> : rk_ivf_probe_kernel<1, 1>;
     static bool attr_set[2];
     if (smem > 48 * 1024 && !attr_set[metric & 1]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_set[metric & 1] = true;
     }
-    kern<<<nq, PR_THREADS, smem, stream>>>(Q, C, lists, dim_pad, null_query, probe_offset, probes, out_list);
+    kern<<<nq, PR_THREADS, smem, stream>>>(Q, nq, C, lists, dim_pad, null_query, probe_offset, probes, out_list);
     return cudaGetLastError();
 }
 

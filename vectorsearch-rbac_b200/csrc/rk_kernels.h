@@ -31,7 +31,8 @@ cudaError_t rk_launch_gather_u32(const uint32_t *src, uint32_t *dst, const uint3
 cudaError_t rk_launch_gather_u64(const uint64_t *src, uint64_t *dst, const uint32_t *perm, size_t n, cudaStream_t stream);
 size_t rk_ivf_probe_smem(int lists, int dim_pad);
 cudaError_t rk_launch_ivf_probe(const float *Q, int nq, const float *C, int lists, int dim_pad, int metric, int null_query,
-                                int probe_offset, int probes, uint32_t *out_list, cudaStream_t stream);
+                                int probe_offset, int probes, uint32_t *out_list, uint32_t *keys_ws, cudaStream_t stream);
+size_t rk_ivf_probe_keys_bytes(int nq, int lists);
 cudaError_t rk_launch_ivf_plan(const uint32_t *probe_list, const uint32_t *list_start, int nq, int probes, int chunks,
                                uint32_t chunk_rows, uint32_t kind, RkSegment *segs, cudaStream_t stream);
 

@@ -162,25 +162,46 @@ struct RkProducer {
         } else if (s.kind == RK_SEG_IVFQ) {
             // probed lists [begin, end) of this query; in every list the rows of one document class are contiguous, so
             // what the user may see is one extent per visible class: no per-row test, masked-out rows cost nothing
+            // The class offsets of the NEXT list are fetched (probe entry -> offsets: two round trips) while the extents
+            // of the current one stream, so the producer does not stall between lists.
             const uint64_t c0 = p.ivf_qcls[2 * (size_t) s.query], c1 = p.ivf_qcls[2 * (size_t) s.query + 1];
             const int nc = p.ivf_ncls;
+            const uint32_t *pl = p.ivf_probe_list + (size_t) s.query * p.ivf_probes;
+            bool vis[4];
+#pragma unroll
+            for (int b4 = 0; b4 < 4; b4++) {
+                const int c = b4 * 32 + lane;
+                vis[b4] = c < nc && (((c < 64 ? c0 >> (c & 63) : c1 >> (c & 63)) & 1ull) != 0);
+            }
+            uint32_t lo[4], hi[4], nlo[4], nhi[4];
+            uint32_t run_begin = 0, run_end = 0;
+            auto fetch = [&](uint32_t pi, uint32_t (&a_)[4], uint32_t (&b_)[4]) {
+                const uint32_t *co = p.ivf_cls_off + (size_t) pl[pi] * (nc + 1);
+#pragma unroll
+                for (int b4 = 0; b4 < 4; b4++) {
+                    a_[b4] = 0; b_[b4] = 0;
+                    if (vis[b4]) { a_[b4] = co[b4 * 32 + lane]; b_[b4] = co[b4 * 32 + lane + 1]; }
+                }
+            };
+            if ((uint32_t) s.begin < (uint32_t) s.end) fetch((uint32_t) s.begin, nlo, nhi);
             for (uint32_t pi = (uint32_t) s.begin; pi < (uint32_t) s.end; pi++) {
-                const uint32_t l = p.ivf_probe_list[(size_t) s.query * p.ivf_probes + pi];
-                const uint32_t *co = p.ivf_cls_off + (size_t) l * (nc + 1);
-                for (int cb = 0; cb < nc; cb += 32) {
-                    const int c = cb + lane;
-                    const bool vis = c < nc && (((c < 64 ? c0 >> c : c1 >> (c - 64)) & 1ull) != 0);
-                    uint32_t lo = 0, hi = 0;
-                    if (vis) { lo = co[c]; hi = co[c + 1]; }
-                    uint32_t m = __ballot_sync(0xffffffffu, vis && hi > lo);
+#pragma unroll
+                for (int b4 = 0; b4 < 4; b4++) { lo[b4] = nlo[b4]; hi[b4] = nhi[b4]; }
+                if (pi + 1 < (uint32_t) s.end) fetch(pi + 1, nlo, nhi);
+#pragma unroll
+                for (int b4 = 0; b4 < 4; b4++) {
+                    uint32_t m = __ballot_sync(0xffffffffu, hi[b4] > lo[b4]);
                     while (m) {
                         const int j = __ffs((int) m) - 1;
                         m &= m - 1;
-                        const uint32_t a = __shfl_sync(0xffffffffu, lo, j), b = __shfl_sync(0xffffffffu, hi, j);
-                        emit_run(a, b - a);
+                        const uint32_t a = __shfl_sync(0xffffffffu, lo[b4], j), b = __shfl_sync(0xffffffffu, hi[b4], j);
+                        if (a == run_end) { run_end = b; continue; }        // neighbouring visible classes: one copy
+                        if (run_end > run_begin) emit_run(run_begin, run_end - run_begin);
+                        run_begin = a; run_end = b;
                     }
                 }
             }
+            if (run_end > run_begin) emit_run(run_begin, run_end - run_begin);
         } else if (s.kind == RK_SEG_EXTENTS) {
             // Partition = table of per-document extents; the host resolved which extents touch
             // [begin, end).  RK_EPL * 32 extents are resolved per step: every lane first tests the
