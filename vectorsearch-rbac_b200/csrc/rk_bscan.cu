@@ -396,19 +396,33 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
     while (P < n) P <<= 1;
     for (int i = n + t; i < P; i += RS_THREADS) { s_key[i] = RK_KEY_SENTINEL; s_tid[i] = ~0ull; s_row[i] = 0xFFFFFFFFu; }
     __syncthreads();
-    // 4 rows per warp step, 8 lanes per row: the scan kernel's summation order
-    const int g = lane >> 3, l8 = lane & 7;
-    for (int i0 = warp * 4; i0 < n; i0 += (RS_THREADS / 32) * 4) {
-        const int i = i0 + g;
-        const bool v = i < n;
-        const uint32_t row = p.sel_row[(size_t) q * p.kp + (v ? i : 0)];
-        const float4 *xr = reinterpret_cast<const float4 *>(p.x + (size_t) row * p.dim_pad);
-        float s = 0.f;
-        if (!p.null_query) s = rk_row_sum8<METRIC>(xr, qs, dim4, l8);
-        if (v && l8 == 0) {
-            s_key[i] = rk_float_to_key(METRIC == 0 ? s : -s);
-            s_row[i] = row;
-            s_tid[i] = p.tid[row];
+    // the scan kernel's summation order: 4 rows per warp step, 8 lanes per row — or, for wide rows, one row per warp step
+    if (p.wide_rows) {
+        for (int i = warp; i < n; i += RS_THREADS / 32) {
+            const uint32_t row = p.sel_row[(size_t) q * p.kp + i];
+            const float4 *xr = reinterpret_cast<const float4 *>(p.x + (size_t) row * p.dim_pad);
+            float s = 0.f;
+            if (!p.null_query) s = rk_row_sum32<METRIC>(xr, qs, dim4, lane);
+            if (lane == 0) {
+                s_key[i] = rk_float_to_key(METRIC == 0 ? s : -s);
+                s_row[i] = row;
+                s_tid[i] = p.tid[row];
+            }
+        }
+    } else {
+        const int g = lane >> 3, l8 = lane & 7;
+        for (int i0 = warp * 4; i0 < n; i0 += (RS_THREADS / 32) * 4) {
+            const int i = i0 + g;
+            const bool v = i < n;
+            const uint32_t row = p.sel_row[(size_t) q * p.kp + (v ? i : 0)];
+            const float4 *xr = reinterpret_cast<const float4 *>(p.x + (size_t) row * p.dim_pad);
+            float s = 0.f;
+            if (!p.null_query) s = rk_row_sum8<METRIC>(xr, qs, dim4, l8);
+            if (v && l8 == 0) {
+                s_key[i] = rk_float_to_key(METRIC == 0 ? s : -s);
+                s_row[i] = row;
+                s_tid[i] = p.tid[row];
+            }
         }
     }
     __syncthreads();

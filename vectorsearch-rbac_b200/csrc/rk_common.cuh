@@ -160,6 +160,7 @@ struct RkRescoreParams {
     // probe[0] = query elements that are not small integers, low word of probe[4] = bits of the largest squared query norm
     const unsigned long long *probe;
     int x_integer;               // the corpus holds only small integers
+    int wide_rows;               // the scan scores a row with a whole warp (tile_rows < 64): use its summation order
     uint64_t *out_tid;
     uint32_t *out_doc;
     double *out_dist;
@@ -320,6 +321,17 @@ __device__ __forceinline__ float rk_row_sum8(const float4 *__restrict__ row, con
     s += __shfl_xor_sync(0xffffffffu, s, 4);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
     s += __shfl_xor_sync(0xffffffffu, s, 1);
+    return s;
+}
+
+// whole warp per row: the scan kernel's order for wide rows (tiles of fewer than 64 rows)
+template <int METRIC>
+__device__ __forceinline__ float rk_row_sum32(const float4 *__restrict__ row, const float4 *__restrict__ q, int dim4, int lane)
+{
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = lane; c < dim4; c += 32) rk_acc4<METRIC>(a, row[c], q[c]);
+    float s = (a.x + a.y) + (a.z + a.w);
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     return s;
 }
 

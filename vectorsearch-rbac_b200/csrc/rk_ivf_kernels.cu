@@ -338,8 +338,11 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
                                                                  int dim_pad, int null_query, int centres_per_block,
                                                                  uint32_t *__restrict__ keys)
 {
+    constexpr int RS = NJ * 32;                                             // float4 per staged centre (columns >= dim4 stay zero)
+    constexpr int NV = QW * TC;                                             // (query, centre) values of a warp per tile: 32 or 8
+    static_assert(NV == 32 || NV == 8, "the reduction below is written for 32 or 8 values per tile");
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4 *tile = reinterpret_cast<float4 *>(smem_raw);                    // [2][TC][dim4]
+    float4 *tile = reinterpret_cast<float4 *>(smem_raw);                    // [2][TC][RS]
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int dim4 = dim_pad >> 2;
     const int qbase = (blockIdx.x * PK_WARPS + warp) * QW;
@@ -348,12 +351,17 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
     const int ntiles = (c_end - c_begin + TC - 1) / TC;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
 
+    // zero both buffers once: the column tail and the rows of a ragged last tile then read as zeros, never as stale bits
+    for (int i = t; i < 2 * TC * RS; i += PK_THREADS) tile[i] = zero4;
+    __syncthreads();
     auto load_tile = [&](int ti, int buf) {
         const int c0 = c_begin + ti * TC;
-        const int n4 = min(TC, c_end - c0) * dim4;
-        const float4 *src = reinterpret_cast<const float4 *>(Cn + (size_t) c0 * dim_pad);
-        float4 *dst = tile + (size_t) buf * TC * dim4;
-        for (int i = t; i < n4; i += PK_THREADS) pk_cp_async16(dst + i, src + i);
+        const int nr = min(TC, c_end - c0);
+        for (int r = 0; r < nr; r++) {
+            const float4 *src = reinterpret_cast<const float4 *>(Cn + (size_t) (c0 + r) * dim_pad);
+            float4 *dst = tile + ((size_t) buf * TC + r) * RS;
+            for (int i = t; i < dim4; i += PK_THREADS) pk_cp_async16(dst + i, src + i);
+        }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     if (ntiles > 0) load_tile(0, 0);
@@ -375,47 +383,61 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float4 *tb = tile + (size_t) (ti & 1) * TC * dim4;
+        const float4 *tb = tile + (size_t) (ti & 1) * TC * RS + lane;
         const int c0 = c_begin + ti * TC;
-        const int nc = min(TC, c_end - c0);
-        uint32_t mykey = 0;
-        for (int c = 0; c < nc; c++) {
+        float v[NV];                                                        // v[b * TC + c]: this lane's part of value(query b, centre c0 + c)
+#pragma unroll
+        for (int c = 0; c < TC; c++) {
             float4 acc[QW];
 #pragma unroll
             for (int b = 0; b < QW; b++) acc[b] = zero4;
             if (!null_query) {
-                float4 x[NJ];
 #pragma unroll
                 for (int jj = 0; jj < NJ; jj++) {
-                    const int j = lane + 32 * jj;
-                    x[jj] = j < dim4 ? tb[c * dim4 + j] : zero4;
-                }
-#pragma unroll
-                for (int jj = 0; jj < NJ; jj++)
+                    const float4 x = tb[c * RS + 32 * jj];
 #pragma unroll
                     for (int b = 0; b < QW; b++) {
                         const float4 y = qr[b][jj];
                         if (METRIC == 0) {
-                            const float d0 = x[jj].x - y.x, d1 = x[jj].y - y.y, d2 = x[jj].z - y.z, d3 = x[jj].w - y.w;
+                            const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
                             acc[b].x = fmaf(d0, d0, acc[b].x); acc[b].y = fmaf(d1, d1, acc[b].y);
                             acc[b].z = fmaf(d2, d2, acc[b].z); acc[b].w = fmaf(d3, d3, acc[b].w);
                         } else {
-                            acc[b].x = fmaf(x[jj].x, y.x, acc[b].x); acc[b].y = fmaf(x[jj].y, y.y, acc[b].y);
-                            acc[b].z = fmaf(x[jj].z, y.z, acc[b].z); acc[b].w = fmaf(x[jj].w, y.w, acc[b].w);
+                            acc[b].x = fmaf(x.x, y.x, acc[b].x); acc[b].y = fmaf(x.y, y.y, acc[b].y);
+                            acc[b].z = fmaf(x.z, y.z, acc[b].z); acc[b].w = fmaf(x.w, y.w, acc[b].w);
                         }
                     }
+                }
             }
 #pragma unroll
-            for (int b = 0; b < QW; b++) {
-                float sv = (acc[b].x + acc[b].y) + (acc[b].z + acc[b].w);
-                for (int o = 16; o > 0; o >>= 1) sv += __shfl_xor_sync(0xffffffffu, sv, o);
-                if (lane == b * TC + c) mykey = rk_float_to_key(METRIC == 0 ? sv : -sv);
+            for (int b = 0; b < QW; b++) v[b * TC + c] = (acc[b].x + acc[b].y) + (acc[b].z + acc[b].w);
+        }
+        // The xor-shuffle sums (16, 8, 4, 2, 1) of all NV values at once: at every step a lane keeps one half of its values
+        // and hands the other half to its partner, which adds the same two numbers the full butterfly would add in both
+        // lanes (a + b == b + a), so each value's sum is bit-identical to `for (o = 16; o; o >>= 1) v += shfl_xor(v, o)`.
+        // Afterwards lane L holds value L * NV / 32.
+#pragma unroll
+        for (int st = 0; st < 5; st++) {
+            const int o = 16 >> st;
+            const int n_in = NV >> st;
+            if (n_in > 1) {
+                const bool up = (lane & o) != 0;
+#pragma unroll
+                for (int i = 0; i < n_in / 2; i++) {
+                    const float keep = up ? v[i + n_in / 2] : v[i];
+                    const float send = up ? v[i] : v[i + n_in / 2];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+                }
+            } else {
+                v[0] += __shfl_xor_sync(0xffffffffu, v[0], o);
             }
         }
-        // lane b * TC + c holds key(query b, centre c0 + c): QW runs of TC consecutive keys
         {
-            const int b = lane / TC, c = lane - b * TC;
-            if (b < QW && c < nc && qbase + b < nq) keys[(size_t) (qbase + b) * lists + c0 + c] = mykey;
+            constexpr int LPV = 32 / NV;                                    // lanes holding the same value
+            const int idx = lane / LPV;
+            const int b = idx / TC, c = idx - b * TC;
+            if ((lane % LPV) == 0 && c0 + c < c_end && qbase + b < nq)
+                keys[(size_t) (qbase + b) * lists + c0 + c] = rk_float_to_key(METRIC == 0 ? v[0] : -v[0]);
         }
         __syncthreads();                                                    // the buffer is refilled two tiles on
     }
@@ -547,7 +569,7 @@ template <int METRIC, int NJ, int QW, int TC>
 static cudaError_t launch_keys(const float *Q, int nq, const float *C, int lists, int dim_pad, int null_query, uint32_t *keys, cudaStream_t stream)
 {
     auto kern = rk_ivf_keys_kernel<METRIC, NJ, QW, TC>;
-    const size_t smem = (size_t) 2 * TC * dim_pad * 4;
+    const size_t smem = (size_t) 2 * TC * NJ * 32 * 16;
     static bool attr_set = false;
     if (smem > 48 * 1024 && !attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);

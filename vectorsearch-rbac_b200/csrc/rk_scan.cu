@@ -426,7 +426,7 @@ __device__ __forceinline__ int rk_compact_le(RkCandBuf cb, int n, uint32_t tau, 
 
 // ---------------------------------------------------------------------------------------------
 
-template <int METRIC>
+template <int METRIC, bool WIDE>
 __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkScanParams p)
 {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -531,33 +531,57 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
         const float4 *tile = reinterpret_cast<const float4 *>(smem + L.off_tiles + (size_t) stage * L.tile_bytes);
         const uint32_t *rid = reinterpret_cast<const uint32_t *>(smem + L.off_rowid) + (size_t) stage * p.tile_rows;
         const int nrows = (int) m.nrows;
-        for (int r0 = warp * 4; r0 < nrows; r0 += RK_CONS_WARPS * 8) {
-            const int ra = r0 + g, rb = ra + RK_CONS_WARPS * 4;
+        // Rows per warp step: narrow rows (tiles of 64 rows or more) take 8 lanes each, 2 x 4 rows per warp; wide rows
+        // (few rows per tile) take the whole warp, 2 rows per warp, so that every warp has work in every tile.
+        constexpr bool lanes8 = !WIDE;                    // WIDE <=> p.tile_rows < 64 (rk_launch_scan)
+        const int r_first = lanes8 ? warp * 4 : warp, r_step = lanes8 ? RK_CONS_WARPS * 8 : RK_CONS_WARPS * 2;
+        const int r_pair = lanes8 ? RK_CONS_WARPS * 4 : RK_CONS_WARPS;
+        for (int r0 = r_first; r0 < nrows; r0 += r_step) {
+            const int ra = lanes8 ? r0 + g : r0, rb = ra + r_pair;
             const bool va = ra < nrows, vb = rb < nrows;
             const float4 *pa = tile + (size_t) (va ? ra : 0) * p.dim4;
             const float4 *pb = tile + (size_t) (vb ? rb : 0) * p.dim4;
             float4 aa = make_float4(0.f, 0.f, 0.f, 0.f), ab = aa;
-            if (!p.null_query) {
+            float sa, sb;
+            if (lanes8) {
+                if (!p.null_query) {
 #pragma unroll 4
-                for (int c = l8; c < p.dim4; c += 8) {
-                    const float4 q = qcur[c];
-                    const float4 xa = pa[c];
-                    const float4 xb = pb[c];
-                    rk_acc<METRIC>(aa, xa, q);
-                    rk_acc<METRIC>(ab, xb, q);
+                    for (int c = l8; c < p.dim4; c += 8) {
+                        const float4 q = qcur[c];
+                        const float4 xa = pa[c];
+                        const float4 xb = pb[c];
+                        rk_acc<METRIC>(aa, xa, q);
+                        rk_acc<METRIC>(ab, xb, q);
+                    }
                 }
+                sa = (aa.x + aa.y) + (aa.z + aa.w);
+                sb = (ab.x + ab.y) + (ab.z + ab.w);
+            } else {
+                if (!p.null_query) {
+#pragma unroll 2
+                    for (int c = lane; c < p.dim4; c += 32) {
+                        const float4 q = qcur[c];
+                        const float4 xa = pa[c];
+                        const float4 xb = pb[c];
+                        rk_acc<METRIC>(aa, xa, q);
+                        rk_acc<METRIC>(ab, xb, q);
+                    }
+                }
+                sa = (aa.x + aa.y) + (aa.z + aa.w);
+                sb = (ab.x + ab.y) + (ab.z + ab.w);
+                sa += __shfl_xor_sync(0xffffffffu, sa, 16); sb += __shfl_xor_sync(0xffffffffu, sb, 16);
+                sa += __shfl_xor_sync(0xffffffffu, sa, 8); sb += __shfl_xor_sync(0xffffffffu, sb, 8);
             }
-            float sa = (aa.x + aa.y) + (aa.z + aa.w);
-            float sb = (ab.x + ab.y) + (ab.z + ab.w);
             sa += __shfl_xor_sync(0xffffffffu, sa, 4); sb += __shfl_xor_sync(0xffffffffu, sb, 4);
             sa += __shfl_xor_sync(0xffffffffu, sa, 2); sb += __shfl_xor_sync(0xffffffffu, sb, 2);
             sa += __shfl_xor_sync(0xffffffffu, sa, 1); sb += __shfl_xor_sync(0xffffffffu, sb, 1);
+            const bool lead = lanes8 ? l8 == 0 : lane == 0;
             // survivors of this warp step: one aggregated atomic for the whole warp
             const uint32_t tau = *s_tau;
             const uint32_t ka = rk_float_to_key(METRIC == 0 ? sa : -sa);
             const uint32_t kb = rk_float_to_key(METRIC == 0 ? sb : -sb);
-            const bool ca = l8 == 0 && va && ka <= tau;
-            const bool cb2 = l8 == 0 && vb && kb <= tau;
+            const bool ca = lead && va && ka <= tau;
+            const bool cb2 = lead && vb && kb <= tau;
             const unsigned ma = __ballot_sync(0xffffffffu, ca), mb = __ballot_sync(0xffffffffu, cb2);
             if (ma | mb) {
                 const int na = __popc(ma);
@@ -638,8 +662,13 @@ void rk_scan_geometry(int dim_pad, int *tile_rows, int *nstages, size_t *smem)
 {
     const int row_bytes = dim_pad * 4;
     int tr = 32768 / row_bytes;
-    if (tr < 1) tr = 1;
     if (tr > 256) tr = 256;
+    if (tr < 64) {
+        // wide rows: a warp scores two rows at a time, so tiles of up to 48 KB holding a multiple of 8 rows where possible
+        tr = 49152 / row_bytes;
+        if (tr >= 8) tr &= ~7;
+    }
+    if (tr < 1) tr = 1;
     int ns = 8;
     const size_t budget = 220 * 1024;
     while (ns > 2 && rk_scan_smem_bytes(row_bytes, tr, ns) > budget) ns--;
@@ -651,12 +680,15 @@ void rk_scan_geometry(int dim_pad, int *tile_rows, int *nstages, size_t *smem)
 cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t stream, int grid_override)
 {
     const size_t smem = rk_scan_smem_bytes(p.row_bytes, p.tile_rows, p.nstages);
-    static bool attr_set[64][2];
-    auto kern = p.metric == 0 ? rk_scan_kernel<0> : rk_scan_kernel<1>;
-    if (!attr_set[device & 63][p.metric & 1]) {
+    static bool attr_set[64][4];
+    const bool wide = p.tile_rows < 64;
+    auto kern = wide ? (p.metric == 0 ? rk_scan_kernel<0, true> : rk_scan_kernel<1, true>)
+                     : (p.metric == 0 ? rk_scan_kernel<0, false> : rk_scan_kernel<1, false>);
+    const int ai = (p.metric & 1) | (wide ? 2 : 0);
+    if (!attr_set[device & 63][ai]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        attr_set[device & 63][p.metric & 1] = true;
+        attr_set[device & 63][ai] = true;
     }
     int grid = grid_override > 0 ? grid_override : rk_device_sm_count(device);
     kern<<<grid, RK_SCAN_THREADS, smem, stream>>>(p);

@@ -683,6 +683,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     rp.eps_scale = eps_scale;
     rp.probe = ts.d_probe.as<unsigned long long>();
     rp.x_integer = ts.x_integer ? 1 : 0;
+    rp.wide_rows = ix->tile_rows < 64 ? 1 : 0;
     rp.xnorm_max = ts.xnorm_max;
     rp.out_tid = out.out_tid;
     rp.out_doc = out.out_doc;
