@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(PR_THREADS) rk_ivf_probe_kernel(const float *_
 //
 //   rk_ivf_keys_kernel   value(q, centre) for a tile of queries x a range of centres -> keys[q][centre].  A warp keeps
 //                        QW queries in registers (lane j holds float4 columns j, j + 32, ... of each) and walks the
-//                        centres of a tile staged in shared memory by cp.async (two buffers); a block of PK_WARPS warps
+//                        centres of a tile staged in shared memory by bulk copies (one per centre row, two buffers on mbarriers); a block of PK_WARPS warps
 //                        shares every centre tile, so a centre is fetched from L2 once per PK_WARPS * QW queries instead
 //                        of once per query.  Per (query, centre) the arithmetic is the one-block-per-query kernel's, in
 //                        the same order (columns j, j + 32, ... into x / y / z / w sums, (x + y) + (z + w), xor-shuffles
@@ -327,11 +327,6 @@ __global__ void __launch_bounds__(PR_THREADS) rk_ivf_probe_kernel(const float *_
 #define PK_THREADS (PK_WARPS * 32)
 #define PO_THREADS 256
 #define PO_MAX_NEED 1024
-
-__device__ __forceinline__ void pk_cp_async16(void *smem, const void *g)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(g) : "memory");
-}
 
 template <int METRIC, int NJ, int QW, int TC>
 __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__restrict__ Q, int nq, const float *__restrict__ Cn, int lists,
@@ -351,18 +346,20 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
     const int ntiles = (c_end - c_begin + TC - 1) / TC;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
 
-    // zero both buffers once: the column tail and the rows of a ragged last tile then read as zeros, never as stale bits
+    // zero both buffers once: the column tail of every staged row stays zero (the copies never touch it)
+    __shared__ __align__(8) uint64_t full[2];
     for (int i = t; i < 2 * TC * RS; i += PK_THREADS) tile[i] = zero4;
+    if (t == 0) { rk_mbar_init(&full[0], 1); rk_mbar_init(&full[1], 1); rk_fence_barrier_init(); }
     __syncthreads();
+    // one bulk copy per centre row, issued by the first lanes of warp 0, landing on the buffer's mbarrier
     auto load_tile = [&](int ti, int buf) {
+        if (warp != 0) return;
         const int c0 = c_begin + ti * TC;
         const int nr = min(TC, c_end - c0);
-        for (int r = 0; r < nr; r++) {
-            const float4 *src = reinterpret_cast<const float4 *>(Cn + (size_t) (c0 + r) * dim_pad);
-            float4 *dst = tile + ((size_t) buf * TC + r) * RS;
-            for (int i = t; i < dim4; i += PK_THREADS) pk_cp_async16(dst + i, src + i);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (lane == 0) rk_mbar_arrive_expect_tx(&full[buf], (uint32_t) nr * (uint32_t) dim_pad * 4u);
+        __syncwarp();
+        if (lane < nr)
+            rk_bulk_g2s(tile + ((size_t) buf * TC + lane) * RS, Cn + (size_t) (c0 + lane) * dim_pad, (uint32_t) dim_pad * 4u, &full[buf]);
     };
     if (ntiles > 0) load_tile(0, 0);
 
@@ -376,13 +373,8 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
         }
 
     for (int ti = 0; ti < ntiles; ti++) {
-        if (ti + 1 < ntiles) {
-            load_tile(ti + 1, (ti + 1) & 1);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
-        __syncthreads();
+        if (ti + 1 < ntiles) load_tile(ti + 1, (ti + 1) & 1);
+        rk_mbar_wait(&full[ti & 1], (uint32_t) (ti >> 1) & 1u);
         const float4 *tb = tile + (size_t) (ti & 1) * TC * RS + lane;
         const int c0 = c_begin + ti * TC;
         float v[NV];                                                        // v[b * TC + c]: this lane's part of value(query b, centre c0 + c)
@@ -439,7 +431,7 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
             if ((lane % LPV) == 0 && c0 + c < c_end && qbase + b < nq)
                 keys[(size_t) (qbase + b) * lists + c0 + c] = rk_float_to_key(METRIC == 0 ? v[0] : -v[0]);
         }
-        __syncthreads();                                                    // the buffer is refilled two tiles on
+        __syncthreads();                                                    // the buffer is refilled by the next iteration's copy
     }
 }
 
@@ -571,14 +563,23 @@ static cudaError_t launch_keys(const float *Q, int nq, const float *C, int lists
     auto kern = rk_ivf_keys_kernel<METRIC, NJ, QW, TC>;
     const size_t smem = (size_t) 2 * TC * NJ * 32 * 16;
     static bool attr_set = false;
-    if (smem > 48 * 1024 && !attr_set) {
+    if (smem + 1024 > 48 * 1024 && !attr_set) {                            // (+ the kernel's static shared memory)
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
     const int qblocks = (nq + PK_WARPS * QW - 1) / (PK_WARPS * QW);
-    // centre ranges: enough blocks for about eight per SM, at least four tiles each
-    int splits = std::max(1, std::min((lists + 4 * TC - 1) / (4 * TC), (148 * 8 + qblocks - 1) / qblocks));
+    // centre ranges: about three full waves of resident blocks (the last wave as full as the others), at least four tiles each
+    static int resident = 0;
+    if (resident == 0) {
+        int per_sm = 0, dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PK_THREADS, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+        resident = per_sm * sms;
+    }
+    const int max_splits = std::max(1, (lists + 4 * TC - 1) / (4 * TC));
+    int splits = std::max(1, std::min(max_splits, 3 * resident / qblocks));
     int cpb = (lists + splits - 1) / splits;
     cpb = (cpb + TC - 1) / TC * TC;
     splits = (lists + cpb - 1) / cpb;
