@@ -517,7 +517,8 @@ def main():
             return {"bound": "hbm", "kernel": "rk_ivf_probe_kernel + rk_scan_kernel (list segments)", "achieved": ach, "peak": peak,
                     "unit": "GB/s", "frac": ach / peak, "frac_of_8TBps": ach / 8000.0, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": int(st["algo_bytes"]), "kernel_ms": tms, "probe_ms": float(st["probe_ms"]),
-                    "list_scan_ms": float(st["scan_ms"]), "launches_timed": 1, "traffic": None}
+                    "list_scan_ms": float(st["scan_ms"]), "launches_timed": 1,
+                    "traffic": traffic_per_launch(args.workload, world, flt_name + ":" + eng_name) if args.nprobe == 16 else None}
         if st["tensor_plan"] == 0:
             # CUDA-core scan, one pass per query: HBM.  Bytes per SURVEY.md §8(d): allowed rows x 4d + mask bytes + 12k, per query
             peak, peak_src = peaks()
@@ -652,7 +653,9 @@ def main():
                                  "survey_8d_GBps_both_kernels": (b_centres + b_lists) / (lms + pms) / 1e9 if lms + pms > 0 else None},
                        "note": "SURVEY.md 8(d) counts the centres once per query (lists x 4d); the batched probe reads them once per "
                                "16 queries from L2, so that figure would exceed the HBM peak and is reported only under probe; the "
-                               "list scan reads only the rows the user may see (one extent per visible document class and probed list)"})
+                               "list scan reads only the rows the user may see (one extent per visible document class and probed list); "
+                               "a read-only stream can exceed the copy-measured peak, and queries probing the same lists share rows in L2 "
+                               "(traffic = dram bytes of the launch)"})
             line["config"].update({"recall_at_100": rec, "nprobe": args.nprobe, "lists": ivf_lists, "ivf_build_s": ivf_build_s,
                                    "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
         if ivf_lists and not args.no_cpu:
