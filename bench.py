@@ -201,26 +201,33 @@ class ClockSampler:
         except Exception:
             self.nv = None
 
-    def _run(self):
+    def _sample(self):
         nv = self.nv
         names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
                  "hw_power_brake": 0x80, "sync_boost": 0x10, "display_clock_setting": 0x100}
-        while not self._stop.is_set():
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                try:
-                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                except Exception:
-                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for n, bit in names.items():
-                    if r & bit:
-                        self.reasons.add(n)
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
             except Exception:
-                pass
-            time.sleep(0.01)
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for n, bit in names.items():
+                if r & bit:
+                    self.reasons.add(n)
+        except Exception:
+            pass
+
+    def _run(self):
+        # The first sample is taken by __enter__ (right after the warm-up steps, before the first timed launch); the thread
+        # then samples every 10 ms.  An NVML query takes the driver about a millisecond and competes with the launching
+        # thread, which a timed region of a few 1-ms steps cannot absorb (8 ranks, C4: 1.36 ms per step with a query
+        # inside the region against 0.9 ms without), so regions shorter than 10 ms carry the pre-region sample only.
+        while not self._stop.wait(0.01):
+            self._sample()
 
     def __enter__(self):
         if self.nv:
+            self._sample()
             self._t = threading.Thread(target=self._run, daemon=True)
             self._t.start()
         return self
@@ -387,8 +394,6 @@ def main():
     ix = vr.Index(dim, metric=metric, device=local_rank, k_max=max(128, args.k))
     ix.reserve_rows(len(mine))
     ivf_lists = int(wl.get("ivf_lists", 0))
-    if ivf_lists and world > 1:
-        raise SystemExit("bench.py: workload c4 (IVFFlat) runs on one GPU")
     keep_host = world == 1 and rank == 0 and not args.no_cpu and not ivf_lists
     X_host = np.empty((rows, dim), dtype=np.float32) if keep_host else None
     CH = 1 << 20 if dim <= 256 else 1 << 18
@@ -414,7 +419,8 @@ def main():
     ivf_build_s = None
     if ivf_lists:
         t_b = time.perf_counter()
-        ix.build_ivf(ivf_lists, seed=42)
+        # N > 1: rank 0 trains the centres on its stripe, all ranks assign their rows to them (sharded.build_ivf_sharded)
+        sharded.build_ivf_sharded(ix, rank, world, ivf_lists, seed=42, device=dev)
         torch.cuda.synchronize()
         ivf_build_s = time.perf_counter() - t_b
     torch.cuda.empty_cache()
@@ -442,7 +448,7 @@ def main():
         # 4.45-4.60 ms per step against 4.53 serial — the collective's CTAs slow the persistent scan kernel by what the
         # overlap saves — so it is not the default).
         step_fn = searcher.search_device_pipelined if (world > 1 and args.pipeline) else searcher.search_device
-        if ivf_lists:
+        if ivf_lists and world == 1:
             def step_fn(Qd, users, o):       # the index-probe path of the C-ABI (one GPU)
                 bf = searcher._get_bufs(Qd.shape[0], o.k)
                 ix.search_batch_device(Qd.data_ptr(), Qd.shape[0], users, o, bf["tid"].data_ptr(), bf["doc"].data_ptr(),
@@ -556,6 +562,14 @@ def main():
     if engine == vr.ENGINE_SCAN and not args.no_batched and not ivf_lists:
         batched_r = measure(vr.ENGINE_AUTO)
 
+    ex_exact = None
+    if ivf_lists:
+        # the engine's own exact filtered result (probes = 0) of the step's queries, for recall@k: a sharded search at
+        # N > 1, so every rank takes part
+        opts0 = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=vr.ENGINE_AUTO)
+        ex_exact = [t.cpu().numpy() for t in searcher.search_device(Q, qusers, opts0)]
+        barrier()
+
     if rank == 0:
         st = main_r["stats"]
         line = {
@@ -594,8 +608,7 @@ def main():
                 "tensor_redo": int(batched_r["stats"]["tensor_redo"]), "clocks": batched_r["clk"]}
         if ivf_lists:
             # recall@k against the engine's own exact filtered result (probes = 0), which the parity tests pin to the oracle
-            opts0 = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=vr.ENGINE_AUTO)
-            ex = [t.cpu().numpy() for t in searcher.search_device(Q, qusers, opts0)]
+            ex = ex_exact
             got_t, got_c = main_r["outs_h"][0].numpy(), main_r["outs_h"][3].numpy()
             rec = float(np.mean([len(set(ex[0][i, :ex[3][i]].tolist()) & set(got_t[i, :got_c[i]].tolist())) / max(1, int(ex[3][i]))
                                  for i in range(args.nq)]))
@@ -604,9 +617,9 @@ def main():
             # row of the probed lists, so the visible rows are recounted here from the index's list assignment.
             from oracle import oracle as orc_
             m_ = orc_.METRIC_L2 if wl["metric"] == "l2" else orc_.METRIC_IP
-            centers_, row_list_ = ix.ivf_info(rows)
+            centers_, row_list_ = ix.ivf_info(len(mine))     # N > 1: this rank's stripe of every list (rank 0's GPU is reported)
             off_, lrows_ = orc_.ivf_lists_csr(row_list_, ivf_lists)
-            doc_np = np.asarray(doc)
+            doc_np = np.asarray(doc)[mine]
             roles_of_, docs_of_ = {}, {}
             for u_, r_ in ur:
                 roles_of_.setdefault(int(u_), set()).add(int(r_))
@@ -617,7 +630,7 @@ def main():
             for i in range(args.nq):
                 u_ = int(qusers[i])
                 if u_ not in vis_cache:
-                    v_ = np.zeros(int(doc_np.max()) + 2, dtype=bool)
+                    v_ = np.zeros(int(np.asarray(doc).max()) + 2, dtype=bool)
                     for r_ in roles_of_.get(u_, ()):
                         v_[np.asarray(docs_of_.get(r_, []), dtype=np.int64)] = True
                     vis_cache[u_] = v_
@@ -658,7 +671,7 @@ def main():
                                "(traffic = dram bytes of the launch)"})
             line["config"].update({"recall_at_100": rec, "nprobe": args.nprobe, "lists": ivf_lists, "ivf_build_s": ivf_build_s,
                                    "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
-        if ivf_lists and not args.no_cpu:
+        if ivf_lists and not args.no_cpu and world == 1:
             # CPU leg: the oracle's restatement of ivfscan.c with the reference's distance loops, same centres and lists, on
             # a sample of the queries; only the rows of the lists the sample probes are brought to the host
             from oracle import oracle as orc

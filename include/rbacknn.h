@@ -205,6 +205,16 @@ int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint3
  * ascending, padded with (+Inf, UINT64_MAX).  d_key/d_tid/d_doc are device buffers [nq*k]. */
 int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
                           const rk_scan_opts *o, float *d_key, uint64_t *d_tid, uint32_t *d_doc);
+/* IVFFlat list choice alone (GetScanLists, pgvector/src/ivfscan.c:36-107): for each of nq device-resident queries the
+ * min(o->probes, lists) nearest lists, nearest first, as list numbers into the device buffer d_lists [nq][that many].
+ * With centres replicated on every rank of a sharded index each rank chooses the lists of nq/G
+ * queries, the choices are all-gathered (4 * probes bytes per query) and rk_search_batch_shard_probed scans them:
+ * the same lists every rank would have chosen itself, at 1/G of the centre scoring per rank. */
+int rk_ivf_probe_device(rk_index *ix, size_t nq, const float *dQ, const rk_scan_opts *o, uint32_t *d_lists);
+/* rk_search_batch_shard with the list choice supplied (d_lists from rk_ivf_probe_device, same o->probes). */
+int rk_search_batch_shard_probed(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                                 const rk_scan_opts *o, const uint32_t *d_lists, float *d_key, uint64_t *d_tid,
+                                 uint32_t *d_doc);
 /* G-way select over all-gathered shard results; writes the final [nq][k] like
  * rk_search_batch_device.  Device pointers.  Shard j's block of each array starts
  * shard_stride_bytes * j bytes after shard 0's (0 = dense [G][nq][k] arrays), so one all-gather of

@@ -194,3 +194,72 @@ def test_ivf_probe_batched_path_matches_single_query_path(metric, dim, monkeypat
                 np.testing.assert_array_equal(got_b[0][qi, :n], t)
     monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
     ix.close()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_ivf_sharded_lists_match_single_index(world):
+    """centres replicated, every list's rows striped with their documents (d mod G).  G shards built
+    from the same centres, searched with probes > 0, exchanged and merged must return exactly what one index holding
+    the whole lists returns (every rank chooses the same lists; a row lives on one rank)."""
+    import torch
+    import vectorsearch_rbac_b200 as vr
+    from vectorsearch_rbac_b200 import sharded
+    ds = make_dataset("sift", n=9000, dim=64, rows_per_doc=15, rbac="random", num_users=20, num_roles=8)
+    lists = 40
+    centers = ds["X"][np.random.default_rng(3).choice(len(ds["X"]), lists, replace=False)].copy()
+    full = load_index(ds, role_parts=False, combo_parts=False)
+    full.finalize()
+    full.build_ivf_from_centers(centers)
+    np.testing.assert_array_equal(full.ivf_centers(), centers)
+    Q, users = _queries(ds, 24)
+    k, nq = 40, 24
+    dev = torch.device("cuda", 0)
+    dQ = torch.from_numpy(Q).to(dev)
+    per = sharded.packed_bytes(nq, k)
+    shards = []
+    for r in range(world):
+        mine = sharded.local_row_mask(ds["doc"], r, world)
+        local = dict(ds, X=ds["X"][mine], tid=ds["tid"][mine], doc=ds["doc"][mine])
+        ix = load_index(local, role_parts=False, combo_parts=False)
+        ix.finalize()
+        ix.build_ivf_from_centers(centers)
+        shards.append(ix)
+    for probes in (1, 4, lists):
+        for flt in (vr.FILTER_BITMASK, vr.FILTER_NONE):
+            recv = torch.empty(per * world, dtype=torch.uint8, device=dev)
+            opts = sharded.make_opts(k, probes=probes, filter=flt)
+            # probes == 4: the list choice comes from outside (each rank chooses for nq / G queries and the choices are
+            # all-gathered — here: shard r chooses for its slice, the slices are concatenated)
+            ext = None
+            if probes == 4:
+                P = min(probes, lists)
+                ext = torch.zeros((nq, P), dtype=torch.int32, device=dev)
+                cnt = (nq + world - 1) // world
+                for r, ix in enumerate(shards):
+                    lo, hi = min(nq, r * cnt), min(nq, (r + 1) * cnt)
+                    if hi > lo:
+                        ix.ivf_probe_device(dQ[lo:hi].data_ptr(), hi - lo, opts, ext[lo:hi].data_ptr())
+                        ix.synchronize()
+            for r, ix in enumerate(shards):
+                s = sharded.ShardedSearcher(ix, r, world, device=dev)
+                if ext is None:
+                    s._cuda_local_search(dQ, users, opts, recv[r * per:(r + 1) * per])
+                else:
+                    key, doc, tid = sharded.split_packed(recv[r * per:(r + 1) * per], nq, k)
+                    ix.search_batch_shard_probed(dQ.data_ptr(), nq, users, opts, ext.data_ptr(), key.data_ptr(), tid.data_ptr(),
+                                                 doc.data_ptr())
+                ix.synchronize()
+            s = sharded.ShardedSearcher(shards[0], 0, world, device=dev)
+            b = s._get_bufs(nq, k)
+            s._cuda_merge(recv, nq, k, (b["tid"], b["doc"], b["dist"], b["cnt"]))
+            shards[0].synchronize()
+            got = (b["tid"].cpu().numpy().view(np.uint64), b["doc"].cpu().numpy(), b["dist"].cpu().numpy(), b["cnt"].cpu().numpy())
+            exp = full.search_batch(Q, users, k, probes=probes, filter=flt)
+            np.testing.assert_array_equal(got[3], exp[3])
+            for q in range(nq):
+                n = int(exp[3][q])
+                np.testing.assert_array_equal(got[0][q, :n], exp[0][q, :n])
+                np.testing.assert_array_equal(got[1][q, :n], exp[1][q, :n])
+                np.testing.assert_array_equal(got[2][q, :n].view(np.uint64), exp[2][q, :n].view(np.uint64))
+    for ix in shards + [full]:
+        ix.close()

@@ -70,6 +70,25 @@ def _worker(rank, world, port, out_dir):
             c = int(exp[4][q])
             np.testing.assert_array_equal(tid.numpy().view(np.uint64)[q, :c], exp[0][q, :c])
             np.testing.assert_array_equal(dst.numpy()[q, :c], exp[2][q, :c])
+
+        # IVFFlat over the stripes: rank 0 trains, everybody assigns to rank 0's centres (stand-in index objects:
+        # k-means and assignment are CUDA stages covered by -m gpu; this checks who calls what with which centres)
+        class FakeIndex:
+            dim = 32
+            device = 0
+            def __init__(self): self.trained = False; self.given = None
+            def build_ivf(self, lists, seed=42):
+                self.trained = True
+                self._c = np.random.default_rng(seed + 1000 * rank).random((lists, self.dim), dtype=np.float32)
+            def ivf_centers(self): return self._c
+            def build_ivf_from_centers(self, c): self.given = np.array(c, copy=True)
+        fi = FakeIndex()
+        centres = sharded.build_ivf_sharded(fi, rank, world, lists=7, seed=42, device=torch.device("cpu"))
+        expect = np.random.default_rng(42).random((7, 32), dtype=np.float32)       # what rank 0 "trained"
+        np.testing.assert_array_equal(centres, expect)
+        assert fi.trained == (rank == 0)
+        if rank != 0:
+            np.testing.assert_array_equal(fi.given, expect)
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
         dist.destroy_process_group()

@@ -60,6 +60,8 @@ SIGNATURES = {
     "rk_search_batch": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_search_batch_device": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_search_batch_shard": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P]),
+    "rk_ivf_probe_device": (C.c_int, [_P, C.c_size_t, _P, C.POINTER(RkScanOpts), _P]),
+    "rk_search_batch_shard_probed": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_merge_shards": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_size_t, _P, _P, _P, _P, _P, _P, _P]),
     "rk_set_stream": (C.c_int, [_P, _P]),
     "rk_synchronize": (C.c_int, [_P]),

@@ -174,9 +174,7 @@ extern "C" void rk_close(rk_index *ix)
 
 static int check_finite(const float *x, size_t n)
 {
-    for (size_t i = 0; i < n; i++)
-        if (!std::isfinite(x[i])) return -1;
-    return 0;
+    return rk_all_finite(x, n) ? 0 : -1;
 }
 
 extern "C" int rk_load_rows(rk_index *ix, const float *x, const uint64_t *tid, const uint32_t *doc, size_t n)

@@ -1,6 +1,8 @@
 // rk_host.h — host-side state of librbacknn (internal; the public surface is include/rbacknn.h).
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdint>
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <string>
@@ -12,6 +14,24 @@
 #include "rk_kernels.h"
 
 int rk_fail(int code, const char *fmt, ...);
+
+// true when no element is NaN or +-Inf (exponent bits all ones).  Branch-free blocks so the compiler vectorises it: the
+// check sits on the host path of every call (pgvector rejects such vectors in vector_in, vector.c:102-113).
+static inline bool rk_all_finite(const float *x, size_t n)
+{
+    size_t i = 0;
+    while (i < n) {
+        const size_t e = n - i > 8192 ? i + 8192 : n;
+        uint32_t bad = 0;
+        for (; i < e; i++) {
+            uint32_t v;
+            memcpy(&v, x + i, 4);
+            bad |= (uint32_t) ((v & 0x7f800000u) == 0x7f800000u);
+        }
+        if (bad) return false;
+    }
+    return true;
+}
 
 struct DevBuf {
     void *p = nullptr;
@@ -38,6 +58,7 @@ struct Workspace {
     DevBuf segs, order, ctl /* [0]=nseg [1]=counter */, cand_key, cand_tid, cand_row, cand_count, qseg, qmask, dq;
     DevBuf out_tid, out_doc, out_dist, out_count;
     DevBuf probe_key, probe_list;        // IVF: per-query selected lists
+    const uint32_t *ext_probe = nullptr; // IVF: list choice supplied by the caller (rk_search_batch_shard_probed), [nq][probes]
     DevBuf ex_key, ex_tid, ex_doc;       // exchange-form results
     PinBuf h_plan_ring[2], h_out;        // plan staging alternates so the host may run one batch ahead
     cudaEvent_t ring_a[RK_TIMING_RING] = {}, ring_b[RK_TIMING_RING] = {};   // scan-kernel event pairs

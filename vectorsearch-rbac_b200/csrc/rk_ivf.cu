@@ -226,6 +226,28 @@ extern "C" int rk_ivf_info(const rk_index *ix, int *lists, float *centers, uint3
 }
 
 // ---------------------------------------------------------------------------------------------
+// list choice alone (the sharded index splits it by query across ranks)
+
+int rk_ivf_probe_only(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const rk_scan_opts *o, uint32_t *d_lists)
+{
+    IvfIndex &iv = ix->ivf;
+    if (!iv.built) return rk_fail(RK_ERR_STATE, "rk_ivf_probe_device: no IVFFlat index was built");
+    const int probes = std::min(o->probes, iv.lists);
+    if (probes < 1) return rk_fail(RK_ERR_INVALID, "rk_ivf_probe_device: probes = %d", o->probes);
+    RK_CUDA(cudaSetDevice(ix->device));
+    // key scratch: nq x lists x 4 B, in slices of at most 256 MB
+    const size_t qb = std::max<size_t>(1, std::min<size_t>(nq, ((size_t) 256 << 20) / ((size_t) iv.lists * 4)));
+    if (ws.probe_key.ensure(std::max<size_t>(rk_ivf_probe_keys_bytes((int) qb, iv.lists), 16)) != 0) return RK_ERR_CUDA;
+    for (size_t q0 = 0; q0 < nq; q0 += qb) {
+        const size_t n = std::min(qb, nq - q0);
+        RK_CUDA(rk_launch_ivf_probe(dQ + q0 * (size_t) ix->dim_pad, (int) n, iv.d_centers.as<float>(), iv.lists, ix->dim_pad, ix->metric,
+                                    o->null_query, 0, probes, d_lists + q0 * (size_t) probes, ws.probe_key.as<uint32_t>(), ws.stream));
+        ix->total_launches += 2;
+    }
+    return RK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // search
 
 void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &p, bool ivf_store, const float *dQ,
@@ -354,17 +376,19 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
 
         if (nseg) {
             if (ws.timing && q0 == 0) RK_CUDA(cudaEventRecord(ws.ev[4], ws.stream));
-            RK_CUDA(rk_launch_ivf_probe(dQ, (int) nq, iv.d_centers.as<float>(), lists, ix->dim_pad, ix->metric, o->null_query,
-                                        probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.probe_key.as<uint32_t>(), ws.stream));
+            const uint32_t *plist = ws.ext_probe ? ws.ext_probe + q0 * (size_t) probes : ws.probe_list.as<uint32_t>();
+            if (!ws.ext_probe)
+                RK_CUDA(rk_launch_ivf_probe(dQ, (int) nq, iv.d_centers.as<float>(), lists, ix->dim_pad, ix->metric, o->null_query,
+                                            probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.probe_key.as<uint32_t>(), ws.stream));
             if (!cls_mode)
-                RK_CUDA(rk_launch_ivf_plan(ws.probe_list.as<uint32_t>(), iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
+                RK_CUDA(rk_launch_ivf_plan(plist, iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
                                            chunk_rows, kind, ws.segs.as<RkSegment>(), ws.stream));
             if (ws.timing && q0 == 0) { RK_CUDA(cudaEventRecord(ws.ev[5], ws.stream)); ws.timed_probe = true; }
             RkScanParams p;
             rk_fill_scan_params(ix, ws, p, true, dQ, o, k);
             p.seg_order = nullptr;
             if (cls_mode) {
-                p.ivf_probe_list = ws.probe_list.as<uint32_t>();
+                p.ivf_probe_list = plist;
                 p.ivf_probes = probes;
                 p.ivf_cls_off = iv.d_cls_off.as<uint32_t>();
                 p.ivf_ncls = iv.ncls;
@@ -375,7 +399,8 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
             const int grid = (int) std::min<uint32_t>((uint32_t) ix->sm_count, nseg);
             RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid));
             if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot], ws.stream)); ws.timed_scan = true; ws.ring_n++; }
-            ws.launches += 3;
+            // list choice (keys + ordering kernels for a batch, one kernel for a single query), work list, list scan
+            ws.launches += (ws.ext_probe ? 0 : (nq >= 4 ? 2 : 1)) + (cls_mode ? 0 : 1) + 1;
         }
         RkSelectParams out = out_all;
         const size_t ob = q0 * (size_t) k;

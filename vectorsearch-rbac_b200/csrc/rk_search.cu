@@ -421,8 +421,7 @@ static int host_search(rk_index *ix, Workspace &ws, size_t nq, const float *Q, c
 {
     RK_CUDA(cudaSetDevice(ix->device));
     if (!o->null_query) {
-        for (size_t i = 0; i < nq * (size_t) ix->dim; i++)
-            if (!std::isfinite(Q[i])) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
+        if (!rk_all_finite(Q, nq * (size_t) ix->dim)) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
     }
     int rc = stage_queries(ix, ws, nq, Q);
     if (rc < 0) return rc;
@@ -490,6 +489,33 @@ extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, c
     memset(&out, 0, sizeof out);
     out.out_key = d_key; out.out_tid = d_tid; out.out_doc = d_doc;
     return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
+}
+
+int rk_ivf_probe_only(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const rk_scan_opts *o, uint32_t *d_lists);
+
+extern "C" int rk_ivf_probe_device(rk_index *ix, size_t nq, const float *dQ, const rk_scan_opts *o, uint32_t *d_lists)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (!ix->finalized) return rk_fail(RK_ERR_STATE, "rk_ivf_probe_device: call rk_finalize first");
+    int rc = validate_opts(ix, o);
+    if (rc < 0) return rc;
+    if (nq == 0) return RK_OK;
+    if (!dQ || !d_lists) return rk_fail(RK_ERR_INVALID, "rk_ivf_probe_device: NULL pointer");
+    if (ix->dim != ix->dim_pad) return rk_fail(RK_ERR_UNSUPPORTED, "device queries need dim %% 4 == 0 (dim = %d)", ix->dim);
+    return rk_ivf_probe_only(ix, ix->ws, nq, dQ, o, d_lists);
+}
+
+extern "C" int rk_search_batch_shard_probed(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                                            const rk_scan_opts *o, const uint32_t *d_lists, float *d_key, uint64_t *d_tid,
+                                            uint32_t *d_doc)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    if (!d_lists) return rk_fail(RK_ERR_INVALID, "rk_search_batch_shard_probed: NULL list choice");
+    if (!o || o->probes < 1) return rk_fail(RK_ERR_INVALID, "rk_search_batch_shard_probed: probes must be >= 1");
+    ix->ws.ext_probe = d_lists;
+    const int rc = rk_search_batch_shard(ix, nq, dQ, user_ids, o, d_key, d_tid, d_doc);
+    ix->ws.ext_probe = nullptr;
+    return rc;
 }
 
 extern "C" int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, size_t shard_stride_bytes, const float *d_key,

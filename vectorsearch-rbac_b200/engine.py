@@ -134,6 +134,14 @@ class Index:
         _check(lib.rk_ivf_info(self._h, C.byref(n), centers.ctypes.data, row_list.ctypes.data))
         return centers, row_list
 
+    def ivf_centers(self) -> np.ndarray:
+        """The list centres [lists, dim] of the built IVFFlat index."""
+        n = C.c_int(0)
+        _check(lib.rk_ivf_info(self._h, C.byref(n), None, None))
+        centers = np.empty((n.value, self.dim), dtype=np.float32)
+        _check(lib.rk_ivf_info(self._h, C.byref(n), centers.ctypes.data, None))
+        return centers
+
     # -- search
     def search_batch(self, Q: np.ndarray, user_ids: Optional[Sequence[int]], k: int, probes: int = 0,
                      filter: int = FILTER_PARTITION, layout: int = LAYOUT_AUTO, keep_duplicates: bool = False,
@@ -168,6 +176,21 @@ class Index:
                            d_tid: int, d_doc: int) -> None:
         users = _u32(user_ids)
         _check(lib.rk_search_batch_shard(self._h, nq, dQ_ptr, users.ctypes.data, C.byref(opts), d_key, d_tid, d_doc))
+
+    def ivf_lists(self) -> int:
+        n = C.c_int(0)
+        _check(lib.rk_ivf_info(self._h, C.byref(n), None, None))
+        return int(n.value)
+
+    def ivf_probe_device(self, dQ_ptr: int, nq: int, opts: RkScanOpts, d_lists: int) -> None:
+        """List choice alone: min(opts.probes, lists) list numbers per query, nearest first, into d_lists (device u32)."""
+        _check(lib.rk_ivf_probe_device(self._h, nq, dQ_ptr, C.byref(opts), d_lists))
+
+    def search_batch_shard_probed(self, dQ_ptr: int, nq: int, user_ids: Sequence[int], opts: RkScanOpts, d_lists: int,
+                                  d_key: int, d_tid: int, d_doc: int) -> None:
+        users = _u32(user_ids)
+        _check(lib.rk_search_batch_shard_probed(self._h, nq, dQ_ptr, users.ctypes.data, C.byref(opts), d_lists, d_key,
+                                                d_tid, d_doc))
 
     def merge_shards(self, nq: int, k: int, n_shards: int, d_key: int, d_tid: int, d_doc: int, d_out_tid: int,
                      d_out_doc: int, d_out_dist: int, d_out_count: int, shard_stride_bytes: int = 0) -> None:

@@ -52,13 +52,43 @@ def split_packed(buf: torch.Tensor, nq: int, k: int) -> Tuple[torch.Tensor, torc
     return key, doc, tid
 
 
+def build_ivf_sharded(index, rank: int, world: int, lists: int, seed: int = 42, group=None,
+                      device: Optional[torch.device] = None) -> np.ndarray:
+    """IVFFlat over a document-striped corpus ("same centroids replicated on all GPUs, each list's rows
+    striped").  Rank 0 trains the centres on its own stripe — documents are striped d mod G, so the stripe is a
+    uniform 1/G sample of the table pgvector would sample from (ivfbuild.c:404-441) — the centres are broadcast, and
+    every other rank assigns its rows to them (`build_ivf_from_centers`, ivfbuild.c:141-198).  All ranks then score
+    the same centres with the same arithmetic, choose the same lists for a query, scan their stripe of those lists,
+    and the usual all-gather + merge returns what one GPU holding the whole lists would return.
+    Returns the centres.  `device` = where the broadcast buffer lives (cuda for NCCL, cpu for gloo)."""
+    if world == 1:
+        index.build_ivf(lists, seed=seed)
+        return index.ivf_centers()
+    dev = device if device is not None else torch.device("cuda", index.device)
+    if rank == 0:
+        index.build_ivf(lists, seed=seed)
+        c = torch.from_numpy(index.ivf_centers()).to(dev)
+    else:
+        c = torch.empty((lists, index.dim), dtype=torch.float32, device=dev)
+    dist.broadcast(c, src=0, group=group)
+    centers = c.cpu().numpy()
+    if rank != 0:
+        index.build_ivf_from_centers(centers)
+    return centers
+
+
 class ShardedSearcher:
     """Search over this rank's shard + all-gather merge.  `index` is this rank's engine.Index (already
     loaded with the rows of the documents it owns, and finalized)."""
 
     def __init__(self, index, rank: int, world: int, group=None, device: Optional[torch.device] = None,
-                 local_search: Optional[Callable] = None, merge: Optional[Callable] = None):
+                 local_search: Optional[Callable] = None, merge: Optional[Callable] = None, shard_probe: bool = True):
         self.index, self.rank, self.world, self.group = index, rank, world, group
+        # IVFFlat (opts.probes > 0) on G > 1 ranks: the centres are replicated, so the list choice of the batch is split by
+        # query — rank r scores the centres for queries [r * ceil(nq / G), ...) only — and all-gathered (4 * probes bytes
+        # per query) before every rank scans its stripe of the chosen lists.  False: every rank chooses for all queries.
+        self.shard_probe = shard_probe
+        self._ivf_lists = None
         self.device = device if device is not None else torch.device("cuda", index.device)
         self._local_search = local_search or self._cuda_local_search
         self._merge = merge or self._cuda_merge
@@ -78,9 +108,33 @@ class ShardedSearcher:
                 "merge": sum(c.elapsed_time(d) for _, _, c, d in ev) / n}
 
     # -- default (CUDA) stages ---------------------------------------------------------------
+    def _cuda_probe_exchange(self, dQ: torch.Tensor, opts) -> torch.Tensor:
+        """Device tensor [>= nq, P] int32 (P = min(probes, lists)): row q = the lists of query q, nearest first."""
+        nq = dQ.shape[0]
+        if self._ivf_lists is None:
+            self._ivf_lists = self.index.ivf_lists()
+        P = min(int(opts.probes), self._ivf_lists)
+        cnt = (nq + self.world - 1) // self.world
+        keyb = ("probe", nq, P)
+        if keyb not in self._bufs:
+            self._bufs[keyb] = (torch.zeros((cnt, P), dtype=torch.int32, device=self.device),
+                                torch.empty((cnt * self.world, P), dtype=torch.int32, device=self.device))
+        send, recv = self._bufs[keyb]
+        lo = min(nq, self.rank * cnt)
+        hi = min(nq, lo + cnt)
+        if hi > lo:
+            self.index.ivf_probe_device(dQ[lo:hi].data_ptr(), hi - lo, opts, send.data_ptr())
+        dist.all_gather_into_tensor(recv, send, group=self.group)
+        return recv
+
     def _cuda_local_search(self, dQ: torch.Tensor, users: np.ndarray, opts, send: torch.Tensor) -> None:
         nq = dQ.shape[0]
         key, doc, tid = split_packed(send, nq, opts.k)
+        if int(opts.probes) > 0 and self.world > 1 and self.shard_probe and dist.is_initialized():
+            lists = self._cuda_probe_exchange(dQ, opts)
+            self.index.search_batch_shard_probed(dQ.data_ptr(), nq, users, opts, lists.data_ptr(), key.data_ptr(),
+                                                 tid.data_ptr(), doc.data_ptr())
+            return
         self.index.search_batch_shard(dQ.data_ptr(), nq, users, opts, key.data_ptr(), tid.data_ptr(), doc.data_ptr())
 
     def _cuda_merge(self, recv: torch.Tensor, nq: int, k: int, out) -> None:
