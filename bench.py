@@ -669,6 +669,13 @@ def main():
                                "list scan reads only the rows the user may see (one extent per visible document class and probed list); "
                                "a read-only stream can exceed the copy-measured peak, and queries probing the same lists share rows in L2 "
                                "(traffic = dram bytes of the launch)"})
+            if world > 1:
+                rf["probe"]["ms"] = None
+                rf["probe"]["fp32_TFLOPs"] = None
+                rf["probe"]["note"] = ("N > 1: the list choice is split by query across the ranks (nq / N queries each) and "
+                                       "all-gathered; its time is part of stages_ms.local_search")
+                line["config"]["ivf_sharding"] = ("centres trained on rank 0's stripe and broadcast; every list's rows striped with "
+                                                  "their documents (d mod N); list choice split by query + all-gather")
             line["config"].update({"recall_at_100": rec, "nprobe": args.nprobe, "lists": ivf_lists, "ivf_build_s": ivf_build_s,
                                    "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
         if ivf_lists and not args.no_cpu and world == 1:
