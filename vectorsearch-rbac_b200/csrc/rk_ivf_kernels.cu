@@ -557,20 +557,31 @@ size_t rk_ivf_probe_smem(int lists, int dim_pad)
 
 size_t rk_ivf_probe_keys_bytes(int nq, int lists) { return (size_t) nq * lists * 4; }
 
+// cudaFuncSetAttribute is per device: remember per (kernel, device) that the shared-memory limit was raised
+static cudaError_t pk_raise_smem(const void *kern, bool (&done)[64], int bytes)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (done[dev & 63]) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done[dev & 63] = true;
+    return e;
+}
+
 template <int METRIC, int NJ, int QW, int TC>
 static cudaError_t launch_keys(const float *Q, int nq, const float *C, int lists, int dim_pad, int null_query, uint32_t *keys, cudaStream_t stream)
 {
     auto kern = rk_ivf_keys_kernel<METRIC, NJ, QW, TC>;
     const size_t smem = (size_t) 2 * TC * NJ * 32 * 16;
-    static bool attr_set = false;
-    if (smem + 1024 > 48 * 1024 && !attr_set) {                            // (+ the kernel's static shared memory)
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    static bool attr_set[64];
+    if (smem + 1024 > 48 * 1024) {                                         // (+ the kernel's static shared memory)
+        cudaError_t e = pk_raise_smem(reinterpret_cast<const void *>(kern), attr_set, (int) smem);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     const int qblocks = (nq + PK_WARPS * QW - 1) / (PK_WARPS * QW);
     // centre ranges: about three full waves of resident blocks (the last wave as full as the others), at least four tiles each
-    static int resident = 0;
+    static int resident = 0;                                               // (one GPU model per process)
     if (resident == 0) {
         int per_sm = 0, dev = 0, sms = 148;
         cudaGetDevice(&dev);
@@ -615,22 +626,20 @@ cudaError_t rk_launch_ivf_probe(const float *Q, int nq, const float *C, int list
         int N2 = 32;
         while (N2 < need) N2 <<= 1;
         const size_t smem = (size_t) N2 * 8 + (size_t) lists * 4;
-        static bool attr_set = false;
-        if (smem > 48 * 1024 && !attr_set) {
-            e = cudaFuncSetAttribute(rk_ivf_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        static bool attr_set[64];
+        if (smem + 2048 > 48 * 1024) {
+            e = pk_raise_smem(reinterpret_cast<const void *>(rk_ivf_order_kernel), attr_set, 128 * 1024);
             if (e != cudaSuccess) return e;
-            attr_set = true;
         }
         rk_ivf_order_kernel<<<nq, PO_THREADS, smem, stream>>>(keys_ws, lists, probe_offset, probes, out_list);
         return cudaGetLastError();
     }
     const size_t smem = rk_ivf_probe_smem(lists, dim_pad);
     auto kern = metric == 0 ? rk_ivf_probe_kernel<0, 1> : rk_ivf_probe_kernel<1, 1>;
-    static bool attr_set[2];
-    if (smem > 48 * 1024 && !attr_set[metric & 1]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    static bool attr_set[2][64];
+    if (smem > 48 * 1024) {
+        cudaError_t e = pk_raise_smem(reinterpret_cast<const void *>(kern), attr_set[metric & 1], 227 * 1024);
         if (e != cudaSuccess) return e;
-        attr_set[metric & 1] = true;
     }
     kern<<<nq, PR_THREADS, smem, stream>>>(Q, nq, C, lists, dim_pad, null_query, probe_offset, probes, out_list);
     return cudaGetLastError();
