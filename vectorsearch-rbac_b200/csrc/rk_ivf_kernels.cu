@@ -432,6 +432,7 @@ __global__ void __launch_bounds__(PK_THREADS) rk_ivf_keys_kernel(const float *__
                 keys[(size_t) (qbase + b) * lists + c0 + c] = rk_float_to_key(METRIC == 0 ? v[0] : -v[0]);
         }
         __syncthreads();                                                    // the buffer is refilled by the next iteration's copy
+                                                                            // (per-warp `empty` mbarriers instead: measured no faster)
     }
 }
 

@@ -420,11 +420,14 @@ static int host_search(rk_index *ix, Workspace &ws, size_t nq, const float *Q, c
                        int32_t *out_count)
 {
     RK_CUDA(cudaSetDevice(ix->device));
-    if (!o->null_query) {
-        if (!rk_all_finite(Q, nq * (size_t) ix->dim)) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
-    }
+    // the upload is started first and the host validates the same bytes while the copy engine moves them (nothing has
+    // been launched on them yet when a bad element makes the call fail)
     int rc = stage_queries(ix, ws, nq, Q);
     if (rc < 0) return rc;
+    if (!o->null_query && !rk_all_finite(Q, nq * (size_t) ix->dim)) {
+        cudaStreamSynchronize(ws.stream);
+        return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
+    }
     const size_t nk = nq * (size_t) o->k;
     if (ws.out_tid.ensure(std::max<size_t>(nk * 8, 16)) != 0 || ws.out_doc.ensure(std::max<size_t>(nk * 4, 16)) != 0 ||
         ws.out_dist.ensure(std::max<size_t>(nk * 8, 16)) != 0 || ws.out_count.ensure(std::max<size_t>(nq * 4, 16)) != 0)
