@@ -192,6 +192,18 @@ def test_ivf_probe_batched_path_matches_single_query_path(metric, dim, monkeypat
                 n = len(t)
                 assert got_b[3][qi] == n
                 np.testing.assert_array_equal(got_b[0][qi, :n], t)
+    # NULL query in a batch: every centre is at distance 0, so the choice is lists 0 .. probes-1 on both paths
+    # (ivfscan.c:196-200, 181-185) and every tuple of those lists ties at 0: ascending tuple id
+    monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
+    got_b = ix.search_batch(Q[:9], users[:9], k, probes=3, filter=vr.FILTER_NONE, null_query=True)
+    monkeypatch.setenv("RK_IVF_PROBE_SINGLE", "1")
+    got_s = ix.search_batch(Q[:9], users[:9], k, probes=3, filter=vr.FILTER_NONE, null_query=True)
+    for a, b in zip(got_b, got_s):
+        np.testing.assert_array_equal(a, b)
+    (t, r, d), = orc.ivf_scan(ds["X"], ds["tid"], centers, off, rows, None, metric, probes=3)
+    n = min(k, len(t))
+    assert got_b[3][0] == n
+    np.testing.assert_array_equal(got_b[0][0, :n], t[:n])
     monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
     ix.close()
 
