@@ -615,17 +615,22 @@ def main():
             # algorithmic bytes per SURVEY.md §8(d): per query lists x 4d (centres) + VISIBLE rows of the probed lists x 4d
             # + mask bytes (row -> document -> role mask, 20 B per probed row) + 12k.  The engine's own figure counts every
             # row of the probed lists, so the visible rows are recounted here from the index's list assignment.
-            from oracle import oracle as orc_
-            m_ = orc_.METRIC_L2 if wl["metric"] == "l2" else orc_.METRIC_IP
-            centers_, row_list_ = ix.ivf_info(len(mine))     # N > 1: this rank's stripe of every list (rank 0's GPU is reported)
-            off_, lrows_ = orc_.ivf_lists_csr(row_list_, ivf_lists)
+            # (bookkeeping in numpy on the engine's own list assignment and list choice; the oracle is only the CPU leg's)
+            _, row_list_ = ix.ivf_info(len(mine))            # N > 1: this rank's stripe of every list (rank 0's GPU is reported)
+            lrows_ = np.argsort(row_list_, kind="stable")
+            off_ = np.searchsorted(row_list_[lrows_], np.arange(ivf_lists + 1))
+            P_ = min(args.nprobe, ivf_lists)
+            pl_ = torch.empty((args.nq, P_), dtype=torch.int32, device=dev)
+            ix.ivf_probe_device(Q.data_ptr(), args.nq, vr.engine.make_opts(args.k, probes=args.nprobe, filter=flt), pl_.data_ptr())
+            ix.synchronize()
+            pl_ = pl_.cpu().numpy()
             doc_np = np.asarray(doc)[mine]
             roles_of_, docs_of_ = {}, {}
             for u_, r_ in ur:
                 roles_of_.setdefault(int(u_), set()).add(int(r_))
             for d_, r_ in dr:
                 docs_of_.setdefault(int(r_), []).append(int(d_))
-            vis_cache, Qn_ = {}, Q.cpu().numpy()
+            vis_cache = {}
             probed_rows = visible_rows = 0
             for i in range(args.nq):
                 u_ = int(qusers[i])
@@ -634,7 +639,7 @@ def main():
                     for r_ in roles_of_.get(u_, ()):
                         v_[np.asarray(docs_of_.get(r_, []), dtype=np.int64)] = True
                     vis_cache[u_] = v_
-                for l_ in orc_.ivf_order_lists(centers_, Qn_[i], m_, args.nprobe)[0]:
+                for l_ in pl_[i]:
                     rr = lrows_[int(off_[l_]):int(off_[l_ + 1])]
                     probed_rows += len(rr)
                     visible_rows += int(vis_cache[u_][doc_np[rr]].sum())
