@@ -13,7 +13,7 @@
 
 #define RK_SEL_THREADS 512
 #define RK_SEL_CHUNK 1024
-#define RK_SEL_LISTS 1024       // non-empty list ids staged per round
+#define RK_SEL_LISTS 2048       // non-empty list ids staged per round
 
 __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelectParams p)
 {
@@ -203,20 +203,25 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
     };
 
     bool need_chunks = overflow;
-    if (overflow && !p.dedup && (size_t) nl * (size_t) k <= 32u * RK_SEL_THREADS) {
+    // With one staging round (nl <= RK_SEL_LISTS) s_lists still names the non-empty lists: a single query cut into many
+    // segments leaves most of them empty (CTAs carry their buffer across segments), and only the live ones count here.
+    const bool live_only = nl <= RK_SEL_LISTS;
+    const uint32_t nsrc = live_only ? s_nlists : nl;
+    if (overflow && !p.dedup && (size_t) nsrc * (size_t) k <= 32u * RK_SEL_THREADS) {
         // More than RK_CAND_CAP entries lie below the bound the full lists gave (many unsorted lists of similar
         // quality: the tensor engine's unit lists).  Instead of sorting them chunk by chunk, find the k-th smallest key
         // over ALL the lists exactly: every thread takes up to 32 entries into registers (all loads independent: a couple
         // of memory round trips), a 4-pass radix select runs over the registers, and only the entries up to the k-th key
         // are gathered and sorted.
-        const uint32_t flat = nl * (uint32_t) k;
+        const uint32_t flat = nsrc * (uint32_t) k;
         uint32_t kr[32];
 #pragma unroll
         for (int r = 0; r < 32; r++) {
             const uint32_t e = (uint32_t) t + (uint32_t) RK_SEL_THREADS * r;
             uint32_t kv = RK_KEY_SENTINEL;
             if (e < flat) {
-                const uint32_t j = e / (uint32_t) k, i = e - j * (uint32_t) k;
+                const uint32_t jj = e / (uint32_t) k, i = e - jj * (uint32_t) k;
+                const uint32_t j = live_only ? s_lists[jj] : jj;
                 if ((int) i < list_count(j)) {
                     kv = load_key(b4(j) + i);
                     if (kv == 0xFF800000u && load_tid(b8(j) + i, b4(j) + i) == 0xFFFFFFFFFFFFFFFFull) kv = RK_KEY_SENTINEL;   // padding
@@ -259,7 +264,8 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
         for (int r = 0; r < 32; r++) {
             if (kr[r] != RK_KEY_SENTINEL && kr[r] <= kth) {
                 const uint32_t e = (uint32_t) t + (uint32_t) RK_SEL_THREADS * r;
-                const uint32_t j = e / (uint32_t) k, i = e - j * (uint32_t) k;
+                const uint32_t jj = e / (uint32_t) k, i = e - jj * (uint32_t) k;
+                const uint32_t j = live_only ? s_lists[jj] : jj;
                 const uint32_t slot = atomicAdd(&s_count, 1u);
                 if (slot >= RK_CAND_CAP) s_overflow = 1;       // more than RK_CAND_CAP ties at the k-th key
                 else { s_key[slot] = kr[r]; s_tid[slot] = load_tid(b8(j) + i, b4(j) + i); s_row[slot] = p.cand_row[b4(j) + i]; }
