@@ -69,6 +69,7 @@ struct Workspace {
     bool timing = false;
     // stats of the last call
     uint64_t launches = 0, segments = 0, rows_scanned = 0, algo_bytes = 0;
+    bool plan_single_partition = false;   // last exact plan: no query walks more than one partition (no tuple can repeat)
     bool timed_scan = false, timed_select = false, timed_probe = false;
     int init(int device);
     void destroy();

@@ -134,6 +134,8 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
         if (rc < 0) return rc;
         for (auto &pi : per_q[q]) { total_rows += pi.rows_est; algo_rows += pi.rows_algo; }
     }
+    ws.plan_single_partition = true;
+    for (size_t q = 0; q < nq; q++) ws.plan_single_partition = ws.plan_single_partition && per_q[q].size() <= 1;
     // Segment sizing.  A segment costs a few microseconds of fixed work (pipeline refill, final
     // compaction + sort) and the dynamic schedule wastes about half a segment per CTA at the tail,
     // so with T = streaming time per CTA the best count per CTA is ~sqrt(T / 2o), o ~ 4 us.
@@ -375,7 +377,9 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
     out.list_stride = o->k;
     out.k = o->k;
     out.metric = ix->metric;
-    out.dedup = o->keep_duplicates ? 0 : 1;
+    // duplicates can only come from a user's several partitions (prefilter_role.py:174-189): a plan in which every query
+    // walks one partition needs no dedup pass, which lets the select cut to the k smallest keys before it sorts
+    out.dedup = (o->keep_duplicates || ws.plan_single_partition) ? 0 : 1;
     out.null_query = o->null_query;
     out.key_is_float = 0;
     out.rowdoc = ix->d_rowdoc.as<uint32_t>();
