@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define RK_ABI_VERSION 1
+#define RK_ABI_VERSION 2
 
 typedef struct rk_index rk_index;
 typedef struct rk_scan rk_scan;
@@ -107,6 +107,13 @@ rk_index *rk_open(const rk_config *cfg);
 void rk_close(rk_index *ix);
 const char *rk_last_error(void);
 int rk_abi_version(void);
+/* Tuning / test switches of one index (stand-ins for pgvector's GUCs, pgvector/src/ivfflat.c:33-54, for engine
+ * internals): "tensor_plan" (0 cheapest | 1 dense | 2 per user mask | 3 per document class), "tensor_pair" (-1 by row
+ * length | 0 one-CTA kernel | 1 CTA-pair kernel), "tensor_bf16" (-1 by row length | 0 TF32 | 1 bf16 nomination),
+ * "tensor_sample", "tensor_sdiv", "tensor_smin", "tensor_tpu", "tensor_host_timing", "ivf_seg_factor",
+ * "ivf_probe_single", "single_fused".  Defaults come from the RK_* environment variables of the same names
+ * (upper case), which are read once, in rk_open — never on the per-call path. */
+int rk_set_option(rk_index *ix, const char *name, int64_t value);
 
 /* ---- loading: what PostgreSQL's heap + catalog hold today ------------------------------------ */
 
@@ -160,7 +167,12 @@ int rk_ivf_info(const rk_index *ix, int *lists, float *centers, uint32_t *row_li
 
 typedef struct rk_scan_opts {
     int32_t k;              /* LIMIT pushed into the scan; 1..k_max                                 */
-    int32_t probes;         /* ivfflat.probes; 0 = exact scan (SeqScan + top-N sort)                */
+    int32_t probes;         /* ivfflat.probes; 0 = exact scan (SeqScan + top-N sort).  probes > 0 searches ONE
+                               global IVFFlat index over all rows with the permission test fused into the list scan
+                               (filter BITMASK semantics), whatever `layout` says: the reference's per-partition
+                               indexes (one ivfflat per role table, initialize_partitions.py:325-336) would choose
+                               lists per partition, so approximate results differ from its partitioned IVF arms
+                               while exact results (probes = lists) are identical                              */
     int32_t max_probes;     /* ivfflat.max_probes; > probes turns on iterative_scan=relaxed_order   */
     int32_t filter;         /* rk_filter */
     int32_t null_query;     /* ORDER BY vec <-> NULL: every distance is 0 (ivfscan.c:181-200)       */
@@ -178,7 +190,13 @@ rk_scan *rk_beginscan(rk_index *ix);
 int rk_rescan(rk_scan *sc, const float *q, int32_t q_dim, uint32_t user_id, const rk_scan_opts *o);
 /* ivfflatgettuple (ivfscan.c:339-389): next tuple in ascending distance.  1 = *tid / *distance
  * set (distance is what `vector <-> q` / `vector <#> q` evaluates to, float8); 0 = exhausted
- * (after the last probe batch in iterative mode, ivfscan.c:375-381); <0 = error. */
+ * (after the last probe batch in iterative mode, ivfscan.c:375-381); <0 = error.
+ *   Index scans (probes > 0) stream EVERY tuple of the probed lists the user may see, in order, like the reference's
+ * tuplesort (ivfscan.c:375-388): opts.k is only how many tuples one GPU pass brings back; when the ring is drained and
+ * the batch held more, the list scan is re-run with the lower bound (key, tid) > the last pair returned, and only when
+ * the batch is exhausted does the scan move to the next `probes` lists.
+ *   Exact scans (probes = 0) stand for `ORDER BY distance LIMIT k` (prefilter_role.py:162-172): opts.k IS the limit and
+ * the scan ends after k tuples. */
 int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *distance);
 /* ivfflatendscan (ivfscan.c:394-406). */
 void rk_endscan(rk_scan *sc);
@@ -194,7 +212,10 @@ int rk_search_batch(rk_index *ix, size_t nq, const float *Q, const uint32_t *use
                     int32_t *out_count);
 
 /* Same, with the query matrix and outputs already resident in HBM (device pointers); user_ids
- * stays a host array (it drives the host-side plan).  Asynchronous on the index stream. */
+ * stays a host array (it drives the host-side plan).  Asynchronous on the index stream.  The NaN / Inf check of the
+ * queries (vector.c:102-113) runs as a kernel and is reported by the next rk_synchronize (RK_ERR_NONFINITE).
+ * The rk_search_batch* / rk_merge_shards entry points of one index share a workspace and serialise on a mutex; for
+ * concurrent searches from several host threads use one rk_scan handle per thread. */
 int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
                            const rk_scan_opts *o, uint64_t *d_out_tid, uint32_t *d_out_doc,
                            double *d_out_dist, int32_t *d_out_count);
@@ -250,7 +271,9 @@ typedef struct rk_stats {
                                   3 = per document class (atoms); +16 when the sampling pass ran      */
     uint64_t tensor_flop;      /* last tensor batch: 2 * dim * (query, row) pairs scored (main pass) */
     uint64_t tensor_plan_bytes;/* last tensor batch: bytes the plan stages (visited tiles x query tiles) */
-    uint64_t reserved[2];
+    uint64_t segment_kinds;    /* last scan launch: bit i set = the work list held segments of kind i (0 extent table,
+                                  2 row range, 3 row range with a per-row permission test, 4 class-ordered IVF lists) */
+    uint64_t single_fused;     /* last call: 1 = a single query ran as ONE fused launch (scan + select)              */
 } rk_stats;
 int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */

@@ -176,6 +176,40 @@ def allowed_rows(row_doc: np.ndarray, rbac: Rbac, user: int) -> np.ndarray:
     return np.nonzero(np.isin(row_doc, docs))[0].astype(np.uint32)
 
 
+def dynamic_partition_plan(row_doc: np.ndarray, rbac: Rbac, partitions: Dict[int, Iterable[int]],
+                           roleset_parts: Dict[Tuple[int, ...], Sequence[int]], users: Sequence[int]):
+    """The per-query scans of dynamic_partition_search (controller/dynamic_partition/search.py:44-111):
+    user -> sorted role set (:44-52) -> partition ids from CombRolePartitions WHERE comb_role = roles (:54-60; a role set
+    without a row gets NO partition) -> one `ORDER BY distance LIMIT k` per partition table (:93-104), on which PostgreSQL
+    applies the RLS policy EXISTS(user_accessible_documents ...) unless the partition is pure
+    (load_result_to_database.py:591-622) — for a pure partition the predicate holds for every row, so applying it always
+    gives the same rows.  Returns (row lists, per-query list indices) for search_batch(dedup=True), whose merge is
+    merge_results (:347-364).  The layout need NOT cover a user's visible set: rows outside the user's partitions are
+    simply never scanned, exactly as in the reference."""
+    row_doc = np.asarray(row_doc)
+    part_rows = {int(p): np.nonzero(np.isin(row_doc, np.asarray(list(d), dtype=np.int64)))[0].astype(np.uint32)
+                 for p, d in partitions.items()}
+    plist: List[np.ndarray] = []
+    index_of: Dict[Tuple[Tuple[int, ...], int], int] = {}
+    qparts: List[List[int]] = []
+    allowed_cache: Dict[Tuple[int, ...], np.ndarray] = {}
+    for u in users:
+        roles = tuple(rbac.roles_of_user(int(u)))
+        mine: List[int] = []
+        for pid in (roleset_parts.get(roles, ()) if roles else ()):
+            key = (roles, int(pid))
+            if key not in index_of:
+                if roles not in allowed_cache:
+                    allowed_cache[roles] = allowed_rows(row_doc, rbac, int(u))
+                rows = np.intersect1d(part_rows[int(pid)], allowed_cache[roles]).astype(np.uint32)
+                index_of[key] = len(plist)
+                plist.append(rows)
+            if len(plist[index_of[key]]):
+                mine.append(index_of[key])
+        qparts.append(mine)
+    return plist, qparts
+
+
 # ----------------------------------------------------------------------------------------------
 # batched search
 

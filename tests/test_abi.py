@@ -23,7 +23,7 @@ def test_header_symbols_all_exported_and_bound():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/rbacknn.h but not exported by librbacknn.so"
     assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
-    assert lib.rk_abi_version() == 1
+    assert lib.rk_abi_version() == _lib.RK_ABI_VERSION == 2
 
 
 def test_struct_sizes_match_header():
@@ -46,7 +46,7 @@ def test_no_cpu_fallback_without_device():
 def test_argument_validation_needs_no_gpu():
     from vectorsearch_rbac_b200 import _lib
     cfg = _lib.RkConfig()
-    cfg.abi_version, cfg.dim, cfg.metric, cfg.device, cfg.k_max = 1, 0, 0, 0, 10
+    cfg.abi_version, cfg.dim, cfg.metric, cfg.device, cfg.k_max = _lib.RK_ABI_VERSION, 0, 0, 0, 10
     assert not _lib.lib.rk_open(C.byref(cfg))
     assert "dim 0" in _lib.last_error()
     cfg.dim, cfg.k_max = 128, 5000

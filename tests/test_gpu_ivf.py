@@ -180,9 +180,9 @@ def test_ivf_probe_batched_path_matches_single_query_path(metric, dim, monkeypat
     Q, users = _queries(ds, 37)
     k = 25
     for probes in (1, 3, 6, 40, lists):
-        monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
+        ix.set_option("ivf_probe_single", 0)
         got_b = ix.search_batch(Q, users, k, probes=probes, filter=vr.FILTER_BITMASK)
-        monkeypatch.setenv("RK_IVF_PROBE_SINGLE", "1")
+        ix.set_option("ivf_probe_single", 1)
         got_s = ix.search_batch(Q, users, k, probes=probes, filter=vr.FILTER_BITMASK)
         for a, b in zip(got_b, got_s):
             np.testing.assert_array_equal(a, b)
@@ -194,9 +194,9 @@ def test_ivf_probe_batched_path_matches_single_query_path(metric, dim, monkeypat
                 np.testing.assert_array_equal(got_b[0][qi, :n], t)
     # NULL query in a batch: every centre is at distance 0, so the choice is lists 0 .. probes-1 on both paths
     # (ivfscan.c:196-200, 181-185) and every tuple of those lists ties at 0: ascending tuple id
-    monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
+    ix.set_option("ivf_probe_single", 0)
     got_b = ix.search_batch(Q[:9], users[:9], k, probes=3, filter=vr.FILTER_NONE, null_query=True)
-    monkeypatch.setenv("RK_IVF_PROBE_SINGLE", "1")
+    ix.set_option("ivf_probe_single", 1)
     got_s = ix.search_batch(Q[:9], users[:9], k, probes=3, filter=vr.FILTER_NONE, null_query=True)
     for a, b in zip(got_b, got_s):
         np.testing.assert_array_equal(a, b)
@@ -204,7 +204,6 @@ def test_ivf_probe_batched_path_matches_single_query_path(metric, dim, monkeypat
     n = min(k, len(t))
     assert got_b[3][0] == n
     np.testing.assert_array_equal(got_b[0][0, :n], t[:n])
-    monkeypatch.delenv("RK_IVF_PROBE_SINGLE", raising=False)
     ix.close()
 
 

@@ -113,13 +113,13 @@ def test_tensor_engine_sampling_pass(kind, metric, flt, monkeypatch):
     Q, users = _queries(ds, 64, seed=9)
     k = 10
     f = vr.FILTER_NONE if flt == "none" else vr.FILTER_BITMASK
-    monkeypatch.setenv("RK_TENSOR_PLAN", "dense")
-    monkeypatch.setenv("RK_TENSOR_SAMPLE", "0")
+    ix.set_option("tensor_plan", 1)                   # dense
+    ix.set_option("tensor_sample", 0)
     base = ix.search_batch(Q, users, k, filter=f, engine=vr.ENGINE_TENSOR)
     units0 = ix.stats()["segments"]
-    monkeypatch.setenv("RK_TENSOR_SAMPLE", "1")
-    monkeypatch.setenv("RK_TENSOR_SDIV", "4")          # sample every 4th.. tile already on this small corpus
-    monkeypatch.setenv("RK_TENSOR_SMIN", "64")
+    ix.set_option("tensor_sample", 1)
+    ix.set_option("tensor_sdiv", 4)                   # sample every 4th.. tile already on this small corpus
+    ix.set_option("tensor_smin", 64)
     got = ix.search_batch(Q, users, k, filter=f, engine=vr.ENGINE_TENSOR)
     assert ix.stats()["tensor_plan"] & 31 == 1 + 16    # dense plan, sampling pass ran
     assert ix.stats()["segments"] > units0
@@ -157,9 +157,9 @@ def test_tensor_engine_long_units_many_compactions(monkeypatch):
     ix = load_index(ds, metric=1, role_parts=False, combo_parts=False, k_max=128)
     ix.finalize()
     Q, users = _queries(ds, 128, seed=21)
-    monkeypatch.setenv("RK_TENSOR_PLAN", "dense")
-    monkeypatch.setenv("RK_TENSOR_SAMPLE", "0")
-    monkeypatch.setenv("RK_TENSOR_TPU", "100000")        # one unit per query tile: the whole corpus in one pass
+    ix.set_option("tensor_plan", 1)
+    ix.set_option("tensor_sample", 0)
+    ix.set_option("tensor_tpu", 100000)                  # one unit per query tile: the whole corpus in one pass
     for flt in (vr.FILTER_NONE, vr.FILTER_BITMASK):
         got = ix.search_batch(Q, users, 100, filter=flt, engine=vr.ENGINE_TENSOR)
         ref = ix.search_batch(Q, users, 100, filter=flt, engine=vr.ENGINE_SCAN)

@@ -12,13 +12,13 @@ RTOL = 1e-5   # BASELINE.json north_star: "ties within a stated fp32 distance to
 
 
 def make_dataset(kind="sift", n=6000, dim=128, rows_per_doc=20, num_users=40, num_roles=12, rbac="tree", seed=3,
-                 m_roles=3):
+                 m_roles=3, tree=(3, 2, 3)):
     import vectorsearch_rbac_b200.synth as synth
     X = synth.corpus(kind, torch.arange(n), dim, seed=seed).numpy()
     tid, doc = synth.row_ids(n, rows_per_doc)
     doc_ids = np.unique(doc)
     if rbac == "tree":
-        ur, dr = synth.tree_rbac(num_users, num_roles, doc_ids.tolist(), h=3, b0=2, b1=3, seed=seed)
+        ur, dr = synth.tree_rbac(num_users, num_roles, doc_ids.tolist(), h=tree[0], b0=tree[1], b1=tree[2], seed=seed)
     else:
         ur, dr = synth.random_rbac(num_users, num_roles, doc_ids.tolist(), m_roles=m_roles,
                                    m_perms=max(2, 3 * len(doc_ids) // num_roles), seed=seed)

@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librbacknn.so")
 
-RK_ABI_VERSION = 1
+RK_ABI_VERSION = 2
 
 
 class RkConfig(C.Structure):
@@ -30,7 +30,8 @@ class RkStats(C.Structure):
                 ("launches", C.c_uint64), ("segments", C.c_uint64), ("rows_scanned", C.c_uint64),
                 ("algo_bytes", C.c_uint64), ("scan_ms", C.c_float), ("select_ms", C.c_float), ("probe_ms", C.c_float),
                 ("reserved_f", C.c_float), ("total_launches", C.c_uint64), ("tensor_redo", C.c_uint64),
-                ("tensor_exact", C.c_uint64), ("tensor_plan", C.c_uint64), ("tensor_flop", C.c_uint64), ("tensor_plan_bytes", C.c_uint64), ("reserved", C.c_uint64 * 2)]
+                ("tensor_exact", C.c_uint64), ("tensor_plan", C.c_uint64), ("tensor_flop", C.c_uint64), ("tensor_plan_bytes", C.c_uint64),
+                ("segment_kinds", C.c_uint64), ("single_fused", C.c_uint64)]
 
 
 # every symbol include/rbacknn.h declares: name -> (restype, argtypes)
@@ -40,6 +41,7 @@ SIGNATURES = {
     "rk_close": (None, [_P]),
     "rk_last_error": (C.c_char_p, []),
     "rk_abi_version": (C.c_int, []),
+    "rk_set_option": (C.c_int, [_P, C.c_char_p, C.c_int64]),
     "rk_load_rows": (C.c_int, [_P, _P, _P, _P, C.c_size_t]),
     "rk_load_rows_device": (C.c_int, [_P, _P, _P, _P, C.c_size_t]),
     "rk_reserve_rows": (C.c_int, [_P, C.c_size_t]),

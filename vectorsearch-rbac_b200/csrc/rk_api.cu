@@ -94,11 +94,17 @@ int Workspace::init(int device_)
     for (auto &e : ring_a) RK_CUDA(cudaEventCreate(&e));
     for (auto &e : ring_b) RK_CUDA(cudaEventCreate(&e));
     for (auto &e : ev_plan) RK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    if (qflag.ensure(16) != 0) return RK_ERR_CUDA;
+    RK_CUDA(cudaMemset(qflag.p, 0, 16));
+    RK_CUDA(cudaHostAlloc((void **) &h_qflag, 16, cudaHostAllocDefault));
+    *h_qflag = 0;
     return 0;
 }
 void Workspace::destroy()
 {
-    DevBuf *bufs[] = {&segs, &order, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
+    if (h_qflag) cudaFreeHost(h_qflag);
+    h_qflag = nullptr;
+    DevBuf *bufs[] = {&qflag, &segs, &order, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
                       &out_doc, &out_dist, &out_count, &probe_key, &probe_list, &ex_key, &ex_tid, &ex_doc};
     for (auto *b : bufs) b->release();
     h_plan_ring[0].release();
@@ -147,8 +153,46 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
     ix->k_max = cfg->k_max;
     ix->sm_count = prop.multiProcessorCount;
     rk_scan_geometry(ix->dim_pad, &ix->tile_rows, &ix->nstages, &ix->scan_smem);
+    // tuning / test switches: the environment is read here, once, never on the per-call path
+    {
+        RkTuning &t = ix->tune;
+        auto env_int = [](const char *name, int dflt) { const char *e = getenv(name); return e && *e ? atoi(e) : dflt; };
+        t.tensor_tpu = std::max(0, env_int("RK_TENSOR_TPU", 0));
+        t.tensor_pair = env_int("RK_TENSOR_PAIR", -1);
+        if (const char *e = getenv("RK_TENSOR_PLAN"))
+            t.tensor_plan = !strcmp(e, "dense") ? 1 : !strcmp(e, "grouped") ? 2 : !strcmp(e, "atoms") ? 3 : 0;
+        t.tensor_sample = env_int("RK_TENSOR_SAMPLE", 1);
+        t.tensor_sdiv = std::max(0, env_int("RK_TENSOR_SDIV", 0));
+        t.tensor_smin = std::max(1, env_int("RK_TENSOR_SMIN", 1024));
+        t.tensor_host_timing = getenv("RK_TENSOR_HOST_TIMING") != nullptr;
+        t.tensor_bf16 = env_int("RK_TENSOR_BF16", -1);
+        t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
+        t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
+        t.single_fused = env_int("RK_SINGLE_FUSED", 1);
+    }
     if (ix->ws.init(cfg->device) != 0) { delete ix; return nullptr; }
     return ix;
+}
+
+extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
+{
+    if (!ix || !name) return rk_fail(RK_ERR_INVALID, "rk_set_option: NULL argument");
+    RkTuning &t = ix->tune;
+    const int v = (int) value;
+    std::lock_guard<std::mutex> g(ix->batch_mu);
+    if (!strcmp(name, "tensor_tpu")) t.tensor_tpu = std::max(0, v);
+    else if (!strcmp(name, "tensor_pair")) t.tensor_pair = v;
+    else if (!strcmp(name, "tensor_plan")) t.tensor_plan = (v >= 0 && v <= 3) ? v : 0;
+    else if (!strcmp(name, "tensor_sample")) t.tensor_sample = v;
+    else if (!strcmp(name, "tensor_sdiv")) t.tensor_sdiv = std::max(0, v);
+    else if (!strcmp(name, "tensor_smin")) t.tensor_smin = std::max(1, v);
+    else if (!strcmp(name, "tensor_host_timing")) t.tensor_host_timing = v != 0;
+    else if (!strcmp(name, "tensor_bf16")) t.tensor_bf16 = v;
+    else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
+    else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
+    else if (!strcmp(name, "single_fused")) t.single_fused = v;
+    else return rk_fail(RK_ERR_INVALID, "rk_set_option: unknown option \"%s\"", name);
+    return RK_OK;
 }
 
 extern "C" void rk_close(rk_index *ix)

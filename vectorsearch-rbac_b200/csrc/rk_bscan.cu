@@ -470,6 +470,9 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
         // The answer is proven iff that exceeds the exact k-th value (strictly, so that no tie on the
         // k-th value with a smaller tuple id can hide outside).
         int uncertain = p.trunc ? p.trunc[q] : 0;
+        // fp32 overflow (vector_type.out:387-391, 413-417: distances come out as Infinity): the tensor-core value may have
+        // been inf - inf = NaN, which no threshold test admits — such rows were never nominated.  Leave it to the scan.
+        if (!(p.xnorm_max < 3.0e38f) || !(p.qnorm[q] < 3.0e38f)) uncertain = 1;
         if (n >= p.kp && cnt > 0) {
             // the nominated ordering value leaves the query's own norm out (L2): add it back
             const float a_last = p.sel_key[(size_t) q * p.kp + (n - 1)] + (METRIC == 0 ? p.qnorm[q] : 0.f);

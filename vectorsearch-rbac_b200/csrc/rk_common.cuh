@@ -70,6 +70,11 @@ struct RkScanParams {
     int nstages;
     int k;
     int metric;      // 0 = L2, 1 = IP
+    // streaming scans (rk_gettuple past the k-th tuple, ivfscan.c:375-388): keep only tuples whose (key, tid) is
+    // strictly greater than the last pair already handed back
+    int lb_on;
+    uint32_t lb_key;
+    uint64_t lb_tid;
 };
 
 struct RkSelectParams {

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <atomic>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -57,6 +58,9 @@ struct Workspace {
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     DevBuf segs, order, ctl /* [0]=nseg [1]=counter */, cand_key, cand_tid, cand_row, cand_count, qseg, qmask, dq;
     DevBuf out_tid, out_doc, out_dist, out_count;
+    DevBuf qflag;                        // [1] u32: set by the device-side NaN / Inf check of device-resident queries
+    bool qflag_armed = false;            // a check was launched since the flag was last read
+    uint32_t *h_qflag = nullptr;         // pinned
     DevBuf probe_key, probe_list;        // IVF: per-query selected lists
     const uint32_t *ext_probe = nullptr; // IVF: list choice supplied by the caller (rk_search_batch_shard_probed), [nq][probes]
     DevBuf ex_key, ex_tid, ex_doc;       // exchange-form results
@@ -67,8 +71,14 @@ struct Workspace {
     bool ev_plan_used[2] = {false, false};
     int plan_idx = 0;
     bool timing = false;
+    // lower bound of a streaming scan (rk_gettuple past the k-th tuple): only tuples with (key, tid) > (lb_key, lb_tid) are kept
+    bool lb_on = false;
+    uint32_t lb_key = 0;
+    uint64_t lb_tid = 0;
     // stats of the last call
     uint64_t launches = 0, segments = 0, rows_scanned = 0, algo_bytes = 0;
+    uint32_t seg_kinds = 0;               // bit per RK_SEG_* kind in the last scan launch's work list
+    bool single_fused = false;            // the last call ran as one fused launch
     bool plan_single_partition = false;   // last exact plan: no query walks more than one partition (no tuple can repeat)
     bool timed_scan = false, timed_select = false, timed_probe = false;
     int init(int device);
@@ -105,7 +115,7 @@ struct IvfIndex {
     int ncls = 0;                                   // 0 = lists keep row order, masks are tested per row
     DevBuf d_cls_off;                               // [lists * (ncls + 1) + 1]
     std::vector<std::vector<uint64_t>> cls_mask;    // role mask of each class
-    std::vector<uint64_t> qcls_by_mask_id;          // [n_mask_ids][2] visible classes per user mask id (filled lazily; ~0 = unset)
+    std::vector<uint64_t> qcls_by_mask_id;          // [n_mask_ids][2] visible classes per user mask id (filled by the build)
 };
 
 // State of the batched tensor-core engine (rk_tensor.cu / rk_bscan.cu); used by the index's own
@@ -131,8 +141,26 @@ struct TensorState {
     bool last_exact = false;
 };
 
+// Tuning / test switches.  Defaults come from the RK_* environment variables, read ONCE in rk_open (never on the per-call
+// path); rk_set_option changes them per index afterwards.
+struct RkTuning {
+    int tensor_tpu = 0;          // RK_TENSOR_TPU: tiles per unit (0 = planner's choice)
+    int tensor_pair = -1;        // RK_TENSOR_PAIR: -1 = by row length, 0 = one-CTA kernel, 1 = CTA-pair kernel
+    int tensor_plan = 0;         // RK_TENSOR_PLAN: 0 = cheapest, 1 = dense, 2 = grouped, 3 = atoms
+    int tensor_sample = 1;       // RK_TENSOR_SAMPLE: 0 disables the sampling pass
+    int tensor_sdiv = 0;         // RK_TENSOR_SDIV: 0 = default (400)
+    int tensor_smin = 1024;      // RK_TENSOR_SMIN
+    int tensor_host_timing = 0;  // RK_TENSOR_HOST_TIMING
+    int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = by row length, 0 = TF32 nomination, 1 = bf16 nomination
+    int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
+    int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
+    int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path
+};
+
 struct rk_index {
     rk_config cfg{};
+    RkTuning tune;
+    std::mutex batch_mu;         // rk_search_batch* / rk_merge_shards share ix->ws: one caller at a time
     int dim = 0, dim_pad = 0, metric = 0, device = 0, k_max = 0, sm_count = 148;
     int tile_rows = 0, nstages = 0;
     size_t scan_smem = 0;
@@ -168,7 +196,7 @@ struct rk_index {
     IvfIndex ivf;
     TensorState tensor;
     Workspace ws;
-    uint64_t total_launches = 0;
+    std::atomic<uint64_t> total_launches{0};
     float last_scan_ms = 0, last_select_ms = 0, last_probe_ms = 0;
 };
 
@@ -183,7 +211,10 @@ struct rk_scan {
     std::vector<uint64_t> r_tid;
     std::vector<uint32_t> r_doc;
     std::vector<double> r_dist;
+    std::vector<float> r_key;   // fp32 ordering values of the ring (the resume bound of a streaming scan)
     int r_count = 0, r_pos = 0;
+    bool batch_more = false;    // the last fetch returned k tuples: the batch may hold more
+    int batch_offset = 0, batch_probes = 0;   // probe offset / count of the batch being streamed
     int probes_done = 0;        // lists consumed so far (iterative scan)
     int max_probes_eff = 0, probes_eff = 0;
 };

@@ -92,7 +92,23 @@ static int build_from_device_centers(rk_index *ix, int lists, const float *d_cen
     if (iv.ncls) {
         if (iv.d_cls_off.ensure(bucket_start.size() * 4) != 0) return RK_ERR_CUDA;
         RK_CUDA(cudaMemcpy(iv.d_cls_off.p, bucket_start.data(), bucket_start.size() * 4, cudaMemcpyHostToDevice));
-        iv.qcls_by_mask_id.assign((size_t) ix->n_mask_ids * 2, ~0ull);
+        // the 128-bit set of classes each distinct user role mask may see, computed HERE — one thread, n_mask_ids known —
+        // so concurrent scans (any number of rk_scan handles, include/rbacknn.h:17-19) only ever read the table
+        iv.qcls_by_mask_id.assign((size_t) ix->n_mask_ids * 2, 0ull);
+        std::vector<char> done(ix->n_mask_ids, 0);
+        for (auto &kv : ix->users) {
+            const UserInfo &u = kv.second;
+            if (done[u.mask_id]) continue;
+            done[u.mask_id] = 1;
+            uint64_t a0 = 0, a1 = 0;
+            for (int c = 0; c < iv.ncls; c++) {
+                uint64_t acc = 0;
+                for (int w = 0; w < W; w++) acc |= iv.cls_mask[(size_t) c][(size_t) w] & u.mask[(size_t) w];
+                if (acc) { if (c < 64) a0 |= 1ull << c; else a1 |= 1ull << (c - 64); }
+            }
+            iv.qcls_by_mask_id[(size_t) u.mask_id * 2] = a0;
+            iv.qcls_by_mask_id[(size_t) u.mask_id * 2 + 1] = a1;
+        }
     }
     DevBuf d_perm;
     if (d_perm.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
@@ -241,7 +257,8 @@ int rk_ivf_probe_only(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, c
     for (size_t q0 = 0; q0 < nq; q0 += qb) {
         const size_t n = std::min(qb, nq - q0);
         RK_CUDA(rk_launch_ivf_probe(dQ + q0 * (size_t) ix->dim_pad, (int) n, iv.d_centers.as<float>(), iv.lists, ix->dim_pad, ix->metric,
-                                    o->null_query, 0, probes, d_lists + q0 * (size_t) probes, ws.probe_key.as<uint32_t>(), ws.stream));
+                                    o->null_query, 0, probes, d_lists + q0 * (size_t) probes,
+                                    ix->tune.ivf_probe_single ? nullptr : ws.probe_key.as<uint32_t>(), ws.stream));
         ix->total_launches += 2;
     }
     return RK_OK;
@@ -253,12 +270,6 @@ int rk_ivf_probe_only(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, c
 void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &p, bool ivf_store, const float *dQ,
                          const rk_scan_opts *o, int k);
 int rk_ensure_cand(Workspace &ws, size_t nlists, int k);
-
-static int ivf_seg_factor()
-{
-    static int f = [] { const char *e = getenv("RK_IVF_SEG_FACTOR"); int v = e ? atoi(e) : 4; return v < 1 ? 1 : v; }();
-    return f;
-}
 
 int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_all, const uint32_t *user_ids,
                   const rk_scan_opts *o, int probe_offset, const RkSelectParams &out_all)
@@ -285,7 +296,7 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
     int cls_group = 1, cls_spq = 0;
     if (cls_mode) {
         // enough segments to fill the SMs four times over, at most one per probed list
-        int spq = (int) std::min<size_t>((size_t) probes, std::max<size_t>(1, ((size_t) ix->sm_count * ivf_seg_factor() + nq_all - 1) / std::max<size_t>(nq_all, 1)));
+        int spq = (int) std::min<size_t>((size_t) probes, std::max<size_t>(1, ((size_t) ix->sm_count * ix->tune.ivf_seg_factor + nq_all - 1) / std::max<size_t>(nq_all, 1)));
         cls_group = (probes + spq - 1) / spq;
         cls_spq = (probes + cls_group - 1) / cls_group;
     }
@@ -294,6 +305,7 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
     if (qb > nq_all) qb = nq_all;
 
     ws.segments = 0;
+    ws.seg_kinds = probes > 0 ? 1u << (cls_mode ? RK_SEG_IVFQ : kind) : 0u;
     ws.rows_scanned = (uint64_t) total_est;
     ws.algo_bytes = (uint64_t) nq_all * ((uint64_t) lists * row_bytes + 12ull * k) + (uint64_t) (total_est * row_bytes);
     for (size_t q0 = 0; q0 < nq_all; q0 += qb) {
@@ -333,27 +345,14 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
                     sg.begin = (uint64_t) s_ * cls_group;
                     sg.end = (uint64_t) std::min(probes, (s_ + 1) * cls_group);
                 }
-                // classes this user may see (cached per distinct role mask)
+                // classes this user may see (precomputed per distinct role mask by the build)
                 uint64_t c0 = 0, c1 = 0;
                 const UserInfo *u = nullptr;
                 if (user_ids) {
                     auto it = ix->users.find(user_ids[q0 + q]);
                     if (it != ix->users.end()) u = &it->second;
                 }
-                if (u) {
-                    uint64_t *cache = &iv.qcls_by_mask_id[(size_t) u->mask_id * 2];
-                    if (cache[0] == ~0ull && cache[1] == ~0ull) {
-                        uint64_t a0 = 0, a1 = 0;
-                        for (int c = 0; c < iv.ncls; c++) {
-                            uint64_t acc = 0;
-                            for (int w = 0; w < W; w++) acc |= iv.cls_mask[(size_t) c][(size_t) w] & u->mask[(size_t) w];
-                            if (acc) { if (c < 64) a0 |= 1ull << c; else a1 |= 1ull << (c - 64); }
-                        }
-                        // (all 128 bits set cannot be confused with "unset": it is stored as computed and recomputed each time)
-                        cache[0] = a0; cache[1] = a1;
-                    }
-                    c0 = cache[0]; c1 = cache[1];
-                }
+                if (u) { c0 = iv.qcls_by_mask_id[(size_t) u->mask_id * 2]; c1 = iv.qcls_by_mask_id[(size_t) u->mask_id * 2 + 1]; }
                 hcl[q * 2] = c0; hcl[q * 2 + 1] = c1;
             }
         }
@@ -379,7 +378,8 @@ int rk_ivf_search(rk_index *ix, Workspace &ws, size_t nq_all, const float *dQ_al
             const uint32_t *plist = ws.ext_probe ? ws.ext_probe + q0 * (size_t) probes : ws.probe_list.as<uint32_t>();
             if (!ws.ext_probe)
                 RK_CUDA(rk_launch_ivf_probe(dQ, (int) nq, iv.d_centers.as<float>(), lists, ix->dim_pad, ix->metric, o->null_query,
-                                            probe_offset, probes, ws.probe_list.as<uint32_t>(), ws.probe_key.as<uint32_t>(), ws.stream));
+                                            probe_offset, probes, ws.probe_list.as<uint32_t>(),
+                                            ix->tune.ivf_probe_single ? nullptr : ws.probe_key.as<uint32_t>(), ws.stream));
             if (!cls_mode)
                 RK_CUDA(rk_launch_ivf_plan(plist, iv.d_list_start.as<uint32_t>(), (int) nq, probes, chunks,
                                            chunk_rows, kind, ws.segs.as<RkSegment>(), ws.stream));

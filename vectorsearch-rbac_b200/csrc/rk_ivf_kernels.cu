@@ -618,8 +618,7 @@ cudaError_t rk_launch_ivf_probe(const float *Q, int nq, const float *C, int list
 {
     if (nq <= 0 || probes <= 0) return cudaSuccess;
     const int need = probe_offset + probes;
-    const bool batched = keys_ws != nullptr && nq >= 4 && need <= PO_MAX_NEED && need <= lists && (dim_pad >> 2) <= 512 &&
-                         getenv("RK_IVF_PROBE_SINGLE") == nullptr;
+    const bool batched = keys_ws != nullptr && nq >= 4 && need <= PO_MAX_NEED && need <= lists && (dim_pad >> 2) <= 512;
     if (batched) {
         cudaError_t e = metric == 0 ? launch_keys_m<0>(Q, nq, C, lists, dim_pad, null_query, keys_ws, stream)
                                     : launch_keys_m<1>(Q, nq, C, lists, dim_pad, null_query, keys_ws, stream);

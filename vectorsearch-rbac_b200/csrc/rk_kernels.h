@@ -18,6 +18,8 @@ cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, 
 // counts NaN / Inf elements of a device array (synchronous; result in *out)
 cudaError_t rk_count_nonfinite(const float *d_x, size_t n, unsigned long long *out, cudaStream_t stream);
 
+cudaError_t rk_launch_flag_nonfinite(const float *d_x, size_t n, uint32_t *d_flag, cudaStream_t stream);
+
 // IVFFlat (rk_ivf_kernels.cu)
 cudaError_t rk_launch_assign(const float *X, size_t nrows, const float *C, int lists, int dim_pad, int metric,
                              uint32_t *out_list, float *out_val, cudaStream_t stream);

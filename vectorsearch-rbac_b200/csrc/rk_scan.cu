@@ -580,8 +580,13 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
             const uint32_t tau = *s_tau;
             const uint32_t ka = rk_float_to_key(METRIC == 0 ? sa : -sa);
             const uint32_t kb = rk_float_to_key(METRIC == 0 ? sb : -sb);
-            const bool ca = lead && va && ka <= tau;
-            const bool cb2 = lead && vb && kb <= tau;
+            bool ca = lead && va && ka <= tau;
+            bool cb2 = lead && vb && kb <= tau;
+            if (p.lb_on) {
+                // a streaming scan resumes after (lb_key, lb_tid): everything up to that pair was already returned
+                if (ca && (ka < p.lb_key || (ka == p.lb_key && p.store.tid[rid[ra]] <= p.lb_tid))) ca = false;
+                if (cb2 && (kb < p.lb_key || (kb == p.lb_key && p.store.tid[rid[rb]] <= p.lb_tid))) cb2 = false;
+            }
             const unsigned ma = __ballot_sync(0xffffffffu, ca), mb = __ballot_sync(0xffffffffu, cb2);
             if (ma | mb) {
                 const int na = __popc(ma);

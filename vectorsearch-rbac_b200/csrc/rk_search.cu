@@ -247,6 +247,7 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
     ws.ev_plan_used[pi_] = true;
 
     ws.segments = nseg;
+    ws.seg_kinds = nseg ? 1u << RK_SEG_EXTENTS : 0u;
     ws.rows_scanned = total_rows;
     ws.algo_bytes = algo_rows * row_bytes + mask_bytes + (uint64_t) nq * 12ull * (uint64_t) o->k;
     *out_nseg = nseg;
@@ -299,6 +300,9 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
     p.nstages = ix->nstages;
     p.k = k;
     p.metric = ix->metric;
+    p.lb_on = ws.lb_on ? 1 : 0;
+    p.lb_key = ws.lb_key;
+    p.lb_tid = ws.lb_tid;
 }
 
 // One batch on device: dQ [nq][dim_pad].  `out` carries the destination pointers (device).
@@ -310,6 +314,8 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
 {
     RK_CUDA(cudaSetDevice(ix->device));
     ws.launches = 0;
+    ws.seg_kinds = 0;
+    ws.single_fused = false;
     ws.timed_scan = ws.timed_select = ws.timed_probe = false;
     if (&ws == &ix->ws) ix->tensor.last_plan = 0;
     if (nq == 0) return RK_OK;
@@ -421,7 +427,7 @@ static int stage_queries(rk_index *ix, Workspace &ws, size_t nq, const float *Q)
 
 static int host_search(rk_index *ix, Workspace &ws, size_t nq, const float *Q, const uint32_t *user_ids,
                        const rk_scan_opts *o, int probe_offset, uint64_t *out_tid, uint32_t *out_doc, double *out_dist,
-                       int32_t *out_count)
+                       int32_t *out_count, float *out_key = nullptr)
 {
     RK_CUDA(cudaSetDevice(ix->device));
     // the upload is started first and the host validates the same bytes while the copy engine moves them (nothing has
@@ -436,18 +442,21 @@ static int host_search(rk_index *ix, Workspace &ws, size_t nq, const float *Q, c
     if (ws.out_tid.ensure(std::max<size_t>(nk * 8, 16)) != 0 || ws.out_doc.ensure(std::max<size_t>(nk * 4, 16)) != 0 ||
         ws.out_dist.ensure(std::max<size_t>(nk * 8, 16)) != 0 || ws.out_count.ensure(std::max<size_t>(nq * 4, 16)) != 0)
         return RK_ERR_CUDA;
+    if (out_key && ws.ex_key.ensure(std::max<size_t>(nk * 4, 16)) != 0) return RK_ERR_CUDA;
     RkSelectParams out;
     memset(&out, 0, sizeof out);
     out.out_tid = ws.out_tid.as<uint64_t>();
     out.out_doc = out_doc ? ws.out_doc.as<uint32_t>() : nullptr;
     out.out_dist = ws.out_dist.as<double>();
     out.out_count = ws.out_count.as<int32_t>();
+    out.out_key = out_key ? ws.ex_key.as<float>() : nullptr;
     rc = search_device(ix, ws, nq, ws.dq.as<float>(), user_ids, o, probe_offset, out);
     if (rc < 0) return rc;
     RK_CUDA(cudaMemcpyAsync(out_tid, ws.out_tid.p, nk * 8, cudaMemcpyDeviceToHost, ws.stream));
     if (out_doc) RK_CUDA(cudaMemcpyAsync(out_doc, ws.out_doc.p, nk * 4, cudaMemcpyDeviceToHost, ws.stream));
     RK_CUDA(cudaMemcpyAsync(out_dist, ws.out_dist.p, nk * 8, cudaMemcpyDeviceToHost, ws.stream));
     RK_CUDA(cudaMemcpyAsync(out_count, ws.out_count.p, nq * 4, cudaMemcpyDeviceToHost, ws.stream));
+    if (out_key) RK_CUDA(cudaMemcpyAsync(out_key, ws.ex_key.p, nk * 4, cudaMemcpyDeviceToHost, ws.stream));
     RK_CUDA(cudaStreamSynchronize(ws.stream));
     return collect_timing(ix, ws);
 }
@@ -462,7 +471,20 @@ extern "C" int rk_search_batch(rk_index *ix, size_t nq, const float *Q, const ui
     if (nq == 0) return RK_OK;
     if (!Q || !out_tid || !out_dist || !out_count) return rk_fail(RK_ERR_INVALID, "rk_search_batch: NULL buffer");
     if (!user_ids && o->filter != RK_FILTER_NONE) return rk_fail(RK_ERR_INVALID, "rk_search_batch: user_ids is NULL");
+    std::lock_guard<std::mutex> g(ix->batch_mu);      // the batch entry points share ix->ws
     return host_search(ix, ix->ws, nq, Q, user_ids, o, 0, out_tid, out_doc, out_dist, out_count);
+}
+
+// Device-resident queries cannot be validated by the host without a sync: a small kernel raises a flag that the next
+// rk_synchronize reports (vector_in's NaN / Inf check, vector.c:102-113).
+static int check_device_queries(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const rk_scan_opts *o)
+{
+    if (o->null_query) return 0;
+    RK_CUDA(cudaSetDevice(ix->device));
+    RK_CUDA(rk_launch_flag_nonfinite(dQ, nq * (size_t) ix->dim_pad, ws.qflag.as<uint32_t>(), ws.stream));
+    ws.qflag_armed = true;
+    ix->total_launches += 1;
+    return 0;
 }
 
 extern "C" int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
@@ -479,13 +501,15 @@ extern "C" int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, 
     RkSelectParams out;
     memset(&out, 0, sizeof out);
     out.out_tid = d_out_tid; out.out_doc = d_out_doc; out.out_dist = d_out_dist; out.out_count = d_out_count;
+    std::lock_guard<std::mutex> g(ix->batch_mu);
+    rc = check_device_queries(ix, ix->ws, nq, dQ, o);
+    if (rc < 0) return rc;
     return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
 }
 
-extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
-                                     const rk_scan_opts *o, float *d_key, uint64_t *d_tid, uint32_t *d_doc)
+static int search_batch_shard_locked(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids, const rk_scan_opts *o,
+                                     float *d_key, uint64_t *d_tid, uint32_t *d_doc)
 {
-    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
     if (!ix->finalized) return rk_fail(RK_ERR_STATE, "rk_search_batch_shard: call rk_finalize first");
     int rc = validate_opts(ix, o);
     if (rc < 0) return rc;
@@ -495,7 +519,17 @@ extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, c
     RkSelectParams out;
     memset(&out, 0, sizeof out);
     out.out_key = d_key; out.out_tid = d_tid; out.out_doc = d_doc;
+    rc = check_device_queries(ix, ix->ws, nq, dQ, o);
+    if (rc < 0) return rc;
     return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
+}
+
+extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,
+                                     const rk_scan_opts *o, float *d_key, uint64_t *d_tid, uint32_t *d_doc)
+{
+    if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    std::lock_guard<std::mutex> g(ix->batch_mu);
+    return search_batch_shard_locked(ix, nq, dQ, user_ids, o, d_key, d_tid, d_doc);
 }
 
 int rk_ivf_probe_only(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const rk_scan_opts *o, uint32_t *d_lists);
@@ -509,6 +543,7 @@ extern "C" int rk_ivf_probe_device(rk_index *ix, size_t nq, const float *dQ, con
     if (nq == 0) return RK_OK;
     if (!dQ || !d_lists) return rk_fail(RK_ERR_INVALID, "rk_ivf_probe_device: NULL pointer");
     if (ix->dim != ix->dim_pad) return rk_fail(RK_ERR_UNSUPPORTED, "device queries need dim %% 4 == 0 (dim = %d)", ix->dim);
+    std::lock_guard<std::mutex> g(ix->batch_mu);
     return rk_ivf_probe_only(ix, ix->ws, nq, dQ, o, d_lists);
 }
 
@@ -519,8 +554,9 @@ extern "C" int rk_search_batch_shard_probed(rk_index *ix, size_t nq, const float
     if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
     if (!d_lists) return rk_fail(RK_ERR_INVALID, "rk_search_batch_shard_probed: NULL list choice");
     if (!o || o->probes < 1) return rk_fail(RK_ERR_INVALID, "rk_search_batch_shard_probed: probes must be >= 1");
+    std::lock_guard<std::mutex> g(ix->batch_mu);
     ix->ws.ext_probe = d_lists;
-    const int rc = rk_search_batch_shard(ix, nq, dQ, user_ids, o, d_key, d_tid, d_doc);
+    const int rc = search_batch_shard_locked(ix, nq, dQ, user_ids, o, d_key, d_tid, d_doc);
     ix->ws.ext_probe = nullptr;
     return rc;
 }
@@ -534,6 +570,7 @@ extern "C" int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, siz
     if (!d_key || !d_tid) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: NULL pointer");
     if (shard_stride_bytes % 8) return rk_fail(RK_ERR_INVALID, "rk_merge_shards: shard stride must be a multiple of 8 bytes");
     if (nq == 0) return RK_OK;
+    std::lock_guard<std::mutex> g(ix->batch_mu);
     RK_CUDA(cudaSetDevice(ix->device));
     RkSelectParams p;
     memset(&p, 0, sizeof p);
@@ -572,21 +609,38 @@ extern "C" rk_scan *rk_beginscan(rk_index *ix)
     return sc;
 }
 
-static int scan_fetch_batch(rk_scan *sc)
+// Fetches the next k tuples of the scan.  resume = false: the next batch of `probes` lists (or, for an exact scan, the
+// first k tuples); resume = true: the k tuples of the CURRENT batch that follow the last pair handed back — the scan is
+// re-run with a lower bound (key, tid) > last, so a batch of any size streams out k tuples at a time, in order, exactly
+// as ivfflatgettuple drains its tuplesort (ivfscan.c:375-388) before it moves on to the next `probes` lists.
+static int scan_fetch_batch(rk_scan *sc, bool resume)
 {
     rk_index *ix = sc->ix;
     const int k = sc->opts.k;
-    sc->r_tid.resize(k); sc->r_doc.resize(k); sc->r_dist.resize(k);
+    sc->r_tid.resize(k); sc->r_doc.resize(k); sc->r_dist.resize(k); sc->r_key.resize(k);
     int32_t cnt = 0;
     rk_scan_opts o = sc->opts;
-    o.probes = sc->probes_eff;
-    if (o.probes > 0) o.probes = std::min(o.probes, sc->max_probes_eff - sc->probes_done);   // ivfscan.c:128 listIndex < maxProbes
-    int rc = host_search(ix, sc->ws, 1, sc->q.data(), &sc->user, &o, sc->probes_done, sc->r_tid.data(), sc->r_doc.data(),
-                         sc->r_dist.data(), &cnt);
+    if (!resume) {
+        sc->batch_offset = sc->probes_done;
+        sc->batch_probes = sc->probes_eff;
+        if (sc->batch_probes > 0) sc->batch_probes = std::min(sc->batch_probes, sc->max_probes_eff - sc->probes_done);   // ivfscan.c:128 listIndex < maxProbes
+        sc->probes_done += sc->probes_eff;
+        sc->ws.lb_on = false;
+    } else {
+        sc->ws.lb_on = true;
+        sc->ws.lb_key = rk_float_to_key(sc->r_key[(size_t) sc->r_count - 1]);
+        sc->ws.lb_tid = sc->r_tid[(size_t) sc->r_count - 1];
+    }
+    o.probes = sc->batch_probes;
+    int rc = host_search(ix, sc->ws, 1, sc->q.data(), &sc->user, &o, sc->batch_offset, sc->r_tid.data(), sc->r_doc.data(),
+                         sc->r_dist.data(), &cnt, sc->r_key.data());
+    sc->ws.lb_on = false;
     if (rc < 0) return rc;
     sc->r_count = cnt;
     sc->r_pos = 0;
-    sc->probes_done += sc->probes_eff;
+    // a full answer from an index scan: the probed lists may hold more tuples beyond the k-th.  (An exact scan stands for
+    // `ORDER BY distance LIMIT k`, prefilter_role.py:162-172: k IS the statement's limit, so it ends after k tuples.)
+    sc->batch_more = cnt == k && sc->batch_probes > 0;
     return 0;
 }
 
@@ -613,7 +667,7 @@ extern "C" int rk_rescan(rk_scan *sc, const float *q, int32_t q_dim, uint32_t us
         sc->max_probes_eff = 0;
     }
     sc->bound = true;
-    return scan_fetch_batch(sc);
+    return scan_fetch_batch(sc, false);
 }
 
 extern "C" int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *distance)
@@ -621,9 +675,15 @@ extern "C" int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *di
     if (!sc) return rk_fail(RK_ERR_INVALID, "NULL scan");
     if (!sc->bound) return rk_fail(RK_ERR_NO_ORDER, "cannot scan without order");
     while (sc->r_pos >= sc->r_count) {
+        if (sc->batch_more && sc->r_count > 0) {
+            // the current batch was cut at k tuples: continue it after the last pair returned
+            int rc = scan_fetch_batch(sc, true);
+            if (rc < 0) return rc;
+            continue;
+        }
         // ivfscan.c:375-381: refill from the next `probes` lists until max_probes is reached
         if (sc->probes_eff == 0 || sc->probes_done >= sc->max_probes_eff) return 0;
-        int rc = scan_fetch_batch(sc);
+        int rc = scan_fetch_batch(sc, false);
         if (rc < 0) return rc;
     }
     if (tid) *tid = sc->r_tid[sc->r_pos];
@@ -648,6 +708,7 @@ extern "C" void rk_endscan(rk_scan *sc)
 extern "C" int rk_set_stream(rk_index *ix, void *cuda_stream)
 {
     if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
+    std::lock_guard<std::mutex> g(ix->batch_mu);
     ix->ws.stream = cuda_stream ? (cudaStream_t) cuda_stream : ix->ws.own_stream;
     return RK_OK;
 }
@@ -656,8 +717,22 @@ extern "C" int rk_synchronize(rk_index *ix)
 {
     if (!ix) return rk_fail(RK_ERR_INVALID, "NULL index");
     RK_CUDA(cudaSetDevice(ix->device));
-    RK_CUDA(cudaStreamSynchronize(ix->ws.stream));
-    return collect_timing(ix, ix->ws);
+    std::lock_guard<std::mutex> g(ix->batch_mu);
+    Workspace &ws = ix->ws;
+    const bool armed = ws.qflag_armed;
+    if (armed) {
+        RK_CUDA(cudaMemcpyAsync(ws.h_qflag, ws.qflag.p, 4, cudaMemcpyDeviceToHost, ws.stream));
+        RK_CUDA(cudaMemsetAsync(ws.qflag.p, 0, 4, ws.stream));
+        ws.qflag_armed = false;
+    }
+    RK_CUDA(cudaStreamSynchronize(ws.stream));
+    int rc = collect_timing(ix, ws);
+    if (rc < 0) return rc;
+    if (armed && *ws.h_qflag) {
+        *ws.h_qflag = 0;
+        return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector (device-resident queries of a call since the last rk_synchronize)");
+    }
+    return RK_OK;
 }
 
 extern "C" int rk_enable_timing(rk_index *ix, int on)
@@ -703,5 +778,7 @@ extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)
     out->tensor_plan = (uint64_t) ix->tensor.last_plan;
     out->tensor_flop = (uint64_t) ix->tensor.last_flop;
     out->tensor_plan_bytes = ix->tensor.last_plan_bytes;
+    out->segment_kinds = ix->ws.seg_kinds;
+    out->single_fused = ix->ws.single_fused ? 1 : 0;
     return RK_OK;
 }

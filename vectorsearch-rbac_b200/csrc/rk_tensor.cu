@@ -180,7 +180,7 @@ struct TPass {
 // Paired mode (rk_bscan2_kernel): query tiles are `qt` = 256 wide, every range of tiles becomes a PAIR of units
 // (2p walks the even visits of the range, 2p + 1 the odd ones) and the schedule places pairs onto clusters.
 static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint32_t> &step, int sm, uint32_t LPQ, size_t nslots,
-                       TPass &ps, bool paired)
+                       TPass &ps, bool paired, int force_tpu)
 {
     const size_t qt = paired ? 256 : 128;
     const uint32_t upr = paired ? 2u : 1u;           // units per range of tiles
@@ -222,7 +222,7 @@ static void build_pass(const std::vector<TGroup> &groups, const std::vector<uint
             }
         }
     }
-    if (const char *e = getenv("RK_TENSOR_TPU")) tpu = (uint32_t) std::max(1, atoi(e));      // debugging aid: tiles per unit
+    if (force_tpu > 0) tpu = (uint32_t) force_tpu;      // debugging aid (rk_set_option "tensor_tpu"): tiles per unit
     ps.lid0.assign(nslots, 0); ps.lstep.assign(nslots, 0); ps.nlists.assign(nslots, 0);
     std::vector<double> unit_work;
     uint32_t slot = 0;
@@ -298,8 +298,9 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
                      const RkSelectParams &out, std::vector<uint32_t> &redo)
 {
     redo.clear();
-    // RK_TENSOR_HOST_TIMING=1: host microseconds per phase of this call on stderr (tuning aid)
-    static const bool host_timing = getenv("RK_TENSOR_HOST_TIMING") != nullptr;
+    // option tensor_host_timing: host microseconds per phase of this call on stderr (tuning aid)
+    const RkTuning &tune = ix->tune;
+    const bool host_timing = tune.tensor_host_timing != 0;
     auto t_prev = std::chrono::steady_clock::now();
     double t_phase[6] = {0, 0, 0, 0, 0, 0};
     auto tick = [&](int i) {
@@ -353,9 +354,9 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     //   atoms    per document class (same role mask): its tiles once, against every query that sees it
     // Which scoring kernel: long rows make the one-CTA kernel L2-feed-bound (32 flop per staged byte), so from 256
     // dimensions on the CTA-pair kernel (64 flop per staged byte, query tiles of 256) takes the batch; short rows
-    // are bound by the epilogue's select work, which the pair does not change.  RK_TENSOR_PAIR=0|1 forces it (tests).
+    // are bound by the epilogue's select work, which the pair does not change.  Option tensor_pair = 0|1 forces it (tests).
     bool paired = ix->dim_pad >= 256;
-    if (const char *e = getenv("RK_TENSOR_PAIR")) paired = atoi(e) != 0;
+    if (tune.tensor_pair >= 0) paired = tune.tensor_pair != 0;
     const size_t qt = paired ? 256 : 128;
     auto visit_cost = [&](double tiles, size_t qn) {
         const double qcols = (double) std::min<size_t>(qt, (qn + 15) & ~(size_t) 15);
@@ -389,12 +390,10 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
             }
             if (cost_a < 0.9 * best) { best = cost_a; plan = PLAN_ATOMS; }
         }
-        // test aid: RK_TENSOR_PLAN=dense|grouped|atoms forces a plan (all three give the same answers)
-        if (const char *force = getenv("RK_TENSOR_PLAN")) {
-            if (!strcmp(force, "dense")) plan = PLAN_DENSE;
-            else if (!strcmp(force, "grouped")) plan = PLAN_GROUPED;
-            else if (!strcmp(force, "atoms") && !ts.atoms.empty()) plan = PLAN_ATOMS;
-        }
+        // test aid: option tensor_plan = 1 dense | 2 grouped | 3 atoms forces a plan (all three give the same answers)
+        if (tune.tensor_plan == 1) plan = PLAN_DENSE;
+        else if (tune.tensor_plan == 2) plan = PLAN_GROUPED;
+        else if (tune.tensor_plan == 3 && !ts.atoms.empty()) plan = PLAN_ATOMS;
     }
     const bool per_slot_mask = plan != PLAN_GROUPED;       // which mask a slot carries: its query's own, or the group's
     if (plan == PLAN_DENSE && groups.size() > 1) {
@@ -449,17 +448,17 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // balance wants.
     std::vector<uint32_t> step_main(groups.size(), 1), step_sample(groups.size(), 0);
     bool sampled = false;
-    // test / tuning aids: RK_TENSOR_SAMPLE=0 disables the sampling pass, RK_TENSOR_SDIV and RK_TENSOR_SMIN move
+    // test / tuning aids: option tensor_sample = 0 disables the sampling pass, tensor_sdiv and tensor_smin move
     // the point where it starts to pay (parity tests use them to exercise it on small corpora)
-    const int env_sample = getenv("RK_TENSOR_SAMPLE") ? atoi(getenv("RK_TENSOR_SAMPLE")) : 1;
-    const int env_sdiv = getenv("RK_TENSOR_SDIV") ? std::max(1, atoi(getenv("RK_TENSOR_SDIV"))) : 400;
-    const uint32_t env_smin = getenv("RK_TENSOR_SMIN") ? (uint32_t) std::max(1, atoi(getenv("RK_TENSOR_SMIN"))) : 1024u;
+    const int env_sample = tune.tensor_sample;
+    const int env_sdiv = tune.tensor_sdiv > 0 ? tune.tensor_sdiv : 400;
+    const uint32_t env_smin = (uint32_t) tune.tensor_smin;
     for (size_t gi = 0; gi < groups.size() && env_sample; gi++) {
         const TGroup &g = groups[gi];
         if (g.tl_n < env_smin) continue;
         // about 1 in 400 of the (visible row, query) pairs should survive the seeded threshold: kp S / visible
         uint64_t S = std::min<uint64_t>(64, g.min_visible / ((uint64_t) env_sdiv * (uint64_t) kp));
-        if (S < 4 && !getenv("RK_TENSOR_SDIV")) {
+        if (S < 4 && tune.tensor_sdiv == 0) {
             // Too few visible rows for that, but a coarser seed still pays: a unit that starts at +inf collects about
             // kp ln(rows / kp) entries per query and stops the whole CTA for a compaction every few tiles.  Seeded
             // from every S-th tile a unit collects about kp S / (ranges the tiles are cut into): keep that near
@@ -473,8 +472,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         if (S >= 4) { step_sample[gi] = (uint32_t) S; sampled = true; }
     }
     TPass pm_, ps_;
-    build_pass(groups, step_main, sm, LPQ, nslots, pm_, paired);
-    if (sampled) build_pass(groups, step_sample, sm, LPQ, nslots, ps_, paired);
+    build_pass(groups, step_main, sm, LPQ, nslots, pm_, paired, tune.tensor_tpu);
+    if (sampled) build_pass(groups, step_sample, sm, LPQ, nslots, ps_, paired, tune.tensor_tpu);
     // final merge: every query owns the main-pass lists of all its slots
     std::vector<uint32_t> qoff(nq + 1, 0), qlist;
     {

@@ -1,5 +1,7 @@
 // rk_util.cu — layout helpers run once at load / index-build time (not on the query path).
 #include "rk_common.cuh"
+#include <algorithm>
+
 #include "rk_kernels.h"
 
 // dst[i][:] = src[perm[i]][:]  (rows of dim_pad floats, float4 granularity)
@@ -61,4 +63,22 @@ cudaError_t rk_count_nonfinite(const float *d_x, size_t n, unsigned long long *o
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     cudaFree(d);
     return e;
+}
+
+// Asynchronous variant for the device-pointer query entry points: sets *flag when any element is NaN / Inf; the host
+// reads the flag at the next rk_synchronize (vector_in's check, vector.c:102-113, without a sync on the search path).
+__global__ void rk_flag_nonfinite_kernel(const float *__restrict__ x, size_t n, uint32_t *flag)
+{
+    unsigned c = 0;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
+        c |= (__float_as_uint(x[i]) & 0x7f800000u) == 0x7f800000u;
+    if (__any_sync(0xffffffffu, c != 0) && (threadIdx.x & 31) == 0) atomicOr(flag, 1u);
+}
+
+cudaError_t rk_launch_flag_nonfinite(const float *d_x, size_t n, uint32_t *d_flag, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    const unsigned grid = (unsigned) std::min<size_t>((n + 2047) / 2048, 148 * 4);
+    rk_flag_nonfinite_kernel<<<grid, 256, 0, stream>>>(d_x, n, d_flag);
+    return cudaGetLastError();
 }

@@ -201,6 +201,10 @@ class Index:
         return Scan(self)
 
     # -- plumbing
+    def set_option(self, name: str, value: int) -> None:
+        """Tuning / test switch of this index (rk_set_option)."""
+        _check(lib.rk_set_option(self._h, name.encode(), int(value)))
+
     def set_stream(self, cuda_stream: Optional[int]) -> None:
         _check(lib.rk_set_stream(self._h, cuda_stream))
 
