@@ -245,6 +245,99 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
+# single-query legs: what one pgvector-shaped scan costs (one query per rescan, ivfscan.c:339-389)
+
+def depth_users(ur, dr):
+    """One user per distinct visible-set size (tree RBAC: role depth t = 1..4 sees t x rows / sets), smallest first."""
+    docs_of_role = {}
+    for _, r in dr:
+        docs_of_role[int(r)] = docs_of_role.get(int(r), 0) + 1
+    out = []
+    for sz in sorted(set(docs_of_role.values())):
+        r = next(r for r, c in docs_of_role.items() if c == sz)
+        us = ur[ur[:, 1] == r]
+        if len(us):
+            out.append((sz, int(us[0, 0])))
+    return out
+
+
+def single_query_legs(ix, wl, ur, dr, dev, k, flt, layout, reps=20, hbm_peak=None):
+    """Device and end-to-end time of ONE query through the host-buffer C-ABI, L2 flushed before every repetition (a 51-205
+    MB visible set would otherwise be served from the 126 MB L2): an unfiltered full-corpus query and one filtered query
+    per role depth.  device_us = CUDA events around the call's kernels (rk_get_scan_times: one fused launch per query);
+    e2e_us = wall clock of rk_search_batch(nq = 1) with pinned host buffers, copies inside; rescan_us = rk_rescan + k
+    rk_gettuple on a scan handle.  frac = (algorithmic bytes / measured HBM peak) / device time."""
+    import torch
+    import vectorsearch_rbac_b200 as vr
+    wl = as_workload(wl)
+    peak = hbm_peak or peaks()[0]
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    Q, _ = make_queries(wl, 8, dev)
+    Qh = torch.empty(Q.shape, dtype=torch.float32, pin_memory=True)
+    Qh.copy_(Q)
+    torch.cuda.synchronize(dev)
+    o_tid = torch.empty((1, k), dtype=torch.int64, pin_memory=True)
+    o_doc = torch.empty((1, k), dtype=torch.int32, pin_memory=True)
+    o_dist = torch.empty((1, k), dtype=torch.float64, pin_memory=True)
+    o_cnt = torch.empty(1, dtype=torch.int32, pin_memory=True)
+    cases = [("unfiltered full corpus", vr.FILTER_NONE, 0, 0)]
+    for t, (sz, u) in enumerate(depth_users(ur, dr), 1):
+        cases.append((f"filtered, role depth {t} ({sz} documents visible)", flt, layout, u))
+    sc = ix.begin_scan()
+    legs = []
+    lib = vr._lib.lib
+    for name, f, lay, user in cases:
+        opts = vr.engine.make_opts(k, filter=f, layout=lay, engine=vr.ENGINE_SCAN)
+        us = np.array([user], dtype=np.uint32)
+
+        def call(i):
+            rc = lib.rk_search_batch(ix._h, 1, Qh[i % 8].data_ptr(), us.ctypes.data, opts, o_tid.data_ptr(), o_doc.data_ptr(),
+                                     o_dist.data_ptr(), o_cnt.data_ptr())
+            if rc < 0:
+                raise RuntimeError(vr._lib.last_error())
+
+        for i in range(3):
+            call(i)
+        dev_us, e2e_us, rs_us = [], [], []
+        ix.enable_timing(True)
+        for i in range(reps):
+            flush.zero_()
+            torch.cuda.synchronize(dev)
+            call(i)
+            st = ix.stats()
+            dev_us.append((st["scan_ms"] + (st["select_ms"] if not st["single_fused"] else 0.0)) * 1e3)
+        ix.enable_timing(False)
+        st = ix.stats()
+        for i in range(reps):
+            flush.zero_()
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            call(i)
+            e2e_us.append((time.perf_counter() - t0) * 1e6)
+        qn = Qh.numpy()
+        for i in range(reps):
+            flush.zero_()
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            sc.rescan(qn[i % 8], user, k=k, filter=f, layout=lay)
+            n = 0
+            while sc.gettuple() is not None:
+                n += 1
+            rs_us.append((time.perf_counter() - t0) * 1e6)
+        roof_us = st["algo_bytes"] / (peak * 1e9) * 1e6
+        d, e, r = float(np.median(dev_us)), float(np.median(e2e_us)), float(np.median(rs_us))
+        legs.append({"case": name, "rows_scanned": int(st["rows_scanned"]), "algorithmic_bytes": int(st["algo_bytes"]),
+                     "roofline_us": roof_us, "device_us": d, "frac_device": roof_us / d if d > 0 else None,
+                     "e2e_us": e, "frac_e2e": roof_us / e if e > 0 else None, "rescan_gettuple_us": r,
+                     "launches_per_query": int(st["launches"]), "fused_single_launch": bool(st["single_fused"]),
+                     "segments": int(st["segments"]), "count": int(o_cnt[0])})
+    sc.end()
+    del flush
+    return {"l2": "flushed (512 MB write) before every repetition", "reps": reps, "k": k, "hbm_peak_gbs": peak, "legs": legs,
+            "note": "rescan_gettuple_us includes k ctypes round trips of the Python binding (about 1 us each)"}
+
+
+# ------------------------------------------------------------------------------------------------
 # CPU leg (the checker timed as a baseline; never on the product path)
 
 def cpu_partitions(doc, ur, dr, qusers):

@@ -415,3 +415,76 @@ def test_device_resident_queries_are_validated():
     with pytest.raises(vr.RkError, match="unknown option"):
         ix.set_option("no_such_switch", 1)
     ix.close()
+
+
+# ---- the one-launch single-query path ---------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("kind,dim,metric", [("sift", 128, 0), ("cohere", 96, 1), ("sift", 772, 0)])
+def test_single_query_fused_launch(kind, dim, metric):
+    """A pgvector scan is one query per rescan (ivfscan.c:339-389): nq = 1 runs as ONE launch (scan + merge by the last
+    CTA), through rk_search_batch and through rk_rescan / rk_gettuple, for every filter whose plan cannot repeat a tuple."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset(kind, n=60000, dim=dim, rows_per_doc=20, rbac="tree", num_users=40, num_roles=12)
+    ix = load_index(ds, metric=metric, k_max=1024)
+    ix.finalize()
+    Q, users = _queries(ds, 12, seed=17)
+    users[1] = 31337                                           # unknown user: empty answer
+    exact = kind == "sift"
+    sc = ix.begin_scan()
+    for mode, flt, layout in (("role", 0, 1), ("combination", 0, 2), ("bitmask", 1, 0), ("none", 2, 0)):
+        for k in (1, 100, 1000):
+            exp = oracle_role_search(ds, Q, users, metric, k, mode=mode)
+            for qi in range(len(Q)):
+                got = ix.search_batch(Q[qi:qi + 1], users[qi:qi + 1], k, filter=flt, layout=layout)
+                st = ix.stats()
+                assert st["single_fused"] == 1 and st["launches"] == 1, st
+                assert_topk_matches(got, tuple(x[qi:qi + 1] for x in exp), exact=exact)
+            if k == 100:
+                for qi in range(0, len(Q), 3):
+                    sc.rescan(Q[qi], int(users[qi]), k=k, filter=flt, layout=layout)
+                    rows = list(sc)
+                    n = int(exp[4][qi])
+                    assert len(rows) == n
+                    if exact:
+                        assert [r[0] for r in rows] == exp[0][qi][:n].tolist()
+                        assert [r[2] for r in rows] == exp[2][qi][:n].tolist()
+    sc.end()
+    # the two-launch path gives the same bits
+    a = ix.search_batch(Q[:1], users[:1], 100, filter=vr.FILTER_BITMASK)
+    ix.set_option("single_fused", 0)
+    b = ix.search_batch(Q[:1], users[:1], 100, filter=vr.FILTER_BITMASK)
+    assert ix.stats()["single_fused"] == 0 and ix.stats()["launches"] == 2
+    for x, y in zip(a, b):
+        np.testing.assert_array_equal(x, y)
+    ix.close()
+
+
+def test_single_query_fused_ties_and_fallbacks():
+    """Ties at the k-th key: the answer takes the smallest tuple ids among them; more ties than the fused merge holds
+    (> 2048) make the call fall back to the two-launch path; a user with several role partitions needs the dedup merge."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("sift", n=40000, dim=16, rows_per_doc=10, rbac="random", num_users=30, num_roles=8)
+    ds["X"][5000:9000] = ds["X"][5000]                       # 4000 identical rows
+    ds["X"][20000:20300] = ds["X"][20000]                    # 300 identical rows
+    ix = load_index(ds)
+    ix.finalize()
+    users = np.unique(ds["user_roles"][:, 0]).astype(np.uint32)
+    for row, k in ((5000, 50), (5000, 100), (20000, 100), (20000, 400), (123, 100)):
+        Q = ds["X"][row:row + 1].copy()
+        got = ix.search_batch(Q, users[:1], k, filter=vr.FILTER_NONE)
+        exp = oracle_role_search(ds, Q, users[:1], orc.METRIC_L2, k, mode="none")
+        assert_topk_matches(got, exp, exact=True)
+    assert ix.stats()["single_fused"] == 1
+    rb = orc.Rbac(ds["doc_roles"], ds["user_roles"])
+    multi = next(int(u) for u in users if len(rb.roles_of_user(int(u))) > 1)
+    one = next(int(u) for u in users if len(rb.roles_of_user(int(u))) == 1)
+    Q = ds["X"][777:778].copy()
+    for u, fused in ((multi, 0), (one, 1)):
+        us = np.array([u], dtype=np.uint32)
+        got = ix.search_batch(Q, us, 60, filter=vr.FILTER_PARTITION, layout=vr.LAYOUT_ROLE)
+        assert ix.stats()["single_fused"] == fused
+        assert_topk_matches(got, oracle_role_search(ds, Q, us, orc.METRIC_L2, 60, mode="role"), exact=True)
+        got = ix.search_batch(Q, us, 60, filter=vr.FILTER_PARTITION, layout=vr.LAYOUT_ROLE, keep_duplicates=True)
+        assert ix.stats()["single_fused"] == 1                # the ground-truth merge keeps duplicates: nothing to dedup
+        assert_topk_matches(got, oracle_role_search(ds, Q, us, orc.METRIC_L2, 60, dedup=False, mode="role"), exact=True)
+    ix.close()

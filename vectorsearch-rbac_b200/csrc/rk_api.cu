@@ -104,6 +104,10 @@ void Workspace::destroy()
 {
     if (h_qflag) cudaFreeHost(h_qflag);
     h_qflag = nullptr;
+    for (auto &kv : fused_plans) kv.second.buf.release();
+    fused_plans.clear();
+    fz_ctl.release(); fz_key.release(); fz_row.release(); fz_pack.release();
+    h_fz.release();
     DevBuf *bufs[] = {&qflag, &segs, &order, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
                       &out_doc, &out_dist, &out_count, &probe_key, &probe_list, &ex_key, &ex_tid, &ex_doc};
     for (auto *b : bufs) b->release();

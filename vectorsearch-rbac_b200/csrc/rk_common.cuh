@@ -75,6 +75,24 @@ struct RkScanParams {
     int lb_on;
     uint32_t lb_key;
     uint64_t lb_tid;
+    // Fused single-query mode: ONE launch per query.  Every segment belongs to the same query and no tuple can reach it
+    // twice, so a CTA keeps one candidate buffer through all its segments, hands its k best (unsorted) to a flat global
+    // list when the work list is drained, and the LAST CTA to finish selects the answer from that list and writes the
+    // outputs — the scan + 148-list select of a pgvector-shaped scan (one query per ivfflatrescan, ivfscan.c:339-389)
+    // without a second launch.  nseg comes by value and the control words are reset by the last CTA, so a call uploads
+    // nothing but the query.
+    int fused;
+    uint32_t nseg_val;              // number of segments when nseg_ptr is NULL
+    int fz_cap;                     // entries one CTA may hand over
+    uint32_t *fz_ctl;               // [0] entries handed over, [1] CTAs done (both 0 between launches)
+    uint32_t *fz_key;               // [grid * fz_cap]
+    uint32_t *fz_row;
+    const uint32_t *fz_doc_ids;     // dense document -> raw id
+    uint64_t *fz_out_tid;           // [k] outputs (any may be NULL except status / count)
+    uint32_t *fz_out_doc;
+    double *fz_out_dist;
+    float *fz_out_key;
+    int32_t *fz_out_count;          // [0] tuples returned; -1 = the merge could not finish (too many ties): rerun unfused
 };
 
 struct RkSelectParams {

@@ -50,6 +50,16 @@ struct PinBuf {
     template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// One cached single-query plan (fused path): the work list and the user's role mask, resident in HBM.  It depends on the
+// user's role set, the filter and the layout only — not on the query vector or k — so a pgvector-shaped scan
+// (one query per rk_rescan) uploads nothing but its query.
+struct FusedPlan {
+    DevBuf buf;                 // [segments][role mask]
+    uint32_t nseg = 0;
+    size_t off_qmask = 0;
+    uint64_t rows_scanned = 0, algo_bytes = 0;   // algo_bytes without the 12k output term
+};
+
 // Everything one search context needs: a stream, the uploaded plan, per-segment candidate lists
 // and result buffers.  The index owns one (rk_search_batch*), every rk_scan owns another.
 struct Workspace {
@@ -64,6 +74,10 @@ struct Workspace {
     DevBuf probe_key, probe_list;        // IVF: per-query selected lists
     const uint32_t *ext_probe = nullptr; // IVF: list choice supplied by the caller (rk_search_batch_shard_probed), [nq][probes]
     DevBuf ex_key, ex_tid, ex_doc;       // exchange-form results
+    // fused single-query path
+    std::unordered_map<uint64_t, FusedPlan> fused_plans;
+    DevBuf fz_ctl, fz_key, fz_row, fz_pack;   // control words, flat hand-over list, packed outputs [count | tid | dist | doc | key]
+    PinBuf h_fz;                              // pinned staging: query in, packed outputs back
     PinBuf h_plan_ring[2], h_out;        // plan staging alternates so the host may run one batch ahead
     cudaEvent_t ring_a[RK_TIMING_RING] = {}, ring_b[RK_TIMING_RING] = {};   // scan-kernel event pairs
     uint64_t ring_n = 0;

@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     }
     __syncthreads();
 
-    const uint32_t nseg = *p.nseg_ptr;
+    const uint32_t nseg = p.nseg_ptr ? *p.nseg_ptr : p.nseg_val;
 
     if (warp == RK_CONS_WARPS) {
         // ===================== producer warp =====================
@@ -603,7 +603,8 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
         const bool last = (m.flags & RK_FLAG_LAST) != 0;
         // a segment whose successor on this CTA continues the same single-partition query ends without a final
         // select: the buffer and the threshold carry over, and this segment's own list stays empty
-        const bool cont = last && (m.flags & RK_FLAG_CONT) != 0;
+        // (fused single-query mode: every segment is the same query's, the buffer lives until the work list is drained)
+        const bool cont = last && ((m.flags & RK_FLAG_CONT) != 0 || p.fused);
         const bool fin = last && !cont;
         if (last || ++since_ckpt == ckpt) {
             since_ckpt = 0;
@@ -641,9 +642,127 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
                 }
                 csync();
             }
-            if (cont && t == 0) p.cand_count[m.seg] = 0;
+            if (cont && t == 0 && !p.fused) p.cand_count[m.seg] = 0;
         }
         if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
+    }
+    if (!p.fused) return;
+
+    // ===================== fused single-query epilogue =====================
+    // (1) this CTA's k best candidates (threshold only, no order) go to the flat global list.
+    csync();                                  // every warp has left the loop: no append is in flight
+    int n = (int) *s_count;
+    if (n > p.k) {
+        const uint32_t tau = rk_radix_kth(cb.key, n, p.k, s_hist, s_wsum, s_sel, t, csync);
+        n = rk_compact_le(cb, n, tau, t, s_wsum, csync);
+        if (n > p.fz_cap) {
+            // more ties at the k-th key than a CTA may hand over: exact (key, tuple id) order keeps precisely k
+            for (int i = t; i < n; i += RK_CONS_THREADS) cb.tid[i] = p.store.tid[cb.row[i]];
+            rk_bitonic_sort(cb, n, t, RK_CONS_THREADS, csync);
+            n = p.k;
+        }
+    }
+    if (t == 0) s_sel[0] = n ? atomicAdd(&p.fz_ctl[0], (uint32_t) n) : 0u;
+    csync();
+    {
+        const uint32_t base = s_sel[0];
+        for (int i = t; i < n; i += RK_CONS_THREADS) {
+            __stcg(&p.fz_key[base + i], cb.key[i]);
+            __stcg(&p.fz_row[base + i], cb.row[i]);
+        }
+    }
+    __threadfence();
+    csync();
+    if (t == 0) s_sel[1] = atomicAdd(&p.fz_ctl[1], 1u);
+    csync();
+    if (s_sel[1] != gridDim.x - 1) return;
+
+    // (2) the last CTA to finish: exact k-th smallest key over everything handed over (4-pass radix select straight from
+    // L2), gather the entries up to it, order them by (key, tuple id), write the answer.
+    __threadfence();
+    const int N = (int) __ldcg(&p.fz_ctl[0]);
+    uint32_t kth = RK_KEY_SENTINEL;
+    if (N > p.k) {
+        uint32_t prefix = 0, mask = 0, kk = (uint32_t) p.k;
+#pragma unroll 1
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            s_hist[t] = 0;
+            csync();
+            for (int i0 = t; i0 < N; i0 += RK_CONS_THREADS * 8) {
+                uint32_t kv[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) { const int i = i0 + j * RK_CONS_THREADS; kv[j] = i < N ? __ldcg(&p.fz_key[i]) : 0u; }
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (i0 + j * RK_CONS_THREADS < N && (kv[j] & mask) == prefix) atomicAdd(&s_hist[(kv[j] >> shift) & 255u], 1u);
+            }
+            csync();
+            const uint32_t c = s_hist[t];
+            uint32_t tot;
+            const uint32_t incl = rk_block_scan(c, t, s_wsum, &tot, csync);
+            const uint32_t excl = incl - c;
+            if (excl < kk && kk <= incl) { s_sel[0] = (uint32_t) t; s_sel[1] = kk - excl; }
+            csync();
+            prefix |= s_sel[0] << shift;
+            mask |= 0xFFu << shift;
+            kk = s_sel[1];
+        }
+        kth = prefix;
+    }
+    if (t == 0) *s_count = 0;
+    csync();
+    for (int i0 = t; i0 < N; i0 += RK_CONS_THREADS * 8) {
+        uint32_t kv[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) { const int i = i0 + j * RK_CONS_THREADS; kv[j] = i < N ? __ldcg(&p.fz_key[i]) : RK_KEY_SENTINEL; }
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int i = i0 + j * RK_CONS_THREADS;
+            if (i < N && kv[j] <= kth) {
+                const uint32_t slot = atomicAdd((uint32_t *) s_count, 1u);
+                if (slot < RK_CAND_CAP) { cb.key[slot] = kv[j]; cb.row[slot] = __ldcg(&p.fz_row[i]); }
+            }
+        }
+    }
+    csync();
+    int m = (int) *s_count;
+    const bool overflow = m > RK_CAND_CAP;     // more than RK_CAND_CAP entries tie at the k-th key: the host reruns unfused
+    if (overflow) m = 0;
+    for (int i = t; i < m; i += RK_CONS_THREADS) cb.tid[i] = p.store.tid[cb.row[i]];
+    csync();
+    const int cnt = overflow ? 0 : (m < p.k ? m : p.k);
+    auto emit = [&](int r, uint32_t key, uint32_t row, uint64_t tid) {
+        const float ord = rk_key_to_float(key);
+        if (p.fz_out_tid) p.fz_out_tid[r] = tid;
+        if (p.fz_out_key) p.fz_out_key[r] = ord;
+        if (p.fz_out_doc) p.fz_out_doc[r] = p.fz_doc_ids[p.store.rowdoc[row]];
+        if (p.fz_out_dist) p.fz_out_dist[r] = p.null_query ? 0.0 : (METRIC == 0 ? sqrt((double) ord) : (double) ord);   // vector.c:577, :635
+    };
+    if (m <= 512) {
+        // rank sort: an entry's position is the number of entries ordered before it — no barriers, m^2 / 256 compares per thread
+        for (int i = t; i < m; i += RK_CONS_THREADS) {
+            const uint32_t ki = cb.key[i];
+            const uint64_t ti = cb.tid[i];
+            int r = 0;
+            for (int j = 0; j < m; j++) r += rk_cand_less(cb.key[j], cb.tid[j], ki, ti) ? 1 : 0;
+            if (r < cnt) emit(r, ki, cb.row[i], ti);
+        }
+    } else {
+        rk_bitonic_sort(cb, m, t, RK_CONS_THREADS, csync);
+        for (int i = t; i < cnt; i += RK_CONS_THREADS) emit(i, cb.key[i], cb.row[i], cb.tid[i]);
+    }
+    for (int i = cnt + t; i < p.k; i += RK_CONS_THREADS) {
+        if (p.fz_out_tid) p.fz_out_tid[i] = 0xFFFFFFFFFFFFFFFFull;
+        if (p.fz_out_key) p.fz_out_key[i] = __int_as_float(0x7f800000);
+        if (p.fz_out_doc) p.fz_out_doc[i] = 0xFFFFFFFFu;
+        if (p.fz_out_dist) p.fz_out_dist[i] = __longlong_as_double(0x7ff0000000000000ll);
+    }
+    if (t == 0) {
+        *p.fz_out_count = overflow ? -1 : cnt;
+        // ready for the next launch: nothing is uploaded per call but the query
+        p.fz_ctl[0] = 0;
+        p.fz_ctl[1] = 0;
+        *p.seg_counter = 0;
     }
 }
 

@@ -119,6 +119,38 @@ static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std
     return 0;
 }
 
+// Cuts the partitions one query walks into segments of about `target` rows (appended to segs); returns the extent /
+// mask bytes the plan makes the producer read (SURVEY.md §8(d) "M").
+static uint64_t append_segments(const rk_index *ix, const std::vector<PlanItem> &items, uint32_t q, uint64_t target,
+                                std::vector<RkSegment> &segs)
+{
+    const int W = ix->mask_words;
+    uint64_t mask_bytes = 0;
+    for (auto &pi : items) {
+        const PartInfo &P = ix->parts[pi.part];
+        uint64_t nchunks = (pi.rows_est + target - 1) / target;
+        if (nchunks < 1) nchunks = 1;
+        if (nchunks > P.rows) nchunks = P.rows;
+        for (uint64_t c = 0; c < nchunks; c++) {
+            RkSegment s;
+            s.query = q; s.kind = RK_SEG_EXTENTS;
+            s.flags = (uint16_t) (pi.flags | (items.size() == 1 ? RK_SEGF_MERGE_OK : 0u));
+            s.begin = P.rows * c / nchunks;
+            s.end = P.rows * (c + 1) / nchunks;
+            if (s.end <= s.begin) continue;
+            // extents [lo, hi) of the partition intersect virtual rows [begin, end)
+            const auto vb = P.vstart.begin(), ve = P.vstart.end();
+            const uint32_t lo = (uint32_t) (std::upper_bound(vb, ve, (uint32_t) s.begin) - vb) - 1;
+            const uint32_t hi = (uint32_t) (std::lower_bound(vb, ve, (uint32_t) s.end) - vb);
+            s.ext_lo = P.ext_off + lo;
+            s.ext_hi = P.ext_off + hi;
+            segs.push_back(s);
+        }
+        if (pi.flags & RK_SEGF_MASKED) mask_bytes += (uint64_t) P.n_ext * (8ull * W + 8);
+    }
+    return mask_bytes;
+}
+
 // Build the work list of an exact (probes == 0) batch into ws.h_plan and upload it.
 static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32_t *user_ids, const rk_scan_opts *o,
                             uint32_t *out_nseg)
@@ -153,28 +185,7 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
     uint64_t mask_bytes = 0;
     for (size_t q = 0; q < nq; q++) {
         qseg[q] = (uint32_t) segs.size();
-        for (auto &pi : per_q[q]) {
-            const PartInfo &P = ix->parts[pi.part];
-            uint64_t nchunks = (pi.rows_est + target - 1) / target;
-            if (nchunks < 1) nchunks = 1;
-            if (nchunks > P.rows) nchunks = P.rows;
-            for (uint64_t c = 0; c < nchunks; c++) {
-                RkSegment s;
-                s.query = (uint32_t) q; s.kind = RK_SEG_EXTENTS;
-                s.flags = (uint16_t) (pi.flags | (per_q[q].size() == 1 ? RK_SEGF_MERGE_OK : 0u));
-                s.begin = P.rows * c / nchunks;
-                s.end = P.rows * (c + 1) / nchunks;
-                if (s.end <= s.begin) continue;
-                // extents [lo, hi) of the partition intersect virtual rows [begin, end)
-                const auto vb = P.vstart.begin(), ve = P.vstart.end();
-                const uint32_t lo = (uint32_t) (std::upper_bound(vb, ve, (uint32_t) s.begin) - vb) - 1;
-                const uint32_t hi = (uint32_t) (std::lower_bound(vb, ve, (uint32_t) s.end) - vb);
-                s.ext_lo = P.ext_off + lo;
-                s.ext_hi = P.ext_off + hi;
-                segs.push_back(s);
-            }
-            if (pi.flags & RK_SEGF_MASKED) mask_bytes += (uint64_t) P.n_ext * (8ull * W + 8);
-        }
+        mask_bytes += append_segments(ix, per_q[q], (uint32_t) q, target, segs);
     }
     qseg[nq] = (uint32_t) segs.size();
     const uint32_t nseg = (uint32_t) segs.size();
@@ -305,6 +316,112 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
     p.lb_tid = ws.lb_tid;
 }
 
+// ---------------------------------------------------------------------------------------------
+// One query, one launch: the pgvector-shaped scan (ivfscan.c:339-389: one query per rescan).  The plan — work list and
+// role mask — depends on the user's role set, the filter and the layout only, so it is built once per (role mask, filter,
+// layout), kept in HBM, and a call uploads nothing but its query.  Returns 1 when the call was served, 0 when this path
+// does not apply (a user with several partitions needs the dedup merge), < 0 on error.
+static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, const uint32_t *user_ids, const rk_scan_opts *o,
+                               const RkSelectParams &out, int32_t *d_count)
+{
+    const UserInfo *u = nullptr;
+    if (user_ids) {
+        auto it = ix->users.find(user_ids[0]);
+        if (it != ix->users.end()) u = &it->second;
+    }
+    int layout = o->filter == RK_FILTER_PARTITION ? o->layout : 0;
+    if (o->filter == RK_FILTER_PARTITION && layout == RK_LAYOUT_AUTO)
+        layout = !ix->roleset_parts.empty() ? RK_LAYOUT_DYNAMIC : ix->want_combo_parts ? RK_LAYOUT_COMBINATION : RK_LAYOUT_ROLE;
+    const uint64_t key = ((uint64_t) o->filter << 40) | ((uint64_t) layout << 36) | ((uint64_t) (o->keep_duplicates != 0) << 44) | (o->filter == RK_FILTER_NONE || !u ? 0ull : (uint64_t) u->mask_id + 1ull);
+    auto pit = ws.fused_plans.find(key);
+    if (pit == ws.fused_plans.end()) {
+        std::vector<PlanItem> items;
+        int rc = plan_user(ix, u, o, items);
+        if (rc < 0) return rc;
+        if (items.size() > 1 && !o->keep_duplicates) {                  // duplicates across partitions: the dedup merge
+            FusedPlan na;
+            na.nseg = 0xFFFFFFFFu;                                      // remembered: this role set does not take the fused path
+            ws.fused_plans.emplace(key, std::move(na));
+            return 0;
+        }
+        if (ws.fused_plans.size() >= 4096) {
+            RK_CUDA(cudaStreamSynchronize(ws.stream));                  // a launch may still read a cached plan
+            for (auto &kv : ws.fused_plans) kv.second.buf.release();
+            ws.fused_plans.clear();
+        }
+        uint64_t total_rows = 0, algo_rows = 0;
+        for (auto &pi : items) { total_rows += pi.rows_est; algo_rows += pi.rows_algo; }
+        // a segment costs about a microsecond here (claim, descriptor, pipeline refill — no per-segment select), so with
+        // T = streaming time per CTA the best count per CTA is ~sqrt(T / 2o): more, smaller segments than a batch plan cuts
+        const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4, sm = (uint64_t) ix->sm_count;
+        const double t_cta_us = (double) total_rows * (double) row_bytes / (double) sm / 44.0e3;
+        double per_cta = std::sqrt(t_cta_us / 2.0);
+        per_cta = std::min(32.0, std::max(1.0, per_cta));
+        uint64_t target = (uint64_t) ((double) total_rows / ((double) sm * per_cta)) + 1;
+        target = std::max<uint64_t>(target, (uint64_t) ix->tile_rows);
+        std::vector<RkSegment> segs;
+        const uint64_t mask_bytes = append_segments(ix, items, 0u, target, segs);
+        FusedPlan fp;
+        fp.nseg = (uint32_t) segs.size();
+        const int W = ix->mask_words;
+        const size_t b_segs = segs.size() * sizeof(RkSegment);
+        fp.off_qmask = (b_segs + 15) & ~(size_t) 15;
+        std::vector<unsigned char> host(fp.off_qmask + (size_t) W * 8, 0);
+        if (b_segs) memcpy(host.data(), segs.data(), b_segs);
+        for (int w = 0; w < W; w++) reinterpret_cast<uint64_t *>(host.data() + fp.off_qmask)[w] = u ? u->mask[(size_t) w] : 0ull;
+        if (fp.buf.ensure(host.size()) != 0) return RK_ERR_CUDA;
+        RK_CUDA(cudaMemcpyAsync(fp.buf.p, host.data(), host.size(), cudaMemcpyHostToDevice, ws.stream));
+        RK_CUDA(cudaStreamSynchronize(ws.stream));                      // `host` goes out of scope
+        fp.rows_scanned = total_rows;
+        fp.algo_bytes = algo_rows * row_bytes + mask_bytes;
+        pit = ws.fused_plans.emplace(key, std::move(fp)).first;
+    }
+    FusedPlan &fp = pit->second;
+    if (fp.nseg == 0xFFFFFFFFu) return 0;
+    const int k = o->k;
+    RkScanParams p;
+    rk_fill_scan_params(ix, ws, p, false, dQ, o, k);
+    const int grid = (int) std::max<uint32_t>(1u, std::min<uint32_t>((uint32_t) ix->sm_count, fp.nseg));
+    // what a CTA may hand over: its k best plus ties (the scan kernel's own limit before it falls back to the exact sort)
+    int ckpt = 512 / ix->tile_rows;
+    ckpt = std::max(1, std::min(16, ckpt));
+    const int trigger = 2048 - ckpt * ix->tile_rows;
+    p.fz_cap = k + (trigger - k) / 2;
+    if (ws.fz_ctl.p == nullptr) {
+        if (ws.fz_ctl.ensure(64) != 0) return RK_ERR_CUDA;
+        RK_CUDA(cudaMemsetAsync(ws.fz_ctl.p, 0, 64, ws.stream));
+    }
+    const size_t flat = (size_t) ix->sm_count * (size_t) p.fz_cap;
+    if (ws.fz_key.ensure(flat * 4) != 0 || ws.fz_row.ensure(flat * 4) != 0) return RK_ERR_CUDA;
+    p.fused = 1;
+    p.segs = fp.buf.as<RkSegment>();
+    p.seg_order = nullptr;
+    p.nseg_ptr = nullptr;
+    p.nseg_val = fp.nseg;
+    p.qmask = reinterpret_cast<const uint64_t *>(fp.buf.as<unsigned char>() + fp.off_qmask);
+    p.seg_counter = ws.fz_ctl.as<uint32_t>() + 2;
+    p.fz_ctl = ws.fz_ctl.as<uint32_t>();
+    p.fz_key = ws.fz_key.as<uint32_t>();
+    p.fz_row = ws.fz_row.as<uint32_t>();
+    p.fz_doc_ids = ix->d_doc_ids.as<uint32_t>();
+    p.fz_out_tid = out.out_tid; p.fz_out_doc = out.out_doc; p.fz_out_dist = out.out_dist; p.fz_out_key = out.out_key;
+    p.fz_out_count = d_count;
+    p.cand_key = nullptr; p.cand_tid = nullptr; p.cand_row = nullptr; p.cand_count = nullptr;
+    const int slot = (int) (ws.ring_n % RK_TIMING_RING);
+    if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot], ws.stream));
+    RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid));
+    if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot], ws.stream)); ws.timed_scan = true; ws.ring_n++; }
+    ws.launches = 1;
+    ws.single_fused = true;
+    ws.segments = fp.nseg;
+    ws.seg_kinds = fp.nseg ? 1u << RK_SEG_EXTENTS : 0u;
+    ws.rows_scanned = fp.rows_scanned;
+    ws.algo_bytes = fp.algo_bytes + 12ull * (uint64_t) k;
+    ws.plan_single_partition = true;
+    ix->total_launches += 1;
+    return 1;
+}
+
 // One batch on device: dQ [nq][dim_pad].  `out` carries the destination pointers (device).
 static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, const uint32_t *user_ids,
                          const rk_scan_opts *o, int probe_offset, RkSelectParams out);
@@ -425,14 +542,61 @@ static int stage_queries(rk_index *ix, Workspace &ws, size_t nq, const float *Q)
     return 0;
 }
 
+// The single-query host path: pinned staging in both directions, ONE host->device copy (the query), ONE launch, ONE
+// device->host copy (count | tid | dist | doc | key, packed).  Returns 1 = served, 0 = not applicable, < 0 = error.
+static int host_search_single(rk_index *ix, Workspace &ws, const float *Q, const uint32_t *user_ids, const rk_scan_opts *o,
+                              uint64_t *out_tid, uint32_t *out_doc, double *out_dist, int32_t *out_count, float *out_key)
+{
+    const int k = o->k;
+    const size_t rb = (size_t) ix->dim_pad * 4;
+    const size_t o_tid = 16, o_dist = o_tid + (size_t) k * 8, o_doc = o_dist + (size_t) k * 8, o_key = o_doc + (size_t) k * 4;
+    const size_t pack = (o_key + (size_t) k * 4 + 15) & ~(size_t) 15;
+    if (ws.dq.ensure(std::max<size_t>(rb, 16)) != 0 || ws.fz_pack.ensure(pack) != 0 || ws.h_fz.ensure(rb + pack) != 0) return RK_ERR_CUDA;
+    unsigned char *hin = ws.h_fz.as<unsigned char>(), *hout = hin + rb;
+    if (!o->null_query && !rk_all_finite(Q, (size_t) ix->dim)) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
+    memcpy(hin, Q, (size_t) ix->dim * 4);
+    if (ix->dim != ix->dim_pad) memset(hin + (size_t) ix->dim * 4, 0, rb - (size_t) ix->dim * 4);
+    RK_CUDA(cudaMemcpyAsync(ws.dq.p, hin, rb, cudaMemcpyHostToDevice, ws.stream));
+    unsigned char *dp = ws.fz_pack.as<unsigned char>();
+    RkSelectParams out;
+    memset(&out, 0, sizeof out);
+    out.out_tid = reinterpret_cast<uint64_t *>(dp + o_tid);
+    out.out_dist = reinterpret_cast<double *>(dp + o_dist);
+    out.out_doc = out_doc ? reinterpret_cast<uint32_t *>(dp + o_doc) : nullptr;
+    out.out_key = out_key ? reinterpret_cast<float *>(dp + o_key) : nullptr;
+    ws.launches = 0;
+    ws.seg_kinds = 0;
+    ws.single_fused = false;
+    ws.timed_scan = ws.timed_select = ws.timed_probe = false;
+    if (&ws == &ix->ws) ix->tensor.last_plan = 0;
+    int rc = search_single_fused(ix, ws, ws.dq.as<float>(), user_ids, o, out, reinterpret_cast<int32_t *>(dp));
+    if (rc <= 0) return rc;                                 // 0: the general path restages the query on the same stream
+    RK_CUDA(cudaMemcpyAsync(hout, dp, pack, cudaMemcpyDeviceToHost, ws.stream));
+    RK_CUDA(cudaStreamSynchronize(ws.stream));
+    const int32_t cnt = *reinterpret_cast<const int32_t *>(hout);
+    if (cnt < 0) return 0;                                  // more ties at the k-th key than the fused merge holds: general path
+    memcpy(out_tid, hout + o_tid, (size_t) k * 8);
+    memcpy(out_dist, hout + o_dist, (size_t) k * 8);
+    if (out_doc) memcpy(out_doc, hout + o_doc, (size_t) k * 4);
+    if (out_key) memcpy(out_key, hout + o_key, (size_t) k * 4);
+    *out_count = cnt;
+    rc = collect_timing(ix, ws);
+    return rc < 0 ? rc : 1;
+}
+
 static int host_search(rk_index *ix, Workspace &ws, size_t nq, const float *Q, const uint32_t *user_ids,
                        const rk_scan_opts *o, int probe_offset, uint64_t *out_tid, uint32_t *out_doc, double *out_dist,
                        int32_t *out_count, float *out_key = nullptr)
 {
     RK_CUDA(cudaSetDevice(ix->device));
+    int rc;
+    if (nq == 1 && o->probes == 0 && o->engine != RK_ENGINE_TENSOR && ix->tune.single_fused) {
+        rc = host_search_single(ix, ws, Q, user_ids, o, out_tid, out_doc, out_dist, out_count, out_key);
+        if (rc != 0) return rc < 0 ? rc : RK_OK;          // served (or failed); 0 = this path does not apply
+    }
     // the upload is started first and the host validates the same bytes while the copy engine moves them (nothing has
     // been launched on them yet when a bad element makes the call fail)
-    int rc = stage_queries(ix, ws, nq, Q);
+    rc = stage_queries(ix, ws, nq, Q);
     if (rc < 0) return rc;
     if (!o->null_query && !rk_all_finite(Q, nq * (size_t) ix->dim)) {
         cudaStreamSynchronize(ws.stream);
