@@ -111,7 +111,7 @@ int rk_abi_version(void);
  * internals): "tensor_plan" (0 cheapest | 1 dense | 2 per user mask | 3 per document class), "tensor_pair" (-1 by row
  * length | 0 one-CTA kernel | 1 CTA-pair kernel), "tensor_bf16" (-1 by row length | 0 TF32 | 1 bf16 nomination),
  * "tensor_sample", "tensor_sdiv", "tensor_smin", "tensor_tpu", "tensor_host_timing", "ivf_seg_factor",
- * "ivf_probe_single", "single_fused".  Defaults come from the RK_* environment variables of the same names
+ * "ivf_probe_single", "single_fused", "single_zero_copy".  Defaults come from the RK_* environment variables of the same names
  * (upper case), which are read once, in rk_open — never on the per-call path. */
 int rk_set_option(rk_index *ix, const char *name, int64_t value);
 
@@ -198,6 +198,9 @@ int rk_rescan(rk_scan *sc, const float *q, int32_t q_dim, uint32_t user_id, cons
  *   Exact scans (probes = 0) stand for `ORDER BY distance LIMIT k` (prefilter_role.py:162-172): opts.k IS the limit and
  * the scan ends after k tuples. */
 int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *distance);
+/* Up to max_n consecutive rk_gettuple results in one call (what a harness-side caller wants: `cur.fetchall()` of
+ * prefilter_role.py:172); arrays may be NULL.  Returns the number of tuples written, 0 = exhausted, <0 = error. */
+int rk_gettuple_batch(rk_scan *sc, int max_n, uint64_t *tid, uint32_t *doc, double *distance);
 /* ivfflatendscan (ivfscan.c:394-406). */
 void rk_endscan(rk_scan *sc);
 

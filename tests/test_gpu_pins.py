@@ -466,7 +466,7 @@ def test_single_query_fused_ties_and_fallbacks():
     ds = make_dataset("sift", n=40000, dim=16, rows_per_doc=10, rbac="random", num_users=30, num_roles=8)
     ds["X"][5000:9000] = ds["X"][5000]                       # 4000 identical rows
     ds["X"][20000:20300] = ds["X"][20000]                    # 300 identical rows
-    ix = load_index(ds)
+    ix = load_index(ds, k_max=512)
     ix.finalize()
     users = np.unique(ds["user_roles"][:, 0]).astype(np.uint32)
     for row, k in ((5000, 50), (5000, 100), (20000, 100), (20000, 400), (123, 100)):

@@ -21,6 +21,8 @@ ap.add_argument("--filter", default="bitmask")
 ap.add_argument("--k", type=int, default=100)
 ap.add_argument("--reps", type=int, default=20)
 ap.add_argument("--fused", type=int, default=1)
+ap.add_argument("--zc", type=int, default=1)
+ap.add_argument("--debug", type=int, default=0)
 a = ap.parse_args()
 wl = dict(bench.WORKLOADS[a.workload])
 if a.rows:
@@ -39,9 +41,31 @@ if a.filter == "partition":
     ix.build_role_partitions()
 ix.finalize()
 ix.set_option("single_fused", a.fused)
+ix.set_option("single_zero_copy", a.zc)
+if a.debug:
+    # phase timeline of a few fused launches per case (stderr), L2 flushed
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    Q, _ = bench.make_queries(wl, 4, dev)
+    Qn = Q.cpu().numpy()
+    for sz, us_ in [(0, [0])] + bench.depth_users(ur, dr):
+        f = vr.FILTER_NONE if sz == 0 else (vr.FILTER_BITMASK if a.filter == "bitmask" else vr.FILTER_PARTITION)
+        lay = vr.LAYOUT_ROLE if f == vr.FILTER_PARTITION else 0
+        for mode in ("rotating", "flushed"):
+            for i in range(10):
+                if mode == "flushed":
+                    flush.zero_(); torch.cuda.synchronize()
+                ix.set_option("single_debug", 1 if i >= 8 else 0)
+                if i >= 8:
+                    print(f"--- docs visible {sz} {mode} rep {i}", file=sys.stderr)
+                ix.search_batch(Qn[i % 4:i % 4 + 1], np.array([us_[i % len(us_)]], np.uint32), a.k, filter=f, layout=lay, engine=vr.ENGINE_SCAN)
+    ix.set_option("single_debug", 0)
+    del flush
 flt = vr.FILTER_BITMASK if a.filter == "bitmask" else vr.FILTER_PARTITION
 lay = 0 if a.filter == "bitmask" else vr.LAYOUT_ROLE
 res = bench.single_query_legs(ix, wl, ur, dr, dev, a.k, flt, lay, reps=a.reps)
 for leg in res["legs"]:
     print(json.dumps(leg))
+    print("%-52s roof %6.1f | rotating dev %6.1f e2e %6.1f rescan %6.1f | flushed dev %6.1f e2e %6.1f rescan %6.1f" % (
+        leg["case"][:52], leg["roofline_us"], leg["rotating"]["device_us"], leg["rotating"]["e2e_us"], leg["rotating"]["rescan_gettuple_us"],
+        leg["flushed"]["device_us"], leg["flushed"]["e2e_us"], leg["flushed"]["rescan_gettuple_us"]), file=sys.stderr)
 ix.close()

@@ -58,6 +58,7 @@ SIGNATURES = {
     "rk_beginscan": (_P, [_P]),
     "rk_rescan": (C.c_int, [_P, _P, C.c_int32, C.c_uint32, C.POINTER(RkScanOpts)]),
     "rk_gettuple": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]),
+    "rk_gettuple_batch": (C.c_int, [_P, C.c_int, _P, _P, _P]),
     "rk_endscan": (None, [_P]),
     "rk_search_batch": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_search_batch_device": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),

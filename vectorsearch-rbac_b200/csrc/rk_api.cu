@@ -108,6 +108,12 @@ void Workspace::destroy()
     fused_plans.clear();
     fz_ctl.release(); fz_key.release(); fz_row.release(); fz_pack.release();
     h_fz.release();
+    if (h_dbg) cudaFreeHost(h_dbg);
+    h_dbg = nullptr;
+    d_dbg.release();
+    if (h_zc) cudaFreeHost(h_zc);
+    h_zc = d_zc = nullptr;
+    zc_cap = 0;
     DevBuf *bufs[] = {&qflag, &segs, &order, &ctl, &cand_key, &cand_tid, &cand_row, &cand_count, &qseg, &qmask, &dq, &out_tid,
                       &out_doc, &out_dist, &out_count, &probe_key, &probe_list, &ex_key, &ex_tid, &ex_doc};
     for (auto *b : bufs) b->release();
@@ -173,6 +179,8 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
         t.single_fused = env_int("RK_SINGLE_FUSED", 1);
+        t.single_zero_copy = env_int("RK_SINGLE_ZERO_COPY", 1);
+        t.single_debug = env_int("RK_SINGLE_DEBUG", 0);
     }
     if (ix->ws.init(cfg->device) != 0) { delete ix; return nullptr; }
     return ix;
@@ -195,6 +203,8 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
     else if (!strcmp(name, "single_fused")) t.single_fused = v;
+    else if (!strcmp(name, "single_zero_copy")) t.single_zero_copy = v;
+    else if (!strcmp(name, "single_debug")) t.single_debug = v;
     else return rk_fail(RK_ERR_INVALID, "rk_set_option: unknown option \"%s\"", name);
     return RK_OK;
 }

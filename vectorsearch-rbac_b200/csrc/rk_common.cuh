@@ -84,7 +84,9 @@ struct RkScanParams {
     int fused;
     uint32_t nseg_val;              // number of segments when nseg_ptr is NULL
     int fz_cap;                     // entries one CTA may hand over
-    uint32_t *fz_ctl;               // [0] entries handed over, [1] CTAs done (both 0 between launches)
+    int fz_r;                       // rows a CTA vouches for in the cooperative threshold (about 3k / grid)
+    uint32_t *fz_ctl;               // [0] entries handed over, [1] CTAs done, [2] segment counter, [4] rows vouched for (low
+                                    // half) | CTAs reported (high half), [6] largest r-th key (all 0 between launches)
     uint32_t *fz_key;               // [grid * fz_cap]
     uint32_t *fz_row;
     const uint32_t *fz_doc_ids;     // dense document -> raw id
@@ -93,6 +95,12 @@ struct RkScanParams {
     double *fz_out_dist;
     float *fz_out_key;
     int32_t *fz_out_count;          // [0] tuples returned; -1 = the merge could not finish (too many ties): rerun unfused
+    // Zero-copy hand-shake with the host (query and outputs live in mapped pinned host memory): the query is read straight
+    // from the host buffer by the consumer warps, and once the outputs are written and fenced system-wide the last thread
+    // stores fz_seq to *fz_flag, which the host polls — no cudaMemcpy and no stream synchronisation on the call path.
+    uint32_t *fz_flag;
+    uint32_t fz_seq;
+    unsigned long long *fz_dbg;     // tuning aid (option single_debug): [grid + 1][8] globaltimer stamps of the launch's phases
 };
 
 struct RkSelectParams {
@@ -216,8 +224,22 @@ __host__ __device__ __forceinline__ float rk_key_to_float(uint32_t k)
 }
 
 #ifdef __CUDACC__
+__device__ __forceinline__ unsigned long long rk_globaltimer()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers: mbarrier + 1-D bulk async copy (TMA unit, SASS UBLKCP)
+
+__device__ __forceinline__ uint32_t rk_ld_volatile_u32(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 __device__ __forceinline__ uint32_t rk_smem_u32(const void *p)
 {

@@ -56,7 +56,8 @@ struct PinBuf {
 struct FusedPlan {
     DevBuf buf;                 // [segments][role mask]
     uint32_t nseg = 0;
-    size_t off_qmask = 0;
+    size_t off_qmask = 0, off_xrow = 0, off_xvstart = 0;
+    bool private_extents = false;   // the plan carries its own extent table: only the documents the role set may see
     uint64_t rows_scanned = 0, algo_bytes = 0;   // algo_bytes without the 12k output term
 };
 
@@ -78,6 +79,12 @@ struct Workspace {
     std::unordered_map<uint64_t, FusedPlan> fused_plans;
     DevBuf fz_ctl, fz_key, fz_row, fz_pack;   // control words, flat hand-over list, packed outputs [count | tid | dist | doc | key]
     PinBuf h_fz;                              // pinned staging: query in, packed outputs back
+    // zero-copy variant: one MAPPED pinned buffer [flag | packed outputs | query] the kernel reads / writes directly
+    unsigned char *h_zc = nullptr, *d_zc = nullptr;
+    size_t zc_cap = 0;
+    uint32_t zc_seq = 0;
+    unsigned long long *h_dbg = nullptr;      // pinned [sm + 1][8] phase stamps (option single_debug)
+    DevBuf d_dbg;
     PinBuf h_plan_ring[2], h_out;        // plan staging alternates so the host may run one batch ahead
     cudaEvent_t ring_a[RK_TIMING_RING] = {}, ring_b[RK_TIMING_RING] = {};   // scan-kernel event pairs
     uint64_t ring_n = 0;
@@ -169,6 +176,8 @@ struct RkTuning {
     int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
     int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path
+    int single_debug = 0;        // RK_SINGLE_DEBUG: print the fused launch's phase timeline (globaltimer stamps) to stderr
+    int single_zero_copy = 1;    // RK_SINGLE_ZERO_COPY: 0 = cudaMemcpy in / out + stream sync instead of mapped host memory + flag
 };
 
 struct rk_index {

@@ -8,7 +8,11 @@ int rk_device_sm_count(int device);
 // Pipeline geometry of the scan kernel for a padded dimension.
 void rk_scan_geometry(int dim_pad, int *tile_rows, int *nstages, size_t *smem);
 size_t rk_scan_smem_bytes(int row_bytes, int tile_rows, int nstages);
-cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t stream, int grid_override);
+// inline_q_host != NULL: fused single-query launch whose query (p.row_bytes <= RK_INLINE_Q * 4 bytes, host memory) rides in
+// the kernel parameters
+#define RK_INLINE_Q 1024
+cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t stream, int grid_override,
+                           const float *inline_q_host = nullptr);
 cudaError_t rk_launch_select(const RkSelectParams &p, int nq, cudaStream_t stream);
 
 // small utility kernels (rk_util.cu)

@@ -23,6 +23,8 @@
 #include "rk_select.cuh"
 #include "rk_kernels.h"
 
+#include <cstring>
+
 #define RK_CONS_WARPS 8
 #define RK_CONS_THREADS (RK_CONS_WARPS * 32)
 #define RK_SCAN_THREADS (RK_CONS_THREADS + 32)
@@ -98,7 +100,7 @@ struct RkProducer {
 
     __device__ __forceinline__ void close_tile(uint32_t flags)
     {
-        if (first) {
+        if (first && !p.fused) {
             flags |= RK_FLAG_FIRST;
             if (lane == 0) {
                 rk_bulk_g2s(smem + L.off_qslot + (size_t) stage * p.row_bytes,
@@ -397,6 +399,80 @@ __device__ __forceinline__ uint32_t rk_radix_kth(const uint32_t *key, int n, int
     return prefix;
 }
 
+// Smallest and largest of key[0..n) over the consumer threads (n >= 1).  wsum: 16 words of scratch.  Two barriers.
+template <typename Sync>
+__device__ __forceinline__ void rk_block_minmax(const uint32_t *key, int n, volatile uint32_t *mm, int t, uint32_t *lo_out, uint32_t *hi_out, Sync sync)
+{
+    uint32_t lo = RK_KEY_SENTINEL, hi = 0;
+    for (int i = t; i < n; i += RK_CONS_THREADS) { const uint32_t kv = key[i]; lo = min(lo, kv); hi = max(hi, kv); }
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    sync();
+    if ((t & 31) == 0) { mm[t >> 5] = lo; mm[8 + (t >> 5)] = hi; }
+    sync();
+    lo = mm[0]; hi = mm[8];
+#pragma unroll
+    for (int w = 1; w < RK_CONS_WARPS; w++) { lo = min(lo, mm[w]); hi = max(hi, mm[8 + w]); }
+    *lo_out = lo; *hi_out = hi;
+}
+
+// k-th smallest (1-based) of key[0..n), n >= k, for the once-per-launch epilogue: digits of up to 12 bits over
+// `key - min`, starting at the top bit the spread of the keys occupies — one or two passes for a candidate set instead of
+// four 8-bit passes over the full word.  hist: 4096 words (the idle tile ring).
+// loose = true stops as soon as the bin holding the k-th key has at most 64 entries and returns that bin's upper end: at
+// least k keys are <= the result and at most 63 of them exceed the exact k-th — enough for a threshold whose survivors are
+// ordered exactly afterwards.
+template <typename Sync>
+__device__ __forceinline__ uint32_t rk_radix_kth_wide(const uint32_t *key, int n, int k, uint32_t *hist, volatile uint32_t *wsum,
+                                                      volatile uint32_t *sel, volatile uint32_t *mm, int t, Sync sync, bool loose = false)
+{
+    uint32_t lo, hi;
+    rk_block_minmax(key, n, mm, t, &lo, &hi, sync);
+    const uint32_t span = hi - lo;
+    if (span == 0) return lo;
+    const int bits = 32 - __clz(span);
+    uint32_t prefix = 0, kk = (uint32_t) k;
+    int prev = 32;                                   // bits [prev, 32) of key - min are fixed to `prefix` (32 = none yet)
+    int shift = bits > 12 ? bits - 12 : 0;
+#pragma unroll 1
+    for (;;) {
+        const int width = (prev == 32 ? bits : prev) - shift;          // <= 12
+        for (int i = t; i < 4096; i += RK_CONS_THREADS) hist[i] = 0;
+        sync();
+        for (int i = t; i < n; i += RK_CONS_THREADS) {
+            const uint32_t kv = key[i] - lo;
+            if (prev == 32 || (kv >> prev) == (prefix >> prev)) atomicAdd(&hist[(kv >> shift) & ((1u << width) - 1u)], 1u);
+        }
+        sync();
+        uint32_t h[16], c = 0;
+#pragma unroll
+        for (int b_ = 0; b_ < 16; b_++) { h[b_] = hist[t * 16 + b_]; c += h[b_]; }
+        uint32_t tot;
+        const uint32_t incl = rk_block_scan(c, t, wsum, &tot, sync);
+        uint32_t run = incl - c;
+        if (run < kk && kk <= incl) {
+#pragma unroll
+            for (int b_ = 0; b_ < 16; b_++) {
+                if (run < kk && kk <= run + h[b_]) { sel[0] = (uint32_t) (t * 16 + b_); sel[1] = kk - run; mm[0] = h[b_]; }
+                run += h[b_];
+            }
+        }
+        sync();
+        prefix |= sel[0] << shift;
+        kk = sel[1];
+        const uint32_t in_bin = mm[0];
+        sync();
+        if (shift == 0) break;
+        if (loose && in_bin <= 64u) {
+            const uint32_t up = prefix | ((1u << shift) - 1u);      // the bin's largest value
+            return up > span ? hi : up + lo;
+        }
+        prev = shift;
+        shift = shift > 12 ? shift - 12 : 0;
+    }
+    return prefix + lo;
+}
+
 // Keep the entries of (key,row)[0..n) with key <= tau, packed to the front (order not preserved
 // across threads' blocks but deterministic).  Returns the number kept.
 template <typename Sync>
@@ -426,8 +502,14 @@ __device__ __forceinline__ int rk_compact_le(RkCandBuf cb, int n, uint32_t tau, 
 
 // ---------------------------------------------------------------------------------------------
 
+// The query of a fused single-query launch rides in the kernel parameters (constant bank): it arrives with the launch
+// command itself, so a call needs no host->device copy at all.  Rows of up to RK_INLINE_Q floats.
+struct RkInlineQuery {
+    float v[RK_INLINE_Q];
+};
+
 template <int METRIC, bool WIDE>
-__global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkScanParams p)
+__device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float *inline_q)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const RkScanSmem L = rk_scan_smem_layout(p.row_bytes, p.tile_rows, p.nstages);
@@ -462,10 +544,10 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
                       rk_policy_evict_last()};
         auto seg_at = [&](uint32_t pos) -> uint32_t { return p.seg_order ? p.seg_order[pos] : pos; };
         // claim two segments ahead: the next descriptor is loaded while the current one streams
-        uint32_t sid0 = 0, sid1 = 0;
-        if (lane == 0) { sid0 = atomicAdd(p.seg_counter, 1u); sid1 = atomicAdd(p.seg_counter, 1u); }
-        sid0 = __shfl_sync(0xffffffffu, sid0, 0);
-        sid1 = __shfl_sync(0xffffffffu, sid1, 0);
+        // (the first two positions of every CTA are static — b and b + grid — so no atomic round trip sits before the first
+        // row is requested; the shared counter hands out the positions from 2 * grid on)
+        const uint32_t sid_dyn0 = 2u * gridDim.x;
+        uint32_t sid0 = blockIdx.x, sid1 = blockIdx.x + gridDim.x;
         RkSegment cur;
         uint32_t cur_id = 0, nxt_id = 0;
         if (sid0 < nseg) { cur_id = seg_at(sid0); cur = p.segs[cur_id]; }
@@ -475,7 +557,7 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
             if (sid1 < nseg) {
                 nxt_id = seg_at(sid1);
                 nxt = p.segs[nxt_id];
-                if (lane == 0) sid2 = atomicAdd(p.seg_counter, 1u);
+                if (lane == 0) sid2 = sid_dyn0 + atomicAdd(p.seg_counter, 1u);
             } else {
                 sid2 = sid1;
             }
@@ -512,12 +594,29 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     // k-th key": fall back to the exact (key, tid) sort that keeps precisely k
     const int tie_limit = p.k + ((int) trigger - p.k) / 2;
 
+    unsigned long long *dbg = p.fused && p.fz_dbg ? p.fz_dbg + (size_t) blockIdx.x * 8 : nullptr;
+    if (dbg && t == 0) dbg[0] = rk_globaltimer();                   // CTA start
+    bool dbg_first = dbg != nullptr;
+    if (p.fused) {
+        // one query for the whole launch: the consumers fetch it themselves — from the kernel parameters when it rides
+        // there, else from HBM — while the producer resolves its first extents
+        float4 *qd = reinterpret_cast<float4 *>(smem + L.off_qcur);
+        if (inline_q) {
+            const float4 *q4 = reinterpret_cast<const float4 *>(inline_q);
+            for (int i = t; i < p.dim4; i += RK_CONS_THREADS) qd[i] = q4[i];
+        } else {
+            const float4 *q4 = reinterpret_cast<const float4 *>(p.q);
+            for (int i = t; i < p.dim4; i += RK_CONS_THREADS) qd[i] = __ldcv(&q4[i]);
+        }
+        csync();
+    }
     int stage = 0;
     uint32_t phase = 0;
     int since_ckpt = 0;
     for (;;) {
         rk_mbar_wait(&full[stage], phase);
         const RkStageMeta m = meta[stage];
+        if (dbg_first && t == 0) { dbg[1] = rk_globaltimer(); dbg_first = false; }       // first tile landed
         if (m.flags & RK_FLAG_END) break;
         if (m.flags & RK_FLAG_FIRST) {
             // Every warp copies the segment's query for itself (identical values from all warps).
@@ -649,11 +748,44 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     if (!p.fused) return;
 
     // ===================== fused single-query epilogue =====================
-    // (1) this CTA's k best candidates (threshold only, no order) go to the flat global list.
+    // (1) Cooperative threshold.  Every CTA publishes the r-th smallest key it found (r ~ 3k / grid): B = the largest such
+    // key over the CTAs that have reported and S = how many rows those CTAs vouch for (r each).  As soon as S >= k, at least k
+    // rows of the query have a key <= B, so nothing above B can be in the answer and each CTA hands over only its
+    // candidates <= B — a few dozen entries in all instead of k per CTA, which is what makes the last CTA's merge short.
+    // Writers update B before S and the reader reads S before B, so any S >= k it sees is covered by the B it reads.  The
+    // wait is bounded (other kernels may hold SMs this grid is waiting for): on timeout, or when every CTA has reported
+    // without reaching k rows, the CTA falls back to handing over its own k best.
     csync();                                  // every warp has left the loop: no append is in flight
+    if (dbg && t == 0) dbg[2] = rk_globaltimer();                   // scan done
+    uint32_t *whist = reinterpret_cast<uint32_t *>(smem + L.off_tiles);     // 4096-bin histogram: the tile ring is idle from here on
+    volatile uint32_t *s_mm = s_count + 16;                                  // [16] min / max scratch
     int n = (int) *s_count;
+    if (gridDim.x > 1) {
+        const int rc_ = n < p.fz_r ? n : p.fz_r;
+        uint32_t vc = 0;
+        if (rc_ == 1) { uint32_t hi_; rk_block_minmax(cb.key, n, s_mm, t, &vc, &hi_, csync); }       // r = 1: the CTA's best key
+        else if (rc_ > 1) vc = rk_radix_kth_wide(cb.key, n, rc_, whist, s_wsum, s_sel, s_mm, t, csync);
+        if (t == 0) {
+            // fz_ctl[4] = rows vouched for (low 16 bits) | CTAs reported (high 16 bits): one atomic publishes both and its
+            // return value is already a snapshot
+            if (rc_ > 0) {
+                atomicMax(&p.fz_ctl[6], vc);
+                __threadfence();
+            }
+            uint32_t sr = atomicAdd(&p.fz_ctl[4], (uint32_t) rc_ | 0x10000u) + ((uint32_t) rc_ | 0x10000u);
+            const unsigned long long t_end = rk_globaltimer() + 20000ull;      // 20 us
+            while ((sr & 0xFFFFu) < (uint32_t) p.k && (sr >> 16) < gridDim.x && rk_globaltimer() <= t_end) sr = rk_ld_volatile_u32(&p.fz_ctl[4]);
+            __threadfence();
+            s_sel[0] = (sr & 0xFFFFu) >= (uint32_t) p.k ? rk_ld_volatile_u32(&p.fz_ctl[6]) : RK_KEY_SENTINEL;
+        }
+        csync();
+        const uint32_t bound = s_sel[0];
+        csync();
+        if (bound != RK_KEY_SENTINEL && n > 0) n = rk_compact_le(cb, n, bound, t, s_wsum, csync);
+    }
+    // (2) at most its k best (threshold only, no order) go to the flat global list
     if (n > p.k) {
-        const uint32_t tau = rk_radix_kth(cb.key, n, p.k, s_hist, s_wsum, s_sel, t, csync);
+        const uint32_t tau = rk_radix_kth_wide(cb.key, n, p.k, whist, s_wsum, s_sel, s_mm, t, csync, true);
         n = rk_compact_le(cb, n, tau, t, s_wsum, csync);
         if (n > p.fz_cap) {
             // more ties at the k-th key than a CTA may hand over: exact (key, tuple id) order keeps precisely k
@@ -662,6 +794,7 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
             n = p.k;
         }
     }
+    if (dbg && t == 0) dbg[3] = rk_globaltimer();                   // local select done
     if (t == 0) s_sel[0] = n ? atomicAdd(&p.fz_ctl[0], (uint32_t) n) : 0u;
     csync();
     {
@@ -675,26 +808,81 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
     csync();
     if (t == 0) s_sel[1] = atomicAdd(&p.fz_ctl[1], 1u);
     csync();
+    if (dbg && t == 0) dbg[4] = rk_globaltimer();                   // handed over
     if (s_sel[1] != gridDim.x - 1) return;
+    dbg = p.fz_dbg ? p.fz_dbg + (size_t) gridDim.x * 8 : nullptr;
+    if (dbg && t == 0) { dbg[0] = rk_globaltimer(); dbg[7] = blockIdx.x; }
 
-    // (2) the last CTA to finish: exact k-th smallest key over everything handed over (4-pass radix select straight from
-    // L2), gather the entries up to it, order them by (key, tuple id), write the answer.
+    // (3) the last CTA to finish selects the answer from everything handed over, orders it by (key, tuple id) and writes it.
     __threadfence();
     const int N = (int) __ldcg(&p.fz_ctl[0]);
+    int m;
+    bool overflow = false;
+    if (N <= RK_CAND_CAP) {
+        // the usual case (the cooperative threshold left a few hundred entries): straight into the candidate buffer, the
+        // CTA's own threshold select over it
+        for (int i = t; i < N; i += RK_CONS_THREADS) { cb.key[i] = __ldcg(&p.fz_key[i]); cb.row[i] = __ldcg(&p.fz_row[i]); }
+        csync();
+        if (dbg && t == 0) { dbg[1] = rk_globaltimer(); dbg[6] = (unsigned long long) N; }
+        m = N;
+        if (m > p.k) {
+            // (a loose threshold will do: the survivors are ordered exactly below)
+            const uint32_t tau = rk_radix_kth_wide(cb.key, m, p.k, whist, s_wsum, s_sel, s_mm, t, csync, true);
+            m = rk_compact_le(cb, m, tau, t, s_wsum, csync);
+        }
+        if (dbg && t == 0) dbg[2] = rk_globaltimer();
+    } else {
     uint32_t kth = RK_KEY_SENTINEL;
+    // The keys are staged ONCE in shared memory — the tile ring is idle by now (every tile was consumed before END) and holds
+    // up to 48 K keys — so the radix passes run from shared memory in compact loops (no instruction-cache-cold unrolled code
+    // on this once-per-launch path).  The select runs over `key - min` and only over the bytes the spread of the keys occupies
+    // (the k best of neighbouring CTAs are close: two or three passes instead of four).  Hand-overs beyond the ring's capacity
+    // (large k with many ties) re-read the keys from L2 on every pass.
+    uint32_t *skeys = reinterpret_cast<uint32_t *>(smem + L.off_tiles);
+    const bool staged = (size_t) N * 4 <= (size_t) L.tile_bytes * (size_t) p.nstages;
+    if (staged) {
+#pragma unroll 8
+        for (int i = t; i < N; i += RK_CONS_THREADS) skeys[i] = __ldcg(&p.fz_key[i]);
+        csync();
+    }
+    if (dbg && t == 0) dbg[1] = rk_globaltimer();                   // keys staged
     if (N > p.k) {
+        uint32_t kmin = 0, span = 0xFFFFFFFFu;
+        if (staged) {
+            uint32_t lo = RK_KEY_SENTINEL, hi = 0;
+            for (int i = t; i < N; i += RK_CONS_THREADS) { const uint32_t kv = skeys[i]; lo = min(lo, kv); hi = max(hi, kv); }
+            lo = __reduce_min_sync(0xffffffffu, lo);
+            hi = __reduce_max_sync(0xffffffffu, hi);
+            if (lane == 0) { s_hist[warp] = lo; s_hist[8 + warp] = hi; }
+            csync();
+            lo = s_hist[0]; hi = s_hist[8];
+#pragma unroll
+            for (int w = 1; w < RK_CONS_WARPS; w++) { lo = min(lo, s_hist[w]); hi = max(hi, s_hist[8 + w]); }
+            csync();
+            kmin = lo;
+            span = hi - lo;
+        }
+        const int npass = span == 0 ? 0 : (39 - __clz(span)) / 8;          // bytes the spread occupies
         uint32_t prefix = 0, mask = 0, kk = (uint32_t) p.k;
 #pragma unroll 1
-        for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int shift = 8 * (npass - 1); shift >= 0; shift -= 8) {
             s_hist[t] = 0;
             csync();
-            for (int i0 = t; i0 < N; i0 += RK_CONS_THREADS * 8) {
-                uint32_t kv[8];
+            if (staged) {
+#pragma unroll 4
+                for (int i = t; i < N; i += RK_CONS_THREADS) {
+                    const uint32_t kv = skeys[i] - kmin;
+                    if ((kv & mask) == prefix) atomicAdd(&s_hist[(kv >> shift) & 255u], 1u);
+                }
+            } else {
+                for (int i0 = t; i0 < N; i0 += RK_CONS_THREADS * 8) {
+                    uint32_t kv[8];
 #pragma unroll
-                for (int j = 0; j < 8; j++) { const int i = i0 + j * RK_CONS_THREADS; kv[j] = i < N ? __ldcg(&p.fz_key[i]) : 0u; }
+                    for (int j = 0; j < 8; j++) { const int i = i0 + j * RK_CONS_THREADS; kv[j] = i < N ? __ldcg(&p.fz_key[i]) : 0u; }
 #pragma unroll
-                for (int j = 0; j < 8; j++)
-                    if (i0 + j * RK_CONS_THREADS < N && (kv[j] & mask) == prefix) atomicAdd(&s_hist[(kv[j] >> shift) & 255u], 1u);
+                    for (int j = 0; j < 8; j++)
+                        if (i0 + j * RK_CONS_THREADS < N && (kv[j] & mask) == prefix) atomicAdd(&s_hist[(kv[j] >> shift) & 255u], 1u);
+                }
             }
             csync();
             const uint32_t c = s_hist[t];
@@ -707,29 +895,42 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
             mask |= 0xFFu << shift;
             kk = s_sel[1];
         }
-        kth = prefix;
+        kth = prefix + kmin;
     }
     if (t == 0) *s_count = 0;
     csync();
-    for (int i0 = t; i0 < N; i0 += RK_CONS_THREADS * 8) {
-        uint32_t kv[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) { const int i = i0 + j * RK_CONS_THREADS; kv[j] = i < N ? __ldcg(&p.fz_key[i]) : RK_KEY_SENTINEL; }
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const int i = i0 + j * RK_CONS_THREADS;
-            if (i < N && kv[j] <= kth) {
+    if (dbg && t == 0) { dbg[2] = rk_globaltimer(); dbg[6] = (unsigned long long) N; }      // k-th key known
+    if (staged) {
+        for (int i = t; i < N; i += RK_CONS_THREADS) {
+            const uint32_t kv = skeys[i];
+            if (kv <= kth) {
                 const uint32_t slot = atomicAdd((uint32_t *) s_count, 1u);
-                if (slot < RK_CAND_CAP) { cb.key[slot] = kv[j]; cb.row[slot] = __ldcg(&p.fz_row[i]); }
+                if (slot < RK_CAND_CAP) { cb.key[slot] = kv; cb.row[slot] = __ldcg(&p.fz_row[i]); }
+            }
+        }
+    } else {
+        for (int i0 = t; i0 < N; i0 += RK_CONS_THREADS * 8) {
+            uint32_t kv[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) { const int i = i0 + j * RK_CONS_THREADS; kv[j] = i < N ? __ldcg(&p.fz_key[i]) : RK_KEY_SENTINEL; }
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int i = i0 + j * RK_CONS_THREADS;
+                if (i < N && kv[j] <= kth) {
+                    const uint32_t slot = atomicAdd((uint32_t *) s_count, 1u);
+                    if (slot < RK_CAND_CAP) { cb.key[slot] = kv[j]; cb.row[slot] = __ldcg(&p.fz_row[i]); }
+                }
             }
         }
     }
     csync();
-    int m = (int) *s_count;
-    const bool overflow = m > RK_CAND_CAP;     // more than RK_CAND_CAP entries tie at the k-th key: the host reruns unfused
+    m = (int) *s_count;
+    overflow = m > RK_CAND_CAP;                // more than RK_CAND_CAP entries tie at the k-th key: the host reruns unfused
     if (overflow) m = 0;
+    }
     for (int i = t; i < m; i += RK_CONS_THREADS) cb.tid[i] = p.store.tid[cb.row[i]];
     csync();
+    if (dbg && t == 0) dbg[3] = rk_globaltimer();                   // gathered, tuple ids fetched
     const int cnt = overflow ? 0 : (m < p.k ? m : p.k);
     auto emit = [&](int r, uint32_t key, uint32_t row, uint64_t tid) {
         const float ord = rk_key_to_float(key);
@@ -744,7 +945,12 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
             const uint32_t ki = cb.key[i];
             const uint64_t ti = cb.tid[i];
             int r = 0;
-            for (int j = 0; j < m; j++) r += rk_cand_less(cb.key[j], cb.tid[j], ki, ti) ? 1 : 0;
+            // (identical (key, tuple id) pairs — the ground-truth merge keeps duplicates — rank by position)
+            for (int j = 0; j < m; j++) {
+                const uint32_t kj = cb.key[j];
+                const uint64_t tj = cb.tid[j];
+                r += (rk_cand_less(kj, tj, ki, ti) || (kj == ki && tj == ti && j < i)) ? 1 : 0;
+            }
             if (r < cnt) emit(r, ki, cb.row[i], ti);
         }
     } else {
@@ -762,8 +968,29 @@ __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkSca
         // ready for the next launch: nothing is uploaded per call but the query
         p.fz_ctl[0] = 0;
         p.fz_ctl[1] = 0;
+        p.fz_ctl[4] = 0;
+        p.fz_ctl[6] = 0;
         *p.seg_counter = 0;
     }
+    if (dbg && t == 0) dbg[4] = rk_globaltimer();                   // outputs written
+    if (p.fz_flag) {
+        __threadfence_system();                 // every thread's outputs are visible to the host ...
+        csync();
+        if (t == 0) *reinterpret_cast<volatile uint32_t *>(p.fz_flag) = p.fz_seq;      // ... before it sees the flag
+    }
+}
+
+template <int METRIC, bool WIDE>
+__global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkScanParams p)
+{
+    rk_scan_body<METRIC, WIDE>(p, nullptr);
+}
+
+template <int METRIC, bool WIDE>
+__global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_single_kernel(const __grid_constant__ RkScanParams p,
+                                                                            const __grid_constant__ RkInlineQuery iq)
+{
+    rk_scan_body<METRIC, WIDE>(p, iq.v);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -801,11 +1028,27 @@ void rk_scan_geometry(int dim_pad, int *tile_rows, int *nstages, size_t *smem)
     *smem = rk_scan_smem_bytes(row_bytes, tr, ns);
 }
 
-cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t stream, int grid_override)
+cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t stream, int grid_override, const float *inline_q_host)
 {
     const size_t smem = rk_scan_smem_bytes(p.row_bytes, p.tile_rows, p.nstages);
-    static bool attr_set[64][4];
+    static bool attr_set[64][8];
     const bool wide = p.tile_rows < 64;
+    const int grid = grid_override > 0 ? grid_override : rk_device_sm_count(device);
+    if (inline_q_host) {
+        // fused single-query launch with the query in the parameters
+        auto kern = wide ? (p.metric == 0 ? rk_scan_single_kernel<0, true> : rk_scan_single_kernel<1, true>)
+                         : (p.metric == 0 ? rk_scan_single_kernel<0, false> : rk_scan_single_kernel<1, false>);
+        const int ai = 4 | (p.metric & 1) | (wide ? 2 : 0);
+        if (!attr_set[device & 63][ai]) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_set[device & 63][ai] = true;
+        }
+        RkInlineQuery iq;
+        memcpy(iq.v, inline_q_host, (size_t) p.row_bytes);
+        kern<<<grid, RK_SCAN_THREADS, smem, stream>>>(p, iq);
+        return cudaGetLastError();
+    }
     auto kern = wide ? (p.metric == 0 ? rk_scan_kernel<0, true> : rk_scan_kernel<1, true>)
                      : (p.metric == 0 ? rk_scan_kernel<0, false> : rk_scan_kernel<1, false>);
     const int ai = (p.metric & 1) | (wide ? 2 : 0);
@@ -814,7 +1057,6 @@ cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t strea
         if (e != cudaSuccess) return e;
         attr_set[device & 63][ai] = true;
     }
-    int grid = grid_override > 0 ? grid_override : rk_device_sm_count(device);
     kern<<<grid, RK_SCAN_THREADS, smem, stream>>>(p);
     return cudaGetLastError();
 }

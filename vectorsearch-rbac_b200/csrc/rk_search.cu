@@ -9,6 +9,7 @@
 //                                 (load_result_to_database.py:591-622)
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 
 #include "rk_host.h"
@@ -119,6 +120,30 @@ static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std
     return 0;
 }
 
+// Cuts one partition (extent table P) into segments of about `target` rows, appended to segs.
+static void segments_of_part(const PartInfo &P, uint32_t flags, uint64_t rows_est, uint32_t q, uint64_t target, bool merge_ok,
+                             std::vector<RkSegment> &segs)
+{
+    uint64_t nchunks = (rows_est + target - 1) / target;
+    if (nchunks < 1) nchunks = 1;
+    if (nchunks > P.rows) nchunks = P.rows;
+    for (uint64_t c = 0; c < nchunks; c++) {
+        RkSegment s;
+        s.query = q; s.kind = RK_SEG_EXTENTS;
+        s.flags = (uint16_t) (flags | (merge_ok ? RK_SEGF_MERGE_OK : 0u));
+        s.begin = P.rows * c / nchunks;
+        s.end = P.rows * (c + 1) / nchunks;
+        if (s.end <= s.begin) continue;
+        // extents [lo, hi) of the partition intersect virtual rows [begin, end)
+        const auto vb = P.vstart.begin(), ve = P.vstart.end();
+        const uint32_t lo = (uint32_t) (std::upper_bound(vb, ve, (uint32_t) s.begin) - vb) - 1;
+        const uint32_t hi = (uint32_t) (std::lower_bound(vb, ve, (uint32_t) s.end) - vb);
+        s.ext_lo = P.ext_off + lo;
+        s.ext_hi = P.ext_off + hi;
+        segs.push_back(s);
+    }
+}
+
 // Cuts the partitions one query walks into segments of about `target` rows (appended to segs); returns the extent /
 // mask bytes the plan makes the producer read (SURVEY.md §8(d) "M").
 static uint64_t append_segments(const rk_index *ix, const std::vector<PlanItem> &items, uint32_t q, uint64_t target,
@@ -128,24 +153,7 @@ static uint64_t append_segments(const rk_index *ix, const std::vector<PlanItem> 
     uint64_t mask_bytes = 0;
     for (auto &pi : items) {
         const PartInfo &P = ix->parts[pi.part];
-        uint64_t nchunks = (pi.rows_est + target - 1) / target;
-        if (nchunks < 1) nchunks = 1;
-        if (nchunks > P.rows) nchunks = P.rows;
-        for (uint64_t c = 0; c < nchunks; c++) {
-            RkSegment s;
-            s.query = q; s.kind = RK_SEG_EXTENTS;
-            s.flags = (uint16_t) (pi.flags | (items.size() == 1 ? RK_SEGF_MERGE_OK : 0u));
-            s.begin = P.rows * c / nchunks;
-            s.end = P.rows * (c + 1) / nchunks;
-            if (s.end <= s.begin) continue;
-            // extents [lo, hi) of the partition intersect virtual rows [begin, end)
-            const auto vb = P.vstart.begin(), ve = P.vstart.end();
-            const uint32_t lo = (uint32_t) (std::upper_bound(vb, ve, (uint32_t) s.begin) - vb) - 1;
-            const uint32_t hi = (uint32_t) (std::lower_bound(vb, ve, (uint32_t) s.end) - vb);
-            s.ext_lo = P.ext_off + lo;
-            s.ext_hi = P.ext_off + hi;
-            segs.push_back(s);
-        }
+        segments_of_part(P, pi.flags, pi.rows_est, q, target, items.size() == 1, segs);
         if (pi.flags & RK_SEGF_MASKED) mask_bytes += (uint64_t) P.n_ext * (8ull * W + 8);
     }
     return mask_bytes;
@@ -322,7 +330,7 @@ void rk_fill_scan_params(const rk_index *ix, const Workspace &ws, RkScanParams &
 // layout), kept in HBM, and a call uploads nothing but its query.  Returns 1 when the call was served, 0 when this path
 // does not apply (a user with several partitions needs the dedup merge), < 0 on error.
 static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, const uint32_t *user_ids, const rk_scan_opts *o,
-                               const RkSelectParams &out, int32_t *d_count)
+                               const RkSelectParams &out, int32_t *d_count, uint32_t *d_flag, uint32_t seq, const float *inline_q_host)
 {
     const UserInfo *u = nullptr;
     if (user_ids) {
@@ -356,19 +364,65 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
         const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4, sm = (uint64_t) ix->sm_count;
         const double t_cta_us = (double) total_rows * (double) row_bytes / (double) sm / 44.0e3;
         double per_cta = std::sqrt(t_cta_us / 2.0);
-        per_cta = std::min(32.0, std::max(1.0, per_cta));
-        uint64_t target = (uint64_t) ((double) total_rows / ((double) sm * per_cta)) + 1;
+        per_cta = std::min(32.0, std::max(1.0, std::floor(per_cta + 0.5)));
+        // a whole number of equal segments per CTA: with one partition every CTA then streams the same number of rows and
+        // the grid drains together (one segment more on some CTAs is a tail as long as a segment)
+        uint64_t target = (total_rows + (uint64_t) (sm * per_cta) - 1) / (uint64_t) (sm * per_cta);
         target = std::max<uint64_t>(target, (uint64_t) ix->tile_rows);
         std::vector<RkSegment> segs;
-        const uint64_t mask_bytes = append_segments(ix, items, 0u, target, segs);
+        uint64_t mask_bytes = 0;
+        bool any_masked = false;
+        for (auto &pi : items) any_masked |= (pi.flags & RK_SEGF_MASKED) != 0;
+        // A plan that would test role masks per extent (the bitmask filter walks the table of ALL documents; impure dynamic
+        // partitions) gets a PRIVATE extent table instead: only the documents this role set may see, physically adjacent
+        // ones fused.  The plan is cached, so the mask test runs once per role set on the host and the kernel's producer
+        // resolves a few thousand visible extents instead of testing every document of the corpus per query.
+        std::vector<uint32_t> x_row, x_vstart;
+        if (any_masked) {
+            const int W = ix->mask_words;
+            for (auto &pi : items) {
+                const PartInfo &P = ix->parts[pi.part];
+                const bool masked = (pi.flags & RK_SEGF_MASKED) != 0;
+                PartInfo T;
+                T.ext_off = (uint32_t) x_row.size();
+                uint64_t v = 0, run_end = ~0ull;
+                for (uint32_t d : P.docs) {
+                    if (masked) {
+                        uint64_t acc = 0;
+                        for (int w = 0; w < W; w++) acc |= ix->doc_mask[(size_t) d * W + w] & (u ? u->mask[(size_t) w] : 0ull);
+                        if (!acc) continue;
+                    }
+                    const uint64_t r0 = ix->doc_row_start[d], r1 = ix->doc_row_start[d + 1];
+                    if (r1 == r0) continue;
+                    if (r0 != run_end) { x_row.push_back((uint32_t) r0); x_vstart.push_back((uint32_t) v); T.vstart.push_back((uint32_t) v); }
+                    v += r1 - r0;
+                    run_end = r1;
+                }
+                T.vstart.push_back((uint32_t) v);
+                T.n_ext = (uint32_t) T.vstart.size() - 1;
+                T.rows = v;
+                x_row.push_back(0u); x_vstart.push_back((uint32_t) v);        // sentinel, as in the index-wide tables
+                if (v) segments_of_part(T, 0u, v, 0u, target, items.size() == 1, segs);
+                mask_bytes += (uint64_t) T.n_ext * 8ull;
+            }
+        } else {
+            mask_bytes = append_segments(ix, items, 0u, target, segs);
+        }
         FusedPlan fp;
         fp.nseg = (uint32_t) segs.size();
         const int W = ix->mask_words;
         const size_t b_segs = segs.size() * sizeof(RkSegment);
         fp.off_qmask = (b_segs + 15) & ~(size_t) 15;
-        std::vector<unsigned char> host(fp.off_qmask + (size_t) W * 8, 0);
+        fp.off_xrow = (fp.off_qmask + (size_t) W * 8 + 15) & ~(size_t) 15;
+        fp.off_xvstart = fp.off_xrow + ((x_row.size() * 4 + 15) & ~(size_t) 15);
+        fp.private_extents = any_masked;
+        std::vector<unsigned char> host(fp.off_xvstart + x_vstart.size() * 4 + 16, 0);
         if (b_segs) memcpy(host.data(), segs.data(), b_segs);
         for (int w = 0; w < W; w++) reinterpret_cast<uint64_t *>(host.data() + fp.off_qmask)[w] = u ? u->mask[(size_t) w] : 0ull;
+        if (!x_row.empty()) {
+            memcpy(host.data() + fp.off_xrow, x_row.data(), x_row.size() * 4);
+            memcpy(host.data() + fp.off_xvstart, x_vstart.data(), x_vstart.size() * 4);
+        }
         if (fp.buf.ensure(host.size()) != 0) return RK_ERR_CUDA;
         RK_CUDA(cudaMemcpyAsync(fp.buf.p, host.data(), host.size(), cudaMemcpyHostToDevice, ws.stream));
         RK_CUDA(cudaStreamSynchronize(ws.stream));                      // `host` goes out of scope
@@ -387,6 +441,8 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
     ckpt = std::max(1, std::min(16, ckpt));
     const int trigger = 2048 - ckpt * ix->tile_rows;
     p.fz_cap = k + (trigger - k) / 2;
+    // rows a CTA vouches for: the bound is valid once r x (CTAs reported) >= k; about three quarters of the grid should do
+    p.fz_r = std::max(1, (4 * k + 3 * grid - 1) / (3 * grid));
     if (ws.fz_ctl.p == nullptr) {
         if (ws.fz_ctl.ensure(64) != 0) return RK_ERR_CUDA;
         RK_CUDA(cudaMemsetAsync(ws.fz_ctl.p, 0, 64, ws.stream));
@@ -399,6 +455,11 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
     p.nseg_ptr = nullptr;
     p.nseg_val = fp.nseg;
     p.qmask = reinterpret_cast<const uint64_t *>(fp.buf.as<unsigned char>() + fp.off_qmask);
+    if (fp.private_extents) {
+        p.ext_row = reinterpret_cast<const uint32_t *>(fp.buf.as<unsigned char>() + fp.off_xrow);
+        p.ext_vstart = reinterpret_cast<const uint32_t *>(fp.buf.as<unsigned char>() + fp.off_xvstart);
+        p.ext_mask = nullptr;
+    }
     p.seg_counter = ws.fz_ctl.as<uint32_t>() + 2;
     p.fz_ctl = ws.fz_ctl.as<uint32_t>();
     p.fz_key = ws.fz_key.as<uint32_t>();
@@ -406,10 +467,19 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
     p.fz_doc_ids = ix->d_doc_ids.as<uint32_t>();
     p.fz_out_tid = out.out_tid; p.fz_out_doc = out.out_doc; p.fz_out_dist = out.out_dist; p.fz_out_key = out.out_key;
     p.fz_out_count = d_count;
+    p.fz_flag = d_flag;
+    p.fz_seq = seq;
+    if (ix->tune.single_debug) {
+        const size_t db = (size_t) (ix->sm_count + 1) * 64;
+        if (!ws.h_dbg) RK_CUDA(cudaHostAlloc((void **) &ws.h_dbg, db, cudaHostAllocDefault));
+        if (ws.d_dbg.ensure(db) != 0) return RK_ERR_CUDA;
+        RK_CUDA(cudaMemsetAsync(ws.d_dbg.p, 0, db, ws.stream));
+        p.fz_dbg = ws.d_dbg.as<unsigned long long>();
+    }
     p.cand_key = nullptr; p.cand_tid = nullptr; p.cand_row = nullptr; p.cand_count = nullptr;
     const int slot = (int) (ws.ring_n % RK_TIMING_RING);
     if (ws.timing) RK_CUDA(cudaEventRecord(ws.ring_a[slot], ws.stream));
-    RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid));
+    RK_CUDA(rk_launch_scan(p, ix->device, ws.stream, grid, inline_q_host));
     if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot], ws.stream)); ws.timed_scan = true; ws.ring_n++; }
     ws.launches = 1;
     ws.single_fused = true;
@@ -542,8 +612,11 @@ static int stage_queries(rk_index *ix, Workspace &ws, size_t nq, const float *Q)
     return 0;
 }
 
-// The single-query host path: pinned staging in both directions, ONE host->device copy (the query), ONE launch, ONE
-// device->host copy (count | tid | dist | doc | key, packed).  Returns 1 = served, 0 = not applicable, < 0 = error.
+// The single-query host path.  Zero-copy (default): the query and the packed outputs live in ONE mapped pinned host
+// buffer that the kernel reads and writes directly; the call is a memcpy of the query, one launch and a poll of the
+// completion flag the kernel stores last — no cudaMemcpy, no stream synchronisation.  With single_zero_copy = 0: pinned
+// staging, one host->device copy (the query), one launch, one device->host copy (count | tid | dist | doc | key), sync.
+// Returns 1 = served, 0 = not applicable, < 0 = error.
 static int host_search_single(rk_index *ix, Workspace &ws, const float *Q, const uint32_t *user_ids, const rk_scan_opts *o,
                               uint64_t *out_tid, uint32_t *out_doc, double *out_dist, int32_t *out_count, float *out_key)
 {
@@ -551,13 +624,48 @@ static int host_search_single(rk_index *ix, Workspace &ws, const float *Q, const
     const size_t rb = (size_t) ix->dim_pad * 4;
     const size_t o_tid = 16, o_dist = o_tid + (size_t) k * 8, o_doc = o_dist + (size_t) k * 8, o_key = o_doc + (size_t) k * 4;
     const size_t pack = (o_key + (size_t) k * 4 + 15) & ~(size_t) 15;
-    if (ws.dq.ensure(std::max<size_t>(rb, 16)) != 0 || ws.fz_pack.ensure(pack) != 0 || ws.h_fz.ensure(rb + pack) != 0) return RK_ERR_CUDA;
-    unsigned char *hin = ws.h_fz.as<unsigned char>(), *hout = hin + rb;
     if (!o->null_query && !rk_all_finite(Q, (size_t) ix->dim)) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
-    memcpy(hin, Q, (size_t) ix->dim * 4);
-    if (ix->dim != ix->dim_pad) memset(hin + (size_t) ix->dim * 4, 0, rb - (size_t) ix->dim * 4);
-    RK_CUDA(cudaMemcpyAsync(ws.dq.p, hin, rb, cudaMemcpyHostToDevice, ws.stream));
-    unsigned char *dp = ws.fz_pack.as<unsigned char>();
+    const bool zc = ix->tune.single_zero_copy != 0;
+    // the query rides in the kernel parameters when it fits (no host->device copy at all), else one copy from pinned staging
+    const bool inline_q = ix->dim_pad <= RK_INLINE_Q;
+    unsigned char *hout, *dp;
+    if (zc) {
+        // mapped pinned buffer: [flag (64 B) | packed outputs]
+        const size_t need = 64 + pack;
+        if (need > ws.zc_cap) {
+            RK_CUDA(cudaStreamSynchronize(ws.stream));
+            if (ws.h_zc) cudaFreeHost(ws.h_zc);
+            ws.h_zc = ws.d_zc = nullptr;
+            const size_t want = std::max(need, ws.zc_cap * 2);
+            RK_CUDA(cudaHostAlloc((void **) &ws.h_zc, want, cudaHostAllocMapped | cudaHostAllocPortable));
+            RK_CUDA(cudaHostGetDevicePointer((void **) &ws.d_zc, ws.h_zc, 0));
+            memset(ws.h_zc, 0, want);
+            ws.zc_cap = want;
+            ws.zc_seq = 0;
+        }
+        hout = ws.h_zc + 64;
+        dp = ws.d_zc + 64;
+    } else {
+        if (ws.fz_pack.ensure(pack) != 0 || ws.h_fz.ensure(rb + pack) != 0) return RK_ERR_CUDA;
+        hout = ws.h_fz.as<unsigned char>() + rb;
+        dp = ws.fz_pack.as<unsigned char>();
+    }
+    float qpad[RK_INLINE_Q];
+    const float *q_host = Q;
+    if (inline_q) {
+        if (ix->dim != ix->dim_pad) {
+            memcpy(qpad, Q, (size_t) ix->dim * 4);
+            for (int i = ix->dim; i < ix->dim_pad; i++) qpad[i] = 0.f;
+            q_host = qpad;
+        }
+    } else {
+        if (ws.dq.ensure(std::max<size_t>(rb, 16)) != 0 || ws.h_fz.ensure(rb + pack) != 0) return RK_ERR_CUDA;
+        unsigned char *hin = ws.h_fz.as<unsigned char>();
+        memcpy(hin, Q, (size_t) ix->dim * 4);
+        if (ix->dim != ix->dim_pad) memset(hin + (size_t) ix->dim * 4, 0, rb - (size_t) ix->dim * 4);
+        RK_CUDA(cudaMemcpyAsync(ws.dq.p, hin, rb, cudaMemcpyHostToDevice, ws.stream));
+    }
+    const float *dq = inline_q ? nullptr : ws.dq.as<float>();
     RkSelectParams out;
     memset(&out, 0, sizeof out);
     out.out_tid = reinterpret_cast<uint64_t *>(dp + o_tid);
@@ -569,11 +677,49 @@ static int host_search_single(rk_index *ix, Workspace &ws, const float *Q, const
     ws.single_fused = false;
     ws.timed_scan = ws.timed_select = ws.timed_probe = false;
     if (&ws == &ix->ws) ix->tensor.last_plan = 0;
-    int rc = search_single_fused(ix, ws, ws.dq.as<float>(), user_ids, o, out, reinterpret_cast<int32_t *>(dp));
+    uint32_t seq = 0;
+    uint32_t *dflag = nullptr;
+    if (zc) { seq = ++ws.zc_seq; if (seq == 0) seq = ++ws.zc_seq; dflag = reinterpret_cast<uint32_t *>(ws.d_zc); }
+    int rc = search_single_fused(ix, ws, dq, user_ids, o, out, reinterpret_cast<int32_t *>(dp), dflag, seq, inline_q ? q_host : nullptr);
     if (rc <= 0) return rc;                                 // 0: the general path restages the query on the same stream
-    RK_CUDA(cudaMemcpyAsync(hout, dp, pack, cudaMemcpyDeviceToHost, ws.stream));
-    RK_CUDA(cudaStreamSynchronize(ws.stream));
-    const int32_t cnt = *reinterpret_cast<const int32_t *>(hout);
+    if (zc) {
+        // poll the flag the kernel stores after its outputs are fenced system-wide; every so often make sure the stream
+        // has not died under us (a failed launch never writes the flag)
+        volatile uint32_t *hflag = reinterpret_cast<volatile uint32_t *>(ws.h_zc);
+        for (uint64_t spin = 1; *hflag != seq; spin++) {
+            if ((spin & 0xFFFF) == 0) {
+                const cudaError_t e = cudaStreamQuery(ws.stream);
+                if (e != cudaSuccess && e != cudaErrorNotReady) return rk_fail(RK_ERR_CUDA, "single-query launch failed: %s", cudaGetErrorString(e));
+                if (e == cudaSuccess && *hflag != seq) return rk_fail(RK_ERR_CUDA, "single-query launch finished without signalling");
+            }
+            __builtin_ia32_pause();
+        }
+        std::atomic_thread_fence(std::memory_order_acquire);
+    } else {
+        RK_CUDA(cudaMemcpyAsync(hout, dp, pack, cudaMemcpyDeviceToHost, ws.stream));
+        RK_CUDA(cudaStreamSynchronize(ws.stream));
+    }
+    if (ix->tune.single_debug && ws.h_dbg) {
+        // phase timeline of the launch, microseconds after the earliest CTA start: median / max over the CTAs, then the merge
+        cudaMemcpyAsync(ws.h_dbg, ws.d_dbg.p, (size_t) (ix->sm_count + 1) * 64, cudaMemcpyDeviceToHost, ws.stream);
+        cudaStreamSynchronize(ws.stream);
+        const int G = (int) std::max<uint32_t>(1u, std::min<uint32_t>((uint32_t) ix->sm_count, (uint32_t) ws.segments));
+        unsigned long long t0 = ~0ull;
+        for (int b = 0; b < G; b++) if (ws.h_dbg[b * 8]) t0 = std::min(t0, ws.h_dbg[b * 8]);
+        const char *names[5] = {"start", "first tile", "scan done", "local select", "handed over"};
+        for (int s_ = 0; s_ < 5; s_++) {
+            std::vector<double> v;
+            for (int b = 0; b < G; b++) if (ws.h_dbg[b * 8 + s_]) v.push_back((double) (ws.h_dbg[b * 8 + s_] - t0) * 1e-3);
+            if (v.empty()) continue;
+            std::sort(v.begin(), v.end());
+            fprintf(stderr, "  cta %-13s min %7.2f med %7.2f max %7.2f us\n", names[s_], v.front(), v[v.size() / 2], v.back());
+        }
+        const unsigned long long *m_ = ws.h_dbg + (size_t) G * 8;
+        fprintf(stderr, "  merge (cta %llu, N = %llu): start %7.2f keys %7.2f kth %7.2f gathered %7.2f written %7.2f us\n", m_[7], m_[6],
+                (double) (m_[0] - t0) * 1e-3, (double) (m_[1] - t0) * 1e-3, (double) (m_[2] - t0) * 1e-3, (double) (m_[3] - t0) * 1e-3,
+                (double) (m_[4] - t0) * 1e-3);
+    }
+    const int32_t cnt = *reinterpret_cast<const volatile int32_t *>(hout);
     if (cnt < 0) return 0;                                  // more ties at the k-th key than the fused merge holds: general path
     memcpy(out_tid, hout + o_tid, (size_t) k * 8);
     memcpy(out_dist, hout + o_dist, (size_t) k * 8);
@@ -855,6 +1001,30 @@ extern "C" int rk_gettuple(rk_scan *sc, uint64_t *tid, uint32_t *doc, double *di
     if (distance) *distance = sc->r_dist[sc->r_pos];
     sc->r_pos++;
     return 1;
+}
+
+extern "C" int rk_gettuple_batch(rk_scan *sc, int max_n, uint64_t *tid, uint32_t *doc, double *distance)
+{
+    if (!sc) return rk_fail(RK_ERR_INVALID, "NULL scan");
+    if (max_n < 0) return rk_fail(RK_ERR_INVALID, "rk_gettuple_batch: max_n = %d", max_n);
+    int n = 0;
+    while (n < max_n) {
+        if (sc->bound && sc->r_pos < sc->r_count) {
+            // straight from the ring
+            const int take = std::min(max_n - n, sc->r_count - sc->r_pos);
+            if (tid) memcpy(tid + n, sc->r_tid.data() + sc->r_pos, (size_t) take * 8);
+            if (doc) memcpy(doc + n, sc->r_doc.data() + sc->r_pos, (size_t) take * 4);
+            if (distance) memcpy(distance + n, sc->r_dist.data() + sc->r_pos, (size_t) take * 8);
+            sc->r_pos += take;
+            n += take;
+            continue;
+        }
+        const int rc = rk_gettuple(sc, tid ? tid + n : nullptr, doc ? doc + n : nullptr, distance ? distance + n : nullptr);   // refills
+        if (rc < 0) return rc;
+        if (rc == 0) break;
+        n++;
+    }
+    return n;
 }
 
 extern "C" void rk_endscan(rk_scan *sc)

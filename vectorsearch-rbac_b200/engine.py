@@ -251,6 +251,14 @@ class Scan:
         rc = _check(lib.rk_gettuple(self._h, C.byref(t), C.byref(d), C.byref(x)))
         return (t.value, d.value, x.value) if rc == 1 else None
 
+    def gettuple_batch(self, max_n: int):
+        """Up to max_n tuples in one call: (tid uint64[n], doc uint32[n], distance float64[n]); n == 0 when exhausted."""
+        tid = np.empty(max_n, dtype=np.uint64)
+        doc = np.empty(max_n, dtype=np.uint32)
+        dist = np.empty(max_n, dtype=np.float64)
+        n = _check(lib.rk_gettuple_batch(self._h, max_n, tid.ctypes.data, doc.ctypes.data, dist.ctypes.data))
+        return tid[:n], doc[:n], dist[:n]
+
     def __iter__(self):
         while True:
             r = self.gettuple()
