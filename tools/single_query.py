@@ -23,6 +23,9 @@ ap.add_argument("--reps", type=int, default=20)
 ap.add_argument("--fused", type=int, default=1)
 ap.add_argument("--zc", type=int, default=1)
 ap.add_argument("--debug", type=int, default=0)
+ap.add_argument("--segs", type=int, default=0)
+ap.add_argument("--seed", type=int, default=0)
+ap.add_argument("--seedmin", type=int, default=2048)
 a = ap.parse_args()
 wl = dict(bench.WORKLOADS[a.workload])
 if a.rows:
@@ -42,6 +45,9 @@ if a.filter == "partition":
 ix.finalize()
 ix.set_option("single_fused", a.fused)
 ix.set_option("single_zero_copy", a.zc)
+ix.set_option("single_segs", a.segs)
+ix.set_option("single_seed", a.seed)
+ix.set_option("single_seed_min", a.seedmin)
 if a.debug:
     # phase timeline of a few fused launches per case (stderr), L2 flushed
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
@@ -54,7 +60,7 @@ if a.debug:
             for i in range(10):
                 if mode == "flushed":
                     flush.zero_(); torch.cuda.synchronize()
-                ix.set_option("single_debug", 1 if i >= 8 else 0)
+                ix.set_option("single_debug", a.debug if i >= 8 else 0)
                 if i >= 8:
                     print(f"--- docs visible {sz} {mode} rep {i}", file=sys.stderr)
                 ix.search_batch(Qn[i % 4:i % 4 + 1], np.array([us_[i % len(us_)]], np.uint32), a.k, filter=f, layout=lay, engine=vr.ENGINE_SCAN)

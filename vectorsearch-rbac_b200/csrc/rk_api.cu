@@ -180,6 +180,9 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
         t.single_fused = env_int("RK_SINGLE_FUSED", 1);
         t.single_zero_copy = env_int("RK_SINGLE_ZERO_COPY", 1);
+        t.single_segs = env_int("RK_SINGLE_SEGS", 0);
+        t.single_seed = env_int("RK_SINGLE_SEED", 0);
+        t.single_seed_min = env_int("RK_SINGLE_SEED_MIN", 2048);
         t.single_debug = env_int("RK_SINGLE_DEBUG", 0);
     }
     if (ix->ws.init(cfg->device) != 0) { delete ix; return nullptr; }
@@ -204,6 +207,9 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
     else if (!strcmp(name, "single_fused")) t.single_fused = v;
     else if (!strcmp(name, "single_zero_copy")) t.single_zero_copy = v;
+    else if (!strcmp(name, "single_segs")) t.single_segs = v;
+    else if (!strcmp(name, "single_seed")) t.single_seed = v;
+    else if (!strcmp(name, "single_seed_min")) t.single_seed_min = v;
     else if (!strcmp(name, "single_debug")) t.single_debug = v;
     else return rk_fail(RK_ERR_INVALID, "rk_set_option: unknown option \"%s\"", name);
     return RK_OK;

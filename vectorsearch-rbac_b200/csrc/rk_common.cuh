@@ -85,6 +85,7 @@ struct RkScanParams {
     uint32_t nseg_val;              // number of segments when nseg_ptr is NULL
     int fz_cap;                     // entries one CTA may hand over
     int fz_r;                       // rows a CTA vouches for in the cooperative threshold (about 3k / grid)
+    int fz_seed;                    // > 0: the first compaction of a CTA runs as soon as it holds this many candidates
     uint32_t *fz_ctl;               // [0] entries handed over, [1] CTAs done, [2] segment counter, [4] rows vouched for (low
                                     // half) | CTAs reported (high half), [6] largest r-th key (all 0 between launches)
     uint32_t *fz_key;               // [grid * fz_cap]

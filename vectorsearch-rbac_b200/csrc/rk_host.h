@@ -177,6 +177,9 @@ struct RkTuning {
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
     int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path
     int single_debug = 0;        // RK_SINGLE_DEBUG: print the fused launch's phase timeline (globaltimer stamps) to stderr
+    int single_segs = 0;         // RK_SINGLE_SEGS: segments per CTA of a fused single-query plan (0 = chosen from the scan length)
+    int single_seed = 0;         // RK_SINGLE_SEED: candidates a CTA of a long fused scan holds before its first compaction (0 = off)
+    int single_seed_min = 2048;  // RK_SINGLE_SEED_MIN: ... for plans with at least this many rows per CTA
     int single_zero_copy = 1;    // RK_SINGLE_ZERO_COPY: 0 = cudaMemcpy in / out + stream sync instead of mapped host memory + flag
 };
 

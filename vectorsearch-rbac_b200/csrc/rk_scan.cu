@@ -154,11 +154,37 @@ struct RkProducer {
         return acc != 0;
     }
 
-    __device__ void run_segment(const RkSegment &s)
+    // row / virtual offsets of one resolve step (RK_EPL extents per lane)
+    struct ExtStep { uint32_t vs[RK_EPL], ve[RK_EPL], er[RK_EPL]; };
+    int dbg_n;
+    __device__ __forceinline__ void stamp()
+    {
+        if (p.fused && p.fz_dbg && blockIdx.x == 0 && lane == 0 && dbg_n < 256) p.fz_dbg[(size_t) (gridDim.x + 1) * 8 + 256 + dbg_n++] = rk_globaltimer();
+    }
+    ExtStep pre;            // first step of the next segment, requested while the previous segment's last rows were issued
+    bool pre_valid;
+
+    __device__ __forceinline__ void ext_load(const RkSegment &s, uint32_t eb, ExtStep &x) const
+    {
+        // unconditional, independent loads (indices clamped): one memory round trip per step, not one per extent
+#pragma unroll
+        for (int j = 0; j < RK_EPL; j++) {
+            const uint32_t e = eb + j * 32 + lane;
+            const uint32_t ec = e < s.ext_hi ? e : s.ext_hi - 1;
+            x.vs[j] = rk_ld_u32_hint(p.ext_vstart + ec, pol_keep);
+            x.ve[j] = rk_ld_u32_hint(p.ext_vstart + ec + 1, pol_keep);
+            x.er[j] = rk_ld_u32_hint(p.ext_row + ec, pol_keep);
+        }
+    }
+
+    // `next`: the segment this CTA runs after `s` (nullptr = none)
+    __device__ __forceinline__ void run_segment(const RkSegment &s, const RkSegment *next)
     {
         query = s.query;
         first = true;
+        stamp();
         open_tile();
+        stamp();
         if (s.kind == RK_SEG_ROWS) {
             emit_run(s.begin, s.end - s.begin);
         } else if (s.kind == RK_SEG_IVFQ) {
@@ -206,16 +232,25 @@ struct RkProducer {
             if (run_end > run_begin) emit_run(run_begin, run_end - run_begin);
         } else if (s.kind == RK_SEG_EXTENTS) {
             // Partition = table of per-document extents; the host resolved which extents touch
-            // [begin, end).  RK_EPL * 32 extents are resolved per step: every lane first tests the
-            // role masks of its RK_EPL extents and fetches their row / virtual offsets (all loads
-            // independent); allowed extents are streamed in order and physically adjacent ones are
-            // fused into one longer copy.
+            // [begin, end).  RK_EPL * 32 extents are resolved per step: every lane fetches the row / virtual offsets of its
+            // RK_EPL extents (all loads independent) and tests their role masks; allowed extents are streamed in order and
+            // physically adjacent ones are fused into one longer copy.  The offsets of the NEXT step — the first step of the
+            // next segment when this one ends — are requested before the current step's rows are issued, so that the table
+            // round trip is hidden behind the copies instead of draining the ring at every step and segment boundary.
             const bool masked = (s.flags & RK_SEGF_MASKED) != 0;
             const uint64_t *um = p.qmask + (size_t) query * p.mask_words;
             uint64_t run_start = 0, run_len = 0;
+            ExtStep x;
+            if (pre_valid) x = pre; else if (s.ext_lo < s.ext_hi) ext_load(s, s.ext_lo, x);
+            pre_valid = false;
             for (uint32_t eb = s.ext_lo; eb < s.ext_hi; eb += 32 * RK_EPL) {
-                // all loads of a step are unconditional and independent (indices clamped), so the
-                // step costs one memory round trip, not one per extent
+                ExtStep nx;
+                if (eb + 32 * RK_EPL < s.ext_hi) {
+                    ext_load(s, eb + 32 * RK_EPL, nx);
+                } else if (next && next->kind == RK_SEG_EXTENTS && next->ext_lo < next->ext_hi) {
+                    ext_load(*next, next->ext_lo, nx);
+                    pre_valid = true;
+                }
                 uint32_t ec[RK_EPL];
                 bool ok[RK_EPL];
 #pragma unroll
@@ -239,20 +274,13 @@ struct RkProducer {
                 }
                 uint64_t prow[RK_EPL];
                 uint32_t plen[RK_EPL];
-                uint32_t vs_[RK_EPL], ve_[RK_EPL], er_[RK_EPL];
 #pragma unroll
                 for (int j = 0; j < RK_EPL; j++) {
-                    vs_[j] = rk_ld_u32_hint(p.ext_vstart + ec[j], pol_keep);
-                    ve_[j] = rk_ld_u32_hint(p.ext_vstart + ec[j] + 1, pol_keep);
-                    er_[j] = rk_ld_u32_hint(p.ext_row + ec[j], pol_keep);
-                }
-#pragma unroll
-                for (int j = 0; j < RK_EPL; j++) {
-                    const uint64_t vs = vs_[j], ve = ve_[j];
+                    const uint64_t vs = x.vs[j], ve = x.ve[j];
                     const uint64_t v0 = vs > s.begin ? vs : s.begin;
                     const uint64_t v1 = ve < s.end ? ve : s.end;
                     const bool take = ok[j] && v1 > v0;
-                    prow[j] = (uint64_t) er_[j] + (v0 - vs);
+                    prow[j] = (uint64_t) x.er[j] + (v0 - vs);
                     plen[j] = take ? (uint32_t) (v1 - v0) : 0u;
                 }
 #pragma unroll
@@ -279,7 +307,10 @@ struct RkProducer {
                     run_start += n;
                     run_len -= n;
                 }
+                if (eb == s.ext_lo) stamp();
+                x = nx;
             }
+            if (pre_valid) pre = x;
             if (run_len) emit_run(run_start, run_len);
         } else {  // RK_SEG_ROWMASK
             // Rows of a store that is NOT sorted by document (IVF lists): the role mask is reached
@@ -543,31 +574,36 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
         RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, false, true, rk_policy_evict_first(),
                       rk_policy_evict_last()};
         auto seg_at = [&](uint32_t pos) -> uint32_t { return p.seg_order ? p.seg_order[pos] : pos; };
-        // claim two segments ahead: the next descriptor is loaded while the current one streams
-        // (the first two positions of every CTA are static — b and b + grid — so no atomic round trip sits before the first
-        // row is requested; the shared counter hands out the positions from 2 * grid on)
-        const uint32_t sid_dyn0 = 2u * gridDim.x;
-        uint32_t sid0 = blockIdx.x, sid1 = blockIdx.x + gridDim.x;
-        RkSegment cur;
+        pr.pre_valid = false;
+        pr.dbg_n = 0;
+        // Claims run three segments ahead: while segment i streams, the descriptor of i + 1 is already in registers (its
+        // query decides whether i may hand its candidate buffer on, and its first extents are requested before i ends),
+        // the descriptor of i + 2 is in flight and the position of i + 3 is being claimed — no load or atomic round trip
+        // sits between two segments.  The first three positions of every CTA are static (b, b + grid, b + 2 grid), so no
+        // atomic sits before the first row is requested either; the shared counter hands out positions from 3 * grid on.
+        const uint32_t sid_dyn0 = 3u * gridDim.x;
+        uint32_t sid0 = blockIdx.x, sid1 = sid0 + gridDim.x, sid2 = sid1 + gridDim.x;
+        RkSegment cur, nxt;
         uint32_t cur_id = 0, nxt_id = 0;
         if (sid0 < nseg) { cur_id = seg_at(sid0); cur = p.segs[cur_id]; }
+        if (sid1 < nseg) { nxt_id = seg_at(sid1); nxt = p.segs[nxt_id]; }
         while (sid0 < nseg) {
-            RkSegment nxt;
-            uint32_t sid2 = 0;
-            if (sid1 < nseg) {
-                nxt_id = seg_at(sid1);
-                nxt = p.segs[nxt_id];
-                if (lane == 0) sid2 = sid_dyn0 + atomicAdd(p.seg_counter, 1u);
-            } else {
-                sid2 = sid1;
+            pr.stamp();
+            RkSegment nn;
+            uint32_t nn_id = 0, claim = 0;
+            const bool more = sid2 < nseg;
+            if (more) {
+                nn_id = seg_at(sid2);
+                nn = p.segs[nn_id];
+                if (lane == 0) claim = atomicAdd(p.seg_counter, 1u);       // (the result is not touched before the segment is out)
             }
             pr.seg_id = cur_id;
             pr.cont_next = sid1 < nseg && nxt.query == cur.query && (cur.flags & nxt.flags & RK_SEGF_MERGE_OK) != 0;
-            pr.run_segment(cur);
-            cur_id = nxt_id;
-            sid2 = __shfl_sync(0xffffffffu, sid2, 0);
-            sid0 = sid1; sid1 = sid2;
-            cur = nxt;
+            pr.run_segment(cur, sid1 < nseg ? &nxt : nullptr);
+            const uint32_t sid3 = more ? sid_dyn0 + __shfl_sync(0xffffffffu, claim, 0) : sid2;
+            sid0 = sid1; sid1 = sid2; sid2 = sid3;
+            cur = nxt; cur_id = nxt_id;
+            nxt = nn; nxt_id = nn_id;
         }
         pr.open_tile();
         pr.first = false;
@@ -597,6 +633,7 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
     unsigned long long *dbg = p.fused && p.fz_dbg ? p.fz_dbg + (size_t) blockIdx.x * 8 : nullptr;
     if (dbg && t == 0) dbg[0] = rk_globaltimer();                   // CTA start
     bool dbg_first = dbg != nullptr;
+    int dbg_tiles = 0;
     if (p.fused) {
         // one query for the whole launch: the consumers fetch it themselves — from the kernel parameters when it rides
         // there, else from HBM — while the producer resolves its first extents
@@ -610,13 +647,18 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
         }
         csync();
     }
+    volatile uint32_t *s_mm = s_count + 16;                                  // [16] min / max scratch
     int stage = 0;
     uint32_t phase = 0;
     int since_ckpt = 0;
+    // a long single-query scan sets its threshold early: until the first compaction every row is a candidate
+    const uint32_t trigger0 = p.fused && p.fz_seed > 0 && (uint32_t) p.fz_seed < trigger ? (uint32_t) p.fz_seed : trigger;
+    bool seeded = false;
     for (;;) {
         rk_mbar_wait(&full[stage], phase);
         const RkStageMeta m = meta[stage];
         if (dbg_first && t == 0) { dbg[1] = rk_globaltimer(); dbg_first = false; }       // first tile landed
+        if (dbg && blockIdx.x == 0 && t == 0 && dbg_tiles < 256) p.fz_dbg[(size_t) (gridDim.x + 1) * 8 + dbg_tiles++] = rk_globaltimer();
         if (m.flags & RK_FLAG_END) break;
         if (m.flags & RK_FLAG_FIRST) {
             // Every warp copies the segment's query for itself (identical values from all warps).
@@ -708,12 +750,15 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
         if (last || ++since_ckpt == ckpt) {
             since_ckpt = 0;
             // one reducing barrier: every warp gets the same verdict whatever it read itself
-            const bool full_buf = rk_named_bar_red_or(1, RK_CONS_THREADS, *s_count > trigger);
+            const bool full_buf = rk_named_bar_red_or(1, RK_CONS_THREADS, *s_count > (seeded ? trigger : trigger0));
             if (fin || full_buf) {
                 int n = (int) *s_count;              // stable: nobody appends before the next barrier
                 uint32_t tau = RK_KEY_SENTINEL;
                 if (n > p.k) {
-                    tau = rk_radix_kth(cb.key, n, p.k, s_hist, s_wsum, s_sel, t, csync);
+                    // 12-bit digits over the spread of the keys; the 4096-bin histogram lies over the tuple-id slots, which
+                    // are only filled for the exact sort below.  A compaction in mid-segment needs a threshold only (loose:
+                    // up to 63 keys above the k-th stay), the end of a segment the exact k-th key.
+                    tau = rk_radix_kth_wide(cb.key, n, p.k, reinterpret_cast<uint32_t *>(cb.tid), s_wsum, s_sel, s_mm, t, csync, !fin);
                     n = rk_compact_le(cb, n, tau, t, s_wsum, csync);
                 }
                 if (fin || n > tie_limit) {
@@ -722,6 +767,7 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
                     rk_bitonic_sort(cb, n, t, RK_CONS_THREADS, csync);
                     if (n > p.k) n = p.k;
                 }
+                seeded = true;
                 if (fin) {
                     const size_t base = (size_t) m.seg * p.k;
                     for (int i = t; i < n; i += RK_CONS_THREADS) {
@@ -758,7 +804,6 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
     csync();                                  // every warp has left the loop: no append is in flight
     if (dbg && t == 0) dbg[2] = rk_globaltimer();                   // scan done
     uint32_t *whist = reinterpret_cast<uint32_t *>(smem + L.off_tiles);     // 4096-bin histogram: the tile ring is idle from here on
-    volatile uint32_t *s_mm = s_count + 16;                                  // [16] min / max scratch
     int n = (int) *s_count;
     if (gridDim.x > 1) {
         const int rc_ = n < p.fz_r ? n : p.fz_r;
@@ -928,19 +973,27 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
     overflow = m > RK_CAND_CAP;                // more than RK_CAND_CAP entries tie at the k-th key: the host reruns unfused
     if (overflow) m = 0;
     }
-    for (int i = t; i < m; i += RK_CONS_THREADS) cb.tid[i] = p.store.tid[cb.row[i]];
+    // tuple ids and (when asked for) document ids of the survivors: fetched together, before the ordering needs them
+    uint32_t *sdoc = whist;                    // [RK_CAND_CAP] document ids, in the idle tile ring
+    for (int i = t; i < m; i += RK_CONS_THREADS) {
+        const uint32_t r = cb.row[i];
+        const uint64_t tid = p.store.tid[r];
+        if (p.fz_out_doc) sdoc[i] = p.fz_doc_ids[p.store.rowdoc[r]];
+        cb.tid[i] = tid;
+    }
     csync();
     if (dbg && t == 0) dbg[3] = rk_globaltimer();                   // gathered, tuple ids fetched
     const int cnt = overflow ? 0 : (m < p.k ? m : p.k);
-    auto emit = [&](int r, uint32_t key, uint32_t row, uint64_t tid) {
+    auto emit = [&](int r, uint32_t key, uint32_t doc, uint64_t tid) {
         const float ord = rk_key_to_float(key);
         if (p.fz_out_tid) p.fz_out_tid[r] = tid;
         if (p.fz_out_key) p.fz_out_key[r] = ord;
-        if (p.fz_out_doc) p.fz_out_doc[r] = p.fz_doc_ids[p.store.rowdoc[row]];
+        if (p.fz_out_doc) p.fz_out_doc[r] = doc;
         if (p.fz_out_dist) p.fz_out_dist[r] = p.null_query ? 0.0 : (METRIC == 0 ? sqrt((double) ord) : (double) ord);   // vector.c:577, :635
     };
     if (m <= 512) {
-        // rank sort: an entry's position is the number of entries ordered before it — no barriers, m^2 / 256 compares per thread
+        // rank sort: an entry's position is the number of entries ordered before it — no barriers, m^2 / 256 compares per
+        // thread
         for (int i = t; i < m; i += RK_CONS_THREADS) {
             const uint32_t ki = cb.key[i];
             const uint64_t ti = cb.tid[i];
@@ -951,11 +1004,13 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
                 const uint64_t tj = cb.tid[j];
                 r += (rk_cand_less(kj, tj, ki, ti) || (kj == ki && tj == ti && j < i)) ? 1 : 0;
             }
-            if (r < cnt) emit(r, ki, cb.row[i], ti);
+            if (r < cnt) emit(r, ki, p.fz_out_doc ? sdoc[i] : 0u, ti);
         }
     } else {
+        // (the sort moves key / row / tuple id; the document ids are looked up again afterwards)
         rk_bitonic_sort(cb, m, t, RK_CONS_THREADS, csync);
-        for (int i = t; i < cnt; i += RK_CONS_THREADS) emit(i, cb.key[i], cb.row[i], cb.tid[i]);
+        for (int i = t; i < cnt; i += RK_CONS_THREADS)
+            emit(i, cb.key[i], p.fz_out_doc ? p.fz_doc_ids[p.store.rowdoc[cb.row[i]]] : 0u, cb.tid[i]);
     }
     for (int i = cnt + t; i < p.k; i += RK_CONS_THREADS) {
         if (p.fz_out_tid) p.fz_out_tid[i] = 0xFFFFFFFFFFFFFFFFull;

@@ -359,12 +359,11 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
         }
         uint64_t total_rows = 0, algo_rows = 0;
         for (auto &pi : items) { total_rows += pi.rows_est; algo_rows += pi.rows_algo; }
-        // a segment costs about a microsecond here (claim, descriptor, pipeline refill — no per-segment select), so with
-        // T = streaming time per CTA the best count per CTA is ~sqrt(T / 2o): more, smaller segments than a batch plan cuts
+        // two equal segments per CTA: every boundary stalls a CTA's issue for ~2 us (measured: 1-2 per CTA is best from
+        // 50 MB to 5 GB; with equal segments the CTAs drain together, so there is little for a finer split to balance)
         const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4, sm = (uint64_t) ix->sm_count;
-        const double t_cta_us = (double) total_rows * (double) row_bytes / (double) sm / 44.0e3;
-        double per_cta = std::sqrt(t_cta_us / 2.0);
-        per_cta = std::min(32.0, std::max(1.0, std::floor(per_cta + 0.5)));
+        double per_cta = 2.0;
+        if (ix->tune.single_segs > 0) per_cta = (double) ix->tune.single_segs;
         // a whole number of equal segments per CTA: with one partition every CTA then streams the same number of rows and
         // the grid drains together (one segment more on some CTAs is a tail as long as a segment)
         uint64_t target = (total_rows + (uint64_t) (sm * per_cta) - 1) / (uint64_t) (sm * per_cta);
@@ -443,6 +442,8 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
     p.fz_cap = k + (trigger - k) / 2;
     // rows a CTA vouches for: the bound is valid once r x (CTAs reported) >= k; about three quarters of the grid should do
     p.fz_r = std::max(1, (4 * k + 3 * grid - 1) / (3 * grid));
+    p.fz_seed = 0;
+    if (ix->tune.single_seed > 0 && fp.rows_scanned / (uint64_t) grid >= (uint64_t) ix->tune.single_seed_min) p.fz_seed = std::max(ix->tune.single_seed, 2 * k) - 1;
     if (ws.fz_ctl.p == nullptr) {
         if (ws.fz_ctl.ensure(64) != 0) return RK_ERR_CUDA;
         RK_CUDA(cudaMemsetAsync(ws.fz_ctl.p, 0, 64, ws.stream));
@@ -470,7 +471,7 @@ static int search_single_fused(rk_index *ix, Workspace &ws, const float *dQ, con
     p.fz_flag = d_flag;
     p.fz_seq = seq;
     if (ix->tune.single_debug) {
-        const size_t db = (size_t) (ix->sm_count + 1) * 64;
+        const size_t db = (size_t) (ix->sm_count + 1) * 64 + 4096;
         if (!ws.h_dbg) RK_CUDA(cudaHostAlloc((void **) &ws.h_dbg, db, cudaHostAllocDefault));
         if (ws.d_dbg.ensure(db) != 0) return RK_ERR_CUDA;
         RK_CUDA(cudaMemsetAsync(ws.d_dbg.p, 0, db, ws.stream));
@@ -701,7 +702,7 @@ static int host_search_single(rk_index *ix, Workspace &ws, const float *Q, const
     }
     if (ix->tune.single_debug && ws.h_dbg) {
         // phase timeline of the launch, microseconds after the earliest CTA start: median / max over the CTAs, then the merge
-        cudaMemcpyAsync(ws.h_dbg, ws.d_dbg.p, (size_t) (ix->sm_count + 1) * 64, cudaMemcpyDeviceToHost, ws.stream);
+        cudaMemcpyAsync(ws.h_dbg, ws.d_dbg.p, (size_t) (ix->sm_count + 1) * 64 + 4096, cudaMemcpyDeviceToHost, ws.stream);
         cudaStreamSynchronize(ws.stream);
         const int G = (int) std::max<uint32_t>(1u, std::min<uint32_t>((uint32_t) ix->sm_count, (uint32_t) ws.segments));
         unsigned long long t0 = ~0ull;
@@ -718,6 +719,14 @@ static int host_search_single(rk_index *ix, Workspace &ws, const float *Q, const
         fprintf(stderr, "  merge (cta %llu, N = %llu): start %7.2f keys %7.2f kth %7.2f gathered %7.2f written %7.2f us\n", m_[7], m_[6],
                 (double) (m_[0] - t0) * 1e-3, (double) (m_[1] - t0) * 1e-3, (double) (m_[2] - t0) * 1e-3, (double) (m_[3] - t0) * 1e-3,
                 (double) (m_[4] - t0) * 1e-3);
+        if (ix->tune.single_debug > 1) {
+            const unsigned long long *tt = ws.h_dbg + (size_t) (G + 1) * 8;
+            fprintf(stderr, "  cta 0 tile arrivals:");
+            for (int i = 0; i < 256 && tt[i]; i++) fprintf(stderr, " %.2f", (double) (tt[i] - t0) * 1e-3);
+            fprintf(stderr, "\n  cta 0 producer (loop top / segment start / tile open / first step out):");
+            for (int i = 0; i < 256 && tt[256 + i]; i++) fprintf(stderr, "%s%.2f", i % 4 ? " " : " | ", (double) (tt[256 + i] - t0) * 1e-3);
+            fprintf(stderr, "\n");
+        }
     }
     const int32_t cnt = *reinterpret_cast<const volatile int32_t *>(hout);
     if (cnt < 0) return 0;                                  // more ties at the k-th key than the fused merge holds: general path
