@@ -98,6 +98,10 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--pipeline", action="store_true", help="N > 1: overlap a step's exchange (side stream) with the next step's scan")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
+    ap.add_argument("--no-single", action="store_true", help="skip the single-query legs (N = 1, tree RBAC workloads)")
+    ap.add_argument("--single-reps", type=int, default=16)
+    ap.add_argument("--no-legs", action="store_true", help="default c3 line at N = 1: skip the short legs of c1 / c2 / c5 / c4")
+    ap.add_argument("--legs-budget-s", type=int, default=200, help="no further short leg is started after this many seconds")
     return ap.parse_args()
 
 
@@ -415,9 +419,27 @@ def cpu_model():
     return "unknown"
 
 
+def make_config(wl, args, world):
+    """The workload-defining keys of the JSON line — identical in the b200 arm and the reference arm (what differs
+    between the arms, engine and per-rank sizes, goes under "run")."""
+    wl = as_workload(wl)
+    gb = wl["rows"] * wl["dim"] * 4 / max(1, world) / 1e9
+    cfg = {"workload": wl["desc"], "rows": wl["rows"], "dim": wl["dim"], "k": args.k, "queries_per_step": args.nq,
+           "filter": args.filter or wl["filter"], "metric_op": wl["metric"], "rbac": wl["rbac"], "users": wl["users"], "roles": wl["roles"],
+           "l2_policy": "no flush between steps: the row store (%.2f GB per GPU at N = %d) is %.0fx the 126 MB L2.  Queries of one step that "
+                        "walk the same rows share them through L2 (scheduled that way), so DRAM traffic is below the algorithmic bytes: "
+                        "roofline.frac is algorithmic bytes / time, roofline.dram_frac is the measured DRAM bytes / time; the "
+                        "single_query legs (one query, L2 flushed or rotated out) are the no-reuse HBM numbers" % (gb, world, gb * 1e3 / 126.0)}
+    if wl.get("ivf_lists"):
+        cfg.update({"lists": int(wl["ivf_lists"]), "nprobe": args.nprobe})
+    return cfg
+
+
 def run_reference(args, wl):
-    """--impl reference: the reference's CPU implementation of the path, all host threads."""
-    import torch
+    """--impl reference: the reference's CPU implementation of the path (its own distance loops from oracle/_ref inside
+    the oracle's restated scan + top-k + merge), all host threads, same config / metric / unit as the b200 arm.  Uses the
+    CPU only: the corpus comes from oracle/synthgen.c (bit-identical to the package's generator), and neither
+    librbacknn.so nor CUDA is loaded."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -426,24 +448,34 @@ def run_reference(args, wl):
         # it is timed inside that arm's cpu_baseline
         emit({"impl": "reference", "unavailable": "workload c4: the IVFFlat CPU leg runs inside the b200 arm (cpu_baseline) on the index it builds"})
         return
-    rows, dim, desc = wl["rows"], wl["dim"], wl["desc"]
-    dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # data generation only
-    tid, doc, ur, dr = build_rbac(wl)
-    X = np.empty((rows, dim), dtype=np.float32)
-    for a in range(0, rows, 1 << 20):
-        b = min(rows, a + (1 << 20))
-        X[a:b] = gen_rows(wl, np.arange(a, b), dev).cpu().numpy()
-    Q, qusers = make_queries(wl, args.nq, dev)
-    Q = Q.cpu().numpy()
-    parts, qparts = cpu_partitions(doc, ur, dr, qusers)
+    from oracle import oracle as orc
+    import vectorsearch_rbac_b200.synth as synth          # input generators only; does not load librbacknn.so
+    rows, dim = wl["rows"], wl["dim"]
     cores = host_cores()
-    # calibrate the bounded sample: one step should take ~2 s, the whole run <= ~3 min
+    tid, doc, ur, dr = build_rbac(wl)
+    qrows, qusers = synth.queries(rows, np.arange(1, wl["users"] + 1), args.nq, seed=7)
+    if wl["kind"] == "sift":
+        X = orc.gen_sift(np.arange(rows, dtype=np.int64), dim, 1234, nthreads=cores)
+        Q = orc.gen_sift(qrows, dim, 1234, nthreads=1)
+        gen = "oracle/synthgen.c on the host (bit-identical to the b200 arm's corpus)"
+    else:
+        # the Cohere shape is floating point (log / cos): generated with torch on the host; last-bit differences from the
+        # GPU-generated corpus of the b200 arm do not matter to a timing
+        import torch
+        X = np.empty((rows, dim), dtype=np.float32)
+        for a in range(0, rows, 1 << 18):
+            b = min(rows, a + (1 << 18))
+            X[a:b] = synth.corpus(wl["kind"], torch.arange(a, b), dim, seed=1234).numpy()
+        Q = synth.corpus(wl["kind"], torch.as_tensor(qrows), dim, seed=1234).numpy()
+        gen = "torch on the host"
+    parts, qparts = cpu_partitions(doc, ur, dr, qusers)
+    # every step times ALL queries of the b200 arm's step unless that cannot end within ~3 minutes; then a bounded prefix
     n0 = min(args.nq, max(cores, 8))
     t0 = time.perf_counter()
     cpu_search(X, tid, parts, qparts[:n0], Q[:n0], args.k, cores, wl["metric"])
     per_q = (time.perf_counter() - t0) / n0
-    budget = min(2.5, 170.0 / max(1, args.steps + args.warmup))
-    S = int(max(min(cores, args.nq), min(args.nq, budget / max(per_q, 1e-6))))
+    total = max(1, args.steps + args.warmup)
+    S = args.nq if per_q * args.nq * total <= 170.0 else int(max(min(cores, args.nq), min(args.nq, 170.0 / total / max(per_q, 1e-6))))
     for _ in range(args.warmup):
         cpu_search(X, tid, parts, qparts[:S], Q[:S], args.k, cores, wl["metric"])
     t0 = time.perf_counter()
@@ -453,12 +485,13 @@ def run_reference(args, wl):
     dt = time.perf_counter() - t0
     qps = S * args.steps / dt
     sample = (f"{S} of the {args.nq} queries of the step per timed step, full visible row sets, "
-              f"{cores} threads on {cpu_model()}; pgvector distance loops without PostgreSQL page/tuple/fmgr overhead")
+              f"{cores} threads on {cpu_model()}; pgvector distance loops without PostgreSQL page/tuple/fmgr overhead; corpus from {gen}")
     line = {
         "impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "rows": rows, "dim": dim, "k": args.k, "queries_per_step": S, "metric_op": wl["metric"]},
+        "config": make_config(wl, args, args.gpus),
+        "run": {"queries_timed_per_step": S, "threads": cores},
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": kind_used, "sample": sample},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -466,40 +499,57 @@ def run_reference(args, wl):
     emit(line)
 
 
+def cpu_single_thread(X, tid, parts, qparts, Q, k, metric, budget_s=4.0):
+    """The harness's own protocol (basic_benchmark/common_function.py:1366-1382, 1414): per query two warm-up calls and one
+    timed call on ONE thread, QPS = 1 / mean latency; with the reference's distance loops at pgvector's Makefile flags
+    (-O2 -ftree-vectorize ...) and as the reference ships them (compile_pgvector.sh:7: -g -O0)."""
+    from oracle import oracle as orc
+    m = orc.METRIC_L2 if metric == "l2" else orc.METRIC_IP
+    out = {"protocol": "per query 2 warm-up calls + 1 timed call, one thread, QPS = 1 / mean latency (common_function.py:1366-1382, 1414)"}
+    for name, o0 in (("O2_pgvector_makefile_flags", False), ("O0_as_shipped_compile_pgvector_sh", True)):
+        ref = orc.ref_loops(o0=o0)
+        if ref is None:
+            out[name] = None
+            continue
+        lat, t_start = [], time.perf_counter()
+        for i in range(len(Q)):
+            if not qparts[i]:
+                continue
+            p = [parts[qparts[i][0]]]
+            for rep in range(3):
+                t0 = time.perf_counter()
+                orc.search_batch(X, tid, p, [[0]], Q[i:i + 1], m, k, dedup=True, nthreads=1, variant="pgvflags", ref=ref)
+                dt = time.perf_counter() - t0
+            lat.append(dt)
+            if time.perf_counter() - t_start > budget_s and len(lat) >= 2:
+                break
+        out[name] = {"value": 1.0 / float(np.mean(lat)), "unit": "queries/s", "queries": len(lat), "mean_latency_ms": float(np.mean(lat)) * 1e3}
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 
-def main():
-    args = parse_args()
-    wl = dict(WORKLOADS[args.workload])
-    if args.rows:
-        wl["rows"] = args.rows
-    if args.impl == "reference":
-        run_reference(args, wl)
-        return
-
+def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
+    """One workload on this rank's GPU; returns the JSON line (rank 0) or None.  leg=True: a short run for the "workloads"
+    object of the default line (no single-query legs, no single-thread CPU protocol)."""
     import torch
     import torch.distributed as dist
     import vectorsearch_rbac_b200 as vr
     from vectorsearch_rbac_b200 import sharded
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the engine has no CPU path")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    rows, dim, desc = wl["rows"], wl["dim"], wl["desc"]
-    flt_name = args.filter or wl["filter"]
+    wl = dict(WORKLOADS[wl_key])
+    if args.rows and not leg:
+        wl["rows"] = args.rows
+    rank, world, local_rank, dev = env["rank"], env["world"], env["local_rank"], env["dev"]
+    rows, dim = wl["rows"], wl["dim"]
+    flt_name = (args.filter if not leg else "") or wl["filter"]
     metric = vr.METRIC_L2 if wl["metric"] == "l2" else vr.METRIC_IP
     flt = {"bitmask": vr.FILTER_BITMASK, "partition": vr.FILTER_PARTITION, "combination": vr.FILTER_PARTITION,
            "dynamic": vr.FILTER_PARTITION}[flt_name]
     layout = {"bitmask": 0, "partition": vr.LAYOUT_ROLE, "combination": vr.LAYOUT_COMBINATION, "dynamic": vr.LAYOUT_DYNAMIC}[flt_name]
-    engine_name = args.engine or wl["engine"]
+    engine_name = (args.engine if not leg else "") or wl["engine"]
     engine = {"scan": vr.ENGINE_SCAN, "tensor": vr.ENGINE_TENSOR, "auto": vr.ENGINE_AUTO}[engine_name]
+    no_cpu = args.no_cpu
 
     # ---- load this rank's shard ---------------------------------------------------------------
     tid, doc, ur, dr = build_rbac(wl)
@@ -507,7 +557,7 @@ def main():
     ix = vr.Index(dim, metric=metric, device=local_rank, k_max=max(128, args.k))
     ix.reserve_rows(len(mine))
     ivf_lists = int(wl.get("ivf_lists", 0))
-    keep_host = world == 1 and rank == 0 and not args.no_cpu and not ivf_lists
+    keep_host = world == 1 and rank == 0 and not no_cpu and not ivf_lists
     X_host = np.empty((rows, dim), dtype=np.float32) if keep_host else None
     CH = 1 << 20 if dim <= 256 else 1 << 18
     for a0 in range(0, len(mine), CH):
@@ -540,7 +590,6 @@ def main():
 
     Q, qusers = make_queries(wl, args.nq, dev)
     Q = Q.contiguous()
-    torch.cuda.set_stream(torch.cuda.Stream(dev))     # a real stream: torch events, NCCL and the engine share it
     stream = torch.cuda.current_stream(dev)
     sharded.use_torch_stream(ix, dev)
     searcher = sharded.ShardedSearcher(ix, rank, world, device=dev)
@@ -557,9 +606,7 @@ def main():
         """One engine over the step: device-resident `value` leg, then the host-buffer `e2e` leg."""
         opts = vr.engine.make_opts(args.k, probes=args.nprobe if ivf_lists else 0, filter=flt, layout=layout, engine=eng)
         # N > 1: scan, all-gather and merge of a step run back to back on one stream (stages_ms reports each).  With
-        # --pipeline the exchange of step i moves to a side stream under the scan of step i + 1 (measured on 8xB200:
-        # 4.45-4.60 ms per step against 4.53 serial — the collective's CTAs slow the persistent scan kernel by what the
-        # overlap saves — so it is not the default).
+        # --pipeline the exchange of step i moves to a side stream under the scan of step i + 1.
         step_fn = searcher.search_device_pipelined if (world > 1 and args.pipeline) else searcher.search_device
         if ivf_lists and world == 1:
             def step_fn(Qd, users, o):       # the index-probe path of the C-ABI (one GPU)
@@ -576,7 +623,7 @@ def main():
         searcher.stage_events = [] if world > 1 else None
         with ClockSampler(local_rank) as clk:
             e0.record(stream)
-            for _ in range(args.steps):
+            for _ in range(steps):
                 out = step_fn(Q, qusers, opts)
             searcher.flush()
             e1.record(stream)
@@ -588,7 +635,7 @@ def main():
         st = ix.stats()
         r["stats"] = st
         r["launches"] = st["total_launches"] - launches0
-        r["scan_ms"] = ix.scan_times_ms(min(64, args.steps))
+        r["scan_ms"] = ix.scan_times_ms(min(64, steps))
         res_dev = tuple(t.clone() for t in out)
         outs_h = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in res_dev)
         r["h2d"] = Qh.numel() * 4
@@ -608,7 +655,7 @@ def main():
             e2e_step()
         barrier()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             e2e_step()
         barrier()
         r["dt_e2e"] = time.perf_counter() - t0
@@ -623,6 +670,20 @@ def main():
             r["launches"] = int(tl[0])
         return r
 
+    def with_traffic(rf, key):
+        """roofline.traffic = dram bytes of one launch of this kernel from the committed `ncu --set full` capture
+        (profiles/traffic.json); dram_frac = those bytes over the live kernel time against the same peak; l2_share = the part
+        of the algorithmic bytes that did not come from DRAM."""
+        tr = traffic_per_launch(wl_key, world, key) if not args.rows or leg else None
+        rf["traffic"] = tr
+        if tr and rf.get("kernel_ms") and rf.get("unit") == "GB/s":
+            algo = rf.get("algorithmic_bytes_per_launch") or rf.get("bytes_per_launch")
+            rf["dram_GBps"] = tr / (rf["kernel_ms"] * 1e-3) / 1e9
+            rf["dram_frac"] = rf["dram_GBps"] / rf["peak"]
+            if algo:
+                rf["l2_share"] = max(0.0, 1.0 - tr / float(algo))
+        return rf
+
     def roofline_of(r, eng_name):
         """The dominant kernel of the step against the roofline that bounds it."""
         st = r["stats"]
@@ -636,22 +697,21 @@ def main():
             return {"bound": "hbm", "kernel": "rk_ivf_probe_kernel + rk_scan_kernel (list segments)", "achieved": ach, "peak": peak,
                     "unit": "GB/s", "frac": ach / peak, "frac_of_8TBps": ach / 8000.0, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": int(st["algo_bytes"]), "kernel_ms": tms, "probe_ms": float(st["probe_ms"]),
-                    "list_scan_ms": float(st["scan_ms"]), "launches_timed": 1,
-                    "traffic": traffic_per_launch(args.workload, world, flt_name + ":" + eng_name) if args.nprobe == 16 else None}
+                    "list_scan_ms": float(st["scan_ms"]), "launches_timed": 1, "traffic": None}
         if st["tensor_plan"] == 0:
             # CUDA-core scan, one pass per query: HBM.  Bytes per SURVEY.md §8(d): allowed rows x 4d + mask bytes + 12k, per query
             peak, peak_src = peaks()
             ach = st["algo_bytes"] / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
-            return {"bound": "hbm", "kernel": "rk_scan_kernel", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "frac_of_8TBps": ach / 8000.0, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(st["algo_bytes"]),
-                    "kernel_ms": kms, "launches_timed": int(len(r["scan_ms"])),
-                    "traffic": traffic_per_launch(args.workload, world, flt_name + ":" + eng_name)}
+            return with_traffic({"bound": "hbm", "kernel": "rk_scan_kernel", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                 "frac_of_8TBps": ach / 8000.0, "peak_source": peak_src, "algorithmic_bytes_per_launch": int(st["algo_bytes"]),
+                                 "kernel_ms": kms, "launches_timed": int(len(r["scan_ms"]))}, flt_name + ":" + eng_name)
         # tensor engine.  SURVEY.md §8(d), batched exact: F = 2 nq_g R_g d over the groups the plan forms
         # (dense plan: all queries x all rows), bytes 4d (R_g + nq_g); the launch sits in whichever regime its
         # arithmetic intensity F / bytes puts it (ridge = TF32 peak / HBM peak).
         plan = {1: "dense", 2: "per user mask", 3: "per document class (atoms)"}[st["tensor_plan"] & 15]
         hbm, hbm_src = peaks()
-        tf32 = tf32_peak(dev)
+        tf32 = env.setdefault("tf32_peak", None) or tf32_peak(dev)
+        env["tf32_peak"] = tf32
         flop = float(st["tensor_flop"])
         byts = float(st["algo_bytes"])
         intensity = flop / max(byts, 1.0)
@@ -659,16 +719,18 @@ def main():
         common = {"kernel": "rk_bscan2_kernel (CTA pairs, tcgen05 cta_group::2)" if st["tensor_plan"] & 32 else "rk_bscan_kernel", "plan": plan + (" + sampling pass" if st["tensor_plan"] & 16 else ""),
                   "kernel_ms": kms, "launches_timed": int(len(r["scan_ms"])), "flop_per_launch": flop, "bytes_per_launch": byts,
                   "plan_bytes_per_launch": float(st["tensor_plan_bytes"]),
-                  "intensity_flop_per_byte": intensity, "ridge_flop_per_byte": ridge,
-                  "traffic": traffic_per_launch(args.workload, world, flt_name + ":" + eng_name)}
+                  "intensity_flop_per_byte": intensity, "ridge_flop_per_byte": ridge}
         if intensity >= ridge:
             ach = flop / (kms * 1e-3) / 1e12 if kms > 0 else 0.0
-            return {"bound": "tensor", "achieved": ach, "peak": tf32, "unit": "TFLOP/s", "frac": ach / tf32,
-                    "peak_source": "measured live: cuBLAS TF32 (torch.matmul, allow_tf32) 8192^3, best of 10 — MEASURED_PEAKS.json has no TF32 figure",
-                    "frac_of_nominal_1100": ach / 1100.0, **common}
+            bf16 = peaks_all().get("bf16_tflops_sustained")
+            return with_traffic({"bound": "tensor", "achieved": ach, "peak": tf32, "unit": "TFLOP/s", "frac": ach / tf32,
+                                 "peak_source": "measured live: cuBLAS TF32 (torch.matmul, allow_tf32) 8192^3, best of 10 — MEASURED_PEAKS.json has no TF32 figure",
+                                 "frac_of_nominal_1100": ach / 1100.0,
+                                 "frac_of_measured_bf16_sustained": (ach / bf16) if bf16 else None, **common}, flt_name + ":" + eng_name)
         ach = byts / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
-        return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "peak_source": hbm_src,
-                "tf32_tflops_achieved": flop / (kms * 1e-3) / 1e12 if kms > 0 else 0.0, "tf32_peak_measured": tf32, **common}
+        return with_traffic({"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "peak_source": hbm_src,
+                             "tf32_tflops_achieved": flop / (kms * 1e-3) / 1e12 if kms > 0 else 0.0, "tf32_peak_measured": tf32, **common},
+                            flt_name + ":" + eng_name)
 
     main_r = measure(engine)
     batched_r = None
@@ -683,171 +745,55 @@ def main():
         ex_exact = [t.cpu().numpy() for t in searcher.search_device(Q, qusers, opts0)]
         barrier()
 
+    single = None
+    if rank == 0 and world == 1 and not leg and not args.no_single and not ivf_lists and wl["rbac"] == "tree":
+        ix.enable_timing(False)
+        single = single_query_legs(ix, wl, ur, dr, dev, args.k, flt, layout, reps=args.single_reps)
+
+    line = None
     if rank == 0:
         st = main_r["stats"]
         line = {
-            "metric": METRIC, "value": args.nq * args.steps / main_r["dt_dev"], "unit": "queries/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": main_r["dt_dev"] / args.steps * 1e3,
+            "metric": METRIC, "value": args.nq * steps / main_r["dt_dev"], "unit": "queries/s", "n_gpus": world,
+            "steps": steps, "warmup": max(3, args.warmup), "ms_per_step": main_r["dt_dev"] / steps * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32" if st["tensor_plan"] == 0 else "tf32 nomination + f32 exact re-score",
             "data": "synthetic",
-            "config": {"workload": desc, "rows": rows, "dim": dim, "k": args.k, "queries_per_step": args.nq,
-                       "filter": flt_name, "engine": engine_name, "metric_op": wl["metric"], "rows_this_rank": int(len(mine)),
-                       "l2_policy": "inputs larger than L2: each step streams %.1f GB of row data per GPU (L2 = 126 MB)" % (st["algo_bytes"] / 1e9),
-                       "recall_at_100": 1.0, "recall_note": "exact search; ids checked against the oracle on the cpu_baseline sample"},
+            "config": make_config(wl, args, world),
+            "run": {"engine": engine_name, "rows_this_rank": int(len(mine)),
+                    "recall_at_100": 1.0, "recall_note": "exact search; ids checked against the oracle on the cpu_baseline sample"},
             "roofline": roofline_of(main_r, engine_name),
-            "e2e": {"value": args.nq * args.steps / main_r["dt_e2e"], "unit": "queries/s", "h2d_bytes_per_step": int(main_r["h2d"]),
-                    "d2h_bytes_per_step": int(main_r["d2h"]), "ms_per_step": main_r["dt_e2e"] / args.steps * 1e3,
+            "e2e": {"value": args.nq * steps / main_r["dt_e2e"], "unit": "queries/s", "h2d_bytes_per_step": int(main_r["h2d"]),
+                    "d2h_bytes_per_step": int(main_r["d2h"]), "ms_per_step": main_r["dt_e2e"] / steps * 1e3,
                     "matches_device_path": bool(main_r["same"])},
             "gpu_launches": int(main_r["launches"]),
             "clocks": main_r["clk"],
         }
         if layout_info is not None:
-            line["config"]["dynamic_layout"] = layout_info
+            line["run"]["dynamic_layout"] = layout_info
         if main_r.get("stages"):
             # rank 0's mean device time per stage of a step (the all-gather also absorbs waiting for the slowest rank)
             line["stages_ms"] = main_r["stages"]
         if world > 1:
-            line["config"]["exchange"] = ("all-gather + merge of step i on a side stream, overlapping the scan of step i + 1"
-                                          if main_r["pipelined"] else "all-gather + merge after every scan, same stream")
+            line["run"]["exchange"] = ("all-gather + merge of step i on a side stream, overlapping the scan of step i + 1"
+                                       if main_r["pipelined"] else "all-gather + merge after every scan, same stream")
+        if single is not None:
+            line["single_query"] = single
         if batched_r is not None:
             # the same step through RK_ENGINE_AUTO (batches of >= 32 exact scans go to the tcgen05 engine): identical
             # results, every row a group of queries shares read once
             line["batched"] = {
                 "engine": "auto -> tensor" if batched_r["stats"]["tensor_plan"] else "auto -> scan",
-                "value": args.nq * args.steps / batched_r["dt_dev"], "unit": "queries/s", "ms_per_step": batched_r["dt_dev"] / args.steps * 1e3,
-                "e2e": {"value": args.nq * args.steps / batched_r["dt_e2e"], "unit": "queries/s", "ms_per_step": batched_r["dt_e2e"] / args.steps * 1e3},
+                "value": args.nq * steps / batched_r["dt_dev"], "unit": "queries/s", "ms_per_step": batched_r["dt_dev"] / steps * 1e3,
+                "e2e": {"value": args.nq * steps / batched_r["dt_e2e"], "unit": "queries/s", "ms_per_step": batched_r["dt_e2e"] / steps * 1e3},
                 "roofline": roofline_of(batched_r, "auto"), "gpu_launches": int(batched_r["launches"]),
                 "identical_to_headline_results": bool(all(torch.equal(x, y) for x, y in zip(main_r["outs_h"], batched_r["outs_h"]))),
                 "tensor_redo": int(batched_r["stats"]["tensor_redo"]), "clocks": batched_r["clk"]}
         if ivf_lists:
-            # recall@k against the engine's own exact filtered result (probes = 0), which the parity tests pin to the oracle
-            ex = ex_exact
-            got_t, got_c = main_r["outs_h"][0].numpy(), main_r["outs_h"][3].numpy()
-            rec = float(np.mean([len(set(ex[0][i, :ex[3][i]].tolist()) & set(got_t[i, :got_c[i]].tolist())) / max(1, int(ex[3][i]))
-                                 for i in range(args.nq)]))
-            # algorithmic bytes per SURVEY.md §8(d): per query lists x 4d (centres) + VISIBLE rows of the probed lists x 4d
-            # + mask bytes (row -> document -> role mask, 20 B per probed row) + 12k.  The engine's own figure counts every
-            # row of the probed lists, so the visible rows are recounted here from the index's list assignment.
-            # (bookkeeping in numpy on the engine's own list assignment and list choice; the oracle is only the CPU leg's)
-            _, row_list_ = ix.ivf_info(len(mine))            # N > 1: this rank's stripe of every list (rank 0's GPU is reported)
-            lrows_ = np.argsort(row_list_, kind="stable")
-            off_ = np.searchsorted(row_list_[lrows_], np.arange(ivf_lists + 1))
-            P_ = min(args.nprobe, ivf_lists)
-            pl_ = torch.empty((args.nq, P_), dtype=torch.int32, device=dev)
-            ix.ivf_probe_device(Q.data_ptr(), args.nq, vr.engine.make_opts(args.k, probes=args.nprobe, filter=flt), pl_.data_ptr())
-            ix.synchronize()
-            pl_ = pl_.cpu().numpy()
-            doc_np = np.asarray(doc)[mine]
-            roles_of_, docs_of_ = {}, {}
-            for u_, r_ in ur:
-                roles_of_.setdefault(int(u_), set()).add(int(r_))
-            for d_, r_ in dr:
-                docs_of_.setdefault(int(r_), []).append(int(d_))
-            vis_cache = {}
-            probed_rows = visible_rows = 0
-            for i in range(args.nq):
-                u_ = int(qusers[i])
-                if u_ not in vis_cache:
-                    v_ = np.zeros(int(np.asarray(doc).max()) + 2, dtype=bool)
-                    for r_ in roles_of_.get(u_, ()):
-                        v_[np.asarray(docs_of_.get(r_, []), dtype=np.int64)] = True
-                    vis_cache[u_] = v_
-                for l_ in pl_[i]:
-                    rr = lrows_[int(off_[l_]):int(off_[l_ + 1])]
-                    probed_rows += len(rr)
-                    visible_rows += int(vis_cache[u_][doc_np[rr]].sum())
-            rb_ = dim * 4
-            b_centres = args.nq * ivf_lists * rb_
-            # mask bytes M: lists ordered by document class (<= 128 distinct role masks) read one offset per class and probed
-            # list; otherwise row -> document -> role mask, 20 B per probed row
-            doc_sets = {}
-            for d_, r_ in dr:
-                doc_sets.setdefault(int(d_), set()).add(int(r_))
-            n_cls = len(set(frozenset(v) for v in doc_sets.values()))
-            m_bytes = args.nq * args.nprobe * (n_cls + 1) * 4 if n_cls <= 128 else probed_rows * 20
-            b_lists = visible_rows * rb_ + m_bytes + args.nq * 12 * args.k
-            rf = line["roofline"]
-            # dominant kernel: the list scan (HBM: visible rows of the probed lists).  The centre scoring shares the
-            # centre matrix across the batch (a 12.6 MB matrix kept in L2, fp32 FMA work), so it is reported beside
-            # it with its own rate and not added into the HBM figure
-            lms, pms = rf["list_scan_ms"] * 1e-3, rf["probe_ms"] * 1e-3
-            fl_centres = 2.0 * args.nq * ivf_lists * dim * (2 if wl["metric"] == "l2" else 1)
-            rf.update({"kernel": "rk_scan_kernel (class-ordered list segments)", "kernel_ms": rf["list_scan_ms"],
-                       "algorithmic_bytes_per_launch": int(b_lists), "achieved": b_lists / lms / 1e9 if lms > 0 else 0.0,
-                       "frac": b_lists / lms / 1e9 / rf["peak"] if lms > 0 else 0.0,
-                       "frac_of_8TBps": b_lists / lms / 1e9 / 8000.0 if lms > 0 else 0.0,
-                       "probed_rows": int(probed_rows), "visible_rows": int(visible_rows), "document_classes": n_cls,
-                       "list_bytes": int(b_lists),
-                       "probe": {"kernels": "rk_ivf_keys_kernel + rk_ivf_order_kernel", "ms": rf["probe_ms"],
-                                 "fp32_TFLOPs": fl_centres / pms / 1e12 if pms > 0 else None,
-                                 "centre_bytes_once": int(ivf_lists * rb_), "centre_bytes_per_query_definition": int(b_centres),
-                                 "survey_8d_GBps_both_kernels": (b_centres + b_lists) / (lms + pms) / 1e9 if lms + pms > 0 else None},
-                       "note": "SURVEY.md 8(d) counts the centres once per query (lists x 4d); the batched probe reads them once per "
-                               "16 queries from L2, so that figure would exceed the HBM peak and is reported only under probe; the "
-                               "list scan reads only the rows the user may see (one extent per visible document class and probed list); "
-                               "a read-only stream can exceed the copy-measured peak, and queries probing the same lists share rows in L2 "
-                               "(traffic = dram bytes of the launch)"})
-            if world > 1:
-                rf["probe"]["ms"] = None
-                rf["probe"]["fp32_TFLOPs"] = None
-                rf["probe"]["note"] = ("N > 1: the list choice is split by query across the ranks (nq / N queries each) and "
-                                       "all-gathered; its time is part of stages_ms.local_search")
-                line["config"]["ivf_sharding"] = ("centres trained on rank 0's stripe and broadcast; every list's rows striped with "
-                                                  "their documents (d mod N); list choice split by query + all-gather")
-            line["config"].update({"recall_at_100": rec, "nprobe": args.nprobe, "lists": ivf_lists, "ivf_build_s": ivf_build_s,
-                                   "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
-        if ivf_lists and not args.no_cpu and world == 1:
-            # CPU leg: the oracle's restatement of ivfscan.c with the reference's distance loops, same centres and lists, on
-            # a sample of the queries; only the rows of the lists the sample probes are brought to the host
-            from oracle import oracle as orc
-            from tests.util import assert_topk_matches
-            S = min(args.nq, 32)
-            m = orc.METRIC_L2 if wl["metric"] == "l2" else orc.METRIC_IP
-            centers, row_list = ix.ivf_info(rows)
-            Qn = Q.cpu().numpy()[:S]
-            need = set()
-            for q in Qn:
-                need.update(int(x) for x in orc.ivf_order_lists(centers, q, m, args.nprobe)[0])
-            need_rows = np.flatnonzero(np.isin(row_list, np.fromiter(need, dtype=np.uint32)))
-            X_sub = np.empty((len(need_rows), dim), dtype=np.float32)
-            for a0 in range(0, len(need_rows), CH):
-                X_sub[a0:a0 + CH] = gen_rows(wl, need_rows[a0:a0 + CH], dev).cpu().numpy()
-            off, lrows = orc.ivf_lists_csr(row_list[need_rows], ivf_lists)
-            tid_sub, doc_sub = tid[need_rows], np.asarray(doc)[need_rows]
-            roles_of, docs_of = {}, {}
-            for u, r in ur:
-                roles_of.setdefault(int(u), set()).add(int(r))
-            for d_, r in dr:
-                docs_of.setdefault(int(r), []).append(int(d_))
-            c_tid = np.full((S, args.k), np.uint64(0xFFFFFFFFFFFFFFFF), dtype=np.uint64)
-            c_dist = np.full((S, args.k), np.inf)
-            c_cnt = np.zeros(S, dtype=np.int32)
-            t0 = time.perf_counter()
-            for i in range(S):
-                vis = np.zeros(int(doc_sub.max()) + 2, dtype=np.uint8)
-                for r in roles_of.get(int(qusers[i]), ()):
-                    dd = np.asarray(docs_of.get(r, []), dtype=np.int64)
-                    vis[dd[dd < len(vis)]] = 1
-                (t_, _, d_), = orc.ivf_scan(X_sub, tid_sub, centers, off, lrows, Qn[i], m, probes=args.nprobe, allowed=vis[doc_sub])
-                n = min(args.k, len(t_))
-                c_tid[i, :n], c_dist[i, :n], c_cnt[i] = t_[:n], d_[:n], n
-            dtc = time.perf_counter() - t0
-            g_tid = main_r["outs_h"][0].numpy().view(np.uint64)[:S]
-            g_dist, g_cnt = main_r["outs_h"][2].numpy()[:S], main_r["outs_h"][3].numpy()[:S]
-            note = "within 1e-5 relative; ids identical outside oracle ties of that width"
-            try:
-                assert_topk_matches((g_tid, None, g_dist, g_cnt), (c_tid, None, c_dist, None, c_cnt), exact=False)
-                ok = True
-            except AssertionError as e:
-                ok = False
-                note += " — MISMATCH: " + str(e)[:200]
-            line["cpu_baseline"] = {
-                "value": S / dtc, "unit": "queries/s", "cores": 1, "kind": "port",
-                "sample": f"{S} of the step's {args.nq} queries, nprobe {args.nprobe}, the oracle's restatement of ivfscan.c (centre scoring, "
-                          f"full sort of the probed lists' visible tuples) on one thread of {cpu_model()}, the GPU build's centres and lists; "
-                          "no PostgreSQL page/tuple/fmgr overhead",
-                "gpu_ids_match": ok, "gpu_distances": note, "gpu_distances_match": ok}
-        if world == 1 and not args.no_cpu and not ivf_lists:
+            ivf_roofline(line, args, wl, ix, vr, torch, dev, mine, doc, ur, dr, qusers, Q, main_r, ex_exact, ivf_lists, ivf_build_s, world, flt)
+            line["roofline"] = with_traffic(line["roofline"], flt_name + ":" + engine_name) if args.nprobe == 16 else line["roofline"]
+        if ivf_lists and not no_cpu and world == 1:
+            ivf_cpu_leg(line, args, wl, ix, dev, tid, doc, ur, dr, qusers, Q, main_r, ivf_lists, rows, dim, CH)
+        if world == 1 and not no_cpu and not ivf_lists:
             cores = host_cores()
             outs_h = main_r["outs_h"]
             parts, qparts = cpu_partitions(doc, ur, dr, qusers)
@@ -856,7 +802,7 @@ def main():
             t0 = time.perf_counter()
             cpu_search(X_host, tid, parts, qparts[:n0], Qn[:n0], args.k, cores, wl["metric"])
             per_q = (time.perf_counter() - t0) / n0
-            S = int(max(min(cores, args.nq), min(args.nq, 20.0 / max(per_q, 1e-6))))
+            S = int(max(min(cores, args.nq), min(args.nq, cpu_budget_s / max(per_q, 1e-6))))
             t0 = time.perf_counter()
             (c_tid, c_dist, c_cnt), kind = cpu_search(X_host, tid, parts, qparts[:S], Qn[:S], args.k, cores, wl["metric"])
             dtc = time.perf_counter() - t0
@@ -884,8 +830,216 @@ def main():
                 "sample": f"{S} of the step's {args.nq} queries, full visible row sets, {cores} threads on {cpu_model()}; "
                           "pgvector distance loops without PostgreSQL page/tuple/fmgr overhead",
                 "gpu_ids_match": ids_ok, "gpu_distances": dist_note, "gpu_distances_match": dist_ok}
-        emit(line)
+            if not leg:
+                line["cpu_baseline"]["single_thread"] = cpu_single_thread(X_host, tid, parts, qparts, Qn, args.k, wl["metric"])
     ix.close()
+    del searcher, Q, Qh, X_host
+    torch.cuda.empty_cache()
+    return line
+
+
+def peaks_all():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return {}
+
+
+def ivf_roofline(line, args, wl, ix, vr, torch, dev, mine, doc, ur, dr, qusers, Q, main_r, ex, ivf_lists, ivf_build_s, world, flt):
+    """C4: recall@k against the engine's own exact filtered result (probes = 0, pinned to the oracle by the parity tests) and
+    the list scan's algorithmic bytes per SURVEY.md §8(d): per query lists x 4d (centres) + VISIBLE rows of the probed lists
+    x 4d + mask bytes + 12k.  The engine's own figure counts every row of the probed lists, so the visible rows are
+    recounted here from the index's list assignment (numpy bookkeeping on the engine's own list choice; the oracle is
+    only the CPU leg's)."""
+    dim = wl["dim"]
+    got_t, got_c = main_r["outs_h"][0].numpy(), main_r["outs_h"][3].numpy()
+    rec = float(np.mean([len(set(ex[0][i, :ex[3][i]].tolist()) & set(got_t[i, :got_c[i]].tolist())) / max(1, int(ex[3][i]))
+                         for i in range(args.nq)]))
+    _, row_list_ = ix.ivf_info(len(mine))            # N > 1: this rank's stripe of every list (rank 0's GPU is reported)
+    lrows_ = np.argsort(row_list_, kind="stable")
+    off_ = np.searchsorted(row_list_[lrows_], np.arange(ivf_lists + 1))
+    P_ = min(args.nprobe, ivf_lists)
+    pl_ = torch.empty((args.nq, P_), dtype=torch.int32, device=dev)
+    ix.ivf_probe_device(Q.data_ptr(), args.nq, vr.engine.make_opts(args.k, probes=args.nprobe, filter=flt), pl_.data_ptr())
+    ix.synchronize()
+    pl_ = pl_.cpu().numpy()
+    doc_np = np.asarray(doc)[mine]
+    roles_of_, docs_of_ = {}, {}
+    for u_, r_ in ur:
+        roles_of_.setdefault(int(u_), set()).add(int(r_))
+    for d_, r_ in dr:
+        docs_of_.setdefault(int(r_), []).append(int(d_))
+    vis_cache = {}
+    probed_rows = visible_rows = 0
+    for i in range(args.nq):
+        u_ = int(qusers[i])
+        if u_ not in vis_cache:
+            v_ = np.zeros(int(np.asarray(doc).max()) + 2, dtype=bool)
+            for r_ in roles_of_.get(u_, ()):
+                v_[np.asarray(docs_of_.get(r_, []), dtype=np.int64)] = True
+            vis_cache[u_] = v_
+        for l_ in pl_[i]:
+            rr = lrows_[int(off_[l_]):int(off_[l_ + 1])]
+            probed_rows += len(rr)
+            visible_rows += int(vis_cache[u_][doc_np[rr]].sum())
+    rb_ = dim * 4
+    b_centres = args.nq * ivf_lists * rb_
+    # mask bytes M: lists ordered by document class (<= 128 distinct role masks) read one offset per class and probed
+    # list; otherwise row -> document -> role mask, 20 B per probed row
+    doc_sets = {}
+    for d_, r_ in dr:
+        doc_sets.setdefault(int(d_), set()).add(int(r_))
+    n_cls = len(set(frozenset(v) for v in doc_sets.values()))
+    m_bytes = args.nq * args.nprobe * (n_cls + 1) * 4 if n_cls <= 128 else probed_rows * 20
+    b_lists = visible_rows * rb_ + m_bytes + args.nq * 12 * args.k
+    rf = line["roofline"]
+    # dominant kernel: the list scan (HBM: visible rows of the probed lists).  The centre scoring shares the
+    # centre matrix across the batch (a 12.6 MB matrix kept in L2, fp32 FMA work), so it is reported beside
+    # it with its own rate and not added into the HBM figure
+    lms, pms = rf["list_scan_ms"] * 1e-3, rf["probe_ms"] * 1e-3
+    fl_centres = 2.0 * args.nq * ivf_lists * dim * (2 if wl["metric"] == "l2" else 1)
+    rf.update({"kernel": "rk_scan_kernel (class-ordered list segments)", "kernel_ms": rf["list_scan_ms"],
+               "algorithmic_bytes_per_launch": int(b_lists), "achieved": b_lists / lms / 1e9 if lms > 0 else 0.0,
+               "frac": b_lists / lms / 1e9 / rf["peak"] if lms > 0 else 0.0,
+               "frac_of_8TBps": b_lists / lms / 1e9 / 8000.0 if lms > 0 else 0.0,
+               "probed_rows": int(probed_rows), "visible_rows": int(visible_rows), "document_classes": n_cls,
+               "list_bytes": int(b_lists),
+               "probe": {"kernels": "rk_ivf_keys_kernel + rk_ivf_order_kernel", "ms": rf["probe_ms"],
+                         "fp32_TFLOPs": fl_centres / pms / 1e12 if pms > 0 else None,
+                         "centre_bytes_once": int(ivf_lists * rb_), "centre_bytes_per_query_definition": int(b_centres),
+                         "survey_8d_GBps_both_kernels": (b_centres + b_lists) / (lms + pms) / 1e9 if lms + pms > 0 else None},
+               "note": "SURVEY.md 8(d) counts the centres once per query (lists x 4d); the batched probe reads them once per "
+                       "16 queries from L2, so that figure would exceed the HBM peak and is reported only under probe; the "
+                       "list scan reads only the rows the user may see (one extent per visible document class and probed list); "
+                       "a read-only stream can exceed the copy-measured peak, and queries probing the same lists share rows in L2 "
+                       "(traffic = dram bytes of the launch)"})
+    if world > 1:
+        rf["probe"]["ms"] = None
+        rf["probe"]["fp32_TFLOPs"] = None
+        rf["probe"]["note"] = ("N > 1: the list choice is split by query across the ranks (nq / N queries each) and "
+                               "all-gathered; its time is part of stages_ms.local_search")
+        line["run"]["ivf_sharding"] = ("centres trained on rank 0's stripe and broadcast; every list's rows striped with "
+                                       "their documents (d mod N); list choice split by query + all-gather")
+    line["run"].update({"recall_at_100": rec, "ivf_build_s": ivf_build_s,
+                        "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
+
+
+def ivf_cpu_leg(line, args, wl, ix, dev, tid, doc, ur, dr, qusers, Q, main_r, ivf_lists, rows, dim, CH):
+    """C4's CPU leg: the oracle's restatement of ivfscan.c with the reference's distance loops, same centres and lists, on a
+    sample of the queries; only the rows of the lists the sample probes are brought to the host.  Also the full-size parity
+    check of the step, and recall@k of the sample against the ORACLE's exact filtered top-k."""
+    from oracle import oracle as orc
+    from tests.util import assert_topk_matches
+    S = min(args.nq, 32)
+    m = orc.METRIC_L2 if wl["metric"] == "l2" else orc.METRIC_IP
+    centers, row_list = ix.ivf_info(rows)
+    Qn = Q.cpu().numpy()[:S]
+    need = set()
+    for q in Qn:
+        need.update(int(x) for x in orc.ivf_order_lists(centers, q, m, args.nprobe)[0])
+    need_rows = np.flatnonzero(np.isin(row_list, np.fromiter(need, dtype=np.uint32)))
+    X_sub = np.empty((len(need_rows), dim), dtype=np.float32)
+    for a0 in range(0, len(need_rows), CH):
+        X_sub[a0:a0 + CH] = gen_rows(wl, need_rows[a0:a0 + CH], dev).cpu().numpy()
+    off, lrows = orc.ivf_lists_csr(row_list[need_rows], ivf_lists)
+    tid_sub, doc_sub = tid[need_rows], np.asarray(doc)[need_rows]
+    roles_of, docs_of = {}, {}
+    for u, r in ur:
+        roles_of.setdefault(int(u), set()).add(int(r))
+    for d_, r in dr:
+        docs_of.setdefault(int(r), []).append(int(d_))
+    c_tid = np.full((S, args.k), np.uint64(0xFFFFFFFFFFFFFFFF), dtype=np.uint64)
+    c_dist = np.full((S, args.k), np.inf)
+    c_cnt = np.zeros(S, dtype=np.int32)
+    t0 = time.perf_counter()
+    for i in range(S):
+        vis = np.zeros(int(doc_sub.max()) + 2, dtype=np.uint8)
+        for r in roles_of.get(int(qusers[i]), ()):
+            dd = np.asarray(docs_of.get(r, []), dtype=np.int64)
+            vis[dd[dd < len(vis)]] = 1
+        (t_, _, d_), = orc.ivf_scan(X_sub, tid_sub, centers, off, lrows, Qn[i], m, probes=args.nprobe, allowed=vis[doc_sub])
+        n = min(args.k, len(t_))
+        c_tid[i, :n], c_dist[i, :n], c_cnt[i] = t_[:n], d_[:n], n
+    dtc = time.perf_counter() - t0
+    g_tid = main_r["outs_h"][0].numpy().view(np.uint64)[:S]
+    g_dist, g_cnt = main_r["outs_h"][2].numpy()[:S], main_r["outs_h"][3].numpy()[:S]
+    note = "within 1e-5 relative; ids identical outside oracle ties of that width"
+    try:
+        assert_topk_matches((g_tid, None, g_dist, g_cnt), (c_tid, None, c_dist, None, c_cnt), exact=False)
+        ok = True
+    except AssertionError as e:
+        ok = False
+        note += " — MISMATCH: " + str(e)[:200]
+    line["cpu_baseline"] = {
+        "value": S / dtc, "unit": "queries/s", "cores": 1, "kind": "port",
+        "sample": f"{S} of the step's {args.nq} queries, nprobe {args.nprobe}, the oracle's restatement of ivfscan.c (centre scoring, "
+                  f"full sort of the probed lists' visible tuples) on one thread of {cpu_model()}, the GPU build's centres and lists; "
+                  "no PostgreSQL page/tuple/fmgr overhead",
+        "gpu_ids_match": ok, "gpu_distances": note, "gpu_distances_match": ok}
+
+
+def leg_summary(line):
+    """What a short leg contributes to the default line's "workloads" object."""
+    rf = line["roofline"]
+    out = {"workload": line["config"]["workload"], "value": line["value"], "unit": line["unit"], "ms_per_step": line["ms_per_step"],
+           "steps": line["steps"], "e2e": line["e2e"]["value"], "engine": line["run"]["engine"], "dtype": line["dtype"],
+           "roofline": {k: rf.get(k) for k in ("bound", "kernel", "achieved", "peak", "unit", "frac", "kernel_ms", "dram_frac", "l2_share", "traffic",
+                                               "plan", "frac_of_measured_bf16_sustained") if rf.get(k) is not None},
+           "gpu_launches": line["gpu_launches"], "recall_at_100": line["run"].get("recall_at_100")}
+    if "cpu_baseline" in line:
+        cb = line["cpu_baseline"]
+        out["cpu_baseline"] = {k: cb.get(k) for k in ("value", "cores", "kind", "gpu_ids_match", "gpu_distances_match")}
+    if "batched" in line:
+        b = line["batched"]
+        out["batched"] = {"value": b["value"], "e2e": b["e2e"]["value"], "frac": b["roofline"]["frac"], "bound": b["roofline"]["bound"],
+                          "identical_to_headline_results": b["identical_to_headline_results"]}
+    if line["config"].get("nprobe"):
+        out["nprobe"] = line["config"]["nprobe"]
+    return out
+
+
+def main():
+    args = parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.rows:
+        wl["rows"] = args.rows
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.cuda.set_stream(torch.cuda.Stream(dev))     # a real stream: torch events, NCCL and the engine share it
+    env = {"rank": rank, "world": world, "local_rank": local_rank, "dev": dev}
+    t_start = time.perf_counter()
+    line = run_b200(args, args.workload, env, args.steps, cpu_budget_s=20.0)
+
+    # the default line (C3, one GPU) also carries short legs of the other single-GPU configs of BASELINE.json
+    if rank == 0 and world == 1 and args.workload == "c3" and not args.rows and not args.no_legs:
+        legs = {}
+        for key in ("c1", "c2", "c5", "c4"):
+            if time.perf_counter() - t_start > args.legs_budget_s:
+                legs[key] = {"skipped": "time budget of the default run (%d s) used up" % args.legs_budget_s}
+                continue
+            try:
+                legs[key] = leg_summary(run_b200(args, key, env, min(args.steps, 5), cpu_budget_s=3.0, leg=True))
+            except Exception as e:            # a failing leg must not take the headline line with it
+                legs[key] = {"error": repr(e)[:300]}
+        line["workloads"] = legs
+    if rank == 0:
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

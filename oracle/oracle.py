@@ -28,7 +28,8 @@ _DISTFN = C.CFUNCTYPE(C.c_float, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_fl
 def build(force: bool = False) -> None:
     """Compile the C restatement (and oracle/_ref when /root/reference is present)."""
     if force or not os.path.exists(os.path.join(_HERE, "liboracle.so")) or \
-            os.path.getmtime(os.path.join(_HERE, "liboracle.so")) < os.path.getmtime(os.path.join(_HERE, "oracle.c")):
+            os.path.getmtime(os.path.join(_HERE, "liboracle.so")) < os.path.getmtime(os.path.join(_HERE, "oracle.c")) or \
+            not os.path.exists(os.path.join(_HERE, "libsynthgen.so")):
         subprocess.run(["make", "-C", _HERE, "all"], check=True, capture_output=True)
 
 
@@ -317,6 +318,25 @@ def ivf_scan(X, tid, centers, list_off, list_rows, q, metric, probes, max_probes
         if limit is not None and produced >= limit:
             break
     return batches
+
+
+def gen_sift(rows: np.ndarray, dim: int = 128, seed: int = 1234, n_clusters: int = 4096, nthreads: int = 1,
+             out: Optional[np.ndarray] = None) -> np.ndarray:
+    """SIFT-shaped synthetic rows on the CPU (synthgen.c), bit-identical to the package's torch generator
+    (synth.sift_like); used by `bench.py --impl reference` so that arm needs neither the GPU nor librbacknn.so."""
+    build()
+    if "synthgen" not in _libs:
+        L = C.CDLL(os.path.join(_HERE, "libsynthgen.so"))
+        L.orc_gen_sift.restype = C.c_int
+        L.orc_gen_sift.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int]
+        _libs["synthgen"] = L
+    rows = np.ascontiguousarray(rows, dtype=np.int64)
+    if out is None:
+        out = np.empty((len(rows), dim), dtype=np.float32)
+    assert out.flags.c_contiguous and out.shape == (len(rows), dim) and out.dtype == np.float32
+    if _libs["synthgen"].orc_gen_sift(rows.ctypes.data, len(rows), dim, seed, n_clusters, out.ctypes.data, nthreads) != 0:
+        raise MemoryError("orc_gen_sift")
+    return out
 
 
 def recall(truth: Iterable[int], pred: Iterable[int]) -> float:

@@ -7,8 +7,26 @@ Layout:
   harness.py   mirror of the reference's Python search / ground-truth functions for this path
   synth.py     seeded synthetic corpora, RBAC generators and query sets
   sharded.py   one-process-per-GPU document-striped search with an all-gather merge
+
+The engine names (Index, Scan, METRIC_L2, ...) resolve on first use and load librbacknn.so then (ImportError
+if it is missing: there is no fallback).  `import vectorsearch_rbac_b200.synth` alone — the input generators, which
+`bench.py --impl reference` needs — does not load the library.
 """
-from . import _lib  # noqa: F401
-from .engine import Index, Scan, RkError, METRIC_L2, METRIC_IP, FILTER_PARTITION, FILTER_BITMASK, FILTER_NONE  # noqa: F401
-from .engine import ENGINE_AUTO, ENGINE_SCAN, ENGINE_TENSOR  # noqa: F401
-from .engine import LAYOUT_AUTO, LAYOUT_ROLE, LAYOUT_COMBINATION, LAYOUT_DYNAMIC  # noqa: F401
+import importlib as _importlib
+
+_ENGINE_NAMES = ("Index", "Scan", "RkError", "METRIC_L2", "METRIC_IP", "FILTER_PARTITION", "FILTER_BITMASK", "FILTER_NONE",
+                 "ENGINE_AUTO", "ENGINE_SCAN", "ENGINE_TENSOR", "LAYOUT_AUTO", "LAYOUT_ROLE", "LAYOUT_COMBINATION",
+                 "LAYOUT_DYNAMIC")
+_SUBMODULES = ("_lib", "engine", "harness", "synth", "sharded", "dynamic_layout", "build")
+
+
+def __getattr__(name):
+    if name in _ENGINE_NAMES:
+        return getattr(_importlib.import_module(__name__ + ".engine"), name)
+    if name in _SUBMODULES:
+        return _importlib.import_module(__name__ + "." + name)
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+
+
+def __dir__():
+    return sorted(list(globals()) + list(_ENGINE_NAMES) + list(_SUBMODULES))

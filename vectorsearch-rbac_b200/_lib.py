@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librbacknn.so")
+# RBACKNN_LIB: another build of the same library (kernel experiments); the default is the in-tree build
+LIB_PATH = os.environ.get("RBACKNN_LIB") or os.path.join(_HERE, "librbacknn.so")
 
 RK_ABI_VERSION = 2
 

@@ -31,6 +31,13 @@
 #define RK_CKPT_ROWS 512     // consumer warps meet at least every this many rows of a segment
 #define RK_EPL 4             // extents resolved per producer lane per step
 
+#ifndef RK_SCAN_XPRE
+#define RK_SCAN_XPRE 0
+#endif
+#ifndef RK_SCAN_SEL8
+#define RK_SCAN_SEL8 0
+#endif
+
 #define RK_FLAG_FIRST 1u
 #define RK_FLAG_LAST 2u
 #define RK_FLAG_END 4u
@@ -76,7 +83,11 @@ size_t rk_scan_smem_bytes(int row_bytes, int tile_rows, int nstages)
 // ---------------------------------------------------------------------------------------------
 // producer
 
+template <bool FUSED>
 struct RkProducer {
+    // cross-segment prefetch of the next segment's first extents: on in the fused single-query kernel, whose segments are few
+    // and whose start-up latency is what matters; the batch kernel has no registers left for it (RK_SCAN_XPRE to try)
+    static constexpr bool XPRE = FUSED || RK_SCAN_XPRE;
     const RkScanParams &p;
     const RkScanSmem &L;
     unsigned char *smem;
@@ -100,7 +111,7 @@ struct RkProducer {
 
     __device__ __forceinline__ void close_tile(uint32_t flags)
     {
-        if (first && !p.fused) {
+        if (first && !FUSED) {
             flags |= RK_FLAG_FIRST;
             if (lane == 0) {
                 rk_bulk_g2s(smem + L.off_qslot + (size_t) stage * p.row_bytes,
@@ -159,7 +170,7 @@ struct RkProducer {
     int dbg_n;
     __device__ __forceinline__ void stamp()
     {
-        if (p.fused && p.fz_dbg && blockIdx.x == 0 && lane == 0 && dbg_n < 256) p.fz_dbg[(size_t) (gridDim.x + 1) * 8 + 256 + dbg_n++] = rk_globaltimer();
+        if (FUSED && p.fz_dbg && blockIdx.x == 0 && lane == 0 && dbg_n < 256) p.fz_dbg[(size_t) (gridDim.x + 1) * 8 + 256 + dbg_n++] = rk_globaltimer();
     }
     ExtStep pre;            // first step of the next segment, requested while the previous segment's last rows were issued
     bool pre_valid;
@@ -241,13 +252,13 @@ struct RkProducer {
             const uint64_t *um = p.qmask + (size_t) query * p.mask_words;
             uint64_t run_start = 0, run_len = 0;
             ExtStep x;
-            if (pre_valid) x = pre; else if (s.ext_lo < s.ext_hi) ext_load(s, s.ext_lo, x);
-            pre_valid = false;
+            if (XPRE && pre_valid) x = pre; else if (s.ext_lo < s.ext_hi) ext_load(s, s.ext_lo, x);
+            if (XPRE) pre_valid = false;
             for (uint32_t eb = s.ext_lo; eb < s.ext_hi; eb += 32 * RK_EPL) {
                 ExtStep nx;
                 if (eb + 32 * RK_EPL < s.ext_hi) {
                     ext_load(s, eb + 32 * RK_EPL, nx);
-                } else if (next && next->kind == RK_SEG_EXTENTS && next->ext_lo < next->ext_hi) {
+                } else if (XPRE && next && next->kind == RK_SEG_EXTENTS && next->ext_lo < next->ext_hi) {
                     ext_load(*next, next->ext_lo, nx);
                     pre_valid = true;
                 }
@@ -310,7 +321,7 @@ struct RkProducer {
                 if (eb == s.ext_lo) stamp();
                 x = nx;
             }
-            if (pre_valid) pre = x;
+            if (XPRE && pre_valid) pre = x;
             if (run_len) emit_run(run_start, run_len);
         } else {  // RK_SEG_ROWMASK
             // Rows of a store that is NOT sorted by document (IVF lists): the role mask is reached
@@ -539,7 +550,10 @@ struct RkInlineQuery {
     float v[RK_INLINE_Q];
 };
 
-template <int METRIC, bool WIDE>
+// FUSED / LB are compile-time so that the batch kernel (neither) carries none of the single-query epilogue's or the
+// streaming lower bound's code and registers: at 288 threads the register file allows 168 per thread, and the batch
+// kernel's inner loop sits right at that limit.
+template <int METRIC, bool WIDE, bool FUSED, bool LB>
 __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float *inline_q)
 {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -571,7 +585,7 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
 
     if (warp == RK_CONS_WARPS) {
         // ===================== producer warp =====================
-        RkProducer pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, false, true, rk_policy_evict_first(),
+        RkProducer<FUSED> pr{p, L, smem, full, empty, meta, lane, 0, 0u, 0u, 0u, 0u, 0u, false, true, rk_policy_evict_first(),
                       rk_policy_evict_last()};
         auto seg_at = [&](uint32_t pos) -> uint32_t { return p.seg_order ? p.seg_order[pos] : pos; };
         pr.pre_valid = false;
@@ -630,11 +644,11 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
     // k-th key": fall back to the exact (key, tid) sort that keeps precisely k
     const int tie_limit = p.k + ((int) trigger - p.k) / 2;
 
-    unsigned long long *dbg = p.fused && p.fz_dbg ? p.fz_dbg + (size_t) blockIdx.x * 8 : nullptr;
+    unsigned long long *dbg = FUSED && p.fz_dbg ? p.fz_dbg + (size_t) blockIdx.x * 8 : nullptr;
     if (dbg && t == 0) dbg[0] = rk_globaltimer();                   // CTA start
     bool dbg_first = dbg != nullptr;
     int dbg_tiles = 0;
-    if (p.fused) {
+    if (FUSED) {
         // one query for the whole launch: the consumers fetch it themselves — from the kernel parameters when it rides
         // there, else from HBM — while the producer resolves its first extents
         float4 *qd = reinterpret_cast<float4 *>(smem + L.off_qcur);
@@ -652,7 +666,7 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
     uint32_t phase = 0;
     int since_ckpt = 0;
     // a long single-query scan sets its threshold early: until the first compaction every row is a candidate
-    const uint32_t trigger0 = p.fused && p.fz_seed > 0 && (uint32_t) p.fz_seed < trigger ? (uint32_t) p.fz_seed : trigger;
+    const uint32_t trigger0 = FUSED && p.fz_seed > 0 && (uint32_t) p.fz_seed < trigger ? (uint32_t) p.fz_seed : trigger;
     bool seeded = false;
     for (;;) {
         rk_mbar_wait(&full[stage], phase);
@@ -723,7 +737,7 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
             const uint32_t kb = rk_float_to_key(METRIC == 0 ? sb : -sb);
             bool ca = lead && va && ka <= tau;
             bool cb2 = lead && vb && kb <= tau;
-            if (p.lb_on) {
+            if (LB) {
                 // a streaming scan resumes after (lb_key, lb_tid): everything up to that pair was already returned
                 if (ca && (ka < p.lb_key || (ka == p.lb_key && p.store.tid[rid[ra]] <= p.lb_tid))) ca = false;
                 if (cb2 && (kb < p.lb_key || (kb == p.lb_key && p.store.tid[rid[rb]] <= p.lb_tid))) cb2 = false;
@@ -745,7 +759,7 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
         // a segment whose successor on this CTA continues the same single-partition query ends without a final
         // select: the buffer and the threshold carry over, and this segment's own list stays empty
         // (fused single-query mode: every segment is the same query's, the buffer lives until the work list is drained)
-        const bool cont = last && ((m.flags & RK_FLAG_CONT) != 0 || p.fused);
+        const bool cont = last && ((m.flags & RK_FLAG_CONT) != 0 || FUSED);
         const bool fin = last && !cont;
         if (last || ++since_ckpt == ckpt) {
             since_ckpt = 0;
@@ -758,7 +772,8 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
                     // 12-bit digits over the spread of the keys; the 4096-bin histogram lies over the tuple-id slots, which
                     // are only filled for the exact sort below.  A compaction in mid-segment needs a threshold only (loose:
                     // up to 63 keys above the k-th stay), the end of a segment the exact k-th key.
-                    tau = rk_radix_kth_wide(cb.key, n, p.k, reinterpret_cast<uint32_t *>(cb.tid), s_wsum, s_sel, s_mm, t, csync, !fin);
+                    if (!FUSED && RK_SCAN_SEL8) tau = rk_radix_kth(cb.key, n, p.k, s_hist, s_wsum, s_sel, t, csync);
+                    else tau = rk_radix_kth_wide(cb.key, n, p.k, reinterpret_cast<uint32_t *>(cb.tid), s_wsum, s_sel, s_mm, t, csync, !fin);
                     n = rk_compact_le(cb, n, tau, t, s_wsum, csync);
                 }
                 if (fin || n > tie_limit) {
@@ -787,11 +802,11 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
                 }
                 csync();
             }
-            if (cont && t == 0 && !p.fused) p.cand_count[m.seg] = 0;
+            if (cont && t == 0 && !FUSED) p.cand_count[m.seg] = 0;
         }
         if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
     }
-    if (!p.fused) return;
+    if (!FUSED) return;
 
     // ===================== fused single-query epilogue =====================
     // (1) Cooperative threshold.  Every CTA publishes the r-th smallest key it found (r ~ 3k / grid): B = the largest such
@@ -1035,17 +1050,17 @@ __device__ __forceinline__ void rk_scan_body(const RkScanParams &p, const float 
     }
 }
 
-template <int METRIC, bool WIDE>
+template <int METRIC, bool WIDE, bool FUSED, bool LB>
 __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_kernel(const RkScanParams p)
 {
-    rk_scan_body<METRIC, WIDE>(p, nullptr);
+    rk_scan_body<METRIC, WIDE, FUSED, LB>(p, nullptr);
 }
 
-template <int METRIC, bool WIDE>
+template <int METRIC, bool WIDE, bool LB>
 __global__ void __launch_bounds__(RK_SCAN_THREADS, 1) rk_scan_single_kernel(const __grid_constant__ RkScanParams p,
                                                                             const __grid_constant__ RkInlineQuery iq)
 {
-    rk_scan_body<METRIC, WIDE>(p, iq.v);
+    rk_scan_body<METRIC, WIDE, true, LB>(p, iq.v);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1083,35 +1098,58 @@ void rk_scan_geometry(int dim_pad, int *tile_rows, int *nstages, size_t *smem)
     *smem = rk_scan_smem_bytes(row_bytes, tr, ns);
 }
 
+template <typename K>
+static cudaError_t rk_scan_attr(K kern, bool *done)
+{
+    if (*done) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) *done = true;
+    return e;
+}
+
+// variant index: metric | wide << 1 | lower bound << 2 | fused << 3
+template <int V>
+static cudaError_t rk_launch_scan_variant(const RkScanParams &p, int grid, size_t smem, cudaStream_t stream, bool *attr_done,
+                                          const float *inline_q_host)
+{
+    constexpr int M = V & 1;
+    constexpr bool W = (V & 2) != 0, LB = (V & 4) != 0, F = (V & 8) != 0;
+    if (F && inline_q_host) {
+        // fused single-query launch with the query in the parameters
+        cudaError_t e = rk_scan_attr(rk_scan_single_kernel<M, W, LB>, attr_done + 16);
+        if (e != cudaSuccess) return e;
+        RkInlineQuery iq;
+        memcpy(iq.v, inline_q_host, (size_t) p.row_bytes);
+        rk_scan_single_kernel<M, W, LB><<<grid, RK_SCAN_THREADS, smem, stream>>>(p, iq);
+        return cudaGetLastError();
+    }
+    cudaError_t e = rk_scan_attr(rk_scan_kernel<M, W, F, LB>, attr_done);
+    if (e != cudaSuccess) return e;
+    rk_scan_kernel<M, W, F, LB><<<grid, RK_SCAN_THREADS, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t rk_launch_scan(const RkScanParams &p, int device, cudaStream_t stream, int grid_override, const float *inline_q_host)
 {
     const size_t smem = rk_scan_smem_bytes(p.row_bytes, p.tile_rows, p.nstages);
-    static bool attr_set[64][8];
+    static bool attr_set[64][32][2];
     const bool wide = p.tile_rows < 64;
     const int grid = grid_override > 0 ? grid_override : rk_device_sm_count(device);
-    if (inline_q_host) {
-        // fused single-query launch with the query in the parameters
-        auto kern = wide ? (p.metric == 0 ? rk_scan_single_kernel<0, true> : rk_scan_single_kernel<1, true>)
-                         : (p.metric == 0 ? rk_scan_single_kernel<0, false> : rk_scan_single_kernel<1, false>);
-        const int ai = 4 | (p.metric & 1) | (wide ? 2 : 0);
-        if (!attr_set[device & 63][ai]) {
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            if (e != cudaSuccess) return e;
-            attr_set[device & 63][ai] = true;
-        }
-        RkInlineQuery iq;
-        memcpy(iq.v, inline_q_host, (size_t) p.row_bytes);
-        kern<<<grid, RK_SCAN_THREADS, smem, stream>>>(p, iq);
-        return cudaGetLastError();
+    const int v = (p.metric & 1) | (wide ? 2 : 0) | (p.lb_on ? 4 : 0) | (p.fused ? 8 : 0);
+    bool *done = &attr_set[device & 63][v][0];
+    // (attr_done + 16 in the variant = the single-kernel's flag: lay the two flags of a variant 16 bools apart)
+    static bool attr_single[64][32];
+    bool flags[17] = {done[0]};
+    flags[16] = attr_single[device & 63][v];
+    cudaError_t e;
+    switch (v) {
+#define RK_SCAN_CASE(V) case V: e = rk_launch_scan_variant<V>(p, grid, smem, stream, flags, inline_q_host); break;
+        RK_SCAN_CASE(0) RK_SCAN_CASE(1) RK_SCAN_CASE(2) RK_SCAN_CASE(3) RK_SCAN_CASE(4) RK_SCAN_CASE(5) RK_SCAN_CASE(6) RK_SCAN_CASE(7)
+        RK_SCAN_CASE(8) RK_SCAN_CASE(9) RK_SCAN_CASE(10) RK_SCAN_CASE(11) RK_SCAN_CASE(12) RK_SCAN_CASE(13) RK_SCAN_CASE(14) RK_SCAN_CASE(15)
+#undef RK_SCAN_CASE
+        default: return cudaErrorInvalidValue;
     }
-    auto kern = wide ? (p.metric == 0 ? rk_scan_kernel<0, true> : rk_scan_kernel<1, true>)
-                     : (p.metric == 0 ? rk_scan_kernel<0, false> : rk_scan_kernel<1, false>);
-    const int ai = (p.metric & 1) | (wide ? 2 : 0);
-    if (!attr_set[device & 63][ai]) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set[device & 63][ai] = true;
-    }
-    kern<<<grid, RK_SCAN_THREADS, smem, stream>>>(p);
-    return cudaGetLastError();
+    done[0] = flags[0];
+    attr_single[device & 63][v] = flags[16];
+    return e;
 }
