@@ -96,8 +96,13 @@ def parse_args():
     ap.add_argument("--engine", default="", choices=["", "scan", "tensor", "auto"], help="override the workload's headline engine")
     ap.add_argument("--nprobe", type=int, default=16, help="workload c4: lists probed per query")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--pipeline", action="store_true", help="N > 1: overlap a step's exchange (side stream) with the next step's scan")
+    ap.add_argument("--pipeline", action="store_true", help="(kept for compatibility: pipelining is the default with the peer exchange)")
+    ap.add_argument("--no-pipeline", action="store_true", help="N > 1: run scan, exchange and merge of a step back to back on one stream")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: peer = stores into the other GPUs' receive rings over NVLink + flags (rk_exchange.cu); nccl = all_gather_into_tensor")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
+    ap.add_argument("--emu-world", type=int, default=0, help="debug, one GPU: load only the stripe rank --emu-rank of this many ranks would hold")
+    ap.add_argument("--emu-rank", type=int, default=0)
     ap.add_argument("--no-single", action="store_true", help="skip the single-query legs (N = 1, tree RBAC workloads)")
     ap.add_argument("--single-reps", type=int, default=16)
     ap.add_argument("--no-legs", action="store_true", help="default c3 line at N = 1: skip the short legs of c1 / c2 / c5 / c4")
@@ -554,6 +559,9 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
     # ---- load this rank's shard ---------------------------------------------------------------
     tid, doc, ur, dr = build_rbac(wl)
     mine = np.flatnonzero(sharded.local_row_mask(doc, rank, world))
+    if args.emu_world > 1 and world == 1:
+        mine = np.flatnonzero(sharded.local_row_mask(doc, args.emu_rank, args.emu_world))
+        no_cpu = True
     ix = vr.Index(dim, metric=metric, device=local_rank, k_max=max(128, args.k))
     ix.reserve_rows(len(mine))
     ivf_lists = int(wl.get("ivf_lists", 0))
@@ -563,6 +571,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
     for a0 in range(0, len(mine), CH):
         idx = mine[a0:a0 + CH]
         xb = gen_rows(wl, idx, dev)
+        torch.cuda.current_stream(dev).synchronize()      # the engine loads on its own stream: the rows must be complete
         ix.load_rows_device(xb.data_ptr(), len(idx), tid[idx], doc[idx])
         if keep_host:
             X_host[idx] = xb.cpu().numpy()
@@ -593,6 +602,10 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
     stream = torch.cuda.current_stream(dev)
     sharded.use_torch_stream(ix, dev)
     searcher = sharded.ShardedSearcher(ix, rank, world, device=dev)
+    peer_ok = world > 1 and args.exchange == "peer" and searcher.enable_peer_exchange(args.nq, max(args.k, 1))
+    # with the peer exchange the merge of step i runs on a side stream under the scan of step i + 1 (no collective's CTAs
+    # compete with the persistent scan kernel); with NCCL the serial order measured faster (round 1) and stays the default
+    pipelined = world > 1 and not args.no_pipeline and (peer_ok or args.pipeline)
     ix.enable_timing(True)
     Qh = torch.empty((args.nq, dim), dtype=torch.float32, pin_memory=True)
     Qh.copy_(Q)
@@ -607,7 +620,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
         opts = vr.engine.make_opts(args.k, probes=args.nprobe if ivf_lists else 0, filter=flt, layout=layout, engine=eng)
         # N > 1: scan, all-gather and merge of a step run back to back on one stream (stages_ms reports each).  With
         # --pipeline the exchange of step i moves to a side stream under the scan of step i + 1.
-        step_fn = searcher.search_device_pipelined if (world > 1 and args.pipeline) else searcher.search_device
+        step_fn = searcher.search_device_pipelined if pipelined else searcher.search_device
         if ivf_lists and world == 1:
             def step_fn(Qd, users, o):       # the index-probe path of the C-ABI (one GPU)
                 bf = searcher._get_bufs(Qd.shape[0], o.k)
@@ -628,7 +641,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
             searcher.flush()
             e1.record(stream)
             barrier()
-        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary(), "stages": searcher.stage_ms(), "pipelined": world > 1 and args.pipeline}
+        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary(), "stages": searcher.stage_ms(), "pipelined": pipelined}
         searcher.stage_events = None
         if ivf_lists:
             ix.synchronize()                 # collects the last launch's probe / list-scan event times
@@ -759,7 +772,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32" if st["tensor_plan"] == 0 else "tf32 nomination + f32 exact re-score",
             "data": "synthetic",
             "config": make_config(wl, args, world),
-            "run": {"engine": engine_name, "rows_this_rank": int(len(mine)),
+            "run": {"engine": engine_name, "rows_this_rank": int(len(mine)), "segments": int(st["segments"]),
                     "recall_at_100": 1.0, "recall_note": "exact search; ids checked against the oracle on the cpu_baseline sample"},
             "roofline": roofline_of(main_r, engine_name),
             "e2e": {"value": args.nq * steps / main_r["dt_e2e"], "unit": "queries/s", "h2d_bytes_per_step": int(main_r["h2d"]),
@@ -774,8 +787,10 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
             # rank 0's mean device time per stage of a step (the all-gather also absorbs waiting for the slowest rank)
             line["stages_ms"] = main_r["stages"]
         if world > 1:
-            line["run"]["exchange"] = ("all-gather + merge of step i on a side stream, overlapping the scan of step i + 1"
-                                       if main_r["pipelined"] else "all-gather + merge after every scan, same stream")
+            line["run"]["exchange"] = searcher.exchange_kind + ("; merge of step i on a side stream under the scan of step i + 1"
+                                                                if main_r["pipelined"] else "; exchange + merge after every scan, same stream")
+            if peer_ok:
+                searcher._ex.status()                   # raises if any wait for a peer timed out
         if single is not None:
             line["single_query"] = single
         if batched_r is not None:
@@ -832,6 +847,9 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
                 "gpu_ids_match": ids_ok, "gpu_distances": dist_note, "gpu_distances_match": dist_ok}
             if not leg:
                 line["cpu_baseline"]["single_thread"] = cpu_single_thread(X_host, tid, parts, qparts, Qn, args.k, wl["metric"])
+    if searcher._ex is not None:
+        barrier()                      # no peer may still be writing into this rank's ring
+        searcher._ex.close()
     ix.close()
     del searcher, Q, Qh, X_host
     torch.cuda.empty_cache()
@@ -1021,7 +1039,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    torch.cuda.set_stream(torch.cuda.Stream(dev))     # a real stream: torch events, NCCL and the engine share it
+    torch.cuda.set_stream(torch.cuda.Stream(dev, priority=-1))     # a real stream: torch events, NCCL and the engine share it
     env = {"rank": rank, "world": world, "local_rank": local_rank, "dev": dev}
     t_start = time.perf_counter()
     line = run_b200(args, args.workload, env, args.steps, cpu_budget_s=20.0)

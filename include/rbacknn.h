@@ -247,6 +247,32 @@ int rk_merge_shards(rk_index *ix, size_t nq, int k, int n_shards, size_t shard_s
                     const float *d_key, const uint64_t *d_tid, const uint32_t *d_doc,
                     uint64_t *d_out_tid, uint32_t *d_out_doc, double *d_out_dist, int32_t *d_out_count);
 
+/* ---- peer exchange: the shard merge over NVLink peer memory, no collective library on the data path -------------
+ * Every rank owns a ring of `depth` receive slots ([world] packed shard results {key f32 | doc u32 | tid u64}[nq * k] each)
+ * with an arrival and an acknowledgement flag per (slot, rank).  rk_search_batch_shard_push searches this rank's shard
+ * into its own block of the next slot and a small kernel stores that block into every peer's slot and raises the peers'
+ * arrival flags; rk_merge_shards_pull waits (in the kernel, bounded) for all peers' flags of the oldest pushed step,
+ * merges, and acknowledges the slot.  Ranks meet only through those flags: the merge of step s may run on another stream
+ * under the scan of step s + 1, and a rank may run up to `depth` steps ahead of the slowest.  All ranks must make the
+ * same sequence of push / pull calls.  One process per GPU: exchange rk_exchange_get_handle's 64 bytes (a CUDA IPC
+ * handle) and rk_exchange_connect_ipc them; several GPUs in one process: rk_exchange_connect_ptr(rk_exchange_base). */
+typedef struct rk_exchange rk_exchange;
+int rk_exchange_create(rk_index *ix, size_t nq_max, int k_max, int world, int rank, int depth, rk_exchange **out);
+int rk_exchange_destroy(rk_exchange *ex);
+int rk_exchange_get_handle(rk_exchange *ex, void *handle64);
+void *rk_exchange_base(rk_exchange *ex);
+size_t rk_exchange_block_bytes(rk_exchange *ex);
+int rk_exchange_connect_ipc(rk_exchange *ex, int peer_rank, const void *handle64);
+int rk_exchange_connect_ptr(rk_exchange *ex, int peer_rank, void *peer_base, int peer_device);
+/* d_lists: NULL, or the IVFFlat list choice as for rk_search_batch_shard_probed.  Asynchronous on the index stream. */
+int rk_search_batch_shard_push(rk_index *ix, rk_exchange *ex, size_t nq, const float *dQ, const uint32_t *user_ids,
+                               const rk_scan_opts *o, const uint32_t *d_lists);
+/* cuda_stream: NULL = the index stream; another stream must be ordered after the matching push by the caller (an event). */
+int rk_merge_shards_pull(rk_index *ix, rk_exchange *ex, size_t nq, int k, void *cuda_stream, uint64_t *d_out_tid,
+                         uint32_t *d_out_doc, double *d_out_dist, int32_t *d_out_count);
+/* Synchronises cuda_stream (NULL = the index stream); RK_ERR_CUDA if a wait for a peer timed out since creation. */
+int rk_exchange_status(rk_exchange *ex, void *cuda_stream);
+
 /* ---- plumbing ------------------------------------------------------------------------------- */
 
 /* Run on the caller's CUDA stream (a cudaStream_t), e.g. torch's current stream. NULL = own stream. */

@@ -89,6 +89,26 @@ def _worker(rank, world, port, out_dir):
         assert fi.trained == (rank == 0)
         if rank != 0:
             np.testing.assert_array_equal(fi.given, expect)
+        # peer-exchange handshake (rk_exchange.cu's rings are CUDA; this checks who learns whose handle, and that one rank
+        # failing to map a ring sends EVERY rank back to the all-gather)
+        class FakeExchange:
+            depth = 4
+            def __init__(self, fail_connect=False): self.seen, self.closed, self.fail_connect = {}, False, fail_connect
+            def handle(self): return bytes([rank]) * 64
+            def connect_ipc(self, g, h):
+                if self.fail_connect:
+                    raise RuntimeError("cannot map")
+                self.seen[g] = h
+            def close(self): self.closed = True
+        sh2 = sharded.ShardedSearcher(None, rank, world, device=torch.device("cpu"), local_search=local_search, merge=merge)
+        fx = FakeExchange()
+        assert sh2.enable_peer_exchange(10, 15, make_exchange=lambda: fx) is True
+        assert sh2._ex is fx and fx.seen == {g: bytes([g]) * 64 for g in range(world) if g != rank}
+        assert "peer stores" in sh2.exchange_kind
+        sh3 = sharded.ShardedSearcher(None, rank, world, device=torch.device("cpu"), local_search=local_search, merge=merge)
+        fx3 = FakeExchange(fail_connect=(rank == 1))
+        assert sh3.enable_peer_exchange(10, 15, make_exchange=lambda: fx3) is False
+        assert sh3._ex is None and fx3.closed and "nccl" in sh3.exchange_kind
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
         dist.destroy_process_group()

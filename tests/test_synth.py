@@ -1,8 +1,12 @@
 """Host logic: the seeded generators follow the reference's procedures."""
+import os
+
 import numpy as np
 import torch
 
 from vectorsearch_rbac_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_sift_like_is_integer_valued_and_position_addressable():
@@ -57,3 +61,25 @@ def test_queries_seeded():
     r, u = synth.queries(1000, [5, 6, 7], 50, seed=7)
     r2, u2 = synth.queries(1000, [5, 6, 7], 50, seed=7)
     assert (r == r2).all() and (u == u2).all() and r.max() < 1000 and set(u.tolist()) <= {5, 6, 7}
+
+
+def test_cpu_generator_of_the_reference_arm_is_bit_identical():
+    """oracle/synthgen.c (what `bench.py --impl reference` fills its host matrix with, so that arm needs neither the GPU
+    nor librbacknn.so) against the package's torch generator, bit for bit."""
+    import torch
+    from oracle import oracle as orc
+    rows = np.concatenate([np.arange(0, 3000), np.random.default_rng(5).integers(0, 10_000_000, 3000)]).astype(np.int64)
+    for dim in (128, 96):
+        a = synth.sift_like(torch.as_tensor(rows), dim, 1234).numpy()
+        b = orc.gen_sift(rows, dim, 1234, nthreads=3)
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+
+
+def test_importing_the_generators_does_not_load_the_engine_library():
+    """`bench.py --impl reference` imports vectorsearch_rbac_b200.synth only: the package must not pull librbacknn.so in."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, %r); import vectorsearch_rbac_b200.synth; "
+            "assert 'librbacknn' not in open('/proc/self/maps').read(); "
+            "assert 'vectorsearch_rbac_b200._lib' not in sys.modules") % ROOT
+    subprocess.run([sys.executable, "-c", code], check=True)

@@ -67,6 +67,16 @@ SIGNATURES = {
     "rk_ivf_probe_device": (C.c_int, [_P, C.c_size_t, _P, C.POINTER(RkScanOpts), _P]),
     "rk_search_batch_shard_probed": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_merge_shards": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_size_t, _P, _P, _P, _P, _P, _P, _P]),
+    "rk_exchange_create": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_P)]),
+    "rk_exchange_destroy": (C.c_int, [_P]),
+    "rk_exchange_get_handle": (C.c_int, [_P, _P]),
+    "rk_exchange_base": (_P, [_P]),
+    "rk_exchange_block_bytes": (C.c_size_t, [_P]),
+    "rk_exchange_connect_ipc": (C.c_int, [_P, C.c_int, _P]),
+    "rk_exchange_connect_ptr": (C.c_int, [_P, C.c_int, _P, C.c_int]),
+    "rk_search_batch_shard_push": (C.c_int, [_P, _P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P]),
+    "rk_merge_shards_pull": (C.c_int, [_P, _P, C.c_size_t, C.c_int, _P, _P, _P, _P, _P]),
+    "rk_exchange_status": (C.c_int, [_P, _P]),
     "rk_set_stream": (C.c_int, [_P, _P]),
     "rk_synchronize": (C.c_int, [_P]),
     "rk_get_stats": (C.c_int, [_P, C.POINTER(RkStats)]),

@@ -179,6 +179,7 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
         t.single_fused = env_int("RK_SINGLE_FUSED", 1);
+        t.seg_cost_x10 = std::max(1, env_int("RK_SEG_COST_X10", 80));
         t.single_zero_copy = env_int("RK_SINGLE_ZERO_COPY", 1);
         t.single_segs = env_int("RK_SINGLE_SEGS", 0);
         t.single_seed = env_int("RK_SINGLE_SEED", 0);
@@ -206,6 +207,7 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
     else if (!strcmp(name, "single_fused")) t.single_fused = v;
+    else if (!strcmp(name, "seg_cost_x10")) t.seg_cost_x10 = std::max(1, v);
     else if (!strcmp(name, "single_zero_copy")) t.single_zero_copy = v;
     else if (!strcmp(name, "single_segs")) t.single_segs = v;
     else if (!strcmp(name, "single_seed")) t.single_seed = v;

@@ -104,6 +104,8 @@ struct RkScanParams {
     unsigned long long *fz_dbg;     // tuning aid (option single_debug): [grid + 1][8] globaltimer stamps of the launch's phases
 };
 
+#define RK_MAX_PEERS 16
+
 struct RkSelectParams {
     const uint32_t *cand_key;
     const uint64_t *cand_tid;
@@ -136,6 +138,18 @@ struct RkSelectParams {
     int32_t *out_count;
     float *out_key;             // exchange form: fp32 ordering value
     uint32_t *out_row;
+    // Peer exchange (rk_exchange.cu): the lists were written into this GPU's memory by the other ranks over NVLink.
+    // Before a block reads them it waits until wait_flag[j] has reached wait_seq for every j < wait_n except wait_self
+    // (system-scope acquire; bounded — on timeout *xerr is set and the block goes on); when the last block of the launch
+    // is done, ack_seq is stored to ack_flag[g] on every peer g < ack_n (system-scope release): the ring slot may be reused.
+    const uint32_t *wait_flag;
+    int wait_n, wait_self;
+    uint32_t wait_seq;
+    uint32_t *ack_flag[RK_MAX_PEERS];
+    int ack_n;
+    uint32_t ack_seq;
+    uint32_t *ack_done;         // local counter of finished blocks (returns to 0)
+    uint32_t *xerr;
 };
 
 // ---- batched tensor-core engine (rk_bscan.cu) ------------------------------------------------
@@ -240,6 +254,33 @@ __device__ __forceinline__ uint32_t rk_ld_volatile_u32(const uint32_t *p)
     uint32_t v;
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
+}
+
+// ---- system-scope flags between GPUs (peer exchange, rk_exchange.cu) ----
+__device__ __forceinline__ uint32_t rk_ld_acquire_sys(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void rk_st_release_sys(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Waits until *flag has reached seq (sequence numbers only grow; compared modulo 2^32).  Bounded: false after
+// RK_FLAG_TIMEOUT_NS, so a lost peer shows up as an error of the call, never as a hung GPU.
+#define RK_FLAG_TIMEOUT_NS 4000000000ull
+__device__ __forceinline__ bool rk_wait_flag_sys(const uint32_t *flag, uint32_t seq)
+{
+    if ((int32_t) (rk_ld_acquire_sys(flag) - seq) >= 0) return true;
+    const unsigned long long t_end = rk_globaltimer() + RK_FLAG_TIMEOUT_NS;
+    for (;;) {
+        if ((int32_t) (rk_ld_acquire_sys(flag) - seq) >= 0) return true;
+        if (rk_globaltimer() > t_end) return false;
+        __nanosleep(200);
+    }
 }
 
 __device__ __forceinline__ uint32_t rk_smem_u32(const void *p)

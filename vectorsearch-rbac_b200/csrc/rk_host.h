@@ -176,6 +176,7 @@ struct RkTuning {
     int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
     int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path
+    int seg_cost_x10 = 80;       // RK_SEG_COST_X10: fixed cost of one segment in 0.1 us (measured: 7.8 us on the 1/8 stripe of C3), for the segment sizing (segments per CTA = sqrt(T / 2o))
     int single_debug = 0;        // RK_SINGLE_DEBUG: print the fused launch's phase timeline (globaltimer stamps) to stderr
     int single_segs = 0;         // RK_SINGLE_SEGS: segments per CTA of a fused single-query plan (0 = chosen from the scan length)
     int single_seed = 0;         // RK_SINGLE_SEED: candidates a CTA of a long fused scan holds before its first compaction (0 = off)

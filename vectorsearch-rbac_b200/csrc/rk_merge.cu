@@ -65,6 +65,10 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
         return p.key_is_float ? rk_float_to_key(__uint_as_float(raw)) : raw;
     };
     if (t == 0) { s_count = 0; s_tau = RK_KEY_SENTINEL; }
+    if (p.wait_n > 0) {
+        // lists pushed by the peers: wait for every peer's arrival flag of this step
+        if (t < p.wait_n && t != p.wait_self && !rk_wait_flag_sys(p.wait_flag + t, p.wait_seq)) *p.xerr = 1u;
+    }
     __syncthreads();
     // upper bound of the k-th best: any list holding k entries proves tau <= its last key
     for (uint32_t j = t; j < nl; j += RK_SEL_THREADS) {
@@ -400,6 +404,18 @@ __global__ void __launch_bounds__(RK_SEL_THREADS) rk_select_kernel(const RkSelec
         }
     }
     if (t == 0 && p.out_count) p.out_count[q] = cnt;
+    if (p.ack_n > 0) {
+        // every block has read its lists: tell the peers that this ring slot may be overwritten
+        __syncthreads();
+        if (t == 0) {
+            __threadfence();
+            if (atomicAdd(p.ack_done, 1u) == gridDim.x - 1) {
+                *p.ack_done = 0;
+                __threadfence_system();
+                for (int g = 0; g < p.ack_n; g++) rk_st_release_sys(p.ack_flag[g], p.ack_seq);
+            }
+        }
+    }
 }
 
 cudaError_t rk_launch_select(const RkSelectParams &p, int nq, cudaStream_t stream)

@@ -178,11 +178,12 @@ static int build_exact_plan(rk_index *ix, Workspace &ws, size_t nq, const uint32
     for (size_t q = 0; q < nq; q++) ws.plan_single_partition = ws.plan_single_partition && per_q[q].size() <= 1;
     // Segment sizing.  A segment costs a few microseconds of fixed work (pipeline refill, final
     // compaction + sort) and the dynamic schedule wastes about half a segment per CTA at the tail,
-    // so with T = streaming time per CTA the best count per CTA is ~sqrt(T / 2o), o ~ 4 us.
+    // so with T = streaming time per CTA the best count per CTA is ~sqrt(T / 2o); o = 8 us (tune.seg_cost_x10; measured
+    // 7.8 us per segment on the 1/8 stripe of C3: the threshold restarts at +inf, ~1500 appends and one compaction follow).
     const uint64_t row_bytes = (uint64_t) ix->dim_pad * 4;
     const uint64_t sm = (uint64_t) ix->sm_count;
     const double t_cta_us = (double) total_rows * (double) row_bytes / (double) sm / 44.0e3;   // ~44 GB/s per SM
-    double per_cta = std::sqrt(t_cta_us / 8.0);
+    double per_cta = std::sqrt(t_cta_us / (2.0 * 0.1 * (double) ix->tune.seg_cost_x10));
     if (per_cta < 1.0) per_cta = 1.0;
     if (per_cta > 64.0) per_cta = 64.0;
     uint64_t target = (uint64_t) ((double) total_rows / ((double) sm * per_cta)) + 1;
@@ -841,6 +842,17 @@ static int search_batch_shard_locked(rk_index *ix, size_t nq, const float *dQ, c
     rc = check_device_queries(ix, ix->ws, nq, dQ, o);
     if (rc < 0) return rc;
     return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
+}
+
+// for rk_exchange.cu (the caller holds ix->batch_mu): d_lists != NULL = the caller supplies the IVFFlat list choice
+int rk_search_batch_shard_locked_for_exchange(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids, const rk_scan_opts *o,
+                                              const uint32_t *d_lists, float *d_key, uint64_t *d_tid, uint32_t *d_doc)
+{
+    if (d_lists && (!o || o->probes < 1)) return rk_fail(RK_ERR_INVALID, "rk_search_batch_shard_push: a list choice needs probes >= 1");
+    ix->ws.ext_probe = d_lists;
+    const int rc = search_batch_shard_locked(ix, nq, dQ, user_ids, o, d_key, d_tid, d_doc);
+    ix->ws.ext_probe = nullptr;
+    return rc;
 }
 
 extern "C" int rk_search_batch_shard(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids,

@@ -226,6 +226,55 @@ class Index:
         return {f: getattr(s, f) for f, _ in RkStats._fields_ if not f.startswith("reserved")}
 
 
+class Exchange:
+    """Ring of receive slots in this rank's HBM that the other ranks' GPUs write their shard results into over NVLink
+    (rk_exchange_* in include/rbacknn.h): push = local search + stores into every peer's slot + arrival flags; pull = wait
+    for the peers' flags inside the merge kernel + G-way merge + acknowledgement.  No collective call on the data path."""
+
+    def __init__(self, index: Index, nq_max: int, k_max: int, world: int, rank: int, depth: int = 4):
+        self.index, self.world, self.rank, self.depth = index, world, rank, depth
+        h = C.c_void_p()
+        _check(lib.rk_exchange_create(index._h, nq_max, k_max, world, rank, depth, C.byref(h)))
+        self._h = h
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            lib.rk_exchange_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def handle(self) -> bytes:
+        """CUDA IPC handle of the ring (64 bytes) for the other processes."""
+        buf = C.create_string_buffer(64)
+        _check(lib.rk_exchange_get_handle(self._h, buf))
+        return buf.raw
+
+    def base(self) -> int:
+        return int(lib.rk_exchange_base(self._h) or 0)
+
+    def connect_ipc(self, peer: int, handle: bytes) -> None:
+        _check(lib.rk_exchange_connect_ipc(self._h, peer, C.create_string_buffer(handle, 64)))
+
+    def connect_ptr(self, peer: int, base: int, device: int = -1) -> None:
+        _check(lib.rk_exchange_connect_ptr(self._h, peer, base, device))
+
+    def push(self, dQ_ptr: int, nq: int, user_ids: Sequence[int], opts: RkScanOpts, d_lists: int = 0) -> None:
+        users = _u32(user_ids)
+        _check(lib.rk_search_batch_shard_push(self.index._h, self._h, nq, dQ_ptr, users.ctypes.data, C.byref(opts), d_lists or None))
+
+    def pull(self, nq: int, k: int, d_out_tid: int, d_out_doc: int, d_out_dist: int, d_out_count: int, stream: int = 0) -> None:
+        _check(lib.rk_merge_shards_pull(self.index._h, self._h, nq, k, stream or None, d_out_tid, d_out_doc, d_out_dist, d_out_count))
+
+    def status(self, stream: int = 0) -> None:
+        """Synchronises the stream; raises if a wait for a peer timed out."""
+        _check(lib.rk_exchange_status(self._h, stream or None))
+
+
 class Scan:
     """begin / rescan / gettuple / endscan — the pgvector index-scan contract
     (pgvector/src/ivfflat.h:335-338, ivfscan.c:241-406)."""

@@ -16,6 +16,11 @@ IndexShards.cpp:197-256).  Here:
 A physical row lives on exactly one rank, so the merge needs no dedup; ties are broken by tuple id
 exactly as on one GPU, which makes the result independent of G.
 
+The exchange itself has two forms: NCCL (`all_gather_into_tensor`, the plumbing default on CPU / gloo) and the peer
+exchange (`enable_peer_exchange`: every rank's select output is stored straight into the other GPUs' receive rings over
+NVLink and the merge kernel waits on arrival flags — rk_exchange.cu), which takes the collective, its launch and its
+implicit barrier off the data path so that the merge of step i runs under the scan of step i + 1.
+
 `local_search` / `merge` are injectable so the exchange logic is testable with the gloo backend on
 CPU (tests/test_sharded_gloo.py); the defaults are the CUDA paths and there is no CPU fallback.
 """
@@ -95,6 +100,8 @@ class ShardedSearcher:
         self._bufs = {}
         # optional per-stage CUDA events of every call (local search | all-gather | merge), for bench.py's "stages_ms"
         self.stage_events = None
+        self._ex = None                  # engine.Exchange once enable_peer_exchange succeeded on every rank
+        self.exchange_kind = "nccl all_gather_into_tensor" if world > 1 else "none (one GPU)"
 
     def stage_ms(self):
         """Mean device time of the three stages over the calls recorded since stage_events was last reset."""
@@ -144,6 +151,57 @@ class ShardedSearcher:
         self.index.merge_shards(nq, k, self.world, base, base + 8 * n, base + 4 * n, o_tid.data_ptr(), o_doc.data_ptr(),
                                 o_dist.data_ptr(), o_cnt.data_ptr(), shard_stride_bytes=packed_bytes(nq, k))
 
+    # -- peer exchange -----------------------------------------------------------------------
+    def enable_peer_exchange(self, nq_max: int, k_max: int, depth: int = 4, make_exchange: Optional[Callable] = None) -> bool:
+        """Sets up the NVLink peer exchange (one process per GPU: the rings' CUDA IPC handles travel through
+        all_gather_object).  All ranks must call it.  Returns False — and leaves the NCCL all-gather in place — unless every
+        rank could map every other rank's ring."""
+        if self.world == 1:
+            return False
+        make_exchange = make_exchange or (lambda: _engine.Exchange(self.index, nq_max, k_max, self.world, self.rank, depth))
+        ex, ok = None, 1
+        try:
+            ex = make_exchange()
+            mine = ex.handle()
+        except Exception:
+            ok, mine = 0, b""
+        handles = [None] * self.world
+        dist.all_gather_object(handles, mine, group=self.group)
+        if ok:
+            try:
+                for g, h in enumerate(handles):
+                    if g != self.rank:
+                        if not h:
+                            raise RuntimeError("peer without a ring")
+                        ex.connect_ipc(g, h)
+            except Exception:
+                ok = 0
+        oks = [None] * self.world
+        dist.all_gather_object(oks, ok, group=self.group)
+        if not all(oks):
+            if ex is not None:
+                ex.close()
+            return False
+        self._ex = ex
+        self.exchange_kind = "peer stores over NVLink into every rank's receive ring + arrival flags (rk_exchange.cu), depth %d" % depth
+        return True
+
+    def _peer_push(self, dQ: torch.Tensor, users: np.ndarray, opts) -> int:
+        """Local search into this rank's block of the next ring slot + push to the peers.  Returns the ring position.  The
+        slot's previous use (depth steps ago) may still be read by a merge on the side stream: order after it."""
+        if not hasattr(self, "_ring_done"):
+            self._ring_done, self._ring_n = [None] * self._ex.depth, 0
+        r = self._ring_n % self._ex.depth
+        self._ring_n += 1
+        if self._ring_done[r] is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._ring_done[r])
+            self._ring_done[r] = None
+        lists = 0
+        if int(opts.probes) > 0 and self.shard_probe:
+            lists = self._cuda_probe_exchange(dQ, opts).data_ptr()
+        self._ex.push(dQ.data_ptr(), dQ.shape[0], users, opts, lists)
+        return r
+
     # -- buffers -----------------------------------------------------------------------------
     def _get_bufs(self, nq: int, k: int, which: int = 0):
         keyb = (nq, k, which)
@@ -170,6 +228,15 @@ class ShardedSearcher:
         rec = self.stage_events is not None and self.device.type == "cuda"
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if rec else None
         if rec: ev[0].record()
+        if self._ex is not None:
+            # peer exchange, same stream: the merge kernel itself waits for the peers' arrival flags
+            self._peer_push(dQ, users, opts)
+            if rec: ev[1].record(); ev[2].record()
+            self._ex.pull(nq, k, b["tid"].data_ptr(), b["doc"].data_ptr(), b["dist"].data_ptr(), b["cnt"].data_ptr())
+            if rec:
+                ev[3].record()
+                self.stage_events.append(tuple(ev))
+            return b["tid"], b["doc"], b["dist"], b["cnt"]
         self._local_search(dQ, users, opts, b["send"])
         if rec: ev[1].record()
         if self.world > 1:
@@ -195,13 +262,36 @@ class ShardedSearcher:
         nq, k = dQ.shape[0], opts.k
         users = np.ascontiguousarray(users, dtype=np.uint32)
         if not hasattr(self, "_side"):
-            self._side = torch.cuda.Stream(device=self.device)
+            # lower priority than the stream the scans run on: the merge's blocks fill SMs as the persistent scan's CTAs retire
+            self._side = torch.cuda.Stream(device=self.device, priority=0)
             self._pipe_n = 0
             self._pipe_done = [None, None]
         s = self._pipe_n & 1
         self._pipe_n += 1
         b = self._get_bufs(nq, k, s)
         main = torch.cuda.current_stream(self.device)
+        if self._ex is not None:
+            # the outputs of set s were last written by the merge issued two calls ago: same side stream, so already ordered
+            rec = self.stage_events is not None
+            ev4 = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if rec else None
+            if rec: ev4[0].record(main)
+            ring = self._peer_push(dQ, users, opts)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            if rec: ev4[1].record(main)
+            self._side.wait_event(ev)
+            with torch.cuda.stream(self._side):
+                if rec: ev4[2].record(self._side)
+                self._ex.pull(nq, k, b["tid"].data_ptr(), b["doc"].data_ptr(), b["dist"].data_ptr(), b["cnt"].data_ptr(),
+                              stream=self._side.cuda_stream)
+                if rec: ev4[3].record(self._side)
+                done = torch.cuda.Event()
+                done.record(self._side)
+            if rec:
+                self.stage_events.append(tuple(ev4))
+            self._pipe_done[s] = done
+            self._ring_done[ring] = done
+            return b["tid"], b["doc"], b["dist"], b["cnt"]
         if self._pipe_done[s] is not None:
             main.wait_event(self._pipe_done[s])          # the exchange that last read this set's send buffer
         self._local_search(dQ, users, opts, b["send"])
