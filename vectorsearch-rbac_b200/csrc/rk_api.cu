@@ -176,6 +176,7 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.tensor_smin = std::max(1, env_int("RK_TENSOR_SMIN", 1024));
         t.tensor_host_timing = getenv("RK_TENSOR_HOST_TIMING") != nullptr;
         t.tensor_bf16 = env_int("RK_TENSOR_BF16", -1);
+        t.tensor_qtau = env_int("RK_TENSOR_QTAU", 1);
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
         t.single_fused = env_int("RK_SINGLE_FUSED", 1);
@@ -204,6 +205,7 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "tensor_smin")) t.tensor_smin = std::max(1, v);
     else if (!strcmp(name, "tensor_host_timing")) t.tensor_host_timing = v != 0;
     else if (!strcmp(name, "tensor_bf16")) t.tensor_bf16 = v;
+    else if (!strcmp(name, "tensor_qtau")) t.tensor_qtau = v;
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
     else if (!strcmp(name, "single_fused")) t.single_fused = v;

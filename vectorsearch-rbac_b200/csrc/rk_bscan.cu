@@ -16,12 +16,14 @@
 // exact scan path by the host).  On integer-valued data (SIFT shape) TF32 is exact and the proof
 // needs no margin.
 //
-// Shape: persistent, one 192-thread CTA per SM, static unit schedule.
+// Shape: persistent, one 320-thread CTA per SM, static unit schedule.
 //   warp 0   TMA producer: per k-chunk of 32 floats one 128x32 box of X and one of Q
 //            (cp.async.bulk.tensor.2d, 128-byte swizzle) into a ring of stages.
 //   warp 1   MMA issuer: 4 x (M=128, N<=128, K=8) tcgen05.mma per stage, accumulators double-buffered
 //            in TMEM (2 x 128 columns); tcgen05.commit releases stages and publishes accumulators.
-//   warps 2-5  epilogue: tcgen05.ld (one TMEM lane = one row), distance, mask test, threshold test
+//   warps 2-9  epilogue, two per TMEM lane quarter (a warp reads lanes 32 (warp % 4) .. + 31 only), each scoring every
+//            other 16-column chunk — with one warp per scheduler the epilogue ran at 0.1 IPC, every dependent instruction's
+//            latency exposed: tcgen05.ld (one TMEM lane = one row), distance, mask test, threshold test
 //            against the running per-query tau, append to per-query candidate buffers (global
 //            scratch, L2 resident); warp-parallel radix-select compaction when a buffer fills.
 #include "rk_bscan_dev.cuh"
@@ -31,7 +33,8 @@
 #define BS_N 128
 #define BS_KC 32
 #define BS_STAGES 5
-#define BS_THREADS 192
+#define BS_EW 8                         // epilogue warps: two per TMEM lane quarter, splitting the 16-column chunks
+#define BS_THREADS (64 + BS_EW * 32)
 #define BS_STAGE_BYTES 32768u          // X box 16 KB + Q box 16 KB
 
 // ---------------------------------------------------------------------------------------------
@@ -54,10 +57,10 @@ __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
     s.off_trunc = o; o += BS_N * 8;
     s.off_qa = o; o += BS_N * 16;       // first two mask words of each query as one 16-byte load
     s.off_um = o; o += BS_N * 8u * (uint32_t) mask_words;
-    s.off_hist = o; o += 4 * 256 * 4;
-    s.off_sel = o; o += 4 * 16;
+    s.off_hist = o; o += BS_EW * 256 * 4;
+    s.off_sel = o; o += BS_EW * 16;
     o = (o + 15) & ~15u;
-    s.off_sort = o; o += 4 * BS_SORT_MAX * 8;
+    s.off_sort = o; o += BS_EW * BS_SORT_MAX * 8;
     s.total = o + 1024;     // slack for the manual 1024-byte alignment of the stage ring
     return s;
 }
@@ -83,7 +86,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < BS_STAGES; s++) { rk_mbar_init(&full[s], 1); rk_mbar_init(&empty[s], 1); }
-        for (int b = 0; b < 2; b++) { rk_mbar_init(&tfull[b], 1); rk_mbar_init(&tempty[b], 4); }
+        for (int b = 0; b < 2; b++) { rk_mbar_init(&tfull[b], 1); rk_mbar_init(&tempty[b], BS_EW); }
         rk_fence_barrier_init();
     }
     if (warp == 1) bs_tmem_alloc(s_tmem, 2 * BS_N);
@@ -165,7 +168,8 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         const int ew = warp - 2;                       // 0..3 (compaction work split)
         const int quarter = warp & 3;                  // TMEM lanes this warp may read: [32 * (warp % 4), +32)
         const int erow = quarter * 32 + lane;          // row of the tile == TMEM lane
-        const int et = ew * 32 + lane;                 // 0..127 epilogue thread index
+        const int chalf = ew >> 2;                     // which 16-column chunks of a tile this warp scores: chalf, chalf + 2, ...
+        const int et = ew * 32 + lane;                 // epilogue thread index; threads below BS_N also own column et's state
         BsCtx c;
         c.tau = reinterpret_cast<uint32_t *>(smem + L.off_tau);
         float *tauf = reinterpret_cast<float *>(smem + L.off_tauf);
@@ -179,22 +183,26 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         uint4 *s_qa = reinterpret_cast<uint4 *>(smem + L.off_qa);
         uint64_t *s_um = reinterpret_cast<uint64_t *>(smem + L.off_um);
         const int W = p.mask_words;
-        auto esync = [] { rk_named_bar_sync(2, 128); };
+        auto esync = [] { rk_named_bar_sync(2, BS_EW * 32); };
         uint32_t tcount = 0;
+        uint32_t qid = 0, qt_next = RK_KEY_SENTINEL;   // this thread's query (column et) and its shared threshold as last fetched
         for (uint32_t ui = p.cta_off[blockIdx.x]; ui < p.cta_off[blockIdx.x + 1]; ui++) {
             const RkBUnit un = p.units[p.cta_units[ui]];
             esync();                                   // previous unit fully emitted
-            {
+            if (et < BS_N) {
                 const bool live = (uint32_t) et < un.nq;
                 // a padded column keeps tau = 0: no key is ever <= 0, so it never collects anything
                 uint32_t tau0 = live ? RK_KEY_SENTINEL : 0u;
                 // seeded threshold: the kp-th smallest ordering value over a SAMPLE of the rows this query
                 // sees bounds the kp-th smallest over all of them from above
                 if (live && p.tau_key && p.tau_count[un.q0 + et] >= p.kp) tau0 = rk_float_to_key(p.tau_key[(size_t) (un.q0 + et) * p.kp + (p.kp - 1)]);
+                qid = live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u;
+                if (live && p.qtau) tau0 = min(tau0, __ldcg(p.qtau + qid));       // what the query's other units have proved so far
+                qt_next = tau0;
                 c.tau[et] = tau0;
                 tauf[et] = bs_tau_float(tau0);
                 c.cnt[et] = 0;
-                s_trunc[et] = p.trunc + (live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u);
+                s_trunc[et] = p.trunc + qid;
                 uint64_t w0 = ~0ull, w1 = 0ull;        // no permission filter: every row passes
                 if (p.use_mask) {
                     w0 = live ? p.qmask[(size_t) (un.q0 + et) * W] : 0ull;
@@ -242,12 +250,17 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
+                if (p.qtau && (ti & 3u) == 3u && (uint32_t) et < un.nq) {
+                    // the shared threshold fetched four tiles ago (no load latency on this path), then the next fetch
+                    if (qt_next < c.tau[et]) { c.tau[et] = qt_next; tauf[et] = bs_tau_float(qt_next); }
+                    qt_next = __ldcg(p.qtau + qid);
+                }
                 if (umask && !(own_n && ma_n == um0 && mb_n == um1)) { own_n = false; ma_n = 0; mb_n = 0; }
                 const bool valid = row < p.nrows && own_n;
                 const float xn = xn_n;
                 // which queries may see each row: the 32 rows of a warp belong to a few documents, so the mask test runs
                 // once per (distinct row mask, query) — lanes test 16 queries at a time and vote — not per (row, query)
-                uint64_t hit_lo = 0ull, hit_hi = 0ull;      // 16 bits per chunk of 16 queries
+                uint64_t hit_lo = 0ull;                     // 16 bits per chunk of 16 queries (this warp's chunks)
                 {
                     const uint64_t ma = ma_n, mb = mb_n;
                     const uint32_t grp = __match_any_sync(0xffffffffu, ma) & __match_any_sync(0xffffffffu, mb);
@@ -261,13 +274,13 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         const bool mine = (g >> lane) & 1u;
                         const uint32_t a0 = (uint32_t) a, a1 = (uint32_t) (a >> 32), b0 = (uint32_t) b, b1 = (uint32_t) (b >> 32);
 #pragma unroll 1
-                        for (int i = 0; i < 8; i++) {
-                            const uint32_t c0 = 16u * (uint32_t) i;
+                        for (int i = 0; i < 4; i++) {
+                            const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
                             if (c0 >= ncol) break;
                             const uint4 qa = s_qa[c0 + (uint32_t) (lane & 15)];
                             const uint32_t hit = (a0 & qa.x) | (a1 & qa.y) | (b0 & qa.z) | (b1 & qa.w);
                             const uint32_t bal = __ballot_sync(0xffffffffu, hit != 0) & 0xFFFFu;
-                            if (mine) { if (i < 4) hit_lo |= (uint64_t) bal << (16 * i); else hit_hi |= (uint64_t) bal << (16 * (i - 4)); }
+                            if (mine) hit_lo |= (uint64_t) bal << (16 * i);
                         }
                     }
                 }
@@ -279,10 +292,10 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 bs_fence_after();
                 const uint32_t taddr = tmem_base + buf * BS_N + ((uint32_t) (quarter * 32) << 16);
 #pragma unroll 1
-                for (int i = 0; i < 8; i++) {
-                    const uint32_t c0 = 16u * (uint32_t) i;
+                for (int i = 0; i < 4; i++) {
+                    const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
                     if (c0 >= ncol) break;
-                    const uint32_t h16 = (uint32_t) (i < 4 ? hit_lo >> (16 * i) : hit_hi >> (16 * (i - 4))) & 0xFFFFu;
+                    const uint32_t h16 = (uint32_t) (hit_lo >> (16 * i)) & 0xFFFFu;
                     if (W <= 2 && !__any_sync(0xffffffffu, h16 != 0)) continue;      // none of the 32 rows is visible to these 16 queries
                     uint32_t r[16];
                     bs_tmem_ld16(taddr + c0, r);
@@ -328,16 +341,17 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 if (lane == 0) rk_mbar_arrive(&tempty[buf]);
                 // a tile adds at most 128 entries per query: compact what could overflow on the next one
                 // (the reducing barrier also publishes this tile's appends)
-                // (the count a thread reads here may still miss this tile's appends by the other three
+                // (the count a thread reads here may still miss this tile's appends by the other
                 // warps — at most 96 — hence the margin of two tiles: seen <= CAP - 256 means at most
                 // CAP - 160 now and at most CAP - 32 after the next tile)
-                const bool need = rk_named_bar_red_or(2, 128, c.cnt[et] > BS_CAP - 2 * BS_M);
+                const bool need = rk_named_bar_red_or(2, BS_EW * 32, et < BS_N && c.cnt[et] > BS_CAP - 2 * BS_M);
                 if (need) {
-                    for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
+                    for (uint32_t q = (uint32_t) ew; q < un.nq; q += BS_EW) {
                         const uint32_t n = c.cnt[q];
                         if (n > BS_CAP - 2 * BS_M) {
                             uint32_t tau;
                             uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
+                            if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);     // >= kp rows are <= tau
                             if (m > BS_CAP / 2 && tau > 0) {
                                 // more than half the buffer ties at the kp-th key: drop that key altogether
                                 // and record that the list is no longer complete (the query is re-run exactly)
@@ -352,11 +366,12 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 }
             }
             // unit end: every query's list, sorted by (approximate key, row), at most kp entries
-            for (uint32_t q = (uint32_t) ew; q < un.nq; q += 4) {
+            for (uint32_t q = (uint32_t) ew; q < un.nq; q += BS_EW) {
                 uint32_t n = c.cnt[q];
                 if (n > (uint32_t) p.kp) {
                     uint32_t tau;
                     n = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                    if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);
                     if (n > BS_SORT_MAX && tau > 0) {
                         n = bs_warp_filter(c, (int) q, n, tau - 1u);
                         if (lane == 0) *s_trunc[q] = 1;

@@ -186,6 +186,11 @@ struct RkBScanParams {
     const int32_t *tau_count;
     const uint64_t *unit_mask;   // [masks][mask_words] exact row masks of the atoms plan's units (see RkBUnit::mask_id)
     const uint32_t *slot_q;      // slot -> query of the caller's batch (trunc[] is indexed by query); NULL = identity
+    // Shared threshold of a query over ALL its units (a query of the atoms plan owns one unit per document class it sees, on
+    // different CTAs): qtau[query] = smallest proven upper bound of the query's kp-th best approximate value.  Every
+    // compaction lowers it (atomicMin), units start from it and re-read it every few tiles — so the units of a query nominate
+    // kp rows between them, not kp each.  RK_KEY_SENTINEL before the launch; NULL = every unit on its own.
+    uint32_t *qtau;
 };
 
 struct RkRescoreParams {

@@ -172,6 +172,7 @@ struct RkTuning {
     int tensor_sdiv = 0;         // RK_TENSOR_SDIV: 0 = default (400)
     int tensor_smin = 1024;      // RK_TENSOR_SMIN
     int tensor_host_timing = 0;  // RK_TENSOR_HOST_TIMING
+    int tensor_qtau = 1;         // RK_TENSOR_QTAU: 0 = every unit of the tensor engine keeps its own threshold
     int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = by row length, 0 = TF32 nomination, 1 = bf16 nomination
     int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE

@@ -553,12 +553,13 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         ts.d_sel_key.ensure(std::max<size_t>(nq * (size_t) kp * 4, 16)) != 0 ||
         ts.d_sel_row.ensure(std::max<size_t>(nq * (size_t) kp * 4, 16)) != 0 || ts.d_sel_count.ensure(std::max<size_t>(nq * 4, 16)) != 0 ||
         ts.d_tau_key.ensure(std::max<size_t>(nslots * (size_t) kp * 4, 16)) != 0 || ts.d_tau_count.ensure(std::max<size_t>(nslots * 4, 16)) != 0 ||
-        ts.d_flags.ensure(std::max<size_t>(3 * nq * 4, 16)) != 0 || ts.h_flags.ensure(std::max<size_t>(nq * 4 + 128, 128)) != 0)
+        ts.d_flags.ensure(std::max<size_t>(4 * nq * 4, 16)) != 0 || ts.h_flags.ensure(std::max<size_t>(nq * 4 + 128, 128)) != 0)
         return RK_ERR_CUDA;
     RK_CUDA(cudaMemcpyAsync(ts.d_plan.p, hp, off, cudaMemcpyHostToDevice, st));
     RK_CUDA(cudaEventRecord(ws.ev_plan[pi_], st));
     ws.ev_plan_used[pi_] = true;
     RK_CUDA(cudaMemsetAsync(ts.d_flags.p, 0, 3 * nq * 4, st));      // [uncertain][trunc][sample-pass trunc], each per query
+    RK_CUDA(cudaMemsetAsync(ts.d_flags.as<int32_t>() + 3 * nq, 0xFF, nq * 4, st));      // [shared thresholds of the main pass] = RK_KEY_SENTINEL
     RK_CUDA(cudaMemsetAsync(ts.d_probe.p, 0, 64, st));
     uint64_t launches = 0;
 
@@ -622,6 +623,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         bind_pass(ps_);
         bp.trunc = ts.d_flags.as<int32_t>() + 2 * nq;      // ties dropped here only loosen the seed
         bp.tau_key = nullptr; bp.tau_count = nullptr;
+        bp.qtau = nullptr;
         RK_CUDA((paired ? rk_launch_bscan2 : rk_launch_bscan)(bp, ix->d_x.as<float>(), dQp, nslots, ps_.grid, st));
         // per slot: the sample's kp smallest values
         sp.lid0 = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lid0);
@@ -636,6 +638,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     if (nslots) {
         bind_pass(pm_);
         bp.trunc = ts.d_flags.as<int32_t>() + nq;
+        bp.qtau = ix->tune.tensor_qtau ? reinterpret_cast<uint32_t *>(ts.d_flags.as<int32_t>() + 3 * nq) : nullptr;
         bp.tau_key = sampled ? ts.d_tau_key.as<float>() : nullptr;
         bp.tau_count = sampled ? ts.d_tau_count.as<int32_t>() : nullptr;
         RK_CUDA((paired ? rk_launch_bscan2 : rk_launch_bscan)(bp, ix->d_x.as<float>(), dQp, nslots, pm_.grid, st));
