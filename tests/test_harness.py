@@ -30,6 +30,28 @@ def test_parse_vector_and_recall_and_cache(tmp_path):
     assert [int(r[0]) for r in r2[1]] == [7, 3, 11] and q2[1]["user_id"] == 4
 
 
+def test_pointer_cache_format(tmp_path):
+    """compute_ground_truth.py:35-73 (writer / reader) and the C++ reader's view of the file (benchmark_utils.cpp:26-76)."""
+    from vectorsearch_rbac_b200 import harness
+    res = [[(7, 1, b"x", 0.5), (9, 1, b"", 0.7), (), ("bad", 2, b"", 0.1), (3,)], None, [(4, 2, b"", 1.0)]]
+    assert harness.to_pointer_results(res) == [[[7, 1], [9, 1]], [], [[4, 2]]]
+    f = tmp_path / "sub" / "ground_truth_cache.json"
+    harness.save_pointer_cache(res, str(f))
+    text = open(f).read()
+    assert text.startswith("[\n  [\n    [\n      7,")                       # json.dump(..., indent=2)
+    assert harness.load_pointer_cache(str(f)) == [[[7, 1], [9, 1]], [], [[4, 2]]]
+    assert harness.load_pointer_cache(str(tmp_path / "missing.json")) is None
+    (tmp_path / "broken.json").write_text("{not json")
+    assert harness.load_pointer_cache(str(tmp_path / "broken.json")) is None
+    (tmp_path / "dict.json").write_text("{}")
+    assert harness.load_pointer_cache(str(tmp_path / "dict.json")) is None
+    ptr = harness.load_pointer_cache(str(f))
+    qs = [{"user_id": 1, "topk": 2}, {"user_id": 2, "topk": 0}, {"user_id": 3, "topk": 1}]
+    assert harness.pointer_cache_as_flat_pairs(ptr, qs) == [(1, 7), (1, 9), (2, 4)]          # (document_id, block_id)
+    assert harness.pointer_cache_as_flat_pairs(ptr, qs[:2]) is None                           # length mismatch
+    assert harness.pointer_cache_as_flat_pairs(ptr, [qs[0], {"topk": 1}, qs[2]]) is None      # a query short of topk pairs
+
+
 @pytest.mark.gpu
 def test_search_funcs_match_oracle():
     import vectorsearch_rbac_b200 as vr

@@ -32,7 +32,9 @@
 #define BS_M 128
 #define BS_N 128
 #define BS_KC 32
+#ifndef BS_STAGES
 #define BS_STAGES 5
+#endif
 #define BS_EW 8                         // epilogue warps: two per TMEM lane quarter, splitting the 16-column chunks
 #define BS_THREADS (64 + BS_EW * 32)
 #define BS_STAGE_BYTES 32768u          // X box 16 KB + Q box 16 KB
@@ -250,6 +252,8 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
+                // the two warps of a lane quarter swap chunk parity every tile (an odd number of chunks evens out over two tiles)
+                const int cpar = (chalf + (int) ti) & 1;
                 if (p.qtau && (ti & 3u) == 3u && (uint32_t) et < un.nq) {
                     // the shared threshold fetched four tiles ago (no load latency on this path), then the next fetch
                     if (qt_next < c.tau[et]) { c.tau[et] = qt_next; tauf[et] = bs_tau_float(qt_next); }
@@ -275,7 +279,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         const uint32_t a0 = (uint32_t) a, a1 = (uint32_t) (a >> 32), b0 = (uint32_t) b, b1 = (uint32_t) (b >> 32);
 #pragma unroll 1
                         for (int i = 0; i < 4; i++) {
-                            const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
+                            const uint32_t c0 = 16u * (uint32_t) (cpar + 2 * i);
                             if (c0 >= ncol) break;
                             const uint4 qa = s_qa[c0 + (uint32_t) (lane & 15)];
                             const uint32_t hit = (a0 & qa.x) | (a1 & qa.y) | (b0 & qa.z) | (b1 & qa.w);
@@ -293,7 +297,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 const uint32_t taddr = tmem_base + buf * BS_N + ((uint32_t) (quarter * 32) << 16);
 #pragma unroll 1
                 for (int i = 0; i < 4; i++) {
-                    const uint32_t c0 = 16u * (uint32_t) (chalf + 2 * i);
+                    const uint32_t c0 = 16u * (uint32_t) (cpar + 2 * i);
                     if (c0 >= ncol) break;
                     const uint32_t h16 = (uint32_t) (hit_lo >> (16 * i)) & 0xFFFFu;
                     if (W <= 2 && !__any_sync(0xffffffffu, h16 != 0)) continue;      // none of the 32 rows is visible to these 16 queries
@@ -343,12 +347,14 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 // (the reducing barrier also publishes this tile's appends)
                 // (the count a thread reads here may still miss this tile's appends by the other
                 // warps — at most 96 — hence the margin of two tiles: seen <= CAP - 256 means at most
-                // CAP - 160 now and at most CAP - 32 after the next tile)
-                const bool need = rk_named_bar_red_or(2, BS_EW * 32, et < BS_N && c.cnt[et] > BS_CAP - 2 * BS_M);
+                // CAP - 160 now and at most CAP - 32 after the next tile.  Checking every second tile with a trigger two
+                // tiles lower was measured: the extra compactions cost more than the barrier saves, 2.31 vs 2.19 ms on C3.)
+                const uint32_t trig = BS_CAP - 2 * BS_M;
+                const bool need = rk_named_bar_red_or(2, BS_EW * 32, et < BS_N && c.cnt[et] > trig);
                 if (need) {
                     for (uint32_t q = (uint32_t) ew; q < un.nq; q += BS_EW) {
                         const uint32_t n = c.cnt[q];
-                        if (n > BS_CAP - 2 * BS_M) {
+                        if (n > trig) {
                             uint32_t tau;
                             uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
                             if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);     // >= kp rows are <= tau

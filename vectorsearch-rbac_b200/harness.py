@@ -17,6 +17,7 @@ There is no CPU fallback here: every call goes through librbacknn.so.
 from __future__ import annotations
 
 import json
+import os
 import time
 from typing import Callable, Iterable, List, Optional, Sequence, Tuple
 
@@ -126,3 +127,63 @@ def load_ground_truth_cache(cache_file: str) -> Tuple[List[dict], List[List[Tupl
     with open(cache_file) as f:
         data = json.load(f)
     return [d["query"] for d in data], [[tuple(r) for r in d["ground_truth"]] for d in data]
+
+
+# ---- "pointer" ground-truth cache (basic_benchmark/compute_ground_truth.py:35-59, read by the C++ benches:
+# acorn_benchmark/src/benchmark_utils.cpp:26-76) ------------------------------------------------------------------
+
+def to_pointer_results(results: Iterable[Iterable]) -> List[List[List[int]]]:
+    """Per query the [block_id, document_id] pairs of its result rows, in result order; rows that are empty, shorter than
+    two fields or whose ids are not integers are skipped (compute_ground_truth.py:35-53)."""
+    out: List[List[List[int]]] = []
+    for rows in results:
+        formatted: List[List[int]] = []
+        for entry in rows or []:
+            if not entry or len(entry) < 2:
+                continue
+            try:
+                formatted.append([int(entry[0]), int(entry[1])])
+            except (TypeError, ValueError):
+                continue
+        out.append(formatted)
+    return out
+
+
+def save_pointer_cache(results: Iterable[Iterable], cache_file: str) -> None:
+    """JSON list (one entry per query) of [block_id, document_id] lists, indent 2 (compute_ground_truth.py:56-59) — the file
+    the C++ benches load as their ground truth."""
+    d = os.path.dirname(cache_file)
+    if d:
+        os.makedirs(d, exist_ok=True)
+    with open(cache_file, "w", encoding="utf-8") as f:
+        json.dump(to_pointer_results(results), f, indent=2)
+
+
+def load_pointer_cache(cache_file: str) -> Optional[List[List[List[int]]]]:
+    """None when the file is missing, is not JSON or does not hold a list (compute_ground_truth.py:62-73)."""
+    if not os.path.exists(cache_file):
+        return None
+    try:
+        with open(cache_file, encoding="utf-8") as f:
+            data = json.load(f)
+    except json.JSONDecodeError:
+        return None
+    return data if isinstance(data, list) else None
+
+
+def pointer_cache_as_flat_pairs(pointer: Sequence[Sequence[Sequence[int]]], queries: Sequence[dict]) -> Optional[List[Tuple[int, int]]]:
+    """What load_groundtruth_from_cache builds from the file (benchmark_utils.cpp:26-76): the first `topk` pairs of every
+    query, flattened, as (document_id, block_id); None when the cache does not match the query list (wrong length, or a query
+    with fewer than topk pairs) — the C++ reader then recomputes the ground truth."""
+    if not queries or len(pointer) != len(queries):
+        return None
+    flat: List[Tuple[int, int]] = []
+    for q, entry in zip(queries, pointer):
+        topk = max(int(q.get("topk", 5)), 0)
+        if not isinstance(entry, (list, tuple)) or len(entry) < topk:
+            return None
+        for pair in entry[:topk]:
+            if not isinstance(pair, (list, tuple)) or len(pair) < 2:
+                return None
+            flat.append((int(pair[1]), int(pair[0])))
+    return flat
