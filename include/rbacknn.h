@@ -273,6 +273,31 @@ int rk_merge_shards_pull(rk_index *ix, rk_exchange *ex, size_t nq, int k, void *
 /* Synchronises cuda_stream (NULL = the index stream); RK_ERR_CUDA if a wait for a peer timed out since creation. */
 int rk_exchange_status(rk_exchange *ex, void *cuda_stream);
 
+/* ---- several GPUs of one box behind one handle (one process; SURVEY.md §8b `n_gpus`) --------------------------------
+ * The nearest thing in the reference is FAISS's IndexShards: host threads over sub-indexes and a CPU merge
+ * (logical_partition_benchmark/benchmark/faiss/faiss/IndexShards.cpp:197-256).  rk_multi keeps one rk_index per device
+ * (document d on shard d mod n_gpus), one host thread per device and the peer exchange above between them; the calls
+ * mirror the single-index ones and results are identical to one index holding all rows.  devices[n_gpus]: CUDA ordinals
+ * (an ordinal may repeat: several shards on one GPU, for tests).  nq_max / cfg->k_max size the exchange rings. */
+typedef struct rk_multi rk_multi;
+rk_multi *rk_multi_open(const rk_config *cfg, const int32_t *devices, int32_t n_gpus, size_t nq_max);
+void rk_multi_close(rk_multi *m);
+int rk_multi_n_gpus(const rk_multi *m);
+rk_index *rk_multi_shard(rk_multi *m, int g);           /* the per-device index (statistics, options) */
+int rk_multi_load_rows(rk_multi *m, const float *x, const uint64_t *tid, const uint32_t *doc, size_t n);
+int rk_multi_set_doc_roles(rk_multi *m, const uint32_t *doc, const uint32_t *role, size_t n);
+int rk_multi_set_user_roles(rk_multi *m, const uint32_t *user, const uint32_t *role, size_t n);
+int rk_multi_build_role_partitions(rk_multi *m);
+int rk_multi_build_combination_partitions(rk_multi *m);
+int rk_multi_define_partition(rk_multi *m, uint32_t part_id, const uint32_t *docs, size_t n);
+int rk_multi_map_roleset_to_partitions(rk_multi *m, const uint32_t *roles, size_t nroles, const uint32_t *parts, size_t nparts);
+int rk_multi_finalize(rk_multi *m);
+/* Shard 0 trains the centres on its stripe, the other shards assign their rows to them. */
+int rk_multi_build_ivf(rk_multi *m, int lists, uint64_t seed);
+/* rk_search_batch over all shards: host buffers in and out, synchronous. */
+int rk_multi_search_batch(rk_multi *m, size_t nq, const float *Q, const uint32_t *user_ids, const rk_scan_opts *o,
+                          uint64_t *out_tid, uint32_t *out_doc, double *out_dist, int32_t *out_count);
+
 /* ---- plumbing ------------------------------------------------------------------------------- */
 
 /* Run on the caller's CUDA stream (a cudaStream_t), e.g. torch's current stream. NULL = own stream. */

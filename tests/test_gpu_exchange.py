@@ -160,3 +160,40 @@ def test_peer_exchange_two_processes_two_gpus(tmp_path):
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     mp.spawn(_two_gpu_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert all((tmp_path / f"ok{r}").exists() for r in range(2))
+
+
+@pytest.mark.parametrize("n_shards", [2, 3])
+def test_multi_index_one_process_matches_oracle(n_shards):
+    """rk_multi_*: several shards behind one handle in one process (here all on cuda:0; real boxes list distinct devices).  Role,
+    combination, bitmask and dynamic filters on both engines against the oracle over the whole corpus."""
+    import torch
+    import vectorsearch_rbac_b200 as vr
+    from vectorsearch_rbac_b200.dynamic_layout import apply_layout, split_roles
+    ds = make_dataset("sift", n=9000, dim=64, rows_per_doc=15, rbac="random", num_users=20, num_roles=8)
+    devs = [0] * n_shards if torch.cuda.device_count() < n_shards else list(range(n_shards))
+    mi = vr.MultiIndex(64, devs, metric=vr.METRIC_L2, k_max=64, nq_max=64)
+    half = len(ds["X"]) // 2
+    mi.load_rows(ds["X"][:half], ds["tid"][:half], ds["doc"][:half])
+    mi.load_rows(ds["X"][half:], ds["tid"][half:], ds["doc"][half:])
+    mi.set_doc_roles(ds["doc_roles"][:, 0], ds["doc_roles"][:, 1])
+    mi.set_user_roles(ds["user_roles"][:, 0], ds["user_roles"][:, 1])
+    mi.build_role_partitions()
+    mi.build_combination_partitions()
+    parts, rp, _ = split_roles(ds["doc_roles"], ds["user_roles"], alpha=2.0)
+    apply_layout(mi, parts, rp)
+    mi.finalize()
+    rng = np.random.default_rng(21)
+    all_users = np.unique(ds["user_roles"][:, 0])
+    for step in range(6):                                            # more steps than the ring is deep
+        nq = 48 if step % 2 == 0 else 33
+        Q = ds["X"][rng.integers(0, len(ds["X"]), nq)].copy()
+        users = all_users[rng.integers(0, len(all_users), nq)].astype(np.uint32)
+        flt, layout, mode = [(vr.FILTER_PARTITION, vr.LAYOUT_ROLE, "role"), (vr.FILTER_PARTITION, vr.LAYOUT_COMBINATION, "combination"),
+                             (vr.FILTER_BITMASK, 0, "bitmask"), (vr.FILTER_PARTITION, vr.LAYOUT_DYNAMIC, "bitmask")][step % 4]
+        eng = vr.ENGINE_SCAN if step < 4 else vr.ENGINE_AUTO
+        got = mi.search_batch(Q, users, 40, filter=flt, layout=layout, engine=eng)
+        exp = oracle_role_search(ds, Q, users, orc.METRIC_L2, 40, mode=mode)
+        assert_topk_matches(got, exp, exact=True)
+    with pytest.raises(vr.RkError):
+        mi.search_batch(np.zeros((65, 64), np.float32), np.ones(65, np.uint32), 40, filter=vr.FILTER_BITMASK)     # beyond nq_max
+    mi.close()

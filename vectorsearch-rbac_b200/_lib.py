@@ -77,6 +77,20 @@ SIGNATURES = {
     "rk_search_batch_shard_push": (C.c_int, [_P, _P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P]),
     "rk_merge_shards_pull": (C.c_int, [_P, _P, C.c_size_t, C.c_int, _P, _P, _P, _P, _P]),
     "rk_exchange_status": (C.c_int, [_P, _P]),
+    "rk_multi_open": (_P, [C.POINTER(RkConfig), _P, C.c_int32, C.c_size_t]),
+    "rk_multi_close": (None, [_P]),
+    "rk_multi_n_gpus": (C.c_int, [_P]),
+    "rk_multi_shard": (_P, [_P, C.c_int]),
+    "rk_multi_load_rows": (C.c_int, [_P, _P, _P, _P, C.c_size_t]),
+    "rk_multi_set_doc_roles": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "rk_multi_set_user_roles": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "rk_multi_build_role_partitions": (C.c_int, [_P]),
+    "rk_multi_build_combination_partitions": (C.c_int, [_P]),
+    "rk_multi_define_partition": (C.c_int, [_P, C.c_uint32, _P, C.c_size_t]),
+    "rk_multi_map_roleset_to_partitions": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_size_t]),
+    "rk_multi_finalize": (C.c_int, [_P]),
+    "rk_multi_build_ivf": (C.c_int, [_P, C.c_int, C.c_uint64]),
+    "rk_multi_search_batch": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
     "rk_set_stream": (C.c_int, [_P, _P]),
     "rk_synchronize": (C.c_int, [_P]),
     "rk_get_stats": (C.c_int, [_P, C.POINTER(RkStats)]),

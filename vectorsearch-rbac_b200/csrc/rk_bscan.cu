@@ -657,11 +657,14 @@ cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float 
     }
     const size_t smem = rk_bscan_smem_bytes(p.mask_words);
     auto kern = p.metric == 0 ? rk_bscan_kernel<0> : rk_bscan_kernel<1>;
-    static bool attr_set[2];
-    if (!attr_set[p.metric & 1]) {
+    // (function attributes are per device: rk_multi runs one index per GPU in one process)
+    static bool attr_set[64][2];
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+    if (!attr_set[dev_ & 63][p.metric & 1]) {
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        attr_set[p.metric & 1] = true;
+        attr_set[dev_ & 63][p.metric & 1] = true;
     }
     kern<<<grid, BS_THREADS, smem, stream>>>(tmx, tmq[0], tmq[1], tmq[2], tmq[3], p);
     return cudaGetLastError();

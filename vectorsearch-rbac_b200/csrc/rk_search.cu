@@ -844,6 +844,17 @@ static int search_batch_shard_locked(rk_index *ix, size_t nq, const float *dQ, c
     return search_device(ix, ix->ws, nq, dQ, user_ids, o, 0, out);
 }
 
+// for rk_multi.cu: host queries -> the index's device staging buffer (padded rows), asynchronous on the index stream
+int rk_stage_host_queries(rk_index *ix, size_t nq, const float *Q, const float **dQ)
+{
+    RK_CUDA(cudaSetDevice(ix->device));
+    std::lock_guard<std::mutex> g(ix->batch_mu);
+    int rc = stage_queries(ix, ix->ws, nq, Q);
+    if (rc < 0) return rc;
+    *dQ = ix->ws.dq.as<float>();
+    return RK_OK;
+}
+
 // for rk_exchange.cu (the caller holds ix->batch_mu): d_lists != NULL = the caller supplies the IVFFlat list choice
 int rk_search_batch_shard_locked_for_exchange(rk_index *ix, size_t nq, const float *dQ, const uint32_t *user_ids, const rk_scan_opts *o,
                                               const uint32_t *d_lists, float *d_key, uint64_t *d_tid, uint32_t *d_doc)

@@ -275,6 +275,81 @@ class Exchange:
         _check(lib.rk_exchange_status(self._h, stream or None))
 
 
+class MultiIndex:
+    """Several GPUs of one box behind one handle, one process (rk_multi_* in include/rbacknn.h): document-striped shards, one
+    host thread per device, the peer exchange between them.  Mirrors Index for loading, layouts and search_batch."""
+
+    def __init__(self, dim: int, devices: Sequence[int], metric: int = METRIC_L2, k_max: int = 128, nq_max: int = 1024):
+        cfg = RkConfig()
+        cfg.abi_version, cfg.dim, cfg.metric, cfg.device, cfg.k_max = _lib.RK_ABI_VERSION, dim, metric, int(devices[0]), k_max
+        dv = np.ascontiguousarray(devices, dtype=np.int32)
+        self._h = lib.rk_multi_open(C.byref(cfg), dv.ctypes.data, len(dv), nq_max)
+        if not self._h:
+            raise RkError(-5, _lib.last_error())
+        self.dim, self.metric, self.devices, self.k_max = dim, metric, list(map(int, devices)), k_max
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            lib.rk_multi_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def load_rows(self, x: np.ndarray, tid: np.ndarray, doc: np.ndarray) -> None:
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        if x.ndim != 2 or x.shape[1] != self.dim:
+            raise RkError(-2, f"expected {self.dim} dimensions, not {x.shape[-1]}")
+        tid = np.ascontiguousarray(tid, dtype=np.uint64)
+        doc = _u32(doc)
+        _check(lib.rk_multi_load_rows(self._h, x.ctypes.data, tid.ctypes.data, doc.ctypes.data, x.shape[0]))
+
+    def set_doc_roles(self, doc: Iterable[int], role: Iterable[int]) -> None:
+        d, r = _u32(doc), _u32(role)
+        _check(lib.rk_multi_set_doc_roles(self._h, d.ctypes.data, r.ctypes.data, len(d)))
+
+    def set_user_roles(self, user: Iterable[int], role: Iterable[int]) -> None:
+        u, r = _u32(user), _u32(role)
+        _check(lib.rk_multi_set_user_roles(self._h, u.ctypes.data, r.ctypes.data, len(u)))
+
+    def build_role_partitions(self) -> None:
+        _check(lib.rk_multi_build_role_partitions(self._h))
+
+    def build_combination_partitions(self) -> None:
+        _check(lib.rk_multi_build_combination_partitions(self._h))
+
+    def define_partition(self, part_id: int, docs: Iterable[int]) -> None:
+        d = _u32(docs)
+        _check(lib.rk_multi_define_partition(self._h, part_id, d.ctypes.data, len(d)))
+
+    def map_roleset_to_partitions(self, roles: Sequence[int], parts: Sequence[int]) -> None:
+        r, p = _u32(roles), _u32(parts)
+        _check(lib.rk_multi_map_roleset_to_partitions(self._h, r.ctypes.data, len(r), p.ctypes.data, len(p)))
+
+    def finalize(self) -> None:
+        _check(lib.rk_multi_finalize(self._h))
+
+    def build_ivf(self, lists: int, seed: int = 42) -> None:
+        _check(lib.rk_multi_build_ivf(self._h, lists, seed))
+
+    def search_batch(self, Q: np.ndarray, user_ids: Optional[Sequence[int]], k: int, probes: int = 0, filter: int = FILTER_PARTITION,
+                     layout: int = LAYOUT_AUTO, engine: int = ENGINE_AUTO, keep_duplicates: bool = False):
+        Q = np.ascontiguousarray(Q, dtype=np.float32).reshape(-1, self.dim)
+        nq = Q.shape[0]
+        users = None if user_ids is None else _u32(user_ids)
+        o = make_opts(k, probes=probes, filter=filter, layout=layout, engine=engine, keep_duplicates=keep_duplicates)
+        tid = np.empty((nq, k), dtype=np.uint64)
+        doc = np.empty((nq, k), dtype=np.uint32)
+        dist = np.empty((nq, k), dtype=np.float64)
+        cnt = np.zeros(nq, dtype=np.int32)
+        _check(lib.rk_multi_search_batch(self._h, nq, Q.ctypes.data, None if users is None else users.ctypes.data, C.byref(o),
+                                         tid.ctypes.data, doc.ctypes.data, dist.ctypes.data, cnt.ctypes.data))
+        return tid, doc, dist, cnt
+
+
 class Scan:
     """begin / rescan / gettuple / endscan — the pgvector index-scan contract
     (pgvector/src/ivfflat.h:335-338, ivfscan.c:241-406)."""
