@@ -98,6 +98,8 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--pipeline", action="store_true", help="(kept for compatibility: pipelining is the default with the peer exchange)")
     ap.add_argument("--no-pipeline", action="store_true", help="N > 1: run scan, exchange and merge of a step back to back on one stream")
+    ap.add_argument("--peer-overlap", default="deferred", choices=["deferred", "side"],
+                    help="pipelined peer exchange: deferred = merge of step i-1 after the push of step i on one stream; side = merge on a side stream")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1: peer = stores into the other GPUs' receive rings over NVLink + flags (rk_exchange.cu); nccl = all_gather_into_tensor")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
@@ -603,6 +605,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
     sharded.use_torch_stream(ix, dev)
     searcher = sharded.ShardedSearcher(ix, rank, world, device=dev)
     peer_ok = world > 1 and args.exchange == "peer" and searcher.enable_peer_exchange(args.nq, max(args.k, 1))
+    searcher.peer_overlap = args.peer_overlap
     # with the peer exchange the merge of step i runs on a side stream under the scan of step i + 1 (no collective's CTAs
     # compete with the persistent scan kernel); with NCCL the serial order measured faster (round 1) and stays the default
     pipelined = world > 1 and not args.no_pipeline and (peer_ok or args.pipeline)
@@ -636,12 +639,16 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
         searcher.stage_events = [] if world > 1 else None
         with ClockSampler(local_rank) as clk:
             e0.record(stream)
+            t_host = 0.0
             for _ in range(steps):
+                th0 = time.perf_counter()
                 out = step_fn(Q, qusers, opts)
+                t_host += time.perf_counter() - th0
             searcher.flush()
             e1.record(stream)
             barrier()
-        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary(), "stages": searcher.stage_ms(), "pipelined": pipelined}
+        r = {"dt_dev": e0.elapsed_time(e1) * 1e-3, "clk": clk.summary(), "stages": searcher.stage_ms(), "pipelined": pipelined,
+             "host_issue_ms": t_host / steps * 1e3}
         searcher.stage_events = None
         if ivf_lists:
             ix.synchronize()                 # collects the last launch's probe / list-scan event times
@@ -773,6 +780,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
             "data": "synthetic",
             "config": make_config(wl, args, world),
             "run": {"engine": engine_name, "rows_this_rank": int(len(mine)), "segments": int(st["segments"]),
+                    "host_issue_ms_per_step": main_r["host_issue_ms"],
                     "recall_at_100": 1.0, "recall_note": "exact search; ids checked against the oracle on the cpu_baseline sample"},
             "roofline": roofline_of(main_r, engine_name),
             "e2e": {"value": args.nq * steps / main_r["dt_e2e"], "unit": "queries/s", "h2d_bytes_per_step": int(main_r["h2d"]),
@@ -787,8 +795,10 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
             # rank 0's mean device time per stage of a step (the all-gather also absorbs waiting for the slowest rank)
             line["stages_ms"] = main_r["stages"]
         if world > 1:
-            line["run"]["exchange"] = searcher.exchange_kind + ("; merge of step i on a side stream under the scan of step i + 1"
-                                                                if main_r["pipelined"] else "; exchange + merge after every scan, same stream")
+            line["run"]["exchange"] = searcher.exchange_kind + (
+                ("; one stream, merge of step i-1 after the push of step i (no wait for the slowest rank, nothing competes with the scan for SMs)"
+                 if peer_ok and searcher.peer_overlap == "deferred" else "; merge of step i on a side stream under the scan of step i + 1")
+                if main_r["pipelined"] else "; exchange + merge after every scan, same stream")
             if peer_ok:
                 searcher._ex.status()                   # raises if any wait for a peer timed out
         if single is not None:

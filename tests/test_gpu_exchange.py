@@ -118,7 +118,9 @@ def _two_gpu_worker(rank, world, port, out_dir):
         all_users = np.unique(ds["user_roles"][:, 0])
         opts = sharded.make_opts(k, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_SCAN)
         steps = []
-        for step in range(8):                                        # pipelined: merge of step i under the scan of step i + 1
+        for step in range(8):                                        # pipelined: the merge one step behind / on a side stream
+            sh.flush()
+            sh.peer_overlap = "deferred" if step < 4 else "side"
             Q = ds["X"][rng.integers(0, len(ds["X"]), nq)].copy()
             users = all_users[rng.integers(0, len(all_users), nq)].astype(np.uint32)
             dQ = torch.from_numpy(Q).to(dev)
@@ -134,6 +136,8 @@ def _two_gpu_worker(rank, world, port, out_dir):
         Q = ds["X"][rng.integers(0, len(ds["X"]), nq)].copy()
         users = all_users[rng.integers(0, len(all_users), nq)].astype(np.uint32)
         dQ = torch.from_numpy(Q).to(dev)
+        sh.flush()
+        sh.peer_overlap = "deferred"
         for _ in range(12):
             out = sh.search_device_pipelined(dQ, users, opts)
         sh.flush()

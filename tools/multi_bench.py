@@ -47,7 +47,7 @@ t0 = time.perf_counter()
 for _ in range(a.steps):
     out = mi.search_batch(Qn, users, a.k, filter=vr.FILTER_BITMASK, engine=eng)
 dt = time.perf_counter() - t0
-print(json.dumps({"what": "rk_multi_search_batch (one process, host buffers, synchronous)", "workload": a.workload, "rows": wl["rows"], "n_gpus": a.gpus,
+bench.emit(({"what": "rk_multi_search_batch (one process, host buffers, synchronous)", "workload": a.workload, "rows": wl["rows"], "n_gpus": a.gpus,
                   "engine": a.engine, "queries_per_s": a.nq * a.steps / dt, "ms_per_step": dt / a.steps * 1e3, "load_s": load_s,
                   "checksum_tid": int(out[0].astype(np.uint64).sum() % (1 << 61)), "count_sum": int(out[3].sum())}))
 mi.close()
