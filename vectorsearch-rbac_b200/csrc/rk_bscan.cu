@@ -249,6 +249,19 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 }
             };
             fetch_row(r0_cur);
+            uint64_t uhit0 = 0ull, uhit1 = 0ull;        // atoms plan: per chunk parity, which queries see the unit's class
+            if (umask) {
+                const uint32_t a0 = (uint32_t) um0, a1 = (uint32_t) (um0 >> 32), b0 = (uint32_t) um1, b1 = (uint32_t) (um1 >> 32);
+#pragma unroll 1
+                for (int i = 0; i < 8; i++) {
+                    const uint32_t c0 = 16u * (uint32_t) i;
+                    if (c0 >= ncol) break;
+                    const uint4 qa = s_qa[c0 + (uint32_t) (lane & 15)];
+                    const uint32_t hit = (a0 & qa.x) | (a1 & qa.y) | (b0 & qa.z) | (b1 & qa.w);
+                    const uint64_t bal = (uint64_t) (__ballot_sync(0xffffffffu, hit != 0) & 0xFFFFu) << (16 * (i >> 1));
+                    if (i & 1) uhit1 |= bal; else uhit0 |= bal;
+                }
+            }
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
@@ -265,7 +278,11 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 // which queries may see each row: the 32 rows of a warp belong to a few documents, so the mask test runs
                 // once per (distinct row mask, query) — lanes test 16 queries at a time and vote — not per (row, query)
                 uint64_t hit_lo = 0ull;                     // 16 bits per chunk of 16 queries (this warp's chunks)
-                {
+                if (umask) {
+                    // atoms plan: every row the unit may nominate carries the unit's own mask, so which queries see it was
+                    // settled once per unit (uhit0 / uhit1) — nothing to group or vote on per tile
+                    if ((ma_n | mb_n) != 0ull) hit_lo = cpar ? uhit1 : uhit0;
+                } else {
                     const uint64_t ma = ma_n, mb = mb_n;
                     const uint32_t grp = __match_any_sync(0xffffffffu, ma) & __match_any_sync(0xffffffffu, mb);
                     uint32_t todo = 0xffffffffu;
