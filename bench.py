@@ -64,11 +64,12 @@ WORKLOADS = {
                     "(1000 users, 100 roles, <=3 roles per user), partitions from the AnonySys greedy role splitter restated with "
                     "a linear scan-cost model at storage alpha = 2.0 (the optimiser's fitted HNSW constants are not shipped), "
                     "per-row permission predicate inside impure partitions, exact top-100 (recall 1.0 >= the 0.95 target)"),
-    "c4": dict(rows=10_000_000, dim=768, kind="cohere", rpd=100, users=1000, roles=100, rbac="tree", metric="l2",
+    "c4": dict(rows=10_000_000, dim=768, kind="cohere2", rpd=100, users=1000, roles=100, rbac="tree", metric="l2",
                filter="bitmask", engine="scan", ivf_lists=4096,
-               desc="C4 IVFFlat role-filtered search: synthetic Cohere shape 10M x 768 fp32 L2, tree RBAC mask fused into the list "
-                    "scan, nlist = 4096 (GPU k-means build), one nprobe point per run (--nprobe; sweep: tools/ivf_sweep.py), "
-                    "top-100, recall@100 against the engine's exact filtered result"),
+               desc="C4 IVFFlat role-filtered search: synthetic Cohere shape 10M x 768 fp32 L2 (two-level mixture: 64 topics x 1024 "
+                    "sub-topics, so that recall depends on nprobe), tree RBAC mask fused into the list scan, nlist = 4096 (GPU k-means "
+                    "build), one nprobe point per run (--nprobe; sweep: tools/ivf_sweep.py), top-100, recall@100 against the exact "
+                    "filtered result (the engine's, and the oracle's on a sample)"),
 }
 
 
@@ -816,6 +817,9 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
         if ivf_lists:
             ivf_roofline(line, args, wl, ix, vr, torch, dev, mine, doc, ur, dr, qusers, Q, main_r, ex_exact, ivf_lists, ivf_build_s, world, flt)
             line["roofline"] = with_traffic(line["roofline"], flt_name + ":" + engine_name) if args.nprobe == 16 else line["roofline"]
+        if ivf_lists and (no_cpu or world != 1):
+            line["run"].pop("_exact_tid", None)
+            line["run"].pop("_exact_cnt", None)
         if ivf_lists and not no_cpu and world == 1:
             ivf_cpu_leg(line, args, wl, ix, dev, tid, doc, ur, dr, qusers, Q, main_r, ivf_lists, rows, dim, CH)
         if world == 1 and not no_cpu and not ivf_lists:
@@ -949,6 +953,7 @@ def ivf_roofline(line, args, wl, ix, vr, torch, dev, mine, doc, ur, dr, qusers, 
                                "all-gathered; its time is part of stages_ms.local_search")
         line["run"]["ivf_sharding"] = ("centres trained on rank 0's stripe and broadcast; every list's rows striped with "
                                        "their documents (d mod N); list choice split by query + all-gather")
+    line["run"]["_exact_tid"], line["run"]["_exact_cnt"] = ex[0], ex[3]
     line["run"].update({"recall_at_100": rec, "ivf_build_s": ivf_build_s,
                         "recall_note": "against the engine's exact filtered top-k of the same queries (probes = 0)"})
 
@@ -999,6 +1004,32 @@ def ivf_cpu_leg(line, args, wl, ix, dev, tid, doc, ur, dr, qusers, Q, main_r, iv
     except AssertionError as e:
         ok = False
         note += " — MISMATCH: " + str(e)[:200]
+    # recall@k against the ORACLE's exact filtered top-k (pgvector's exact scan restated on the CPU over every row the user may
+    # see) on a few of the queries: the engine's own exact result, which the line's recall is taken against, is thereby checked
+    # at full size as well
+    S2 = min(S, 4)
+    rec_o, same_exact = [], True
+    ex_t, ex_c = line["run"].get("_exact_tid"), line["run"].get("_exact_cnt")
+    doc_all = np.asarray(doc)
+    for i in range(S2):
+        vis = np.zeros(int(doc_all.max()) + 2, dtype=bool)
+        for r in roles_of.get(int(qusers[i]), ()):
+            vis[np.asarray(docs_of.get(r, []), dtype=np.int64)] = True
+        vrows = np.flatnonzero(vis[doc_all])
+        Xv = np.empty((len(vrows), dim), dtype=np.float32)
+        for a0 in range(0, len(vrows), CH):
+            Xv[a0:a0 + CH] = gen_rows(wl, vrows[a0:a0 + CH], dev).cpu().numpy()
+        t_, _, _, _, c_ = orc.search_batch(Xv, tid[vrows], [np.arange(len(vrows), dtype=np.uint32)], [[0]] if len(vrows) else [[]], Qn[i:i + 1],
+                                           m, args.k, dedup=False, nthreads=host_cores(), variant="pgvflags", ref=orc.ref_loops())
+        truth = set(t_[0, :int(c_[0])].tolist())
+        rec_o.append(len(truth & set(g_tid[i, :int(g_cnt[i])].tolist())) / max(1, len(truth)))
+        if ex_t is not None:
+            same_exact = same_exact and set(ex_t[i, :int(ex_c[i])].view(np.uint64).tolist()) == truth
+        del Xv
+    line["run"]["recall_at_100_vs_oracle_exact"] = {"value": float(np.mean(rec_o)) if rec_o else None, "queries": S2,
+                                                    "engine_exact_ids_equal_oracle_exact": bool(same_exact) if ex_t is not None else None}
+    line["run"].pop("_exact_tid", None)
+    line["run"].pop("_exact_cnt", None)
     line["cpu_baseline"] = {
         "value": S / dtc, "unit": "queries/s", "cores": 1, "kind": "port",
         "sample": f"{S} of the step's {args.nq} queries, nprobe {args.nprobe}, the oracle's restatement of ivfscan.c (centre scoring, "
@@ -1014,7 +1045,8 @@ def leg_summary(line):
            "steps": line["steps"], "e2e": line["e2e"]["value"], "engine": line["run"]["engine"], "dtype": line["dtype"],
            "roofline": {k: rf.get(k) for k in ("bound", "kernel", "achieved", "peak", "unit", "frac", "kernel_ms", "dram_frac", "l2_share", "traffic",
                                                "plan", "frac_of_measured_bf16_sustained") if rf.get(k) is not None},
-           "gpu_launches": line["gpu_launches"], "recall_at_100": line["run"].get("recall_at_100")}
+           "gpu_launches": line["gpu_launches"], "recall_at_100": line["run"].get("recall_at_100"),
+           "recall_at_100_vs_oracle_exact": line["run"].get("recall_at_100_vs_oracle_exact")}
     if "cpu_baseline" in line:
         cb = line["cpu_baseline"]
         out["cpu_baseline"] = {k: cb.get(k) for k in ("value", "cores", "kind", "gpu_ids_match", "gpu_distances_match")}

@@ -83,3 +83,18 @@ def test_importing_the_generators_does_not_load_the_engine_library():
             "assert 'librbacknn' not in open('/proc/self/maps').read(); "
             "assert 'vectorsearch_rbac_b200._lib' not in sys.modules") % ROOT
     subprocess.run([sys.executable, "-c", code], check=True)
+
+
+def test_two_level_cohere_shape():
+    """The C4 corpus: finite, norms of order one, any row range regenerates identically, rows of one sub-topic closer to each
+    other than rows of different topics."""
+    rows = torch.arange(0, 4000)
+    c = synth.corpus("cohere2", rows, 96, seed=5)
+    assert torch.isfinite(c).all() and 0.5 < c.norm(dim=1).mean() < 1.5
+    assert torch.equal(synth.corpus("cohere2", torch.arange(1000, 1500), 96, seed=5), c[1000:1500])
+    h = synth._lsr(synth._mix64(rows ^ synth._s64(5 * 7919 + 21)), 11)
+    macro = (h % 64).numpy()
+    d = torch.cdist(c[:400], c[:400]).numpy()
+    same = macro[:400, None] == macro[None, :400]
+    off = ~np.eye(400, dtype=bool)
+    assert d[same & off].mean() < d[~same].mean()

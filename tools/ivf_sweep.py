@@ -11,7 +11,7 @@ import bench, vectorsearch_rbac_b200 as vr
 ap = argparse.ArgumentParser()
 ap.add_argument("--rows", type=int, default=10_000_000)
 ap.add_argument("--dim", type=int, default=768)
-ap.add_argument("--kind", default="cohere")
+ap.add_argument("--kind", default="cohere2")
 ap.add_argument("--lists", type=int, default=4096)
 ap.add_argument("--nq", type=int, default=1000)
 ap.add_argument("--k", type=int, default=100)
