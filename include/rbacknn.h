@@ -322,7 +322,8 @@ typedef struct rk_stats {
     uint64_t tensor_redo;      /* RK_ENGINE_TENSOR: queries of the last batch re-run on the scan   */
     uint64_t tensor_exact;     /* RK_ENGINE_TENSOR: 1 = TF32 was exact for the last batch          */
     uint64_t tensor_plan;      /* last batch: 0 = not on the tensor engine, 1 = dense, 2 = per user mask,
-                                  3 = per document class (atoms); +16 when the sampling pass ran      */
+                                  3 = per document class (atoms); +16 when the sampling pass ran, +32 CTA-pair kernel,
+                                  +64 bf16 nomination                                                */
     uint64_t tensor_flop;      /* last tensor batch: 2 * dim * (query, row) pairs scored (main pass) */
     uint64_t tensor_plan_bytes;/* last tensor batch: bytes the plan stages (visited tiles x query tiles) */
     uint64_t segment_kinds;    /* last scan launch: bit i set = the work list held segments of kind i (0 extent table,

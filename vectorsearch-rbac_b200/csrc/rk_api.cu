@@ -176,6 +176,8 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.tensor_smin = std::max(1, env_int("RK_TENSOR_SMIN", 1024));
         t.tensor_host_timing = getenv("RK_TENSOR_HOST_TIMING") != nullptr;
         t.tensor_bf16 = env_int("RK_TENSOR_BF16", -1);
+        t.tensor_kp_extra = std::max(0, env_int("RK_TENSOR_KP_EXTRA", 0));
+        t.tensor_kp_bf16 = std::max(0, env_int("RK_TENSOR_KP_BF16", 64));
         t.tensor_qtau = env_int("RK_TENSOR_QTAU", 1);
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
@@ -205,6 +207,8 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "tensor_smin")) t.tensor_smin = std::max(1, v);
     else if (!strcmp(name, "tensor_host_timing")) t.tensor_host_timing = v != 0;
     else if (!strcmp(name, "tensor_bf16")) t.tensor_bf16 = v;
+    else if (!strcmp(name, "tensor_kp_extra")) t.tensor_kp_extra = std::max(0, v);
+    else if (!strcmp(name, "tensor_kp_bf16")) t.tensor_kp_bf16 = std::max(0, v);
     else if (!strcmp(name, "tensor_qtau")) t.tensor_qtau = v;
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
@@ -231,7 +235,8 @@ extern "C" void rk_close(rk_index *ix)
     for (auto *b : bufs) b->release();
     TensorState &ts = ix->tensor;
     DevBuf *tb[] = {&ts.d_xnorm, &ts.d_rowmask, &ts.d_probe, &ts.d_units, &ts.d_qnorm, &ts.d_scratch, &ts.d_cand_key, &ts.d_cand_row,
-                    &ts.d_cand_count, &ts.d_sel_key, &ts.d_sel_row, &ts.d_sel_count, &ts.d_flags, &ts.d_plan, &ts.d_qp, &ts.d_tiles};
+                    &ts.d_cand_count, &ts.d_sel_key, &ts.d_sel_row, &ts.d_sel_count, &ts.d_flags, &ts.d_plan, &ts.d_qp, &ts.d_tiles,
+                    &ts.d_rowmask2, &ts.d_tau_key, &ts.d_tau_count, &ts.d_xb, &ts.d_qpb, &ts.d_redo};
     for (auto *b : tb) b->release();
     ts.h_flags.release();
     delete ix;

@@ -26,6 +26,8 @@
 //            latency exposed: tcgen05.ld (one TMEM lane = one row), distance, mask test, threshold test
 //            against the running per-query tau, append to per-query candidate buffers (global
 //            scratch, L2 resident); warp-parallel radix-select compaction when a buffer fills.
+#include <cuda_bf16.h>
+
 #include "rk_bscan_dev.cuh"
 #include "rk_kernels.h"
 
@@ -521,7 +523,8 @@ __global__ void __launch_bounds__(RS_THREADS) rk_rescore_kernel(const RkRescoreP
                 // exact iff operands are small integers (exact in TF32, products exact in fp32) and every partial sum
                 // stays below 2^24: |x|^2 + |q|^2 + 2 |x.q| <= (|x| + |q|)^2 by Cauchy-Schwarz
                 const float nx = sqrtf(p.xnorm_max), nq = sqrtf(__uint_as_float((uint32_t) (p.probe[4] & 0xFFFFFFFFull)));
-                if (p.x_integer && p.probe[0] == 0ull && (nx + nq) * (nx + nq) < 16700000.0f) eps_scale = 0.f;
+                const float qabs = __uint_as_float((uint32_t) (p.probe[1] & 0xFFFFFFFFull));       // largest |value| of the queries
+                if (p.x_integer && p.probe[0] == 0ull && (nx + nq) * (nx + nq) < 16700000.0f && fmaxf(p.x_absmax, qabs) <= p.exact_absmax) eps_scale = 0.f;
             }
             if (eps_scale > 0.f) eps = eps_scale * sqrtf(p.xnorm_max * p.qnorm[q]) + 1e-6f * (p.xnorm_max + p.qnorm[q]);
             if (cnt < k || !(a_last - eps > e_k)) uncertain = 1;
@@ -603,6 +606,23 @@ __global__ void rk_max_f32_kernel(const float *__restrict__ x, size_t n, unsigne
     if ((threadIdx.x & 31) == 0) atomicMax(out, mx);
 }
 
+// fp32 rows [n][dim_pad] -> bf16 rows [n][dim_b] (round to nearest even; dim_b >= dim_pad, the tail is zero)
+__global__ void rk_rows_to_bf16_kernel(const float *__restrict__ x, size_t n, int dim_pad, int dim_b, __nv_bfloat16 *__restrict__ out)
+{
+    const size_t total = n * (size_t) dim_b;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < total; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / (size_t) dim_b;
+        const int c = (int) (i - r * (size_t) dim_b);
+        out[i] = __float2bfloat16_rn(c < dim_pad ? x[r * (size_t) dim_pad + c] : 0.f);
+    }
+}
+
+cudaError_t rk_launch_rows_to_bf16(const float *x, size_t n, int dim_pad, int dim_b, void *out, cudaStream_t stream)
+{
+    if (n) rk_rows_to_bf16_kernel<<<148 * 16, 256, 0, stream>>>(x, n, dim_pad, dim_b, reinterpret_cast<__nv_bfloat16 *>(out));
+    return cudaGetLastError();
+}
+
 cudaError_t rk_launch_row_norms(const float *x, size_t n, int dim_pad, float *out, cudaStream_t stream)
 {
     if (n) rk_row_norms_kernel<<<148 * 8, 256, 0, stream>>>(x, n, dim_pad, out);
@@ -641,8 +661,15 @@ typedef CUresult (*rk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t,
                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// 2-D fp32 tensor [rows][dim_pad], box = 32 floats x box_rows, 128-byte swizzle, zero fill out of bounds.
+// 2-D tensor [rows][row_elems] of fp32 (box = 32 elements x box_rows) or bf16 (box = 64 elements x box_rows): 128 bytes per box
+// row either way, 128-byte swizzle, zero fill out of bounds.
+cudaError_t rk_make_tensor_map_2d_t(CUtensorMap *tm, const void *base, uint64_t rows, int row_elems, uint32_t box_rows, bool bf16);
 cudaError_t rk_make_tensor_map_2d(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad, uint32_t box_rows)
+{
+    return rk_make_tensor_map_2d_t(tm, base, rows, dim_pad, box_rows, false);
+}
+
+cudaError_t rk_make_tensor_map_2d_t(CUtensorMap *tm, const void *base, uint64_t rows, int row_elems, uint32_t box_rows, bool bf16)
 {
     static rk_encode_fn encode = nullptr;
     if (!encode) {
@@ -653,11 +680,11 @@ cudaError_t rk_make_tensor_map_2d(CUtensorMap *tm, const float *base, uint64_t r
         if (!fn || qres != cudaDriverEntryPointSuccess) return cudaErrorNotSupported;
         encode = reinterpret_cast<rk_encode_fn>(fn);
     }
-    cuuint64_t gdim[2] = {(cuuint64_t) dim_pad, (cuuint64_t) (rows ? rows : 1)};
-    cuuint64_t gstride[1] = {(cuuint64_t) dim_pad * 4};
-    cuuint32_t box[2] = {BS_KC, box_rows};
+    cuuint64_t gdim[2] = {(cuuint64_t) row_elems, (cuuint64_t) (rows ? rows : 1)};
+    cuuint64_t gstride[1] = {(cuuint64_t) row_elems * (bf16 ? 2u : 4u)};
+    cuuint32_t box[2] = {bf16 ? 2u * BS_KC : BS_KC, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estr,
+    CUresult r = encode(tm, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void *>(base), gdim, gstride, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;

@@ -123,6 +123,19 @@ __device__ __forceinline__ void b2_commit(uint64_t *bar)
                  : "memory");
 }
 
+// bf16 operands (kind::f16, a/b format bf16 in the instruction descriptor), K = 16 elements = 32 bytes per instruction
+__device__ __forceinline__ void b2_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 __device__ __forceinline__ void b2_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
 {
     asm volatile(
@@ -220,6 +233,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
             const CUtensorMap *tq = half <= 8 ? &tmq8 : half <= 16 ? &tmq16 : half <= 32 ? &tmq32 : half <= 64 ? &tmq64 : &tmq128;
             const uint32_t tx = 2u * (16384u + half * 128u);      // both CTAs' boxes land on the leader's barrier
             const int qrow = (int) (un.q0 + rank * half);
+            const int kc_elems = p.bf16 ? 2 * B2_KC : B2_KC;          // 128 bytes of a row per k-chunk either way
             for (uint32_t i0 = 0; i0 < ntiles; i0 += 32) {
                 const uint32_t idx = i0 + (uint32_t) lane;
                 uint32_t rmine = B2_DUMMY_ROW;
@@ -236,8 +250,8 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                             unsigned char *st = smem + L.off_stage + (size_t) stage * B2_STAGE_BYTES;
                             if (leader) rk_mbar_arrive_expect_tx(&full[stage], tx);
                             const uint32_t lbar = b2_mapa(rk_smem_u32(&full[stage]), 0);
-                            b2_tma_2d(st, &tmx, kc * B2_KC, row0, lbar);
-                            b2_tma_2d(st + 16384, tq, kc * B2_KC, qrow, lbar);
+                            b2_tma_2d(st, &tmx, kc * kc_elems, row0, lbar);
+                            b2_tma_2d(st + 16384, tq, kc * kc_elems, qrow, lbar);
                             if (++stage == S) { stage = 0; phase ^= 1u; }
                         }
                     }
@@ -255,7 +269,9 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 const RkBUnit ua = p.units[2 * pi], ub = p.units[2 * pi + 1];
                 const uint32_t ncol = b2_ncol(ua.nq);
                 // c=F32, a=b=TF32, K-major both, N>>3, M>>4 (M = 256 over the pair)
-                const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((ncol >> 3) << 17) | ((256u >> 4) << 24);
+                // (bf16 nomination: a = b = BF16, kind::f16)
+                const uint32_t fmt = p.bf16 ? 1u : 2u;
+                const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((ncol >> 3) << 17) | ((256u >> 4) << 24);
                 const uint32_t ntiles = max(bs_unit_tiles(ua), bs_unit_tiles(ub));
                 for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                     const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
@@ -268,9 +284,16 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                         if (lane == 0) {
                             const uint32_t a0 = rk_smem_u32(smem + L.off_stage + (size_t) stage * B2_STAGE_BYTES);
                             const uint64_t ad = bs_smem_desc(a0), bd = bs_smem_desc(a0 + 16384u);
+                            // four MMAs per k-chunk, 32 bytes of K each: 8 TF32 or 16 bf16 elements (+2 in 16-byte units)
+                            if (p.bf16) {
 #pragma unroll
-                            for (int k = 0; k < B2_KC / 8; k++)
-                                b2_mma_tf32(d_tmem, ad + (uint64_t) (2 * k), bd + (uint64_t) (2 * k), idesc, (kc | k) != 0);
+                                for (int k = 0; k < 4; k++)
+                                    b2_mma_bf16(d_tmem, ad + (uint64_t) (2 * k), bd + (uint64_t) (2 * k), idesc, (kc | k) != 0);
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < 4; k++)
+                                    b2_mma_tf32(d_tmem, ad + (uint64_t) (2 * k), bd + (uint64_t) (2 * k), idesc, (kc | k) != 0);
+                            }
                             b2_commit(&empty[stage]);
                             if (kc == p.kchunks - 1) b2_commit(&tfull[buf]);
                         }
@@ -303,6 +326,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
         auto esync = [] { rk_named_bar_sync(2, B2_EW * 32); };
         const uint32_t te0 = b2_mapa(rk_smem_u32(&tempty[0]), 0), te1 = b2_mapa(rk_smem_u32(&tempty[1]), 0);
         uint32_t tcount = 0;
+        uint32_t qid = 0, qt_next = RK_KEY_SENTINEL;   // this thread's query (column et) and its shared threshold as last fetched
         for (uint32_t ui = u_begin; ui < u_end; ui++) {
             const uint32_t pi = p.cta_units[ui];
             const RkBUnit un = p.units[2 * pi + rank];
@@ -313,10 +337,13 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 const bool live = (uint32_t) et < un.nq;
                 uint32_t tau0 = live ? RK_KEY_SENTINEL : 0u;      // a padded column never collects anything
                 if (live && p.tau_key && p.tau_count[un.q0 + et] >= p.kp) tau0 = rk_float_to_key(p.tau_key[(size_t) (un.q0 + et) * p.kp + (p.kp - 1)]);
+                qid = live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u;
+                if (live && p.qtau) tau0 = min(tau0, __ldcg(p.qtau + qid));       // what the query's other units have proved so far (RkBScanParams::qtau)
+                qt_next = tau0;
                 c.tau[et] = tau0;
                 tauf[et] = bs_tau_float(tau0);
                 c.cnt[et] = 0;
-                s_trunc[et] = p.trunc + (live ? (p.slot_q ? p.slot_q[un.q0 + et] : un.q0 + (uint32_t) et) : 0u);
+                s_trunc[et] = p.trunc + qid;
                 uint64_t w0 = ~0ull, w1 = 0ull;
                 if (p.use_mask) {
                     w0 = live ? p.qmask[(size_t) (un.q0 + et) * W] : 0ull;
@@ -359,6 +386,11 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
+                if (p.qtau && (ti & 3u) == 3u && (uint32_t) et < un.nq) {
+                    // the shared threshold fetched four tiles ago (no load latency on this path), then the next fetch
+                    if (qt_next < c.tau[et]) { c.tau[et] = qt_next; tauf[et] = bs_tau_float(qt_next); }
+                    qt_next = __ldcg(p.qtau + qid);
+                }
                 if (umask && !(own_n && ma_n == um0 && mb_n == um1)) { own_n = false; ma_n = 0; mb_n = 0; }
                 const bool valid = row < p.nrows && own_n;
                 const float xn = xn_n;
@@ -453,6 +485,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                         if (n > BS_CAP - 2 * B2_M) {
                             uint32_t tau;
                             uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
+                            if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);     // >= kp rows are <= tau
                             if (m > BS_CAP / 2 && tau > 0) {
                                 tau -= 1u;
                                 m = bs_warp_filter(c, (int) q, m, tau);
@@ -469,6 +502,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 if (n > (uint32_t) p.kp) {
                     uint32_t tau;
                     n = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau);
+                    if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);
                     if (n > BS_SORT_MAX && tau > 0) {
                         n = bs_warp_filter(c, (int) q, n, tau - 1u);
                         if (lane == 0) *s_trunc[q] = 1;
@@ -493,13 +527,15 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
 size_t rk_bscan2_smem_bytes(int mask_words) { return b2_smem_layout(mask_words).total; }
 size_t rk_bscan2_scratch_bytes(int grid) { return (size_t) grid * B2_N * BS_CAP * sizeof(uint2); }
 
-cudaError_t rk_launch_bscan2(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream)
+cudaError_t rk_launch_bscan2(const RkBScanParams &p, const void *x, const void *q, uint64_t nq, int grid, cudaStream_t stream, int row_elems_b)
 {
     CUtensorMap tmx, tmq[5];
-    cudaError_t e = rk_make_tensor_map_2d(&tmx, x, p.nrows, p.dim_pad, B2_M);
+    const bool bf = p.bf16 != 0;
+    const int row_elems = bf ? row_elems_b : p.dim_pad;
+    cudaError_t e = rk_make_tensor_map_2d_t(&tmx, x, p.nrows, row_elems, B2_M, bf);
     if (e != cudaSuccess) return e;
     for (int i = 0; i < 5; i++) {
-        e = rk_make_tensor_map_2d(&tmq[i], q, nq, p.dim_pad, 8u << i);
+        e = rk_make_tensor_map_2d_t(&tmq[i], q, nq, row_elems, 8u << i, bf);
         if (e != cudaSuccess) return e;
     }
     const size_t smem = rk_bscan2_smem_bytes(p.mask_words);

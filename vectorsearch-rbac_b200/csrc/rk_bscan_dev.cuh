@@ -276,3 +276,4 @@ __device__ __forceinline__ uint32_t bs_unit_tiles(const RkBUnit &un)
 
 // 2-D fp32 tensor map [rows][dim_pad], box = 32 floats x box_rows, 128-byte swizzle, zero fill out of bounds (rk_bscan.cu)
 cudaError_t rk_make_tensor_map_2d(CUtensorMap *tm, const float *base, uint64_t rows, int dim_pad, uint32_t box_rows);
+cudaError_t rk_make_tensor_map_2d_t(CUtensorMap *tm, const void *base, uint64_t rows, int row_elems, uint32_t box_rows, bool bf16);

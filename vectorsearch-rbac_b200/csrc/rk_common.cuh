@@ -191,6 +191,9 @@ struct RkBScanParams {
     // compaction lowers it (atomicMin), units start from it and re-read it every few tiles — so the units of a query nominate
     // kp rows between them, not kp each.  RK_KEY_SENTINEL before the launch; NULL = every unit on its own.
     uint32_t *qtau;
+    // bf16 nomination (CTA-pair kernel): the tensor maps describe bf16 shadow copies of the rows and the queries, a k-chunk is
+    // 64 elements (the same 128 bytes per row) and the MMA is kind::f16 with bf16 operands, fp32 accumulation
+    int bf16;
 };
 
 struct RkRescoreParams {
@@ -211,6 +214,8 @@ struct RkRescoreParams {
     // probe[0] = query elements that are not small integers, low word of probe[4] = bits of the largest squared query norm
     const unsigned long long *probe;
     int x_integer;               // the corpus holds only small integers
+    float exact_absmax;          // largest |value| the nomination format holds exactly for integers (TF32: 2047, bf16: 256)
+    float x_absmax;              // largest |value| of the corpus
     int wide_rows;               // the scan scores a row with a whole warp (tile_rows < 64): use its summation order
     uint64_t *out_tid;
     uint32_t *out_doc;

@@ -147,6 +147,9 @@ struct TensorState {
     bool x_integer = false;
     float x_absmax = 0.f, xnorm_max = 0.f;
     DevBuf d_plan, d_qp, d_tiles;
+    DevBuf d_xb, d_qpb;                  // bf16 nomination: shadow copy of the row store [rows][dim_b] (built on first use), of the gathered queries
+    bool bf16_off = false;               // the bf16 nomination's proof refused too many queries of a batch: this index nominates in TF32 from now on
+    int dim_b = 0;                       // elements per bf16 row (dim_pad rounded up to 8: 16-byte rows for the tensor map)
     std::vector<uint32_t> h_tiles;                                              // tile lists of all cached role masks
     std::map<std::vector<uint64_t>, std::pair<uint32_t, uint32_t>> tile_cache;  // role mask -> (offset, count) in h_tiles
     std::vector<std::pair<uint32_t, uint32_t>> tile_by_mask_id;                 // the same, by UserInfo::mask_id (count ~0u = not built yet)
@@ -155,6 +158,7 @@ struct TensorState {
     bool tiles_dirty = false;                                                   // h_tiles grew since the last upload
     int last_plan = 0;
     uint64_t last_plan_bytes = 0;
+    DevBuf d_redo;                       // queries the proof refused: their indices, vectors and the sub-batch's outputs (one block)
     DevBuf d_units, d_qnorm, d_scratch, d_cand_key, d_cand_row, d_cand_count, d_sel_key, d_sel_row, d_sel_count, d_tau_key, d_tau_count, d_flags;
     PinBuf h_flags;
     double last_flop = 0.0;
@@ -173,7 +177,9 @@ struct RkTuning {
     int tensor_smin = 1024;      // RK_TENSOR_SMIN
     int tensor_host_timing = 0;  // RK_TENSOR_HOST_TIMING
     int tensor_qtau = 1;         // RK_TENSOR_QTAU: 0 = every unit of the tensor engine keeps its own threshold
-    int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = by row length, 0 = TF32 nomination, 1 = bf16 nomination
+    int tensor_kp_extra = 0;     // RK_TENSOR_KP_EXTRA: added to the nominations per query (kp = max(2k, k + 128) + ...; at most 512)
+    int tensor_kp_bf16 = 64;     // RK_TENSOR_KP_BF16: added on top when the nomination runs in bf16 (C2: 9 refused queries per 1000 -> 1)
+    int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = bf16 on the CTA-pair kernel while the proof accepts it, 0 = TF32 nomination, 1 = bf16 always
     int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
     int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path

@@ -18,6 +18,7 @@ cudaError_t rk_launch_select(const RkSelectParams &p, int nq, cudaStream_t strea
 // small utility kernels (rk_util.cu)
 cudaError_t rk_launch_gather_rows(const float *src, float *dst, const uint32_t *perm, size_t n, int dim_pad,
                                   cudaStream_t stream);
+cudaError_t rk_launch_scatter_chunks(const void *src, void *dst, const uint32_t *idx, size_t n, int words, cudaStream_t stream);
 cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, int dim_pad, cudaStream_t stream);
 // counts NaN / Inf elements of a device array (synchronous; result in *out)
 cudaError_t rk_count_nonfinite(const float *d_x, size_t n, unsigned long long *out, cudaStream_t stream);
@@ -51,7 +52,9 @@ cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float 
 // cta_off / cta_units schedule PAIRS onto clusters; grid = 2 x clusters
 size_t rk_bscan2_smem_bytes(int mask_words);
 size_t rk_bscan2_scratch_bytes(int grid);
-cudaError_t rk_launch_bscan2(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream);
+// x / q: fp32 [rows][dim_pad], or with p.bf16 their bf16 shadow copies [rows][row_elems_b]
+cudaError_t rk_launch_bscan2(const RkBScanParams &p, const void *x, const void *q, uint64_t nq, int grid, cudaStream_t stream, int row_elems_b = 0);
+cudaError_t rk_launch_rows_to_bf16(const float *x, size_t n, int dim_pad, int dim_b, void *out, cudaStream_t stream);
 cudaError_t rk_launch_rescore(const RkRescoreParams &p, int nq, cudaStream_t stream);
 cudaError_t rk_launch_row_norms(const float *x, size_t n, int dim_pad, float *out, cudaStream_t stream);
 cudaError_t rk_launch_rowmask(const uint32_t *rowdoc, const uint64_t *doc_mask, size_t n, int W, uint64_t *out, cudaStream_t stream);

@@ -528,23 +528,57 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
         o2.engine = RK_ENGINE_SCAN;
         const uint64_t tl = ws.launches;
         const int plan_used = ix->tensor.last_plan;
+        const bool timing_was = ws.timing, ts_scan = ws.timed_scan, ts_sel = ws.timed_select;
+        ws.timing = false;               // the timing ring keeps the scoring passes of this call, not the re-runs' scans
         if (redo.size() * 4 > nq) {
             rc = search_device(ix, ws, nq, dQ, user_ids, &o2, 0, out);
+        } else if (redo.size() == 1) {
+            const uint32_t q = redo[0];
+            RkSelectParams o1 = out;
+            const size_t ob = (size_t) q * o->k;
+            if (o1.out_tid) o1.out_tid += ob;
+            if (o1.out_doc) o1.out_doc += ob;
+            if (o1.out_dist) o1.out_dist += ob;
+            if (o1.out_key) o1.out_key += ob;
+            if (o1.out_row) o1.out_row += ob;
+            if (o1.out_count) o1.out_count += q;
+            rc = search_device(ix, ws, 1, dQ + (size_t) q * ix->dim_pad, user_ids ? user_ids + q : nullptr, &o2, 0, o1);
         } else {
-            for (uint32_t q : redo) {
-                RkSelectParams o1 = out;
-                const size_t ob = (size_t) q * o->k;
-                if (o1.out_tid) o1.out_tid += ob;
-                if (o1.out_doc) o1.out_doc += ob;
-                if (o1.out_dist) o1.out_dist += ob;
-                if (o1.out_key) o1.out_key += ob;
-                if (o1.out_row) o1.out_row += ob;
-                if (o1.out_count) o1.out_count += q;
-                rc = search_device(ix, ws, 1, dQ + (size_t) q * ix->dim_pad, user_ids ? user_ids + q : nullptr, &o2, 0, o1);
-                if (rc < 0) break;
+            // the refused queries as ONE sub-batch on the scan engine (one scan launch + one select, not a pair per query):
+            // gather their vectors, search into a scratch block, scatter the rows of every output array to their places
+            const size_t nr = redo.size(), k = (size_t) o->k, rb = (size_t) ix->dim_pad * 4;
+            const size_t o_idx = 0, o_q = (nr * 4 + 255) & ~(size_t) 255, o_tid = o_q + ((nr * rb + 255) & ~(size_t) 255),
+                         o_dist = o_tid + nr * k * 8, o_doc = o_dist + nr * k * 8, o_key = o_doc + nr * k * 4, o_row = o_key + nr * k * 4,
+                         o_cnt = o_row + nr * k * 4, total = o_cnt + nr * 4 + 256;
+            DevBuf &rb_ = ix->tensor.d_redo;
+            if (rb_.ensure(total) != 0) return RK_ERR_CUDA;
+            unsigned char *base = rb_.as<unsigned char>();
+            std::vector<uint32_t> sub_users(nr);
+            for (size_t i = 0; i < nr; i++) sub_users[i] = user_ids ? user_ids[redo[i]] : 0u;
+            // (pageable source: the copy is staged by the runtime before the call returns)
+            RK_CUDA(cudaMemcpyAsync(base + o_idx, redo.data(), nr * 4, cudaMemcpyHostToDevice, ws.stream));
+            const uint32_t *d_idx = reinterpret_cast<const uint32_t *>(base + o_idx);
+            RK_CUDA(rk_launch_gather_rows(dQ, reinterpret_cast<float *>(base + o_q), d_idx, nr, ix->dim_pad, ws.stream));
+            RkSelectParams o1 = out;
+            o1.out_tid = out.out_tid ? reinterpret_cast<uint64_t *>(base + o_tid) : nullptr;
+            o1.out_dist = out.out_dist ? reinterpret_cast<double *>(base + o_dist) : nullptr;
+            o1.out_doc = out.out_doc ? reinterpret_cast<uint32_t *>(base + o_doc) : nullptr;
+            o1.out_key = out.out_key ? reinterpret_cast<float *>(base + o_key) : nullptr;
+            o1.out_row = out.out_row ? reinterpret_cast<uint32_t *>(base + o_row) : nullptr;
+            o1.out_count = out.out_count ? reinterpret_cast<int32_t *>(base + o_cnt) : nullptr;
+            rc = search_device(ix, ws, nr, reinterpret_cast<const float *>(base + o_q), user_ids ? sub_users.data() : nullptr, &o2, 0, o1);
+            if (rc >= 0) {
+                if (out.out_tid) RK_CUDA(rk_launch_scatter_chunks(o1.out_tid, out.out_tid, d_idx, nr, (int) (2 * k), ws.stream));
+                if (out.out_dist) RK_CUDA(rk_launch_scatter_chunks(o1.out_dist, out.out_dist, d_idx, nr, (int) (2 * k), ws.stream));
+                if (out.out_doc) RK_CUDA(rk_launch_scatter_chunks(o1.out_doc, out.out_doc, d_idx, nr, (int) k, ws.stream));
+                if (out.out_key) RK_CUDA(rk_launch_scatter_chunks(o1.out_key, out.out_key, d_idx, nr, (int) k, ws.stream));
+                if (out.out_row) RK_CUDA(rk_launch_scatter_chunks(o1.out_row, out.out_row, d_idx, nr, (int) k, ws.stream));
+                if (out.out_count) RK_CUDA(rk_launch_scatter_chunks(o1.out_count, out.out_count, d_idx, nr, 1, ws.stream));
+                ws.launches += 7;
             }
         }
         ws.launches += tl;
+        ws.timing = timing_was; ws.timed_scan = ts_scan; ws.timed_select = ts_sel; ws.timed_probe = false;
         ix->tensor.last_plan = plan_used;
         return rc;
     }

@@ -314,7 +314,11 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     TensorState &ts = ix->tensor;
     const int W = ix->mask_words;
     const int k = o->k;
-    int kp = std::max(2 * k, k + 128);
+    // nominations per query: the proof needs the kp-th approximate value to clear the exact k-th by the error bound; the
+    // coarser bf16 nomination takes a longer list (option tensor_kp_extra adds to either)
+    const bool bf16_likely = (ix->tune.tensor_pair >= 0 ? ix->tune.tensor_pair != 0 : ix->dim_pad >= 256) &&
+                             (ix->tune.tensor_bf16 == 1 || (ix->tune.tensor_bf16 < 0 && !ix->tensor.bf16_off));
+    int kp = std::max(2 * k, k + 128) + ix->tune.tensor_kp_extra + (bf16_likely ? ix->tune.tensor_kp_bf16 : 0);
     if (kp > 512) kp = 512;
     const size_t n = ix->nrows;
     const uint32_t T = (uint32_t) ((n + 127) / 128);
@@ -574,6 +578,27 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // (the probe result is only needed for the rescore launch: the scoring passes are queued first)
     const float *dQp = ts.d_qp.as<float>();
     if (nslots) { RK_CUDA(rk_launch_gather_rows(dQ, ts.d_qp.as<float>(), d_slotq, nslots, ix->dim_pad, st)); launches++; }
+    // bf16 nomination (CTA-pair kernel only; option tensor_bf16: 1 = on, 0 / -1 = TF32): half the operand bytes through the
+    // shared-memory port that bounds the TF32 main pass and twice the MMA rate.  The exact fp32 re-score and the sufficiency
+    // proof make the ANSWER independent of the nomination precision; what changes is the proof's margin (eps below), i.e.
+    // how often a query has to be re-run.  The shadow copy of the row store is built on first use.
+    // -1 (default): on for the pair kernel until a batch has had more than 2 % of its queries refused by the proof — the
+    // margin depends on the data — after which this index goes back to TF32; 1 = always, 0 = never
+    const bool bf16 = paired && (tune.tensor_bf16 == 1 || (tune.tensor_bf16 < 0 && !ts.bf16_off));
+    if (bf16) {
+        const int dim_b = (ix->dim_pad + 7) & ~7;
+        if (ts.dim_b != dim_b || ts.d_xb.p == nullptr) {
+            if (ts.d_xb.ensure((n + 256) * (size_t) dim_b * 2) != 0) return RK_ERR_CUDA;
+            RK_CUDA(rk_launch_rows_to_bf16(ix->d_x.as<float>(), n, ix->dim_pad, dim_b, ts.d_xb.p, st));
+            ts.dim_b = dim_b;
+            ix->device_bytes += ts.d_xb.cap;
+            launches++;
+        }
+        if (ts.d_qpb.ensure(std::max<size_t>(nslots * (size_t) dim_b * 2, 16)) != 0) return RK_ERR_CUDA;
+        if (nslots) { RK_CUDA(rk_launch_rows_to_bf16(dQp, nslots, ix->dim_pad, dim_b, ts.d_qpb.p, st)); launches++; }
+    }
+    const void *x_nom = bf16 ? ts.d_xb.p : ix->d_x.p;
+    const void *q_nom = bf16 ? ts.d_qpb.p : (const void *) dQp;
 
     tick(2);      // staged, uploads and query preparation enqueued
     RkBScanParams bp;
@@ -581,7 +606,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     bp.tile_rows = plan != PLAN_DENSE ? ts.d_tiles.as<uint32_t>() : nullptr;
     bp.nrows = n;
     bp.dim_pad = ix->dim_pad;
-    bp.kchunks = (ix->dim_pad + 31) / 32;
+    bp.kchunks = bf16 ? (ts.dim_b + 63) / 64 : (ix->dim_pad + 31) / 32;
+    bp.bf16 = bf16 ? 1 : 0;
     bp.metric = ix->metric;
     bp.kp = kp;
     bp.mask_words = W;
@@ -624,7 +650,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         bp.trunc = ts.d_flags.as<int32_t>() + 2 * nq;      // ties dropped here only loosen the seed
         bp.tau_key = nullptr; bp.tau_count = nullptr;
         bp.qtau = nullptr;
-        RK_CUDA((paired ? rk_launch_bscan2 : rk_launch_bscan)(bp, ix->d_x.as<float>(), dQp, nslots, ps_.grid, st));
+        if (paired) RK_CUDA(rk_launch_bscan2(bp, x_nom, q_nom, nslots, ps_.grid, st, ts.dim_b));
+        else RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, ps_.grid, st));
         // per slot: the sample's kp smallest values
         sp.lid0 = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lid0);
         sp.lstep = reinterpret_cast<const uint32_t *>(dplan + ps_.o_lstep);
@@ -641,7 +668,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
         bp.qtau = ix->tune.tensor_qtau ? reinterpret_cast<uint32_t *>(ts.d_flags.as<int32_t>() + 3 * nq) : nullptr;
         bp.tau_key = sampled ? ts.d_tau_key.as<float>() : nullptr;
         bp.tau_count = sampled ? ts.d_tau_count.as<int32_t>() : nullptr;
-        RK_CUDA((paired ? rk_launch_bscan2 : rk_launch_bscan)(bp, ix->d_x.as<float>(), dQp, nslots, pm_.grid, st));
+        if (paired) RK_CUDA(rk_launch_bscan2(bp, x_nom, q_nom, nslots, pm_.grid, st, ts.dim_b));
+        else RK_CUDA(rk_launch_bscan(bp, ix->d_x.as<float>(), dQp, nslots, pm_.grid, st));
         launches++;
     }
     if (ws.timing) { RK_CUDA(cudaEventRecord(ws.ring_b[slot_ev], st)); ws.timed_scan = true; ws.ring_n++; }
@@ -660,7 +688,9 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     // TF32 keeps 10 mantissa bits and the MMA truncates: each operand is off by < 2^-10 relative, a
     // product by < 2^-9; |x.q| error <= 2^-9 * |x||q|; the L2 form doubles it.  Whether this batch is exact instead
     // (small-integer corpus and queries) is decided by the re-score kernel from the probe results on the device.
-    const float eps_scale = (ix->metric == RK_METRIC_L2 ? 2.f : 1.f) * (1.0f / 512.0f);
+    // bf16 (round to nearest, 8 significant bits): each operand off by <= 2^-8 relative (half a unit in the last place), a
+    // product by < 2^-7.
+    const float eps_scale = (ix->metric == RK_METRIC_L2 ? 2.f : 1.f) * (bf16 ? 1.0f / 128.0f : 1.0f / 512.0f);
 
     // exact re-score of every query's nominations in the caller's order (a query without lists gets an
     // empty result)
@@ -685,6 +715,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     rp.eps_scale = eps_scale;
     rp.probe = ts.d_probe.as<unsigned long long>();
     rp.x_integer = ts.x_integer ? 1 : 0;
+    rp.exact_absmax = bf16 ? 256.f : 2047.f;
+    rp.x_absmax = ts.x_absmax;
     rp.wide_rows = ix->tile_rows < 64 ? 1 : 0;
     rp.xnorm_max = ts.xnorm_max;
     rp.out_tid = out.out_tid;
@@ -703,6 +735,7 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     tick(4);      // device done
     for (size_t q = 0; q < nq; q++)
         if (hflags[q]) redo.push_back((uint32_t) q);
+    if (bf16 && tune.tensor_bf16 < 0 && nq >= 50 && redo.size() * 50 > nq) ts.bf16_off = true;
     float qnorm_max;
     { uint32_t b = (uint32_t) (hprobe[4] & 0xFFFFFFFFull); memcpy(&qnorm_max, &b, 4); }
     const double nx = std::sqrt((double) ts.xnorm_max), nqm = std::sqrt((double) qnorm_max);
@@ -726,6 +759,6 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     if (host_timing)
         fprintf(stderr, "rk_tensor_search host us: groups %.0f passes %.0f stage %.0f launch %.0f wait %.0f\n", t_phase[0], t_phase[1],
                 t_phase[2], t_phase[3], t_phase[4]);
-    ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0) + (paired ? 32 : 0);
+    ts.last_plan = 1 + (int) plan + (sampled ? 16 : 0) + (paired ? 32 : 0) + (bf16 ? 64 : 0);
     return RK_OK;
 }

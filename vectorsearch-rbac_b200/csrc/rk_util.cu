@@ -36,6 +36,25 @@ cudaError_t rk_launch_gather_rows(const float *src, float *dst, const uint32_t *
     return cudaGetLastError();
 }
 
+// dst[idx[i]][:] = src[i][:]  (chunks of `words` 32-bit words)
+__global__ void rk_scatter_chunks_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, const uint32_t *__restrict__ idx,
+                                         size_t n, int words)
+{
+    const size_t total = n * (size_t) words;
+    for (size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < total; i += (size_t) gridDim.x * blockDim.x) {
+        const size_t r = i / words;
+        dst[(size_t) idx[r] * words + (i - r * words)] = src[i];
+    }
+}
+
+cudaError_t rk_launch_scatter_chunks(const void *src, void *dst, const uint32_t *idx, size_t n, int words, cudaStream_t stream)
+{
+    if (n == 0 || words == 0) return cudaSuccess;
+    rk_scatter_chunks_kernel<<<(unsigned) std::min<size_t>(148 * 4, (n * words + 255) / 256), 256, 0, stream>>>(
+        reinterpret_cast<const uint32_t *>(src), reinterpret_cast<uint32_t *>(dst), idx, n, words);
+    return cudaGetLastError();
+}
+
 cudaError_t rk_launch_pad_rows(const float *src, float *dst, size_t n, int dim, int dim_pad, cudaStream_t stream)
 {
     if (n == 0) return cudaSuccess;
