@@ -62,6 +62,33 @@ def test_tensor_engine_float_data(metric, dim):
     ix.close()
 
 
+@pytest.mark.parametrize("metric,dim,kind", [(1, 768, "cohere"), (0, 512, "cohere"), (0, 256, "sift"), (1, 300, "cohere2")])
+def test_bf16_and_tf32_nomination_give_the_scan_engines_answer(metric, dim, kind):
+    """The CTA-pair kernel nominates in bf16 (tcgen05.mma kind::f16 on bf16 shadow copies) or TF32; the exact fp32 re-score and
+    the sufficiency proof make the ANSWER the scan engine's either way (pgvector/src/vector.c:549-563, 596-606 arithmetic), only
+    the number of refused queries may differ.  Integers up to 255 (SIFT shape) are exact in bf16: no error margin at all."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset(kind, n=14000, dim=dim, rows_per_doc=8, rbac="random", num_users=30, num_roles=10)
+    ix = load_index(ds, metric=metric, role_parts=False, combo_parts=False, k_max=256)
+    ix.finalize()
+    ix.set_option("tensor_pair", 1)              # bf16 nomination exists on the CTA-pair kernel only
+    Q, users = _queries(ds, 120)
+    k = 40
+    ref = ix.search_batch(Q, users, k, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_SCAN)
+    exp = oracle_role_search(ds, Q, users, metric, k, mode="bitmask")
+    assert_topk_matches(ref, exp, exact=kind == "sift")
+    for bf16 in (1, 0):
+        ix.set_option("tensor_bf16", bf16)
+        got = ix.search_batch(Q, users, k, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_TENSOR)
+        st = ix.stats()
+        assert bool(st["tensor_plan"] & 32) and bool(st["tensor_plan"] & 64) == bool(bf16)      # pair kernel; bf16 as asked
+        for a, b in zip(got, ref):
+            np.testing.assert_array_equal(a, b)
+        if kind == "sift":
+            assert st["tensor_exact"] == 1
+    ix.close()
+
+
 def test_tensor_engine_unfiltered_and_small_visible_sets():
     import vectorsearch_rbac_b200 as vr
     ds = make_dataset("sift", n=9000, dim=64, rows_per_doc=30, rbac="tree", num_users=12, num_roles=6)

@@ -739,7 +739,10 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     float qnorm_max;
     { uint32_t b = (uint32_t) (hprobe[4] & 0xFFFFFFFFull); memcpy(&qnorm_max, &b, 4); }
     const double nx = std::sqrt((double) ts.xnorm_max), nqm = std::sqrt((double) qnorm_max);
-    const bool exact = ts.x_integer && hprobe[0] == 0 && (nx + nqm) * (nx + nqm) < 16777216.0;      // (statistics only)
+    float q_absmax;
+    { uint32_t b = (uint32_t) (hprobe[1] & 0xFFFFFFFFull); memcpy(&q_absmax, &b, 4); }
+    const bool exact = ts.x_integer && hprobe[0] == 0 && (nx + nqm) * (nx + nqm) < 16777216.0 &&
+                       std::max(ts.x_absmax, q_absmax) <= (bf16 ? 256.f : 2047.f);      // (statistics only; the re-score kernel decides)
 
     ws.launches += launches;
     ws.segments = pm_.units.size() + ps_.units.size();
