@@ -223,6 +223,24 @@ int rk_search_batch_device(rk_index *ix, size_t nq, const float *dQ, const uint3
                            const rk_scan_opts *o, uint64_t *d_out_tid, uint32_t *d_out_doc,
                            double *d_out_dist, int32_t *d_out_count);
 
+/* ---- a search that allocates nothing ------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Exact, unfiltered (RK_FILTER_NONE) top-k of nq device-resident queries over all rows of the index, with the same kernels,
+ * arithmetic and tie rule as rk_search_batch_device(filter = RK_FILTER_NONE, engine = RK_ENGINE_SCAN) — results are
+ * identical — but the scan's work list and candidate lists live in a file-scope static device array (about 4.9 MB, held by
+ * every GPU that loads the library until the process exits) and the work list is written on the device: the call makes no
+ * cudaMalloc / cudaFree / cudaHostAlloc and no host<->device copy, only three kernel launches on the index stream
+ * (asynchronous).  Limits: nq <= RK_NOALLOC_MAX_NQ, k <= RK_NOALLOC_MAX_K (and <= k_max), dim % 4 == 0; larger sizes are
+ * rejected with RK_ERR_INVALID.  All calls share the array, which keeps the previous call's contents (every word a call
+ * reads is rewritten first, so calls in stream order are independent); calls that OVERLAP on the GPU — other streams, other
+ * indexes on the same device, several host threads — race on it and must be serialised by the caller.  Inputs and outputs
+ * are the caller's device buffers: dQ [nq][dim], d_out_tid / d_out_doc (may be NULL) / d_out_dist [nq][k], d_out_count [nq]. */
+#define RK_NOALLOC_MAX_NQ 16
+#define RK_NOALLOC_MAX_K 128
+int rk_search_rows_noalloc(rk_index *ix, size_t nq, const float *dQ, int32_t k, uint64_t *d_out_tid, uint32_t *d_out_doc,
+                           double *d_out_dist, int32_t *d_out_count);
+
 /* ---- multi-GPU shard merge (new; the reference has no collective) ------------- */
 
 /* Local shard result in exchange form: per query k (fp32 ordering key, tid, doc) triples sorted

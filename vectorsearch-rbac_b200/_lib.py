@@ -91,6 +91,7 @@ SIGNATURES = {
     "rk_multi_finalize": (C.c_int, [_P]),
     "rk_multi_build_ivf": (C.c_int, [_P, C.c_int, C.c_uint64]),
     "rk_multi_search_batch": (C.c_int, [_P, C.c_size_t, _P, _P, C.POINTER(RkScanOpts), _P, _P, _P, _P]),
+    "rk_search_rows_noalloc": (C.c_int, [_P, C.c_size_t, _P, C.c_int32, _P, _P, _P, _P]),
     "rk_set_stream": (C.c_int, [_P, _P]),
     "rk_synchronize": (C.c_int, [_P]),
     "rk_get_stats": (C.c_int, [_P, C.POINTER(RkStats)]),
