@@ -106,6 +106,7 @@ def parse_args():
     ap.add_argument("--no-batched", action="store_true", help="skip the batched (RK_ENGINE_AUTO) leg of a scan-engine workload")
     ap.add_argument("--emu-world", type=int, default=0, help="debug, one GPU: load only the stripe rank --emu-rank of this many ranks would hold")
     ap.add_argument("--emu-rank", type=int, default=0)
+    ap.add_argument("--no-replicas", action="store_true", help="N > 1: skip the query-split replica leg")
     ap.add_argument("--no-single", action="store_true", help="skip the single-query legs (N = 1, tree RBAC workloads)")
     ap.add_argument("--single-reps", type=int, default=16)
     ap.add_argument("--no-legs", action="store_true", help="default c3 line at N = 1: skip the short legs of c1 / c2 / c5 / c4")
@@ -658,6 +659,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
         r["launches"] = st["total_launches"] - launches0
         r["scan_ms"] = ix.scan_times_ms(min(64, steps))
         res_dev = tuple(t.clone() for t in out)
+        r["res_dev"] = res_dev
         outs_h = tuple(torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in res_dev)
         r["h2d"] = Qh.numel() * 4
         r["d2h"] = sum(t.numel() * t.element_size() for t in outs_h)
@@ -775,6 +777,62 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
         ex_exact = [t.cpu().numpy() for t in searcher.search_device(Q, qusers, opts0)]
         barrier()
 
+    # ---- replicas (N > 1; SURVEY.md §8e "replicas only ... separate line"): every GPU holds the WHOLE corpus (it fits: C3 is
+    # 5.12 GB) and answers its own 1/N slice of the step's queries; no exchange at all.  Reported beside the sharded headline,
+    # never instead of it: sharding is what a corpus larger than one GPU needs, replication is the better layout when it fits.
+    replicas = None
+    if world > 1 and not leg and not args.no_replicas and not ivf_lists and rows * dim * 4 <= 40e9:
+        ixr = vr.Index(dim, metric=metric, device=local_rank, k_max=max(128, args.k))
+        ixr.reserve_rows(rows)
+        for a0 in range(0, rows, CH):
+            idx = np.arange(a0, min(rows, a0 + CH))
+            xb = gen_rows(wl, idx, dev)
+            torch.cuda.current_stream(dev).synchronize()
+            ixr.load_rows_device(xb.data_ptr(), len(idx), tid[idx], doc[idx])
+            del xb
+        ixr.set_doc_roles(dr[:, 0], dr[:, 1])
+        ixr.set_user_roles(ur[:, 0], ur[:, 1])
+        if flt_name == "partition":
+            ixr.build_role_partitions()
+        if flt_name == "combination":
+            ixr.build_combination_partitions()
+        ixr.finalize()
+        sharded.use_torch_stream(ixr, dev)
+        per = (args.nq + world - 1) // world
+        lo, hi = min(args.nq, rank * per), min(args.nq, (rank + 1) * per)
+        nloc = hi - lo
+        rb = [torch.empty((max(nloc, 1), args.k), dtype=t, device=dev) for t in (torch.int64, torch.int32, torch.float64)] + \
+             [torch.empty(max(nloc, 1), dtype=torch.int32, device=dev)]
+        Qloc = Q[lo:hi].contiguous()
+        replicas = {}
+        for name_, eng_ in (("scan", vr.ENGINE_SCAN), ("auto", vr.ENGINE_AUTO)):
+            o_ = vr.engine.make_opts(args.k, filter=flt, layout=layout, engine=eng_)
+
+            def rstep():
+                if nloc:
+                    ixr.search_batch_device(Qloc.data_ptr(), nloc, qusers[lo:hi], o_, *[t.data_ptr() for t in rb])
+            for _ in range(max(3, args.warmup)):
+                rstep()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(steps):
+                rstep()
+            e1.record(stream)
+            barrier()
+            dt_ = torch.tensor([e0.elapsed_time(e1) * 1e-3], device=dev, dtype=torch.float64)
+            dist.all_reduce(dt_, op=dist.ReduceOp.MAX)
+            # the slice's answers against the sharded path's answers for the same queries
+            same_ = torch.tensor([int(nloc == 0 or all(torch.equal(a[:nloc], b[lo:hi]) for a, b in zip(rb, main_r["res_dev"])))], device=dev)
+            dist.all_reduce(same_, op=dist.ReduceOp.MIN)
+            replicas[name_] = {"value": args.nq * steps / float(dt_[0]), "unit": "queries/s", "ms_per_step": float(dt_[0]) / steps * 1e3,
+                               "identical_to_sharded_results": bool(int(same_[0]))}
+        replicas["layout"] = ("every GPU holds all %d rows (%.2f GB) and answers %d of the step's %d queries; no exchange; value = all queries of the "
+                              "step / slowest rank's device time" % (rows, rows * dim * 4 / 1e9, per, args.nq))
+        ixr.close()
+        del ixr, rb
+        torch.cuda.empty_cache()
+
     single = None
     if rank == 0 and world == 1 and not leg and not args.no_single and not ivf_lists and wl["rbac"] == "tree":
         ix.enable_timing(False)
@@ -813,6 +871,8 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
                 searcher._ex.status()                   # raises if any wait for a peer timed out
         if single is not None:
             line["single_query"] = single
+        if replicas is not None:
+            line["replicas"] = replicas
         if batched_r is not None:
             # the same step through RK_ENGINE_AUTO (batches of >= 32 exact scans go to the tcgen05 engine): identical
             # results, every row a group of queries shares read once
