@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define RK_ABI_VERSION 2
+#define RK_ABI_VERSION 3
 
 typedef struct rk_index rk_index;
 typedef struct rk_scan rk_scan;
@@ -111,7 +111,8 @@ int rk_abi_version(void);
  * internals): "tensor_plan" (0 cheapest | 1 dense | 2 per user mask | 3 per document class), "tensor_pair" (-1 by row
  * length | 0 one-CTA kernel | 1 CTA-pair kernel), "tensor_bf16" (-1 by row length | 0 TF32 | 1 bf16 nomination),
  * "tensor_sample", "tensor_sdiv", "tensor_smin", "tensor_tpu", "tensor_host_timing", "ivf_seg_factor",
- * "ivf_probe_single", "single_fused", "single_zero_copy".  Defaults come from the RK_* environment variables of the same names
+ * "ivf_probe_single", "ivf_assign_tc" (1 = k-means / build assignment on the tensor cores, 0 = fp32 kernel), "single_fused",
+ * "single_zero_copy".  Defaults come from the RK_* environment variables of the same names
  * (upper case), which are read once, in rk_open — never on the per-call path. */
 int rk_set_option(rk_index *ix, const char *name, int64_t value);
 
@@ -347,6 +348,8 @@ typedef struct rk_stats {
     uint64_t segment_kinds;    /* last scan launch: bit i set = the work list held segments of kind i (0 extent table,
                                   2 row range, 3 row range with a per-row permission test, 4 class-ordered IVF lists) */
     uint64_t single_fused;     /* last call: 1 = a single query ran as ONE fused launch (scan + select)              */
+    uint64_t ivf_assign_tc_rows;       /* IVFFlat builds so far: row assignments made through the tensor-core path ...  */
+    uint64_t ivf_assign_fallback_rows; /* ... and how many of them its proof refused (re-assigned by the fp32 kernel)   */
 } rk_stats;
 int rk_get_stats(rk_index *ix, rk_stats *out);
 /* Record CUDA events around the kernels of each search call (costs two events per kernel). */

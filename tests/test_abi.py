@@ -23,14 +23,14 @@ def test_header_symbols_all_exported_and_bound():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/rbacknn.h but not exported by librbacknn.so"
     assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
-    assert lib.rk_abi_version() == _lib.RK_ABI_VERSION == 2
+    assert lib.rk_abi_version() == _lib.RK_ABI_VERSION == 3
 
 
 def test_struct_sizes_match_header():
     from vectorsearch_rbac_b200 import _lib
     assert C.sizeof(_lib.RkConfig) == 16 * 4
     assert C.sizeof(_lib.RkScanOpts) == 8 * 4
-    assert C.sizeof(_lib.RkStats) == 8 * 8 + 4 * 4 + 8 + 7 * 8
+    assert C.sizeof(_lib.RkStats) == 8 * 8 + 4 * 4 + 8 + 9 * 8
 
 
 def test_no_cpu_fallback_without_device():

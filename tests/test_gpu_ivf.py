@@ -274,3 +274,54 @@ def test_ivf_sharded_lists_match_single_index(world):
                 np.testing.assert_array_equal(got[2][q, :n].view(np.uint64), exp[2][q, :n].view(np.uint64))
     for ix in shards + [full]:
         ix.close()
+
+
+@pytest.mark.parametrize("kind,dim,metric,lists", [("sift", 64, 0, 300), ("sift", 128, 1, 256), ("cohere2", 96, 0, 512), ("cohere", 100, 1, 260),
+                                                     ("cohere2", 768, 0, 1024)])
+def test_tensor_core_assignment_equals_the_fp32_kernel_and_the_oracle(kind, dim, metric, lists):
+    """The build's nearest-centre assignment (pgvector/src/ivfbuild.c:141-198, ivfkmeans.c:258-494) on the tensor cores
+    (rk_assign_tc.cu: TF32 nomination, exact re-score, proof, refused rows through the fp32 kernel) must give, row for row,
+    what the fp32 kernel gives; on integer-valued data both equal the oracle's orc_ivf_assign (first minimum wins)."""
+    import vectorsearch_rbac_b200 as vr
+    n = 20000 if dim <= 128 else 9000
+    ds = make_dataset(kind, n=n, dim=dim, rows_per_doc=10, rbac="random", num_users=20, num_roles=8)
+    rng = np.random.default_rng(4)
+    centers = ds["X"][rng.choice(n, lists, replace=False)].copy()
+    if kind != "sift":
+        centers += rng.normal(0, 0.01, centers.shape).astype(np.float32)      # centres are means, not rows
+    out = {}
+    for tc in (1, 0):
+        ix = load_index(ds, metric=metric, role_parts=False, combo_parts=False)
+        ix.finalize()
+        ix.set_option("ivf_assign_tc", tc)
+        ix.build_ivf_from_centers(centers)
+        st = ix.stats()
+        assert st["ivf_assign_tc_rows"] == (n if tc else 0)
+        if tc:
+            # the proof must carry most rows (duplicated rows tie exactly with their centre's twin: those are refused)
+            assert st["ivf_assign_fallback_rows"] <= n // 2, st["ivf_assign_fallback_rows"]
+        out[tc] = ix.ivf_info(n)[1]
+        ix.close()
+    np.testing.assert_array_equal(out[1], out[0])
+    if kind == "sift":
+        np.testing.assert_array_equal(out[1], orc.ivf_assign(ds["X"], centers, metric))
+
+
+def test_ivf_build_with_tensor_core_kmeans_reaches_the_same_recall():
+    """rk_build_ivf end to end (k-means iterations + final assignment) with the tensor-core assignment on and off.  The
+    assignment is bit-identical; the centre update sums rows with floating-point atomics, whose order differs from run to run,
+    so centres agree to rounding and only rows on a knife's edge between two centres may change list."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("cohere2", n=30000, dim=64, rows_per_doc=10, rbac="random", num_users=20, num_roles=8)
+    res = {}
+    for tc in (1, 0):
+        ix = load_index(ds, metric=0, role_parts=False, combo_parts=False)
+        ix.finalize()
+        ix.set_option("ivf_assign_tc", tc)
+        ix.build_ivf(256, seed=7)
+        res[tc] = ix.ivf_info(len(ds["X"]))
+        if tc:
+            assert ix.stats()["ivf_assign_tc_rows"] > len(ds["X"])              # the k-means iterations used it as well
+        ix.close()
+    np.testing.assert_allclose(res[1][0], res[0][0], rtol=1e-3, atol=1e-5)
+    assert np.mean(res[1][1] == res[0][1]) > 0.995

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # RBACKNN_LIB: another build of the same library (kernel experiments); the default is the in-tree build
 LIB_PATH = os.environ.get("RBACKNN_LIB") or os.path.join(_HERE, "librbacknn.so")
 
-RK_ABI_VERSION = 2
+RK_ABI_VERSION = 3
 
 
 class RkConfig(C.Structure):
@@ -32,7 +32,8 @@ class RkStats(C.Structure):
                 ("algo_bytes", C.c_uint64), ("scan_ms", C.c_float), ("select_ms", C.c_float), ("probe_ms", C.c_float),
                 ("reserved_f", C.c_float), ("total_launches", C.c_uint64), ("tensor_redo", C.c_uint64),
                 ("tensor_exact", C.c_uint64), ("tensor_plan", C.c_uint64), ("tensor_flop", C.c_uint64), ("tensor_plan_bytes", C.c_uint64),
-                ("segment_kinds", C.c_uint64), ("single_fused", C.c_uint64)]
+                ("segment_kinds", C.c_uint64), ("single_fused", C.c_uint64), ("ivf_assign_tc_rows", C.c_uint64),
+                ("ivf_assign_fallback_rows", C.c_uint64)]
 
 
 # every symbol include/rbacknn.h declares: name -> (restype, argtypes)

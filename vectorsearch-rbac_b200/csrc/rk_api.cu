@@ -181,6 +181,7 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.tensor_qtau = env_int("RK_TENSOR_QTAU", 1);
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
+        t.ivf_assign_tc = env_int("RK_IVF_ASSIGN_TC", 1);
         t.single_fused = env_int("RK_SINGLE_FUSED", 1);
         t.seg_cost_x10 = std::max(1, env_int("RK_SEG_COST_X10", 80));
         t.single_zero_copy = env_int("RK_SINGLE_ZERO_COPY", 1);
@@ -212,6 +213,7 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "tensor_qtau")) t.tensor_qtau = v;
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
+    else if (!strcmp(name, "ivf_assign_tc")) t.ivf_assign_tc = v;
     else if (!strcmp(name, "single_fused")) t.single_fused = v;
     else if (!strcmp(name, "seg_cost_x10")) t.seg_cost_x10 = std::max(1, v);
     else if (!strcmp(name, "single_zero_copy")) t.single_zero_copy = v;

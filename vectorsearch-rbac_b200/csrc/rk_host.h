@@ -124,6 +124,7 @@ struct UserInfo {
 
 struct IvfIndex {
     bool built = false;
+    uint64_t assign_tc_rows = 0, assign_fallback_rows = 0;   // rk_stats: tensor-core assignments and the rows their proof refused
     int lists = 0;
     DevBuf d_x, d_tid, d_rowdoc;        // list-sorted copy of the row store
     DevBuf d_centers, d_center_tid, d_list_start;
@@ -181,6 +182,7 @@ struct RkTuning {
     int tensor_kp_bf16 = 64;     // RK_TENSOR_KP_BF16: added on top when the nomination runs in bf16 (C2: 9 refused queries per 1000 -> 1)
     int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = bf16 on the CTA-pair kernel while the proof accepts it, 0 = TF32 nomination, 1 = bf16 always
     int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
+    int ivf_assign_tc = 1;       // RK_IVF_ASSIGN_TC: 0 = the fp32 assignment kernel for k-means and the final assignment
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
     int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path
     int seg_cost_x10 = 80;       // RK_SEG_COST_X10: fixed cost of one segment in 0.1 us (measured: 7.8 us on the 1/8 stripe of C3), for the segment sizing (segments per CTA = sqrt(T / 2o))

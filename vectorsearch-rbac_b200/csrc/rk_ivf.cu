@@ -29,6 +29,27 @@
 #define RK_IVF_MAX_LISTS_SMEM 16384   // the probe kernel sorts (key, list) pairs of one query in shared memory
 #define RK_IVF_MAX_SEGS (1u << 18)    // segments per sub-batch (bounds the candidate buffers)
 
+// Nearest centre of n rows (ivfbuild.c:141-198, ivfkmeans.c:258-494): on the tensor cores when the shape allows
+// (rk_assign_tc.cu: TF32 nomination + exact re-score + proof, refused rows through the fp32 kernel — identical results), else
+// the fp32 kernel.
+static int assign_rows(rk_index *ix, const float *X, size_t n, const float *C, int lists, int metric, uint32_t *out, cudaStream_t st)
+{
+    if (ix->tune.ivf_assign_tc && rk_assign_tc_supported(n, lists, ix->dim_pad)) {
+        const size_t chunk = std::min<size_t>(n, (size_t) 1 << 21);
+        DevBuf scratch;
+        if (scratch.ensure(rk_assign_tc_scratch_bytes(chunk, lists)) != 0) return RK_ERR_CUDA;
+        size_t nf = 0;
+        cudaError_t e = rk_assign_tc(X, n, C, lists, ix->dim_pad, metric, out, nullptr, scratch.p, chunk, ix->sm_count, st, &nf);
+        scratch.release();
+        if (e != cudaSuccess) return rk_fail(RK_ERR_CUDA, "tensor-core assignment failed: %s", cudaGetErrorString(e));
+        ix->ivf.assign_tc_rows += n;
+        ix->ivf.assign_fallback_rows += nf;
+        return RK_OK;
+    }
+    RK_CUDA(rk_launch_assign(X, n, C, lists, ix->dim_pad, metric, out, nullptr, st));
+    return RK_OK;
+}
+
 // Upload padded centres, assign every row, pack the list-sorted copy of the store.
 static int build_from_device_centers(rk_index *ix, int lists, const float *d_centers)
 {
@@ -38,8 +59,7 @@ static int build_from_device_centers(rk_index *ix, int lists, const float *d_cen
     cudaStream_t st = 0;
     DevBuf d_row_list;
     if (d_row_list.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
-    RK_CUDA(rk_launch_assign(ix->d_x.as<float>(), n, d_centers, lists, ix->dim_pad, ix->metric, d_row_list.as<uint32_t>(),
-                             nullptr, st));
+    { const int rc_ = assign_rows(ix, ix->d_x.as<float>(), n, d_centers, lists, ix->metric, d_row_list.as<uint32_t>(), st); if (rc_ < 0) return rc_; }
     iv.row_list.assign(n, 0);
     if (n) RK_CUDA(cudaMemcpy(iv.row_list.data(), d_row_list.p, n * 4, cudaMemcpyDeviceToHost));
     d_row_list.release();
@@ -210,7 +230,7 @@ extern "C" int rk_build_ivf(rk_index *ix, int lists, uint64_t seed)
     const int max_iter = 25;
     for (int it = 0; it < max_iter; it++) {
         // on normalised data the nearest centre by L2 is the one with the largest dot product
-        RK_CUDA(rk_launch_assign(d_s.as<float>(), ns, C, lists, ix->dim_pad, spherical ? 1 : 0, d_label.as<uint32_t>(), nullptr, st));
+        { const int rc_ = assign_rows(ix, d_s.as<float>(), ns, C, lists, spherical ? 1 : 0, d_label.as<uint32_t>(), st); if (rc_ < 0) return rc_; }
         RK_CUDA(cudaMemsetAsync(d_changed.p, 0, 8, st));
         RK_CUDA(rk_launch_count_changed(d_label.as<uint32_t>(), d_prev.as<uint32_t>(), ns, d_changed.as<unsigned long long>(), st));
         unsigned long long changed = 0;

@@ -21,7 +21,7 @@
 template <int METRIC>
 __global__ void __launch_bounds__(256) rk_assign_kernel(const float *__restrict__ X, size_t nrows, const float *__restrict__ Cn,
                                                         int lists, int dim_pad, uint32_t *__restrict__ out_list,
-                                                        float *__restrict__ out_val)
+                                                        float *__restrict__ out_val, const uint32_t *__restrict__ idx)
 {
     __shared__ float Xs[AS_BK][AS_BM + 4];
     __shared__ float Cs[AS_BK][AS_BN + 4];
@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(256) rk_assign_kernel(const float *__restrict_
         for (int k0 = 0; k0 < dim_pad; k0 += AS_BK) {
             float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), cv = xv;
             if (k0 + lc < dim_pad) {
-                if (row0 + lr < nrows) xv = *reinterpret_cast<const float4 *>(X + (row0 + lr) * (size_t) dim_pad + k0 + lc);
+                // (idx: the rows to assign are X[idx[0 .. nrows)], results go to out[idx[.]] — the tensor-core path's refused rows)
+                if (row0 + lr < nrows) xv = *reinterpret_cast<const float4 *>(X + (idx ? (size_t) idx[row0 + lr] : row0 + lr) * (size_t) dim_pad + k0 + lc);
                 if (n0 + lr < lists) cv = *reinterpret_cast<const float4 *>(Cn + (size_t) (n0 + lr) * dim_pad + k0 + lc);
             }
             __syncthreads();
@@ -91,20 +92,21 @@ __global__ void __launch_bounds__(256) rk_assign_kernel(const float *__restrict_
         for (int i = 0; i < 4; i++) {
             const size_t r = row0 + ty * 4 + i;
             if (r < nrows) {
-                out_list[r] = besti[i];
-                if (out_val) out_val[r] = best[i];
+                const size_t ro = idx ? (size_t) idx[r] : r;
+                out_list[ro] = besti[i];
+                if (out_val) out_val[ro] = best[i];
             }
         }
     }
 }
 
 cudaError_t rk_launch_assign(const float *X, size_t nrows, const float *C, int lists, int dim_pad, int metric,
-                             uint32_t *out_list, float *out_val, cudaStream_t stream)
+                             uint32_t *out_list, float *out_val, cudaStream_t stream, const uint32_t *idx)
 {
     if (nrows == 0) return cudaSuccess;
     const unsigned grid = (unsigned) ((nrows + AS_BM - 1) / AS_BM);
-    if (metric == 0) rk_assign_kernel<0><<<grid, 256, 0, stream>>>(X, nrows, C, lists, dim_pad, out_list, out_val);
-    else rk_assign_kernel<1><<<grid, 256, 0, stream>>>(X, nrows, C, lists, dim_pad, out_list, out_val);
+    if (metric == 0) rk_assign_kernel<0><<<grid, 256, 0, stream>>>(X, nrows, C, lists, dim_pad, out_list, out_val, idx);
+    else rk_assign_kernel<1><<<grid, 256, 0, stream>>>(X, nrows, C, lists, dim_pad, out_list, out_val, idx);
     return cudaGetLastError();
 }
 

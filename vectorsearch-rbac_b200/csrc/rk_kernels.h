@@ -27,7 +27,13 @@ cudaError_t rk_launch_flag_nonfinite(const float *d_x, size_t n, uint32_t *d_fla
 
 // IVFFlat (rk_ivf_kernels.cu)
 cudaError_t rk_launch_assign(const float *X, size_t nrows, const float *C, int lists, int dim_pad, int metric,
-                             uint32_t *out_list, float *out_val, cudaStream_t stream);
+                             uint32_t *out_list, float *out_val, cudaStream_t stream, const uint32_t *idx = nullptr);
+// the same assignment through the tensor cores (rk_assign_tc.cu): TF32 nomination, exact re-score + proof, refused rows through
+// rk_launch_assign — identical results
+bool rk_assign_tc_supported(size_t nrows, int lists, int dim_pad);
+size_t rk_assign_tc_scratch_bytes(size_t chunk, int lists);
+cudaError_t rk_assign_tc(const float *X, size_t nrows, const float *C, int lists, int dim_pad, int metric, uint32_t *out_list, float *out_val,
+                         void *scratch, size_t chunk, int sm_count, cudaStream_t stream, size_t *n_fallback);
 cudaError_t rk_launch_km_accumulate(const float *S, size_t ns, int dim_pad, const uint32_t *label, float *sums, uint32_t *counts,
                                     cudaStream_t stream);
 cudaError_t rk_launch_km_finalize(float *C, const float *sums, const uint32_t *counts, int lists, int dim_pad, const float *S,

@@ -1180,5 +1180,7 @@ extern "C" int rk_get_stats(rk_index *ix, rk_stats *out)
     out->tensor_plan_bytes = ix->tensor.last_plan_bytes;
     out->segment_kinds = ix->ws.seg_kinds;
     out->single_fused = ix->ws.single_fused ? 1 : 0;
+    out->ivf_assign_tc_rows = ix->ivf.assign_tc_rows;
+    out->ivf_assign_fallback_rows = ix->ivf.assign_fallback_rows;
     return RK_OK;
 }
