@@ -111,7 +111,8 @@ int rk_abi_version(void);
  * internals): "tensor_plan" (0 cheapest | 1 dense | 2 per user mask | 3 per document class), "tensor_pair" (-1 by row
  * length | 0 one-CTA kernel | 1 CTA-pair kernel), "tensor_bf16" (-1 by row length | 0 TF32 | 1 bf16 nomination),
  * "tensor_sample", "tensor_sdiv", "tensor_smin", "tensor_tpu", "tensor_host_timing", "ivf_seg_factor",
- * "ivf_probe_single", "ivf_assign_tc" (1 = k-means / build assignment on the tensor cores, 0 = fp32 kernel), "single_fused",
+ * "ivf_probe_single", "ivf_assign_tc" (1 = k-means / build assignment on the tensor cores, 0 = fp32 kernel), "ivf_kmeanspp" (1 = k-means++ seeding,
+ * 0 = first sampled rows), "ivf_kmeans_iters", "ivf_sample_identity", "single_fused",
  * "single_zero_copy".  Defaults come from the RK_* environment variables of the same names
  * (upper case), which are read once, in rk_open — never on the per-call path. */
 int rk_set_option(rk_index *ix, const char *name, int64_t value);

@@ -325,3 +325,75 @@ def test_ivf_build_with_tensor_core_kmeans_reaches_the_same_recall():
         ix.close()
     np.testing.assert_allclose(res[1][0], res[0][0], rtol=1e-3, atol=1e-5)
     assert np.mean(res[1][1] == res[0][1]) > 0.995
+
+
+def _splitmix(h):
+    M = (1 << 64) - 1
+    h &= M
+    h ^= h >> 30; h = (h * 0xBF58476D1CE4E5B9) & M
+    h ^= h >> 27; h = (h * 0x94D049BB133111EB) & M
+    h ^= h >> 31
+    return h
+
+
+def test_kmeanspp_seeding_follows_initcenters():
+    """pgvector/src/ivfkmeans.c:21-89 restated in numpy with the engine's documented random numbers (first centre
+    splitmix(seed) % n, then u_i = splitmix(seed, i) / 2^53): weight = min(weight, l2_distance^2) as a float, choice = sum * u,
+    next centre = first sample whose running total reaches the choice.  Integer-valued data: every weight and every running
+    total is an exact integer, so the GPU's block-wise double sums pick exactly the rows the sequential loop picks."""
+    import vectorsearch_rbac_b200 as vr
+    n, dim, lists, seed = 3000, 32, 40, 12345
+    ds = make_dataset("sift", n=n, dim=dim, rows_per_doc=10, rbac="random", num_users=20, num_roles=8)
+    ix = load_index(ds, metric=0, role_parts=False, combo_parts=False)
+    ix.finalize()
+    ix.set_option("ivf_sample_identity", 1)          # the sample = the table in index order (n <= 10000: everything is sampled)
+    ix.set_option("ivf_kmeans_iters", 0)             # the seeds become the centres
+    ix.build_ivf(lists, seed=seed)
+    got = ix.ivf_centers()
+    ix.close()
+    M = (1 << 64) - 1
+    S = ds["X"].astype(np.float64)
+    chosen = [(_splitmix((seed * 0x9E3779B97F4A7C15 + 0x632BE59BD9B4E019) & M) >> 32) % n]
+    weight = np.full(n, np.finfo(np.float32).max, dtype=np.float32)
+    for i in range(lists - 1):
+        d = np.sqrt(((S - S[chosen[i]]) ** 2).sum(axis=1))
+        d2 = d * d
+        upd = d2 < weight.astype(np.float64)
+        weight[upd] = d2[upd].astype(np.float32)
+        cum = np.cumsum(weight.astype(np.float64))
+        u = (_splitmix((seed + 0x9E3779B97F4A7C15 * (i + 1)) & M) >> 11) / 9007199254740992.0
+        choice = cum[-1] * u
+        j = int(np.searchsorted(cum, choice, side="left"))
+        chosen.append(min(j, n - 1))
+    np.testing.assert_array_equal(got, ds["X"][chosen])
+    assert len(set(chosen)) == lists                  # a chosen row's weight is 0: it is not drawn again
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_kmeanspp_build_is_reproducible_and_not_worse_than_first_rows(metric):
+    """Same seed, same centres (no floating-point atomics in the seeding); and the k-means objective after the build is not worse
+    than from the first sampled rows on clustered data."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("cohere2", n=20000, dim=48, rows_per_doc=10, rbac="random", num_users=20, num_roles=8)
+    X = ds["X"] / np.linalg.norm(ds["X"], axis=1, keepdims=True) if metric else ds["X"]
+
+    def build(pp, iters):
+        ix = load_index(ds, metric=metric, role_parts=False, combo_parts=False)
+        ix.finalize()
+        ix.set_option("ivf_kmeanspp", pp)
+        ix.set_option("ivf_kmeans_iters", iters)
+        ix.build_ivf(128, seed=3)
+        c, rl = ix.ivf_info(len(X))
+        ix.close()
+        return c, rl
+
+    a, _ = build(1, 0)
+    b, _ = build(1, 0)
+    np.testing.assert_array_equal(a, b)
+    assert len(np.unique(a, axis=0)) == 128
+    obj = {}
+    for pp in (1, 0):
+        c, rl = build(pp, 25)
+        cc = c / np.maximum(np.linalg.norm(c, axis=1, keepdims=True), 1e-30) if metric else c
+        obj[pp] = float(((X - cc[rl]) ** 2).sum())
+    assert obj[1] <= obj[0] * 1.02, obj

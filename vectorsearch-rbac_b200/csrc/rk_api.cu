@@ -182,6 +182,9 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
         t.ivf_probe_single = getenv("RK_IVF_PROBE_SINGLE") != nullptr;
         t.ivf_assign_tc = env_int("RK_IVF_ASSIGN_TC", 1);
+        t.ivf_kmeanspp = env_int("RK_IVF_KMEANSPP", 1);
+        t.ivf_kmeans_iters = std::max(0, env_int("RK_IVF_KMEANS_ITERS", 25));
+        t.ivf_sample_identity = env_int("RK_IVF_SAMPLE_IDENTITY", 0);
         t.single_fused = env_int("RK_SINGLE_FUSED", 1);
         t.seg_cost_x10 = std::max(1, env_int("RK_SEG_COST_X10", 80));
         t.single_zero_copy = env_int("RK_SINGLE_ZERO_COPY", 1);
@@ -214,6 +217,9 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);
     else if (!strcmp(name, "ivf_probe_single")) t.ivf_probe_single = v != 0;
     else if (!strcmp(name, "ivf_assign_tc")) t.ivf_assign_tc = v;
+    else if (!strcmp(name, "ivf_kmeanspp")) t.ivf_kmeanspp = v;
+    else if (!strcmp(name, "ivf_kmeans_iters")) t.ivf_kmeans_iters = std::max(0, v);
+    else if (!strcmp(name, "ivf_sample_identity")) t.ivf_sample_identity = v;
     else if (!strcmp(name, "single_fused")) t.single_fused = v;
     else if (!strcmp(name, "seg_cost_x10")) t.seg_cost_x10 = std::max(1, v);
     else if (!strcmp(name, "single_zero_copy")) t.single_zero_copy = v;

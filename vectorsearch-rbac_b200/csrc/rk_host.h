@@ -182,6 +182,9 @@ struct RkTuning {
     int tensor_kp_bf16 = 64;     // RK_TENSOR_KP_BF16: added on top when the nomination runs in bf16 (C2: 9 refused queries per 1000 -> 1)
     int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = bf16 on the CTA-pair kernel while the proof accepts it, 0 = TF32 nomination, 1 = bf16 always
     int ivf_seg_factor = 4;      // RK_IVF_SEG_FACTOR
+    int ivf_kmeanspp = 1;        // RK_IVF_KMEANSPP: 1 = k-means++ seeding (ivfkmeans.c:21-89), 0 = the first `lists` sampled rows
+    int ivf_kmeans_iters = 25;   // RK_IVF_KMEANS_ITERS: Lloyd iterations at most (0 = the seeds become the centres; tests)
+    int ivf_sample_identity = 0; // RK_IVF_SAMPLE_IDENTITY: the sample is the first rows in index order, unshuffled (tests)
     int ivf_assign_tc = 1;       // RK_IVF_ASSIGN_TC: 0 = the fp32 assignment kernel for k-means and the final assignment
     int ivf_probe_single = 0;    // RK_IVF_PROBE_SINGLE
     int single_fused = 1;        // RK_SINGLE_FUSED: 0 = single queries take the two-launch scan + select path

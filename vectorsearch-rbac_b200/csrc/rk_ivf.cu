@@ -198,7 +198,9 @@ extern "C" int rk_build_ivf(rk_index *ix, int lists, uint64_t seed)
     if (ns > n) ns = n;
     std::vector<uint32_t> sample(ns);
     std::mt19937_64 rng(seed);
-    if (ns == n) {
+    if (ix->tune.ivf_sample_identity) {
+        for (size_t i = 0; i < ns; i++) sample[i] = (uint32_t) i;
+    } else if (ns == n) {
         for (size_t i = 0; i < n; i++) sample[i] = (uint32_t) i;
         std::shuffle(sample.begin(), sample.end(), rng);
     } else {
@@ -219,15 +221,27 @@ extern "C" int rk_build_ivf(rk_index *ix, int lists, uint64_t seed)
     RK_CUDA(rk_launch_gather_rows(ix->d_x.as<float>(), d_s.as<float>(), d_sidx.as<uint32_t>(), ns, ix->dim_pad, st));
     const int spherical = ix->metric == RK_METRIC_IP;      // vector_ip_ops: FUNCTION 3 spherical distance, FUNCTION 4 norm
     if (spherical) RK_CUDA(rk_launch_km_normalize_rows(d_s.as<float>(), ns, ix->dim_pad, st));
-    // initial centres: the first `lists` sampled rows (the sample is a random permutation); with fewer
-    // samples than lists the rest wrap around (pgvector warns "index created with little data")
+    // initial centres: k-means++ over the sample; with the option off, or no more samples than lists (pgvector warns "index created
+    // with little data"), the first `lists` sampled rows (the sample is a random permutation), wrapping around
     float *C = ix->ivf.d_centers.as<float>();
-    for (size_t l = 0; l < (size_t) lists; l += ns) {
-        const size_t cnt = std::min<size_t>(ns, (size_t) lists - l);
-        RK_CUDA(cudaMemcpyAsync((unsigned char *) C + l * rb, d_s.p, cnt * rb, cudaMemcpyDeviceToDevice, st));
+    if (ix->tune.ivf_kmeanspp && ns > (size_t) lists) {
+        // k-means++ (ivfkmeans.c:21-89): each next centre is a sample drawn with probability proportional to its squared
+        // distance from the centres chosen so far
+        DevBuf d_w, d_bs, d_ch;
+        if (d_w.ensure(ns * 4) != 0 || d_bs.ensure((size_t) rk_kpp_blocks((uint32_t) ns) * 8) != 0 || d_ch.ensure((size_t) lists * 4) != 0) return RK_ERR_CUDA;
+        RK_CUDA(rk_launch_kmeanspp(d_s.as<float>(), (uint32_t) ns, ix->dim_pad, lists, spherical, seed, d_w.as<float>(), d_bs.as<double>(),
+                                   d_ch.as<uint32_t>(), st));
+        RK_CUDA(rk_launch_gather_rows(d_s.as<float>(), C, d_ch.as<uint32_t>(), (size_t) lists, ix->dim_pad, st));
+        RK_CUDA(cudaStreamSynchronize(st));
+        d_w.release(); d_bs.release(); d_ch.release();
+    } else {
+        for (size_t l = 0; l < (size_t) lists; l += ns) {
+            const size_t cnt = std::min<size_t>(ns, (size_t) lists - l);
+            RK_CUDA(cudaMemcpyAsync((unsigned char *) C + l * rb, d_s.p, cnt * rb, cudaMemcpyDeviceToDevice, st));
+        }
     }
     RK_CUDA(cudaMemsetAsync(d_prev.p, 0xFF, ns * 4, st));
-    const int max_iter = 25;
+    const int max_iter = ix->tune.ivf_kmeans_iters;
     for (int it = 0; it < max_iter; it++) {
         // on normalised data the nearest centre by L2 is the one with the largest dot product
         { const int rc_ = assign_rows(ix, d_s.as<float>(), ns, C, lists, spherical ? 1 : 0, d_label.as<uint32_t>(), st); if (rc_ < 0) return rc_; }

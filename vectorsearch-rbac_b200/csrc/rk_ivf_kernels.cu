@@ -8,6 +8,8 @@
 //   list choice ..... pgvector/src/ivfscan.c:36-107    distance to ALL centres, `probes` nearest, nearest first
 //   list scan ....... pgvector/src/ivfscan.c:112-176   every tuple of the probed lists scored (rk_scan_kernel)
 #include "rk_common.cuh"
+#include <algorithm>
+
 #include "rk_kernels.h"
 
 // ---------------------------------------------------------------------------------------------
@@ -107,6 +109,159 @@ cudaError_t rk_launch_assign(const float *X, size_t nrows, const float *C, int l
     const unsigned grid = (unsigned) ((nrows + AS_BM - 1) / AS_BM);
     if (metric == 0) rk_assign_kernel<0><<<grid, 256, 0, stream>>>(X, nrows, C, lists, dim_pad, out_list, out_val, idx);
     else rk_assign_kernel<1><<<grid, 256, 0, stream>>>(X, nrows, C, lists, dim_pad, out_list, out_val, idx);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// k-means++ seeding (pgvector/src/ivfkmeans.c:21-89, InitCenters).  The reference's loop, per new centre i: every sample's
+// distance to centre i (the operator class's k-means distance: l2_distance, or the spherical distance acos(x.c) / pi on
+// normalised rows), weight[j] = min(weight[j], distance^2) (distance a double, weight a float), sum of the weights (double);
+// then choice = sum * RandomDouble() and the next centre is the first sample whose running weight total reaches it.
+// Here: two small kernels per centre, no host round trip (the chosen row number stays on the device).  Block b owns the
+// sample rows [b R, (b + 1) R); it writes the double sum of its rows' weights, always added in the same order, so a build is
+// reproducible for a seed.  The reference draws from PostgreSQL's PRNG; here u_i = splitmix64(seed, i) / 2^53.
+
+#define KPP_THREADS 256
+
+__device__ __forceinline__ double rk_kpp_uniform(uint64_t seed, uint32_t i)
+{
+    uint64_t h = (seed + 0x9E3779B97F4A7C15ull * (uint64_t) (i + 1));
+    h ^= h >> 30; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 27; h *= 0x94D049BB133111EBull; h ^= h >> 31;
+    return (double) (h >> 11) * (1.0 / 9007199254740992.0);
+}
+
+template <int SPHERICAL>
+__global__ void __launch_bounds__(KPP_THREADS) rk_kpp_dist_kernel(const float *__restrict__ S, uint32_t ns, int dim_pad, uint32_t rows_per_block,
+                                                                   const uint32_t *__restrict__ chosen, uint32_t i, float *__restrict__ weight,
+                                                                   double *__restrict__ blocksum)
+{
+    extern __shared__ float kpp_c[];                 // the new centre
+    __shared__ double wsum[KPP_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float4 *c4g = reinterpret_cast<const float4 *>(S + (size_t) chosen[i] * dim_pad);
+    float4 *c4 = reinterpret_cast<float4 *>(kpp_c);
+    const int dim4 = dim_pad >> 2;
+    for (int k = threadIdx.x; k < dim4; k += KPP_THREADS) c4[k] = c4g[k];
+    __syncthreads();
+    const uint32_t r0 = blockIdx.x * rows_per_block, r1 = min(ns, r0 + rows_per_block);
+    double acc = 0.0;
+    for (uint32_t r = r0 + (uint32_t) warp; r < r1; r += KPP_THREADS / 32) {
+        const float4 *x4 = reinterpret_cast<const float4 *>(S + (size_t) r * dim_pad);
+        float s = 0.f;
+        for (int k = lane; k < dim4; k += 32) {
+            const float4 a = x4[k], b = c4[k];
+            if (SPHERICAL) { s = fmaf(a.x, b.x, s); s = fmaf(a.y, b.y, s); s = fmaf(a.z, b.z, s); s = fmaf(a.w, b.w, s); }
+            else {
+                float d = a.x - b.x; s = fmaf(d, d, s);
+                d = a.y - b.y; s = fmaf(d, d, s);
+                d = a.z - b.z; s = fmaf(d, d, s);
+                d = a.w - b.w; s = fmaf(d, d, s);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) {
+            double d;
+            if (SPHERICAL) {                         // vector_spherical_distance (vector.c): acos of the clamped dot, over pi
+                double dp = (double) s;
+                dp = dp > 1.0 ? 1.0 : (dp < -1.0 ? -1.0 : dp);
+                d = acos(dp) / 3.14159265358979323846;
+            } else {
+                d = sqrt((double) s);                // l2_distance (vector.c:568-578)
+            }
+            d *= d;
+            float w = weight[r];
+            if (d < (double) w) { w = (float) d; weight[r] = w; }
+            acc += (double) w;
+        }
+    }
+    if (lane == 0) wsum[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < KPP_THREADS / 32; w++) t += wsum[w];
+        blocksum[blockIdx.x] = t;
+    }
+}
+
+// One warp: choice = (sum of the weights) * u_i; chosen[i + 1] = the first sample whose running total reaches it.
+__global__ void rk_kpp_pick_kernel(const float *__restrict__ weight, const double *__restrict__ blocksum, uint32_t nblocks, uint32_t ns,
+                                   uint32_t rows_per_block, uint64_t seed, uint32_t i, uint32_t *__restrict__ chosen)
+{
+    const uint32_t lane = threadIdx.x;
+    // level 1: which block
+    const uint32_t per = (nblocks + 31) / 32;
+    const uint32_t b0 = min(nblocks, lane * per), b1 = min(nblocks, b0 + per);
+    double loc = 0.0;
+    for (uint32_t b = b0; b < b1; b++) loc += blocksum[b];
+    double inc = loc;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double u = __shfl_up_sync(0xffffffffu, inc, o); if ((int) lane >= o) inc += u; }
+    const double total = __shfl_sync(0xffffffffu, inc, 31);
+    double choice = total * rk_kpp_uniform(seed, i);
+    uint32_t hit = __ballot_sync(0xffffffffu, b1 > b0 && inc >= choice);
+    uint32_t blk = nblocks - 1;
+    double rem = 0.0;
+    bool found = hit != 0;
+    if (found) {
+        const int L = __ffs((int) hit) - 1;
+        double c = choice - (inc - loc);              // what is left when lane L's blocks begin
+        uint32_t bb = b1 - 1;
+        for (uint32_t b = b0; b < b1; b++) { const double v = blocksum[b]; if (c <= v) { bb = b; break; } c -= v; }
+        blk = __shfl_sync(0xffffffffu, bb, L);
+        rem = __shfl_sync(0xffffffffu, c, L);
+    }
+    uint32_t pick = ns - 1;                           // the reference's loop ends on the last sample when the total is never reached
+    if (found) {
+        // level 2: which row of the block
+        const uint32_t r0 = blk * rows_per_block, r1 = min(ns, r0 + rows_per_block), n = r1 - r0;
+        const uint32_t per2 = (n + 31) / 32;
+        const uint32_t a0 = min(n, lane * per2), a1 = min(n, a0 + per2);
+        double l2 = 0.0;
+        for (uint32_t j = a0; j < a1; j++) l2 += (double) weight[r0 + j];
+        double in2 = l2;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const double u = __shfl_up_sync(0xffffffffu, in2, o); if ((int) lane >= o) in2 += u; }
+        const uint32_t hit2 = __ballot_sync(0xffffffffu, a1 > a0 && in2 >= rem);
+        uint32_t jj = r1 - 1;
+        if (hit2) {
+            const int L2 = __ffs((int) hit2) - 1;
+            double c = rem - (in2 - l2);
+            uint32_t j2 = a1 - 1;
+            for (uint32_t j = a0; j < a1; j++) { const double v = (double) weight[r0 + j]; if (c <= v) { j2 = j; break; } c -= v; }
+            jj = r0 + __shfl_sync(0xffffffffu, j2, L2);
+        }
+        pick = jj;
+    }
+    if (lane == 0) chosen[i + 1] = pick;
+}
+
+// chosen[lists] (device) = the sample rows k-means++ seeds the centres with.  weight: [ns] floats, blocksum: [nblocks] doubles
+// (nblocks = rk_kpp_blocks(ns)).  Asynchronous on `stream`.
+uint32_t rk_kpp_blocks(uint32_t ns) { return std::min<uint32_t>(1184u, (ns + 63u) / 64u); }
+
+__global__ void rk_kpp_init_kernel(float *weight, uint32_t ns, uint32_t *chosen, uint64_t seed)
+{
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ns; j += gridDim.x * blockDim.x) weight[j] = 3.402823466e38f;   // FLT_MAX
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // "Choose an initial center uniformly at random": RandomInt() % samples->length
+        uint64_t h = seed * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
+        h ^= h >> 30; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 27; h *= 0x94D049BB133111EBull; h ^= h >> 31;
+        chosen[0] = (uint32_t) ((h >> 32) % (uint64_t) ns);
+    }
+}
+
+cudaError_t rk_launch_kmeanspp(const float *S, uint32_t ns, int dim_pad, int lists, int spherical, uint64_t seed, float *weight,
+                               double *blocksum, uint32_t *chosen, cudaStream_t stream)
+{
+    const uint32_t nb = rk_kpp_blocks(ns), rpb = (ns + nb - 1) / nb;
+    rk_kpp_init_kernel<<<148, 256, 0, stream>>>(weight, ns, chosen, seed);
+    const size_t smem = (size_t) dim_pad * 4;
+    for (int i = 0; i + 1 < lists; i++) {
+        if (spherical) rk_kpp_dist_kernel<1><<<nb, KPP_THREADS, smem, stream>>>(S, ns, dim_pad, rpb, chosen, (uint32_t) i, weight, blocksum);
+        else rk_kpp_dist_kernel<0><<<nb, KPP_THREADS, smem, stream>>>(S, ns, dim_pad, rpb, chosen, (uint32_t) i, weight, blocksum);
+        rk_kpp_pick_kernel<<<1, 32, 0, stream>>>(weight, blocksum, nb, ns, rpb, seed, (uint32_t) i, chosen);
+    }
     return cudaGetLastError();
 }
 

@@ -34,6 +34,10 @@ bool rk_assign_tc_supported(size_t nrows, int lists, int dim_pad);
 size_t rk_assign_tc_scratch_bytes(size_t chunk, int lists);
 cudaError_t rk_assign_tc(const float *X, size_t nrows, const float *C, int lists, int dim_pad, int metric, uint32_t *out_list, float *out_val,
                          void *scratch, size_t chunk, int sm_count, cudaStream_t stream, size_t *n_fallback);
+// k-means++ seeding (ivfkmeans.c:21-89): chosen[lists] = sample rows to start the centres from
+uint32_t rk_kpp_blocks(uint32_t ns);
+cudaError_t rk_launch_kmeanspp(const float *S, uint32_t ns, int dim_pad, int lists, int spherical, uint64_t seed, float *weight,
+                               double *blocksum, uint32_t *chosen, cudaStream_t stream);
 cudaError_t rk_launch_km_accumulate(const float *S, size_t ns, int dim_pad, const uint32_t *label, float *sums, uint32_t *counts,
                                     cudaStream_t stream);
 cudaError_t rk_launch_km_finalize(float *C, const float *sums, const uint32_t *counts, int lists, int dim_pad, const float *S,
