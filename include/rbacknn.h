@@ -162,8 +162,30 @@ int rk_finalize(rk_index *ix);
 int rk_build_ivf(rk_index *ix, int lists, uint64_t seed);
 /* Same index from caller-supplied centres[lists*dim] (assignment + packing only). */
 int rk_build_ivf_from_centers(rk_index *ix, int lists, const float *centers);
+/* Same index from centres AND the row -> list assignment of an index that already exists (row_list[n] by load order, values
+ * < lists), e.g. what rk_ivfpages_read() found on disk: the lists are scanned as stored (ivfscan.c:128-168), nothing is
+ * re-assigned. */
+int rk_build_ivf_from_lists(rk_index *ix, int lists, const float *centers, const uint32_t *row_list);
 /* Introspection for tests: copies out centres and the row->list assignment. */
 int rk_ivf_info(const rk_index *ix, int *lists, float *centers, uint32_t *row_list /* by load order */);
+
+/* ---- the on-disk form of a pgvector ivfflat index --------------------------
+ * Reader for the main fork of an ivfflat index relation (base/<db>/<relfilenode>, segments concatenated): BLCKSZ 8192,
+ * little-endian, IVFFLAT_VERSION 1.  Host code, needs no device.  Replaces the page walks of pgvector/src/ivfscan.c:45-101
+ * (meta page ivfflat.h:222-230 -> list pages, IvfflatListData ivfflat.h:240-246, chained by IvfflatPageOpaqueData.nextblkno
+ * ivfflat.h:232-238) and ivfscan.c:128-168 (a list's entry pages from startPage; index tuples formed at ivfbuild.c:240):
+ * an AM shim reads the index file once, loads the rows and builds the same lists in HBM with
+ * rk_load_rows + rk_build_ivf_from_lists.  `rel` must stay valid until rk_ivfpages_close.  Corrupt or foreign pages are
+ * an error of the call (RK_ERR_INVALID / RK_ERR_UNSUPPORTED with the block and item in rk_last_error()), never a wild read. */
+typedef struct rk_ivfpages rk_ivfpages;
+int rk_ivfpages_open(const void *rel, size_t nbytes, rk_ivfpages **out);
+/* unused_items: line pointers that are not LP_NORMAL (skipped, as PageGetItem callers after a vacuum would not see them) */
+int rk_ivfpages_info(const rk_ivfpages *p, int32_t *dim, int32_t *lists, uint64_t *tuples, uint64_t *unused_items);
+/* Any output may be NULL.  centers[lists*dim] in list order (list l = l-th item along the list pages); tuples come out list
+ * by list in page order: list_start[lists+1], row_list[tuples] (the list of each tuple), x[tuples*dim], tid[tuples] = heap
+ * tuple id packed as (block << 16) | offset — the packing INTEGRATION.md §2 unpacks into xs_heaptid. */
+int rk_ivfpages_read(const rk_ivfpages *p, float *centers, uint32_t *list_start, uint32_t *row_list, float *x, uint64_t *tid);
+void rk_ivfpages_close(rk_ivfpages *p);
 
 /* ---- scans: the IndexAmRoutine contract (pgvector/src/ivfflat.c:236-240, ivfflat.h:335-338) --- */
 

@@ -14,7 +14,7 @@ if it is missing: there is no fallback).  `import vectorsearch_rbac_b200.synth` 
 """
 import importlib as _importlib
 
-_ENGINE_NAMES = ("Index", "MultiIndex", "Exchange", "Scan", "RkError", "METRIC_L2", "METRIC_IP", "FILTER_PARTITION", "FILTER_BITMASK", "FILTER_NONE",
+_ENGINE_NAMES = ("Index", "MultiIndex", "Exchange", "Scan", "IvfflatPages", "RkError", "METRIC_L2", "METRIC_IP", "FILTER_PARTITION", "FILTER_BITMASK", "FILTER_NONE",
                  "ENGINE_AUTO", "ENGINE_SCAN", "ENGINE_TENSOR", "LAYOUT_AUTO", "LAYOUT_ROLE", "LAYOUT_COMBINATION",
                  "LAYOUT_DYNAMIC")
 _SUBMODULES = ("_lib", "engine", "harness", "synth", "sharded", "dynamic_layout", "build")

@@ -56,7 +56,12 @@ SIGNATURES = {
     "rk_finalize": (C.c_int, [_P]),
     "rk_build_ivf": (C.c_int, [_P, C.c_int, C.c_uint64]),
     "rk_build_ivf_from_centers": (C.c_int, [_P, C.c_int, _P]),
+    "rk_build_ivf_from_lists": (C.c_int, [_P, C.c_int, _P, _P]),
     "rk_ivf_info": (C.c_int, [_P, C.POINTER(C.c_int), _P, _P]),
+    "rk_ivfpages_open": (C.c_int, [_P, C.c_size_t, C.POINTER(_P)]),
+    "rk_ivfpages_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "rk_ivfpages_read": (C.c_int, [_P, _P, _P, _P, _P, _P]),
+    "rk_ivfpages_close": (None, [_P]),
     "rk_beginscan": (_P, [_P]),
     "rk_rescan": (C.c_int, [_P, _P, C.c_int32, C.c_uint32, C.POINTER(RkScanOpts)]),
     "rk_gettuple": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]),

@@ -9,7 +9,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librbacknn.so")
-SOURCES = ["rk_api.cu", "rk_search.cu", "rk_scan.cu", "rk_merge.cu", "rk_util.cu", "rk_ivf.cu", "rk_ivf_kernels.cu", "rk_bscan.cu", "rk_bscan2.cu", "rk_tensor.cu", "rk_exchange.cu", "rk_multi.cu", "rk_noalloc.cu", "rk_assign_tc.cu"]
+SOURCES = ["rk_api.cu", "rk_search.cu", "rk_scan.cu", "rk_merge.cu", "rk_util.cu", "rk_ivf.cu", "rk_ivf_kernels.cu", "rk_bscan.cu", "rk_bscan2.cu", "rk_tensor.cu", "rk_exchange.cu", "rk_multi.cu", "rk_noalloc.cu", "rk_assign_tc.cu", "rk_pgpage.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

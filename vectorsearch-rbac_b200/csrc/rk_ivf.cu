@@ -50,19 +50,27 @@ static int assign_rows(rk_index *ix, const float *X, size_t n, const float *C, i
     return RK_OK;
 }
 
-// Upload padded centres, assign every row, pack the list-sorted copy of the store.
-static int build_from_device_centers(rk_index *ix, int lists, const float *d_centers)
+// Upload padded centres, assign every row (or take the caller's assignment, `given` by load order), pack the list-sorted
+// copy of the store.
+static int build_from_device_centers(rk_index *ix, int lists, const float *d_centers, const uint32_t *given = nullptr)
 {
     IvfIndex &iv = ix->ivf;
     const size_t n = ix->nrows;
     const size_t rb = (size_t) ix->dim_pad * 4;
     cudaStream_t st = 0;
-    DevBuf d_row_list;
-    if (d_row_list.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
-    { const int rc_ = assign_rows(ix, ix->d_x.as<float>(), n, d_centers, lists, ix->metric, d_row_list.as<uint32_t>(), st); if (rc_ < 0) return rc_; }
     iv.row_list.assign(n, 0);
-    if (n) RK_CUDA(cudaMemcpy(iv.row_list.data(), d_row_list.p, n * 4, cudaMemcpyDeviceToHost));
-    d_row_list.release();
+    if (given) {
+        for (size_t i = 0; i < n; i++) {
+            if (given[i] >= (uint32_t) lists) return rk_fail(RK_ERR_INVALID, "rk_build_ivf_from_lists: row %zu is in list %u of %d", i, given[i], lists);
+            iv.row_list[ix->load_to_row[i]] = given[i];
+        }
+    } else {
+        DevBuf d_row_list;
+        if (d_row_list.ensure(std::max<size_t>(n * 4, 16)) != 0) return RK_ERR_CUDA;
+        { const int rc_ = assign_rows(ix, ix->d_x.as<float>(), n, d_centers, lists, ix->metric, d_row_list.as<uint32_t>(), st); if (rc_ < 0) return rc_; }
+        if (n) RK_CUDA(cudaMemcpy(iv.row_list.data(), d_row_list.p, n * 4, cudaMemcpyDeviceToHost));
+        d_row_list.release();
+    }
     // Document classes: documents with the same role mask are visible to exactly the same users.  With at most 128 of them
     // (role hierarchies: one per role) every list keeps its rows ordered by class, so the rows a user may see in a list are
     // one extent per visible class and the list scan needs no per-row permission test.  Class `ncls` holds the documents
@@ -169,11 +177,11 @@ static int check_build_args(rk_index *ix, int lists, const char *who)
     return 0;
 }
 
-extern "C" int rk_build_ivf_from_centers(rk_index *ix, int lists, const float *centers)
+static int build_from_host_centers(rk_index *ix, int lists, const float *centers, const uint32_t *given, const char *who)
 {
-    int rc = check_build_args(ix, lists, "rk_build_ivf_from_centers");
+    int rc = check_build_args(ix, lists, who);
     if (rc < 0) return rc;
-    if (!centers) return rk_fail(RK_ERR_INVALID, "rk_build_ivf_from_centers: NULL centers");
+    if (!centers) return rk_fail(RK_ERR_INVALID, "%s: NULL centers", who);
     for (size_t i = 0; i < (size_t) lists * ix->dim; i++)
         if (!std::isfinite(centers[i])) return rk_fail(RK_ERR_NONFINITE, "NaN or infinite value not allowed in vector");
     RK_CUDA(cudaSetDevice(ix->device));
@@ -181,7 +189,20 @@ extern "C" int rk_build_ivf_from_centers(rk_index *ix, int lists, const float *c
     if (ix->ivf.d_centers.ensure((size_t) lists * rb) != 0) return RK_ERR_CUDA;
     RK_CUDA(cudaMemset(ix->ivf.d_centers.p, 0, (size_t) lists * rb));
     RK_CUDA(cudaMemcpy2D(ix->ivf.d_centers.p, rb, centers, (size_t) ix->dim * 4, (size_t) ix->dim * 4, lists, cudaMemcpyHostToDevice));
-    return build_from_device_centers(ix, lists, ix->ivf.d_centers.as<float>());
+    return build_from_device_centers(ix, lists, ix->ivf.d_centers.as<float>(), given);
+}
+
+extern "C" int rk_build_ivf_from_centers(rk_index *ix, int lists, const float *centers)
+{
+    return build_from_host_centers(ix, lists, centers, nullptr, "rk_build_ivf_from_centers");
+}
+
+// An index that already exists on disk (rk_ivfpages_read): the lists are taken as stored — ivfscan.c:128-168 scans a list's
+// pages whatever centre its tuples are nearest to — so nothing is re-assigned.
+extern "C" int rk_build_ivf_from_lists(rk_index *ix, int lists, const float *centers, const uint32_t *row_list)
+{
+    if (!row_list) return rk_fail(RK_ERR_INVALID, "rk_build_ivf_from_lists: NULL row_list");
+    return build_from_host_centers(ix, lists, centers, row_list, "rk_build_ivf_from_lists");
 }
 
 extern "C" int rk_build_ivf(rk_index *ix, int lists, uint64_t seed)

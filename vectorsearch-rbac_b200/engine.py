@@ -126,6 +126,13 @@ class Index:
         assert c.ndim == 2 and c.shape[1] == self.dim
         _check(lib.rk_build_ivf_from_centers(self._h, c.shape[0], c.ctypes.data))
 
+    def build_ivf_from_lists(self, centers: np.ndarray, row_list: np.ndarray) -> None:
+        """Centres and the row -> list assignment (by load order) of an index that already exists, e.g. IvfflatPages.read()."""
+        c = np.ascontiguousarray(centers, dtype=np.float32)
+        rl = np.ascontiguousarray(row_list, dtype=np.uint32)
+        assert c.ndim == 2 and c.shape[1] == self.dim
+        _check(lib.rk_build_ivf_from_lists(self._h, c.shape[0], c.ctypes.data, rl.ctypes.data))
+
     def ivf_info(self, nrows: int) -> Tuple[np.ndarray, np.ndarray]:
         n = C.c_int(0)
         _check(lib.rk_ivf_info(self._h, C.byref(n), None, None))
@@ -398,5 +405,40 @@ class Scan:
     def __del__(self):
         try:
             self.end()
+        except Exception:
+            pass
+
+
+class IvfflatPages:
+    """The main fork of a pgvector ivfflat index relation, parsed (rk_ivfpages_*; pgvector/src/ivfscan.c:45-101, 128-168).
+    Host code: needs no device."""
+
+    def __init__(self, rel: bytes):
+        self._buf = np.frombuffer(rel, dtype=np.uint8)          # keeps the bytes alive: the handle points into them
+        h = C.c_void_p()
+        _check(lib.rk_ivfpages_open(self._buf.ctypes.data, self._buf.size, C.byref(h)))
+        self._h = h
+        d, l, n, u = C.c_int32(), C.c_int32(), C.c_uint64(), C.c_uint64()
+        _check(lib.rk_ivfpages_info(self._h, C.byref(d), C.byref(l), C.byref(n), C.byref(u)))
+        self.dim, self.lists, self.tuples, self.unused_items = d.value, l.value, n.value, u.value
+
+    def read(self):
+        """-> centers [lists, dim], list_start [lists + 1], row_list [tuples], x [tuples, dim], tid [tuples]"""
+        centers = np.empty((self.lists, self.dim), dtype=np.float32)
+        list_start = np.empty(self.lists + 1, dtype=np.uint32)
+        row_list = np.empty(self.tuples, dtype=np.uint32)
+        x = np.empty((self.tuples, self.dim), dtype=np.float32)
+        tid = np.empty(self.tuples, dtype=np.uint64)
+        _check(lib.rk_ivfpages_read(self._h, centers.ctypes.data, list_start.ctypes.data, row_list.ctypes.data, x.ctypes.data, tid.ctypes.data))
+        return centers, list_start, row_list, x, tid
+
+    def close(self) -> None:
+        if self._h:
+            lib.rk_ivfpages_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
         except Exception:
             pass
