@@ -697,7 +697,7 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
         """roofline.traffic = dram bytes of one launch of this kernel from the committed `ncu --set full` capture
         (profiles/traffic.json); dram_frac = those bytes over the live kernel time against the same peak; l2_share = the part
         of the algorithmic bytes that did not come from DRAM."""
-        tr = traffic_per_launch(wl_key, world, key) if not args.rows or leg else None
+        tr = traffic_per_launch(wl_key, world, key) if (not args.rows or leg) and args.emu_world <= 1 else None
         rf["traffic"] = tr
         if tr and rf.get("kernel_ms") and rf.get("unit") == "GB/s":
             algo = rf.get("algorithmic_bytes_per_launch") or rf.get("bytes_per_launch")
