@@ -81,7 +81,7 @@ typedef enum rk_layout { RK_LAYOUT_AUTO = 0, RK_LAYOUT_ROLE = 1, RK_LAYOUT_COMBI
  *                     contraction (|q|^2 - 2 q.x + |x|^2 or -q.x) with the permission mask in the
  *                     epilogue; nominates candidates in TF32, re-scores them in exact fp32 and falls
  *                     back to the scan for any query whose answer it cannot prove.  Results are
- *                     identical to RK_ENGINE_SCAN.  Exact scans only (probes = 0), k <= 256.
+ *                     identical to RK_ENGINE_SCAN.  Exact scans only (probes = 0), k <= 384.
  *   RK_ENGINE_AUTO    RK_ENGINE_TENSOR for batches of 32 or more exact scans it supports (role,
  *                     combination, bitmask or no filter), RK_ENGINE_SCAN otherwise. */
 typedef enum rk_engine { RK_ENGINE_AUTO = 0, RK_ENGINE_SCAN = 1, RK_ENGINE_TENSOR = 2 } rk_engine;

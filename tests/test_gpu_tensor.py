@@ -25,11 +25,11 @@ def _queries(ds, nq, seed=11):
     return ds["X"][rows].copy(), users[rng.integers(0, len(users), nq)].astype(np.uint32)
 
 
-@pytest.mark.parametrize("nq,k", [(5, 10), (128, 100), (300, 30)])
+@pytest.mark.parametrize("nq,k", [(5, 10), (128, 100), (300, 30), (40, 384)])
 def test_tensor_engine_sift_bitmask_exact(nq, k):
     import vectorsearch_rbac_b200 as vr
     ds = make_dataset("sift", n=20000, dim=128, rows_per_doc=20, rbac="random", num_users=40, num_roles=12)
-    ix = load_index(ds, role_parts=False, combo_parts=False, k_max=256)
+    ix = load_index(ds, role_parts=False, combo_parts=False, k_max=384)
     ix.finalize()
     Q, users = _queries(ds, nq)
     got = ix.search_batch(Q, users, k, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_TENSOR)
@@ -103,7 +103,7 @@ def test_tensor_engine_unfiltered_and_small_visible_sets():
             np.testing.assert_array_equal(a, b)
     assert got[3][0] == 0
     with pytest.raises(vr.RkError):
-        ix.search_batch(Q, users, 300, engine=vr.ENGINE_TENSOR)        # k > 256
+        ix.search_batch(Q, users, 400, engine=vr.ENGINE_TENSOR)        # k > 384
     ix.close()
 
 

@@ -516,7 +516,7 @@ static int search_device(rk_index *ix, Workspace &ws, size_t nq, const float *dQ
     const bool auto_tensor = o->engine == RK_ENGINE_AUTO && nq >= 32 && &ws == &ix->ws && rk_tensor_supported(ix, o) &&
                              !(o->filter == RK_FILTER_PARTITION && (o->layout == RK_LAYOUT_DYNAMIC || (o->layout == RK_LAYOUT_AUTO && !ix->roleset_parts.empty())));
     if (o->engine == RK_ENGINE_TENSOR || auto_tensor) {
-        if (!rk_tensor_supported(ix, o)) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR needs an exact scan (probes = 0), k <= 256, no keep_duplicates / NULL query");
+        if (!rk_tensor_supported(ix, o)) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR needs an exact scan (probes = 0), k <= 384, no keep_duplicates / NULL query");
         if (&ws != &ix->ws) return rk_fail(RK_ERR_UNSUPPORTED, "RK_ENGINE_TENSOR is a batch engine (rk_search_batch*), not available on scan handles");
         std::vector<uint32_t> redo;
         int rc = rk_tensor_search(ix, ws, nq, dQ, user_ids, o, out, redo);
