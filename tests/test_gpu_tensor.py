@@ -193,3 +193,43 @@ def test_tensor_engine_long_units_many_compactions(monkeypatch):
         for a, b in zip(got, ref):
             np.testing.assert_array_equal(a, b)
     ix.close()
+
+
+@pytest.mark.parametrize("dim,lay", [(128, "bitmask"), (256, "role")])
+def test_short_nomination_lists_on_exact_data_and_compaction_marks(dim, lay):
+    """Integer rows + integer queries: from the second batch on the nomination list is k + 28 entries (option tensor_kp_exact);
+    a batch of NON-integer queries that follows is still answered exactly (the proof refuses what the short list cannot cover);
+    the compaction-round mark (tensor_round_mark) and tensor_kp_exact = -1 change nothing in the results.  One-CTA kernel (128
+    floats) and CTA-pair kernel (256)."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("sift", n=40000, dim=dim, rows_per_doc=20, rbac="tree", num_users=40, num_roles=12)
+    ix = load_index(ds, combo_parts=False, k_max=128)
+    ix.finalize()
+    flt, layout, mode = (vr.FILTER_BITMASK, 0, "bitmask") if lay == "bitmask" else (vr.FILTER_PARTITION, vr.LAYOUT_ROLE, "role")
+    k = 50
+    for rep, (mark, kpx) in enumerate([(512, 28), (512, 28), (768, 28), (200, 4), (512, -1)]):
+        ix.set_option("tensor_round_mark", mark)
+        ix.set_option("tensor_kp_exact", kpx)
+        Q, users = _queries(ds, 96, seed=20 + rep)
+        got = ix.search_batch(Q, users, k, filter=flt, layout=layout, engine=vr.ENGINE_TENSOR)
+        st = ix.stats()
+        exp = oracle_role_search(ds, Q, users, orc.METRIC_L2, k, mode=mode)
+        assert_topk_matches(got, exp, exact=True)
+        assert st["tensor_exact"] == 1 and st["tensor_redo"] <= 24
+    # non-integer queries right after an exact batch: the short list meets a non-zero error bound
+    ix.set_option("tensor_kp_exact", 28)
+    Q, users = _queries(ds, 96, seed=31)
+    Qf = (Q + np.random.default_rng(1).uniform(-0.4, 0.4, Q.shape)).astype(np.float32)
+    got = ix.search_batch(Qf, users, k, filter=flt, layout=layout, engine=vr.ENGINE_TENSOR)
+    assert ix.stats()["tensor_exact"] == 0
+    ref = ix.search_batch(Qf, users, k, filter=flt, layout=layout, engine=vr.ENGINE_SCAN)
+    for a, b in zip(got, ref):
+        np.testing.assert_array_equal(a, b)
+    exp = oracle_role_search(ds, Qf, users, orc.METRIC_L2, k, mode=mode)
+    assert_topk_matches(got, exp, exact=False)
+    # and the batch after it is back on the full list, then short again
+    for _ in range(2):
+        Q, users = _queries(ds, 96, seed=33)
+        got = ix.search_batch(Q, users, k, filter=flt, layout=layout, engine=vr.ENGINE_TENSOR)
+        assert_topk_matches(got, oracle_role_search(ds, Q, users, orc.METRIC_L2, k, mode=mode), exact=True)
+    ix.close()

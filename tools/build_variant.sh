@@ -8,7 +8,7 @@ mkdir -p gpurun_tmp/obj_$N
 P=vectorsearch-rbac_b200
 FL="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden --expt-relaxed-constexpr"
 OBJS=""
-for f in rk_api rk_search rk_scan rk_merge rk_util rk_ivf rk_ivf_kernels rk_bscan rk_bscan2 rk_tensor rk_exchange rk_multi rk_noalloc rk_assign_tc; do
+for f in rk_api rk_search rk_scan rk_merge rk_util rk_ivf rk_ivf_kernels rk_bscan rk_bscan2 rk_tensor rk_exchange rk_multi rk_noalloc rk_assign_tc rk_pgpage; do
   if echo " ${FILES:-rk_scan} " | grep -q " $f "; then
     /usr/local/cuda/bin/nvcc $FL "$@" -c $P/csrc/$f.cu -o gpurun_tmp/obj_$N/$f.o &
     OBJS="$OBJS gpurun_tmp/obj_$N/$f.o"

@@ -177,6 +177,9 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.tensor_host_timing = getenv("RK_TENSOR_HOST_TIMING") != nullptr;
         t.tensor_bf16 = env_int("RK_TENSOR_BF16", -1);
         t.tensor_kp_extra = std::max(0, env_int("RK_TENSOR_KP_EXTRA", 0));
+        t.tensor_kp_exact = env_int("RK_TENSOR_KP_EXACT", 28);
+        t.tensor_loose = std::max(0, env_int("RK_TENSOR_LOOSE", 128));
+        t.tensor_round_mark = std::min(768, std::max(1, env_int("RK_TENSOR_ROUND_MARK", 512)));
         t.tensor_kp_bf16 = std::max(0, env_int("RK_TENSOR_KP_BF16", 64));
         t.tensor_qtau = env_int("RK_TENSOR_QTAU", 1);
         t.ivf_seg_factor = std::max(1, env_int("RK_IVF_SEG_FACTOR", 4));
@@ -212,6 +215,9 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "tensor_host_timing")) t.tensor_host_timing = v != 0;
     else if (!strcmp(name, "tensor_bf16")) t.tensor_bf16 = v;
     else if (!strcmp(name, "tensor_kp_extra")) t.tensor_kp_extra = std::max(0, v);
+    else if (!strcmp(name, "tensor_kp_exact")) t.tensor_kp_exact = v;
+    else if (!strcmp(name, "tensor_loose")) t.tensor_loose = std::max(0, v);
+    else if (!strcmp(name, "tensor_round_mark")) t.tensor_round_mark = std::min(768, std::max(1, v));
     else if (!strcmp(name, "tensor_kp_bf16")) t.tensor_kp_bf16 = std::max(0, v);
     else if (!strcmp(name, "tensor_qtau")) t.tensor_qtau = v;
     else if (!strcmp(name, "ivf_seg_factor")) t.ivf_seg_factor = std::max(1, v);

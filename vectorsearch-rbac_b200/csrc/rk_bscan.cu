@@ -70,6 +70,16 @@ __host__ __device__ inline BsSmem bs_smem_layout(int mask_words)
 }
 
 
+#ifdef BS_TRACE
+// experiment build only (tools/build_variant.sh ... -DBS_TRACE): clock64 stamps of CTA 0's warps over tiles [BS_TR_T0, BS_TR_T0 + 64)
+#define BS_TR_T0 300u
+#define BS_TR_SLOTS 64
+__device__ unsigned long long *bs_trace_ptr;
+#define BS_STAMP(tile, slot) do { if (blockIdx.x == 0 && lane == 0 && (tile) >= BS_TR_T0 && (tile) < BS_TR_T0 + 64u) bs_trace_ptr[((tile) - BS_TR_T0) * BS_TR_SLOTS + (slot)] = clock64(); } while (0)
+#else
+#define BS_STAMP(tile, slot) do { } while (0)
+#endif
+
 template <int METRIC>
 __global__ void __launch_bounds__(BS_THREADS, 1)
 rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmq16,
@@ -103,6 +113,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         // ===================== TMA producer =====================
         int stage = 0;
         uint32_t phase = 0;
+        uint32_t ptile = 0; (void) ptile;
         for (uint32_t ui = p.cta_off[blockIdx.x]; ui < p.cta_off[blockIdx.x + 1]; ui++) {
             const RkBUnit un = p.units[p.cta_units[ui]];
             // the query box is only as tall as the unit needs (16 / 32 / 64 / 128 rows)
@@ -123,6 +134,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                     if (lane == 0) {
                         for (int kc = 0; kc < p.kchunks; kc++) {
                             rk_mbar_wait(&empty[stage], phase ^ 1u);
+                            BS_STAMP(ptile, 0 + kc);                 // producer: stage free, about to issue k-chunk kc
                             unsigned char *st = smem + L.off_stage + (size_t) stage * BS_STAGE_BYTES;
                             rk_mbar_arrive_expect_tx(&full[stage], tx);
                             bs_tma_2d(st, &tmx, kc * BS_KC, row0, &full[stage]);
@@ -131,6 +143,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         }
                     }
                     __syncwarp();
+                    ptile++;
                 }
             }
         }
@@ -147,11 +160,14 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             const uint32_t ntiles = bs_unit_tiles(un);
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
+                BS_STAMP(tcount, 8);                                 // MMA warp: at the tile
                 rk_mbar_wait(&tempty[buf], tph ^ 1u);
+                BS_STAMP(tcount, 9);                                 // accumulator buffer free
                 bs_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * BS_N;
                 for (int kc = 0; kc < p.kchunks; kc++) {
                     rk_mbar_wait(&full[stage], phase);
+                    BS_STAMP(tcount, 10 + kc);                       // k-chunk kc has landed
                     bs_fence_after();
                     if (lane == 0) {
                         const uint32_t a0 = rk_smem_u32(smem + L.off_stage + (size_t) stage * BS_STAGE_BYTES);
@@ -183,6 +199,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
         c.scratch = p.scratch + (size_t) blockIdx.x * BS_N * BS_CAP;
         c.sortbuf = reinterpret_cast<uint64_t *>(smem + L.off_sort) + ew * BS_SORT_MAX;
         c.lane = lane;
+        c.loose_extra = p.loose_extra;
         int32_t **s_trunc = reinterpret_cast<int32_t **>(smem + L.off_trunc);     // each query's trunc flag
         uint4 *s_qa = reinterpret_cast<uint4 *>(smem + L.off_qa);
         uint64_t *s_um = reinterpret_cast<uint64_t *>(smem + L.off_um);
@@ -266,6 +283,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
             }
             for (uint32_t ti = 0; ti < ntiles; ti++, tcount++) {
                 const uint32_t buf = tcount & 1u, tph = (tcount >> 1) & 1u;
+                BS_STAMP(tcount, 16 + ew * 6 + 0);                   // epilogue warp ew: loop top
                 const uint64_t row = (uint64_t) r0_cur + (uint64_t) erow;
                 // the two warps of a lane quarter swap chunk parity every tile (an odd number of chunks evens out over two tiles)
                 const int cpar = (chalf + (int) ti) & 1;
@@ -311,7 +329,9 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 r0_cur = r0_next;
                 r0_next = tile_row0(ti + 2);
                 fetch_row(r0_cur);
+                BS_STAMP(tcount, 16 + ew * 6 + 1);                   // masks settled, next tile's loads issued
                 rk_mbar_wait(&tfull[buf], tph);
+                BS_STAMP(tcount, 16 + ew * 6 + 2);                   // accumulators ready
                 bs_fence_after();
                 const uint32_t taddr = tmem_base + buf * BS_N + ((uint32_t) (quarter * 32) << 16);
 #pragma unroll 1
@@ -359,6 +379,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         }
                     }
                 }
+                BS_STAMP(tcount, 16 + ew * 6 + 3);                   // chunks scored
                 bs_fence_before();
                 __syncwarp();
                 if (lane == 0) rk_mbar_arrive(&tempty[buf]);
@@ -370,10 +391,11 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                 // tiles lower was measured: the extra compactions cost more than the barrier saves, 2.31 vs 2.19 ms on C3.)
                 const uint32_t trig = BS_CAP - 2 * BS_M;
                 const bool need = rk_named_bar_red_or(2, BS_EW * 32, et < BS_N && c.cnt[et] > trig);
+                BS_STAMP(tcount, 16 + ew * 6 + 4);                   // past the barrier
                 if (need) {
                     for (uint32_t q = (uint32_t) ew; q < un.nq; q += BS_EW) {
                         const uint32_t n = c.cnt[q];
-                        if (n > trig) {
+                        if (n > p.round_mark) {
                             uint32_t tau;
                             uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
                             if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);     // >= kp rows are <= tau
@@ -388,6 +410,7 @@ rk_bscan_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__
                         }
                     }
                     esync();
+                    BS_STAMP(tcount, 16 + ew * 6 + 5);               // compaction round done
                 }
             }
             // unit end: every query's list, sorted by (approximate key, row), at most kp entries
@@ -690,8 +713,36 @@ cudaError_t rk_make_tensor_map_2d_t(CUtensorMap *tm, const void *base, uint64_t 
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
+#ifdef BS_TRACE
+#include <cstdio>
+#include <cstdlib>
+static unsigned long long *bs_trace_host = nullptr;
+static void bs_trace_dump()
+{
+    const char *path = getenv("BS_TRACE_OUT");
+    FILE *f = fopen(path ? path : "gpurun_out/bs_trace.txt", "w");
+    if (!f || !bs_trace_host) return;
+    for (int t = 0; t < 64; t++) {
+        fprintf(f, "%d", t);
+        for (int s = 0; s < BS_TR_SLOTS; s++) fprintf(f, " %llu", bs_trace_host[t * BS_TR_SLOTS + s]);
+        fprintf(f, "\n");
+    }
+    fclose(f);
+}
+#endif
+
 cudaError_t rk_launch_bscan(const RkBScanParams &p, const float *x, const float *q, uint64_t nq, int grid, cudaStream_t stream)
 {
+#ifdef BS_TRACE
+    if (!bs_trace_host) {
+        cudaHostAlloc(&bs_trace_host, 64 * BS_TR_SLOTS * 8, cudaHostAllocMapped);
+        unsigned long long *dp = nullptr;
+        cudaHostGetDevicePointer(&dp, bs_trace_host, 0);
+        cudaMemcpyToSymbol(bs_trace_ptr, &dp, sizeof dp);
+        atexit(bs_trace_dump);
+    }
+    memset(bs_trace_host, 0, 64 * BS_TR_SLOTS * 8);
+#endif
     CUtensorMap tmx, tmq[4];
     cudaError_t e = rk_make_tensor_map_2d(&tmx, x, p.nrows, p.dim_pad, BS_M);
     if (e != cudaSuccess) return e;

@@ -318,6 +318,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
         c.scratch = p.scratch + (size_t) blockIdx.x * B2_N * BS_CAP;
         c.sortbuf = reinterpret_cast<uint64_t *>(smem + L.off_sort) + ew * BS_SORT_MAX;
         c.lane = lane;
+        c.loose_extra = p.loose_extra;
         float *tauf = reinterpret_cast<float *>(smem + L.off_tauf);
         int32_t **s_trunc = reinterpret_cast<int32_t **>(smem + L.off_trunc);
         uint4 *s_qa = reinterpret_cast<uint4 *>(smem + L.off_qa);
@@ -482,7 +483,7 @@ rk_bscan2_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant_
                 if (need) {
                     for (uint32_t q = (uint32_t) ew; q < un.nq; q += B2_EW) {
                         const uint32_t n = c.cnt[q];
-                        if (n > BS_CAP - 2 * B2_M) {
+                        if (n > p.round_mark) {
                             uint32_t tau;
                             uint32_t m = bs_warp_compact(c, (int) q, n, (uint32_t) p.kp, &tau, false);
                             if (p.qtau && lane == 0) atomicMin(p.qtau + (uint32_t) (s_trunc[q] - p.trunc), tau);     // >= kp rows are <= tau

@@ -82,6 +82,7 @@ struct BsCtx {
     uint2 *scratch;     // this CTA's [BS_N][BS_CAP]
     uint64_t *sortbuf;  // this warp's [BS_SORT_MAX]
     int lane;
+    uint32_t loose_extra;
 };
 
 // kp-th smallest key of one query's buffer by a warp-level radix select (8 bits per pass), then in-place
@@ -99,7 +100,7 @@ __device__ __forceinline__ uint32_t bs_warp_compact(const BsCtx &c, int q, uint3
         key[j] = i < n ? __ldcg(&buf[i].x) : RK_KEY_SENTINEL;
     }
     uint32_t prefix = 0, mask = 0, kk = kp, below = 0, tau = 0;
-    const uint32_t loose = min(kp + 128u, (uint32_t) BS_CAP / 2u);
+    const uint32_t loose = min(kp + c.loose_extra, (uint32_t) BS_CAP / 2u);
 #pragma unroll 1
     for (int shift = 24; shift >= 0; shift -= 8) {
 #pragma unroll

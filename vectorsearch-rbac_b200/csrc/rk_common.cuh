@@ -194,6 +194,9 @@ struct RkBScanParams {
     // bf16 nomination (CTA-pair kernel): the tensor maps describe bf16 shadow copies of the rows and the queries, a k-chunk is
     // 64 elements (the same 128 bytes per row) and the MMA is kind::f16 with bf16 operands, fp32 accumulation
     int bf16;
+    // compaction tuning: a mid-unit compaction keeps up to kp + loose_extra entries; once a compaction round has been called
+    // (some buffer above the trigger) every buffer above round_mark is compacted in it
+    uint32_t loose_extra, round_mark;
 };
 
 struct RkRescoreParams {

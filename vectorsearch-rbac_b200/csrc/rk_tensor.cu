@@ -321,6 +321,13 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     const bool bf16_likely = (ix->tune.tensor_pair >= 0 ? ix->tune.tensor_pair != 0 : ix->dim_pad >= 256) &&
                              (ix->tune.tensor_bf16 == 1 || (ix->tune.tensor_bf16 < 0 && !ix->tensor.bf16_off));
     int kp = std::max(2 * k, k + 128) + ix->tune.tensor_kp_extra + (bf16_likely ? ix->tune.tensor_kp_bf16 : 0);
+    // Exact nomination needs no error margin: when the rows are small integers (known since tensor_prepare) and the previous
+    // batch's queries were too, the approximate order IS the exact order and k + a few nominations (ties at the k-th value)
+    // are enough — fewer appends, fewer compactions, a shorter merge and re-score (C3 batched kernel 2.06 -> 1.93 ms).  A batch
+    // that turns out inexact after all is still answered correctly: the proof then works with its usual error bound on the
+    // shorter list and refuses more queries (re-run on the scan engine), and the next batch is back to the full list.
+    if (ix->tune.tensor_kp_exact >= 0 && ts.x_integer && ts.last_exact)
+        kp = std::min(kp, k + std::max(ix->tune.tensor_kp_exact, 4) + ix->tune.tensor_kp_extra);
     if (kp > 512) kp = 512;
     const size_t n = ix->nrows;
     const uint32_t T = (uint32_t) ((n + 127) / 128);
@@ -610,6 +617,8 @@ int rk_tensor_search(rk_index *ix, Workspace &ws, size_t nq, const float *dQ, co
     bp.dim_pad = ix->dim_pad;
     bp.kchunks = bf16 ? (ts.dim_b + 63) / 64 : (ix->dim_pad + 31) / 32;
     bp.bf16 = bf16 ? 1 : 0;
+    bp.loose_extra = (uint32_t) ix->tune.tensor_loose;
+    bp.round_mark = (uint32_t) std::max(ix->tune.tensor_round_mark, kp + 64);      // never compact a buffer that holds little more than kp
     bp.metric = ix->metric;
     bp.kp = kp;
     bp.mask_words = W;
