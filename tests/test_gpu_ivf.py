@@ -345,6 +345,7 @@ def test_kmeanspp_seeding_follows_initcenters():
     n, dim, lists, seed = 3000, 32, 40, 12345
     ds = make_dataset("sift", n=n, dim=dim, rows_per_doc=10, rbac="random", num_users=20, num_roles=8)
     ix = load_index(ds, metric=0, role_parts=False, combo_parts=False)
+    ix.set_option("class_order", 0)                  # index order = load order (by document id), the order the restatement walks
     ix.finalize()
     ix.set_option("ivf_sample_identity", 1)          # the sample = the table in index order (n <= 10000: everything is sampled)
     ix.set_option("ivf_kmeans_iters", 0)             # the seeds become the centres

@@ -196,3 +196,36 @@ def test_shard_exchange_form_and_merge(world):
             assert got[1][q, i] == ds["doc"][row_of_tid[int(got[0][q, i])]]
     for ix in shards:
         ix.close()
+
+
+@pytest.mark.parametrize("rbac", ["tree", "random"])
+def test_document_order_by_class_does_not_change_results(rbac):
+    """rk_finalize orders the documents (= the rows) by (role mask, id) — option class_order, default 1 — so that what a user may
+    see is a few runs of rows; with it the planner cuts a masked scan inside those runs (no per-extent mask test).  Results are
+    those of the by-id order and of the oracle, bit for bit, on every engine / filter; tree RBAC gives a few runs per user
+    (the run-based plan: fewer segments than extents walked), random RBAC thousands (the per-extent mask path)."""
+    import vectorsearch_rbac_b200 as vr
+    ds = make_dataset("sift", n=60000, dim=64, rows_per_doc=10, rbac=rbac, num_users=60, num_roles=20)
+    rng = np.random.default_rng(9)
+    users = np.unique(ds["user_roles"][:, 0])
+    Q = ds["X"][rng.integers(0, len(ds["X"]), 48)].copy()
+    qu = users[rng.integers(0, len(users), len(Q))].astype(np.uint32)
+    out = {}
+    for co in (0, 1):
+        ix = load_index(ds, k_max=64)
+        ix.set_option("class_order", co)
+        ix.finalize()
+        res = []
+        for flt, lay, eng in ((vr.FILTER_BITMASK, 0, vr.ENGINE_SCAN), (vr.FILTER_BITMASK, 0, vr.ENGINE_TENSOR),
+                              (vr.FILTER_PARTITION, vr.LAYOUT_ROLE, vr.ENGINE_SCAN), (vr.FILTER_PARTITION, vr.LAYOUT_COMBINATION, vr.ENGINE_SCAN),
+                              (vr.FILTER_NONE, 0, vr.ENGINE_SCAN)):
+            res.append(ix.search_batch(Q, qu, 40, filter=flt, layout=lay, engine=eng))
+        res.append(ix.search_batch(Q[:1], qu[:1], 40, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_SCAN))      # fused single-query launch
+        out[co] = res
+        if co == 1:
+            exp = oracle_role_search(ds, Q, qu, orc.METRIC_L2, 40, mode="bitmask")
+            assert_topk_matches(res[0], exp, exact=True)
+        ix.close()
+    for a, b in zip(out[0], out[1]):
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)

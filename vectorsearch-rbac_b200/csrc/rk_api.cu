@@ -178,6 +178,7 @@ extern "C" rk_index *rk_open(const rk_config *cfg)
         t.tensor_bf16 = env_int("RK_TENSOR_BF16", -1);
         t.tensor_kp_extra = std::max(0, env_int("RK_TENSOR_KP_EXTRA", 0));
         t.tensor_kp_exact = env_int("RK_TENSOR_KP_EXACT", 28);
+        t.class_order = env_int("RK_CLASS_ORDER", 1);
         t.tensor_loose = std::max(0, env_int("RK_TENSOR_LOOSE", 128));
         t.tensor_round_mark = std::min(768, std::max(1, env_int("RK_TENSOR_ROUND_MARK", 512)));
         t.tensor_kp_bf16 = std::max(0, env_int("RK_TENSOR_KP_BF16", 64));
@@ -216,6 +217,7 @@ extern "C" int rk_set_option(rk_index *ix, const char *name, int64_t value)
     else if (!strcmp(name, "tensor_bf16")) t.tensor_bf16 = v;
     else if (!strcmp(name, "tensor_kp_extra")) t.tensor_kp_extra = std::max(0, v);
     else if (!strcmp(name, "tensor_kp_exact")) t.tensor_kp_exact = v;
+    else if (!strcmp(name, "class_order")) t.class_order = v;
     else if (!strcmp(name, "tensor_loose")) t.tensor_loose = std::max(0, v);
     else if (!strcmp(name, "tensor_round_mark")) t.tensor_round_mark = std::min(768, std::max(1, v));
     else if (!strcmp(name, "tensor_kp_bf16")) t.tensor_kp_bf16 = std::max(0, v);
@@ -439,15 +441,53 @@ extern "C" int rk_finalize(rk_index *ix)
     const size_t n = ix->nrows;
     const size_t rb = (size_t) ix->dim_pad * 4;
 
-    // documents: dense index in ascending raw id
-    ix->doc_ids = ix->h_doc;
-    std::sort(ix->doc_ids.begin(), ix->doc_ids.end());
-    ix->doc_ids.erase(std::unique(ix->doc_ids.begin(), ix->doc_ids.end()), ix->doc_ids.end());
-    const size_t D = ix->doc_ids.size();
+    // roles: dense bit positions in ascending raw id
+    for (auto &pr : ix->doc_roles) ix->role_ids.push_back(pr.second);
+    for (auto &pr : ix->user_roles) ix->role_ids.push_back(pr.second);
+    std::sort(ix->role_ids.begin(), ix->role_ids.end());
+    ix->role_ids.erase(std::unique(ix->role_ids.begin(), ix->role_ids.end()), ix->role_ids.end());
+    ix->mask_words = std::max<int>(1, (int) ((ix->role_ids.size() + 63) / 64));
+    if (ix->mask_words > 16) return rk_fail(RK_ERR_UNSUPPORTED, "rk_finalize: %zu roles, at most 1024 supported", ix->role_ids.size());
+    const int W = ix->mask_words;
+
+    // documents.  The dense document index — which is also the physical order of the rows — goes by (role mask, raw id):
+    // documents with the same role mask (a document class: visible to exactly the same users) are neighbours, so what a user
+    // may see is a few long runs of rows instead of documents scattered over the whole store.  The scan's producer fuses
+    // adjacent extents into one bulk copy, a single query's private extent table shrinks to a handful of runs, and a unit of
+    // the tensor engine's per-class plan covers whole 128-row tiles of its own class (before: a document of 100 rows dragged
+    // 28 rows of some other class into every tile).  Results do not depend on the order (ties break by tuple id).
+    std::vector<uint32_t> raw_sorted = ix->h_doc;
+    std::sort(raw_sorted.begin(), raw_sorted.end());
+    raw_sorted.erase(std::unique(raw_sorted.begin(), raw_sorted.end()), raw_sorted.end());
+    const size_t D = raw_sorted.size();
+    auto raw_index = [&](uint32_t raw) -> size_t {       // position in raw_sorted, or D
+        auto it = std::lower_bound(raw_sorted.begin(), raw_sorted.end(), raw);
+        return it != raw_sorted.end() && *it == raw ? (size_t) (it - raw_sorted.begin()) : D;
+    };
+    std::vector<uint64_t> mask0(std::max<size_t>(D, 1) * W, 0);
+    for (auto &pr : ix->doc_roles) {
+        const size_t d = raw_index(pr.first);
+        if (d == D) continue;   // permission for a document with no rows
+        size_t b = (size_t) (std::lower_bound(ix->role_ids.begin(), ix->role_ids.end(), pr.second) - ix->role_ids.begin());
+        mask0[d * W + (b >> 6)] |= 1ull << (b & 63);
+    }
+    std::vector<uint32_t> doc_order(D), new_of_raw(D);
+    for (size_t d = 0; d < D; d++) doc_order[d] = (uint32_t) d;
+    if (ix->tune.class_order)
+        std::stable_sort(doc_order.begin(), doc_order.end(), [&](uint32_t a, uint32_t b) {
+            return std::lexicographical_compare(&mask0[(size_t) a * W], &mask0[(size_t) a * W] + W, &mask0[(size_t) b * W], &mask0[(size_t) b * W] + W);
+        });
+    ix->doc_ids.resize(D);
+    ix->doc_mask.assign(std::max<size_t>(D, 1) * W, 0);
+    for (size_t i = 0; i < D; i++) {
+        new_of_raw[doc_order[i]] = (uint32_t) i;
+        ix->doc_ids[i] = raw_sorted[doc_order[i]];
+        for (int w = 0; w < W; w++) ix->doc_mask[i * W + w] = mask0[(size_t) doc_order[i] * W + w];
+    }
     std::vector<uint32_t> dense(n);
     bool sorted = true;
     for (size_t i = 0; i < n; i++) {
-        dense[i] = (uint32_t) (std::lower_bound(ix->doc_ids.begin(), ix->doc_ids.end(), ix->h_doc[i]) - ix->doc_ids.begin());
+        dense[i] = new_of_raw[raw_index(ix->h_doc[i])];
         if (i && dense[i] < dense[i - 1]) sorted = false;
     }
     // rows ordered by document (stable), so a document is one contiguous extent
@@ -480,23 +520,6 @@ extern "C" int rk_finalize(rk_index *ix)
     ix->doc_row_start.assign(D + 1, 0);
     for (size_t i = 0; i < n; i++) ix->doc_row_start[ix->h_rowdoc[i] + 1]++;
     for (size_t d = 0; d < D; d++) ix->doc_row_start[d + 1] += ix->doc_row_start[d];
-
-    // roles: dense bit positions in ascending raw id
-    for (auto &pr : ix->doc_roles) ix->role_ids.push_back(pr.second);
-    for (auto &pr : ix->user_roles) ix->role_ids.push_back(pr.second);
-    std::sort(ix->role_ids.begin(), ix->role_ids.end());
-    ix->role_ids.erase(std::unique(ix->role_ids.begin(), ix->role_ids.end()), ix->role_ids.end());
-    ix->mask_words = std::max<int>(1, (int) ((ix->role_ids.size() + 63) / 64));
-    if (ix->mask_words > 16) return rk_fail(RK_ERR_UNSUPPORTED, "rk_finalize: %zu roles, at most 1024 supported", ix->role_ids.size());
-    const int W = ix->mask_words;
-    ix->doc_mask.assign(std::max<size_t>(D, 1) * W, 0);
-    for (auto &pr : ix->doc_roles) {
-        auto it = std::lower_bound(ix->doc_ids.begin(), ix->doc_ids.end(), pr.first);
-        if (it == ix->doc_ids.end() || *it != pr.first) continue;   // permission for a document with no rows
-        size_t d = (size_t) (it - ix->doc_ids.begin());
-        size_t b = (size_t) (std::lower_bound(ix->role_ids.begin(), ix->role_ids.end(), pr.second) - ix->role_ids.begin());
-        ix->doc_mask[d * W + (b >> 6)] |= 1ull << (b & 63);
-    }
 
     // users
     for (auto &pr : ix->user_roles) ix->users[pr.first].roles.push_back(pr.second);
@@ -562,8 +585,8 @@ extern "C" int rk_finalize(rk_index *ix)
         // load_result_to_database.py:207-250 — documentblocks_partition_<p>
         PartInfo pi;
         for (uint32_t raw : kv.second) {
-            auto it = std::lower_bound(ix->doc_ids.begin(), ix->doc_ids.end(), raw);
-            if (it != ix->doc_ids.end() && *it == raw) pi.docs.push_back((uint32_t) (it - ix->doc_ids.begin()));
+            const size_t d = raw_index(raw);
+            if (d != D) pi.docs.push_back(new_of_raw[d]);
         }
         std::sort(pi.docs.begin(), pi.docs.end());
         pi.docs.erase(std::unique(pi.docs.begin(), pi.docs.end()), pi.docs.end());

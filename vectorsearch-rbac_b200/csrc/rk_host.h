@@ -114,6 +114,14 @@ struct PartInfo {
     std::vector<uint32_t> vstart; // [n_ext + 1] virtual row offset of each extent, last = rows
 };
 
+// The extents of a partition one role mask may see, as maximal runs of neighbouring extents [lo, hi) (indices inside the
+// partition).  `few` = at most RK_FEW_RUNS of them (documents ordered by role mask: rk_finalize) — only then are lo / hi filled.
+#define RK_FEW_RUNS 64
+struct VisRuns {
+    bool few = false;
+    std::vector<uint32_t> lo, hi;
+};
+
 struct UserInfo {
     std::vector<uint32_t> roles;        // raw role ids, ascending, unique
     std::vector<uint64_t> mask;         // [mask_words]
@@ -181,6 +189,7 @@ struct RkTuning {
     int tensor_kp_exact = 28;    // RK_TENSOR_KP_EXACT: nominations beyond k while nomination is EXACT (integer data, the previous batch proved it); < 0 = off
     int tensor_loose = 128;      // RK_TENSOR_LOOSE: entries beyond kp a mid-unit compaction may keep
     int tensor_round_mark = 512; // RK_TENSOR_ROUND_MARK: buffers above this many entries are compacted whenever a compaction round runs (trigger: 768)
+    int class_order = 1;         // RK_CLASS_ORDER: 1 = rk_finalize orders the documents (= the rows) by (role mask, id), 0 = by id (round-2 A/B)
     int tensor_kp_extra = 0;     // RK_TENSOR_KP_EXTRA: added to the nominations per query (kp = max(2k, k + 128) + ...; at most 512)
     int tensor_kp_bf16 = 64;     // RK_TENSOR_KP_BF16: added on top when the nomination runs in bf16 (C2: 9 refused queries per 1000 -> 1)
     int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = bf16 on the CTA-pair kernel while the proof accepts it, 0 = TF32 nomination, 1 = bf16 always
@@ -218,7 +227,7 @@ struct rk_index {
     bool want_role_parts = false, want_combo_parts = false;
     // finalized layout
     std::vector<uint32_t> load_to_row;            // load order -> finalized row
-    std::vector<uint32_t> doc_ids;                // dense -> raw document id (ascending)
+    std::vector<uint32_t> doc_ids;                // dense -> raw document id (dense order: by (role mask, raw id), see rk_finalize)
     std::vector<uint32_t> doc_row_start;          // [docs+1]
     std::vector<uint32_t> h_rowdoc;               // dense doc of each finalized row
     std::vector<uint32_t> role_ids;               // dense -> raw role id (ascending)
@@ -232,6 +241,7 @@ struct rk_index {
     uint32_t n_mask_ids = 0;                      // distinct user role masks (UserInfo::mask_id < n_mask_ids)
     std::map<std::pair<std::vector<uint32_t>, uint32_t>, bool> pure_cache;  // (role set, part) -> pure?
     std::map<std::pair<std::vector<uint32_t>, uint32_t>, uint64_t> visible_cache;  // (role set, part) -> rows of the part the role set sees
+    std::map<std::pair<uint32_t, uint32_t>, VisRuns> runs_cache;   // (user mask id, part) -> the visible extents as runs (rk_search.cu: visible_runs)
     std::mutex mu;
     DevBuf d_tid, d_rowdoc, d_doc_ids, d_doc_mask, d_ext_row, d_ext_vstart, d_ext_mask, d_part_ext_off;
     uint64_t device_bytes = 0;

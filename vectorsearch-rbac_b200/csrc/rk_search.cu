@@ -70,8 +70,37 @@ static uint64_t partition_visible_rows(rk_index *ix, const UserInfo &u, uint32_t
     return rows;
 }
 
-// rows_est: rows the segments cover (sizing, scheduling); rows_algo: rows that count as algorithmic traffic
-struct PlanItem { uint32_t part; uint32_t flags; uint64_t rows_est; uint64_t rows_algo; };
+// Which extents of partition pidx does this user's role mask see?  Cached per (mask id, partition).
+static const VisRuns *visible_runs(rk_index *ix, const UserInfo &u, uint32_t pidx)
+{
+    std::lock_guard<std::mutex> g(ix->mu);
+    auto key = std::make_pair(u.mask_id, pidx);
+    auto it = ix->runs_cache.find(key);
+    if (it != ix->runs_cache.end()) return &it->second;
+    VisRuns vr;
+    vr.few = true;
+    const int W = ix->mask_words;
+    const PartInfo &P = ix->parts[pidx];
+    bool open = false;
+    for (uint32_t e = 0; e < P.n_ext && vr.few; e++) {
+        const uint32_t d = P.docs[e];
+        uint64_t acc = 0;
+        for (int w = 0; w < W; w++) acc |= ix->doc_mask[(size_t) d * W + w] & u.mask[w];
+        if (acc) {
+            if (!open) {
+                if (vr.lo.size() == RK_FEW_RUNS) { vr.few = false; break; }
+                vr.lo.push_back(e); vr.hi.push_back(e + 1); open = true;
+            } else vr.hi.back() = e + 1;
+        } else open = false;
+    }
+    if (!vr.few) { vr.lo.clear(); vr.hi.clear(); }
+    return &(ix->runs_cache[key] = std::move(vr));
+}
+
+// rows_est: rows the segments cover (sizing, scheduling); rows_algo: rows that count as algorithmic traffic; runs: the
+// visible extents of a masked partition when they form a few runs (segments are then cut inside the runs, need no mask test
+// and skip what lies between them)
+struct PlanItem { uint32_t part; uint32_t flags; uint64_t rows_est; uint64_t rows_algo; const VisRuns *runs = nullptr; };
 
 // Which partitions does this user's scan walk?  Returns <0 on error.
 static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std::vector<PlanItem> &items)
@@ -83,7 +112,11 @@ static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std
     }
     if (!u || u->roles.empty()) return 0;   // no roles -> nothing visible
     if (o->filter == RK_FILTER_BITMASK) {
-        if (u->allowed_rows) items.push_back({0u, RK_SEGF_MASKED, u->allowed_rows, u->allowed_rows});
+        if (u->allowed_rows) {
+            items.push_back({0u, RK_SEGF_MASKED, u->allowed_rows, u->allowed_rows});
+            const VisRuns *vr = visible_runs(ix, *u, 0u);
+            if (vr->few) items.back().runs = vr;
+        }
         return 0;
     }
     int layout = o->layout;
@@ -113,6 +146,10 @@ static int plan_user(rk_index *ix, const UserInfo *u, const rk_scan_opts *o, std
             if (!ix->parts[pidx].rows) continue;
             bool pure = partition_pure(ix, *u, pidx);
             items.push_back({pidx, pure ? 0u : RK_SEGF_MASKED, ix->parts[pidx].rows, pure ? ix->parts[pidx].rows : partition_visible_rows(ix, *u, pidx)});
+            if (!pure) {
+                const VisRuns *vr = visible_runs(ix, *u, pidx);
+                if (vr->few) { items.back().runs = vr; items.back().rows_est = items.back().rows_algo; }
+            }
         }
     } else {
         return rk_fail(RK_ERR_INVALID, "unknown layout %d", layout);
@@ -153,6 +190,28 @@ static uint64_t append_segments(const rk_index *ix, const std::vector<PlanItem> 
     uint64_t mask_bytes = 0;
     for (auto &pi : items) {
         const PartInfo &P = ix->parts[pi.part];
+        if (pi.runs) {
+            // the visible extents are a few runs: cut each run on its own — every row of such a segment is visible, so no mask
+            // test (and no mask bytes), nothing between the runs is walked, and the segments are equal in VISIBLE rows
+            for (size_t r = 0; r < pi.runs->lo.size(); r++) {
+                const uint64_t v0 = P.vstart[pi.runs->lo[r]], v1 = P.vstart[pi.runs->hi[r]];
+                uint64_t nch = (v1 - v0 + target / 2) / target;
+                if (nch < 1) nch = 1;
+                for (uint64_t c = 0; c < nch; c++) {
+                    RkSegment s;
+                    s.query = q; s.kind = RK_SEG_EXTENTS;
+                    s.flags = (uint16_t) ((pi.flags & ~RK_SEGF_MASKED) | (items.size() == 1 ? RK_SEGF_MERGE_OK : 0u));
+                    s.begin = v0 + (v1 - v0) * c / nch;
+                    s.end = v0 + (v1 - v0) * (c + 1) / nch;
+                    if (s.end <= s.begin) continue;
+                    const auto vb = P.vstart.begin(), ve = P.vstart.end();
+                    s.ext_lo = P.ext_off + (uint32_t) (std::upper_bound(vb, ve, (uint32_t) s.begin) - vb) - 1;
+                    s.ext_hi = P.ext_off + (uint32_t) (std::lower_bound(vb, ve, (uint32_t) s.end) - vb);
+                    segs.push_back(s);
+                }
+            }
+            continue;
+        }
         segments_of_part(P, pi.flags, pi.rows_est, q, target, items.size() == 1, segs);
         if (pi.flags & RK_SEGF_MASKED) mask_bytes += (uint64_t) P.n_ext * (8ull * W + 8);
     }
