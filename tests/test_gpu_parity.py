@@ -211,7 +211,7 @@ def test_document_order_by_class_does_not_change_results(rbac):
     Q = ds["X"][rng.integers(0, len(ds["X"]), 48)].copy()
     qu = users[rng.integers(0, len(users), len(Q))].astype(np.uint32)
     out = {}
-    for co in (0, 1):
+    for co in (0, 2):
         ix = load_index(ds, k_max=64)
         ix.set_option("class_order", co)
         ix.finalize()
@@ -222,10 +222,10 @@ def test_document_order_by_class_does_not_change_results(rbac):
             res.append(ix.search_batch(Q, qu, 40, filter=flt, layout=lay, engine=eng))
         res.append(ix.search_batch(Q[:1], qu[:1], 40, filter=vr.FILTER_BITMASK, engine=vr.ENGINE_SCAN))      # fused single-query launch
         out[co] = res
-        if co == 1:
+        if co == 2:
             exp = oracle_role_search(ds, Q, qu, orc.METRIC_L2, 40, mode="bitmask")
             assert_topk_matches(res[0], exp, exact=True)
         ix.close()
-    for a, b in zip(out[0], out[1]):
+    for a, b in zip(out[0], out[2]):
         for x, y in zip(a, b):
             np.testing.assert_array_equal(x, y)

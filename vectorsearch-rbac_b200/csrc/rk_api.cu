@@ -473,10 +473,27 @@ extern "C" int rk_finalize(rk_index *ix)
     }
     std::vector<uint32_t> doc_order(D), new_of_raw(D);
     for (size_t d = 0; d < D; d++) doc_order[d] = (uint32_t) d;
-    if (ix->tune.class_order)
+    bool class_order = ix->tune.class_order != 0;
+    if (class_order) {
+        // (re-ordering the rows takes a second copy of the row store for a moment: a store that fills more than half of the
+        // free HBM keeps the order by id)
+        size_t fr = 0, tot = 0;
+        if (cudaMemGetInfo(&fr, &tot) == cudaSuccess && fr < n * rb + ((size_t) 256 << 20)) class_order = false;
+    }
+    if (class_order)
         std::stable_sort(doc_order.begin(), doc_order.end(), [&](uint32_t a, uint32_t b) {
             return std::lexicographical_compare(&mask0[(size_t) a * W], &mask0[(size_t) a * W] + W, &mask0[(size_t) b * W], &mask0[(size_t) b * W] + W);
         });
+    if (class_order && ix->tune.class_order == 1) {
+        // worth it only when classes are groups: with (nearly) one mask per document — random RBAC — there are no runs to gain,
+        // and the tensor engine's sampling pass (every S-th tile) would no longer see a uniform sample of each user's rows
+        // (C2 measured 5 % slower).  class_order = 2 forces the order (tests).
+        size_t classes = D ? 1 : 0;
+        for (size_t i = 1; i < D; i++)
+            classes += !std::equal(&mask0[(size_t) doc_order[i] * W], &mask0[(size_t) doc_order[i] * W] + W, &mask0[(size_t) doc_order[i - 1] * W]);
+        if (classes * 4 > D)
+            for (size_t d = 0; d < D; d++) doc_order[d] = (uint32_t) d;
+    }
     ix->doc_ids.resize(D);
     ix->doc_mask.assign(std::max<size_t>(D, 1) * W, 0);
     for (size_t i = 0; i < D; i++) {

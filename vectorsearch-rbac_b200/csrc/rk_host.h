@@ -189,7 +189,7 @@ struct RkTuning {
     int tensor_kp_exact = 28;    // RK_TENSOR_KP_EXACT: nominations beyond k while nomination is EXACT (integer data, the previous batch proved it); < 0 = off
     int tensor_loose = 128;      // RK_TENSOR_LOOSE: entries beyond kp a mid-unit compaction may keep
     int tensor_round_mark = 512; // RK_TENSOR_ROUND_MARK: buffers above this many entries are compacted whenever a compaction round runs (trigger: 768)
-    int class_order = 1;         // RK_CLASS_ORDER: 1 = rk_finalize orders the documents (= the rows) by (role mask, id), 0 = by id (round-2 A/B)
+    int class_order = 1;         // RK_CLASS_ORDER: 1 = rk_finalize orders the documents (= the rows) by (role mask, id) when masks repeat (at least 4 documents per distinct mask on average), 2 = always, 0 = by id
     int tensor_kp_extra = 0;     // RK_TENSOR_KP_EXTRA: added to the nominations per query (kp = max(2k, k + 128) + ...; at most 512)
     int tensor_kp_bf16 = 64;     // RK_TENSOR_KP_BF16: added on top when the nomination runs in bf16 (C2: 9 refused queries per 1000 -> 1)
     int tensor_bf16 = -1;        // RK_TENSOR_BF16: -1 = bf16 on the CTA-pair kernel while the proof accepts it, 0 = TF32 nomination, 1 = bf16 always
