@@ -705,6 +705,10 @@ def run_b200(args, wl_key, env, steps, cpu_budget_s, leg=False):
             rf["dram_frac"] = rf["dram_GBps"] / rf["peak"]
             if algo:
                 rf["l2_share"] = max(0.0, 1.0 - tr / float(algo))
+        if rf.get("bound") == "hbm" and rf.get("frac", 0) > 1.0:
+            rf["note"] = ("algorithmic bytes / time is above the HBM peak because part of the algorithmic bytes is served from L2 "
+                          "(queries of one document class stream the same contiguous rows at the same time): dram_frac is the "
+                          "DRAM-based fraction, l2_share the part that did not come from DRAM")
         return rf
 
     def roofline_of(r, eng_name):
