@@ -113,7 +113,10 @@ int rk_abi_version(void);
  * "tensor_sample", "tensor_sdiv", "tensor_smin", "tensor_tpu", "tensor_host_timing", "ivf_seg_factor",
  * "ivf_probe_single", "ivf_assign_tc" (1 = k-means / build assignment on the tensor cores, 0 = fp32 kernel), "ivf_kmeanspp" (1 = k-means++ seeding,
  * 0 = first sampled rows), "ivf_kmeans_iters", "ivf_sample_identity", "single_fused",
- * "single_zero_copy".  Defaults come from the RK_* environment variables of the same names
+ * "single_zero_copy", "class_order" (before rk_finalize: 1 = order the documents, and with them the rows, by (role mask, id)
+ * when role masks repeat, 2 = always, 0 = by id), "tensor_kp_exact" (nominations beyond k while nomination is exact, < 0 = off),
+ * "tensor_round_mark" (buffers above this many entries are compacted in every compaction round), "tensor_loose",
+ * "tensor_kp_extra", "tensor_kp_bf16", "tensor_qtau", "seg_cost_x10".  Defaults come from the RK_* environment variables of the same names
  * (upper case), which are read once, in rk_open — never on the per-call path. */
 int rk_set_option(rk_index *ix, const char *name, int64_t value);
 
