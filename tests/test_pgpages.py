@@ -112,3 +112,73 @@ def test_corrupt_or_foreign_pages_are_errors_not_wild_reads():
             vr.IvfflatPages(bad)
         assert msg in str(e.value), (msg, str(e.value))
     vr.IvfflatPages(rel).close()                                    # the untouched file still reads
+
+
+def test_random_corruption_never_reads_outside_the_relation():
+    """Fuzz: thousands of random byte / field mutations of a valid relation.  Every outcome must be an RkError or a successful
+    parse whose outputs can be read back — never a crash (the reader bounds-checks every offset it follows)."""
+    import vectorsearch_rbac_b200 as vr
+    rel, centers, tuples = _make(24, 5, lambda l: (0, 40, 333)[l % 3], late=50)
+    rng = np.random.default_rng(123)
+    B = pg.BLCKSZ
+    nblk = len(rel) // B
+    ok = bad = 0
+    for it in range(3000):
+        b = bytearray(rel)
+        for _ in range(int(rng.integers(1, 4))):
+            blk = int(rng.integers(0, nblk))
+            kind = int(rng.integers(0, 5))
+            if kind == 0:                                        # a header field
+                off = blk * B + int(rng.choice([12, 14, 16, 18]))
+                struct.pack_into("<H", b, off, int(rng.integers(0, 65536)))
+            elif kind == 1:                                      # a line pointer
+                off = blk * B + pg.HDR + 4 * int(rng.integers(0, 120))
+                struct.pack_into("<I", b, off, int(rng.integers(0, 1 << 32)))
+            elif kind == 2:                                      # the special space (next block, page id)
+                off = blk * B + B - 8 + int(rng.integers(0, 7))
+                b[off] = int(rng.integers(0, 256))
+            elif kind == 3:                                      # tuple / datum headers somewhere in the item area
+                off = blk * B + int(rng.integers(pg.HDR, B - 8))
+                b[off] = int(rng.integers(0, 256))
+            else:                                                # a burst of random bytes
+                off = blk * B + int(rng.integers(0, B - 16))
+                b[off:off + 16] = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+        try:
+            p = vr.IvfflatPages(bytes(b))
+        except vr.RkError:
+            bad += 1
+            continue
+        c, ls, rl, x, tid = p.read()
+        assert c.shape == (p.lists, p.dim) and len(tid) == p.tuples == ls[-1] and x.shape == (p.tuples, p.dim)
+        p.close()
+        ok += 1
+    assert bad > 300 and ok > 0
+
+
+def test_reader_under_address_and_ub_sanitizers(tmp_path):
+    """The reader is host code: compile csrc/rk_pgpage.cu alone with g++ -fsanitize=address,undefined (tests/pgpage_asan/
+    harness.cpp) and feed it thousands of mutated relations held in exact-size heap blocks — a read one byte outside the relation,
+    a misaligned access or an overflow would abort the run."""
+    import os
+    import shutil
+    import subprocess
+    gxx = shutil.which("g++")
+    if not gxx:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "harness")
+    cmd = [gxx, "-std=c++17", "-g", "-O1", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-fno-omit-frame-pointer",
+           "-x", "c++", "-I" + os.path.join(root, "vectorsearch-rbac_b200", "csrc"), "-I" + os.path.join(root, "include"),
+           "-I/usr/local/cuda/include", os.path.join(root, "tests", "pgpage_asan", "harness.cpp"), "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0 and "sanitize" in r.stderr and "cannot find" in r.stderr:
+        pytest.skip("sanitizer runtime not installed")
+    assert r.returncode == 0, r.stderr[-2000:]
+    for dim, lists, short in ((24, 5, None), (128, 12, None), (3, 2, False)):
+        rel, _, _ = _make(dim, lists, lambda l: (0, 40, 333)[l % 3], short=short, late=30)
+        path = tmp_path / f"rel_{dim}.bin"
+        path.write_bytes(rel)
+        run = subprocess.run([exe, str(path), "4000"], capture_output=True, text=True, env=dict(os.environ, ASAN_OPTIONS="detect_leaks=1"))
+        assert run.returncode == 0, (run.stdout[-500:], run.stderr[-3000:])
+        ok, bad = [int(x) for x in run.stdout.split()[1::2]]
+        assert ok > 0 and bad > 0
